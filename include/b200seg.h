@@ -1,0 +1,175 @@
+/* b200seg.h — C ABI of libb200seg.so, the sm_100a (B200) implementation of the pytorch_segmentation hot path.
+ *
+ * Plain pointers and sizes only; every call enqueues work on the CUDA stream it is given and returns
+ * immediately (0 = OK, non-zero = error, text via b200seg_last_error()).  All device buffers are owned by the
+ * caller; the library allocates nothing on the device.  There is no CPU and no cuDNN fallback: an
+ * unsupported shape is an error.
+ *
+ * Data layout: activations are NHWC bf16; a `b200seg_act`-style triple (ptr, c_total, c_offset) addresses a
+ * channel slice of a wider buffer so producers write straight into concat buffers (replaces torch.cat at
+ * reference models/aspp.py:36, models/deeplabv3plus.py:38, models/unet.py:34,40,46).
+ *
+ * Each entry point cites the reference call it replaces (paths relative to the reference root).
+ */
+#ifndef B200SEG_H
+#define B200SEG_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* b200seg_stream_t; /* a cudaStream_t */
+
+#define B200SEG_MAX_CONV_SRC 4
+
+/* ---- housekeeping -------------------------------------------------------------------------------------- */
+const char* b200seg_last_error(void);
+int b200seg_version(void);
+/* fills SM count and compute capability of the current device; fails if it is not sm_100 */
+int b200seg_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---- layout / packing ---------------------------------------------------------------------------------- */
+/* fp32 NCHW -> bf16 NHWC slice, and back (gradients).  Boundary of the drop-in forward(x: N x C x H x W)
+ * (models/deeplabv3plus.py:28, models/unet.py:27). */
+int b200seg_nchw_to_nhwc(const float* src, void* dst, int n, int c, int h, int w, int dst_c_total, int dst_c_offset,
+                         b200seg_stream_t st);
+int b200seg_nhwc_to_nchw(const void* src, float* dst, int n, int c, int h, int w, int src_c_total, int src_c_offset,
+                         b200seg_stream_t st);
+/* fp32 OIHW conv weight (nn.Conv2d.weight inside ConvNormAct / cls_conv) -> two bf16 packings:
+ *   w_fprop [r*s][k_rows][c]           (tap-major, K-major over input channels)
+ *   w_dgrad [r*s flipped][c_rows][k]   (taps mirrored, in/out channels swapped) — either may be NULL.
+ * k_rows >= k and c_rows >= c are zero padded. */
+int b200seg_pack_weights(const float* w_oihw, int k, int c, int r, int s, void* w_fprop, int k_rows, void* w_dgrad,
+                         int c_rows, b200seg_stream_t st);
+
+/* ---- convolution: tcgen05 implicit GEMM ------------------------------------------------------------------ */
+/* One input of a stride-1 "same" convolution: activation slice + packed weights + filter geometry. */
+typedef struct b200seg_conv_src {
+    const void* x;        /* bf16 NHWC */
+    int32_t x_c_total;    /* channels per pixel of the buffer */
+    int32_t x_c_offset;   /* first channel of the slice (multiple of 8) */
+    int32_t c;            /* channels in the slice (multiple of 8) */
+    const void* w;        /* packed bf16 [r*s][w_rows][c] from b200seg_pack_weights */
+    int32_t w_rows;       /* rows per tap in the packed weight (>= output channels) */
+    int32_t r, s;         /* filter taps: 1x1 or 3x3 */
+    int32_t dil;          /* dilation; padding is ((r-1)/2)*dil */
+} b200seg_conv_src;
+
+typedef struct b200seg_conv_out {
+    void* y;              /* bf16 (or fp32 when out_fp32) NHWC */
+    int32_t y_c_total;
+    int32_t y_c_offset;
+    int32_t k;            /* output channels stored (multiple of 8) */
+    int32_t out_fp32;
+    const float* scale;   /* per-channel multiplier or NULL (eval-mode BN folded: gamma/sqrt(var+eps)) */
+    const float* bias;    /* per-channel addend or NULL (BN shift, or nn.Conv2d bias) — length >= k */
+    int32_t relu;
+} b200seg_conv_out;
+
+/* y = act(scale * sum_src conv(x_src, w_src) + bias).
+ * Replaces nn.Conv2d inside ConvNormAct (models/aspp.py:12,27,29,30; models/deeplabv3plus.py:20;
+ * models/unet.py:19-21) and cls_conv (models/deeplabv3plus.py:22,39; models/unet.py:23,51).  With w packed by
+ * the dgrad packing and x = dy this is the data gradient; several sources accumulate in TMEM, which is how
+ * the five ASPP branches' gradients w.r.t. the shared input are summed without extra passes. */
+int b200seg_conv_fprop(int n, int h, int w, int n_src, const b200seg_conv_src* src, const b200seg_conv_out* out,
+                       b200seg_stream_t st);
+/* Same kernel; separate symbol so call sites say which autograd edge they are (conv backward-data). */
+int b200seg_conv_dgrad(int n, int h, int w, int n_src, const b200seg_conv_src* src, const b200seg_conv_out* out,
+                       b200seg_stream_t st);
+
+typedef struct b200seg_wgrad_desc {
+    int32_t n, h, w;
+    const void* dy;       /* bf16 NHWC gradient of the conv output */
+    int32_t dy_c_total, dy_c_offset, k;   /* k: channels in the dy slice (multiple of 8) */
+    const void* x;        /* bf16 NHWC conv input */
+    int32_t x_c_total, x_c_offset, c;
+    int32_t r, s, dil;
+    float* dw;            /* fp32 OIHW [k_out][c][r][s] */
+    int32_t k_out;        /* logical output channels (<= k) */
+    int32_t accumulate;   /* dw += result instead of dw = result */
+    void* workspace;
+    size_t workspace_bytes;
+} b200seg_wgrad_desc;
+
+size_t b200seg_conv_wgrad_workspace(const b200seg_wgrad_desc* d);
+/* dW[k][c][r][s] = sum_pixels dy[p][k] * x[p + tap][c]  (conv backward-weights of the same convs). */
+int b200seg_conv_wgrad(const b200seg_wgrad_desc* d, b200seg_stream_t st);
+
+/* ---- BatchNorm (train mode) around the conv -------------------------------------------------------------- */
+/* Per-channel sum and sum of squares of a bf16 NHWC slice into stats[2*c] (fp32; zeroed by the call).
+ * nn.BatchNorm2d inside ConvNormAct, training statistics. */
+int b200seg_bn_stats(const void* x, int x_c_total, int x_c_offset, int c, int64_t pixels, float* stats,
+                     b200seg_stream_t st);
+/* stats -> scale/shift for the apply pass, saved mean / inv-std for backward, running-stat update
+ * (momentum, unbiased variance) exactly as nn.BatchNorm2d. */
+int b200seg_bn_finalize(const float* stats, int c, int64_t count, const float* gamma, const float* beta, float eps,
+                        float momentum, float* running_mean, float* running_var, float* scale, float* shift,
+                        float* save_mean, float* save_invstd, b200seg_stream_t st);
+/* y = relu?(x*scale + shift) from one NHWC slice into another (BN apply + nn.ReLU + concat placement). */
+int b200seg_bn_apply(const void* x, int x_c_total, int x_c_offset, void* y, int y_c_total, int y_c_offset, int c,
+                     int64_t pixels, const float* scale, const float* shift, int relu, b200seg_stream_t st);
+/* Backward of y = relu?(gamma*(x-mean)*invstd + beta): pass 1 reduces sum(dz), sum(dz*xhat) into red[2*c]
+ * (dz = dy masked by y > 0), pass 2 writes dx and dgamma/dbeta. */
+int b200seg_bn_bwd_reduce(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total,
+                          int x_c_offset, int c, int64_t pixels, const float* scale, const float* shift,
+                          const float* save_mean, const float* save_invstd, int relu, float* red,
+                          b200seg_stream_t st);
+int b200seg_bn_bwd_apply(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total,
+                         int x_c_offset, void* dx, int dx_c_total, int dx_c_offset, int c, int64_t pixels,
+                         const float* gamma, const float* scale, const float* shift, const float* save_mean,
+                         const float* save_invstd, int relu, const float* red, float* dgamma, float* dbeta,
+                         int accumulate_param_grads, b200seg_stream_t st);
+
+/* ---- resampling ------------------------------------------------------------------------------------------ */
+/* Bilinear resize of an NHWC bf16 slice into another slice (F.interpolate(..., mode='bilinear') +
+ * torch.cat placement: models/deeplabv3plus.py:34-38, models/unet.py:30-50). */
+int b200seg_upsample_fwd(const void* x, int x_c_total, int x_c_offset, int n, int h, int w, void* y, int y_c_total,
+                         int y_c_offset, int oh, int ow, int c, int align_corners, b200seg_stream_t st);
+/* Its adjoint: dx[src] = sum over the destination pixels that read it (gather form, no atomics). */
+int b200seg_upsample_bwd(const void* dy, int dy_c_total, int dy_c_offset, int n, int oh, int ow, void* dx,
+                         int dx_c_total, int dx_c_offset, int h, int w, int c, int align_corners,
+                         b200seg_stream_t st);
+/* nn.AdaptiveAvgPool2d(1) (models/aspp.py:11): mean over H*W of an NHWC slice -> bf16 [n][c]. */
+int b200seg_gap_fwd(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, void* y, b200seg_stream_t st);
+/* Broadcast a per-image vector over H*W into a slice: the 1x1 -> HxW bilinear(align_corners=False) of
+ * models/aspp.py:16-19, and (with scale = 1/HW, accumulate) the backward of the average pool. */
+int b200seg_broadcast_hw(const void* v, int n, int c, float scale, void* y, int y_c_total, int y_c_offset, int hw,
+                         int accumulate, b200seg_stream_t st);
+/* Sum an NHWC slice over H*W -> bf16 [n][c] (backward of the broadcast above). */
+int b200seg_sum_hw(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, void* y, b200seg_stream_t st);
+/* Per-channel sum over all pixels of a bf16 NHWC slice -> fp32 [c] (bias gradient of cls_conv). */
+int b200seg_channel_sum(const void* x, int x_c_total, int x_c_offset, int c, int64_t pixels, float* out,
+                        int accumulate, b200seg_stream_t st);
+
+/* ---- logits, loss, metrics ------------------------------------------------------------------------------- */
+/* Final bilinear(align_corners=True) of the class map, NHWC fp32 [n][h][w][c_total] -> NCHW fp32
+ * [n][nc][oh][ow] (models/deeplabv3plus.py:40-43, models/unet.py:52-55, utils/utils.py:18-20). */
+int b200seg_logits_upsample_fwd(const float* x, int c_total, int n, int h, int w, int nc, float* y, int oh, int ow,
+                                b200seg_stream_t st);
+/* Adjoint: NCHW fp32 gradient -> NHWC bf16 [n][h][w][c_total] (pad channels zero). */
+int b200seg_logits_upsample_bwd(const float* dy, int n, int nc, int oh, int ow, void* dx, int c_total, int h, int w,
+                                b200seg_stream_t st);
+/* nn.CrossEntropyLoss() of utils/utils.py:12,21 on NCHW fp32 logits and int64 targets: accumulates
+ * sum_pixels -log softmax[target] into *loss_sum (fp64; caller zeroes it and divides by the pixel count) and
+ * writes dlogits = (softmax - onehot) * grad_scale when dlogits != NULL.  Targets outside [0, nc) other than
+ * ignore_index set *status = 1. */
+int b200seg_softmax_ce(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
+                       float grad_scale, double* loss_sum, int64_t* valid_count, float* dlogits, int* status,
+                       b200seg_stream_t st);
+/* outputs.max(1)[1] (test.py:31): NCHW fp32 -> int64 [n][hw], lowest index wins ties. */
+int b200seg_argmax(const float* logits, int n, int nc, int64_t hw, int64_t* pred, b200seg_stream_t st);
+/* cm[t*nc + p] += 1 over all pixels — superset of the tp/fn/fp loop at test.py:34-46 (tp = diag,
+ * fn = row sum - diag, fp = column sum - diag).  Labels outside [0, nc) are skipped. */
+int b200seg_confusion(const int64_t* pred, const int64_t* targets, int64_t count, int nc, int64_t* cm,
+                      b200seg_stream_t st);
+/* argmax + confusion in one pass over the logits (never materialises the prediction). */
+int b200seg_argmax_confusion(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t* cm,
+                             b200seg_stream_t st);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SEG_H */

@@ -1,0 +1,367 @@
+// Convolution weight gradient on tcgen05: for every filter tap a GEMM whose reduction runs over pixels.
+//
+//   dW[tap][k][c] = sum over pixels p of dY[p][k] * X[p + tap_offset][c]
+//
+// Both operands are NHWC (channels contiguous, pixels strided), i.e. "MN-major" for this GEMM, which
+// tcgen05.mma consumes directly through MN-major shared-memory descriptors — no transposes are materialised.
+// One pipeline stage = a patch of 64 pixels (bw x bh x bi): TMA loads (64 channels x patch) boxes of the
+// M-side tensor (2 boxes = 128 rows of D) and of the N-side tensor (bn/64 boxes), the X boxes shifted by the
+// tap offset with out-of-bounds pixels zero-filled (that is the padding).  Patches whose shifted window is
+// entirely padding are skipped.  The reduction is split across CTAs (split-K) when taps x tiles alone do not
+// fill the GPU; partials go to a caller-provided fp32 workspace and a second kernel reduces them in a fixed
+// order (deterministic) while scattering into the OIHW fp32 gradient.
+//
+// The M side is whichever of (dY, X) has more channels to tile by 128; the other is the N side (<= 256 per
+// tile).  For cls_conv (21 classes) that puts X's 384 channels on M and the padded 32 classes on N.
+#include "common.cuh"
+#include "ptx.cuh"
+
+#include <string.h>
+
+namespace b200seg {
+namespace {
+
+constexpr int kBM = 128;
+constexpr int kBKP = 64;            // pixels per stage
+constexpr int kMaxBN = 256;
+constexpr int kStages = 4;
+constexpr int kBoxBytes = 64 * kBKP * 2;          // 8 KB: 64 channels x 64 pixels
+constexpr int kABytes = 2 * kBoxBytes;
+constexpr int kBBytesMax = (kMaxBN / 64) * kBoxBytes;
+constexpr int kStageBytes = kABytes + kBBytesMax;
+constexpr int kThreads = 256;
+constexpr int kSmemBytes = kStages * kStageBytes + 256 + 1024;
+
+struct __align__(64) WgradParams {
+    CUtensorMap m_map;     // M-side tensor (channels, W, H, N)
+    CUtensorMap n_map;     // N-side tensor
+    int N, H, W;
+    int R, S, dil;
+    int shift_m;           // 1: the M side is X (gets the tap shift); 0: the N side is X
+    int bw, bh, bi;
+    int patches_x, patches_y, patches;
+    int tiles_m, tiles_n, bn;
+    int splits, patches_per_split;
+    int m_pad, n_pad;      // workspace matrix dims per (split, tap)
+    float* ws;
+};
+
+__device__ __forceinline__ bool patch_in_bounds(const WgradParams& p, int kp, int dy, int dx, int& x0, int& y0, int& n0) {
+    x0 = (kp % p.patches_x) * p.bw;
+    int t = kp / p.patches_x;
+    y0 = (t % p.patches_y) * p.bh;
+    n0 = (t / p.patches_y) * p.bi;
+    return (y0 + dy < p.H) && (y0 + p.bh - 1 + dy >= 0) && (x0 + dx < p.W) && (x0 + p.bw - 1 + dx >= 0);
+}
+
+__global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constant__ WgradParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + kStages;
+    uint64_t* tfull = bars + 2 * kStages;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 1);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    // tile decode: n_tile fastest, then m_tile, tap, split
+    int tile = blockIdx.x;
+    const int n_tile = tile % p.tiles_n;
+    tile /= p.tiles_n;
+    const int m_tile = tile % p.tiles_m;
+    tile /= p.tiles_m;
+    const int taps = p.R * p.S;
+    const int tap = tile % taps;
+    const int split = tile / taps;
+    const int dy = (tap / p.S - p.R / 2) * p.dil;
+    const int dx = (tap % p.S - p.S / 2) * p.dil;
+    const int kp_begin = split * p.patches_per_split;
+    const int kp_end = min(kp_begin + p.patches_per_split, p.patches);
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&p.m_map);
+        tma_prefetch_desc(&p.n_map);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < kStages; ++i) {
+            mbar_init(&full[i], 1);
+            mbar_init(&empty[i], 1);
+        }
+        mbar_init(tfull, 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) {
+        tmem_alloc(tmem_slot, kMaxBN);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int n_boxes = p.bn / 64;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            const uint32_t tx_bytes = kABytes + n_boxes * kBoxBytes;
+            const int mdx = p.shift_m ? dx : 0, mdy = p.shift_m ? dy : 0;
+            const int ndx = p.shift_m ? 0 : dx, ndy = p.shift_m ? 0 : dy;
+            for (int kp = kp_begin; kp < kp_end; ++kp) {
+                int x0, y0, n0;
+                if (!patch_in_bounds(p, kp, dy, dx, x0, y0, n0)) continue;
+                mbar_wait(&empty[stage], phase ^ 1);
+                uint8_t* sa = smem + stage * kStageBytes;
+                mbar_arrive_expect_tx(&full[stage], tx_bytes);
+                for (int b = 0; b < 2; ++b)
+                    tma_load_4d(sa + b * kBoxBytes, &p.m_map, &full[stage], m_tile * kBM + b * 64, x0 + mdx, y0 + mdy, n0);
+                for (int b = 0; b < n_boxes; ++b)
+                    tma_load_4d(sa + kABytes + b * kBoxBytes, &p.n_map, &full[stage], n_tile * p.bn + b * 64, x0 + ndx,
+                                y0 + ndy, n0);
+                if (++stage == kStages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_bf16(kBM, p.bn, 1, 1);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int kp = kp_begin; kp < kp_end; ++kp) {
+                int x0, y0, n0;
+                if (!patch_in_bounds(p, kp, dy, dx, x0, y0, n0)) continue;
+                mbar_wait(&full[stage], phase);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + stage * kStageBytes);
+#pragma unroll
+                for (int k = 0; k < kBKP / 16; ++k) {
+                    // 16 pixels (K) = 16 rows of 128 B; 64-channel chunks are one 8 KB box apart (LBO),
+                    // 8-pixel groups 1 KB apart (SBO)
+                    const uint64_t a_desc = umma_smem_desc(sa + k * 2048, kBoxBytes, 1024);
+                    const uint64_t b_desc = umma_smem_desc(sa + kABytes + k * 2048, kBoxBytes, 1024);
+                    tc_mma_f16(tmem_base, a_desc, b_desc, idesc, (it | k) != 0);
+                }
+                tc_commit(&empty[stage]);
+                ++it;
+                if (++stage == kStages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+            if (it > 0)
+                tc_commit(tfull);
+            else
+                mbar_arrive(tfull);
+        }
+    } else if (warp >= 4) {
+        // any work at all for this (tap, split)?  (uniform across the CTA)
+        bool any = false;
+        for (int kp = kp_begin; kp < kp_end && !any; ++kp) {
+            int x0, y0, n0;
+            any = patch_in_bounds(p, kp, dy, dx, x0, y0, n0);
+        }
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        mbar_wait(tfull, 0);
+        tc_fence_after();
+        float* dst = p.ws + ((static_cast<size_t>(split) * taps + tap) * p.m_pad + (m_tile * kBM + row)) * p.n_pad +
+                     n_tile * p.bn;
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+        for (int ch = 0; ch < p.bn; ch += 32) {
+            uint32_t v[32];
+            if (any) {
+                tmem_ld_32x32(taddr + ch, v);
+                tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = 0;
+            }
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<uint4*>(dst + ch + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kMaxBN);
+    }
+}
+
+// dw[k][c][r][s] (+)= sum_split ws[split][tap][m][n], (m, n) = (k, c) or (c, k)
+__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int k_out, int c, int taps,
+                                    int splits, int m_pad, int n_pad, int m_is_c, int accumulate) {
+    const long long total = static_cast<long long>(k_out) * c * taps;
+    const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    if (i >= total) return;
+    // thread index enumerates the workspace-contiguous order (tap, m, n) so reads coalesce
+    const int n_dim = m_is_c ? k_out : c;
+    const int m_dim = m_is_c ? c : k_out;
+    const int n = static_cast<int>(i % n_dim);
+    const int m = static_cast<int>((i / n_dim) % m_dim);
+    const int tap = static_cast<int>(i / (static_cast<long long>(n_dim) * m_dim));
+    const size_t plane = static_cast<size_t>(m_pad) * n_pad;
+    const float* src = ws + (static_cast<size_t>(tap) * m_pad + m) * n_pad + n;
+    float acc = 0.f;
+    for (int s = 0; s < splits; ++s) acc += src[static_cast<size_t>(s) * taps * plane];
+    const int kk = m_is_c ? n : m;
+    const int cc = m_is_c ? m : n;
+    float* d = dw + (static_cast<size_t>(kk) * c + cc) * taps + tap;
+    *d = accumulate ? (*d + acc) : acc;
+}
+
+struct WgradPlan {
+    int shift_m, bw, bh, bi, patches_x, patches_y, patches_i, tiles_m, tiles_n, bn, splits, pps, m_pad, n_pad;
+    size_t ws_bytes;
+};
+
+int plan_wgrad(const b200seg_wgrad_desc* d, WgradPlan* pl) {
+    B200SEG_CHECK(d && d->dy && d->x && d->dw, "wgrad: null pointer");
+    B200SEG_CHECK(d->n > 0 && d->h > 0 && d->w > 0, "wgrad: bad shape");
+    B200SEG_CHECK((d->r == 1 && d->s == 1) || (d->r == 3 && d->s == 3), "wgrad: only 1x1 and 3x3 filters");
+    B200SEG_CHECK(d->k % 8 == 0 && d->dy_c_offset % 8 == 0 && d->dy_c_total % 8 == 0 && d->c % 8 == 0 &&
+                      d->x_c_offset % 8 == 0 && d->x_c_total % 8 == 0,
+                  "wgrad: channel counts/offsets must be multiples of 8");
+    B200SEG_CHECK(d->k_out > 0 && d->k_out <= d->k, "wgrad: k_out %d vs k %d", d->k_out, d->k);
+    // M side = the tensor with more channels
+    pl->shift_m = d->c > d->k ? 1 : 0;
+    const int m_ch = pl->shift_m ? d->c : d->k;
+    const int n_ch = pl->shift_m ? d->k : d->c;
+    pl->tiles_m = ceil_div(m_ch, kBM);
+    pl->tiles_n = ceil_div(n_ch, kMaxBN);
+    pl->bn = round_up(ceil_div(n_ch, pl->tiles_n), 64);
+    pl->m_pad = pl->tiles_m * kBM;
+    pl->n_pad = pl->tiles_n * pl->bn;
+    // 64-pixel patch with the fewest non-padding (tap, patch) pairs
+    long long best = -1;
+    for (int bi = 1; bi <= 64; bi *= 2) {
+        for (int bw = 1; bw * bi <= 64; bw *= 2) {
+            const int bh = 64 / (bw * bi);
+            const int px = ceil_div(d->w, bw), py = ceil_div(d->h, bh), pi = ceil_div(d->n, bi);
+            long long cost = 0;
+            for (int y = 0; y < py; ++y)
+                for (int x = 0; x < px; ++x)
+                    for (int r = 0; r < d->r; ++r)
+                        for (int s = 0; s < d->s; ++s) {
+                            const int dy = (r - d->r / 2) * d->dil, dx = (s - d->s / 2) * d->dil;
+                            const int y0 = y * bh, x0 = x * bw;
+                            if ((y0 + dy < d->h) && (y0 + bh - 1 + dy >= 0) && (x0 + dx < d->w) && (x0 + bw - 1 + dx >= 0))
+                                ++cost;
+                        }
+            cost *= pi;
+            if (best < 0 || cost < best || (cost == best && bw > pl->bw)) {
+                best = cost;
+                pl->bw = bw;
+                pl->bh = bh;
+                pl->bi = bi;
+                pl->patches_x = px;
+                pl->patches_y = py;
+                pl->patches_i = pi;
+            }
+        }
+    }
+    B200SEG_CHECK(best > 0, "wgrad: no patch shape");
+    const int patches = pl->patches_x * pl->patches_y * pl->patches_i;
+    const int base_tiles = d->r * d->s * pl->tiles_m * pl->tiles_n;
+    int sms = sm_count();
+    if (sms <= 0) sms = 148;
+    int splits = sms / base_tiles;
+    if (splits < 1) splits = 1;
+    const int max_splits = patches / 8 > 0 ? patches / 8 : 1;
+    if (splits > max_splits) splits = max_splits;
+    pl->pps = ceil_div(patches, splits);
+    pl->splits = ceil_div(patches, pl->pps);
+    pl->ws_bytes = static_cast<size_t>(pl->splits) * d->r * d->s * pl->m_pad * pl->n_pad * sizeof(float);
+    return 0;
+}
+
+}  // namespace
+}  // namespace b200seg
+
+extern "C" {
+
+size_t b200seg_conv_wgrad_workspace(const b200seg_wgrad_desc* d) {
+    b200seg::WgradPlan pl;
+    memset(&pl, 0, sizeof(pl));
+    if (b200seg::plan_wgrad(d, &pl)) return 0;
+    return pl.ws_bytes;
+}
+
+int b200seg_conv_wgrad(const b200seg_wgrad_desc* d, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    WgradPlan pl;
+    memset(&pl, 0, sizeof(pl));
+    if (plan_wgrad(d, &pl)) return 1;
+    B200SEG_CHECK(d->workspace && d->workspace_bytes >= pl.ws_bytes, "wgrad: workspace of %zu bytes needed, %zu given",
+                  pl.ws_bytes, d->workspace_bytes);
+    B200SEG_CHECK((reinterpret_cast<uintptr_t>(d->workspace) & 15) == 0, "wgrad: workspace not 16-byte aligned");
+
+    WgradParams p;
+    memset(&p, 0, sizeof(p));
+    p.N = d->n;
+    p.H = d->h;
+    p.W = d->w;
+    p.R = d->r;
+    p.S = d->s;
+    p.dil = d->dil;
+    p.shift_m = pl.shift_m;
+    p.bw = pl.bw;
+    p.bh = pl.bh;
+    p.bi = pl.bi;
+    p.patches_x = pl.patches_x;
+    p.patches_y = pl.patches_y;
+    p.patches = pl.patches_x * pl.patches_y * pl.patches_i;
+    p.tiles_m = pl.tiles_m;
+    p.tiles_n = pl.tiles_n;
+    p.bn = pl.bn;
+    p.splits = pl.splits;
+    p.patches_per_split = pl.pps;
+    p.m_pad = pl.m_pad;
+    p.n_pad = pl.n_pad;
+    p.ws = static_cast<float*>(d->workspace);
+
+    const uint32_t box[4] = {64, (uint32_t)pl.bw, (uint32_t)pl.bh, (uint32_t)pl.bi};
+    const uint64_t xdims[4] = {(uint64_t)d->c, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n};
+    const uint64_t xstr[3] = {(uint64_t)d->x_c_total * 2, (uint64_t)d->w * d->x_c_total * 2,
+                              (uint64_t)d->h * d->w * d->x_c_total * 2};
+    const uint64_t ydims[4] = {(uint64_t)d->k, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n};
+    const uint64_t ystr[3] = {(uint64_t)d->dy_c_total * 2, (uint64_t)d->w * d->dy_c_total * 2,
+                              (uint64_t)d->h * d->w * d->dy_c_total * 2};
+    const char* xbase = static_cast<const char*>(d->x) + (size_t)d->x_c_offset * 2;
+    const char* ybase = static_cast<const char*>(d->dy) + (size_t)d->dy_c_offset * 2;
+    if (pl.shift_m) {
+        if (encode_tmap_bf16(&p.m_map, xbase, 4, xdims, xstr, box)) return 1;
+        if (encode_tmap_bf16(&p.n_map, ybase, 4, ydims, ystr, box)) return 1;
+    } else {
+        if (encode_tmap_bf16(&p.m_map, ybase, 4, ydims, ystr, box)) return 1;
+        if (encode_tmap_bf16(&p.n_map, xbase, 4, xdims, xstr, box)) return 1;
+    }
+
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200SEG_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        attr_set = true;
+    }
+    const int taps = d->r * d->s;
+    const int grid = pl.splits * taps * pl.tiles_m * pl.tiles_n;
+    wgrad_kernel<<<grid, kThreads, kSmemBytes, st>>>(p);
+    B200SEG_LAUNCH_CHECK();
+
+    const long long total = static_cast<long long>(d->k_out) * d->c * taps;
+    const int rb = 256;
+    wgrad_reduce_kernel<<<static_cast<unsigned>((total + rb - 1) / rb), rb, 0, st>>>(
+        p.ws, d->dw, d->k_out, d->c, taps, pl.splits, pl.m_pad, pl.n_pad, pl.shift_m, d->accumulate);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // extern "C"
