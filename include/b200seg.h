@@ -39,11 +39,12 @@ int b200seg_nchw_to_nhwc(const float* src, void* dst, int n, int c, int h, int w
 int b200seg_nhwc_to_nchw(const void* src, float* dst, int n, int c, int h, int w, int src_c_total, int src_c_offset,
                          b200seg_stream_t st);
 /* fp32 OIHW conv weight (nn.Conv2d.weight inside ConvNormAct / cls_conv) -> two bf16 packings:
- *   w_fprop [r*s][k_rows][c]           (tap-major, K-major over input channels)
- *   w_dgrad [r*s flipped][c_rows][k]   (taps mirrored, in/out channels swapped) — either may be NULL.
- * k_rows >= k and c_rows >= c are zero padded. */
+ *   w_fprop [r*s][k_rows][c]                (tap-major, K-major over input channels)
+ *   w_dgrad [r*s flipped][c_rows][k_cols]   (taps mirrored, in/out channels swapped) — either may be NULL.
+ * k_rows >= k, c_rows >= c and k_cols >= k (a multiple of 8: the dgrad reduction runs over the channels of the
+ * padded gradient buffer) are zero padded. */
 int b200seg_pack_weights(const float* w_oihw, int k, int c, int r, int s, void* w_fprop, int k_rows, void* w_dgrad,
-                         int c_rows, b200seg_stream_t st);
+                         int c_rows, int k_cols, b200seg_stream_t st);
 
 /* ---- convolution: tcgen05 implicit GEMM ------------------------------------------------------------------ */
 /* One input of a stride-1 "same" convolution: activation slice + packed weights + filter geometry. */
@@ -67,6 +68,9 @@ typedef struct b200seg_conv_out {
     const float* scale;   /* per-channel multiplier or NULL (eval-mode BN folded: gamma/sqrt(var+eps)) */
     const float* bias;    /* per-channel addend or NULL (BN shift, or nn.Conv2d bias) — length >= k */
     int32_t relu;
+    float* stats;         /* NULL, or fp32 [2*k] zeroed by the caller: the epilogue adds the per-channel sum and sum
+                             of squares of the raw fp32 accumulators (before scale/bias/relu) — the training-mode
+                             nn.BatchNorm2d statistics of ConvNormAct without a second pass over the output */
 } b200seg_conv_out;
 
 /* y = act(scale * sum_src conv(x_src, w_src) + bias).
@@ -111,16 +115,22 @@ int b200seg_bn_finalize(const float* stats, int c, int64_t count, const float* g
 /* y = relu?(x*scale + shift) from one NHWC slice into another (BN apply + nn.ReLU + concat placement). */
 int b200seg_bn_apply(const void* x, int x_c_total, int x_c_offset, void* y, int y_c_total, int y_c_offset, int c,
                      int64_t pixels, const float* scale, const float* shift, int relu, b200seg_stream_t st);
+/* eval mode (test.py:16, inference.py:24): scale/shift from the running statistics; feeds the conv epilogue so
+ * Conv+BN+ReLU is one kernel.  save_mean/save_invstd (optional) receive the running mean and 1/sqrt(var+eps). */
+int b200seg_bn_eval_affine(int c, const float* gamma, const float* beta, const float* running_mean,
+                           const float* running_var, float eps, float* scale, float* shift, float* save_mean,
+                           float* save_invstd, b200seg_stream_t st);
 /* Backward of y = relu?(gamma*(x-mean)*invstd + beta): pass 1 reduces sum(dz), sum(dz*xhat) into red[2*c]
- * (dz = dy masked by y > 0), pass 2 writes dx and dgamma/dbeta. */
+ * (dz = dy masked by y > 0), pass 2 writes dx and dgamma/dbeta.  training = 0 treats the statistics as
+ * constants (eval-mode BN): dx = scale * dz. */
 int b200seg_bn_bwd_reduce(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total,
                           int x_c_offset, int c, int64_t pixels, const float* scale, const float* shift,
                           const float* save_mean, const float* save_invstd, int relu, float* red,
                           b200seg_stream_t st);
 int b200seg_bn_bwd_apply(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total,
                          int x_c_offset, void* dx, int dx_c_total, int dx_c_offset, int c, int64_t pixels,
-                         const float* gamma, const float* scale, const float* shift, const float* save_mean,
-                         const float* save_invstd, int relu, const float* red, float* dgamma, float* dbeta,
+                         const float* scale, const float* shift, const float* save_mean, const float* save_invstd,
+                         int relu, int training, const float* red, float* dgamma, float* dbeta,
                          int accumulate_param_grads, b200seg_stream_t st);
 
 /* ---- resampling ------------------------------------------------------------------------------------------ */
@@ -132,26 +142,35 @@ int b200seg_upsample_fwd(const void* x, int x_c_total, int x_c_offset, int n, in
 int b200seg_upsample_bwd(const void* dy, int dy_c_total, int dy_c_offset, int n, int oh, int ow, void* dx,
                          int dx_c_total, int dx_c_offset, int h, int w, int c, int align_corners,
                          b200seg_stream_t st);
-/* nn.AdaptiveAvgPool2d(1) (models/aspp.py:11): mean over H*W of an NHWC slice -> bf16 [n][c]. */
-int b200seg_gap_fwd(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, void* y, b200seg_stream_t st);
+/* nn.AdaptiveAvgPool2d(1) (models/aspp.py:11): mean over H*W of an NHWC slice -> bf16 [n][c].
+ * acc_ws: caller-provided fp32 [n*c] scratch (the H*W range is split across CTAs). */
+int b200seg_gap_fwd(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, float* acc_ws, void* y,
+                    b200seg_stream_t st);
 /* Broadcast a per-image vector over H*W into a slice: the 1x1 -> HxW bilinear(align_corners=False) of
  * models/aspp.py:16-19, and (with scale = 1/HW, accumulate) the backward of the average pool. */
 int b200seg_broadcast_hw(const void* v, int n, int c, float scale, void* y, int y_c_total, int y_c_offset, int hw,
                          int accumulate, b200seg_stream_t st);
 /* Sum an NHWC slice over H*W -> bf16 [n][c] (backward of the broadcast above). */
-int b200seg_sum_hw(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, void* y, b200seg_stream_t st);
+int b200seg_sum_hw(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, float* acc_ws, void* y,
+                   b200seg_stream_t st);
 /* Per-channel sum over all pixels of a bf16 NHWC slice -> fp32 [c] (bias gradient of cls_conv). */
 int b200seg_channel_sum(const void* x, int x_c_total, int x_c_offset, int c, int64_t pixels, float* out,
                         int accumulate, b200seg_stream_t st);
 
 /* ---- logits, loss, metrics ------------------------------------------------------------------------------- */
-/* Final bilinear(align_corners=True) of the class map, NHWC fp32 [n][h][w][c_total] -> NCHW fp32
- * [n][nc][oh][ow] (models/deeplabv3plus.py:40-43, models/unet.py:52-55, utils/utils.py:18-20). */
+/* Final bilinear of the class map, NHWC fp32 [n][h][w][c_total] -> NCHW fp32 [n][nc][oh][ow]
+ * (models/deeplabv3plus.py:40-43, models/unet.py:52-55; align_corners=True there). */
 int b200seg_logits_upsample_fwd(const float* x, int c_total, int n, int h, int w, int nc, float* y, int oh, int ow,
-                                b200seg_stream_t st);
-/* Adjoint: NCHW fp32 gradient -> NHWC bf16 [n][h][w][c_total] (pad channels zero). */
+                                int align_corners, b200seg_stream_t st);
+/* Adjoint: NCHW fp32 gradient -> NHWC bf16 [n][h][w][c_total] (pad channels zero; c_total <= 64). */
 int b200seg_logits_upsample_bwd(const float* dy, int n, int nc, int oh, int ow, void* dx, int c_total, int h, int w,
-                                b200seg_stream_t st);
+                                int align_corners, b200seg_stream_t st);
+/* Bilinear resize of `planes` = N*C fp32 planes and its adjoint: the F.interpolate of utils/utils.py:18-20 when
+ * logits and targets differ in size (identity, and skipped by the caller, when they match). */
+int b200seg_resize_nchw_fwd(const float* x, int64_t planes, int h, int w, float* y, int oh, int ow, int align_corners,
+                            b200seg_stream_t st);
+int b200seg_resize_nchw_bwd(const float* dy, int64_t planes, int oh, int ow, float* dx, int h, int w, int align_corners,
+                            b200seg_stream_t st);
 /* nn.CrossEntropyLoss() of utils/utils.py:12,21 on NCHW fp32 logits and int64 targets: accumulates
  * sum_pixels -log softmax[target] into *loss_sum (fp64; caller zeroes it and divides by the pixel count) and
  * writes dlogits = (softmax - onehot) * grad_scale when dlogits != NULL.  Targets outside [0, nc) other than

@@ -1,0 +1,370 @@
+// Training-mode BatchNorm around the tcgen05 convs: per-channel statistics, scale/shift finalisation with the
+// running-stat update, the normalise(+ReLU) apply pass that also places the result in a concat slice, and the
+// two-pass backward.  All HBM-bound: 128-bit loads of 8 bf16 channels per thread, consecutive threads on
+// consecutive channel groups of one pixel (coalesced over the NHWC row), fp32 math, one atomic per channel per
+// block for the reductions.
+#include "common.cuh"
+#include "vec.cuh"
+
+namespace b200seg {
+namespace {
+
+constexpr int kRedThreads = 256;
+
+// Geometry of a column reduction over a [pixels][c] slice: G = c/8 channel groups; a block covers
+// `gpb` groups (<= 256) and 256/gpb pixel rows per iteration.
+struct ColGeom {
+    int groups, gpb, rows, gy;
+    int64_t pixels_per_block;
+    int gx;
+};
+
+ColGeom col_geom(int c, int64_t pixels) {
+    ColGeom g;
+    g.groups = c / 8;
+    g.gpb = g.groups < kRedThreads ? g.groups : kRedThreads;
+    g.rows = kRedThreads / g.gpb;
+    g.gy = ceil_div(g.groups, g.gpb);
+    int sms = sm_count();
+    if (sms <= 0) sms = 148;
+    int64_t want = static_cast<int64_t>(sms) * 8 / g.gy;
+    if (want < 1) want = 1;
+    int64_t ppb = ceil_div64(pixels, want);
+    const int64_t min_ppb = static_cast<int64_t>(g.rows) * 4;
+    if (ppb < min_ppb) ppb = min_ppb;
+    ppb = ceil_div64(ppb, g.rows) * g.rows;
+    g.pixels_per_block = ppb;
+    g.gx = static_cast<int>(ceil_div64(pixels, ppb));
+    return g;
+}
+
+// Shared tail of the column reductions: NV values per thread, reduce over the `rows` pixel lanes of the block
+// and add to out[v * c + channel].
+template <int NV>
+__device__ __forceinline__ void block_col_reduce(float (&acc)[NV][8], int g_local, int row, int gpb, int rows, int group,
+                                                 int groups, int c, float* out) {
+    __shared__ float red[kRedThreads * 8];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+        __syncthreads();
+        if (row < rows) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) red[(row * gpb + g_local) * 8 + j] = acc[v][j];
+        }
+        __syncthreads();
+        // thread t < gpb*8 sums channel (t) over rows
+        for (int t = threadIdx.x; t < gpb * 8; t += blockDim.x) {
+            const int gl = t >> 3, j = t & 7;
+            const int gg = blockIdx.y * gpb + gl;
+            if (gg < groups) {
+                float s = 0.f;
+                for (int r = 0; r < rows; ++r) s += red[(r * gpb + gl) * 8 + j];
+                atomicAdd(out + v * c + gg * 8 + j, s);
+            }
+        }
+    }
+    (void)group;
+}
+
+__global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int c_total, int c_off,
+                                                                int c, int64_t pixels, int64_t ppb, int gpb, int rows,
+                                                                float* __restrict__ stats) {
+    const int groups = c >> 3;
+    const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
+    const int group = blockIdx.y * gpb + g_local;
+    float acc[2][8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[0][j] = acc[1][j] = 0.f;
+    if (row < rows && group < groups) {
+        const int64_t p0 = blockIdx.x * ppb;
+        const int64_t p1 = min(p0 + ppb, pixels);
+        const __nv_bfloat16* base = x + c_off + group * 8;
+        for (int64_t p = p0 + row; p < p1; p += rows) {
+            float f[8];
+            unpack8(ldg128(base + p * c_total), f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                acc[0][j] += f[j];
+                acc[1][j] = fmaf(f[j], f[j], acc[1][j]);
+            }
+        }
+    }
+    block_col_reduce<2>(acc, g_local, row, gpb, rows, group, groups, c, stats);
+}
+
+// optional second output: plain per-channel sum only
+__global__ void __launch_bounds__(kRedThreads) channel_sum_kernel(const __nv_bfloat16* __restrict__ x, int c_total,
+                                                                   int c_off, int c, int64_t pixels, int64_t ppb, int gpb,
+                                                                   int rows, float* __restrict__ out) {
+    const int groups = c >> 3;
+    const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
+    const int group = blockIdx.y * gpb + g_local;
+    float acc[1][8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[0][j] = 0.f;
+    if (row < rows && group < groups) {
+        const int64_t p0 = blockIdx.x * ppb;
+        const int64_t p1 = min(p0 + ppb, pixels);
+        const __nv_bfloat16* base = x + c_off + group * 8;
+        for (int64_t p = p0 + row; p < p1; p += rows) {
+            float f[8];
+            unpack8(ldg128(base + p * c_total), f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[0][j] += f[j];
+        }
+    }
+    block_col_reduce<1>(acc, g_local, row, gpb, rows, group, groups, c, out);
+}
+
+__global__ void bn_finalize_kernel(const float* __restrict__ stats, int c, float inv_count, float unbias,
+                                   const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                                   float momentum, float* running_mean, float* running_var, float* scale, float* shift,
+                                   float* save_mean, float* save_invstd) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= c) return;
+    const float mean = stats[i] * inv_count;
+    float var = fmaf(-mean, mean, stats[c + i] * inv_count);
+    var = fmaxf(var, 0.f);
+    const float invstd = rsqrtf(var + eps);
+    const float g = gamma ? gamma[i] : 1.f, b = beta ? beta[i] : 0.f;
+    const float sc = g * invstd;
+    scale[i] = sc;
+    shift[i] = fmaf(-mean, sc, b);
+    if (save_mean) save_mean[i] = mean;
+    if (save_invstd) save_invstd[i] = invstd;
+    if (running_mean) running_mean[i] = fmaf(momentum, mean - running_mean[i], running_mean[i]);
+    if (running_var) running_var[i] = fmaf(momentum, var * unbias - running_var[i], running_var[i]);
+}
+
+// eval mode: scale/shift from the running statistics
+__global__ void bn_eval_affine_kernel(int c, const float* __restrict__ gamma, const float* __restrict__ beta,
+                                      const float* __restrict__ running_mean, const float* __restrict__ running_var,
+                                      float eps, float* scale, float* shift, float* save_mean, float* save_invstd) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= c) return;
+    const float invstd = rsqrtf(running_var[i] + eps);
+    const float sc = (gamma ? gamma[i] : 1.f) * invstd;
+    scale[i] = sc;
+    shift[i] = fmaf(-running_mean[i], sc, beta ? beta[i] : 0.f);
+    if (save_mean) save_mean[i] = running_mean[i];
+    if (save_invstd) save_invstd[i] = invstd;
+}
+
+__global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __restrict__ x, int x_ct, int x_off,
+                                                        __nv_bfloat16* __restrict__ y, int y_ct, int y_off, int groups,
+                                                        int64_t total, const float* __restrict__ scale,
+                                                        const float* __restrict__ shift, int relu) {
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int g = static_cast<int>(i % groups);
+        const int64_t p = i / groups;
+        float f[8], sc[8], sh[8];
+        unpack8(ldg128(x + p * x_ct + x_off + g * 8), f);
+        load8f(scale + g * 8, sc);
+        load8f(shift + g * 8, sh);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            f[j] = fmaf(f[j], sc[j], sh[j]);
+            if (relu) f[j] = fmaxf(f[j], 0.f);
+        }
+        st128(y + p * y_ct + y_off + g * 8, pack8(f));
+    }
+}
+
+// red[0..c) = sum dz', red[c..2c) = sum dz' * xhat   with dz' = dy * (y > 0 if relu)
+__global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(
+    const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off, const __nv_bfloat16* __restrict__ x, int x_ct, int x_off,
+    int c, int64_t pixels, int64_t ppb, int gpb, int rows, const float* __restrict__ scale, const float* __restrict__ shift,
+    const float* __restrict__ mean, const float* __restrict__ invstd, int relu, float* __restrict__ red) {
+    const int groups = c >> 3;
+    const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
+    const int group = blockIdx.y * gpb + g_local;
+    float acc[2][8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[0][j] = acc[1][j] = 0.f;
+    if (row < rows && group < groups) {
+        float sc[8], sh[8], mu[8], is[8];
+        load8f(scale + group * 8, sc);
+        load8f(shift + group * 8, sh);
+        load8f(mean + group * 8, mu);
+        load8f(invstd + group * 8, is);
+        const int64_t p0 = blockIdx.x * ppb;
+        const int64_t p1 = min(p0 + ppb, pixels);
+        const __nv_bfloat16* xb = x + x_off + group * 8;
+        const __nv_bfloat16* db = dy + dy_off + group * 8;
+        for (int64_t p = p0 + row; p < p1; p += rows) {
+            float f[8], d[8];
+            unpack8(ldg128(xb + p * x_ct), f);
+            unpack8(ldg128(db + p * dy_ct), d);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float dz = (relu && fmaf(f[j], sc[j], sh[j]) <= 0.f) ? 0.f : d[j];
+                acc[0][j] += dz;
+                acc[1][j] = fmaf(dz, (f[j] - mu[j]) * is[j], acc[1][j]);
+            }
+        }
+    }
+    block_col_reduce<2>(acc, g_local, row, gpb, rows, group, groups, c, red);
+}
+
+// dx = scale * (dz' - red0/M - xhat * red1/M)   (training)   or   scale * dz'   (eval: statistics are constants)
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(
+    const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off, const __nv_bfloat16* __restrict__ x, int x_ct, int x_off,
+    __nv_bfloat16* __restrict__ dx, int dx_ct, int dx_off, int groups, int64_t total, float inv_count,
+    const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
+    const float* __restrict__ invstd, int relu, int training, const float* __restrict__ red, int c) {
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int g = static_cast<int>(i % groups);
+        const int64_t p = i / groups;
+        float f[8], d[8], sc[8], sh[8], mu[8], is[8], r0[8], r1[8];
+        unpack8(ldg128(x + p * x_ct + x_off + g * 8), f);
+        unpack8(ldg128(dy + p * dy_ct + dy_off + g * 8), d);
+        load8f(scale + g * 8, sc);
+        load8f(shift + g * 8, sh);
+        load8f(mean + g * 8, mu);
+        load8f(invstd + g * 8, is);
+        if (training) {
+            load8f(red + g * 8, r0);
+            load8f(red + c + g * 8, r1);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float dz = (relu && fmaf(f[j], sc[j], sh[j]) <= 0.f) ? 0.f : d[j];
+            float v = dz;
+            if (training) v = dz - r0[j] * inv_count - (f[j] - mu[j]) * is[j] * r1[j] * inv_count;
+            f[j] = v * sc[j];
+        }
+        st128(dx + p * dx_ct + dx_off + g * 8, pack8(f));
+    }
+}
+
+// dgamma = red1, dbeta = red0 (optionally accumulated into existing .grad)
+__global__ void bn_param_grad_kernel(const float* __restrict__ red, int c, float* dgamma, float* dbeta, int accumulate) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= c) return;
+    if (dbeta) dbeta[i] = accumulate ? dbeta[i] + red[i] : red[i];
+    if (dgamma) dgamma[i] = accumulate ? dgamma[i] + red[c + i] : red[c + i];
+}
+
+}  // namespace
+}  // namespace b200seg
+
+extern "C" {
+
+int b200seg_bn_stats(const void* x, int x_c_total, int x_c_offset, int c, int64_t pixels, float* stats,
+                     b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (check_slice("bn_stats", x, x_c_total, x_c_offset, c)) return 1;
+    B200SEG_CHECK(stats && pixels > 0, "bn_stats: bad arguments");
+    B200SEG_CUDA(cudaMemsetAsync(stats, 0, sizeof(float) * 2 * c, st));
+    const ColGeom g = col_geom(c, pixels);
+    bn_stats_kernel<<<dim3(g.gx, g.gy), kRedThreads, 0, st>>>(static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, c,
+                                                             pixels, g.pixels_per_block, g.gpb, g.rows, stats);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_channel_sum(const void* x, int x_c_total, int x_c_offset, int c, int64_t pixels, float* out, int accumulate,
+                        b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (check_slice("channel_sum", x, x_c_total, x_c_offset, c)) return 1;
+    B200SEG_CHECK(out && pixels > 0, "channel_sum: bad arguments");
+    if (!accumulate) B200SEG_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * c, st));
+    const ColGeom g = col_geom(c, pixels);
+    channel_sum_kernel<<<dim3(g.gx, g.gy), kRedThreads, 0, st>>>(static_cast<const __nv_bfloat16*>(x), x_c_total,
+                                                                x_c_offset, c, pixels, g.pixels_per_block, g.gpb, g.rows,
+                                                                out);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_bn_finalize(const float* stats, int c, int64_t count, const float* gamma, const float* beta, float eps,
+                        float momentum, float* running_mean, float* running_var, float* scale, float* shift,
+                        float* save_mean, float* save_invstd, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(stats && scale && shift && c > 0 && count > 0, "bn_finalize: bad arguments");
+    const float unbias = count > 1 ? static_cast<float>(static_cast<double>(count) / static_cast<double>(count - 1)) : 1.f;
+    bn_finalize_kernel<<<ceil_div(c, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+        stats, c, static_cast<float>(1.0 / static_cast<double>(count)), unbias, gamma, beta, eps, momentum, running_mean,
+        running_var, scale, shift, save_mean, save_invstd);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_bn_eval_affine(int c, const float* gamma, const float* beta, const float* running_mean,
+                           const float* running_var, float eps, float* scale, float* shift, float* save_mean,
+                           float* save_invstd, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(running_mean && running_var && scale && shift && c > 0, "bn_eval_affine: bad arguments");
+    bn_eval_affine_kernel<<<ceil_div(c, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+        c, gamma, beta, running_mean, running_var, eps, scale, shift, save_mean, save_invstd);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_bn_apply(const void* x, int x_c_total, int x_c_offset, void* y, int y_c_total, int y_c_offset, int c,
+                     int64_t pixels, const float* scale, const float* shift, int relu, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    if (check_slice("bn_apply(x)", x, x_c_total, x_c_offset, c)) return 1;
+    if (check_slice("bn_apply(y)", y, y_c_total, y_c_offset, c)) return 1;
+    B200SEG_CHECK(scale && shift && pixels > 0, "bn_apply: bad arguments");
+    const int64_t total = pixels * (c / 8);
+    bn_apply_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset,
+        c / 8, total, scale, shift, relu);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_bn_bwd_reduce(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total, int x_c_offset,
+                          int c, int64_t pixels, const float* scale, const float* shift, const float* save_mean,
+                          const float* save_invstd, int relu, float* red, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (check_slice("bn_bwd_reduce(dy)", dy, dy_c_total, dy_c_offset, c)) return 1;
+    if (check_slice("bn_bwd_reduce(x)", x, x_c_total, x_c_offset, c)) return 1;
+    B200SEG_CHECK(scale && shift && save_mean && save_invstd && red && pixels > 0, "bn_bwd_reduce: bad arguments");
+    B200SEG_CUDA(cudaMemsetAsync(red, 0, sizeof(float) * 2 * c, st));
+    const ColGeom g = col_geom(c, pixels);
+    bn_bwd_reduce_kernel<<<dim3(g.gx, g.gy), kRedThreads, 0, st>>>(
+        static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, static_cast<const __nv_bfloat16*>(x), x_c_total,
+        x_c_offset, c, pixels, g.pixels_per_block, g.gpb, g.rows, scale, shift, save_mean, save_invstd, relu, red);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_bn_bwd_apply(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total, int x_c_offset,
+                         void* dx, int dx_c_total, int dx_c_offset, int c, int64_t pixels, const float* scale,
+                         const float* shift, const float* save_mean, const float* save_invstd, int relu, int training,
+                         const float* red, float* dgamma, float* dbeta, int accumulate_param_grads,
+                         b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (check_slice("bn_bwd_apply(dy)", dy, dy_c_total, dy_c_offset, c)) return 1;
+    if (check_slice("bn_bwd_apply(x)", x, x_c_total, x_c_offset, c)) return 1;
+    if (check_slice("bn_bwd_apply(dx)", dx, dx_c_total, dx_c_offset, c)) return 1;
+    B200SEG_CHECK(scale && shift && save_mean && save_invstd && red && pixels > 0, "bn_bwd_apply: bad arguments");
+    const int64_t total = pixels * (c / 8);
+    bn_bwd_apply_kernel<<<elementwise_grid(total), 256, 0, st>>>(
+        static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, static_cast<const __nv_bfloat16*>(x), x_c_total,
+        x_c_offset, static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, c / 8, total,
+        static_cast<float>(1.0 / static_cast<double>(pixels)), scale, shift, save_mean, save_invstd, relu, training, red, c);
+    B200SEG_LAUNCH_CHECK();
+    if (dgamma || dbeta) {
+        bn_param_grad_kernel<<<ceil_div(c, 128), 128, 0, st>>>(red, c, dgamma, dbeta, accumulate_param_grads);
+        B200SEG_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+}  // extern "C"

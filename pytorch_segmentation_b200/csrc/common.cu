@@ -75,6 +75,24 @@ int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_
     return 0;
 }
 
+int check_slice(const char* what, const void* p, int c_total, int c_off, int c) {
+    B200SEG_CHECK(p != nullptr, "%s: null pointer", what);
+    B200SEG_CHECK(c > 0 && c % 8 == 0 && c_off % 8 == 0 && c_total % 8 == 0 && c_off + c <= c_total,
+                  "%s: bad channel slice (c=%d offset=%d total=%d; all must be multiples of 8)", what, c, c_off, c_total);
+    B200SEG_CHECK((reinterpret_cast<uintptr_t>(p) & 15) == 0, "%s: pointer not 16-byte aligned", what);
+    return 0;
+}
+
+int elementwise_grid(int64_t total) {
+    int sms = sm_count();
+    if (sms <= 0) sms = 148;
+    int64_t blocks = ceil_div64(total, 256);
+    const int64_t cap = static_cast<int64_t>(sms) * 16;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return static_cast<int>(blocks);
+}
+
 }  // namespace b200seg
 
 extern "C" {

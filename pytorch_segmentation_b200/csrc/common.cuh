@@ -35,6 +35,11 @@ int sm_count();   // SMs of the current device (cached), 0 on failure
 int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                      const uint32_t* box);
 
+// validates a bf16 NHWC channel slice (multiples of 8 channels, 16-byte aligned base); 0 = OK
+int check_slice(const char* what, const void* p, int c_total, int c_off, int c);
+// grid size for a 256-thread grid-stride elementwise kernel over `total` items (capped at 16 CTAs per SM)
+int elementwise_grid(int64_t total);
+
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
 inline int round_up(int a, int b) { return ceil_div(a, b) * b; }

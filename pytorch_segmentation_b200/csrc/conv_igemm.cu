@@ -57,6 +57,7 @@ struct __align__(64) IgemmParams {
     const float* scale;
     const float* bias;
     int relu;
+    float* stats;
 };
 
 struct TileCoord {
@@ -214,6 +215,34 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
                 tmem_ld_32x32(taddr + ch, v);
                 tmem_ld_wait();
                 const int k0 = t.n_tile * p.bn + ch;
+                if (p.stats) {
+                    // column sums over this warp's 32 rows by recursive halving: 31 shuffles leave lane j
+                    // holding the total of channel k0 + j (rows outside the image contribute zero)
+                    float s1[32], s2[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float a = valid ? __uint_as_float(v[j]) : 0.f;
+                        s1[j] = a;
+                        s2[j] = a * a;
+                    }
+#pragma unroll
+                    for (int off = 16; off >= 1; off >>= 1) {
+                        const bool upper = (lane & off) != 0;
+#pragma unroll
+                        for (int j = 0; j < off; ++j) {
+                            const float send1 = upper ? s1[j] : s1[j + off];
+                            const float keep1 = upper ? s1[j + off] : s1[j];
+                            s1[j] = keep1 + __shfl_xor_sync(0xffffffffu, send1, off);
+                            const float send2 = upper ? s2[j] : s2[j + off];
+                            const float keep2 = upper ? s2[j + off] : s2[j];
+                            s2[j] = keep2 + __shfl_xor_sync(0xffffffffu, send2, off);
+                        }
+                    }
+                    if (k0 + lane < p.k_store) {
+                        atomicAdd(p.stats + k0 + lane, s1[0]);
+                        atomicAdd(p.stats + p.k_store + k0 + lane, s2[0]);
+                    }
+                }
                 if (valid) {
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
@@ -372,6 +401,7 @@ int launch_igemm(int n, int h, int w, int n_src, const b200seg_conv_src* src, co
     p.scale = out->scale;
     p.bias = out->bias;
     p.relu = out->relu;
+    p.stats = out->stats;
     B200SEG_CHECK((reinterpret_cast<uintptr_t>(out->y) & 15) == 0, "conv: output pointer not 16-byte aligned");
 
     static bool attr_set = false;

@@ -1,0 +1,459 @@
+// Class-map resampling, pixel-wise softmax cross-entropy and the mIoU confusion histogram.
+// All HBM-bound.  Logits at the drop-in boundary are NCHW fp32 (what the reference's forward returns), so the
+// per-pixel kernels put consecutive threads on consecutive pixels of one class plane (coalesced 128-byte rows)
+// and walk the class dimension in registers.
+#include "common.cuh"
+#include "vec.cuh"
+
+namespace b200seg {
+namespace {
+
+// ------------------------------------------------------------------------------------------------------------
+// final bilinear of the class map: NHWC fp32 [n][h][w][ct] -> NCHW fp32 [n][nc][oh][ow]
+__global__ void __launch_bounds__(256) logits_up_fwd_kernel(const float* __restrict__ x, int ct, int h, int w, int nc,
+                                                             float* __restrict__ y, int oh, int ow, int64_t total,
+                                                             float sh, float sw, int ac) {
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int ox = static_cast<int>(i % ow);
+        int64_t p = i / ow;
+        const int oy = static_cast<int>(p % oh);
+        const int n = static_cast<int>(p / oh);
+        const Lerp ly = bilinear_src(sh, oy, h, ac), lx = bilinear_src(sw, ox, w, ac);
+        const float* b = x + static_cast<int64_t>(n) * h * w * ct;
+        const float4* p00 = reinterpret_cast<const float4*>(b + (static_cast<int64_t>(ly.i0) * w + lx.i0) * ct);
+        const float4* p01 = reinterpret_cast<const float4*>(b + (static_cast<int64_t>(ly.i0) * w + lx.i1) * ct);
+        const float4* p10 = reinterpret_cast<const float4*>(b + (static_cast<int64_t>(ly.i1) * w + lx.i0) * ct);
+        const float4* p11 = reinterpret_cast<const float4*>(b + (static_cast<int64_t>(ly.i1) * w + lx.i1) * ct);
+        float* out = y + (static_cast<int64_t>(n) * nc * oh + oy) * ow + ox;
+        const int64_t plane = static_cast<int64_t>(oh) * ow;
+        for (int c4 = 0; c4 * 4 < nc; ++c4) {
+            const float4 a = __ldg(p00 + c4), bb = __ldg(p01 + c4), cc = __ldg(p10 + c4), d = __ldg(p11 + c4);
+            const float v[4] = {ly.w0 * (lx.w0 * a.x + lx.w1 * bb.x) + ly.w1 * (lx.w0 * cc.x + lx.w1 * d.x),
+                                ly.w0 * (lx.w0 * a.y + lx.w1 * bb.y) + ly.w1 * (lx.w0 * cc.y + lx.w1 * d.y),
+                                ly.w0 * (lx.w0 * a.z + lx.w1 * bb.z) + ly.w1 * (lx.w0 * cc.z + lx.w1 * d.z),
+                                ly.w0 * (lx.w0 * a.w + lx.w1 * bb.w) + ly.w1 * (lx.w0 * cc.w + lx.w1 * d.w)};
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (c4 * 4 + j < nc) __stcs(out + (c4 * 4 + j) * plane, v[j]);
+        }
+    }
+}
+
+// adjoint: NCHW fp32 gradient -> NHWC bf16 [n][h][w][ct]; one thread per source pixel gathers its window
+template <int NCMAX>
+__global__ void __launch_bounds__(128) logits_up_bwd_kernel(const float* __restrict__ dy, int nc, int oh, int ow,
+                                                             __nv_bfloat16* __restrict__ dx, int ct, int h, int w,
+                                                             int64_t total, float sh, float sw, int ac) {
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int sx = static_cast<int>(i % w);
+        int64_t p = i / w;
+        const int sy = static_cast<int>(p % h);
+        const int n = static_cast<int>(p / h);
+        int ylo, yhi, xlo, xhi;
+        bilinear_dst_range(sh, sy, h, oh, ac, ylo, yhi);
+        bilinear_dst_range(sw, sx, w, ow, ac, xlo, xhi);
+        float acc[NCMAX];
+#pragma unroll
+        for (int c = 0; c < NCMAX; ++c) acc[c] = 0.f;
+        const int64_t plane = static_cast<int64_t>(oh) * ow;
+        const float* b = dy + static_cast<int64_t>(n) * nc * plane;
+        for (int oy = ylo; oy <= yhi; ++oy) {
+            const Lerp ly = bilinear_src(sh, oy, h, ac);
+            const float wy = (ly.i0 == sy ? ly.w0 : 0.f) + (ly.i1 == sy ? ly.w1 : 0.f);
+            if (wy == 0.f) continue;
+            for (int ox = xlo; ox <= xhi; ++ox) {
+                const Lerp lx = bilinear_src(sw, ox, w, ac);
+                const float wx = (lx.i0 == sx ? lx.w0 : 0.f) + (lx.i1 == sx ? lx.w1 : 0.f);
+                if (wx == 0.f) continue;
+                const float wt = wy * wx;
+                const float* q = b + static_cast<int64_t>(oy) * ow + ox;
+#pragma unroll
+                for (int c = 0; c < NCMAX; ++c)
+                    if (c < nc) acc[c] = fmaf(wt, __ldcs(q + c * plane), acc[c]);
+            }
+        }
+        __nv_bfloat16* o = dx + ((static_cast<int64_t>(n) * h + sy) * w + sx) * ct;
+#pragma unroll
+        for (int c8 = 0; c8 < NCMAX / 8; ++c8) {
+            if (c8 * 8 < ct) {
+                float f[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] = (c8 * 8 + j < nc) ? acc[c8 * 8 + j] : 0.f;
+                st128(o + c8 * 8, pack8(f));
+            }
+        }
+    }
+}
+
+// generic NCHW fp32 bilinear resize (compute_loss when the logits and the targets differ in size)
+__global__ void __launch_bounds__(256) resize_nchw_fwd_kernel(const float* __restrict__ x, int h, int w,
+                                                               float* __restrict__ y, int oh, int ow, int64_t total,
+                                                               float sh, float sw, int ac) {
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int ox = static_cast<int>(i % ow);
+        int64_t p = i / ow;
+        const int oy = static_cast<int>(p % oh);
+        const int64_t nc = p / oh;   // fused (n, c) plane index
+        const Lerp ly = bilinear_src(sh, oy, h, ac), lx = bilinear_src(sw, ox, w, ac);
+        const float* b = x + nc * h * w;
+        y[i] = ly.w0 * (lx.w0 * __ldg(b + ly.i0 * w + lx.i0) + lx.w1 * __ldg(b + ly.i0 * w + lx.i1)) +
+               ly.w1 * (lx.w0 * __ldg(b + ly.i1 * w + lx.i0) + lx.w1 * __ldg(b + ly.i1 * w + lx.i1));
+    }
+}
+
+__global__ void __launch_bounds__(256) resize_nchw_bwd_kernel(const float* __restrict__ dy, int oh, int ow,
+                                                               float* __restrict__ dx, int h, int w, int64_t total,
+                                                               float sh, float sw, int ac) {
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int sx = static_cast<int>(i % w);
+        int64_t p = i / w;
+        const int sy = static_cast<int>(p % h);
+        const int64_t nc = p / h;
+        int ylo, yhi, xlo, xhi;
+        bilinear_dst_range(sh, sy, h, oh, ac, ylo, yhi);
+        bilinear_dst_range(sw, sx, w, ow, ac, xlo, xhi);
+        const float* b = dy + nc * oh * ow;
+        float acc = 0.f;
+        for (int oy = ylo; oy <= yhi; ++oy) {
+            const Lerp ly = bilinear_src(sh, oy, h, ac);
+            const float wy = (ly.i0 == sy ? ly.w0 : 0.f) + (ly.i1 == sy ? ly.w1 : 0.f);
+            if (wy == 0.f) continue;
+            for (int ox = xlo; ox <= xhi; ++ox) {
+                const Lerp lx = bilinear_src(sw, ox, w, ac);
+                const float wx = (lx.i0 == sx ? lx.w0 : 0.f) + (lx.i1 == sx ? lx.w1 : 0.f);
+                if (wx != 0.f) acc = fmaf(wy * wx, __ldg(b + static_cast<int64_t>(oy) * ow + ox), acc);
+            }
+        }
+        dx[i] = acc;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// softmax cross-entropy, one thread per pixel, class vector in registers
+template <int NCMAX>
+__global__ void __launch_bounds__(256) softmax_ce_kernel(const float* __restrict__ logits, const int64_t* __restrict__ tgt,
+                                                          int nc, int64_t hw, int64_t total, int64_t ignore_index,
+                                                          float grad_scale, double* loss_sum,
+                                                          unsigned long long* valid_count, float* __restrict__ dlogits,
+                                                          int* status) {
+    double lsum = 0.0;
+    unsigned int lcount = 0;
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int64_t n = i / hw, p = i - n * hw;
+        const float* q = logits + n * nc * hw + p;
+        const int64_t t = __ldcs(tgt + i);
+        float v[NCMAX];
+        float m = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < NCMAX; ++c) {
+            v[c] = c < nc ? __ldcs(q + c * hw) : -INFINITY;
+            m = fmaxf(m, v[c]);
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int c = 0; c < NCMAX; ++c) {
+            v[c] = c < nc ? __expf(v[c] - m) : 0.f;
+            s += v[c];
+        }
+        const bool ignored = (t == ignore_index);
+        const bool bad = !ignored && (t < 0 || t >= nc);
+        if (bad) *status = 1;
+        const bool valid = !ignored && !bad;
+        float xt = 0.f;
+        if (valid) {
+            xt = __ldg(q + t * hw);
+            lsum += static_cast<double>(__logf(s) + m - xt);
+            ++lcount;
+        }
+        if (dlogits) {
+            const float inv = valid ? grad_scale / s : 0.f;
+            float* d = dlogits + n * nc * hw + p;
+#pragma unroll
+            for (int c = 0; c < NCMAX; ++c)
+                if (c < nc) __stcs(d + c * hw, v[c] * inv - ((valid && c == t) ? grad_scale : 0.f));
+        }
+    }
+    lsum = warp_sum(lsum);
+    lcount = __reduce_add_sync(0xffffffffu, lcount);
+    __shared__ double ssum[8];
+    __shared__ unsigned int scnt[8];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) {
+        ssum[warp] = lsum;
+        scnt[warp] = lcount;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0;
+        unsigned long long b = 0;
+        for (int k = 0; k < (blockDim.x >> 5); ++k) {
+            a += ssum[k];
+            b += scnt[k];
+        }
+        atomicAdd(loss_sum, a);
+        if (valid_count) atomicAdd(valid_count, b);
+    }
+}
+
+// any class count: three passes over the class dimension (max, sum, gradient)
+__global__ void __launch_bounds__(256) softmax_ce_generic_kernel(const float* __restrict__ logits,
+                                                                  const int64_t* __restrict__ tgt, int nc, int64_t hw,
+                                                                  int64_t total, int64_t ignore_index, float grad_scale,
+                                                                  double* loss_sum, unsigned long long* valid_count,
+                                                                  float* __restrict__ dlogits, int* status) {
+    double lsum = 0.0;
+    unsigned int lcount = 0;
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int64_t n = i / hw, p = i - n * hw;
+        const float* q = logits + n * nc * hw + p;
+        const int64_t t = tgt[i];
+        float m = -INFINITY;
+        for (int c = 0; c < nc; ++c) m = fmaxf(m, q[c * hw]);
+        float s = 0.f;
+        for (int c = 0; c < nc; ++c) s += __expf(q[c * hw] - m);
+        const bool ignored = (t == ignore_index);
+        const bool bad = !ignored && (t < 0 || t >= nc);
+        if (bad) *status = 1;
+        const bool valid = !ignored && !bad;
+        if (valid) {
+            lsum += static_cast<double>(__logf(s) + m - q[t * hw]);
+            ++lcount;
+        }
+        if (dlogits) {
+            const float inv = valid ? grad_scale / s : 0.f;
+            float* d = dlogits + n * nc * hw + p;
+            for (int c = 0; c < nc; ++c)
+                d[c * hw] = __expf(q[c * hw] - m) * inv - ((valid && c == t) ? grad_scale : 0.f);
+        }
+    }
+    lsum = warp_sum(lsum);
+    lcount = __reduce_add_sync(0xffffffffu, lcount);
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(loss_sum, lsum);
+        if (valid_count) atomicAdd(valid_count, static_cast<unsigned long long>(lcount));
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// argmax over the class planes; lowest index wins ties (strict >), NaN counts as the maximum like torch.max
+__device__ __forceinline__ int argmax_planes(const float* q, int nc, int64_t hw) {
+    float best = __ldcs(q);
+    int bi = 0;
+    for (int c = 1; c < nc; ++c) {
+        const float v = __ldcs(q + c * hw);
+        if (v > best || (v != v && best == best)) {
+            best = v;
+            bi = c;
+        }
+    }
+    return bi;
+}
+
+__global__ void __launch_bounds__(256) argmax_kernel(const float* __restrict__ logits, int nc, int64_t hw, int64_t total,
+                                                      int64_t* __restrict__ pred) {
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int64_t n = i / hw, p = i - n * hw;
+        pred[i] = argmax_planes(logits + n * nc * hw + p, nc, hw);
+    }
+}
+
+// Confusion histogram: every warp owns a private nc x nc uint32 histogram in shared memory (no inter-warp
+// contention), flushed with one 64-bit global atomic per non-zero bin at the end of the block.
+constexpr int kHistThreads = 256;
+constexpr int kHistWarps = kHistThreads / 32;
+
+template <bool FUSED_ARGMAX>
+__global__ void __launch_bounds__(kHistThreads) confusion_kernel(const float* __restrict__ logits,
+                                                                  const int64_t* __restrict__ pred,
+                                                                  const int64_t* __restrict__ tgt, int nc, int64_t hw,
+                                                                  int64_t total, int copies,
+                                                                  unsigned long long* __restrict__ cm) {
+    extern __shared__ unsigned int hist[];
+    const int bins = nc * nc;
+    for (int b = threadIdx.x; b < bins * copies; b += blockDim.x) hist[b] = 0;
+    __syncthreads();
+    unsigned int* mine = hist + ((threadIdx.x >> 5) % copies) * bins;
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int64_t t = __ldcs(tgt + i);
+        int64_t pr;
+        if (FUSED_ARGMAX) {
+            const int64_t n = i / hw, p = i - n * hw;
+            pr = argmax_planes(logits + n * nc * hw + p, nc, hw);
+        } else {
+            pr = __ldcs(pred + i);
+        }
+        if (t >= 0 && t < nc && pr >= 0 && pr < nc) atomicAdd(mine + static_cast<int>(t) * nc + static_cast<int>(pr), 1u);
+    }
+    __syncthreads();
+    for (int b = threadIdx.x; b < bins; b += blockDim.x) {
+        unsigned long long s = 0;
+        for (int k = 0; k < copies; ++k) s += hist[k * bins + b];
+        if (s) atomicAdd(cm + b, s);
+    }
+}
+
+int hist_launch_geometry(int nc, int64_t total, int* copies, size_t* smem, int* grid) {
+    B200SEG_CHECK(nc > 0, "confusion: nc = %d", nc);
+    const size_t bins = static_cast<size_t>(nc) * nc;
+    B200SEG_CHECK(bins * 4 <= 48 * 1024, "confusion: %d classes need %zu bytes of shared memory (max 110 classes)", nc,
+                  bins * 4);
+    int cp = static_cast<int>((48 * 1024) / (bins * 4));
+    if (cp > kHistWarps) cp = kHistWarps;
+    *copies = cp;
+    *smem = bins * 4 * cp;
+    int sms = sm_count();
+    if (sms <= 0) sms = 148;
+    // each thread keeps its 32-bit bins far from overflow: at most 2^31 items per block
+    int64_t blocks = ceil_div64(total, static_cast<int64_t>(kHistThreads) * 16);
+    if (blocks > static_cast<int64_t>(sms) * 8) blocks = static_cast<int64_t>(sms) * 8;
+    if (blocks < 1) blocks = 1;
+    *grid = static_cast<int>(blocks);
+    return 0;
+}
+
+}  // namespace
+}  // namespace b200seg
+
+extern "C" {
+
+int b200seg_logits_upsample_fwd(const float* x, int c_total, int n, int h, int w, int nc, float* y, int oh, int ow,
+                                int align_corners, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(x && y && n > 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "logits_upsample_fwd: bad arguments");
+    B200SEG_CHECK(nc > 0 && nc <= c_total && c_total % 4 == 0, "logits_upsample_fwd: nc %d vs padded %d", nc, c_total);
+    B200SEG_CHECK((reinterpret_cast<uintptr_t>(x) & 15) == 0, "logits_upsample_fwd: input not 16-byte aligned");
+    const int64_t total = static_cast<int64_t>(n) * oh * ow;
+    logits_up_fwd_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        x, c_total, h, w, nc, y, oh, ow, total, bilinear_scale(h, oh, align_corners), bilinear_scale(w, ow, align_corners),
+        align_corners);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_logits_upsample_bwd(const float* dy, int n, int nc, int oh, int ow, void* dx, int c_total, int h, int w,
+                                int align_corners, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(dy && dx && n > 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "logits_upsample_bwd: bad arguments");
+    B200SEG_CHECK(nc > 0 && nc <= c_total && c_total % 8 == 0 && c_total <= 64,
+                  "logits_upsample_bwd: nc %d, padded %d (multiple of 8, at most 64)", nc, c_total);
+    B200SEG_CHECK((reinterpret_cast<uintptr_t>(dx) & 15) == 0, "logits_upsample_bwd: output not 16-byte aligned");
+    const int64_t total = static_cast<int64_t>(n) * h * w;
+    const float sh = bilinear_scale(h, oh, align_corners), sw = bilinear_scale(w, ow, align_corners);
+    const int grid = static_cast<int>(ceil_div64(total, 128));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    __nv_bfloat16* o = static_cast<__nv_bfloat16*>(dx);
+    if (c_total <= 8)
+        logits_up_bwd_kernel<8><<<grid, 128, 0, st>>>(dy, nc, oh, ow, o, c_total, h, w, total, sh, sw, align_corners);
+    else if (c_total <= 24)
+        logits_up_bwd_kernel<24><<<grid, 128, 0, st>>>(dy, nc, oh, ow, o, c_total, h, w, total, sh, sw, align_corners);
+    else if (c_total <= 32)
+        logits_up_bwd_kernel<32><<<grid, 128, 0, st>>>(dy, nc, oh, ow, o, c_total, h, w, total, sh, sw, align_corners);
+    else
+        logits_up_bwd_kernel<64><<<grid, 128, 0, st>>>(dy, nc, oh, ow, o, c_total, h, w, total, sh, sw, align_corners);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_resize_nchw_fwd(const float* x, int64_t planes, int h, int w, float* y, int oh, int ow, int align_corners,
+                            b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(x && y && planes > 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "resize_nchw_fwd: bad arguments");
+    const int64_t total = planes * oh * ow;
+    resize_nchw_fwd_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        x, h, w, y, oh, ow, total, bilinear_scale(h, oh, align_corners), bilinear_scale(w, ow, align_corners),
+        align_corners);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_resize_nchw_bwd(const float* dy, int64_t planes, int oh, int ow, float* dx, int h, int w, int align_corners,
+                            b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(dy && dx && planes > 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "resize_nchw_bwd: bad arguments");
+    const int64_t total = planes * h * w;
+    resize_nchw_bwd_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        dy, oh, ow, dx, h, w, total, bilinear_scale(h, oh, align_corners), bilinear_scale(w, ow, align_corners),
+        align_corners);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_softmax_ce(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
+                       float grad_scale, double* loss_sum, int64_t* valid_count, float* dlogits, int* status,
+                       b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(logits && targets && loss_sum && status && n > 0 && nc > 0 && hw > 0, "softmax_ce: bad arguments");
+    const int64_t total = static_cast<int64_t>(n) * hw;
+    const int grid = elementwise_grid(total);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    unsigned long long* vc = reinterpret_cast<unsigned long long*>(valid_count);
+    if (nc <= 8)
+        softmax_ce_kernel<8><<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum, vc,
+                                                    dlogits, status);
+    else if (nc <= 24)
+        softmax_ce_kernel<24><<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum, vc,
+                                                     dlogits, status);
+    else if (nc <= 32)
+        softmax_ce_kernel<32><<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum, vc,
+                                                     dlogits, status);
+    else
+        softmax_ce_generic_kernel<<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum,
+                                                        vc, dlogits, status);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_argmax(const float* logits, int n, int nc, int64_t hw, int64_t* pred, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(logits && pred && n > 0 && nc > 0 && hw > 0, "argmax: bad arguments");
+    const int64_t total = static_cast<int64_t>(n) * hw;
+    argmax_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(logits, nc, hw, total, pred);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_confusion(const int64_t* pred, const int64_t* targets, int64_t count, int nc, int64_t* cm,
+                      b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(pred && targets && cm && count >= 0, "confusion: bad arguments");
+    if (count == 0) return 0;
+    int copies, grid;
+    size_t smem;
+    if (hist_launch_geometry(nc, count, &copies, &smem, &grid)) return 1;
+    confusion_kernel<false><<<grid, kHistThreads, smem, static_cast<cudaStream_t>(stream)>>>(
+        nullptr, pred, targets, nc, 1, count, copies, reinterpret_cast<unsigned long long*>(cm));
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_argmax_confusion(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t* cm,
+                             b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(logits && targets && cm && n > 0 && hw > 0, "argmax_confusion: bad arguments");
+    int copies, grid;
+    size_t smem;
+    const int64_t total = static_cast<int64_t>(n) * hw;
+    if (hist_launch_geometry(nc, total, &copies, &smem, &grid)) return 1;
+    confusion_kernel<true><<<grid, kHistThreads, smem, static_cast<cudaStream_t>(stream)>>>(
+        logits, nullptr, targets, nc, hw, total, copies, reinterpret_cast<unsigned long long*>(cm));
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // extern "C"

@@ -45,7 +45,7 @@ __global__ void nhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float
 
 // One thread per packed element; both packings in one launch (grid.y selects which).
 __global__ void pack_weights_kernel(const float* __restrict__ w, int k, int c, int r, int s, __nv_bfloat16* wf,
-                                    int k_rows, __nv_bfloat16* wd, int c_rows) {
+                                    int k_rows, __nv_bfloat16* wd, int c_rows, int k_cols) {
     const int taps = r * s;
     const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
     if (blockIdx.y == 0) {
@@ -59,14 +59,14 @@ __global__ void pack_weights_kernel(const float* __restrict__ w, int k, int c, i
         wf[i] = __float2bfloat16(v);
     } else {
         if (!wd) return;
-        const long long total = static_cast<long long>(taps) * c_rows * k;
+        const long long total = static_cast<long long>(taps) * c_rows * k_cols;
         if (i >= total) return;
-        const int kk = static_cast<int>(i % k);
-        const int cc = static_cast<int>((i / k) % c_rows);
-        const int tap = static_cast<int>(i / (static_cast<long long>(k) * c_rows));
+        const int kk = static_cast<int>(i % k_cols);
+        const int cc = static_cast<int>((i / k_cols) % c_rows);
+        const int tap = static_cast<int>(i / (static_cast<long long>(k_cols) * c_rows));
         // dgrad reads dy at +offset(tap') where tap' mirrors the forward tap: (r', s') = (R-1-r, S-1-s)
         const int src_tap = taps - 1 - tap;
-        const float v = cc < c ? w[(static_cast<size_t>(kk) * c + cc) * taps + src_tap] : 0.f;
+        const float v = (cc < c && kk < k) ? w[(static_cast<size_t>(kk) * c + cc) * taps + src_tap] : 0.f;
         wd[i] = __float2bfloat16(v);
     }
 }
@@ -105,19 +105,21 @@ int b200seg_nhwc_to_nchw(const void* src, float* dst, int n, int c, int h, int w
 }
 
 int b200seg_pack_weights(const float* w_oihw, int k, int c, int r, int s, void* w_fprop, int k_rows, void* w_dgrad,
-                         int c_rows, b200seg_stream_t st) {
+                         int c_rows, int k_cols, b200seg_stream_t st) {
     using namespace b200seg;
     clear_error();
     B200SEG_CHECK(w_oihw && k > 0 && c > 0 && r > 0 && s > 0, "pack_weights: bad arguments");
     B200SEG_CHECK(!w_fprop || k_rows >= k, "pack_weights: k_rows %d < k %d", k_rows, k);
-    B200SEG_CHECK(!w_dgrad || c_rows >= c, "pack_weights: c_rows %d < c %d", c_rows, c);
+    B200SEG_CHECK(!w_dgrad || (c_rows >= c && k_cols >= k), "pack_weights: c_rows %d < c %d or k_cols %d < k %d", c_rows,
+                  c, k_cols, k);
     const long long tf = w_fprop ? static_cast<long long>(r) * s * k_rows * c : 0;
-    const long long td = w_dgrad ? static_cast<long long>(r) * s * c_rows * k : 0;
+    const long long td = w_dgrad ? static_cast<long long>(r) * s * c_rows * k_cols : 0;
     const long long tmax = tf > td ? tf : td;
     if (tmax == 0) return 0;
     dim3 grid(static_cast<unsigned>((tmax + 255) / 256), 2);
     pack_weights_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(st)>>>(
-        w_oihw, k, c, r, s, static_cast<__nv_bfloat16*>(w_fprop), k_rows, static_cast<__nv_bfloat16*>(w_dgrad), c_rows);
+        w_oihw, k, c, r, s, static_cast<__nv_bfloat16*>(w_fprop), k_rows, static_cast<__nv_bfloat16*>(w_dgrad), c_rows,
+        k_cols);
     B200SEG_LAUNCH_CHECK();
     return 0;
 }

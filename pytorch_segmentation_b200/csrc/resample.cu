@@ -1,0 +1,233 @@
+// Bilinear resampling between NHWC bf16 channel slices (decoder upsample + concat placement), its adjoint in
+// gather form, and the H*W reductions / broadcasts of the ASPP image-pooling branch.  HBM-bound: one thread per
+// (pixel, 8-channel group), 128-bit accesses, consecutive threads on consecutive channel groups.
+#include "common.cuh"
+#include "vec.cuh"
+
+namespace b200seg {
+namespace {
+
+__global__ void __launch_bounds__(256) upsample_fwd_kernel(const __nv_bfloat16* __restrict__ x, int x_ct, int x_off, int h,
+                                                            int w, __nv_bfloat16* __restrict__ y, int y_ct, int y_off,
+                                                            int oh, int ow, int groups, int64_t total, float sh, float sw,
+                                                            int ac) {
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int g = static_cast<int>(i % groups);
+        int64_t p = i / groups;
+        const int ox = static_cast<int>(p % ow);
+        p /= ow;
+        const int oy = static_cast<int>(p % oh);
+        const int n = static_cast<int>(p / oh);
+        const Lerp ly = bilinear_src(sh, oy, h, ac), lx = bilinear_src(sw, ox, w, ac);
+        const __nv_bfloat16* b = x + (static_cast<int64_t>(n) * h * w) * x_ct + x_off + g * 8;
+        float v00[8], v01[8], v10[8], v11[8], o[8];
+        unpack8(ldg128(b + (static_cast<int64_t>(ly.i0) * w + lx.i0) * x_ct), v00);
+        unpack8(ldg128(b + (static_cast<int64_t>(ly.i0) * w + lx.i1) * x_ct), v01);
+        unpack8(ldg128(b + (static_cast<int64_t>(ly.i1) * w + lx.i0) * x_ct), v10);
+        unpack8(ldg128(b + (static_cast<int64_t>(ly.i1) * w + lx.i1) * x_ct), v11);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            o[j] = ly.w0 * (lx.w0 * v00[j] + lx.w1 * v01[j]) + ly.w1 * (lx.w0 * v10[j] + lx.w1 * v11[j]);
+        st128(y + ((static_cast<int64_t>(n) * oh + oy) * ow + ox) * y_ct + y_off + g * 8, pack8(o));
+    }
+}
+
+// dx[n, y, x, :] = sum over destination pixels (oy, ox) that read (y, x) of weight * dy[n, oy, ox, :]
+__global__ void __launch_bounds__(256) upsample_bwd_kernel(const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off,
+                                                            int oh, int ow, __nv_bfloat16* __restrict__ dx, int dx_ct,
+                                                            int dx_off, int h, int w, int groups, int64_t total, float sh,
+                                                            float sw, int ac) {
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int g = static_cast<int>(i % groups);
+        int64_t p = i / groups;
+        const int sx = static_cast<int>(p % w);
+        p /= w;
+        const int sy = static_cast<int>(p % h);
+        const int n = static_cast<int>(p / h);
+        int ylo, yhi, xlo, xhi;
+        bilinear_dst_range(sh, sy, h, oh, ac, ylo, yhi);
+        bilinear_dst_range(sw, sx, w, ow, ac, xlo, xhi);
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        const __nv_bfloat16* b = dy + (static_cast<int64_t>(n) * oh * ow) * dy_ct + dy_off + g * 8;
+        for (int oy = ylo; oy <= yhi; ++oy) {
+            const Lerp ly = bilinear_src(sh, oy, h, ac);
+            const float wy = (ly.i0 == sy ? ly.w0 : 0.f) + (ly.i1 == sy ? ly.w1 : 0.f);
+            if (wy == 0.f) continue;
+            for (int ox = xlo; ox <= xhi; ++ox) {
+                const Lerp lx = bilinear_src(sw, ox, w, ac);
+                const float wx = (lx.i0 == sx ? lx.w0 : 0.f) + (lx.i1 == sx ? lx.w1 : 0.f);
+                if (wx == 0.f) continue;
+                float f[8];
+                unpack8(ldg128(b + (static_cast<int64_t>(oy) * ow + ox) * dy_ct), f);
+                const float wt = wy * wx;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] = fmaf(wt, f[j], acc[j]);
+            }
+        }
+        st128(dx + ((static_cast<int64_t>(n) * h + sy) * w + sx) * dx_ct + dx_off + g * 8, pack8(acc));
+    }
+}
+
+// acc[n][c] += sum over a chunk of H*W (fp32 atomics), then a tiny kernel scales and rounds to bf16.
+__global__ void __launch_bounds__(256) reduce_hw_kernel(const __nv_bfloat16* __restrict__ x, int x_ct, int x_off, int hw,
+                                                         int c, int gpb, int rows, int chunk, float* __restrict__ acc) {
+    __shared__ float red[256 * 8];
+    const int groups = c >> 3;
+    const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
+    const int group = blockIdx.y * gpb + g_local;
+    const int n = blockIdx.z;
+    float a[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = 0.f;
+    if (row < rows && group < groups) {
+        const int p0 = blockIdx.x * chunk, p1 = min(p0 + chunk, hw);
+        const __nv_bfloat16* b = x + static_cast<int64_t>(n) * hw * x_ct + x_off + group * 8;
+        for (int p = p0 + row; p < p1; p += rows) {
+            float f[8];
+            unpack8(ldg128(b + static_cast<int64_t>(p) * x_ct), f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a[j] += f[j];
+        }
+    }
+    if (row < rows) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) red[(row * gpb + g_local) * 8 + j] = a[j];
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < gpb * 8; t += blockDim.x) {
+        const int gl = t >> 3, j = t & 7;
+        const int gg = blockIdx.y * gpb + gl;
+        if (gg < groups) {
+            float s = 0.f;
+            for (int r = 0; r < rows; ++r) s += red[(r * gpb + gl) * 8 + j];
+            atomicAdd(acc + static_cast<int64_t>(n) * c + gg * 8 + j, s);
+        }
+    }
+}
+
+__global__ void scale_to_bf16_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ y, int64_t total,
+                                     float scale) {
+    const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+    if (i < total) y[i] = __float2bfloat16(acc[i] * scale);
+}
+
+// y[n, p, slice] (+)= scale * v[n, :]
+__global__ void __launch_bounds__(256) broadcast_hw_kernel(const __nv_bfloat16* __restrict__ v, int c, float scale,
+                                                            __nv_bfloat16* __restrict__ y, int y_ct, int y_off, int hw,
+                                                            int groups, int64_t total, int accumulate) {
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int g = static_cast<int>(i % groups);
+        const int64_t p = i / groups;          // n * hw + pixel
+        const int n = static_cast<int>(p / hw);
+        float f[8];
+        unpack8(ldg128(v + static_cast<int64_t>(n) * c + g * 8), f);
+        __nv_bfloat16* dst = y + p * y_ct + y_off + g * 8;
+        if (accumulate) {
+            float o[8];
+            unpack8(*reinterpret_cast<const uint4*>(dst), o);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] = fmaf(scale, f[j], o[j]);
+        } else if (scale != 1.f) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] *= scale;
+        }
+        st128(dst, pack8(f));
+    }
+}
+
+int reduce_hw(const char* what, const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, float scale,
+              float* acc_ws, void* y, cudaStream_t st) {
+    clear_error();
+    if (check_slice(what, x, x_c_total, x_c_offset, c)) return 1;
+    B200SEG_CHECK(n > 0 && hw > 0 && acc_ws && y, "%s: bad arguments", what);
+    const int64_t total = static_cast<int64_t>(n) * c;
+    B200SEG_CUDA(cudaMemsetAsync(acc_ws, 0, sizeof(float) * total, st));
+    const int groups = c / 8;
+    const int gpb = groups < 256 ? groups : 256;
+    const int rows = 256 / gpb;
+    const int gy = ceil_div(groups, gpb);
+    int sms = sm_count();
+    if (sms <= 0) sms = 148;
+    int splits = ceil_div(sms * 8, n * gy);
+    const int max_splits = ceil_div(hw, rows * 4);
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+    const int chunk = round_up(ceil_div(hw, splits), rows);
+    reduce_hw_kernel<<<dim3(ceil_div(hw, chunk), gy, n), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), x_c_total,
+                                                                      x_c_offset, hw, c, gpb, rows, chunk, acc_ws);
+    B200SEG_LAUNCH_CHECK();
+    scale_to_bf16_kernel<<<static_cast<unsigned>(ceil_div64(total, 256)), 256, 0, st>>>(
+        acc_ws, static_cast<__nv_bfloat16*>(y), total, scale);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace
+}  // namespace b200seg
+
+extern "C" {
+
+int b200seg_upsample_fwd(const void* x, int x_c_total, int x_c_offset, int n, int h, int w, void* y, int y_c_total,
+                         int y_c_offset, int oh, int ow, int c, int align_corners, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    if (check_slice("upsample_fwd(x)", x, x_c_total, x_c_offset, c)) return 1;
+    if (check_slice("upsample_fwd(y)", y, y_c_total, y_c_offset, c)) return 1;
+    B200SEG_CHECK(n > 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "upsample_fwd: bad shape");
+    const int64_t total = static_cast<int64_t>(n) * oh * ow * (c / 8);
+    upsample_fwd_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, h, w, static_cast<__nv_bfloat16*>(y), y_c_total,
+        y_c_offset, oh, ow, c / 8, total, bilinear_scale(h, oh, align_corners), bilinear_scale(w, ow, align_corners),
+        align_corners);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_upsample_bwd(const void* dy, int dy_c_total, int dy_c_offset, int n, int oh, int ow, void* dx, int dx_c_total,
+                         int dx_c_offset, int h, int w, int c, int align_corners, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    if (check_slice("upsample_bwd(dy)", dy, dy_c_total, dy_c_offset, c)) return 1;
+    if (check_slice("upsample_bwd(dx)", dx, dx_c_total, dx_c_offset, c)) return 1;
+    B200SEG_CHECK(n > 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "upsample_bwd: bad shape");
+    const int64_t total = static_cast<int64_t>(n) * h * w * (c / 8);
+    upsample_bwd_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, oh, ow, static_cast<__nv_bfloat16*>(dx), dx_c_total,
+        dx_c_offset, h, w, c / 8, total, bilinear_scale(h, oh, align_corners), bilinear_scale(w, ow, align_corners),
+        align_corners);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_gap_fwd(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, float* acc_ws, void* y,
+                    b200seg_stream_t stream) {
+    return b200seg::reduce_hw("gap_fwd", x, x_c_total, x_c_offset, n, hw, c, 1.f / static_cast<float>(hw), acc_ws, y,
+                              static_cast<cudaStream_t>(stream));
+}
+
+int b200seg_sum_hw(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, float* acc_ws, void* y,
+                   b200seg_stream_t stream) {
+    return b200seg::reduce_hw("sum_hw", x, x_c_total, x_c_offset, n, hw, c, 1.f, acc_ws, y,
+                              static_cast<cudaStream_t>(stream));
+}
+
+int b200seg_broadcast_hw(const void* v, int n, int c, float scale, void* y, int y_c_total, int y_c_offset, int hw,
+                         int accumulate, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    if (check_slice("broadcast_hw(y)", y, y_c_total, y_c_offset, c)) return 1;
+    B200SEG_CHECK(v && n > 0 && hw > 0 && (reinterpret_cast<uintptr_t>(v) & 15) == 0, "broadcast_hw: bad arguments");
+    const int64_t total = static_cast<int64_t>(n) * hw * (c / 8);
+    broadcast_hw_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(v), c, scale, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset, hw, c / 8,
+        total, accumulate);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // extern "C"

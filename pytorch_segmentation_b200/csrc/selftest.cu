@@ -65,9 +65,9 @@ static int run_fprop(const ConvCase& cs) {
     CK(cudaMemcpy(d_w, w.data(), w.size() * 4, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(d_scale, scale.data(), cs.k * 4, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(d_bias, bias.data(), cs.k * 4, cudaMemcpyHostToDevice));
-    AB(b200seg_pack_weights(d_w, cs.k, cs.c, cs.r, cs.r, d_wf, k_rows, nullptr, 0, 0));
+    AB(b200seg_pack_weights(d_w, cs.k, cs.c, cs.r, cs.r, d_wf, k_rows, nullptr, 0, 0, 0));
     b200seg_conv_src src = {d_x, cs.c_total, cs.c_off, cs.c, d_wf, k_rows, cs.r, cs.r, cs.dil};
-    b200seg_conv_out out = {d_y, cs.y_total, cs.y_off, cs.k, cs.fp32_out, cs.use_scale ? d_scale : nullptr, d_bias, cs.relu};
+    b200seg_conv_out out = {d_y, cs.y_total, cs.y_off, cs.k, cs.fp32_out, cs.use_scale ? d_scale : nullptr, d_bias, cs.relu, nullptr};
     AB(b200seg_conv_fprop(cs.n, cs.h, cs.w, 1, &src, &out, 0));
     CK(cudaDeviceSynchronize());
     std::vector<uint8_t> yraw(ybytes);
@@ -137,10 +137,10 @@ static int run_dgrad(int n, int h, int w, int c, int k, int dil) {
     CK(cudaMemcpy(d2, b2.data(), b2.size() * 2, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(dw1, w1.data(), w1.size() * 4, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(dw2, w2.data(), w2.size() * 4, cudaMemcpyHostToDevice));
-    AB(b200seg_pack_weights(dw1, k, c, 3, 3, nullptr, 0, wd1, c_rows, 0));
-    AB(b200seg_pack_weights(dw2, k, c, 1, 1, nullptr, 0, wd2, c_rows, 0));
+    AB(b200seg_pack_weights(dw1, k, c, 3, 3, nullptr, 0, wd1, c_rows, k, 0));
+    AB(b200seg_pack_weights(dw2, k, c, 1, 1, nullptr, 0, wd2, c_rows, k, 0));
     b200seg_conv_src src[2] = {{d1, k, 0, k, wd1, c_rows, 3, 3, dil}, {d2, k, 0, k, wd2, c_rows, 1, 1, 1}};
-    b200seg_conv_out out = {dx, c, 0, c, 0, nullptr, nullptr, 0};
+    b200seg_conv_out out = {dx, c, 0, c, 0, nullptr, nullptr, 0, nullptr};
     AB(b200seg_conv_dgrad(n, h, w, 2, src, &out, 0));
     CK(cudaDeviceSynchronize());
     std::vector<__nv_bfloat16> got(npix * c);

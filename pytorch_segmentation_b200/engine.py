@@ -1,0 +1,381 @@
+"""Host side of the hot path: NHWC bf16 activation slices and one thin wrapper per C-ABI entry point.
+
+PyTorch is used for device memory (caching allocator), streams and autograd plumbing only; every
+arithmetic step below is a call into libb200seg.so on ``torch.cuda.current_stream()``.  There is no
+CPU / cuDNN fallback: tensors that are not on a CUDA device raise.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import ConvOut, ConvSrc, WgradDesc
+
+BF16 = torch.bfloat16
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _require_cuda(t, what):
+    if not t.is_cuda:
+        raise RuntimeError('%s: tensor is on %s — pytorch_segmentation_b200 runs on CUDA (sm_100a) only and has '
+                           'no CPU fallback' % (what, t.device))
+
+
+class Act:
+    """A channel slice [c_off, c_off + c) of an NHWC bf16 buffer ``t`` of shape [n, h, w, c_total]."""
+    __slots__ = ('t', 'c_off', 'c')
+
+    def __init__(self, t, c_off=0, c=None):
+        assert t.dim() == 4 and t.dtype == BF16 and t.is_contiguous(), (t.shape, t.dtype, t.stride())
+        self.t, self.c_off = t, c_off
+        self.c = t.shape[3] - c_off if c is None else c
+        assert self.c_off % 8 == 0 and self.c % 8 == 0 and t.shape[3] % 8 == 0, \
+            'channel counts and offsets must be multiples of 8 (got c=%d off=%d total=%d)' % (self.c, c_off, t.shape[3])
+
+    n = property(lambda s: s.t.shape[0])
+    h = property(lambda s: s.t.shape[1])
+    w = property(lambda s: s.t.shape[2])
+    ct = property(lambda s: s.t.shape[3])
+    pixels = property(lambda s: s.t.shape[0] * s.t.shape[1] * s.t.shape[2])
+    ptr = property(lambda s: s.t.data_ptr())
+
+    def slice(self, off, c):
+        return Act(self.t, self.c_off + off, c)
+
+    @staticmethod
+    def empty(n, h, w, c, device):
+        return Act(torch.empty((n, h, w, c), dtype=BF16, device=device))
+
+    def nchw(self):
+        """NCHW-shaped (channels_last-strided) view of the slice — what module boundaries hand out."""
+        v = self.t.permute(0, 3, 1, 2)
+        return v if (self.c_off == 0 and self.c == self.ct) else v[:, self.c_off:self.c_off + self.c]
+
+
+def as_act(x, what='input'):
+    """NCHW-shaped tensor (any float dtype / memory format) -> contiguous NHWC bf16 Act.
+    bf16 channels_last input is a zero-copy view; fp32 NCHW goes through the layout kernel."""
+    _require_cuda(x, what)
+    if x.dim() != 4:
+        raise ValueError('%s: expected an N x C x H x W tensor, got shape %s' % (what, tuple(x.shape)))
+    n, c, h, w = x.shape
+    if c % 8:
+        raise ValueError('%s: %d channels — the tcgen05 conv path needs a multiple of 8' % (what, c))
+    if x.dtype == BF16 and x.permute(0, 2, 3, 1).is_contiguous():
+        return Act(x.permute(0, 2, 3, 1))
+    if x.dtype == torch.float32 and x.is_contiguous():
+        out = Act.empty(n, h, w, c, x.device)
+        _lib.check(_lib.load().b200seg_nchw_to_nhwc(x.data_ptr(), out.ptr, n, c, h, w, c, 0, _stream()),
+                   'nchw_to_nhwc')
+        _lib.count_launch()
+        return out
+    # other dtypes / strides: plumbing copy
+    return Act(x.detach().to(BF16).permute(0, 2, 3, 1).contiguous())
+
+
+def grad_like(x, g):
+    """Gradient Act ``g`` (full buffer) -> tensor shaped/typed like the forward input ``x``."""
+    if x.dtype == BF16:
+        return g.nchw()
+    if x.dtype == torch.float32:
+        n, c, h, w = x.shape
+        out = torch.empty((n, c, h, w), dtype=torch.float32, device=x.device)
+        _lib.check(_lib.load().b200seg_nhwc_to_nchw(g.ptr, out.data_ptr(), n, c, h, w, g.ct, g.c_off, _stream()),
+                   'nhwc_to_nchw')
+        _lib.count_launch()
+        return out
+    return g.nchw().to(x.dtype)
+
+
+# ------------------------------------------------------------------------------------------------
+# weights
+# ------------------------------------------------------------------------------------------------
+def _round_up(a, b):
+    return (a + b - 1) // b * b
+
+
+class PackedWeight:
+    """bf16 packings of an fp32 OIHW conv weight for fprop ([taps][k_rows][c]) and dgrad
+    ([taps mirrored][c_rows][k_cols]); refreshed when the parameter's version changes."""
+    __slots__ = ('k', 'c', 'r', 's', 'k_rows', 'c_rows', 'k_cols', 'wf', 'wd', 'key')
+
+    def __init__(self):
+        self.key = None
+
+    def update(self, w, need_dgrad=True):
+        _require_cuda(w, 'conv weight')
+        key = (w.data_ptr(), w._version, tuple(w.shape), need_dgrad)
+        if key == self.key:
+            return self
+        w = w.detach()
+        if w.dtype != torch.float32 or not w.is_contiguous():
+            w = w.float().contiguous()
+        k, c, r, s = w.shape
+        if c % 8:
+            raise ValueError('conv weight with %d input channels: need a multiple of 8' % c)
+        self.k, self.c, self.r, self.s = k, c, r, s
+        self.k_rows = _round_up(k, 8)
+        self.c_rows = _round_up(c, 8)
+        self.k_cols = _round_up(k, 8)
+        taps = r * s
+        self.wf = torch.empty((taps, self.k_rows, c), dtype=BF16, device=w.device)
+        keep_wd = need_dgrad or (self.key is not None and self.key[3])
+        self.wd = torch.empty((taps, self.c_rows, self.k_cols), dtype=BF16, device=w.device) if keep_wd else None
+        _lib.check(_lib.load().b200seg_pack_weights(w.data_ptr(), k, c, r, s, self.wf.data_ptr(), self.k_rows,
+                                                    self.wd.data_ptr() if keep_wd else None, self.c_rows, self.k_cols,
+                                                    _stream()), 'pack_weights')
+        _lib.count_launch()
+        self.key = (key[0], key[1], key[2], keep_wd)
+        return self
+
+
+# ------------------------------------------------------------------------------------------------
+# convolution
+# ------------------------------------------------------------------------------------------------
+def _conv(fn, what, n, h, w, srcs, out_ptr, y_ct, y_off, k, out_fp32, scale, bias, relu, stats):
+    arr = (ConvSrc * len(srcs))()
+    for i, (x, wptr, w_rows, r, s, dil) in enumerate(srcs):
+        arr[i] = ConvSrc(x.ptr, x.ct, x.c_off, x.c, wptr, w_rows, r, s, dil)
+    out = ConvOut(out_ptr, y_ct, y_off, k, int(out_fp32),
+                  scale.data_ptr() if scale is not None else None,
+                  bias.data_ptr() if bias is not None else None, int(relu),
+                  stats.data_ptr() if stats is not None else None)
+    _lib.check(fn(n, h, w, len(srcs), arr, ctypes.byref(out), _stream()), what)
+    _lib.count_launch()
+
+
+def conv_fprop(srcs, out, scale=None, bias=None, relu=False, stats=None):
+    """srcs: list of (x: Act, pw: PackedWeight, dil).  out: Act (bf16) — y = act(scale * sum conv + bias)."""
+    x0 = srcs[0][0]
+    _conv(_lib.load().b200seg_conv_fprop, 'conv_fprop', x0.n, x0.h, x0.w,
+          [(x, pw.wf.data_ptr(), pw.k_rows, pw.r, pw.s, dil) for x, pw, dil in srcs],
+          out.ptr, out.ct, out.c_off, out.c, False, scale, bias, relu, stats)
+
+
+def conv_fprop_f32(srcs, out_t, k, bias=None):
+    """Same, fp32 NHWC output tensor [n, h, w, k] (the class map of cls_conv)."""
+    x0 = srcs[0][0]
+    _conv(_lib.load().b200seg_conv_fprop, 'conv_fprop', x0.n, x0.h, x0.w,
+          [(x, pw.wf.data_ptr(), pw.k_rows, pw.r, pw.s, dil) for x, pw, dil in srcs],
+          out_t.data_ptr(), out_t.shape[3], 0, k, True, None, bias, False, None)
+
+
+def conv_dgrad(srcs, dx):
+    """srcs: list of (dy: Act, pw: PackedWeight, dil); dx: Act receiving the sum of the data gradients."""
+    d0 = srcs[0][0]
+    _conv(_lib.load().b200seg_conv_dgrad, 'conv_dgrad', d0.n, d0.h, d0.w,
+          [(dy, pw.wd.data_ptr(), pw.c_rows, pw.r, pw.s, dil) for dy, pw, dil in srcs],
+          dx.ptr, dx.ct, dx.c_off, dx.c, False, None, None, False, None)
+
+
+def conv_wgrad(dy, x, k_out, r, s, dil, dw=None):
+    """dW fp32 OIHW [k_out, x.c, r, s] = sum_pixels dy (x) shifted x."""
+    desc = WgradDesc()
+    desc.n, desc.h, desc.w = x.n, x.h, x.w
+    desc.dy, desc.dy_c_total, desc.dy_c_offset, desc.k = dy.ptr, dy.ct, dy.c_off, dy.c
+    desc.x, desc.x_c_total, desc.x_c_offset, desc.c = x.ptr, x.ct, x.c_off, x.c
+    desc.r, desc.s, desc.dil = r, s, dil
+    accumulate = dw is not None
+    if dw is None:
+        dw = torch.empty((k_out, x.c, r, s), dtype=torch.float32, device=x.t.device)
+    desc.dw, desc.k_out, desc.accumulate = dw.data_ptr(), k_out, int(accumulate)
+    desc.workspace, desc.workspace_bytes = None, 0
+    lib = _lib.load()
+    # the query validates everything except the workspace itself
+    nbytes = lib.b200seg_conv_wgrad_workspace(ctypes.byref(desc))
+    if nbytes == 0:
+        raise RuntimeError('conv_wgrad: %s' % _lib.last_error())
+    ws = torch.empty((nbytes,), dtype=torch.uint8, device=x.t.device)
+    desc.workspace, desc.workspace_bytes = ws.data_ptr(), nbytes
+    _lib.check(lib.b200seg_conv_wgrad(ctypes.byref(desc), _stream()), 'conv_wgrad')
+    _lib.count_launch(2)
+    return dw
+
+
+# ------------------------------------------------------------------------------------------------
+# batch norm
+# ------------------------------------------------------------------------------------------------
+def bn_stats(x):
+    stats = torch.empty((2 * x.c,), dtype=torch.float32, device=x.t.device)
+    _lib.check(_lib.load().b200seg_bn_stats(x.ptr, x.ct, x.c_off, x.c, x.pixels, stats.data_ptr(), _stream()),
+               'bn_stats')
+    _lib.count_launch()
+    return stats
+
+
+def bn_finalize(stats, c, count, gamma, beta, eps, momentum, running_mean, running_var):
+    """-> vec[4, c] = (scale, shift, mean, invstd); updates the running statistics in place."""
+    vec = torch.empty((4, c), dtype=torch.float32, device=stats.device)
+    p = vec.data_ptr()
+    _lib.check(_lib.load().b200seg_bn_finalize(
+        stats.data_ptr(), c, count, gamma.data_ptr(), beta.data_ptr(), eps, momentum,
+        running_mean.data_ptr() if running_mean is not None else None,
+        running_var.data_ptr() if running_var is not None else None,
+        p, p + 4 * c, p + 8 * c, p + 12 * c, _stream()), 'bn_finalize')
+    _lib.count_launch()
+    return vec
+
+
+def bn_eval_affine(c, gamma, beta, running_mean, running_var, eps):
+    vec = torch.empty((4, c), dtype=torch.float32, device=gamma.device)
+    p = vec.data_ptr()
+    _lib.check(_lib.load().b200seg_bn_eval_affine(c, gamma.data_ptr(), beta.data_ptr(), running_mean.data_ptr(),
+                                                  running_var.data_ptr(), eps, p, p + 4 * c, p + 8 * c, p + 12 * c,
+                                                  _stream()), 'bn_eval_affine')
+    _lib.count_launch()
+    return vec
+
+
+def bn_apply(x, y, vec, relu):
+    c = x.c
+    p = vec.data_ptr()
+    _lib.check(_lib.load().b200seg_bn_apply(x.ptr, x.ct, x.c_off, y.ptr, y.ct, y.c_off, c, x.pixels, p, p + 4 * c,
+                                            int(relu), _stream()), 'bn_apply')
+    _lib.count_launch()
+
+
+def bn_backward(dy, x, dx, vec, relu, training):
+    """dy: grad of the BN(+ReLU) output, x: saved raw conv output, dx: receives the grad of x.
+    Returns (dgamma, dbeta)."""
+    c = x.c
+    p = vec.data_ptr()
+    red = torch.empty((2 * c,), dtype=torch.float32, device=x.t.device)
+    lib = _lib.load()
+    _lib.check(lib.b200seg_bn_bwd_reduce(dy.ptr, dy.ct, dy.c_off, x.ptr, x.ct, x.c_off, c, x.pixels, p, p + 4 * c,
+                                         p + 8 * c, p + 12 * c, int(relu), red.data_ptr(), _stream()), 'bn_bwd_reduce')
+    _lib.check(lib.b200seg_bn_bwd_apply(dy.ptr, dy.ct, dy.c_off, x.ptr, x.ct, x.c_off, dx.ptr, dx.ct, dx.c_off, c,
+                                        x.pixels, p, p + 4 * c, p + 8 * c, p + 12 * c, int(relu), int(training),
+                                        red.data_ptr(), None, None, 0, _stream()), 'bn_bwd_apply')
+    _lib.count_launch(2)
+    return red[c:], red[:c]
+
+
+# ------------------------------------------------------------------------------------------------
+# resampling / pooling
+# ------------------------------------------------------------------------------------------------
+def upsample_fwd(x, y, align_corners=True):
+    _lib.check(_lib.load().b200seg_upsample_fwd(x.ptr, x.ct, x.c_off, x.n, x.h, x.w, y.ptr, y.ct, y.c_off, y.h, y.w,
+                                                x.c, int(align_corners), _stream()), 'upsample_fwd')
+    _lib.count_launch()
+
+
+def upsample_bwd(dy, dx, align_corners=True):
+    _lib.check(_lib.load().b200seg_upsample_bwd(dy.ptr, dy.ct, dy.c_off, dy.n, dy.h, dy.w, dx.ptr, dx.ct, dx.c_off,
+                                                dx.h, dx.w, dy.c, int(align_corners), _stream()), 'upsample_bwd')
+    _lib.count_launch()
+
+
+def _reduce_hw(fn, what, x):
+    ws = torch.empty((x.n * x.c,), dtype=torch.float32, device=x.t.device)
+    y = Act.empty(x.n, 1, 1, x.c, x.t.device)
+    _lib.check(fn(x.ptr, x.ct, x.c_off, x.n, x.h * x.w, x.c, ws.data_ptr(), y.ptr, _stream()), what)
+    _lib.count_launch(2)
+    return y
+
+
+def gap_fwd(x):
+    return _reduce_hw(_lib.load().b200seg_gap_fwd, 'gap_fwd', x)
+
+
+def sum_hw(x):
+    return _reduce_hw(_lib.load().b200seg_sum_hw, 'sum_hw', x)
+
+
+def broadcast_hw(v, y, scale=1.0, accumulate=False):
+    """v: Act [n,1,1,c] (full buffer) broadcast over y's H*W into the slice y."""
+    assert v.c_off == 0 and v.c == v.ct == y.c
+    _lib.check(_lib.load().b200seg_broadcast_hw(v.ptr, y.n, y.c, scale, y.ptr, y.ct, y.c_off, y.h * y.w,
+                                                int(accumulate), _stream()), 'broadcast_hw')
+    _lib.count_launch()
+
+
+def channel_sum(x):
+    out = torch.empty((x.c,), dtype=torch.float32, device=x.t.device)
+    _lib.check(_lib.load().b200seg_channel_sum(x.ptr, x.ct, x.c_off, x.c, x.pixels, out.data_ptr(), 0, _stream()),
+               'channel_sum')
+    _lib.count_launch()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# class map, loss, metrics
+# ------------------------------------------------------------------------------------------------
+def logits_upsample_fwd(x_nhwc_f32, nc, oh, ow, align_corners=True):
+    n, h, w, ct = x_nhwc_f32.shape
+    y = torch.empty((n, nc, oh, ow), dtype=torch.float32, device=x_nhwc_f32.device)
+    _lib.check(_lib.load().b200seg_logits_upsample_fwd(x_nhwc_f32.data_ptr(), ct, n, h, w, nc, y.data_ptr(), oh, ow,
+                                                       int(align_corners), _stream()), 'logits_upsample_fwd')
+    _lib.count_launch()
+    return y
+
+
+def logits_upsample_bwd(dy_nchw_f32, h, w, ct, align_corners=True):
+    n, nc, oh, ow = dy_nchw_f32.shape
+    dx = Act.empty(n, h, w, ct, dy_nchw_f32.device)
+    _lib.check(_lib.load().b200seg_logits_upsample_bwd(dy_nchw_f32.data_ptr(), n, nc, oh, ow, dx.ptr, ct, h, w,
+                                                       int(align_corners), _stream()), 'logits_upsample_bwd')
+    _lib.count_launch()
+    return dx
+
+
+def resize_nchw_fwd(x, oh, ow, align_corners=True):
+    n, c, h, w = x.shape
+    y = torch.empty((n, c, oh, ow), dtype=torch.float32, device=x.device)
+    _lib.check(_lib.load().b200seg_resize_nchw_fwd(x.data_ptr(), n * c, h, w, y.data_ptr(), oh, ow,
+                                                   int(align_corners), _stream()), 'resize_nchw_fwd')
+    _lib.count_launch()
+    return y
+
+
+def resize_nchw_bwd(dy, h, w, align_corners=True):
+    n, c, oh, ow = dy.shape
+    dx = torch.empty((n, c, h, w), dtype=torch.float32, device=dy.device)
+    _lib.check(_lib.load().b200seg_resize_nchw_bwd(dy.data_ptr(), n * c, oh, ow, dx.data_ptr(), h, w,
+                                                   int(align_corners), _stream()), 'resize_nchw_bwd')
+    _lib.count_launch()
+    return dx
+
+
+def softmax_ce(logits, targets, ignore_index=-100, want_grad=True):
+    """logits NCHW fp32, targets int64 [n, h, w].  Returns (acc, dlogits): ``acc`` is a 3-element fp64
+    device tensor (sum of -log p[target], number of valid pixels as int64 bits, status flag as int32
+    bits); dlogits = softmax - onehot (unscaled; 0 on ignored pixels) or None."""
+    n, nc, h, w = logits.shape
+    acc = torch.zeros((3,), dtype=torch.float64, device=logits.device)
+    dl = torch.empty_like(logits) if want_grad else None
+    p = acc.data_ptr()
+    _lib.check(_lib.load().b200seg_softmax_ce(logits.data_ptr(), targets.data_ptr(), n, nc, h * w, ignore_index, 1.0,
+                                              p, p + 8, dl.data_ptr() if want_grad else None, p + 16, _stream()),
+               'softmax_ce')
+    _lib.count_launch()
+    return acc, dl
+
+
+def argmax(logits):
+    n, nc, h, w = logits.shape
+    pred = torch.empty((n, h, w), dtype=torch.int64, device=logits.device)
+    _lib.check(_lib.load().b200seg_argmax(logits.data_ptr(), n, nc, h * w, pred.data_ptr(), _stream()), 'argmax')
+    _lib.count_launch()
+    return pred
+
+
+def confusion(pred, targets, nc, cm=None):
+    if cm is None:
+        cm = torch.zeros((nc, nc), dtype=torch.int64, device=pred.device)
+    _lib.check(_lib.load().b200seg_confusion(pred.data_ptr(), targets.data_ptr(), pred.numel(), nc, cm.data_ptr(),
+                                             _stream()), 'confusion')
+    _lib.count_launch()
+    return cm
+
+
+def argmax_confusion(logits, targets, cm=None):
+    n, nc, h, w = logits.shape
+    if cm is None:
+        cm = torch.zeros((nc, nc), dtype=torch.int64, device=logits.device)
+    _lib.check(_lib.load().b200seg_argmax_confusion(logits.data_ptr(), targets.data_ptr(), n, nc, h * w,
+                                                    cm.data_ptr(), _stream()), 'argmax_confusion')
+    _lib.count_launch()
+    return cm

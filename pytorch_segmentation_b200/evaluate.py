@@ -1,0 +1,51 @@
+"""``test(model, fetcher)`` — drop-in for test.py:14-73 on the sm_100a path.
+
+The reference loop issues three ``.item()`` host syncs per class per batch (test.py:38-46).  Here each
+batch is one fused argmax + confusion-histogram kernel accumulating into an int64 nc x nc matrix on the
+device; the host reads it once at the end (and, under torch.distributed, all-reduces that one matrix
+instead of three float vectors, test.py:51-57).  tp / fn / fp are exact integers; the reference's
+float32 accumulators stop being exact above 2**24 pixels per class.
+"""
+import torch
+import torch.distributed as dist
+
+from . import engine as E
+from .utils.utils import compute_loss, compute_metrics, counts_from_confusion
+
+
+@torch.no_grad()
+def test(model, fetcher, verbose=True):
+    model.eval()
+    classes = fetcher.loader.dataset.classes
+    num_classes = len(classes)
+    cm = None
+    loss_sum = None
+    batches = 0
+    for inputs, targets in fetcher:
+        outputs = model(inputs)
+        loss = compute_loss(outputs, targets, model)
+        loss_sum = loss if loss_sum is None else loss_sum + loss
+        batches += 1
+        if cm is None:
+            cm = torch.zeros((num_classes, num_classes), dtype=torch.int64, device=outputs.device)
+        logits = outputs if (outputs.dtype == torch.float32 and outputs.is_contiguous()) else outputs.float().contiguous()
+        if logits.shape[2:] == targets.shape[1:]:
+            E.argmax_confusion(logits, targets.contiguous(), cm)
+        else:
+            E.confusion(E.argmax(logits).reshape(-1), targets.reshape(-1).contiguous(), num_classes, cm)
+    if cm is None:
+        cm = torch.zeros((num_classes, num_classes), dtype=torch.int64)
+    if dist.is_available() and dist.is_initialized():
+        dist.all_reduce(cm, op=dist.ReduceOp.SUM)
+    tp, fn, fp = (t.cpu().float() for t in counts_from_confusion(cm))
+    T, P, R, miou, F1 = compute_metrics(tp, fn, fp)
+    if verbose:
+        val_loss = float(loss_sum) / max(batches, 1) if loss_sum is not None else 0.0
+        print('loss: %8g, mAP: %8g, F1: %8g, miou: %8g' % (val_loss, P.mean(), F1.mean(), miou.mean()))
+        order = range(num_classes) if num_classes < 10 else miou.argsort()[:5].tolist()
+        if num_classes >= 10:
+            print('top error 5')
+        for c_i in order:
+            print('cls: %8s, targets: %8d, pre: %8g, rec: %8g, iou: %8g, F1: %8g'
+                  % (classes[c_i], T[c_i], P[c_i], R[c_i], miou[c_i], F1[c_i]))
+    return miou.mean().item()

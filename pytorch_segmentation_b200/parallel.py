@@ -1,0 +1,107 @@
+"""Data-parallel gradient exchange: bucketed all-reduce overlapped with backward.
+
+The reference trains with one process per GPU (train.py:108-119) and leaves the gradient all-reduce to
+the external ``Trainer``'s DDP wrap.  This is the equivalent for the new path, without wrapping the
+model: parameters are grouped into ~25 MB buckets in reverse registration order (the order backward
+produces them); a post-accumulate-grad hook copies each gradient into its slot of the bucket's flat
+buffer, re-points ``param.grad`` at that slot, and — when the bucket is full — launches one
+asynchronous ``all_reduce`` (NCCL over NVLink/NVSwitch on GPUs, gloo in the CPU tests) while backward
+keeps running.  ``finish()`` waits for the outstanding buckets and averages.
+
+There is no collective on the data path itself: images are independent through every kernel
+(train-mode BatchNorm statistics stay per-GPU, as in the reference, which shows no SyncBN).
+"""
+import torch
+import torch.distributed as dist
+
+
+class GradBucketer:
+    def __init__(self, params, bucket_mb=25.0, first_bucket_mb=1.0, process_group=None, average=True):
+        self.params = [p for p in params if p.requires_grad]
+        self.group = process_group
+        self.average = average
+        self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
+        self._buckets = []          # (flat buffer, [(param, offset, numel)])
+        self._slot = {}             # id(param) -> (bucket index, offset, numel)
+        self._pending = []
+        self._ready = []
+        self._handles = []
+        self._build(bucket_mb, first_bucket_mb)
+        self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
+        self.enabled = True         # set False on non-final micro-steps of gradient accumulation
+
+    def _build(self, bucket_mb, first_bucket_mb):
+        cap = int(first_bucket_mb * (1 << 20))
+        cur, cur_bytes = [], 0
+        groups = []
+        for p in reversed(self.params):
+            nbytes = p.numel() * p.element_size()
+            if cur and (cur_bytes + nbytes > cap or cur[0].dtype != p.dtype or cur[0].device != p.device):
+                groups.append(cur)
+                cur, cur_bytes = [], 0
+                cap = int(bucket_mb * (1 << 20))
+            cur.append(p)
+            cur_bytes += nbytes
+        if cur:
+            groups.append(cur)
+        for bi, g in enumerate(groups):
+            total = sum(p.numel() for p in g)
+            flat = torch.zeros((total,), dtype=g[0].dtype, device=g[0].device)
+            slots, off = [], 0
+            for p in g:
+                slots.append((p, off, p.numel()))
+                self._slot[id(p)] = (bi, off, p.numel())
+                off += p.numel()
+            self._buckets.append((flat, slots))
+            self._pending.append(len(slots))
+        self._ready = [0] * len(self._buckets)
+
+    @property
+    def num_buckets(self):
+        return len(self._buckets)
+
+    def bucket_sizes(self):
+        return [b[0].numel() for b in self._buckets]
+
+    def _on_grad(self, p):
+        if not self.enabled:
+            return
+        bi, off, n = self._slot[id(p)]
+        flat = self._buckets[bi][0]
+        view = flat[off:off + n].view_as(p)
+        if p.grad.data_ptr() != view.data_ptr():
+            view.copy_(p.grad)
+            p.grad = view
+        self._ready[bi] += 1
+        if self._ready[bi] == self._pending[bi]:
+            self._launch(bi)
+
+    def _launch(self, bi):
+        if self.world > 1:
+            self._handles.append((bi, dist.all_reduce(self._buckets[bi][0], op=dist.ReduceOp.SUM, group=self.group,
+                                                      async_op=True)))
+
+    def finish(self):
+        """Call after backward (before the optimizer step): flushes partially filled buckets (parameters
+        that received no gradient contribute zeros), waits for the collectives and averages."""
+        launched = {bi for bi, _ in self._handles}
+        for bi in range(len(self._buckets)):
+            if self._ready[bi] != self._pending[bi] and self._ready[bi] >= 0 and self.enabled:
+                if bi not in launched and self._ready[bi] > 0:
+                    self._launch(bi)
+        for bi, h in self._handles:
+            h.wait()
+            if self.average and self.world > 1:
+                self._buckets[bi][0].div_(self.world)
+        self._handles = []
+        self._ready = [0] * len(self._buckets)
+
+    def zero_grad(self):
+        """Zero the flat buffers in place (gradients stay views of them)."""
+        for flat, _ in self._buckets:
+            flat.zero_()
+
+    def remove(self):
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []

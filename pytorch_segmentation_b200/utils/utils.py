@@ -1,0 +1,73 @@
+"""Loss and metric functions of the hot path — drop-ins for utils/utils.py:17-24 and :51-65."""
+import torch
+
+from .. import engine as E
+
+IGNORE_INDEX = -100      # nn.CrossEntropyLoss() default (utils/utils.py:12)
+
+
+class _CrossEntropyFn(torch.autograd.Function):
+    """bilinear(align_corners=True) resize to the target size + mean softmax cross-entropy."""
+
+    @staticmethod
+    def forward(ctx, outputs, targets):
+        E._require_cuda(outputs, 'compute_loss(outputs)')
+        E._require_cuda(targets, 'compute_loss(targets)')
+        if targets.dtype != torch.int64:
+            raise RuntimeError('compute_loss: expected int64 targets, got %s' % targets.dtype)
+        x = outputs.detach()
+        if x.dtype != torch.float32 or not x.is_contiguous():
+            x = x.float().contiguous()
+        th, tw = targets.shape[1], targets.shape[2]
+        resized = (x.shape[2], x.shape[3]) != (th, tw)
+        if resized:          # utils/utils.py:18-20; identity (skipped) when the sizes match
+            x = E.resize_nchw_fwd(x, th, tw, align_corners=True)
+        need = ctx.needs_input_grad[0]
+        acc, dl = E.softmax_ce(x, targets.contiguous(), IGNORE_INDEX, want_grad=need)
+        count = acc[1:2].view(torch.int64).to(torch.float64)
+        loss = (acc[0:1] / count).to(torch.float32).reshape(())
+        # an out-of-range target raises in the reference; here it poisons the loss (no host sync)
+        bad = acc[2:3].view(torch.int32)[0] != 0
+        loss = torch.where(bad, torch.full_like(loss, float('nan')), loss)
+        if need:
+            ctx.save_for_backward(dl, count)
+            ctx.resized, ctx.in_hw, ctx.in_dtype = resized, (outputs.shape[2], outputs.shape[3]), outputs.dtype
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        dl, count = ctx.saved_tensors
+        dl = dl * (g.to(torch.float32) / count.to(torch.float32))
+        if ctx.resized:
+            dl = E.resize_nchw_bwd(dl, ctx.in_hw[0], ctx.in_hw[1], align_corners=True)
+        return dl.to(ctx.in_dtype), None
+
+
+def compute_loss(outputs, targets, model=None):
+    """utils/utils.py:17-24: logits N x nc x h x w, int64 targets N x H x W -> 0-dim loss tensor."""
+    return _CrossEntropyFn.apply(outputs, targets)
+
+
+def compute_metrics(tp, fn, fp):
+    """utils/utils.py:51-65, same float32 op order (so identical integer counts give bit-identical
+    IoU / P / R / F1).  Host-side vectors of length num_classes; inputs are not modified."""
+    union = tp + fp + fn
+    union[union <= 0] = 1
+    miou = tp / union
+    T = tp + fn
+    P = tp + fp
+    P[P <= 0] = 1
+    P = tp / P
+    R = tp + fn
+    R[R <= 0] = 1
+    R = tp / R
+    F1 = (2 * tp + fp + fn)
+    F1[F1 <= 0] = 1
+    F1 = 2 * tp / F1
+    return T, P, R, miou, F1
+
+
+def counts_from_confusion(cm):
+    """tp / fn / fp of test.py:38-46 from the confusion matrix CM[target, predicted]."""
+    tp = cm.diag()
+    return tp, cm.sum(1) - tp, cm.sum(0) - tp

@@ -1,0 +1,343 @@
+"""Per-kernel parity of the C-ABI entry points against the CPU oracle (PyTorch fp32 on the host — the same
+library calls the reference makes).  Tolerances: bf16 kernels max|d|/max|ref| <= 2e-2 (BASELINE.json
+north_star), in practice ~4e-3; integer work bit-exact."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+TOL = 2e-2
+
+
+def rel_err(got, ref):
+    got, ref = got.detach().float().cpu(), ref.detach().float().cpu()
+    return float((got - ref).abs().max()) / max(float(ref.abs().max()), 1e-30)
+
+
+def bf16_round(t):
+    return t.to(torch.bfloat16).float()
+
+
+@pytest.fixture(scope='module')
+def E(lib):
+    from pytorch_segmentation_b200 import engine
+    return engine
+
+
+def nhwc(x):
+    """NCHW fp32 CPU -> Act on cuda"""
+    from pytorch_segmentation_b200.engine import Act
+    return Act(x.permute(0, 2, 3, 1).contiguous().to('cuda', torch.bfloat16))
+
+
+def from_act(a):
+    return a.nchw().float().cpu()
+
+
+CONV_CASES = [
+    # n, h, w, c, k, ksize, dil
+    (1, 8, 16, 64, 32, 1, 1),
+    (2, 32, 32, 128, 256, 3, 6),
+    (2, 32, 32, 192, 256, 3, 12),
+    (2, 32, 32, 64, 64, 3, 18),
+    (3, 10, 10, 160, 64, 3, 1),
+    (2, 20, 20, 352, 128, 3, 1),
+    (4, 1, 1, 256, 256, 1, 1),
+    (1, 40, 40, 128, 352, 3, 2),
+    (2, 17, 23, 88, 8, 3, 1),
+]
+
+
+@pytest.mark.parametrize('n,h,w,c,k,ks,dil', CONV_CASES)
+def test_conv_fprop_dgrad_wgrad(E, n, h, w, c, k, ks, dil):
+    g = torch.Generator().manual_seed(n * 1000 + h * 10 + c + k + dil)
+    x = bf16_round(torch.randn(n, c, h, w, generator=g))
+    wt = bf16_round(torch.randn(k, c, ks, ks, generator=g) * (2.0 / (c * ks * ks)) ** 0.5)
+    dy = bf16_round(torch.randn(n, k, h, w, generator=g))
+    pad = (ks // 2) * dil
+    x.requires_grad_(True)
+    wt.requires_grad_(True)
+    y_ref = F.conv2d(x, wt, None, 1, pad, dil)
+    y_ref.backward(dy)
+
+    pw = E.PackedWeight().update(wt.detach().cuda(), need_dgrad=True)
+    xa = nhwc(x.detach())
+    ya = E.Act.empty(n, h, w, k, 'cuda')
+    stats = torch.zeros(2 * k, device='cuda')
+    E.conv_fprop([(xa, pw, dil)], ya, stats=stats)
+    assert rel_err(from_act(ya), y_ref) < TOL
+    # fused BN statistics: sum and sum of squares of the fp32 accumulators
+    ref_sum = y_ref.detach().sum((0, 2, 3))
+    ref_sq = (y_ref.detach() ** 2).sum((0, 2, 3))
+    assert rel_err(stats[:k], ref_sum) < 2e-3 + 1e-3
+    assert rel_err(stats[k:], ref_sq) < 2e-3
+
+    dya = nhwc(dy)
+    dxa = E.Act.empty(n, h, w, c, 'cuda')
+    E.conv_dgrad([(dya, pw, dil)], dxa)
+    assert rel_err(from_act(dxa), x.grad) < TOL
+
+    dw = E.conv_wgrad(dya, xa, k, ks, ks, dil)
+    assert rel_err(dw, wt.grad) < 5e-3
+
+
+def test_conv_epilogue_scale_bias_relu_into_slice(E):
+    g = torch.Generator().manual_seed(5)
+    n, h, w, c, k = 2, 16, 16, 64, 128
+    x = bf16_round(torch.randn(n, c, h, w, generator=g))
+    wt = bf16_round(torch.randn(k, c, 1, 1, generator=g) * 0.2)
+    scale, bias = torch.rand(k, generator=g) + 0.5, torch.randn(k, generator=g)
+    ref = F.relu(F.conv2d(x, wt) * scale.view(1, -1, 1, 1) + bias.view(1, -1, 1, 1))
+    # input is a slice [64:128) of a 192-channel buffer, output a slice [256:384) of a 384-channel buffer
+    xb = torch.zeros(n, h, w, 192, dtype=torch.bfloat16, device='cuda')
+    xb[..., 64:128] = x.permute(0, 2, 3, 1).cuda()
+    yb = torch.zeros(n, h, w, 384, dtype=torch.bfloat16, device='cuda')
+    pw = E.PackedWeight().update(wt.cuda(), need_dgrad=False)
+    E.conv_fprop([(E.Act(xb, 64, 64), pw, 1)], E.Act(yb, 256, 128), scale=scale.cuda(), bias=bias.cuda(), relu=True)
+    assert rel_err(yb[..., 256:384].permute(0, 3, 1, 2), ref) < TOL
+    assert float(yb[..., :256].abs().max()) == 0.0      # neighbours untouched
+
+
+def test_conv_multi_source_sum(E):
+    """Two sources accumulate in TMEM: conv over a concat == sum of convs over the parts."""
+    g = torch.Generator().manual_seed(6)
+    n, h, w = 2, 12, 12
+    x1 = bf16_round(torch.randn(n, 64, h, w, generator=g))
+    x2 = bf16_round(torch.randn(n, 24, h, w, generator=g))
+    w1 = bf16_round(torch.randn(32, 64, 3, 3, generator=g) * 0.1)
+    w2 = bf16_round(torch.randn(32, 24, 1, 1, generator=g) * 0.1)
+    ref = F.conv2d(x1, w1, None, 1, 2, 2) + F.conv2d(x2, w2)
+    p1 = E.PackedWeight().update(w1.cuda(), False)
+    p2 = E.PackedWeight().update(w2.cuda(), False)
+    ya = E.Act.empty(n, h, w, 32, 'cuda')
+    E.conv_fprop([(nhwc(x1), p1, 2), (nhwc(x2), p2, 1)], ya)
+    assert rel_err(from_act(ya), ref) < TOL
+
+
+def test_cls_conv_fp32_narrow(E):
+    """21 classes padded to 24: fp32 NHWC class map with bias; wgrad/dgrad through the padded gradient."""
+    g = torch.Generator().manual_seed(7)
+    n, h, w, c, nc = 2, 24, 24, 384, 21
+    x = bf16_round(torch.randn(n, c, h, w, generator=g)).requires_grad_(True)
+    wt = bf16_round(torch.randn(nc, c, 3, 3, generator=g) * 0.05).requires_grad_(True)
+    b = torch.randn(nc, generator=g)
+    dy = bf16_round(torch.randn(n, nc, h, w, generator=g))
+    ref = F.conv2d(x, wt, b, 1, 1)
+    ref.backward(dy)
+    pw = E.PackedWeight().update(wt.detach().cuda(), True)
+    bias = torch.zeros(24, device='cuda')
+    bias[:nc] = b.cuda()
+    out = torch.empty(n, h, w, 24, device='cuda')
+    xa = nhwc(x.detach())
+    E.conv_fprop_f32([(xa, pw, 1)], out, 24, bias=bias)
+    assert rel_err(out[..., :nc].permute(0, 3, 1, 2), ref) < 5e-3
+    dyp = torch.zeros(n, h, w, 24, dtype=torch.bfloat16, device='cuda')
+    dyp[..., :nc] = dy.permute(0, 2, 3, 1).cuda()
+    dya = E.Act(dyp)
+    dxa = E.Act.empty(n, h, w, c, 'cuda')
+    E.conv_dgrad([(dya, pw, 1)], dxa)
+    assert rel_err(from_act(dxa), x.grad) < TOL
+    dw = E.conv_wgrad(dya, xa, nc, 3, 3, 1)
+    assert rel_err(dw, wt.grad) < 5e-3
+    assert rel_err(E.channel_sum(dya)[:nc], dy.sum((0, 2, 3))) < 1e-3
+
+
+@pytest.mark.parametrize('n,h,w,c,ct,off', [(2, 16, 16, 64, 64, 0), (3, 7, 9, 24, 88, 64), (16, 1, 1, 256, 256, 0),
+                                            (2, 32, 32, 2048, 2048, 0)])
+def test_batchnorm_train_forward_backward(E, n, h, w, c, ct, off):
+    g = torch.Generator().manual_seed(c + h)
+    x = bf16_round(torch.randn(n, c, h, w, generator=g) * 1.5 + 0.3).requires_grad_(True)
+    gamma = (1 + 0.2 * torch.randn(c, generator=g)).requires_grad_(True)
+    beta = (0.1 * torch.randn(c, generator=g)).requires_grad_(True)
+    rm, rv = 0.1 * torch.randn(c, generator=g), 1 + 0.1 * torch.rand(c, generator=g)
+    dz = bf16_round(torch.randn(n, c, h, w, generator=g))
+    rm_ref, rv_ref = rm.clone(), rv.clone()
+    z_ref = F.relu(F.batch_norm(x, rm_ref, rv_ref, gamma, beta, True, 0.1, 1e-5))
+    z_ref.backward(dz)
+
+    xb = torch.zeros(n, h, w, ct, dtype=torch.bfloat16, device='cuda')
+    xb[..., off:off + c] = x.detach().permute(0, 2, 3, 1).cuda()
+    xa = E.Act(xb, off, c)
+    stats = E.bn_stats(xa)
+    rm_d, rv_d = rm.cuda(), rv.cuda()
+    vec = E.bn_finalize(stats, c, n * h * w, gamma.detach().cuda(), beta.detach().cuda(), 1e-5, 0.1, rm_d, rv_d)
+    za = E.Act.empty(n, h, w, c, 'cuda')
+    E.bn_apply(xa, za, vec, True)
+    assert rel_err(from_act(za), z_ref) < TOL
+    assert rel_err(rm_d, rm_ref) < 1e-3 and rel_err(rv_d, rv_ref) < 1e-3
+    dza = nhwc(dz)
+    dxa = E.Act.empty(n, h, w, c, 'cuda')
+    dgamma, dbeta = E.bn_backward(dza, xa, dxa, vec, True, True)
+    assert rel_err(from_act(dxa), x.grad) < TOL
+    assert rel_err(dgamma, gamma.grad) < 5e-3 and rel_err(dbeta, beta.grad) < 5e-3
+
+
+def test_batchnorm_eval_affine_and_backward(E):
+    g = torch.Generator().manual_seed(3)
+    n, h, w, c = 2, 8, 8, 32
+    x = bf16_round(torch.randn(n, c, h, w, generator=g)).requires_grad_(True)
+    gamma = (1 + 0.2 * torch.randn(c, generator=g)).requires_grad_(True)
+    beta = (0.1 * torch.randn(c, generator=g)).requires_grad_(True)
+    rm, rv = 0.1 * torch.randn(c, generator=g), 1 + 0.1 * torch.rand(c, generator=g)
+    dz = bf16_round(torch.randn(n, c, h, w, generator=g))
+    z_ref = F.relu(F.batch_norm(x, rm, rv, gamma, beta, False, 0.1, 1e-5))
+    z_ref.backward(dz)
+    vec = E.bn_eval_affine(c, gamma.detach().cuda(), beta.detach().cuda(), rm.cuda(), rv.cuda(), 1e-5)
+    xa, za = nhwc(x.detach()), E.Act.empty(n, h, w, c, 'cuda')
+    E.bn_apply(xa, za, vec, True)
+    assert rel_err(from_act(za), z_ref) < TOL
+    dxa = E.Act.empty(n, h, w, c, 'cuda')
+    dgamma, dbeta = E.bn_backward(nhwc(dz), xa, dxa, vec, True, False)
+    assert rel_err(from_act(dxa), x.grad) < TOL
+    assert rel_err(dgamma, gamma.grad) < 5e-3 and rel_err(dbeta, beta.grad) < 5e-3
+
+
+@pytest.mark.parametrize('h,w,oh,ow,ac', [(8, 8, 32, 32, True), (10, 10, 20, 20, True), (5, 7, 20, 28, True),
+                                           (8, 8, 8, 8, True), (6, 9, 13, 31, False), (1, 1, 16, 16, False),
+                                           (16, 16, 7, 5, True)])
+def test_bilinear_upsample_and_adjoint(E, h, w, oh, ow, ac):
+    g = torch.Generator().manual_seed(h * w + oh)
+    n, c = 2, 24
+    x = bf16_round(torch.randn(n, c, h, w, generator=g)).requires_grad_(True)
+    dy = bf16_round(torch.randn(n, c, oh, ow, generator=g))
+    ref = F.interpolate(x, size=(oh, ow), mode='bilinear', align_corners=ac)
+    ref.backward(dy)
+    # into a slice of a wider buffer
+    yb = torch.zeros(n, oh, ow, 40, dtype=torch.bfloat16, device='cuda')
+    E.upsample_fwd(nhwc(x.detach()), E.Act(yb, 8, c), align_corners=ac)
+    assert rel_err(yb[..., 8:8 + c].permute(0, 3, 1, 2), ref) < 1e-2
+    assert float(yb[..., :8].abs().max()) == 0.0 and float(yb[..., 32:].abs().max()) == 0.0
+    dxa = E.Act.empty(n, h, w, c, 'cuda')
+    E.upsample_bwd(nhwc(dy), dxa, align_corners=ac)
+    assert rel_err(from_act(dxa), x.grad) < 1e-2
+
+
+def test_gap_broadcast_sum(E):
+    g = torch.Generator().manual_seed(9)
+    n, c, h, w = 3, 2048, 16, 16
+    x = bf16_round(torch.randn(n, c, h, w, generator=g))
+    xa = nhwc(x)
+    ga = E.gap_fwd(xa)
+    assert rel_err(ga.t.reshape(n, c), x.mean((2, 3))) < 1e-2
+    sa = E.sum_hw(xa)
+    assert rel_err(sa.t.reshape(n, c), x.sum((2, 3))) < 1e-2
+    yb = torch.zeros(n, h, w, c + 8, dtype=torch.bfloat16, device='cuda')
+    E.broadcast_hw(ga, E.Act(yb, 8, c))
+    assert torch.equal(yb[..., 8:], ga.t.reshape(n, 1, 1, c).expand(n, h, w, c))
+    base = bf16_round(torch.randn(n, c, h, w, generator=g))
+    ba = nhwc(base)
+    E.broadcast_hw(ga, ba, scale=0.5, accumulate=True)
+    ref = base + 0.5 * ga.t.reshape(n, c, 1, 1).float().cpu()
+    assert rel_err(from_act(ba), ref) < 1e-2
+
+
+@pytest.mark.parametrize('nc,h,w,oh,ow', [(21, 8, 8, 32, 32), (2, 10, 12, 20, 24), (19, 6, 5, 24, 20)])
+def test_logits_upsample_and_adjoint(E, nc, h, w, oh, ow):
+    g = torch.Generator().manual_seed(nc)
+    n = 2
+    ncp = (nc + 7) // 8 * 8
+    x = torch.randn(n, nc, h, w, generator=g).requires_grad_(True)
+    dy = torch.randn(n, nc, oh, ow, generator=g)
+    ref = F.interpolate(x, size=(oh, ow), mode='bilinear', align_corners=True)
+    ref.backward(dy)
+    xp = torch.zeros(n, h, w, ncp)
+    xp[..., :nc] = x.detach().permute(0, 2, 3, 1)
+    y = E.logits_upsample_fwd(xp.cuda(), nc, oh, ow, True)
+    assert rel_err(y, ref) < 1e-5
+    dxa = E.logits_upsample_bwd(dy.cuda(), h, w, ncp, True)
+    got = dxa.t.float().cpu()
+    assert rel_err(got[..., :nc].permute(0, 3, 1, 2), x.grad) < 1e-2
+    assert float(got[..., nc:].abs().max()) == 0.0 if ncp > nc else True
+
+
+def test_resize_nchw_and_adjoint(E):
+    g = torch.Generator().manual_seed(4)
+    x = torch.randn(2, 5, 8, 16, generator=g).requires_grad_(True)
+    dy = torch.randn(2, 5, 29, 37, generator=g)
+    ref = F.interpolate(x, size=(29, 37), mode='bilinear', align_corners=True)
+    ref.backward(dy)
+    assert rel_err(E.resize_nchw_fwd(x.detach().cuda(), 29, 37, True), ref) < 1e-5
+    assert rel_err(E.resize_nchw_bwd(dy.cuda(), 8, 16, True), x.grad) < 1e-5
+
+
+@pytest.mark.parametrize('nc', [2, 21, 19, 40])
+def test_softmax_cross_entropy(E, nc):
+    g = torch.Generator().manual_seed(nc)
+    n, h, w = 3, 17, 23
+    logits = (torch.randn(n, nc, h, w, generator=g) * 3).requires_grad_(True)
+    tgt = torch.randint(0, nc, (n, h, w), generator=g)
+    tgt[0, 0, :5] = -100                                  # ignore_index pixels
+    loss_ref = F.cross_entropy(logits, tgt)
+    loss_ref.backward()
+    acc, dl = E.softmax_ce(logits.detach().cuda(), tgt.cuda(), -100, True)
+    count = int(acc[1:2].view(torch.int64))
+    assert count == int((tgt != -100).sum())
+    assert abs(float(acc[0]) / count - float(loss_ref)) < 1e-5 * max(1.0, abs(float(loss_ref)))
+    assert int(acc[2:3].view(torch.int32)[0]) == 0
+    assert rel_err(dl / count, logits.grad) < 1e-5
+    # out-of-range target sets the status flag
+    bad = tgt.clone()
+    bad[1, 2, 3] = nc
+    acc, _ = E.softmax_ce(logits.detach().cuda(), bad.cuda(), -100, False)
+    assert int(acc[2:3].view(torch.int32)[0]) == 1
+
+
+@pytest.mark.parametrize('nc', [2, 5, 21, 19, 64])
+def test_argmax_and_confusion_bit_exact(E, nc):
+    g = torch.Generator().manual_seed(100 + nc)
+    n, h, w = 2, 37, 41
+    logits = torch.randn(n, nc, h, w, generator=g)
+    logits[0, :, 0, 0] = 1.0                               # full tie -> lowest index
+    logits[1, nc - 1, 3, 3] = logits[1, 0, 3, 3] = 9.0     # two-way tie -> index 0
+    tgt = torch.randint(0, nc, (n, h, w), generator=g)
+    pred_ref = logits.max(1)[1]
+    pred = E.argmax(logits.cuda())
+    assert torch.equal(pred.cpu(), pred_ref)
+    cm_ref = torch.bincount(tgt.reshape(-1) * nc + pred_ref.reshape(-1), minlength=nc * nc).reshape(nc, nc)
+    cm = E.confusion(pred, tgt.cuda(), nc)
+    assert torch.equal(cm.cpu(), cm_ref)
+    cm2 = E.argmax_confusion(logits.cuda(), tgt.cuda())
+    assert torch.equal(cm2.cpu(), cm_ref)
+    # accumulation across calls and labels outside [0, nc) skipped
+    tgt2 = tgt.clone()
+    tgt2[0, 0, :7] = 255
+    E.confusion(pred, tgt2.cuda(), nc, cm)
+    keep = tgt2.reshape(-1) < nc
+    cm_ref2 = cm_ref + torch.bincount((tgt2.reshape(-1) * nc + pred_ref.reshape(-1))[keep],
+                                      minlength=nc * nc).reshape(nc, nc)
+    assert torch.equal(cm.cpu(), cm_ref2)
+
+
+def test_confusion_skewed_and_large(E):
+    """Uniform regions (every lane of a warp hits one bin) and > 2**24 pixels: int64 counts stay exact
+    where the reference's float32 accumulators (test.py:22-24) would not."""
+    nc = 21
+    n = 1 << 25
+    tgt = torch.zeros(n, dtype=torch.int64, device='cuda')
+    pred = torch.zeros(n, dtype=torch.int64, device='cuda')
+    pred[::3] = 7
+    cm = E.confusion(pred, tgt, nc)
+    assert int(cm[0, 7]) == (n + 2) // 3 and int(cm[0, 0]) == n - (n + 2) // 3 and int(cm.sum()) == n
+
+
+def test_layout_kernels_roundtrip(E, lib):
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(2, 24, 9, 11, generator=g)
+    a = E.as_act(x.cuda())
+    assert torch.equal(a.t.cpu(), x.to(torch.bfloat16).permute(0, 2, 3, 1))
+    back = E.grad_like(x.cuda(), a)
+    assert torch.equal(back.cpu(), bf16_round(x))
+    # bf16 channels_last input is a zero-copy view
+    xc = x.cuda().to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    assert E.as_act(xc).ptr == xc.data_ptr()
+
+
+def test_errors_are_loud(E):
+    with pytest.raises(RuntimeError, match='no CPU fallback'):
+        E.as_act(torch.zeros(1, 8, 4, 4))
+    with pytest.raises(ValueError, match='multiple of 8'):
+        E.as_act(torch.zeros(1, 3, 4, 4, device='cuda'))
+    from pytorch_segmentation_b200 import ConvNormAct
+    with pytest.raises(NotImplementedError):
+        ConvNormAct(8, 8, 3, 2)
