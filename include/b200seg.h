@@ -69,8 +69,9 @@ typedef struct b200seg_conv_out {
     const float* bias;    /* per-channel addend or NULL (BN shift, or nn.Conv2d bias) — length >= k */
     int32_t relu;
     float* stats;         /* NULL, or fp32 [2*k] zeroed by the caller: the epilogue adds the per-channel sum and sum
-                             of squares of the raw fp32 accumulators (before scale/bias/relu) — the training-mode
-                             nn.BatchNorm2d statistics of ConvNormAct without a second pass over the output */
+                             of squares of the conv result as stored (rounded to bf16 when the output is bf16; before
+                             scale/bias/relu) — the training-mode nn.BatchNorm2d statistics of ConvNormAct
+                             without a second pass over the output */
 } b200seg_conv_out;
 
 /* y = act(scale * sum_src conv(x_src, w_src) + bias).
@@ -142,17 +143,30 @@ int b200seg_upsample_fwd(const void* x, int x_c_total, int x_c_offset, int n, in
 int b200seg_upsample_bwd(const void* dy, int dy_c_total, int dy_c_offset, int n, int oh, int ow, void* dx,
                          int dx_c_total, int dx_c_offset, int h, int w, int c, int align_corners,
                          b200seg_stream_t st);
-/* nn.AdaptiveAvgPool2d(1) (models/aspp.py:11): mean over H*W of an NHWC slice -> bf16 [n][c].
- * acc_ws: caller-provided fp32 [n*c] scratch (the H*W range is split across CTAs). */
-int b200seg_gap_fwd(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, float* acc_ws, void* y,
-                    b200seg_stream_t st);
-/* Broadcast a per-image vector over H*W into a slice: the 1x1 -> HxW bilinear(align_corners=False) of
- * models/aspp.py:16-19, and (with scale = 1/HW, accumulate) the backward of the average pool. */
-int b200seg_broadcast_hw(const void* v, int n, int c, float scale, void* y, int y_c_total, int y_c_offset, int hw,
+/* nn.AdaptiveAvgPool2d(1) (models/aspp.py:11): mean over H*W of an NHWC bf16 slice -> fp32 [n][c]
+ * (the H*W range is split across CTAs; fp32 atomics into y). */
+int b200seg_gap_fwd(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, float* y, b200seg_stream_t st);
+/* Broadcast a per-image fp32 vector [n][c] over H*W into a bf16 slice: the 1x1 -> HxW bilinear
+ * (align_corners=False) of models/aspp.py:16-19, and (with scale = 1/HW, accumulate) the backward of the
+ * average pool. */
+int b200seg_broadcast_hw(const float* v, int n, int c, float scale, void* y, int y_c_total, int y_c_offset, int hw,
                          int accumulate, b200seg_stream_t st);
-/* Sum an NHWC slice over H*W -> bf16 [n][c] (backward of the broadcast above). */
-int b200seg_sum_hw(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, float* acc_ws, void* y,
-                   b200seg_stream_t st);
+/* Sum an NHWC bf16 slice over H*W -> fp32 [n][c] (backward of the broadcast above). */
+int b200seg_sum_hw(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, float* y, b200seg_stream_t st);
+
+/* ---- the image-pooling branch after the pool: fp32 CUDA-core kernels on [n][c] rows ----------------------- */
+/* 1x1 ConvNormAct on the N x C x 1 x 1 pooled map (models/aspp.py:12): y[n][k] = sum_c x[n][c] * w[k][c] with w the
+ * fp32 OIHW master weight itself; its two gradients; BatchNorm(+ReLU) over the n rows and its backward. */
+int b200seg_linear_f32_fwd(const float* x, const float* w, float* y, int n, int c, int k, b200seg_stream_t st);
+int b200seg_linear_f32_bwd_data(const float* dy, const float* w, float* dx, int n, int c, int k, b200seg_stream_t st);
+int b200seg_linear_f32_bwd_weight(const float* dy, const float* x, float* dw, int n, int c, int k, int accumulate,
+                                  b200seg_stream_t st);
+int b200seg_bn_rows_fwd(const float* x, int n, int k, const float* gamma, const float* beta, float eps, float momentum,
+                        float* running_mean, float* running_var, int training, int relu, float* y, float* save_mean,
+                        float* save_invstd, b200seg_stream_t st);
+int b200seg_bn_rows_bwd(const float* dy, const float* x, int n, int k, const float* gamma, const float* beta,
+                        const float* save_mean, const float* save_invstd, int training, int relu, float* dx, float* dgamma,
+                        float* dbeta, b200seg_stream_t st);
 /* Per-channel sum over all pixels of a bf16 NHWC slice -> fp32 [c] (bias gradient of cls_conv). */
 int b200seg_channel_sum(const void* x, int x_c_total, int x_c_offset, int c, int64_t pixels, float* out,
                         int accumulate, b200seg_stream_t st);

@@ -182,6 +182,13 @@ class OracleModel:
             for k in self.sd:
                 self.sd[k].copy_(state[k])
 
+    def to(self, device):
+        """Moves the oracle (tests use the GPU copy under autocast to measure the bf16 noise floor of a
+        library implementation; the parity reference itself stays fp32 on the CPU)."""
+        self.backbone.to(device)
+        self.sd = {k: v.detach().to(device).requires_grad_(v.requires_grad) for k, v in self.sd.items()}
+        return self
+
     def zero_grad(self):
         self.backbone.zero_grad()
         for v in self.sd.values():

@@ -62,8 +62,13 @@ PROTOTYPES = {
                                      _P, _I, _P]),
     'b200seg_upsample_fwd': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _I, _I, _P]),
     'b200seg_upsample_bwd': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _I, _I, _P]),
-    'b200seg_gap_fwd': (c_int, [_P, _I, _I, _I, _I, _I, _P, _P, _P]),
-    'b200seg_sum_hw': (c_int, [_P, _I, _I, _I, _I, _I, _P, _P, _P]),
+    'b200seg_gap_fwd': (c_int, [_P, _I, _I, _I, _I, _I, _P, _P]),
+    'b200seg_sum_hw': (c_int, [_P, _I, _I, _I, _I, _I, _P, _P]),
+    'b200seg_linear_f32_fwd': (c_int, [_P, _P, _P, _I, _I, _I, _P]),
+    'b200seg_linear_f32_bwd_data': (c_int, [_P, _P, _P, _I, _I, _I, _P]),
+    'b200seg_linear_f32_bwd_weight': (c_int, [_P, _P, _P, _I, _I, _I, _I, _P]),
+    'b200seg_bn_rows_fwd': (c_int, [_P, _I, _I, _P, _P, _F, _F, _P, _P, _I, _I, _P, _P, _P, _P]),
+    'b200seg_bn_rows_bwd': (c_int, [_P, _P, _I, _I, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P]),
     'b200seg_broadcast_hw': (c_int, [_P, _I, _I, _F, _P, _I, _I, _I, _I, _P]),
     'b200seg_channel_sum': (c_int, [_P, _I, _I, _I, _L, _P, _I, _P]),
     'b200seg_logits_upsample_fwd': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _P]),

@@ -221,7 +221,10 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
                     float s1[32], s2[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
-                        const float a = valid ? __uint_as_float(v[j]) : 0.f;
+                        // statistics of the values as stored (bf16-rounded), so the saved mean / inv-std are
+                        // exactly those of the tensor the backward pass re-reads
+                        float a = valid ? __uint_as_float(v[j]) : 0.f;
+                        if (!p.out_fp32) a = __bfloat162float(__float2bfloat16(a));
                         s1[j] = a;
                         s2[j] = a * a;
                     }

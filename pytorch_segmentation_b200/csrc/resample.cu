@@ -109,14 +109,13 @@ __global__ void __launch_bounds__(256) reduce_hw_kernel(const __nv_bfloat16* __r
     }
 }
 
-__global__ void scale_to_bf16_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ y, int64_t total,
-                                     float scale) {
+__global__ void scale_inplace_kernel(float* __restrict__ y, int64_t total, float scale) {
     const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
-    if (i < total) y[i] = __float2bfloat16(acc[i] * scale);
+    if (i < total) y[i] *= scale;
 }
 
-// y[n, p, slice] (+)= scale * v[n, :]
-__global__ void __launch_bounds__(256) broadcast_hw_kernel(const __nv_bfloat16* __restrict__ v, int c, float scale,
+// y[n, p, slice] (+)= scale * v[n, :]   (v fp32 [n][c])
+__global__ void __launch_bounds__(256) broadcast_hw_kernel(const float* __restrict__ v, int c, float scale,
                                                             __nv_bfloat16* __restrict__ y, int y_ct, int y_off, int hw,
                                                             int groups, int64_t total, int accumulate) {
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
@@ -125,7 +124,7 @@ __global__ void __launch_bounds__(256) broadcast_hw_kernel(const __nv_bfloat16* 
         const int64_t p = i / groups;          // n * hw + pixel
         const int n = static_cast<int>(p / hw);
         float f[8];
-        unpack8(ldg128(v + static_cast<int64_t>(n) * c + g * 8), f);
+        load8f(v + static_cast<int64_t>(n) * c + g * 8, f);
         __nv_bfloat16* dst = y + p * y_ct + y_off + g * 8;
         if (accumulate) {
             float o[8];
@@ -141,12 +140,12 @@ __global__ void __launch_bounds__(256) broadcast_hw_kernel(const __nv_bfloat16* 
 }
 
 int reduce_hw(const char* what, const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, float scale,
-              float* acc_ws, void* y, cudaStream_t st) {
+              float* y, cudaStream_t st) {
     clear_error();
     if (check_slice(what, x, x_c_total, x_c_offset, c)) return 1;
-    B200SEG_CHECK(n > 0 && hw > 0 && acc_ws && y, "%s: bad arguments", what);
+    B200SEG_CHECK(n > 0 && hw > 0 && y, "%s: bad arguments", what);
     const int64_t total = static_cast<int64_t>(n) * c;
-    B200SEG_CUDA(cudaMemsetAsync(acc_ws, 0, sizeof(float) * total, st));
+    B200SEG_CUDA(cudaMemsetAsync(y, 0, sizeof(float) * total, st));
     const int groups = c / 8;
     const int gpb = groups < 256 ? groups : 256;
     const int rows = 256 / gpb;
@@ -159,11 +158,12 @@ int reduce_hw(const char* what, const void* x, int x_c_total, int x_c_offset, in
     if (splits < 1) splits = 1;
     const int chunk = round_up(ceil_div(hw, splits), rows);
     reduce_hw_kernel<<<dim3(ceil_div(hw, chunk), gy, n), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), x_c_total,
-                                                                      x_c_offset, hw, c, gpb, rows, chunk, acc_ws);
+                                                                      x_c_offset, hw, c, gpb, rows, chunk, y);
     B200SEG_LAUNCH_CHECK();
-    scale_to_bf16_kernel<<<static_cast<unsigned>(ceil_div64(total, 256)), 256, 0, st>>>(
-        acc_ws, static_cast<__nv_bfloat16*>(y), total, scale);
-    B200SEG_LAUNCH_CHECK();
+    if (scale != 1.f) {
+        scale_inplace_kernel<<<static_cast<unsigned>(ceil_div64(total, 256)), 256, 0, st>>>(y, total, scale);
+        B200SEG_LAUNCH_CHECK();
+    }
     return 0;
 }
 
@@ -204,19 +204,18 @@ int b200seg_upsample_bwd(const void* dy, int dy_c_total, int dy_c_offset, int n,
     return 0;
 }
 
-int b200seg_gap_fwd(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, float* acc_ws, void* y,
+int b200seg_gap_fwd(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, float* y,
                     b200seg_stream_t stream) {
-    return b200seg::reduce_hw("gap_fwd", x, x_c_total, x_c_offset, n, hw, c, 1.f / static_cast<float>(hw), acc_ws, y,
+    return b200seg::reduce_hw("gap_fwd", x, x_c_total, x_c_offset, n, hw, c, 1.f / static_cast<float>(hw), y,
                               static_cast<cudaStream_t>(stream));
 }
 
-int b200seg_sum_hw(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, float* acc_ws, void* y,
+int b200seg_sum_hw(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, float* y,
                    b200seg_stream_t stream) {
-    return b200seg::reduce_hw("sum_hw", x, x_c_total, x_c_offset, n, hw, c, 1.f, acc_ws, y,
-                              static_cast<cudaStream_t>(stream));
+    return b200seg::reduce_hw("sum_hw", x, x_c_total, x_c_offset, n, hw, c, 1.f, y, static_cast<cudaStream_t>(stream));
 }
 
-int b200seg_broadcast_hw(const void* v, int n, int c, float scale, void* y, int y_c_total, int y_c_offset, int hw,
+int b200seg_broadcast_hw(const float* v, int n, int c, float scale, void* y, int y_c_total, int y_c_offset, int hw,
                          int accumulate, b200seg_stream_t stream) {
     using namespace b200seg;
     clear_error();
@@ -224,8 +223,7 @@ int b200seg_broadcast_hw(const void* v, int n, int c, float scale, void* y, int 
     B200SEG_CHECK(v && n > 0 && hw > 0 && (reinterpret_cast<uintptr_t>(v) & 15) == 0, "broadcast_hw: bad arguments");
     const int64_t total = static_cast<int64_t>(n) * hw * (c / 8);
     broadcast_hw_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const __nv_bfloat16*>(v), c, scale, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset, hw, c / 8,
-        total, accumulate);
+        v, c, scale, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset, hw, c / 8, total, accumulate);
     B200SEG_LAUNCH_CHECK();
     return 0;
 }

@@ -135,7 +135,25 @@ class PackedWeight:
 # ------------------------------------------------------------------------------------------------
 # convolution
 # ------------------------------------------------------------------------------------------------
+# bench.py sets this to a list to time every tcgen05 conv launch with CUDA events on the launching stream:
+# entries are (kind, nominal dense flops, start event, end event)
+PROFILE = None
+
+
 def _conv(fn, what, n, h, w, srcs, out_ptr, y_ct, y_off, k, out_fp32, scale, bias, relu, stats):
+    if PROFILE is not None:
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        flops = 2.0 * n * h * w * k * sum(x.c * r * s for x, _, _, r, s, _ in srcs)
+        tag = '%s %dx%dx%d k%d %s' % (what, n, h, w, k, '+'.join('c%d r%d d%d' % (x.c, r, d) for x, _, _, r, _, d in srcs))
+        ev0.record()
+        _conv_launch(fn, what, n, h, w, srcs, out_ptr, y_ct, y_off, k, out_fp32, scale, bias, relu, stats)
+        ev1.record()
+        PROFILE.append((tag, flops, ev0, ev1))
+        return
+    _conv_launch(fn, what, n, h, w, srcs, out_ptr, y_ct, y_off, k, out_fp32, scale, bias, relu, stats)
+
+
+def _conv_launch(fn, what, n, h, w, srcs, out_ptr, y_ct, y_off, k, out_fp32, scale, bias, relu, stats):
     arr = (ConvSrc * len(srcs))()
     for i, (x, wptr, w_rows, r, s, dil) in enumerate(srcs):
         arr[i] = ConvSrc(x.ptr, x.ct, x.c_off, x.c, wptr, w_rows, r, s, dil)
@@ -190,7 +208,14 @@ def conv_wgrad(dy, x, k_out, r, s, dil, dw=None):
         raise RuntimeError('conv_wgrad: %s' % _lib.last_error())
     ws = torch.empty((nbytes,), dtype=torch.uint8, device=x.t.device)
     desc.workspace, desc.workspace_bytes = ws.data_ptr(), nbytes
+    if PROFILE is not None:
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
     _lib.check(lib.b200seg_conv_wgrad(ctypes.byref(desc), _stream()), 'conv_wgrad')
+    if PROFILE is not None:
+        ev1.record()
+        PROFILE.append(('conv_wgrad %dx%dx%d k%d c%d r%d d%d' % (x.n, x.h, x.w, dy.c, x.c, r, dil),
+                        2.0 * x.pixels * dy.c * x.c * r * s, ev0, ev1))
     _lib.count_launch(2)
     return dw
 
@@ -269,27 +294,89 @@ def upsample_bwd(dy, dx, align_corners=True):
 
 
 def _reduce_hw(fn, what, x):
-    ws = torch.empty((x.n * x.c,), dtype=torch.float32, device=x.t.device)
-    y = Act.empty(x.n, 1, 1, x.c, x.t.device)
-    _lib.check(fn(x.ptr, x.ct, x.c_off, x.n, x.h * x.w, x.c, ws.data_ptr(), y.ptr, _stream()), what)
+    y = torch.empty((x.n, x.c), dtype=torch.float32, device=x.t.device)
+    _lib.check(fn(x.ptr, x.ct, x.c_off, x.n, x.h * x.w, x.c, y.data_ptr(), _stream()), what)
     _lib.count_launch(2)
     return y
 
 
 def gap_fwd(x):
+    """mean over H*W -> fp32 [n, c]"""
     return _reduce_hw(_lib.load().b200seg_gap_fwd, 'gap_fwd', x)
 
 
 def sum_hw(x):
+    """sum over H*W -> fp32 [n, c]"""
     return _reduce_hw(_lib.load().b200seg_sum_hw, 'sum_hw', x)
 
 
 def broadcast_hw(v, y, scale=1.0, accumulate=False):
-    """v: Act [n,1,1,c] (full buffer) broadcast over y's H*W into the slice y."""
-    assert v.c_off == 0 and v.c == v.ct == y.c
-    _lib.check(_lib.load().b200seg_broadcast_hw(v.ptr, y.n, y.c, scale, y.ptr, y.ct, y.c_off, y.h * y.w,
+    """v: fp32 [n, c] broadcast over y's H*W into the bf16 slice y (optionally y += scale * v)."""
+    assert v.dtype == torch.float32 and v.is_contiguous() and tuple(v.shape) == (y.n, y.c), (v.shape, y.n, y.c)
+    _lib.check(_lib.load().b200seg_broadcast_hw(v.data_ptr(), y.n, y.c, scale, y.ptr, y.ct, y.c_off, y.h * y.w,
                                                 int(accumulate), _stream()), 'broadcast_hw')
     _lib.count_launch()
+
+
+def linear_f32_fwd(x, w):
+    """x fp32 [n, c], w fp32 [k, c, 1, 1] (the master weight) -> fp32 [n, k]"""
+    n, c = x.shape
+    k = w.shape[0]
+    w = w.detach()
+    assert w.dtype == torch.float32 and w.is_contiguous() and w.numel() == k * c
+    y = torch.empty((n, k), dtype=torch.float32, device=x.device)
+    _lib.check(_lib.load().b200seg_linear_f32_fwd(x.data_ptr(), w.data_ptr(), y.data_ptr(), n, c, k, _stream()),
+               'linear_f32_fwd')
+    _lib.count_launch()
+    return y
+
+
+def linear_f32_bwd(dy, x, w, need_dx=True):
+    """-> (dx fp32 [n, c] or None, dw fp32 shaped like w)"""
+    n, k = dy.shape
+    c = x.shape[1]
+    w = w.detach()
+    lib = _lib.load()
+    dw = torch.empty_like(w)
+    _lib.check(lib.b200seg_linear_f32_bwd_weight(dy.data_ptr(), x.data_ptr(), dw.data_ptr(), n, c, k, 0, _stream()),
+               'linear_f32_bwd_weight')
+    dx = None
+    if need_dx:
+        dx = torch.empty((n, c), dtype=torch.float32, device=dy.device)
+        _lib.check(lib.b200seg_linear_f32_bwd_data(dy.data_ptr(), w.data_ptr(), dx.data_ptr(), n, c, k, _stream()),
+                   'linear_f32_bwd_data')
+    _lib.count_launch(2 if need_dx else 1)
+    return dx, dw
+
+
+def bn_rows_fwd(x, bn, training, relu):
+    """BatchNorm(+ReLU) over the rows of x fp32 [n, k] with an nn.BatchNorm2d's parameters.
+    -> (y fp32 [n, k], save [2, k] = mean / invstd)"""
+    n, k = x.shape
+    y = torch.empty_like(x)
+    save = torch.empty((2, k), dtype=torch.float32, device=x.device)
+    track = bn.track_running_stats and bn.running_mean is not None
+    if not training and not track:
+        raise RuntimeError('eval-mode BatchNorm without running statistics')
+    _lib.check(_lib.load().b200seg_bn_rows_fwd(
+        x.data_ptr(), n, k, bn.weight.data_ptr(), bn.bias.data_ptr(), bn.eps, bn.momentum if bn.momentum else 0.0,
+        bn.running_mean.data_ptr() if track else None, bn.running_var.data_ptr() if track else None, int(training),
+        int(relu), y.data_ptr(), save.data_ptr(), save.data_ptr() + 4 * k, _stream()), 'bn_rows_fwd')
+    _lib.count_launch()
+    return y, save
+
+
+def bn_rows_bwd(dy, x, bn, save, training, relu):
+    """-> (dx, dgamma, dbeta)"""
+    n, k = x.shape
+    dx = torch.empty_like(x)
+    dgb = torch.empty((2, k), dtype=torch.float32, device=x.device)
+    _lib.check(_lib.load().b200seg_bn_rows_bwd(
+        dy.data_ptr(), x.data_ptr(), n, k, bn.weight.data_ptr(), bn.bias.data_ptr(), save.data_ptr(),
+        save.data_ptr() + 4 * k, int(training), int(relu), dx.data_ptr(), dgb.data_ptr(), dgb.data_ptr() + 4 * k,
+        _stream()), 'bn_rows_bwd')
+    _lib.count_launch()
+    return dx, dgb[0], dgb[1]
 
 
 def channel_sum(x):

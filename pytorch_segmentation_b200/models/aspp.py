@@ -22,26 +22,36 @@ class ASPPPooling(nn.Module):
     def forward(self, x):
         return _PoolFn.apply(self, x, *self.gap[1].tensors())
 
-    # explicit records used by ASPP
+    # explicit records used by ASPP.  The whole branch after the pool is fp32 on CUDA cores
+    # (csrc/pool_branch.cu): N = batch rows, reads the fp32 master weight directly.
     def run_forward(self, x, out, training, save):
-        g = E.gap_fwd(x)                                   # [n,1,1,cin]
         cna = self.gap[1]
-        p = E.Act.empty(x.n, 1, 1, cna[0].out_channels, x.t.device)
-        rec = cna.run_forward(g, p, training, save)
-        E.broadcast_hw(p, out)
-        return (rec, x.h * x.w) if save else None
+        conv, bn = cna[0], cna[1]
+        if training:
+            if bn.momentum is None:
+                raise NotImplementedError('BatchNorm2d(momentum=None) (cumulative average) is not supported')
+            if x.n <= 1:
+                raise ValueError('Expected more than 1 value per channel when training, got input size %s'
+                                 % ([x.n, conv.out_channels, 1, 1],))
+        g = E.gap_fwd(x)                                        # fp32 [n, cin]
+        raw = E.linear_f32_fwd(g, conv.weight)                  # fp32 [n, planes]
+        z, bn_save = E.bn_rows_fwd(raw, bn, training, cna.relu)
+        if training and bn.track_running_stats and bn.num_batches_tracked is not None:
+            bn.num_batches_tracked.add_(1)
+        E.broadcast_hw(z, out)
+        return (g, raw, bn_save, training, x.h * x.w) if save else None
 
     def run_backward(self, rec, dout, dx, accumulate):
         """dout: grad slice of the broadcast output; adds (or writes) the branch's input grad into dx."""
-        crec, hw = rec
+        g, raw, bn_save, training, hw = rec
         cna = self.gap[1]
-        dp = E.sum_hw(dout)
-        draw, pgrads = cna.run_backward_params(crec, dp)
+        conv, bn = cna[0], cna[1]
+        dz = E.sum_hw(dout)                                     # fp32 [n, planes]
+        draw, dgamma, dbeta = E.bn_rows_bwd(dz, raw, bn, bn_save, training, cna.relu)
+        dg, dw = E.linear_f32_bwd(draw, g, conv.weight, need_dx=dx is not None)
         if dx is not None:
-            dg = E.Act.empty(dp.n, 1, 1, cna[0].in_channels, dp.t.device)
-            E.conv_dgrad([cna.dgrad_src(draw)], dg)
             E.broadcast_hw(dg, dx, scale=1.0 / hw, accumulate=accumulate)
-        return pgrads
+        return [dw, dgamma, dbeta]
 
 
 class _PoolFn(torch.autograd.Function):

@@ -67,11 +67,10 @@ def test_conv_fprop_dgrad_wgrad(E, n, h, w, c, k, ks, dil):
     stats = torch.zeros(2 * k, device='cuda')
     E.conv_fprop([(xa, pw, dil)], ya, stats=stats)
     assert rel_err(from_act(ya), y_ref) < TOL
-    # fused BN statistics: sum and sum of squares of the fp32 accumulators
-    ref_sum = y_ref.detach().sum((0, 2, 3))
-    ref_sq = (y_ref.detach() ** 2).sum((0, 2, 3))
-    assert rel_err(stats[:k], ref_sum) < 2e-3 + 1e-3
-    assert rel_err(stats[k:], ref_sq) < 2e-3
+    # fused BN statistics: sum and sum of squares of the conv output as stored (bf16-rounded)
+    y_st = from_act(ya)
+    assert rel_err(stats[:k], y_st.sum((0, 2, 3))) < 1e-4 + 1e-3 * (n * h * w > 64)
+    assert rel_err(stats[k:], (y_st ** 2).sum((0, 2, 3))) < 1e-4
 
     dya = nhwc(dy)
     dxa = E.Act.empty(n, h, w, c, 'cuda')
@@ -219,17 +218,54 @@ def test_gap_broadcast_sum(E):
     x = bf16_round(torch.randn(n, c, h, w, generator=g))
     xa = nhwc(x)
     ga = E.gap_fwd(xa)
-    assert rel_err(ga.t.reshape(n, c), x.mean((2, 3))) < 1e-2
-    sa = E.sum_hw(xa)
-    assert rel_err(sa.t.reshape(n, c), x.sum((2, 3))) < 1e-2
+    assert ga.dtype == torch.float32 and rel_err(ga, x.mean((2, 3))) < 1e-5
+    assert rel_err(E.sum_hw(xa), x.sum((2, 3))) < 1e-5
     yb = torch.zeros(n, h, w, c + 8, dtype=torch.bfloat16, device='cuda')
     E.broadcast_hw(ga, E.Act(yb, 8, c))
-    assert torch.equal(yb[..., 8:], ga.t.reshape(n, 1, 1, c).expand(n, h, w, c))
+    assert torch.equal(yb[..., 8:], ga.to(torch.bfloat16).reshape(n, 1, 1, c).expand(n, h, w, c))
+    assert float(yb[..., :8].abs().max()) == 0.0
     base = bf16_round(torch.randn(n, c, h, w, generator=g))
     ba = nhwc(base)
     E.broadcast_hw(ga, ba, scale=0.5, accumulate=True)
-    ref = base + 0.5 * ga.t.reshape(n, c, 1, 1).float().cpu()
+    ref = base + 0.5 * ga.reshape(n, c, 1, 1).cpu()
     assert rel_err(from_act(ba), ref) < 1e-2
+
+
+@pytest.mark.parametrize('n,c,k,training', [(16, 2048, 256, True), (3, 128, 64, True), (2, 2048, 256, True),
+                                            (20, 96, 40, False)])
+def test_pooled_branch_fp32_kernels(E, n, c, k, training):
+    """1x1 ConvNormAct on the N x C x 1 x 1 pooled map (models/aspp.py:12) in fp32: forward, BN over the N rows,
+    and every gradient against F.conv2d / F.batch_norm."""
+    g = torch.Generator().manual_seed(n + c)
+    x = (torch.randn(n, c, generator=g) * 0.3 + 2.0).requires_grad_(True)     # mean >> spread, like pooled features
+    wt = (torch.randn(k, c, 1, 1, generator=g) * 0.05).requires_grad_(True)
+    bn = torch.nn.BatchNorm2d(k)
+    with torch.no_grad():
+        bn.weight.copy_(1 + 0.2 * torch.randn(k, generator=g))
+        bn.bias.copy_(0.1 * torch.randn(k, generator=g))
+        bn.running_mean.copy_(0.1 * torch.randn(k, generator=g))
+        bn.running_var.copy_(1 + 0.1 * torch.rand(k, generator=g))
+    bn.train(training)
+    import copy
+    bn_dev = copy.deepcopy(bn).cuda()
+    dz = torch.randn(n, k, generator=g)
+    raw_ref = F.conv2d(x.view(n, c, 1, 1), wt)
+    z_ref = F.relu(bn(raw_ref))
+    z_ref.backward(dz.view(n, k, 1, 1))
+    xd, wd = x.detach().cuda(), wt.detach().cuda()
+    raw = E.linear_f32_fwd(xd, wd)
+    assert rel_err(raw, raw_ref.view(n, k)) < 1e-5
+    z, save = E.bn_rows_fwd(raw, bn_dev, training, True)
+    assert rel_err(z, z_ref.view(n, k)) < 1e-4
+    if training:
+        assert rel_err(bn_dev.running_mean, bn.running_mean) < 1e-5
+        assert rel_err(bn_dev.running_var, bn.running_var) < 1e-4
+    draw, dgamma, dbeta = E.bn_rows_bwd(dz.cuda(), raw, bn_dev, save, training, True)
+    dx, dw = E.linear_f32_bwd(draw, xd, wd)
+    tol = 2e-3 if n > 2 else 5e-2          # n == 2: the BN input gradient is ~0 by cancellation
+    assert rel_err(dgamma, bn.weight.grad) < 1e-4 and rel_err(dbeta, bn.bias.grad) < 1e-4
+    assert rel_err(dw, wt.grad) < tol
+    assert rel_err(dx, x.grad) < tol
 
 
 @pytest.mark.parametrize('nc,h,w,oh,ow', [(21, 8, 8, 32, 32), (2, 10, 12, 20, 24), (19, 6, 5, 24, 20)])
@@ -273,7 +309,7 @@ def test_softmax_cross_entropy(E, nc):
     acc, dl = E.softmax_ce(logits.detach().cuda(), tgt.cuda(), -100, True)
     count = int(acc[1:2].view(torch.int64))
     assert count == int((tgt != -100).sum())
-    assert abs(float(acc[0]) / count - float(loss_ref)) < 1e-5 * max(1.0, abs(float(loss_ref)))
+    assert abs(float(acc[0]) / count - float(loss_ref.detach())) < 1e-5 * max(1.0, abs(float(loss_ref)))
     assert int(acc[2:3].view(torch.int32)[0]) == 0
     assert rel_err(dl / count, logits.grad) < 1e-5
     # out-of-range target sets the status flag
