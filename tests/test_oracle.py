@@ -1,0 +1,146 @@
+"""The oracle (oracle/restatement.py) against the golden vectors generated from the UNMODIFIED reference
+(oracle/make_golden.py -> tests/golden/*.npz), and — when /root/reference is present (build container) — against
+the reference itself, live.  CPU only."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import golden as G
+from oracle import reference_loader
+from oracle import restatement as R
+
+FP32_TOL = 2e-4     # same library calls as the reference; differences are thread-count / summation order only
+
+
+def test_compute_loss_golden():
+    gold = G.load('compute_loss')
+    i = 0
+    while 'shape%d' % i in gold:
+        logits = torch.from_numpy(gold['logits%d' % i]).requires_grad_(True)
+        loss = R.compute_loss(logits, torch.from_numpy(gold['targets%d' % i]))
+        loss.backward()
+        assert abs(float(loss) - float(gold['loss%d' % i])) < 1e-6
+        assert np.allclose(logits.grad.numpy(), gold['dlogits%d' % i], atol=1e-8, rtol=1e-5)
+        i += 1
+    assert i == 4
+
+
+def test_metrics_golden_bit_exact():
+    gold = G.load('metrics')
+    for i in range(int(gold['ncases'])):
+        nc = int(gold['nc%d' % i])
+        pred, tgt = torch.from_numpy(gold['pred%d' % i]), torch.from_numpy(gold['tgt%d' % i])
+        tp, fn, fp = R.tp_fn_fp_loop(pred, tgt, nc)
+        assert np.array_equal(tp.numpy(), gold['tp%d' % i])
+        assert np.array_equal(fn.numpy(), gold['fn%d' % i])
+        assert np.array_equal(fp.numpy(), gold['fp%d' % i])
+        # the confusion matrix is a superset of the loop
+        tp2, fn2, fp2 = R.counts_from_confusion(R.confusion_matrix(pred, tgt, nc))
+        assert torch.equal(tp2, tp) and torch.equal(fn2, fn) and torch.equal(fp2, fp)
+        T, P, Rr, iou, F1 = R.compute_metrics(tp.float(), fn.float(), fp.float())
+        for name, v in (('iou', iou), ('P', P), ('R', Rr), ('F1', F1)):
+            assert np.array_equal(v.numpy(), gold['%s%d' % (name, i)]), name
+        assert np.float32(iou.mean().item()) == gold['miou%d' % i]
+
+
+def test_evaluate_replays_reference_test_loop():
+    gold = G.load('metrics')
+
+    class Replay:
+        def __init__(self, logits):
+            self.l, self.i = logits, 0
+
+        def eval(self):
+            return self
+
+        def __call__(self, x):
+            y = self.l[self.i % len(self.l)]
+            self.i += 1
+            return y
+
+    for i in range(int(gold['ncases'])):
+        nc = int(gold['nc%d' % i])
+        pred, tgt = torch.from_numpy(gold['pred%d' % i]), torch.from_numpy(gold['tgt%d' % i])
+        logits = [torch.nn.functional.one_hot(p, nc).permute(0, 3, 1, 2).float() * 4 for p in pred]
+        miou, _, _ = R.evaluate(Replay(logits), [(None, tg) for tg in tgt], nc)
+        assert np.float32(miou) == gold['miou%d' % i]
+
+
+@pytest.mark.parametrize('name', ['aspp_small', 'aspp_full'])
+def test_aspp_golden(name):
+    c = G.CASES[name]
+    gold = G.load(name)
+    sd = {('a.' + k): v.clone() for k, v in G.small_aspp_state(c).items()}
+    for k, v in sd.items():
+        if v.is_floating_point() and 'running_' not in k:
+            v.requires_grad_(True)
+    g = torch.Generator().manual_seed(c['seed'] + 1)
+    x = torch.randn(c['n'], c['cin'], c['h'], c['w'], generator=g).requires_grad_(True)
+    gy = torch.randn(c['n'], c['cout'], c['h'], c['w'], generator=g)
+    with torch.no_grad():
+        y = R.aspp(sd, 'a', x, c['rates'], False)
+    assert G.summary_error(gold, 'eval_out', y)[0] < FP32_TOL
+    y = R.aspp(sd, 'a', x, c['rates'], True)
+    y.backward(gy)
+    assert G.summary_error(gold, 'train_out', y)[0] < FP32_TOL
+    assert G.summary_error(gold, 'grad_in', x.grad)[0] < FP32_TOL
+    for k, v in sd.items():
+        if v.requires_grad:
+            assert G.summary_error(gold, 'grad:' + k[2:], v.grad)[0] < FP32_TOL, k
+        if 'running_' in k:
+            assert np.allclose(v.numpy(), gold['stat:' + k[2:]], rtol=1e-4, atol=1e-6), k
+
+
+@pytest.mark.parametrize('name', ['unet_320', 'deeplab_small', 'deeplab_512'])
+def test_model_golden(name):
+    c = G.CASES[name]
+    gold = G.load(name)
+    m = R.OracleModel(c['kind'], c['nc'], seed=c['seed'])
+    x, t = G.make_inputs(c)
+    m.eval()
+    with torch.no_grad():
+        y = m(x)
+    assert G.summary_error(gold, 'eval_logits', y)[0] < FP32_TOL
+    assert abs(float(R.compute_loss(y, t)) - float(gold['eval_loss'])) < 1e-4 * abs(float(gold['eval_loss']))
+    assert np.array_equal(y.max(1)[1].flatten()[::997].numpy(), gold['eval_argmax_sample'])
+    m.train()
+    y = m(x)
+    loss = R.compute_loss(y, t)
+    loss.backward()
+    assert G.summary_error(gold, 'train_logits', y)[0] < 5e-4
+    assert abs(float(loss.detach()) - float(gold['train_loss'])) < 1e-4 * abs(float(gold['train_loss']))
+    for k, v in m.sd.items():
+        if v.requires_grad:
+            assert G.summary_error(gold, 'grad:' + k, v.grad)[0] < 2e-3, k
+        if 'running_' in k:
+            assert np.allclose(v.numpy(), gold['stat:' + k], rtol=1e-3, atol=1e-5), k
+
+
+@pytest.mark.skipif(not reference_loader.available(), reason='/root/reference not present (GPU box)')
+def test_restatement_equals_reference_live():
+    """The unmodified reference modules, imported from /root/reference, against the restatement on a fresh case."""
+    ref = reference_loader.load()
+    oracle = R.OracleModel('unet', 3, seed=21)
+    torch.manual_seed(0)
+    model = ref.UNet(3)
+    model.load_state_dict(oracle.state_dict())
+    x, t = G.make_inputs(dict(n=2, nc=3, h=64, w=96, seed=21))
+    model.train()
+    oracle.train()
+    y_ref = model(x)
+    loss_ref = ref.compute_loss(y_ref, t, model)
+    loss_ref.backward()
+    y = oracle(x)
+    loss = R.compute_loss(y, t)
+    loss.backward()
+    assert torch.allclose(y, y_ref, rtol=1e-4, atol=1e-5)
+    assert abs(float(loss.detach()) - float(loss_ref.detach())) < 1e-6
+    grads = dict(model.named_parameters())
+    for k, v in oracle.sd.items():
+        if v.requires_grad:
+            assert torch.allclose(v.grad, grads[k].grad, rtol=1e-3, atol=1e-6), k
+    tp = torch.tensor([5., 0., 7.])
+    fn = torch.tensor([1., 0., 0.])
+    fp = torch.tensor([2., 0., 3.])
+    for a, b in zip(ref.compute_metrics(tp.clone(), fn.clone(), fp.clone()), R.compute_metrics(tp, fn, fp)):
+        assert torch.equal(a, b)
