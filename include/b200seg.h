@@ -31,6 +31,11 @@ int b200seg_version(void);
 /* fills SM count and compute capability of the current device; fails if it is not sm_100 */
 int b200seg_device_info(int* sm_count, int* cc_major, int* cc_minor);
 
+/* Diagnostics: when buf != NULL, the epilogue of CTA 0 of every following conv launch writes globaltimer stamps
+ * (int64 nanoseconds; 8 per staged 64-channel slab, at most `slots` slabs) into the device buffer; NULL turns
+ * it off.  Used by scripts/ to attribute epilogue time; never set on the product path. */
+int b200seg_debug_timing(int64_t* buf, int slots);
+
 /* ---- layout / packing ---------------------------------------------------------------------------------- */
 /* fp32 NCHW -> bf16 NHWC slice, and back (gradients).  Boundary of the drop-in forward(x: N x C x H x W)
  * (models/deeplabv3plus.py:28, models/unet.py:27). */

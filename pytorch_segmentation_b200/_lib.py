@@ -46,6 +46,7 @@ PROTOTYPES = {
     'b200seg_last_error': (c_char_p, []),
     'b200seg_version': (c_int, []),
     'b200seg_device_info': (c_int, [POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
+    'b200seg_debug_timing': (c_int, [_P, _I]),
     'b200seg_nchw_to_nhwc': (c_int, [_P, _P, _I, _I, _I, _I, _I, _I, _P]),
     'b200seg_nhwc_to_nchw': (c_int, [_P, _P, _I, _I, _I, _I, _I, _I, _P]),
     'b200seg_pack_weights': (c_int, [_P, _I, _I, _I, _I, _P, _I, _P, _I, _I, _P]),

@@ -21,6 +21,11 @@
 
 #include <string.h>
 
+#include <array>
+#include <map>
+#include <mutex>
+#include <vector>
+
 namespace b200seg {
 
 namespace {
@@ -32,9 +37,13 @@ constexpr int kStages = 4;
 constexpr int kABytes = kBM * kBK * 2;
 constexpr int kBBytesMax = kMaxBN * kBK * 2;
 constexpr int kStageBytes = kABytes + kBBytesMax;
-constexpr int kThreads = 256;
+constexpr int kThreads = 384;          // warps 0-3: TMA / MMA / TMEM alloc / idle, warps 4-11: epilogue
+constexpr int kEpiThreads = 256;
 constexpr int kBarrierBytes = 256;
-constexpr int kSmemBytes = kStages * kStageBytes + kBarrierBytes + 1024;   // +1024: manual 1 KB alignment
+constexpr int kOutSlab = 64;                       // output channels per TMA store box (128 bytes of bf16)
+constexpr int kOutBufBytes = kBM * kOutSlab * 2;   // 16 KB: one 128-pixel x 64-channel slab, 128-byte swizzled
+constexpr int kOutBufs = 2;
+constexpr int kSmemBytes = kStages * kStageBytes + kOutBufs * kOutBufBytes + kBarrierBytes + 1024;   // +1024: alignment
 constexpr int kTmemCols = 512;
 
 struct IgemmSeg {
@@ -44,6 +53,7 @@ struct IgemmSeg {
 struct __align__(64) IgemmParams {
     CUtensorMap a_map[B200SEG_MAX_CONV_SRC];
     CUtensorMap b_map[B200SEG_MAX_CONV_SRC];
+    CUtensorMap y_map;       // bf16 output slice (channels, W, H, N), box = 64 channels x pixel patch
     IgemmSeg seg[B200SEG_MAX_CONV_SRC];
     int nseg;
     int N, H, W;
@@ -58,7 +68,18 @@ struct __align__(64) IgemmParams {
     const float* bias;
     int relu;
     float* stats;
+    long long* dbg;
+    int dbg_slots;
 };
+
+long long* g_dbg = nullptr;
+int g_dbg_slots = 0;
+
+__device__ __forceinline__ long long gtime() {
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 
 struct TileCoord {
     int n_tile, x0, y0, n0;
@@ -82,13 +103,13 @@ __device__ __forceinline__ bool tap_in_bounds(const IgemmParams& p, const TileCo
 __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constant__ IgemmParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
+    uint8_t* out_buf = smem + kStages * kStageBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(out_buf + kOutBufs * kOutBufBytes);
     uint64_t* full = bars;                    // [kStages] TMA -> MMA
     uint64_t* empty = bars + kStages;         // [kStages] MMA -> TMA
     uint64_t* tfull = bars + 2 * kStages;     // [2] MMA -> epilogue
     uint64_t* tempty = bars + 2 * kStages + 2;   // [2] epilogue -> MMA
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
-
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
@@ -97,6 +118,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
             tma_prefetch_desc(&p.a_map[i]);
             tma_prefetch_desc(&p.b_map[i]);
         }
+        if (!p.out_fp32) tma_prefetch_desc(&p.y_map);
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < kStages; ++i) {
@@ -105,7 +127,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tfull[i], 1);
-            mbar_init(&tempty[i], 4);
+            mbar_init(&tempty[i], p.out_fp32 ? 4 : 8);
         }
         fence_barrier_init();
     }
@@ -199,93 +221,234 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
         const int wl = row & (p.bw - 1);
         const int hl = (row >> p.lbw) & (p.bh - 1);
         const int il = row >> (p.lbw + p.lbh);
-        int lt = 0;
-        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++lt) {
-            const TileCoord t = decode_tile(p, tile);
-            const int acc = lt & 1;
-            const uint32_t acc_phase = (lt >> 1) & 1;
-            const int px = t.x0 + wl, py = t.y0 + hl, pn = t.n0 + il;
-            const bool valid = (px < p.W) && (py < p.H) && (pn < p.N);
-            const size_t pix = (static_cast<size_t>(pn) * p.H + py) * p.W + px;
-            mbar_wait(&tfull[acc], acc_phase);
-            tc_fence_after();
-            const uint32_t taddr = tmem_base + acc * kMaxBN + (static_cast<uint32_t>(q * 32) << 16);
-            for (int ch = 0; ch < p.bn; ch += 32) {
-                uint32_t v[32];
-                tmem_ld_32x32(taddr + ch, v);
-                tmem_ld_wait();
-                const int k0 = t.n_tile * p.bn + ch;
-                if (p.stats) {
-                    // column sums over this warp's 32 rows by recursive halving: 31 shuffles leave lane j
-                    // holding the total of channel k0 + j (rows outside the image contribute zero)
-                    float s1[32], s2[32];
+        if (!p.out_fp32) {
+            // bf16 output: TMEM -> registers -> (scale/bias/ReLU) -> 128-byte-swizzled shared-memory slab (64 channels
+            // x 128 pixels) -> one TMA store per slab (the TMA unit clips pixels outside the image and channels
+            // beyond the slice).  Eight warps: warp w reads TMEM lanes 32*(w%4).., warps 4-7 take the low 32 columns
+            // of the slab, warps 8-11 the high 32 (two warps per scheduler hide each other's latencies).
+            // BN statistics are column sums of the staged bf16 slab: thread (row group rg, channel pair cp) keeps
+            // running sums in registers over all tiles of this CTA and flushes once.
+            const int et = threadIdx.x - 128;            // 0..255
+            const int half = et >> 7;
+            const int cp = et & 31, rg = et >> 5;        // rg 0..7: 16 rows each
+            const bool affine = p.scale != nullptr || p.bias != nullptr || p.relu != 0;
+            float st1[4][2], st2[4][2];
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        // statistics of the values as stored (bf16-rounded), so the saved mean / inv-std are
-                        // exactly those of the tensor the backward pass re-reads
-                        float a = valid ? __uint_as_float(v[j]) : 0.f;
-                        if (!p.out_fp32) a = __bfloat162float(__float2bfloat16(a));
-                        s1[j] = a;
-                        s2[j] = a * a;
-                    }
+            for (int i = 0; i < 4; ++i) st1[i][0] = st1[i][1] = st2[i][0] = st2[i][1] = 0.f;
+            int cur_n_tile = -1;
+            int slab_seq = 0;
+            // Flush: the row groups' partial sums meet in shared memory (the staging buffers are idle then), so each
+            // channel costs one global atomic per CTA, issued by consecutive lanes on consecutive channels.
+            auto flush_stats = [&](int n_tile) {
+                float* red = reinterpret_cast<float*>(out_buf);        // [rg 8][slab 4][sum/sumsq 2][64]
+                if (et == 0) tma_store_wait_read<0>();
+                named_bar_sync(1, kEpiThreads);
 #pragma unroll
-                    for (int off = 16; off >= 1; off >>= 1) {
-                        const bool upper = (lane & off) != 0;
+                for (int sl = 0; sl < 4; ++sl) {
 #pragma unroll
-                        for (int j = 0; j < off; ++j) {
-                            const float send1 = upper ? s1[j] : s1[j + off];
-                            const float keep1 = upper ? s1[j + off] : s1[j];
-                            s1[j] = keep1 + __shfl_xor_sync(0xffffffffu, send1, off);
-                            const float send2 = upper ? s2[j] : s2[j + off];
-                            const float keep2 = upper ? s2[j + off] : s2[j];
-                            s2[j] = keep2 + __shfl_xor_sync(0xffffffffu, send2, off);
-                        }
-                    }
-                    if (k0 + lane < p.k_store) {
-                        atomicAdd(p.stats + k0 + lane, s1[0]);
-                        atomicAdd(p.stats + p.k_store + k0 + lane, s2[0]);
+                    for (int e = 0; e < 2; ++e) {
+                        red[((rg * 4 + sl) * 2 + 0) * 64 + cp * 2 + e] = st1[sl][e];
+                        red[((rg * 4 + sl) * 2 + 1) * 64 + cp * 2 + e] = st2[sl][e];
+                        st1[sl][e] = st2[sl][e] = 0.f;
                     }
                 }
-                if (valid) {
+                named_bar_sync(2, kEpiThreads);
+                for (int i = et; i < 4 * 2 * 64; i += kEpiThreads) {
+                    const int c = i & 63, which = (i >> 6) & 1, sl = i >> 7;
+                    const int ch = n_tile * p.bn + sl * kOutSlab + c;
+                    if (sl * kOutSlab < p.bn && ch < p.k_store) {
+                        float v = 0.f;
 #pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        const int kg = k0 + g * 8;
-                        if (kg < p.k_store) {
-                            float f[8];
+                        for (int r = 0; r < 8; ++r) v += red[((r * 4 + sl) * 2 + which) * 64 + c];
+                        atomicAdd(p.stats + which * p.k_store + ch, v);
+                    }
+                }
+                named_bar_sync(1, kEpiThreads);      // red[] is read before the next slab is staged over it
+            };
+            int lt = 0;
+            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++lt) {
+                const TileCoord t = decode_tile(p, tile);
+                const int acc = lt & 1;
+                const uint32_t acc_phase = (lt >> 1) & 1;
+                // rows outside the image exist only in border tiles (uniform test); they are clipped by the store
+                // and must be zero for the statistics
+                const bool border = (t.x0 + p.bw > p.W) || (t.y0 + p.bh > p.H) || (t.n0 + p.bi > p.N);
+                const bool valid = !border || ((t.x0 + wl < p.W) && (t.y0 + hl < p.H) && (t.n0 + il < p.N));
+                if (p.stats && t.n_tile != cur_n_tile) {
+                    if (cur_n_tile >= 0) flush_stats(cur_n_tile);
+                    cur_n_tile = t.n_tile;
+                }
+                mbar_wait(&tfull[acc], acc_phase);
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + acc * kMaxBN + (static_cast<uint32_t>(q * 32) << 16) + half * 32;
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[g * 8 + j]);
-                            if (p.scale) {
+                for (int sl = 0; sl < 4; ++sl) {
+                    if (sl * kOutSlab < p.bn) {
+                        uint8_t* buf = out_buf + (slab_seq & 1) * kOutBufBytes;
+                        long long* dbg = (p.dbg && blockIdx.x == 0 && et == 0 && slab_seq < p.dbg_slots) ? p.dbg + slab_seq * 8
+                                                                                                   : nullptr;
+                        ++slab_seq;
+                        if (dbg) dbg[0] = gtime();
+                        const int k0 = t.n_tile * p.bn + sl * kOutSlab;
+                        const int kh = k0 + half * 32;
+                        uint32_t v[32];
+                        const bool have = sl * kOutSlab + half * 32 < p.bn;
+                        if (have) {
+                            tmem_ld_32x32(taddr + sl * kOutSlab, v);
+                            tmem_ld_wait();
+                        }
+                        if (!have || !valid) {
 #pragma unroll
-                                for (int j = 0; j < 8; ++j) f[j] *= __ldg(p.scale + kg + j);
-                            }
-                            if (p.bias) {
+                            for (int j = 0; j < 32; ++j) v[j] = 0u;
+                        }
+                        if (dbg) dbg[1] = gtime();
+                        // the buffer is free once the store issued two slabs ago has read it (thread 128 waited for
+                        // that before arriving here)
+                        named_bar_sync(1, kEpiThreads);
+                        if (dbg) dbg[2] = gtime();
+                        uint8_t* rowp = buf + row * 128;
+                        const int sw = row & 7;
+                        if (affine) {
 #pragma unroll
-                                for (int j = 0; j < 8; ++j) f[j] += __ldg(p.bias + kg + j);
-                            }
-                            if (p.relu) {
+                            for (int g = 0; g < 4; ++g) {
+                                const int kg = kh + g * 8;
+                                float f[8];
 #pragma unroll
-                                for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
-                            }
-                            const size_t off = pix * p.y_c_total + p.y_c_offset + kg;
-                            if (p.out_fp32) {
-                                float4* dst = reinterpret_cast<float4*>(static_cast<float*>(p.y) + off);
-                                dst[0] = make_float4(f[0], f[1], f[2], f[3]);
-                                dst[1] = make_float4(f[4], f[5], f[6], f[7]);
-                            } else {
+                                for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[g * 8 + j]);
+                                if (kg < p.k_store) {
+                                    if (p.scale) {
+                                        const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.scale + kg));
+                                        const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.scale + kg) + 1);
+                                        f[0] *= s0.x; f[1] *= s0.y; f[2] *= s0.z; f[3] *= s0.w;
+                                        f[4] *= s1.x; f[5] *= s1.y; f[6] *= s1.z; f[7] *= s1.w;
+                                    }
+                                    if (p.bias) {
+                                        const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + kg));
+                                        const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + kg) + 1);
+                                        f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
+                                        f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+                                    }
+                                    if (p.relu) {
+#pragma unroll
+                                        for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+                                    }
+                                }
                                 uint4 o;
                                 o.x = pack_bf16x2(f[0], f[1]);
                                 o.y = pack_bf16x2(f[2], f[3]);
                                 o.z = pack_bf16x2(f[4], f[5]);
                                 o.w = pack_bf16x2(f[6], f[7]);
-                                *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.y) + off) = o;
+                                *reinterpret_cast<uint4*>(rowp + (((half * 4 + g) ^ sw) << 4)) = o;
+                            }
+                        } else {
+#pragma unroll
+                            for (int g = 0; g < 4; ++g) {
+                                uint4 o;
+                                o.x = pack_bf16x2(__uint_as_float(v[g * 8 + 0]), __uint_as_float(v[g * 8 + 1]));
+                                o.y = pack_bf16x2(__uint_as_float(v[g * 8 + 2]), __uint_as_float(v[g * 8 + 3]));
+                                o.z = pack_bf16x2(__uint_as_float(v[g * 8 + 4]), __uint_as_float(v[g * 8 + 5]));
+                                o.w = pack_bf16x2(__uint_as_float(v[g * 8 + 6]), __uint_as_float(v[g * 8 + 7]));
+                                *reinterpret_cast<uint4*>(rowp + (((half * 4 + g) ^ sw) << 4)) = o;
+                            }
+                        }
+                        if (dbg) dbg[3] = gtime();
+                        fence_proxy_async();
+                        if (dbg) dbg[4] = gtime();
+                        named_bar_sync(2, kEpiThreads);
+                        if (dbg) dbg[5] = gtime();
+                        if (et == 0) {
+                            tma_store_4d(&p.y_map, buf, k0, t.x0, t.y0, t.n0);
+                            tma_store_commit();
+                            tma_store_wait_read<1>();      // the previous slab's buffer may be overwritten
+                        }
+                        if (dbg) dbg[6] = gtime();
+                        if (p.stats) {
+                            float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+                            const uint8_t* colp = buf + rg * 16 * 128 + (cp & 3) * 4;
+                            const int cq = cp >> 2;
+#pragma unroll
+                            for (int r = 0; r < 16; ++r) {
+                                // rows rg*16 + r: (row & 7) == (r & 7) because rg*16 is a multiple of 8
+                                const uint32_t wv = *reinterpret_cast<const uint32_t*>(colp + r * 128 + ((cq ^ (r & 7)) << 4));
+                                const float x0 = __uint_as_float(wv << 16), x1 = __uint_as_float(wv & 0xffff0000u);
+                                a0 += x0;
+                                a1 += x1;
+                                b0 = fmaf(x0, x0, b0);
+                                b1 = fmaf(x1, x1, b1);
+                            }
+                            st1[sl][0] += a0;
+                            st1[sl][1] += a1;
+                            st2[sl][0] += b0;
+                            st2[sl][1] += b1;
+                        }
+                        if (dbg) dbg[7] = gtime();
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tempty[acc]);
+            }
+            if (p.stats && cur_n_tile >= 0) flush_stats(cur_n_tile);
+            if (et == 0) tma_store_wait_all<0>();
+        } else if (warp < 8) {
+            // fp32 class map (cls_conv): direct stores, four warps
+            int lt = 0;
+            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++lt) {
+                const TileCoord t = decode_tile(p, tile);
+                const int acc = lt & 1;
+                const uint32_t acc_phase = (lt >> 1) & 1;
+                const int px = t.x0 + wl, py = t.y0 + hl, pn = t.n0 + il;
+                const bool valid = (px < p.W) && (py < p.H) && (pn < p.N);
+                const size_t pix = (static_cast<size_t>(pn) * p.H + py) * p.W + px;
+                mbar_wait(&tfull[acc], acc_phase);
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + acc * kMaxBN + (static_cast<uint32_t>(q * 32) << 16);
+                for (int ch = 0; ch < p.bn; ch += 32) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(taddr + ch, v);
+                    tmem_ld_wait();
+                    const int k0 = t.n_tile * p.bn + ch;
+                    if (valid) {
+    #pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            const int kg = k0 + g * 8;
+                            if (kg < p.k_store) {
+                                float f[8];
+    #pragma unroll
+                                for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[g * 8 + j]);
+                                if (p.scale) {
+    #pragma unroll
+                                    for (int j = 0; j < 8; ++j) f[j] *= __ldg(p.scale + kg + j);
+                                }
+                                if (p.bias) {
+    #pragma unroll
+                                    for (int j = 0; j < 8; ++j) f[j] += __ldg(p.bias + kg + j);
+                                }
+                                if (p.relu) {
+    #pragma unroll
+                                    for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+                                }
+                                const size_t off = pix * p.y_c_total + p.y_c_offset + kg;
+                                if (p.out_fp32) {
+                                    float4* dst = reinterpret_cast<float4*>(static_cast<float*>(p.y) + off);
+                                    dst[0] = make_float4(f[0], f[1], f[2], f[3]);
+                                    dst[1] = make_float4(f[4], f[5], f[6], f[7]);
+                                } else {
+                                    uint4 o;
+                                    o.x = pack_bf16x2(f[0], f[1]);
+                                    o.y = pack_bf16x2(f[2], f[3]);
+                                    o.z = pack_bf16x2(f[4], f[5]);
+                                    o.w = pack_bf16x2(f[6], f[7]);
+                                    *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.y) + off) = o;
+                                }
                             }
                         }
                     }
                 }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tempty[acc]);
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty[acc]);
         }
     }
 
@@ -357,21 +520,46 @@ int launch_igemm(int n, int h, int w, int n_src, const b200seg_conv_src* src, co
 
     // output-channel tiling
     p.tiles_n = ceil_div(out->k, kMaxBN);
-    p.bn = round_up(ceil_div(out->k, p.tiles_n), 32);
+    // whole 64-channel store slabs per n-tile (a narrow single tile may be 32 wide: the store clips at k)
+    p.bn = out->k <= 32 ? 32 : round_up(ceil_div(out->k, p.tiles_n), kOutSlab);
     B200SEG_CHECK(p.bn <= kMaxBN, "conv: internal bn %d", p.bn);
+    B200SEG_CHECK(!(out->stats && (out->scale || out->bias || out->relu || out->out_fp32)),
+                  "conv: fused BN statistics are those of the stored bf16 conv result; scale/bias/relu/fp32 output "
+                  "cannot be combined with them");
 
-    // pixel patch: the power-of-two bw x bh x bi = 128 shape that needs the fewest pipeline iterations
+    // pixel patch: the power-of-two bw x bh x bi = 128 shape that needs the fewest pipeline iterations.  The search
+    // walks every tile of the map, so its result is memoised per geometry (a training step repeats the same few).
     long long best = -1;
-    for (int bi = 1; bi <= 128; bi *= 2) {
-        for (int bw = 1; bw * bi <= 128; bw *= 2) {
-            const int bh = 128 / (bw * bi);
-            const long long c = patch_cost(n, h, w, bw, bh, bi, n_src, p.seg);
-            if (best < 0 || c < best || (c == best && bw > p.bw)) {
-                best = c;
-                p.bw = bw;
-                p.bh = bh;
-                p.bi = bi;
+    {
+        static std::mutex mu;
+        static std::map<std::vector<int>, std::array<int, 3>> memo;
+        std::vector<int> key = {n, h, w, n_src};
+        for (int i = 0; i < n_src; ++i) {
+            key.push_back(p.seg[i].r);
+            key.push_back(p.seg[i].dil);
+            key.push_back(p.seg[i].cblks);
+        }
+        std::lock_guard<std::mutex> lock(mu);
+        auto it = memo.find(key);
+        if (it != memo.end()) {
+            p.bw = it->second[0];
+            p.bh = it->second[1];
+            p.bi = it->second[2];
+            best = 1;
+        } else {
+            for (int bi = 1; bi <= 128; bi *= 2) {
+                for (int bw = 1; bw * bi <= 128; bw *= 2) {
+                    const int bh = 128 / (bw * bi);
+                    const long long c = patch_cost(n, h, w, bw, bh, bi, n_src, p.seg);
+                    if (best < 0 || c < best || (c == best && bw > p.bw)) {
+                        best = c;
+                        p.bw = bw;
+                        p.bh = bh;
+                        p.bi = bi;
+                    }
+                }
             }
+            if (best > 0) memo[key] = {p.bw, p.bh, p.bi};
         }
     }
     B200SEG_CHECK(best > 0, "conv: no tile shape for %dx%dx%d", n, h, w);
@@ -396,6 +584,14 @@ int launch_igemm(int n, int h, int w, int n_src, const b200seg_conv_src* src, co
         if (encode_tmap_bf16(&p.b_map[i], s.w, 3, bdims, bstr, bbox)) return 1;
     }
 
+    if (!out->out_fp32) {
+        const uint64_t ydims[4] = {(uint64_t)out->k, (uint64_t)w, (uint64_t)h, (uint64_t)n};
+        const uint64_t ystr[3] = {(uint64_t)out->y_c_total * 2, (uint64_t)w * out->y_c_total * 2,
+                                  (uint64_t)h * w * out->y_c_total * 2};
+        const uint32_t ybox[4] = {kOutSlab, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bi};
+        const char* ybase = static_cast<const char*>(out->y) + (size_t)out->y_c_offset * 2;
+        if (encode_tmap_bf16(&p.y_map, ybase, 4, ydims, ystr, ybox)) return 1;
+    }
     p.y = out->y;
     p.y_c_total = out->y_c_total;
     p.y_c_offset = out->y_c_offset;
@@ -405,6 +601,8 @@ int launch_igemm(int n, int h, int w, int n_src, const b200seg_conv_src* src, co
     p.bias = out->bias;
     p.relu = out->relu;
     p.stats = out->stats;
+    p.dbg = g_dbg;
+    p.dbg_slots = g_dbg_slots;
     B200SEG_CHECK((reinterpret_cast<uintptr_t>(out->y) & 15) == 0, "conv: output pointer not 16-byte aligned");
 
     static bool attr_set = false;
@@ -424,6 +622,12 @@ int launch_igemm(int n, int h, int w, int n_src, const b200seg_conv_src* src, co
 }  // namespace b200seg
 
 extern "C" {
+
+int b200seg_debug_timing(int64_t* buf, int slots) {
+    b200seg::g_dbg = reinterpret_cast<long long*>(buf);
+    b200seg::g_dbg_slots = buf ? slots : 0;
+    return 0;
+}
 
 int b200seg_conv_fprop(int n, int h, int w, int n_src, const b200seg_conv_src* src, const b200seg_conv_out* out,
                        b200seg_stream_t st) {

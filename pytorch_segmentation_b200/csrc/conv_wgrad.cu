@@ -18,6 +18,10 @@
 
 #include <string.h>
 
+#include <map>
+#include <mutex>
+#include <vector>
+
 namespace b200seg {
 namespace {
 
@@ -46,13 +50,30 @@ struct __align__(64) WgradParams {
     float* ws;
 };
 
-__device__ __forceinline__ bool patch_in_bounds(const WgradParams& p, int kp, int dy, int dx, int& x0, int& y0, int& n0) {
-    x0 = (kp % p.patches_x) * p.bw;
-    int t = kp / p.patches_x;
-    y0 = (t % p.patches_y) * p.bh;
-    n0 = (t / p.patches_y) * p.bi;
-    return (y0 + dy < p.H) && (y0 + p.bh - 1 + dy >= 0) && (x0 + dx < p.W) && (x0 + p.bw - 1 + dx >= 0);
-}
+// Walks the pixel patches kp = begin, begin+1, ... with running (x, y, image) patch counters: the producer and the
+// MMA issuer are single threads, so a division per pipeline stage would sit on the critical path.
+struct PatchWalker {
+    int px, py, pn;
+    __device__ __forceinline__ void init(const WgradParams& p, int kp) {
+        px = kp % p.patches_x;
+        const int t = kp / p.patches_x;
+        py = t % p.patches_y;
+        pn = t / p.patches_y;
+    }
+    __device__ __forceinline__ void next(const WgradParams& p) {
+        if (++px == p.patches_x) {
+            px = 0;
+            if (++py == p.patches_y) {
+                py = 0;
+                ++pn;
+            }
+        }
+    }
+    __device__ __forceinline__ bool in_bounds(const WgradParams& p, int dy, int dx) const {
+        const int x0 = px * p.bw, y0 = py * p.bh;
+        return (y0 + dy < p.H) && (y0 + p.bh - 1 + dy >= 0) && (x0 + dx < p.W) && (x0 + p.bw - 1 + dx >= 0);
+    }
+};
 
 __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constant__ WgradParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -109,9 +130,11 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
             const uint32_t tx_bytes = kABytes + n_boxes * kBoxBytes;
             const int mdx = p.shift_m ? dx : 0, mdy = p.shift_m ? dy : 0;
             const int ndx = p.shift_m ? 0 : dx, ndy = p.shift_m ? 0 : dy;
-            for (int kp = kp_begin; kp < kp_end; ++kp) {
-                int x0, y0, n0;
-                if (!patch_in_bounds(p, kp, dy, dx, x0, y0, n0)) continue;
+            PatchWalker pw;
+            pw.init(p, kp_begin);
+            for (int kp = kp_begin; kp < kp_end; ++kp, pw.next(p)) {
+                if (!pw.in_bounds(p, dy, dx)) continue;
+                const int x0 = pw.px * p.bw, y0 = pw.py * p.bh, n0 = pw.pn * p.bi;
                 mbar_wait(&empty[stage], phase ^ 1);
                 uint8_t* sa = smem + stage * kStageBytes;
                 mbar_arrive_expect_tx(&full[stage], tx_bytes);
@@ -132,9 +155,10 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
-            for (int kp = kp_begin; kp < kp_end; ++kp) {
-                int x0, y0, n0;
-                if (!patch_in_bounds(p, kp, dy, dx, x0, y0, n0)) continue;
+            PatchWalker pw;
+            pw.init(p, kp_begin);
+            for (int kp = kp_begin; kp < kp_end; ++kp, pw.next(p)) {
+                if (!pw.in_bounds(p, dy, dx)) continue;
                 mbar_wait(&full[stage], phase);
                 tc_fence_after();
                 const uint32_t sa = smem_u32(smem + stage * kStageBytes);
@@ -161,10 +185,9 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
     } else if (warp >= 4) {
         // any work at all for this (tap, split)?  (uniform across the CTA)
         bool any = false;
-        for (int kp = kp_begin; kp < kp_end && !any; ++kp) {
-            int x0, y0, n0;
-            any = patch_in_bounds(p, kp, dy, dx, x0, y0, n0);
-        }
+        PatchWalker pw;
+        pw.init(p, kp_begin);
+        for (int kp = kp_begin; kp < kp_end && !any; ++kp, pw.next(p)) any = pw.in_bounds(p, dy, dx);
         const int q = warp & 3;
         const int row = q * 32 + lane;
         mbar_wait(tfull, 0);
@@ -222,7 +245,7 @@ struct WgradPlan {
     size_t ws_bytes;
 };
 
-int plan_wgrad(const b200seg_wgrad_desc* d, WgradPlan* pl) {
+int plan_wgrad_uncached(const b200seg_wgrad_desc* d, WgradPlan* pl) {
     B200SEG_CHECK(d && d->dy && d->x && d->dw, "wgrad: null pointer");
     B200SEG_CHECK(d->n > 0 && d->h > 0 && d->w > 0, "wgrad: bad shape");
     B200SEG_CHECK((d->r == 1 && d->s == 1) || (d->r == 3 && d->s == 3), "wgrad: only 1x1 and 3x3 filters");
@@ -279,6 +302,27 @@ int plan_wgrad(const b200seg_wgrad_desc* d, WgradPlan* pl) {
     pl->pps = ceil_div(patches, splits);
     pl->splits = ceil_div(patches, pl->pps);
     pl->ws_bytes = static_cast<size_t>(pl->splits) * d->r * d->s * pl->m_pad * pl->n_pad * sizeof(float);
+    return 0;
+}
+
+// The patch search walks every patch of the map: memoise the plan per geometry.
+int plan_wgrad(const b200seg_wgrad_desc* d, WgradPlan* pl) {
+    B200SEG_CHECK(d, "wgrad: null descriptor");
+    static std::mutex mu;
+    static std::map<std::vector<int>, WgradPlan> memo;
+    const std::vector<int> key = {d->n, d->h, d->w, d->k, d->c, d->r, d->s, d->dil, d->k_out, d->dy_c_offset % 8,
+                                  d->dy_c_total % 8, d->x_c_offset % 8, d->x_c_total % 8};
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        auto it = memo.find(key);
+        if (it != memo.end() && d->dy && d->x && d->dw) {
+            *pl = it->second;
+            return 0;
+        }
+    }
+    if (plan_wgrad_uncached(d, pl)) return 1;
+    std::lock_guard<std::mutex> lock(mu);
+    memo[key] = *pl;
     return 0;
 }
 
