@@ -52,7 +52,7 @@ int b200seg_pack_weights(const float* w_oihw, int k, int c, int r, int s, void* 
                          int c_rows, int k_cols, b200seg_stream_t st);
 
 /* ---- convolution: tcgen05 implicit GEMM ------------------------------------------------------------------ */
-/* One input of a stride-1 "same" convolution: activation slice + packed weights + filter geometry. */
+/* One input of a "same"-padded convolution (stride 1 or 2): activation slice + packed weights + filter geometry. */
 typedef struct b200seg_conv_src {
     const void* x;        /* bf16 NHWC */
     int32_t x_c_total;    /* channels per pixel of the buffer */
@@ -62,6 +62,8 @@ typedef struct b200seg_conv_src {
     int32_t w_rows;       /* rows per tap in the packed weight (>= output channels) */
     int32_t r, s;         /* filter taps: 1x1 or 3x3 */
     int32_t dil;          /* dilation; padding is ((r-1)/2)*dil */
+    int32_t stride;       /* 1 or 2 (2 needs dil == 1).  fprop: x is (stride*h) x (stride*w).  dgrad: x (= dY) is
+                             (h/stride) x (w/stride) and the call's n,h,w is the dX grid */
 } b200seg_conv_src;
 
 typedef struct b200seg_conv_out {
@@ -79,7 +81,7 @@ typedef struct b200seg_conv_out {
                              without a second pass over the output */
 } b200seg_conv_out;
 
-/* y = act(scale * sum_src conv(x_src, w_src) + bias).
+/* y = act(scale * sum_src conv(x_src, w_src) + bias) on the n x h x w OUTPUT grid.
  * Replaces nn.Conv2d inside ConvNormAct (models/aspp.py:12,27,29,30; models/deeplabv3plus.py:20;
  * models/unet.py:19-21) and cls_conv (models/deeplabv3plus.py:22,39; models/unet.py:23,51).  With w packed by
  * the dgrad packing and x = dy this is the data gradient; several sources accumulate in TMEM, which is how
@@ -97,6 +99,7 @@ typedef struct b200seg_wgrad_desc {
     const void* x;        /* bf16 NHWC conv input */
     int32_t x_c_total, x_c_offset, c;
     int32_t r, s, dil;
+    int32_t stride;       /* 1 or 2 (2 needs dil == 1): n, h, w is the dY grid, x is (stride*h) x (stride*w) */
     float* dw;            /* fp32 OIHW [k_out][c][r][s] */
     int32_t k_out;        /* logical output channels (<= k) */
     int32_t accumulate;   /* dw += result instead of dw = result */

@@ -16,7 +16,8 @@ MAX_CONV_SRC = 4
 class ConvSrc(Structure):
     """struct b200seg_conv_src"""
     _fields_ = [('x', c_void_p), ('x_c_total', c_int32), ('x_c_offset', c_int32), ('c', c_int32),
-                ('w', c_void_p), ('w_rows', c_int32), ('r', c_int32), ('s', c_int32), ('dil', c_int32)]
+                ('w', c_void_p), ('w_rows', c_int32), ('r', c_int32), ('s', c_int32), ('dil', c_int32),
+                ('stride', c_int32)]
 
 
 class ConvOut(Structure):
@@ -31,7 +32,7 @@ class WgradDesc(Structure):
     _fields_ = [('n', c_int32), ('h', c_int32), ('w', c_int32),
                 ('dy', c_void_p), ('dy_c_total', c_int32), ('dy_c_offset', c_int32), ('k', c_int32),
                 ('x', c_void_p), ('x_c_total', c_int32), ('x_c_offset', c_int32), ('c', c_int32),
-                ('r', c_int32), ('s', c_int32), ('dil', c_int32),
+                ('r', c_int32), ('s', c_int32), ('dil', c_int32), ('stride', c_int32),
                 ('dw', c_void_p), ('k_out', c_int32), ('accumulate', c_int32),
                 ('workspace', c_void_p), ('workspace_bytes', c_size_t)]
 

@@ -46,15 +46,23 @@ constexpr int kOutBufs = 2;
 constexpr int kSmemBytes = kStages * kStageBytes + kOutBufs * kOutBufBytes + kBarrierBytes + 1024;   // +1024: alignment
 constexpr int kTmemCols = 512;
 
+constexpr int kMaxSeg = 8;
+constexpr int kMaxTaps = 9;
+
+// One reduction segment: an activation view (tensor map), a packed weight, and the filter taps that read this view
+// — each tap is a pixel shift (dy, dx) in the view's grid plus the index of its weight slab.  A stride-1 conv is one
+// segment with all R*S taps (shift = (r - R/2) * dilation); a stride-2 conv is one segment per input parity
+// sub-grid (a strided view of the input) with the taps that land on it.
 struct IgemmSeg {
-    int r, s, dil, cblks;
+    int ntaps, cblks;
+    short dy[kMaxTaps], dx[kMaxTaps], wtap[kMaxTaps];
 };
 
 struct __align__(64) IgemmParams {
-    CUtensorMap a_map[B200SEG_MAX_CONV_SRC];
-    CUtensorMap b_map[B200SEG_MAX_CONV_SRC];
-    CUtensorMap y_map;       // bf16 output slice (channels, W, H, N), box = 64 channels x pixel patch
-    IgemmSeg seg[B200SEG_MAX_CONV_SRC];
+    CUtensorMap a_map[kMaxSeg];
+    CUtensorMap b_map[kMaxSeg];
+    CUtensorMap y_map;       // bf16 output view (channels, W, H, N), box = 64 channels x pixel patch
+    IgemmSeg seg[kMaxSeg];
     int nseg;
     int N, H, W;
     int bw, bh, bi;          // patch dims (powers of two)
@@ -149,23 +157,20 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
             for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
                 const TileCoord t = decode_tile(p, tile);
                 for (int sg = 0; sg < p.nseg; ++sg) {
-                    const IgemmSeg seg = p.seg[sg];
-                    for (int r = 0; r < seg.r; ++r) {
-                        const int dy = (r - seg.r / 2) * seg.dil;
-                        for (int s = 0; s < seg.s; ++s) {
-                            const int dx = (s - seg.s / 2) * seg.dil;
-                            if (!tap_in_bounds(p, t, dy, dx)) continue;
-                            const int tap = r * seg.s + s;
-                            for (int cb = 0; cb < seg.cblks; ++cb) {
-                                mbar_wait(&empty[stage], phase ^ 1);
-                                uint8_t* sa = smem + stage * kStageBytes;
-                                mbar_arrive_expect_tx(&full[stage], tx_bytes);
-                                tma_load_4d(sa, &p.a_map[sg], &full[stage], cb * kBK, t.x0 + dx, t.y0 + dy, t.n0);
-                                tma_load_3d(sa + kABytes, &p.b_map[sg], &full[stage], cb * kBK, t.n_tile * p.bn, tap);
-                                if (++stage == kStages) {
-                                    stage = 0;
-                                    phase ^= 1;
-                                }
+                    const IgemmSeg& seg = p.seg[sg];
+                    for (int tp = 0; tp < seg.ntaps; ++tp) {
+                        const int dy = seg.dy[tp], dx = seg.dx[tp];
+                        if (!tap_in_bounds(p, t, dy, dx)) continue;
+                        const int tap = seg.wtap[tp];
+                        for (int cb = 0; cb < seg.cblks; ++cb) {
+                            mbar_wait(&empty[stage], phase ^ 1);
+                            uint8_t* sa = smem + stage * kStageBytes;
+                            mbar_arrive_expect_tx(&full[stage], tx_bytes);
+                            tma_load_4d(sa, &p.a_map[sg], &full[stage], cb * kBK, t.x0 + dx, t.y0 + dy, t.n0);
+                            tma_load_3d(sa + kABytes, &p.b_map[sg], &full[stage], cb * kBK, t.n_tile * p.bn, tap);
+                            if (++stage == kStages) {
+                                stage = 0;
+                                phase ^= 1;
                             }
                         }
                     }
@@ -183,11 +188,9 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
                 const TileCoord t = decode_tile(p, tile);
                 int kiters = 0;
                 for (int sg = 0; sg < p.nseg; ++sg) {
-                    const IgemmSeg seg = p.seg[sg];
-                    for (int r = 0; r < seg.r; ++r)
-                        for (int s = 0; s < seg.s; ++s)
-                            if (tap_in_bounds(p, t, (r - seg.r / 2) * seg.dil, (s - seg.s / 2) * seg.dil))
-                                kiters += seg.cblks;
+                    const IgemmSeg& seg = p.seg[sg];
+                    for (int tp = 0; tp < seg.ntaps; ++tp)
+                        if (tap_in_bounds(p, t, seg.dy[tp], seg.dx[tp])) kiters += seg.cblks;
                 }
                 const int acc = lt & 1;
                 const uint32_t acc_phase = (lt >> 1) & 1;
@@ -466,78 +469,74 @@ int ilog2(int v) {
     return l;
 }
 
+// Host-side description of one segment before its tensor maps are encoded.
+struct SegPlan {
+    const char* a_base;        // first element of the activation view
+    uint64_t adims[4];         // (channels, W, H, N) of the view
+    uint64_t astr[3];          // byte strides of W, H, N
+    const void* w;             // packed weights [taps][w_rows][c]
+    int w_rows, c, w_taps;
+    IgemmSeg seg;
+};
+
+// Output view of one launch: (channels, W, H, N) with byte strides (a parity sub-grid of dX is a strided view).
+struct OutPlan {
+    char* base;
+    uint64_t dims[4];
+    uint64_t str[3];
+};
+
 // Total pipeline iterations (TMA box pairs) the whole problem costs with a bw x bh x bi patch.
-long long patch_cost(int N, int H, int W, int bw, int bh, int bi, int nseg, const IgemmSeg* seg) {
+long long patch_cost(int N, int H, int W, int bw, int bh, int bi, int nseg, const SegPlan* sp) {
     const int tx = ceil_div(W, bw), ty = ceil_div(H, bh), ti = ceil_div(N, bi);
     long long per_image = 0;
-    for (int y = 0; y < ty; ++y)
-        for (int x = 0; x < tx; ++x) {
-            const int y0 = y * bh, x0 = x * bw;
-            for (int g = 0; g < nseg; ++g)
-                for (int r = 0; r < seg[g].r; ++r)
-                    for (int s = 0; s < seg[g].s; ++s) {
-                        const int dy = (r - seg[g].r / 2) * seg[g].dil, dx = (s - seg[g].s / 2) * seg[g].dil;
-                        if ((y0 + dy < H) && (y0 + bh - 1 + dy >= 0) && (x0 + dx < W) && (x0 + bw - 1 + dx >= 0))
-                            per_image += seg[g].cblks;
-                    }
+    for (int g = 0; g < nseg; ++g) {
+        const IgemmSeg& seg = sp[g].seg;
+        for (int tp = 0; tp < seg.ntaps; ++tp) {
+            const int dy = seg.dy[tp], dx = seg.dx[tp];
+            // the in-bounds test is separable: count tile rows and tile columns that touch the image
+            int ny = 0, nx = 0;
+            for (int y = 0; y < ty; ++y) ny += (y * bh + dy < H) && (y * bh + bh - 1 + dy >= 0);
+            for (int x = 0; x < tx; ++x) nx += (x * bw + dx < W) && (x * bw + bw - 1 + dx >= 0);
+            per_image += static_cast<long long>(ny) * nx * seg.cblks;
         }
+    }
     return per_image * ti;
 }
 
-int launch_igemm(int n, int h, int w, int n_src, const b200seg_conv_src* src, const b200seg_conv_out* out,
-                 cudaStream_t st) {
-    clear_error();
-    B200SEG_CHECK(n > 0 && h > 0 && w > 0, "conv: bad activation shape %dx%dx%d", n, h, w);
-    B200SEG_CHECK(n_src >= 1 && n_src <= B200SEG_MAX_CONV_SRC, "conv: n_src %d out of range", n_src);
-    B200SEG_CHECK(out && out->y, "conv: null output");
-    B200SEG_CHECK(out->k > 0 && out->k % 8 == 0 && out->y_c_offset % 8 == 0 && out->y_c_total % 8 == 0,
-                  "conv: output channels (k=%d, offset=%d, total=%d) must be multiples of 8", out->k,
-                  out->y_c_offset, out->y_c_total);
-    B200SEG_CHECK(out->y_c_offset + out->k <= out->y_c_total, "conv: output slice exceeds buffer channels");
-
+// Encodes the maps and launches the persistent kernel over an n x h x w output grid.
+int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPlan& op, const b200seg_conv_out* out,
+                   cudaStream_t st) {
     IgemmParams p;
     memset(&p, 0, sizeof(p));
-    p.nseg = n_src;
+    p.nseg = nseg;
     p.N = n;
     p.H = h;
     p.W = w;
-    for (int i = 0; i < n_src; ++i) {
-        const b200seg_conv_src& s = src[i];
-        B200SEG_CHECK(s.x && s.w, "conv: source %d has null pointers", i);
-        B200SEG_CHECK((s.r == 1 && s.s == 1) || (s.r == 3 && s.s == 3), "conv: only 1x1 and 3x3 filters (got %dx%d)",
-                      s.r, s.s);
-        B200SEG_CHECK(s.dil >= 1, "conv: dilation %d", s.dil);
-        B200SEG_CHECK(s.c > 0 && s.c % 8 == 0 && s.x_c_offset % 8 == 0 && s.x_c_total % 8 == 0,
-                      "conv: input channels (c=%d, offset=%d, total=%d) must be multiples of 8", s.c, s.x_c_offset,
-                      s.x_c_total);
-        B200SEG_CHECK(s.x_c_offset + s.c <= s.x_c_total, "conv: input slice exceeds buffer channels");
-        B200SEG_CHECK(s.w_rows >= out->k, "conv: packed weight has %d rows < %d output channels", s.w_rows, out->k);
-        p.seg[i].r = s.r;
-        p.seg[i].s = s.s;
-        p.seg[i].dil = s.dil;
-        p.seg[i].cblks = ceil_div(s.c, kBK);
+    bool has_center = false;
+    for (int i = 0; i < nseg; ++i) {
+        p.seg[i] = sp[i].seg;
+        for (int tp = 0; tp < sp[i].seg.ntaps; ++tp) has_center |= sp[i].seg.dy[tp] == 0 && sp[i].seg.dx[tp] == 0;
     }
+    B200SEG_CHECK(has_center, "conv: internal: launch without an unshifted tap");
 
-    // output-channel tiling
+    // output-channel tiling: whole 64-channel store slabs per n-tile (a narrow single tile may be 32 wide: the
+    // store clips at k)
     p.tiles_n = ceil_div(out->k, kMaxBN);
-    // whole 64-channel store slabs per n-tile (a narrow single tile may be 32 wide: the store clips at k)
     p.bn = out->k <= 32 ? 32 : round_up(ceil_div(out->k, p.tiles_n), kOutSlab);
     B200SEG_CHECK(p.bn <= kMaxBN, "conv: internal bn %d", p.bn);
-    B200SEG_CHECK(!(out->stats && (out->scale || out->bias || out->relu || out->out_fp32)),
-                  "conv: fused BN statistics are those of the stored bf16 conv result; scale/bias/relu/fp32 output "
-                  "cannot be combined with them");
 
-    // pixel patch: the power-of-two bw x bh x bi = 128 shape that needs the fewest pipeline iterations.  The search
-    // walks every tile of the map, so its result is memoised per geometry (a training step repeats the same few).
+    // pixel patch: the power-of-two bw x bh x bi = 128 shape that needs the fewest pipeline iterations (memoised
+    // per geometry: a training step repeats the same few)
     long long best = -1;
     {
         static std::mutex mu;
         static std::map<std::vector<int>, std::array<int, 3>> memo;
-        std::vector<int> key = {n, h, w, n_src};
-        for (int i = 0; i < n_src; ++i) {
-            key.push_back(p.seg[i].r);
-            key.push_back(p.seg[i].dil);
+        std::vector<int> key = {n, h, w, nseg};
+        for (int i = 0; i < nseg; ++i) {
+            key.push_back(p.seg[i].ntaps);
             key.push_back(p.seg[i].cblks);
+            for (int tp = 0; tp < p.seg[i].ntaps; ++tp) key.push_back(p.seg[i].dy[tp] * 65536 + p.seg[i].dx[tp]);
         }
         std::lock_guard<std::mutex> lock(mu);
         auto it = memo.find(key);
@@ -550,7 +549,7 @@ int launch_igemm(int n, int h, int w, int n_src, const b200seg_conv_src* src, co
             for (int bi = 1; bi <= 128; bi *= 2) {
                 for (int bw = 1; bw * bi <= 128; bw *= 2) {
                     const int bh = 128 / (bw * bi);
-                    const long long c = patch_cost(n, h, w, bw, bh, bi, n_src, p.seg);
+                    const long long c = patch_cost(n, h, w, bw, bh, bi, nseg, sp);
                     if (best < 0 || c < best || (c == best && bw > p.bw)) {
                         best = c;
                         p.bw = bw;
@@ -570,27 +569,17 @@ int launch_igemm(int n, int h, int w, int n_src, const b200seg_conv_src* src, co
     p.tiles_i = ceil_div(n, p.bi);
     p.num_tiles = p.tiles_x * p.tiles_y * p.tiles_i * p.tiles_n;
 
-    for (int i = 0; i < n_src; ++i) {
-        const b200seg_conv_src& s = src[i];
-        const uint64_t adims[4] = {(uint64_t)s.c, (uint64_t)w, (uint64_t)h, (uint64_t)n};
-        const uint64_t astr[3] = {(uint64_t)s.x_c_total * 2, (uint64_t)w * s.x_c_total * 2,
-                                  (uint64_t)h * w * s.x_c_total * 2};
+    for (int i = 0; i < nseg; ++i) {
         const uint32_t abox[4] = {kBK, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bi};
-        const char* abase = static_cast<const char*>(s.x) + (size_t)s.x_c_offset * 2;
-        if (encode_tmap_bf16(&p.a_map[i], abase, 4, adims, astr, abox)) return 1;
-        const uint64_t bdims[3] = {(uint64_t)s.c, (uint64_t)s.w_rows, (uint64_t)(s.r * s.s)};
-        const uint64_t bstr[2] = {(uint64_t)s.c * 2, (uint64_t)s.w_rows * s.c * 2};
+        if (encode_tmap_bf16(&p.a_map[i], sp[i].a_base, 4, sp[i].adims, sp[i].astr, abox)) return 1;
+        const uint64_t bdims[3] = {(uint64_t)sp[i].c, (uint64_t)sp[i].w_rows, (uint64_t)sp[i].w_taps};
+        const uint64_t bstr[2] = {(uint64_t)sp[i].c * 2, (uint64_t)sp[i].w_rows * sp[i].c * 2};
         const uint32_t bbox[3] = {kBK, (uint32_t)p.bn, 1};
-        if (encode_tmap_bf16(&p.b_map[i], s.w, 3, bdims, bstr, bbox)) return 1;
+        if (encode_tmap_bf16(&p.b_map[i], sp[i].w, 3, bdims, bstr, bbox)) return 1;
     }
-
     if (!out->out_fp32) {
-        const uint64_t ydims[4] = {(uint64_t)out->k, (uint64_t)w, (uint64_t)h, (uint64_t)n};
-        const uint64_t ystr[3] = {(uint64_t)out->y_c_total * 2, (uint64_t)w * out->y_c_total * 2,
-                                  (uint64_t)h * w * out->y_c_total * 2};
         const uint32_t ybox[4] = {kOutSlab, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bi};
-        const char* ybase = static_cast<const char*>(out->y) + (size_t)out->y_c_offset * 2;
-        if (encode_tmap_bf16(&p.y_map, ybase, 4, ydims, ystr, ybox)) return 1;
+        if (encode_tmap_bf16(&p.y_map, op.base, 4, op.dims, op.str, ybox)) return 1;
     }
     p.y = out->y;
     p.y_c_total = out->y_c_total;
@@ -603,7 +592,6 @@ int launch_igemm(int n, int h, int w, int n_src, const b200seg_conv_src* src, co
     p.stats = out->stats;
     p.dbg = g_dbg;
     p.dbg_slots = g_dbg_slots;
-    B200SEG_CHECK((reinterpret_cast<uintptr_t>(out->y) & 15) == 0, "conv: output pointer not 16-byte aligned");
 
     static bool attr_set = false;
     if (!attr_set) {
@@ -615,6 +603,208 @@ int launch_igemm(int n, int h, int w, int n_src, const b200seg_conv_src* src, co
     const int grid = p.num_tiles < sms ? p.num_tiles : sms;
     igemm_kernel<<<grid, kThreads, kSmemBytes, st>>>(p);
     B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int check_common(int n, int h, int w, int n_src, const b200seg_conv_src* src, const b200seg_conv_out* out) {
+    B200SEG_CHECK(n > 0 && h > 0 && w > 0, "conv: bad activation shape %dx%dx%d", n, h, w);
+    B200SEG_CHECK(n_src >= 1 && n_src <= B200SEG_MAX_CONV_SRC, "conv: n_src %d out of range", n_src);
+    B200SEG_CHECK(out && out->y, "conv: null output");
+    B200SEG_CHECK(out->k > 0 && out->k % 8 == 0 && out->y_c_offset % 8 == 0 && out->y_c_total % 8 == 0,
+                  "conv: output channels (k=%d, offset=%d, total=%d) must be multiples of 8", out->k,
+                  out->y_c_offset, out->y_c_total);
+    B200SEG_CHECK(out->y_c_offset + out->k <= out->y_c_total, "conv: output slice exceeds buffer channels");
+    B200SEG_CHECK((reinterpret_cast<uintptr_t>(out->y) & 15) == 0, "conv: output pointer not 16-byte aligned");
+    B200SEG_CHECK(!(out->stats && (out->scale || out->bias || out->relu || out->out_fp32)),
+                  "conv: fused BN statistics are those of the stored bf16 conv result; scale/bias/relu/fp32 output "
+                  "cannot be combined with them");
+    for (int i = 0; i < n_src; ++i) {
+        const b200seg_conv_src& s = src[i];
+        B200SEG_CHECK(s.x && s.w, "conv: source %d has null pointers", i);
+        B200SEG_CHECK((s.r == 1 && s.s == 1) || (s.r == 3 && s.s == 3), "conv: only 1x1 and 3x3 filters (got %dx%d)",
+                      s.r, s.s);
+        B200SEG_CHECK(s.dil >= 1 && s.dil <= 4096, "conv: dilation %d", s.dil);
+        B200SEG_CHECK(s.stride == 1 || s.stride == 2, "conv: stride %d (only 1 and 2)", s.stride);
+        B200SEG_CHECK(s.stride == 1 || s.dil == 1, "conv: stride 2 with dilation %d is not supported", s.dil);
+        B200SEG_CHECK(s.c > 0 && s.c % 8 == 0 && s.x_c_offset % 8 == 0 && s.x_c_total % 8 == 0,
+                      "conv: input channels (c=%d, offset=%d, total=%d) must be multiples of 8", s.c, s.x_c_offset,
+                      s.x_c_total);
+        B200SEG_CHECK(s.x_c_offset + s.c <= s.x_c_total, "conv: input slice exceeds buffer channels");
+        B200SEG_CHECK(s.w_rows >= out->k, "conv: packed weight has %d rows < %d output channels", s.w_rows, out->k);
+    }
+    return 0;
+}
+
+// Activation view: the (hv x wv) sub-grid of an (hf x wf) NHWC tensor starting at pixel (oy, ox) with pixel step
+// `step` in both directions.
+void set_view(SegPlan* sp, const void* x, int c_total, int c_off, int c, int n, int hf, int wf, int oy, int ox, int step,
+              int hv, int wv) {
+    sp->a_base = static_cast<const char*>(x) + (static_cast<size_t>(oy) * wf + ox) * c_total * 2 + static_cast<size_t>(c_off) * 2;
+    sp->adims[0] = c;
+    sp->adims[1] = wv;
+    sp->adims[2] = hv;
+    sp->adims[3] = n;
+    sp->astr[0] = static_cast<uint64_t>(step) * c_total * 2;
+    sp->astr[1] = static_cast<uint64_t>(step) * wf * c_total * 2;
+    sp->astr[2] = static_cast<uint64_t>(hf) * wf * c_total * 2;
+}
+
+void plain_out(OutPlan* op, const b200seg_conv_out* out, int n, int h, int w) {
+    op->base = static_cast<char*>(out->y) + static_cast<size_t>(out->y_c_offset) * 2;
+    op->dims[0] = out->k;
+    op->dims[1] = w;
+    op->dims[2] = h;
+    op->dims[3] = n;
+    op->str[0] = static_cast<uint64_t>(out->y_c_total) * 2;
+    op->str[1] = static_cast<uint64_t>(w) * out->y_c_total * 2;
+    op->str[2] = static_cast<uint64_t>(h) * w * out->y_c_total * 2;
+}
+
+inline int floor_div2(int v) { return v >= 0 ? v / 2 : -((-v + 1) / 2); }
+
+// Forward: n x h x w is the OUTPUT grid; a stride-2 source reads a (2h x 2w) input through its four parity views.
+int launch_fprop(int n, int h, int w, int n_src, const b200seg_conv_src* src, const b200seg_conv_out* out,
+                 cudaStream_t st) {
+    clear_error();
+    if (check_common(n, h, w, n_src, src, out)) return 1;
+    SegPlan sp[kMaxSeg];
+    memset(sp, 0, sizeof(sp));
+    int nseg = 0;
+    for (int i = 0; i < n_src; ++i) {
+        const b200seg_conv_src& s = src[i];
+        if (s.stride == 1) {
+            B200SEG_CHECK(nseg < kMaxSeg, "conv: too many segments");
+            SegPlan& g = sp[nseg++];
+            set_view(&g, s.x, s.x_c_total, s.x_c_offset, s.c, n, h, w, 0, 0, 1, h, w);
+            g.w = s.w;
+            g.w_rows = s.w_rows;
+            g.c = s.c;
+            g.w_taps = s.r * s.s;
+            g.seg.cblks = ceil_div(s.c, kBK);
+            for (int r = 0; r < s.r; ++r)
+                for (int q = 0; q < s.s; ++q) {
+                    const int t = g.seg.ntaps++;
+                    g.seg.dy[t] = static_cast<short>((r - s.r / 2) * s.dil);
+                    g.seg.dx[t] = static_cast<short>((q - s.s / 2) * s.dil);
+                    g.seg.wtap[t] = static_cast<short>(r * s.s + q);
+                }
+        } else {
+            // input pixel = 2*o + (r - R/2): parity picks the view, floor((r - R/2)/2) is the shift inside it
+            for (int py = 0; py < 2; ++py)
+                for (int px = 0; px < 2; ++px) {
+                    SegPlan g;
+                    memset(&g, 0, sizeof(g));
+                    for (int r = 0; r < s.r; ++r)
+                        for (int q = 0; q < s.s; ++q) {
+                            const int oy = r - s.r / 2, ox = q - s.s / 2;
+                            if ((oy & 1) != py || (ox & 1) != px) continue;
+                            const int t = g.seg.ntaps++;
+                            g.seg.dy[t] = static_cast<short>(floor_div2(oy));
+                            g.seg.dx[t] = static_cast<short>(floor_div2(ox));
+                            g.seg.wtap[t] = static_cast<short>(r * s.s + q);
+                        }
+                    if (g.seg.ntaps == 0) continue;
+                    B200SEG_CHECK(nseg < kMaxSeg, "conv: too many segments");
+                    set_view(&g, s.x, s.x_c_total, s.x_c_offset, s.c, n, 2 * h, 2 * w, py, px, 2, h, w);
+                    g.w = s.w;
+                    g.w_rows = s.w_rows;
+                    g.c = s.c;
+                    g.w_taps = s.r * s.s;
+                    g.seg.cblks = ceil_div(s.c, kBK);
+                    sp[nseg++] = g;
+                }
+        }
+    }
+    OutPlan op;
+    plain_out(&op, out, n, h, w);
+    return launch_planned(n, h, w, nseg, sp, op, out, st);
+}
+
+// Backward-data: n x h x w is the dX grid.  A source that was a stride-1 conv brings a dY of the same size; a
+// stride-2 source brings a dY of (h/2 x w/2).  Weights are the dgrad packing (taps mirrored), so
+//   dX[i] = sum_t' dY[(i + (t' - R/2) * dil) / stride] * Wd[t']      over the t' for which the division is exact.
+// With any stride-2 source the launch is split into the four parity sub-grids of dX (strided output views); each
+// source contributes, per parity, the taps that land on it.
+int launch_dgrad(int n, int h, int w, int n_src, const b200seg_conv_src* src, const b200seg_conv_out* out,
+                 cudaStream_t st) {
+    clear_error();
+    if (check_common(n, h, w, n_src, src, out)) return 1;
+    bool any_s2 = false;
+    for (int i = 0; i < n_src; ++i) any_s2 |= src[i].stride == 2;
+    if (!any_s2) return launch_fprop(n, h, w, n_src, src, out, st);     // same GEMM, mirrored weights
+
+    B200SEG_CHECK(h % 2 == 0 && w % 2 == 0, "conv dgrad: stride 2 needs even dX size (got %dx%d)", h, w);
+    B200SEG_CHECK(!out->out_fp32 && !out->stats, "conv dgrad: stride 2 writes bf16 without statistics");
+    const int hs = h / 2, ws = w / 2;
+    for (int py = 0; py < 2; ++py)
+        for (int px = 0; px < 2; ++px) {
+            SegPlan sp[kMaxSeg];
+            memset(sp, 0, sizeof(sp));
+            int nseg = 0;
+            for (int i = 0; i < n_src; ++i) {
+                const b200seg_conv_src& s = src[i];
+                if (s.stride == 2) {
+                    SegPlan g;
+                    memset(&g, 0, sizeof(g));
+                    for (int r = 0; r < s.r; ++r)
+                        for (int q = 0; q < s.s; ++q) {
+                            const int ey = py + r - s.r / 2, ex = px + q - s.s / 2;
+                            if ((ey & 1) || (ex & 1)) continue;
+                            const int t = g.seg.ntaps++;
+                            g.seg.dy[t] = static_cast<short>(ey / 2);
+                            g.seg.dx[t] = static_cast<short>(ex / 2);
+                            g.seg.wtap[t] = static_cast<short>(r * s.s + q);
+                        }
+                    if (g.seg.ntaps == 0) continue;
+                    B200SEG_CHECK(nseg < kMaxSeg, "conv dgrad: too many segments");
+                    set_view(&g, s.x, s.x_c_total, s.x_c_offset, s.c, n, hs, ws, 0, 0, 1, hs, ws);
+                    g.w = s.w;
+                    g.w_rows = s.w_rows;
+                    g.c = s.c;
+                    g.w_taps = s.r * s.s;
+                    g.seg.cblks = ceil_div(s.c, kBK);
+                    sp[nseg++] = g;
+                } else {
+                    // full-resolution dY seen from the parity sub-grid: pixel 2i' + p + o -> view (p+o)&1, shift floor
+                    for (int vy = 0; vy < 2; ++vy)
+                        for (int vx = 0; vx < 2; ++vx) {
+                            SegPlan g;
+                            memset(&g, 0, sizeof(g));
+                            for (int r = 0; r < s.r; ++r)
+                                for (int q = 0; q < s.s; ++q) {
+                                    const int oy = py + (r - s.r / 2) * s.dil, ox = px + (q - s.s / 2) * s.dil;
+                                    if ((oy & 1) != vy || (ox & 1) != vx) continue;
+                                    const int t = g.seg.ntaps++;
+                                    g.seg.dy[t] = static_cast<short>(floor_div2(oy));
+                                    g.seg.dx[t] = static_cast<short>(floor_div2(ox));
+                                    g.seg.wtap[t] = static_cast<short>(r * s.s + q);
+                                }
+                            if (g.seg.ntaps == 0) continue;
+                            B200SEG_CHECK(nseg < kMaxSeg, "conv dgrad: too many segments");
+                            set_view(&g, s.x, s.x_c_total, s.x_c_offset, s.c, n, h, w, vy, vx, 2, hs, ws);
+                            g.w = s.w;
+                            g.w_rows = s.w_rows;
+                            g.c = s.c;
+                            g.w_taps = s.r * s.s;
+                            g.seg.cblks = ceil_div(s.c, kBK);
+                            sp[nseg++] = g;
+                        }
+                }
+            }
+            B200SEG_CHECK(nseg > 0, "conv dgrad: parity (%d,%d) of dX receives no gradient from any source; zero-fill "
+                                    "is not implemented (combine the stride-2 1x1 with a stride-1 source)", py, px);
+            OutPlan op;
+            op.base = static_cast<char*>(out->y) + (static_cast<size_t>(py) * w + px) * out->y_c_total * 2 +
+                      static_cast<size_t>(out->y_c_offset) * 2;
+            op.dims[0] = out->k;
+            op.dims[1] = ws;
+            op.dims[2] = hs;
+            op.dims[3] = n;
+            op.str[0] = 2ull * out->y_c_total * 2;
+            op.str[1] = 2ull * w * out->y_c_total * 2;
+            op.str[2] = static_cast<uint64_t>(h) * w * out->y_c_total * 2;
+            if (launch_planned(n, hs, ws, nseg, sp, op, out, st)) return 1;
+        }
     return 0;
 }
 
@@ -631,12 +821,12 @@ int b200seg_debug_timing(int64_t* buf, int slots) {
 
 int b200seg_conv_fprop(int n, int h, int w, int n_src, const b200seg_conv_src* src, const b200seg_conv_out* out,
                        b200seg_stream_t st) {
-    return b200seg::launch_igemm(n, h, w, n_src, src, out, static_cast<cudaStream_t>(st));
+    return b200seg::launch_fprop(n, h, w, n_src, src, out, static_cast<cudaStream_t>(st));
 }
 
 int b200seg_conv_dgrad(int n, int h, int w, int n_src, const b200seg_conv_src* src, const b200seg_conv_out* out,
                        b200seg_stream_t st) {
-    return b200seg::launch_igemm(n, h, w, n_src, src, out, static_cast<cudaStream_t>(st));
+    return b200seg::launch_dgrad(n, h, w, n_src, src, out, static_cast<cudaStream_t>(st));
 }
 
 }  // extern "C"

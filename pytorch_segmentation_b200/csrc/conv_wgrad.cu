@@ -37,11 +37,12 @@ constexpr int kThreads = 256;
 constexpr int kSmemBytes = kStages * kStageBytes + 256 + 1024;
 
 struct __align__(64) WgradParams {
-    CUtensorMap m_map;     // M-side tensor (channels, W, H, N)
-    CUtensorMap n_map;     // N-side tensor
-    int N, H, W;
-    int R, S, dil;
-    int shift_m;           // 1: the M side is X (gets the tap shift); 0: the N side is X
+    CUtensorMap x_map[4];  // X views (channels, W, H, N): one for stride 1, the four parity sub-grids for stride 2
+    CUtensorMap y_map;     // dY (channels, W, H, N)
+    int N, H, W;           // the dY grid
+    int R, S;
+    short tap_map[9], tap_dy[9], tap_dx[9];   // per filter tap: which X view it reads and its pixel shift there
+    int shift_m;           // 1: the M side is X; 0: the N side is X
     int bw, bh, bi;
     int patches_x, patches_y, patches;
     int tiles_m, tiles_n, bn;
@@ -96,14 +97,17 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
     const int taps = p.R * p.S;
     const int tap = tile % taps;
     const int split = tile / taps;
-    const int dy = (tap / p.S - p.R / 2) * p.dil;
-    const int dx = (tap % p.S - p.S / 2) * p.dil;
+    const int dy = p.tap_dy[tap];
+    const int dx = p.tap_dx[tap];
+    const CUtensorMap* xm = &p.x_map[p.tap_map[tap]];
+    const CUtensorMap* m_map = p.shift_m ? xm : &p.y_map;
+    const CUtensorMap* n_map = p.shift_m ? &p.y_map : xm;
     const int kp_begin = split * p.patches_per_split;
     const int kp_end = min(kp_begin + p.patches_per_split, p.patches);
 
     if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&p.m_map);
-        tma_prefetch_desc(&p.n_map);
+        tma_prefetch_desc(m_map);
+        tma_prefetch_desc(n_map);
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < kStages; ++i) {
@@ -139,9 +143,9 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
                 uint8_t* sa = smem + stage * kStageBytes;
                 mbar_arrive_expect_tx(&full[stage], tx_bytes);
                 for (int b = 0; b < 2; ++b)
-                    tma_load_4d(sa + b * kBoxBytes, &p.m_map, &full[stage], m_tile * kBM + b * 64, x0 + mdx, y0 + mdy, n0);
+                    tma_load_4d(sa + b * kBoxBytes, m_map, &full[stage], m_tile * kBM + b * 64, x0 + mdx, y0 + mdy, n0);
                 for (int b = 0; b < n_boxes; ++b)
-                    tma_load_4d(sa + kABytes + b * kBoxBytes, &p.n_map, &full[stage], n_tile * p.bn + b * 64, x0 + ndx,
+                    tma_load_4d(sa + kABytes + b * kBoxBytes, n_map, &full[stage], n_tile * p.bn + b * 64, x0 + ndx,
                                 y0 + ndy, n0);
                 if (++stage == kStages) {
                     stage = 0;
@@ -249,6 +253,8 @@ int plan_wgrad_uncached(const b200seg_wgrad_desc* d, WgradPlan* pl) {
     B200SEG_CHECK(d && d->dy && d->x && d->dw, "wgrad: null pointer");
     B200SEG_CHECK(d->n > 0 && d->h > 0 && d->w > 0, "wgrad: bad shape");
     B200SEG_CHECK((d->r == 1 && d->s == 1) || (d->r == 3 && d->s == 3), "wgrad: only 1x1 and 3x3 filters");
+    B200SEG_CHECK(d->stride == 1 || (d->stride == 2 && d->dil == 1), "wgrad: stride %d / dilation %d not supported",
+                  d->stride, d->dil);
     B200SEG_CHECK(d->k % 8 == 0 && d->dy_c_offset % 8 == 0 && d->dy_c_total % 8 == 0 && d->c % 8 == 0 &&
                       d->x_c_offset % 8 == 0 && d->x_c_total % 8 == 0,
                   "wgrad: channel counts/offsets must be multiples of 8");
@@ -273,7 +279,11 @@ int plan_wgrad_uncached(const b200seg_wgrad_desc* d, WgradPlan* pl) {
                 for (int x = 0; x < px; ++x)
                     for (int r = 0; r < d->r; ++r)
                         for (int s = 0; s < d->s; ++s) {
-                            const int dy = (r - d->r / 2) * d->dil, dx = (s - d->s / 2) * d->dil;
+                            int dy = (r - d->r / 2) * d->dil, dx = (s - d->s / 2) * d->dil;
+                            if (d->stride == 2) {
+                                dy = dy >= 0 ? dy / 2 : -((-dy + 1) / 2);
+                                dx = dx >= 0 ? dx / 2 : -((-dx + 1) / 2);
+                            }
                             const int y0 = y * bh, x0 = x * bw;
                             if ((y0 + dy < d->h) && (y0 + bh - 1 + dy >= 0) && (x0 + dx < d->w) && (x0 + bw - 1 + dx >= 0))
                                 ++cost;
@@ -310,7 +320,7 @@ int plan_wgrad(const b200seg_wgrad_desc* d, WgradPlan* pl) {
     B200SEG_CHECK(d, "wgrad: null descriptor");
     static std::mutex mu;
     static std::map<std::vector<int>, WgradPlan> memo;
-    const std::vector<int> key = {d->n, d->h, d->w, d->k, d->c, d->r, d->s, d->dil, d->k_out, d->dy_c_offset % 8,
+    const std::vector<int> key = {d->n, d->h, d->w, d->k, d->c, d->r, d->s, d->dil, d->stride, d->k_out, d->dy_c_offset % 8,
                                   d->dy_c_total % 8, d->x_c_offset % 8, d->x_c_total % 8};
     {
         std::lock_guard<std::mutex> lock(mu);
@@ -356,7 +366,6 @@ int b200seg_conv_wgrad(const b200seg_wgrad_desc* d, b200seg_stream_t stream) {
     p.W = d->w;
     p.R = d->r;
     p.S = d->s;
-    p.dil = d->dil;
     p.shift_m = pl.shift_m;
     p.bw = pl.bw;
     p.bh = pl.bh;
@@ -373,22 +382,39 @@ int b200seg_conv_wgrad(const b200seg_wgrad_desc* d, b200seg_stream_t stream) {
     p.n_pad = pl.n_pad;
     p.ws = static_cast<float*>(d->workspace);
 
+    // n, h, w describe the dY grid; X is (stride*h) x (stride*w).  Tap (r, s) reads X pixel stride*o + (r - R/2)*dil:
+    // for stride 2 its parity picks one of four strided views of X and floor(./2) is the shift inside that view.
     const uint32_t box[4] = {64, (uint32_t)pl.bw, (uint32_t)pl.bh, (uint32_t)pl.bi};
-    const uint64_t xdims[4] = {(uint64_t)d->c, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n};
-    const uint64_t xstr[3] = {(uint64_t)d->x_c_total * 2, (uint64_t)d->w * d->x_c_total * 2,
-                              (uint64_t)d->h * d->w * d->x_c_total * 2};
+    const int cs = d->stride;
+    const int hx = d->h * cs, wx = d->w * cs;
     const uint64_t ydims[4] = {(uint64_t)d->k, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n};
     const uint64_t ystr[3] = {(uint64_t)d->dy_c_total * 2, (uint64_t)d->w * d->dy_c_total * 2,
                               (uint64_t)d->h * d->w * d->dy_c_total * 2};
-    const char* xbase = static_cast<const char*>(d->x) + (size_t)d->x_c_offset * 2;
     const char* ybase = static_cast<const char*>(d->dy) + (size_t)d->dy_c_offset * 2;
-    if (pl.shift_m) {
-        if (encode_tmap_bf16(&p.m_map, xbase, 4, xdims, xstr, box)) return 1;
-        if (encode_tmap_bf16(&p.n_map, ybase, 4, ydims, ystr, box)) return 1;
-    } else {
-        if (encode_tmap_bf16(&p.m_map, ybase, 4, ydims, ystr, box)) return 1;
-        if (encode_tmap_bf16(&p.n_map, xbase, 4, xdims, xstr, box)) return 1;
-    }
+    if (encode_tmap_bf16(&p.y_map, ybase, 4, ydims, ystr, box)) return 1;
+    const uint64_t xdims[4] = {(uint64_t)d->c, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n};
+    const uint64_t xstr[3] = {(uint64_t)cs * d->x_c_total * 2, (uint64_t)cs * wx * d->x_c_total * 2,
+                              (uint64_t)hx * wx * d->x_c_total * 2};
+    for (int vy = 0; vy < cs; ++vy)
+        for (int vx = 0; vx < cs; ++vx) {
+            const char* xbase = static_cast<const char*>(d->x) + ((size_t)vy * wx + vx) * d->x_c_total * 2 +
+                                (size_t)d->x_c_offset * 2;
+            if (encode_tmap_bf16(&p.x_map[vy * 2 + vx], xbase, 4, xdims, xstr, box)) return 1;
+        }
+    for (int r = 0; r < d->r; ++r)
+        for (int s = 0; s < d->s; ++s) {
+            const int oy = (r - d->r / 2) * d->dil, ox = (s - d->s / 2) * d->dil;
+            const int t = r * d->s + s;
+            if (cs == 1) {
+                p.tap_map[t] = 0;
+                p.tap_dy[t] = static_cast<short>(oy);
+                p.tap_dx[t] = static_cast<short>(ox);
+            } else {
+                p.tap_map[t] = static_cast<short>((oy & 1) * 2 + (ox & 1));
+                p.tap_dy[t] = static_cast<short>(oy >= 0 ? oy / 2 : -((-oy + 1) / 2));
+                p.tap_dx[t] = static_cast<short>(ox >= 0 ? ox / 2 : -((-ox + 1) / 2));
+            }
+        }
 
     static bool attr_set = false;
     if (!attr_set) {

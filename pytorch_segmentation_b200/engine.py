@@ -143,8 +143,11 @@ PROFILE = None
 def _conv(fn, what, n, h, w, srcs, out_ptr, y_ct, y_off, k, out_fp32, scale, bias, relu, stats):
     if PROFILE is not None:
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        flops = 2.0 * n * h * w * k * sum(x.c * r * s for x, _, _, r, s, _ in srcs)
-        tag = '%s %dx%dx%d k%d %s' % (what, n, h, w, k, '+'.join('c%d r%d d%d' % (x.c, r, d) for x, _, _, r, _, d in srcs))
+        # nominal dense flops: fprop counts output pixels; a stride-2 dgrad source has h*w/4 dY pixels
+        flops = 2.0 * n * h * w * k * sum(x.c * r * s / (st * st if what == 'conv_dgrad' else 1)
+                                          for x, _, _, r, s, _, st in srcs)
+        tag = '%s %dx%dx%d k%d %s' % (what, n, h, w, k, '+'.join('c%d r%d d%d%s' % (x.c, r, d, ' s2' if st == 2 else '')
+                                                              for x, _, _, r, _, d, st in srcs))
         ev0.record()
         _conv_launch(fn, what, n, h, w, srcs, out_ptr, y_ct, y_off, k, out_fp32, scale, bias, relu, stats)
         ev1.record()
@@ -155,47 +158,60 @@ def _conv(fn, what, n, h, w, srcs, out_ptr, y_ct, y_off, k, out_fp32, scale, bia
 
 def _conv_launch(fn, what, n, h, w, srcs, out_ptr, y_ct, y_off, k, out_fp32, scale, bias, relu, stats):
     arr = (ConvSrc * len(srcs))()
-    for i, (x, wptr, w_rows, r, s, dil) in enumerate(srcs):
-        arr[i] = ConvSrc(x.ptr, x.ct, x.c_off, x.c, wptr, w_rows, r, s, dil)
+    for i, (x, wptr, w_rows, r, s, dil, stride) in enumerate(srcs):
+        arr[i] = ConvSrc(x.ptr, x.ct, x.c_off, x.c, wptr, w_rows, r, s, dil, stride)
     out = ConvOut(out_ptr, y_ct, y_off, k, int(out_fp32),
                   scale.data_ptr() if scale is not None else None,
                   bias.data_ptr() if bias is not None else None, int(relu),
                   stats.data_ptr() if stats is not None else None)
     _lib.check(fn(n, h, w, len(srcs), arr, ctypes.byref(out), _stream()), what)
-    _lib.count_launch()
+    # a dgrad with a stride-2 source is one launch per parity sub-grid of dX
+    _lib.count_launch(4 if what == 'conv_dgrad' and any(t[6] == 2 for t in srcs) else 1)
+
+
+def _src(t):
+    """(act, pw, dil) or (act, pw, dil, stride) -> (act, pw, dil, stride)"""
+    return t if len(t) == 4 else (t[0], t[1], t[2], 1)
 
 
 def conv_fprop(srcs, out, scale=None, bias=None, relu=False, stats=None):
-    """srcs: list of (x: Act, pw: PackedWeight, dil).  out: Act (bf16) — y = act(scale * sum conv + bias)."""
-    x0 = srcs[0][0]
-    _conv(_lib.load().b200seg_conv_fprop, 'conv_fprop', x0.n, x0.h, x0.w,
-          [(x, pw.wf.data_ptr(), pw.k_rows, pw.r, pw.s, dil) for x, pw, dil in srcs],
+    """srcs: list of (x: Act, pw: PackedWeight, dil[, stride]).  out: Act (bf16) on the output grid —
+    y = act(scale * sum conv + bias); a stride-2 source's x is twice the size of out."""
+    srcs = [_src(t) for t in srcs]
+    for x, pw, dil, stride in srcs:
+        assert (x.n, x.h, x.w) == (out.n, out.h * stride, out.w * stride), 'conv_fprop: input/output size mismatch'
+    _conv(_lib.load().b200seg_conv_fprop, 'conv_fprop', out.n, out.h, out.w,
+          [(x, pw.wf.data_ptr(), pw.k_rows, pw.r, pw.s, dil, stride) for x, pw, dil, stride in srcs],
           out.ptr, out.ct, out.c_off, out.c, False, scale, bias, relu, stats)
 
 
 def conv_fprop_f32(srcs, out_t, k, bias=None):
     """Same, fp32 NHWC output tensor [n, h, w, k] (the class map of cls_conv)."""
-    x0 = srcs[0][0]
-    _conv(_lib.load().b200seg_conv_fprop, 'conv_fprop', x0.n, x0.h, x0.w,
-          [(x, pw.wf.data_ptr(), pw.k_rows, pw.r, pw.s, dil) for x, pw, dil in srcs],
+    srcs = [_src(t) for t in srcs]
+    _conv(_lib.load().b200seg_conv_fprop, 'conv_fprop', out_t.shape[0], out_t.shape[1], out_t.shape[2],
+          [(x, pw.wf.data_ptr(), pw.k_rows, pw.r, pw.s, dil, stride) for x, pw, dil, stride in srcs],
           out_t.data_ptr(), out_t.shape[3], 0, k, True, None, bias, False, None)
 
 
 def conv_dgrad(srcs, dx):
-    """srcs: list of (dy: Act, pw: PackedWeight, dil); dx: Act receiving the sum of the data gradients."""
-    d0 = srcs[0][0]
-    _conv(_lib.load().b200seg_conv_dgrad, 'conv_dgrad', d0.n, d0.h, d0.w,
-          [(dy, pw.wd.data_ptr(), pw.c_rows, pw.r, pw.s, dil) for dy, pw, dil in srcs],
+    """srcs: list of (dy: Act, pw: PackedWeight, dil[, stride]); dx: Act receiving the sum of the data gradients
+    (a stride-2 source's dy is half the size of dx)."""
+    srcs = [_src(t) for t in srcs]
+    for dy, pw, dil, stride in srcs:
+        assert (dy.n, dy.h * stride, dy.w * stride) == (dx.n, dx.h, dx.w), 'conv_dgrad: gradient size mismatch'
+    _conv(_lib.load().b200seg_conv_dgrad, 'conv_dgrad', dx.n, dx.h, dx.w,
+          [(dy, pw.wd.data_ptr(), pw.c_rows, pw.r, pw.s, dil, stride) for dy, pw, dil, stride in srcs],
           dx.ptr, dx.ct, dx.c_off, dx.c, False, None, None, False, None)
 
 
-def conv_wgrad(dy, x, k_out, r, s, dil, dw=None):
+def conv_wgrad(dy, x, k_out, r, s, dil, dw=None, stride=1):
     """dW fp32 OIHW [k_out, x.c, r, s] = sum_pixels dy (x) shifted x."""
     desc = WgradDesc()
-    desc.n, desc.h, desc.w = x.n, x.h, x.w
+    assert (x.n, x.h, x.w) == (dy.n, dy.h * stride, dy.w * stride), 'conv_wgrad: size mismatch'
+    desc.n, desc.h, desc.w = dy.n, dy.h, dy.w
     desc.dy, desc.dy_c_total, desc.dy_c_offset, desc.k = dy.ptr, dy.ct, dy.c_off, dy.c
     desc.x, desc.x_c_total, desc.x_c_offset, desc.c = x.ptr, x.ct, x.c_off, x.c
-    desc.r, desc.s, desc.dil = r, s, dil
+    desc.r, desc.s, desc.dil, desc.stride = r, s, dil, stride
     accumulate = dw is not None
     if dw is None:
         dw = torch.empty((k_out, x.c, r, s), dtype=torch.float32, device=x.t.device)
@@ -214,8 +230,9 @@ def conv_wgrad(dy, x, k_out, r, s, dil, dw=None):
     _lib.check(lib.b200seg_conv_wgrad(ctypes.byref(desc), _stream()), 'conv_wgrad')
     if PROFILE is not None:
         ev1.record()
-        PROFILE.append(('conv_wgrad %dx%dx%d k%d c%d r%d d%d' % (x.n, x.h, x.w, dy.c, x.c, r, dil),
-                        2.0 * x.pixels * dy.c * x.c * r * s, ev0, ev1))
+        PROFILE.append(('conv_wgrad %dx%dx%d k%d c%d r%d d%d%s' % (dy.n, dy.h, dy.w, dy.c, x.c, r, dil,
+                                                                   ' s2' if stride == 2 else ''),
+                        2.0 * dy.pixels * dy.c * x.c * r * s, ev0, ev1))
     _lib.count_launch(2)
     return dw
 

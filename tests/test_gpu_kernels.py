@@ -81,6 +81,90 @@ def test_conv_fprop_dgrad_wgrad(E, n, h, w, c, k, ks, dil):
     assert rel_err(dw, wt.grad) < 5e-3
 
 
+STRIDE2_CASES = [
+    # n, h_out, w_out, c, k, ksize
+    (2, 16, 16, 128, 128, 3),
+    (1, 8, 24, 64, 96, 3),
+    (2, 16, 16, 256, 512, 1),
+    (3, 4, 4, 72, 40, 3),
+]
+
+
+@pytest.mark.parametrize('n,h,w,c,k,ks', STRIDE2_CASES)
+def test_conv_stride2_fprop_dgrad_wgrad(E, n, h, w, c, k, ks):
+    """Stride-2 convs of the ResNet backbone (3x3 conv2 and 1x1 downsample of layer2.0 / layer3.0): the input is
+    read through its four parity sub-grid views, dgrad writes the four parity sub-grids of dX."""
+    g = torch.Generator().manual_seed(n * 1000 + h * 10 + c + k)
+    x = bf16_round(torch.randn(n, c, 2 * h, 2 * w, generator=g))
+    wt = bf16_round(torch.randn(k, c, ks, ks, generator=g) * (2.0 / (c * ks * ks)) ** 0.5)
+    dy = bf16_round(torch.randn(n, k, h, w, generator=g))
+    x.requires_grad_(True)
+    wt.requires_grad_(True)
+    y_ref = F.conv2d(x, wt, None, 2, ks // 2, 1)
+    assert y_ref.shape == dy.shape
+    y_ref.backward(dy)
+
+    pw = E.PackedWeight().update(wt.detach().cuda(), need_dgrad=True)
+    xa = nhwc(x.detach())
+    ya = E.Act.empty(n, h, w, k, 'cuda')
+    stats = torch.zeros(2 * k, device='cuda')
+    E.conv_fprop([(xa, pw, 1, 2)], ya, stats=stats)
+    assert rel_err(from_act(ya), y_ref) < TOL
+    y_st = from_act(ya)
+    assert rel_err(stats[:k], y_st.sum((0, 2, 3))) < 2e-3
+    assert rel_err(stats[k:], (y_st ** 2).sum((0, 2, 3))) < 1e-4
+
+    dya = nhwc(dy)
+    dw = E.conv_wgrad(dya, xa, k, ks, ks, 1, stride=2)
+    assert rel_err(dw, wt.grad) < 5e-3
+
+    if ks == 3:
+        dxa = E.Act(torch.full((n, 2 * h, 2 * w, c), 7.0, dtype=torch.bfloat16, device='cuda'))
+        E.conv_dgrad([(dya, pw, 1, 2)], dxa)
+        assert rel_err(from_act(dxa), x.grad) < TOL
+    else:
+        # a stride-2 1x1 alone leaves three of four dX pixels without gradient: refused (no silent garbage)
+        dxa = E.Act.empty(n, 2 * h, 2 * w, c, 'cuda')
+        with pytest.raises(RuntimeError):
+            E.conv_dgrad([(dya, pw, 1, 2)], dxa)
+
+
+def test_conv_dgrad_mixed_stride_sources(E):
+    """Block-input gradient of a ResNet downsampling bottleneck: dX = dgrad(conv1: 1x1 s1) + dgrad(downsample: 1x1 s2)
+    in the same launches."""
+    g = torch.Generator().manual_seed(11)
+    n, h, w, c, k1, k2 = 2, 16, 16, 128, 64, 256
+    x = bf16_round(torch.randn(n, c, h, w, generator=g)).requires_grad_(True)
+    w1 = bf16_round(torch.randn(k1, c, 1, 1, generator=g) * 0.1).requires_grad_(True)
+    w2 = bf16_round(torch.randn(k2, c, 1, 1, generator=g) * 0.1).requires_grad_(True)
+    dy1 = bf16_round(torch.randn(n, k1, h, w, generator=g))
+    dy2 = bf16_round(torch.randn(n, k2, h // 2, w // 2, generator=g))
+    (F.conv2d(x, w1) * dy1).sum().backward()
+    (F.conv2d(x, w2, None, 2) * dy2).sum().backward()
+    p1 = E.PackedWeight().update(w1.detach().cuda(), True)
+    p2 = E.PackedWeight().update(w2.detach().cuda(), True)
+    dxa = E.Act.empty(n, h, w, c, 'cuda')
+    E.conv_dgrad([(nhwc(dy1), p1, 1, 1), (nhwc(dy2), p2, 1, 2)], dxa)
+    assert rel_err(from_act(dxa), x.grad) < TOL
+
+
+def test_conv_dgrad_mixed_3x3_s1_and_s2(E):
+    g = torch.Generator().manual_seed(12)
+    n, h, w, c = 1, 12, 20, 64
+    x = bf16_round(torch.randn(n, c, h, w, generator=g)).requires_grad_(True)
+    w1 = bf16_round(torch.randn(32, c, 3, 3, generator=g) * 0.1).requires_grad_(True)
+    w2 = bf16_round(torch.randn(48, c, 3, 3, generator=g) * 0.1).requires_grad_(True)
+    dy1 = bf16_round(torch.randn(n, 32, h, w, generator=g))
+    dy2 = bf16_round(torch.randn(n, 48, h // 2, w // 2, generator=g))
+    (F.conv2d(x, w1, None, 1, 2, 2) * dy1).sum().backward()
+    (F.conv2d(x, w2, None, 2, 1) * dy2).sum().backward()
+    p1 = E.PackedWeight().update(w1.detach().cuda(), True)
+    p2 = E.PackedWeight().update(w2.detach().cuda(), True)
+    dxa = E.Act.empty(n, h, w, c, 'cuda')
+    E.conv_dgrad([(nhwc(dy1), p1, 2, 1), (nhwc(dy2), p2, 1, 2)], dxa)
+    assert rel_err(from_act(dxa), x.grad) < TOL
+
+
 def test_conv_epilogue_scale_bias_relu_into_slice(E):
     g = torch.Generator().manual_seed(5)
     n, h, w, c, k = 2, 16, 16, 64, 128
