@@ -248,8 +248,8 @@ def run_b200(args):
             'config': {'workload': 'DeepLabV3+ 21-class 512x512 bf16 training, fwd+loss+bwd+SGD (BASELINE configs[3])',
                        'per_gpu_batch': B, 'global_batch': B * world, 'parallelism': 'dp%d' % world,
                        'l2': 'no explicit flush: one step streams several GB of activations (>> 126 MB L2)',
-                       'backbone': 'torchvision ResNet-50 OS16, channels_last bf16 autocast (cuDNN) — outside the '
-                                   'hot path this round (SURVEY.md 8f-1); head + loss on libb200seg'},
+                       'backbone': 'ResNet-50 OS16 on libb200seg (tcgen05 convs incl. stride 2, fused BN/ReLU/residual, '
+                                   'max pool); only the 3-channel 7x7 stem conv is cuDNN (SURVEY.md 8f-1)'},
             'e2e': {'value': ips_e2e, 'unit': 'images/sec', 'h2d_bytes_per_step': x_host.numel() * 4 + t_host.numel() * 8,
                     'd2h_bytes_per_step': 4, 'ms_per_step': secs_e2e / args.steps * 1e3},
             'gpu_launches': launches,

@@ -124,6 +124,16 @@ int b200seg_bn_finalize(const float* stats, int c, int64_t count, const float* g
 /* y = relu?(x*scale + shift) from one NHWC slice into another (BN apply + nn.ReLU + concat placement). */
 int b200seg_bn_apply(const void* x, int x_c_total, int x_c_offset, void* y, int y_c_total, int y_c_offset, int c,
                      int64_t pixels, const float* scale, const float* shift, int relu, b200seg_stream_t st);
+/* Residual form used by the ResNet bottlenecks of the backbone (pytorch_modules.backbones.resnet50, called at
+ * models/deeplabv3plus.py:17-19,29): y = relu?(x*scale + shift + r) with r = res (identity) or res*res_scale +
+ * res_shift (the downsample conv's raw output and its BN); res == NULL reduces to b200seg_bn_apply. */
+int b200seg_bn_apply_add(const void* x, int x_c_total, int x_c_offset, void* y, int y_c_total, int y_c_offset, int c,
+                         int64_t pixels, const float* scale, const float* shift, int relu, const void* res,
+                         int res_c_total, int res_c_offset, const float* res_scale, const float* res_shift,
+                         b200seg_stream_t st);
+/* dx += dy * (y > 0): the identity branch's gradient joins the conv branch's at a residual block's input. */
+int b200seg_relu_bwd_add(void* dx, int dx_c_total, int dx_c_offset, const void* dy, int dy_c_total, int dy_c_offset,
+                         const void* y, int y_c_total, int y_c_offset, int c, int64_t pixels, b200seg_stream_t st);
 /* eval mode (test.py:16, inference.py:24): scale/shift from the running statistics; feeds the conv epilogue so
  * Conv+BN+ReLU is one kernel.  save_mean/save_invstd (optional) receive the running mean and 1/sqrt(var+eps). */
 int b200seg_bn_eval_affine(int c, const float* gamma, const float* beta, const float* running_mean,
@@ -142,6 +152,19 @@ int b200seg_bn_bwd_apply(const void* dy, int dy_c_total, int dy_c_offset, const 
                          int relu, int training, const float* red, float* dgamma, float* dbeta,
                          int accumulate_param_grads, b200seg_stream_t st);
 
+/* Same two passes with the ReLU mask taken from a stored tensor (mask > 0) instead of recomputed from x: after a
+ * residual add the sign of the block output is not a function of this BN's input alone. */
+int b200seg_bn_bwd_reduce_masked(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total,
+                                 int x_c_offset, int c, int64_t pixels, const float* scale, const float* shift,
+                                 const float* save_mean, const float* save_invstd, int relu, float* red, const void* mask,
+                                 int mask_c_total, int mask_c_offset, b200seg_stream_t st);
+int b200seg_bn_bwd_apply_masked(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total,
+                                int x_c_offset, void* dx, int dx_c_total, int dx_c_offset, int c, int64_t pixels,
+                                const float* scale, const float* shift, const float* save_mean, const float* save_invstd,
+                                int relu, int training, const float* red, float* dgamma, float* dbeta,
+                                int accumulate_param_grads, const void* mask, int mask_c_total, int mask_c_offset,
+                                b200seg_stream_t st);
+
 /* ---- resampling ------------------------------------------------------------------------------------------ */
 /* Bilinear resize of an NHWC bf16 slice into another slice (F.interpolate(..., mode='bilinear') +
  * torch.cat placement: models/deeplabv3plus.py:34-38, models/unet.py:30-50). */
@@ -151,6 +174,13 @@ int b200seg_upsample_fwd(const void* x, int x_c_total, int x_c_offset, int n, in
 int b200seg_upsample_bwd(const void* dy, int dy_c_total, int dy_c_offset, int n, int oh, int ow, void* dx,
                          int dx_c_total, int dx_c_offset, int h, int w, int c, int align_corners,
                          b200seg_stream_t st);
+/* nn.MaxPool2d(3, stride 2, padding 1) of the ResNet stem (pytorch_modules.backbones.resnet50, called at
+ * models/deeplabv3plus.py:17-19,29) on NHWC bf16: (h x w) -> ((h+1)/2 x (w+1)/2).  idx [n][oh][ow][c] (one byte per
+ * element) receives the window position of each maximum for the gather-form backward. */
+int b200seg_maxpool3x3s2_fwd(const void* x, int x_c_total, int x_c_offset, int n, int h, int w, void* y, int y_c_total,
+                             int y_c_offset, uint8_t* idx, int c, b200seg_stream_t st);
+int b200seg_maxpool3x3s2_bwd(const void* dy, int dy_c_total, int dy_c_offset, const uint8_t* idx, int n, int h, int w,
+                             void* dx, int dx_c_total, int dx_c_offset, int c, b200seg_stream_t st);
 /* nn.AdaptiveAvgPool2d(1) (models/aspp.py:11): mean over H*W of an NHWC bf16 slice -> fp32 [n][c]
  * (the H*W range is split across CTAs; fp32 atomics into y). */
 int b200seg_gap_fwd(const void* x, int x_c_total, int x_c_offset, int n, int hw, int c, float* y, b200seg_stream_t st);

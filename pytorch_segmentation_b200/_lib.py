@@ -59,11 +59,18 @@ PROTOTYPES = {
     'b200seg_bn_finalize': (c_int, [_P, _I, _L, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P]),
     'b200seg_bn_eval_affine': (c_int, [_I, _P, _P, _P, _P, _F, _P, _P, _P, _P, _P]),
     'b200seg_bn_apply': (c_int, [_P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _I, _P]),
+    'b200seg_bn_apply_add': (c_int, [_P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _I, _P, _I, _I, _P, _P, _P]),
+    'b200seg_relu_bwd_add': (c_int, [_P, _I, _I, _P, _I, _I, _P, _I, _I, _I, _L, _P]),
+    'b200seg_bn_bwd_reduce_masked': (c_int, [_P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _P, _P, _I, _P, _P, _I, _I, _P]),
+    'b200seg_bn_bwd_apply_masked': (c_int, [_P, _I, _I, _P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _P, _P, _I, _I, _P, _P,
+                                            _P, _I, _P, _I, _I, _P]),
     'b200seg_bn_bwd_reduce': (c_int, [_P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _P, _P, _I, _P, _P]),
     'b200seg_bn_bwd_apply': (c_int, [_P, _I, _I, _P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _P, _P, _I, _I, _P, _P,
                                      _P, _I, _P]),
     'b200seg_upsample_fwd': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _I, _I, _P]),
     'b200seg_upsample_bwd': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _I, _I, _P]),
+    'b200seg_maxpool3x3s2_fwd': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _I, _P, _I, _P]),
+    'b200seg_maxpool3x3s2_bwd': (c_int, [_P, _I, _I, _P, _I, _I, _I, _P, _I, _I, _I, _P]),
     'b200seg_gap_fwd': (c_int, [_P, _I, _I, _I, _I, _I, _P, _P]),
     'b200seg_sum_hw': (c_int, [_P, _I, _I, _I, _I, _I, _P, _P]),
     'b200seg_linear_f32_fwd': (c_int, [_P, _P, _P, _I, _I, _I, _P]),

@@ -48,7 +48,12 @@ class _ResNetFeatures(_Features):
         return feats
 
 
-def resnet50(pretrained=False, replace_stride_with_dilation=None, **kw):
+def resnet50(pretrained=False, replace_stride_with_dilation=None, native=True, **kw):
+    """native=True (default): the tcgen05 path (resnet.py).  native=False: the torchvision/cuDNN stand-in kept for
+    A/B measurements (scripts/)."""
+    if native:
+        from .resnet import ResNet50Features
+        return ResNet50Features(replace_stride_with_dilation)
     net = torchvision.models.resnet50(weights=None, replace_stride_with_dilation=replace_stride_with_dilation)
     return _ResNetFeatures(net).to(memory_format=torch.channels_last)
 

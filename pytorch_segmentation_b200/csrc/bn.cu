@@ -153,7 +153,10 @@ __global__ void bn_eval_affine_kernel(int c, const float* __restrict__ gamma, co
 __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __restrict__ x, int x_ct, int x_off,
                                                         __nv_bfloat16* __restrict__ y, int y_ct, int y_off, int groups,
                                                         int64_t total, const float* __restrict__ scale,
-                                                        const float* __restrict__ shift, int relu) {
+                                                        const float* __restrict__ shift, int relu,
+                                                        const __nv_bfloat16* __restrict__ res, int r_ct, int r_off,
+                                                        const float* __restrict__ res_scale,
+                                                        const float* __restrict__ res_shift) {
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int g = static_cast<int>(i % groups);
@@ -163,9 +166,23 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
         load8f(scale + g * 8, sc);
         load8f(shift + g * 8, sh);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            f[j] = fmaf(f[j], sc[j], sh[j]);
-            if (relu) f[j] = fmaxf(f[j], 0.f);
+        for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]);
+        if (res) {
+            // residual branch: the identity, or the downsample conv's raw output with its own BN affine
+            float r[8];
+            unpack8(ldg128(res + p * r_ct + r_off + g * 8), r);
+            if (res_scale) {
+                load8f(res_scale + g * 8, sc);
+                load8f(res_shift + g * 8, sh);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) r[j] = fmaf(r[j], sc[j], sh[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] += r[j];
+        }
+        if (relu) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
         }
         st128(y + p * y_ct + y_off + g * 8, pack8(f));
     }
@@ -175,7 +192,8 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
 __global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(
     const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off, const __nv_bfloat16* __restrict__ x, int x_ct, int x_off,
     int c, int64_t pixels, int64_t ppb, int gpb, int rows, const float* __restrict__ scale, const float* __restrict__ shift,
-    const float* __restrict__ mean, const float* __restrict__ invstd, int relu, float* __restrict__ red) {
+    const float* __restrict__ mean, const float* __restrict__ invstd, int relu, float* __restrict__ red,
+    const __nv_bfloat16* __restrict__ mask, int m_ct, int m_off) {
     const int groups = c >> 3;
     const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
     const int group = blockIdx.y * gpb + g_local;
@@ -192,13 +210,21 @@ __global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(
         const int64_t p1 = min(p0 + ppb, pixels);
         const __nv_bfloat16* xb = x + x_off + group * 8;
         const __nv_bfloat16* db = dy + dy_off + group * 8;
+        const __nv_bfloat16* mb = mask ? mask + m_off + group * 8 : nullptr;
         for (int64_t p = p0 + row; p < p1; p += rows) {
-            float f[8], d[8];
+            float f[8], d[8], m[8];
             unpack8(ldg128(xb + p * x_ct), f);
             unpack8(ldg128(db + p * dy_ct), d);
+            if (mb) {
+                // ReLU mask from the stored block output (BN output + residual), not recomputable from x alone
+                unpack8(ldg128(mb + p * m_ct), m);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) m[j] = fmaf(f[j], sc[j], sh[j]);
+            }
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                const float dz = (relu && fmaf(f[j], sc[j], sh[j]) <= 0.f) ? 0.f : d[j];
+                const float dz = (relu && m[j] <= 0.f) ? 0.f : d[j];
                 acc[0][j] += dz;
                 acc[1][j] = fmaf(dz, (f[j] - mu[j]) * is[j], acc[1][j]);
             }
@@ -212,7 +238,8 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(
     const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off, const __nv_bfloat16* __restrict__ x, int x_ct, int x_off,
     __nv_bfloat16* __restrict__ dx, int dx_ct, int dx_off, int groups, int64_t total, float inv_count,
     const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
-    const float* __restrict__ invstd, int relu, int training, const float* __restrict__ red, int c) {
+    const float* __restrict__ invstd, int relu, int training, const float* __restrict__ red, int c,
+    const __nv_bfloat16* __restrict__ mask, int m_ct, int m_off) {
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int g = static_cast<int>(i % groups);
@@ -228,14 +255,41 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(
             load8f(red + g * 8, r0);
             load8f(red + c + g * 8, r1);
         }
+        float m[8];
+        if (mask) {
+            unpack8(ldg128(mask + p * m_ct + m_off + g * 8), m);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) m[j] = fmaf(f[j], sc[j], sh[j]);
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const float dz = (relu && fmaf(f[j], sc[j], sh[j]) <= 0.f) ? 0.f : d[j];
+            const float dz = (relu && m[j] <= 0.f) ? 0.f : d[j];
             float v = dz;
             if (training) v = dz - r0[j] * inv_count - (f[j] - mu[j]) * is[j] * r1[j] * inv_count;
             f[j] = v * sc[j];
         }
         st128(dx + p * dx_ct + dx_off + g * 8, pack8(f));
+    }
+}
+
+// dx += dy * (y > 0): the identity branch of a residual block joins the conv branch's data gradient
+__global__ void __launch_bounds__(256) relu_bwd_add_kernel(__nv_bfloat16* __restrict__ dx, int dx_ct, int dx_off,
+                                                            const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off,
+                                                            const __nv_bfloat16* __restrict__ y, int y_ct, int y_off,
+                                                            int groups, int64_t total) {
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int g = static_cast<int>(i % groups);
+        const int64_t p = i / groups;
+        float a[8], d[8], m[8];
+        __nv_bfloat16* dst = dx + p * dx_ct + dx_off + g * 8;
+        unpack8(*reinterpret_cast<const uint4*>(dst), a);
+        unpack8(ldg128(dy + p * dy_ct + dy_off + g * 8), d);
+        unpack8(ldg128(y + p * y_ct + y_off + g * 8), m);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] += m[j] > 0.f ? d[j] : 0.f;
+        st128(dst, pack8(a));
     }
 }
 
@@ -309,17 +363,44 @@ int b200seg_bn_eval_affine(int c, const float* gamma, const float* beta, const f
     return 0;
 }
 
-int b200seg_bn_apply(const void* x, int x_c_total, int x_c_offset, void* y, int y_c_total, int y_c_offset, int c,
-                     int64_t pixels, const float* scale, const float* shift, int relu, b200seg_stream_t stream) {
+int b200seg_bn_apply_add(const void* x, int x_c_total, int x_c_offset, void* y, int y_c_total, int y_c_offset, int c,
+                         int64_t pixels, const float* scale, const float* shift, int relu, const void* res,
+                         int res_c_total, int res_c_offset, const float* res_scale, const float* res_shift,
+                         b200seg_stream_t stream) {
     using namespace b200seg;
     clear_error();
     if (check_slice("bn_apply(x)", x, x_c_total, x_c_offset, c)) return 1;
     if (check_slice("bn_apply(y)", y, y_c_total, y_c_offset, c)) return 1;
+    if (res && check_slice("bn_apply(res)", res, res_c_total, res_c_offset, c)) return 1;
     B200SEG_CHECK(scale && shift && pixels > 0, "bn_apply: bad arguments");
+    B200SEG_CHECK((res_scale == nullptr) == (res_shift == nullptr), "bn_apply: residual scale and shift go together");
     const int64_t total = pixels * (c / 8);
     bn_apply_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
         static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset,
-        c / 8, total, scale, shift, relu);
+        c / 8, total, scale, shift, relu, static_cast<const __nv_bfloat16*>(res), res_c_total, res_c_offset, res_scale,
+        res_shift);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_bn_apply(const void* x, int x_c_total, int x_c_offset, void* y, int y_c_total, int y_c_offset, int c,
+                     int64_t pixels, const float* scale, const float* shift, int relu, b200seg_stream_t stream) {
+    return b200seg_bn_apply_add(x, x_c_total, x_c_offset, y, y_c_total, y_c_offset, c, pixels, scale, shift, relu, nullptr,
+                                0, 0, nullptr, nullptr, stream);
+}
+
+int b200seg_relu_bwd_add(void* dx, int dx_c_total, int dx_c_offset, const void* dy, int dy_c_total, int dy_c_offset,
+                         const void* y, int y_c_total, int y_c_offset, int c, int64_t pixels, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    if (check_slice("relu_bwd_add(dx)", dx, dx_c_total, dx_c_offset, c)) return 1;
+    if (check_slice("relu_bwd_add(dy)", dy, dy_c_total, dy_c_offset, c)) return 1;
+    if (check_slice("relu_bwd_add(y)", y, y_c_total, y_c_offset, c)) return 1;
+    B200SEG_CHECK(pixels > 0, "relu_bwd_add: bad arguments");
+    const int64_t total = pixels * (c / 8);
+    relu_bwd_add_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, static_cast<const __nv_bfloat16*>(dy), dy_c_total,
+        dy_c_offset, static_cast<const __nv_bfloat16*>(y), y_c_total, y_c_offset, c / 8, total);
     B200SEG_LAUNCH_CHECK();
     return 0;
 }
@@ -327,17 +408,27 @@ int b200seg_bn_apply(const void* x, int x_c_total, int x_c_offset, void* y, int 
 int b200seg_bn_bwd_reduce(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total, int x_c_offset,
                           int c, int64_t pixels, const float* scale, const float* shift, const float* save_mean,
                           const float* save_invstd, int relu, float* red, b200seg_stream_t stream) {
+    return b200seg_bn_bwd_reduce_masked(dy, dy_c_total, dy_c_offset, x, x_c_total, x_c_offset, c, pixels, scale, shift,
+                                        save_mean, save_invstd, relu, red, nullptr, 0, 0, stream);
+}
+
+int b200seg_bn_bwd_reduce_masked(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total,
+                                 int x_c_offset, int c, int64_t pixels, const float* scale, const float* shift,
+                                 const float* save_mean, const float* save_invstd, int relu, float* red, const void* mask,
+                                 int mask_c_total, int mask_c_offset, b200seg_stream_t stream) {
     using namespace b200seg;
     clear_error();
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (check_slice("bn_bwd_reduce(dy)", dy, dy_c_total, dy_c_offset, c)) return 1;
     if (check_slice("bn_bwd_reduce(x)", x, x_c_total, x_c_offset, c)) return 1;
+    if (mask && check_slice("bn_bwd_reduce(mask)", mask, mask_c_total, mask_c_offset, c)) return 1;
     B200SEG_CHECK(scale && shift && save_mean && save_invstd && red && pixels > 0, "bn_bwd_reduce: bad arguments");
     B200SEG_CUDA(cudaMemsetAsync(red, 0, sizeof(float) * 2 * c, st));
     const ColGeom g = col_geom(c, pixels);
     bn_bwd_reduce_kernel<<<dim3(g.gx, g.gy), kRedThreads, 0, st>>>(
         static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, static_cast<const __nv_bfloat16*>(x), x_c_total,
-        x_c_offset, c, pixels, g.pixels_per_block, g.gpb, g.rows, scale, shift, save_mean, save_invstd, relu, red);
+        x_c_offset, c, pixels, g.pixels_per_block, g.gpb, g.rows, scale, shift, save_mean, save_invstd, relu, red,
+        static_cast<const __nv_bfloat16*>(mask), mask_c_total, mask_c_offset);
     B200SEG_LAUNCH_CHECK();
     return 0;
 }
@@ -347,18 +438,31 @@ int b200seg_bn_bwd_apply(const void* dy, int dy_c_total, int dy_c_offset, const 
                          const float* shift, const float* save_mean, const float* save_invstd, int relu, int training,
                          const float* red, float* dgamma, float* dbeta, int accumulate_param_grads,
                          b200seg_stream_t stream) {
+    return b200seg_bn_bwd_apply_masked(dy, dy_c_total, dy_c_offset, x, x_c_total, x_c_offset, dx, dx_c_total, dx_c_offset, c,
+                                       pixels, scale, shift, save_mean, save_invstd, relu, training, red, dgamma, dbeta,
+                                       accumulate_param_grads, nullptr, 0, 0, stream);
+}
+
+int b200seg_bn_bwd_apply_masked(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total,
+                                int x_c_offset, void* dx, int dx_c_total, int dx_c_offset, int c, int64_t pixels,
+                                const float* scale, const float* shift, const float* save_mean, const float* save_invstd,
+                                int relu, int training, const float* red, float* dgamma, float* dbeta,
+                                int accumulate_param_grads, const void* mask, int mask_c_total, int mask_c_offset,
+                                b200seg_stream_t stream) {
     using namespace b200seg;
     clear_error();
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (check_slice("bn_bwd_apply(dy)", dy, dy_c_total, dy_c_offset, c)) return 1;
     if (check_slice("bn_bwd_apply(x)", x, x_c_total, x_c_offset, c)) return 1;
     if (check_slice("bn_bwd_apply(dx)", dx, dx_c_total, dx_c_offset, c)) return 1;
+    if (mask && check_slice("bn_bwd_apply(mask)", mask, mask_c_total, mask_c_offset, c)) return 1;
     B200SEG_CHECK(scale && shift && save_mean && save_invstd && red && pixels > 0, "bn_bwd_apply: bad arguments");
     const int64_t total = pixels * (c / 8);
     bn_bwd_apply_kernel<<<elementwise_grid(total), 256, 0, st>>>(
         static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, static_cast<const __nv_bfloat16*>(x), x_c_total,
         x_c_offset, static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, c / 8, total,
-        static_cast<float>(1.0 / static_cast<double>(pixels)), scale, shift, save_mean, save_invstd, relu, training, red, c);
+        static_cast<float>(1.0 / static_cast<double>(pixels)), scale, shift, save_mean, save_invstd, relu, training, red, c,
+        static_cast<const __nv_bfloat16*>(mask), mask_c_total, mask_c_offset);
     B200SEG_LAUNCH_CHECK();
     if (dgamma || dbeta) {
         bn_param_grad_kernel<<<ceil_div(c, 128), 128, 0, st>>>(red, c, dgamma, dbeta, accumulate_param_grads);

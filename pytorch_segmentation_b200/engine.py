@@ -271,28 +271,64 @@ def bn_eval_affine(c, gamma, beta, running_mean, running_var, eps):
     return vec
 
 
-def bn_apply(x, y, vec, relu):
+def bn_apply(x, y, vec, relu, res=None, res_vec=None):
+    """y = relu?(x*scale + shift [+ res | + res*res_scale + res_shift])"""
     c = x.c
     p = vec.data_ptr()
-    _lib.check(_lib.load().b200seg_bn_apply(x.ptr, x.ct, x.c_off, y.ptr, y.ct, y.c_off, c, x.pixels, p, p + 4 * c,
-                                            int(relu), _stream()), 'bn_apply')
+    if res is None:
+        _lib.check(_lib.load().b200seg_bn_apply(x.ptr, x.ct, x.c_off, y.ptr, y.ct, y.c_off, c, x.pixels, p, p + 4 * c,
+                                                int(relu), _stream()), 'bn_apply')
+    else:
+        rp = res_vec.data_ptr() if res_vec is not None else None
+        _lib.check(_lib.load().b200seg_bn_apply_add(
+            x.ptr, x.ct, x.c_off, y.ptr, y.ct, y.c_off, c, x.pixels, p, p + 4 * c, int(relu), res.ptr, res.ct, res.c_off,
+            rp, rp + 4 * c if rp is not None else None, _stream()), 'bn_apply_add')
     _lib.count_launch()
 
 
-def bn_backward(dy, x, dx, vec, relu, training):
-    """dy: grad of the BN(+ReLU) output, x: saved raw conv output, dx: receives the grad of x.
-    Returns (dgamma, dbeta)."""
+def bn_backward(dy, x, dx, vec, relu, training, mask=None):
+    """dy: grad of the BN(+ReLU) output, x: saved raw conv output, dx: receives the grad of x.  ``mask``: stored
+    block output whose sign is the ReLU mask (residual blocks); None recomputes it from x.  Returns (dgamma, dbeta)."""
     c = x.c
     p = vec.data_ptr()
     red = torch.empty((2 * c,), dtype=torch.float32, device=x.t.device)
     lib = _lib.load()
-    _lib.check(lib.b200seg_bn_bwd_reduce(dy.ptr, dy.ct, dy.c_off, x.ptr, x.ct, x.c_off, c, x.pixels, p, p + 4 * c,
-                                         p + 8 * c, p + 12 * c, int(relu), red.data_ptr(), _stream()), 'bn_bwd_reduce')
-    _lib.check(lib.b200seg_bn_bwd_apply(dy.ptr, dy.ct, dy.c_off, x.ptr, x.ct, x.c_off, dx.ptr, dx.ct, dx.c_off, c,
-                                        x.pixels, p, p + 4 * c, p + 8 * c, p + 12 * c, int(relu), int(training),
-                                        red.data_ptr(), None, None, 0, _stream()), 'bn_bwd_apply')
-    _lib.count_launch(2)
+    m = (mask.ptr, mask.ct, mask.c_off) if mask is not None else (None, 0, 0)
+    _lib.check(lib.b200seg_bn_bwd_reduce_masked(dy.ptr, dy.ct, dy.c_off, x.ptr, x.ct, x.c_off, c, x.pixels, p, p + 4 * c,
+                                                p + 8 * c, p + 12 * c, int(relu), red.data_ptr(), m[0], m[1], m[2],
+                                                _stream()), 'bn_bwd_reduce')
+    _lib.check(lib.b200seg_bn_bwd_apply_masked(dy.ptr, dy.ct, dy.c_off, x.ptr, x.ct, x.c_off, dx.ptr, dx.ct, dx.c_off, c,
+                                               x.pixels, p, p + 4 * c, p + 8 * c, p + 12 * c, int(relu), int(training),
+                                               red.data_ptr(), None, None, 0, m[0], m[1], m[2], _stream()),
+               'bn_bwd_apply')
+    _lib.count_launch(3)      # memset + reduce + apply
     return red[c:], red[:c]
+
+
+def relu_bwd_add(dx, dy, y):
+    """dx += dy * (y > 0)"""
+    _lib.check(_lib.load().b200seg_relu_bwd_add(dx.ptr, dx.ct, dx.c_off, dy.ptr, dy.ct, dy.c_off, y.ptr, y.ct, y.c_off,
+                                                dx.c, dx.pixels, _stream()), 'relu_bwd_add')
+    _lib.count_launch()
+
+
+def maxpool_fwd(x):
+    """3x3 stride-2 pad-1 max pool -> (y: Act, idx: uint8 tensor of window positions)"""
+    oh, ow = (x.h + 1) // 2, (x.w + 1) // 2
+    y = Act.empty(x.n, oh, ow, x.c, x.t.device)
+    idx = torch.empty((x.n, oh, ow, x.c), dtype=torch.uint8, device=x.t.device)
+    _lib.check(_lib.load().b200seg_maxpool3x3s2_fwd(x.ptr, x.ct, x.c_off, x.n, x.h, x.w, y.ptr, y.ct, y.c_off,
+                                                    idx.data_ptr(), x.c, _stream()), 'maxpool_fwd')
+    _lib.count_launch()
+    return y, idx
+
+
+def maxpool_bwd(dy, idx, h, w):
+    dx = Act.empty(dy.n, h, w, dy.c, dy.t.device)
+    _lib.check(_lib.load().b200seg_maxpool3x3s2_bwd(dy.ptr, dy.ct, dy.c_off, idx.data_ptr(), dy.n, h, w, dx.ptr, dx.ct,
+                                                    dx.c_off, dy.c, _stream()), 'maxpool_bwd')
+    _lib.count_launch()
+    return dx
 
 
 # ------------------------------------------------------------------------------------------------

@@ -1,0 +1,257 @@
+"""ResNet-50 (output stride 16) feature extractor on the tcgen05 path — SURVEY.md §8f-1.
+
+The reference gets its backbone from the external ``pytorch_modules.backbones.resnet50(pretrained=True,
+replace_stride_with_dilation=[False, False, True])`` (models/deeplabv3plus.py:17-19) and indexes the list of five
+feature maps it returns (models/deeplabv3plus.py:29-32).  Parameters live in an ordinary torchvision ResNet-50
+module tree (same state-dict keys as the oracle shim); the arithmetic below is libb200seg:
+
+* every 1x1 / 3x3 convolution (stride 1, stride 2, dilation 2) is the tcgen05 implicit GEMM with the train-mode
+  BatchNorm statistics taken in its epilogue; BN-apply + ReLU (+ residual add, + the downsample branch's BN) is one
+  bandwidth kernel; backward is the two-pass BN backward, the tcgen05 wgrad and dgrad (the block-input gradient of a
+  downsampling bottleneck — conv1's and the downsample conv's data gradients — is one accumulation in TMEM);
+* the 3x3 max pool is a gather kernel pair;
+* the 7x7 stride-2 stem convolution over 3 input channels is the ONE convolution left on the library (cuDNN through
+  ``F.conv2d``): 3 channels cannot feed a 64-wide K block.  DESIGN.md §7 lists it as not yet native.
+
+Forward and backward are explicit kernel sequences inside one autograd node (no per-op autograd graph).
+"""
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+import torchvision
+
+from . import engine as E
+
+
+class _Unit:
+    """conv (no bias) + BatchNorm2d bound to the modules that own the parameters."""
+
+    def __init__(self, conv, bn):
+        k = conv.kernel_size[0]
+        if conv.kernel_size not in ((1, 1), (3, 3)) or conv.groups != 1 or conv.bias is not None:
+            raise NotImplementedError('backbone conv %r is outside the tcgen05 path' % (conv,))
+        if conv.stride not in ((1, 1), (2, 2)) or conv.padding[0] != (k // 2) * conv.dilation[0]:
+            raise NotImplementedError('backbone conv %r: stride/padding outside the tcgen05 path' % (conv,))
+        self.conv, self.bn = conv, bn
+        self.k, self.stride, self.dil = k, conv.stride[0], conv.dilation[0]
+        self.cout = conv.out_channels
+        self.packed = E.PackedWeight()
+
+    def params(self):
+        return [self.conv.weight, self.bn.weight, self.bn.bias]
+
+    def forward_raw(self, x, training, stats, need_dgrad=True):
+        """-> (raw conv output Act, vec[4, c] = scale/shift/mean/invstd)"""
+        bn = self.bn
+        pw = self.packed.update(self.conv.weight, need_dgrad=need_dgrad)
+        raw = E.Act.empty(x.n, x.h // self.stride, x.w // self.stride, self.cout, x.t.device)
+        if training:
+            E.conv_fprop([(x, pw, self.dil, self.stride)], raw, stats=stats)
+            track = bn.track_running_stats and bn.running_mean is not None
+            vec = E.bn_finalize(stats, self.cout, raw.pixels, bn.weight, bn.bias, bn.eps, bn.momentum,
+                                bn.running_mean if track else None, bn.running_var if track else None)
+        else:
+            E.conv_fprop([(x, pw, self.dil, self.stride)], raw)
+            vec = E.bn_eval_affine(self.cout, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
+        return raw, vec
+
+    def wgrad(self, draw, x):
+        return E.conv_wgrad(draw, x, self.cout, self.k, self.k, self.dil, stride=self.stride)
+
+    def dgrad_src(self, draw):
+        return (draw, self.packed, self.dil, self.stride)
+
+
+class _Block:
+    """torchvision Bottleneck: conv1 1x1 -> conv2 3x3 (stride / dilation) -> conv3 1x1, + identity or downsample."""
+
+    def __init__(self, blk):
+        self.u1, self.u2, self.u3 = _Unit(blk.conv1, blk.bn1), _Unit(blk.conv2, blk.bn2), _Unit(blk.conv3, blk.bn3)
+        self.ud = _Unit(blk.downsample[0], blk.downsample[1]) if blk.downsample is not None else None
+
+    def units(self):
+        return [self.u1, self.u2, self.u3] + ([self.ud] if self.ud is not None else [])
+
+    def forward(self, x, training, stats_of):
+        dev = x.t.device
+        raw1, v1 = self.u1.forward_raw(x, training, stats_of(self.u1))
+        a1 = E.Act.empty(raw1.n, raw1.h, raw1.w, raw1.c, dev)
+        E.bn_apply(raw1, a1, v1, True)
+        raw2, v2 = self.u2.forward_raw(a1, training, stats_of(self.u2))
+        a2 = E.Act.empty(raw2.n, raw2.h, raw2.w, raw2.c, dev)
+        E.bn_apply(raw2, a2, v2, True)
+        raw3, v3 = self.u3.forward_raw(a2, training, stats_of(self.u3))
+        out = E.Act.empty(raw3.n, raw3.h, raw3.w, raw3.c, dev)
+        if self.ud is not None:
+            rawd, vd = self.ud.forward_raw(x, training, stats_of(self.ud))
+            E.bn_apply(raw3, out, v3, True, res=rawd, res_vec=vd)
+        else:
+            rawd = vd = None
+            E.bn_apply(raw3, out, v3, True, res=x)
+        return out, (x, raw1, v1, a1, raw2, v2, a2, raw3, v3, rawd, vd, out)
+
+    def backward(self, rec, dout, training, grads, need_dx=True):
+        """dout: Act grad of the block output.  Fills grads[param] and returns the Act grad of the block input."""
+        x, raw1, v1, a1, raw2, v2, a2, raw3, v3, rawd, vd, out = rec
+        dev = x.t.device
+
+        def unit_bwd(u, dy, raw, vec, xin, mask=None):
+            draw = E.Act.empty(raw.n, raw.h, raw.w, raw.c, dev)
+            dgamma, dbeta = E.bn_backward(dy, raw, draw, vec, True, training, mask=mask)
+            grads[u.conv.weight] = u.wgrad(draw, xin)
+            grads[u.bn.weight], grads[u.bn.bias] = dgamma, dbeta
+            return draw
+
+        draw3 = unit_bwd(self.u3, dout, raw3, v3, a2, mask=out)
+        da2 = E.Act.empty(a2.n, a2.h, a2.w, a2.c, dev)
+        E.conv_dgrad([self.u3.dgrad_src(draw3)], da2)
+        draw2 = unit_bwd(self.u2, da2, raw2, v2, a1)
+        da1 = E.Act.empty(a1.n, a1.h, a1.w, a1.c, dev)
+        E.conv_dgrad([self.u2.dgrad_src(draw2)], da1)
+        draw1 = unit_bwd(self.u1, da1, raw1, v1, x)
+        drawd = unit_bwd(self.ud, dout, rawd, vd, x, mask=out) if self.ud is not None else None
+        if not need_dx:
+            return None
+        dx = E.Act.empty(x.n, x.h, x.w, x.c, dev)
+        if self.ud is not None:
+            E.conv_dgrad([self.u1.dgrad_src(draw1), self.ud.dgrad_src(drawd)], dx)
+        else:
+            E.conv_dgrad([self.u1.dgrad_src(draw1)], dx)
+            E.relu_bwd_add(dx, dout, out)
+        return dx
+
+
+class ResNet50Features(nn.Module):
+    """[relu(bn1(conv1 x)), layer1, layer2, layer3, layer4] — strides 2, 4, 8, 16, 16 with layer4 dilated, the list
+    the reference indexes at models/deeplabv3plus.py:29-32.  ``forward`` returns NCHW-shaped bf16 tensors that are
+    views of NHWC buffers (what the heads consume without a copy)."""
+
+    def __init__(self, replace_stride_with_dilation=None):
+        super().__init__()
+        net = torchvision.models.resnet50(weights=None, replace_stride_with_dilation=replace_stride_with_dilation)
+        self.conv1, self.bn1, self.relu, self.maxpool = net.conv1, net.bn1, net.relu, net.maxpool
+        self.layer1, self.layer2, self.layer3, self.layer4 = net.layer1, net.layer2, net.layer3, net.layer4
+        self._plan = None
+
+    def _build_plan(self):
+        layers = [[_Block(b) for b in layer] for layer in (self.layer1, self.layer2, self.layer3, self.layer4)]
+        units = [u for layer in layers for blk in layer for u in blk.units()]
+        offs, off = {}, 0
+        for u in units:
+            offs[id(u)] = off
+            off += 2 * u.cout
+        self._plan = (layers, units, offs, off)
+        return self._plan
+
+    def forward(self, x):
+        params = list(self.parameters())
+        feats = _ResNetFn.apply(self, x, *params)
+        return list(feats)
+
+    # ---- explicit forward / backward -------------------------------------------------------------------------
+    def run_forward(self, x, training, save):
+        E._require_cuda(x, 'backbone input')
+        layers, units, offs, total = self._plan or self._build_plan()
+        dev = x.device
+        # stem: 7x7 stride-2 conv over 3 channels on the library (see module docstring), then our BN/ReLU/max-pool
+        xb = x.detach().to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        wb = self.conv1.weight.detach().to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        raw0_t = F.conv2d(xb, wb, None, 2, 3).contiguous(memory_format=torch.channels_last)
+        raw0 = E.Act(raw0_t.permute(0, 2, 3, 1))
+        bn = self.bn1
+        if training:
+            track = bn.track_running_stats and bn.running_mean is not None
+            v0 = E.bn_finalize(E.bn_stats(raw0), raw0.c, raw0.pixels, bn.weight, bn.bias, bn.eps, bn.momentum,
+                               bn.running_mean if track else None, bn.running_var if track else None)
+        else:
+            v0 = E.bn_eval_affine(raw0.c, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
+        a0 = E.Act.empty(raw0.n, raw0.h, raw0.w, raw0.c, dev)
+        E.bn_apply(raw0, a0, v0, True)
+        p0, idx = E.maxpool_fwd(a0)
+
+        stats_all = torch.zeros((total,), dtype=torch.float32, device=dev) if training else None
+
+        def stats_of(u):
+            if stats_all is None:
+                return None
+            o = offs[id(u)]
+            return stats_all[o:o + 2 * u.cout]
+
+        feats, recs = [a0], []
+        cur = p0
+        for layer in layers:
+            lrec = []
+            for blk in layer:
+                cur, rec = blk.forward(cur, training, stats_of)
+                lrec.append(rec if save else None)
+            recs.append(lrec)
+            feats.append(cur)
+        if training:
+            nbt = [m.num_batches_tracked for m in self.modules()
+                   if isinstance(m, nn.BatchNorm2d) and m.track_running_stats and m.num_batches_tracked is not None]
+            if nbt:
+                torch._foreach_add_(nbt, 1)
+        saved = (xb, wb, raw0, v0, a0, idx, recs, training) if save else None
+        return feats, saved
+
+    def run_backward(self, saved, gfeats):
+        """gfeats: gradients of the five feature maps (None where unused).  -> {parameter: gradient}"""
+        xb, wb, raw0, v0, a0, idx, recs, training = saved
+        layers = self._plan[0]
+        grads = {}
+        d = None
+        for li in (3, 2, 1, 0):
+            g = gfeats[li + 1]
+            if g is not None:
+                ga = E.as_act(g, 'backbone feature gradient')
+                if d is None:
+                    d = ga
+                else:
+                    d.nchw().add_(ga.nchw())
+            if d is None:
+                continue
+            for bi in range(len(layers[li]) - 1, -1, -1):
+                d = layers[li][bi].backward(recs[li][bi], d, training, grads)
+        if d is not None:
+            da0 = E.maxpool_bwd(d, idx, a0.h, a0.w)
+            if gfeats[0] is not None:
+                da0.nchw().add_(E.as_act(gfeats[0], 'backbone feature gradient').nchw())
+        elif gfeats[0] is not None:
+            da0 = E.as_act(gfeats[0], 'backbone feature gradient')
+        else:
+            return grads
+        draw0 = E.Act.empty(raw0.n, raw0.h, raw0.w, raw0.c, raw0.t.device)
+        dgamma, dbeta = E.bn_backward(da0, raw0, draw0, v0, True, training)
+        gw = torch.ops.aten.convolution_backward(draw0.nchw(), xb, wb, None, [2, 2], [3, 3], [1, 1], False, [0, 0], 1,
+                                                 [False, True, False])[1]
+        grads[self.conv1.weight] = gw.float().contiguous()
+        grads[self.bn1.weight], grads[self.bn1.bias] = dgamma, dbeta
+        return grads
+
+
+class _ResNetFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, mod, x, *params):
+        save = any(ctx.needs_input_grad[2:])
+        feats, saved = mod.run_forward(x, mod.training, save)
+        ctx.mod, ctx.saved, ctx.params = mod, saved, params
+        outs = tuple(f.nchw() for f in feats)
+        return outs
+
+    @staticmethod
+    def backward(ctx, *gfeats):
+        grads = ctx.mod.run_backward(ctx.saved, list(gfeats))
+        ctx.saved = None
+        out = []
+        for p, need in zip(ctx.params, ctx.needs_input_grad[2:]):
+            g = grads.get(p) if need else None
+            if g is not None and g.shape != p.shape:
+                g = g.reshape(p.shape)
+            out.append(g)
+        # the image itself gets no gradient (the reference never asks for one: inputs come from the data loader)
+        return (None, None) + tuple(out)
+
+
+def resnet50(pretrained=False, replace_stride_with_dilation=None, **kw):
+    """Drop-in for ``pytorch_modules.backbones.resnet50`` (``pretrained`` ignored: no network, random init)."""
+    return ResNet50Features(replace_stride_with_dilation)
