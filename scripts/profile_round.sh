@@ -12,6 +12,6 @@ cat gpurun_out/bench_${R}_short.log
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 12000 --csv \
     --log-file gpurun_out/launches_${R}.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_list_${R}.log 2>&1
 echo "launch list rc=$?"; wc -l gpurun_out/launches_${R}.csv
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'igemm_kernel|wgrad_kernel' --launch-skip 66 -c 24 \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'igemm_kernel|wgrad_kernel' --launch-skip 0 -c 30 \
     -o gpurun_out/convs_${R} -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_full_${R}.log 2>&1
 echo "full capture rc=$?"; ls -la gpurun_out/
