@@ -19,7 +19,7 @@ struct ColGeom {
     int gx;
 };
 
-ColGeom col_geom(int c, int64_t pixels) {
+ColGeom col_geom(int c, int64_t pixels, int ctas_per_sm = 8) {
     ColGeom g;
     g.groups = c / 8;
     g.gpb = g.groups < kRedThreads ? g.groups : kRedThreads;
@@ -27,7 +27,7 @@ ColGeom col_geom(int c, int64_t pixels) {
     g.gy = ceil_div(g.groups, g.gpb);
     int sms = sm_count();
     if (sms <= 0) sms = 148;
-    int64_t want = static_cast<int64_t>(sms) * 8 / g.gy;
+    int64_t want = static_cast<int64_t>(sms) * ctas_per_sm / g.gy;
     if (want < 1) want = 1;
     int64_t ppb = ceil_div64(pixels, want);
     const int64_t min_ppb = static_cast<int64_t>(g.rows) * 4;
@@ -76,10 +76,14 @@ __global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(const __nv_bfloat
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[0][j] = acc[1][j] = 0.f;
     if (row < rows && group < groups) {
-        const int64_t p0 = blockIdx.x * ppb;
-        const int64_t p1 = min(p0 + ppb, pixels);
+        // strided sweep: all CTAs move through the tensor together (measured faster than one contiguous chunk per CTA)
+        const int64_t p0 = static_cast<int64_t>(blockIdx.x) * rows;
+        const int64_t p1 = pixels;
+        const int64_t pstep = static_cast<int64_t>(gridDim.x) * rows;
+        (void)ppb;
         const __nv_bfloat16* base = x + c_off + group * 8;
-        for (int64_t p = p0 + row; p < p1; p += rows) {
+#pragma unroll 4
+        for (int64_t p = p0 + row; p < p1; p += pstep) {
             float f[8];
             unpack8(ldg128(base + p * c_total), f);
 #pragma unroll
@@ -103,10 +107,13 @@ __global__ void __launch_bounds__(kRedThreads) channel_sum_kernel(const __nv_bfl
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[0][j] = 0.f;
     if (row < rows && group < groups) {
-        const int64_t p0 = blockIdx.x * ppb;
-        const int64_t p1 = min(p0 + ppb, pixels);
+        // strided sweep: all CTAs move through the tensor together (measured faster than one contiguous chunk per CTA)
+        const int64_t p0 = static_cast<int64_t>(blockIdx.x) * rows;
+        const int64_t p1 = pixels;
+        const int64_t pstep = static_cast<int64_t>(gridDim.x) * rows;
+        (void)ppb;
         const __nv_bfloat16* base = x + c_off + group * 8;
-        for (int64_t p = p0 + row; p < p1; p += rows) {
+        for (int64_t p = p0 + row; p < p1; p += pstep) {
             float f[8];
             unpack8(ldg128(base + p * c_total), f);
 #pragma unroll
@@ -150,32 +157,45 @@ __global__ void bn_eval_affine_kernel(int c, const float* __restrict__ gamma, co
     if (save_invstd) save_invstd[i] = invstd;
 }
 
-__global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __restrict__ x, int x_ct, int x_off,
-                                                        __nv_bfloat16* __restrict__ y, int y_ct, int y_off, int groups,
-                                                        int64_t total, const float* __restrict__ scale,
-                                                        const float* __restrict__ shift, int relu,
-                                                        const __nv_bfloat16* __restrict__ res, int r_ct, int r_off,
-                                                        const float* __restrict__ res_scale,
-                                                        const float* __restrict__ res_shift) {
-    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
-         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int g = static_cast<int>(i % groups);
-        const int64_t p = i / groups;
-        float f[8], sc[8], sh[8];
-        unpack8(ldg128(x + p * x_ct + x_off + g * 8), f);
-        load8f(scale + g * 8, sc);
-        load8f(shift + g * 8, sh);
+// Elementwise kernels over a [pixels][c] slice use the column geometry too: a thread owns one 8-channel group for
+// its whole pixel range, so the per-channel parameters live in registers (reloading them per element made these
+// kernels L1-bound at ~65 % of HBM bandwidth).
+__global__ void __launch_bounds__(kRedThreads) bn_apply_kernel(
+    const __nv_bfloat16* __restrict__ x, int x_ct, int x_off, __nv_bfloat16* __restrict__ y, int y_ct, int y_off, int groups,
+    int64_t pixels, int64_t ppb, int gpb, int rows, const float* __restrict__ scale, const float* __restrict__ shift,
+    int relu, const __nv_bfloat16* __restrict__ res, int r_ct, int r_off, const float* __restrict__ res_scale,
+    const float* __restrict__ res_shift) {
+    const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
+    const int group = blockIdx.y * gpb + g_local;
+    if (row >= rows || group >= groups) return;
+    float sc[8], sh[8], rsc[8], rsh[8];
+    load8f(scale + group * 8, sc);
+    load8f(shift + group * 8, sh);
+    const bool res_affine = res != nullptr && res_scale != nullptr;
+    if (res_affine) {
+        load8f(res_scale + group * 8, rsc);
+        load8f(res_shift + group * 8, rsh);
+    }
+    const int64_t p0 = static_cast<int64_t>(blockIdx.x) * rows;
+    const int64_t p1 = pixels;
+    const int64_t pstep = static_cast<int64_t>(gridDim.x) * rows;
+    (void)ppb;
+    const __nv_bfloat16* xb = x + x_off + group * 8;
+    const __nv_bfloat16* rb = res ? res + r_off + group * 8 : nullptr;
+    __nv_bfloat16* yb = y + y_off + group * 8;
+#pragma unroll 2
+    for (int64_t p = p0 + row; p < p1; p += pstep) {
+        float f[8];
+        unpack8(ldcs128(xb + p * x_ct), f);
 #pragma unroll
         for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]);
-        if (res) {
+        if (rb) {
             // residual branch: the identity, or the downsample conv's raw output with its own BN affine
             float r[8];
-            unpack8(ldg128(res + p * r_ct + r_off + g * 8), r);
-            if (res_scale) {
-                load8f(res_scale + g * 8, sc);
-                load8f(res_shift + g * 8, sh);
+            unpack8(ldcs128(rb + p * r_ct), r);
+            if (res_affine) {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) r[j] = fmaf(r[j], sc[j], sh[j]);
+                for (int j = 0; j < 8; ++j) r[j] = fmaf(r[j], rsc[j], rsh[j]);
             }
 #pragma unroll
             for (int j = 0; j < 8; ++j) f[j] += r[j];
@@ -184,7 +204,7 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
 #pragma unroll
             for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
         }
-        st128(y + p * y_ct + y_off + g * 8, pack8(f));
+        st128(yb + p * y_ct, pack8(f));
     }
 }
 
@@ -206,12 +226,16 @@ __global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(
         load8f(shift + group * 8, sh);
         load8f(mean + group * 8, mu);
         load8f(invstd + group * 8, is);
-        const int64_t p0 = blockIdx.x * ppb;
-        const int64_t p1 = min(p0 + ppb, pixels);
+        // strided sweep: all CTAs move through the tensor together (measured faster than one contiguous chunk per CTA)
+        const int64_t p0 = static_cast<int64_t>(blockIdx.x) * rows;
+        const int64_t p1 = pixels;
+        const int64_t pstep = static_cast<int64_t>(gridDim.x) * rows;
+        (void)ppb;
         const __nv_bfloat16* xb = x + x_off + group * 8;
         const __nv_bfloat16* db = dy + dy_off + group * 8;
         const __nv_bfloat16* mb = mask ? mask + m_off + group * 8 : nullptr;
-        for (int64_t p = p0 + row; p < p1; p += rows) {
+#pragma unroll 2
+        for (int64_t p = p0 + row; p < p1; p += pstep) {
             float f[8], d[8], m[8];
             unpack8(ldg128(xb + p * x_ct), f);
             unpack8(ldg128(db + p * dy_ct), d);
@@ -226,38 +250,61 @@ __global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(
             for (int j = 0; j < 8; ++j) {
                 const float dz = (relu && m[j] <= 0.f) ? 0.f : d[j];
                 acc[0][j] += dz;
-                acc[1][j] = fmaf(dz, (f[j] - mu[j]) * is[j], acc[1][j]);
+                acc[1][j] = fmaf(dz, f[j], acc[1][j]);      // sum dz * x; centred and scaled once below
             }
         }
+        // sum dz * xhat = invstd * (sum dz*x - mean * sum dz), per thread (a few hundred terms: no cancellation issue)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[1][j] = is[j] * (acc[1][j] - mu[j] * acc[0][j]);
     }
     block_col_reduce<2>(acc, g_local, row, gpb, rows, group, groups, c, red);
 }
 
 // dx = scale * (dz' - red0/M - xhat * red1/M)   (training)   or   scale * dz'   (eval: statistics are constants)
-__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(
+// rewritten per channel as dx = A * dz' + B * x + C with A = scale, B = -scale*invstd*red1/M (xhat = (x-mean)*invstd),
+// C = -scale*red0/M - B*mean (all per-channel registers).
+__global__ void __launch_bounds__(kRedThreads) bn_bwd_apply_kernel(
     const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off, const __nv_bfloat16* __restrict__ x, int x_ct, int x_off,
-    __nv_bfloat16* __restrict__ dx, int dx_ct, int dx_off, int groups, int64_t total, float inv_count,
-    const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
+    __nv_bfloat16* __restrict__ dx, int dx_ct, int dx_off, int groups, int64_t pixels, int64_t ppb, int gpb, int rows,
+    float inv_count, const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
     const float* __restrict__ invstd, int relu, int training, const float* __restrict__ red, int c,
     const __nv_bfloat16* __restrict__ mask, int m_ct, int m_off) {
-    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
-         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int g = static_cast<int>(i % groups);
-        const int64_t p = i / groups;
-        float f[8], d[8], sc[8], sh[8], mu[8], is[8], r0[8], r1[8];
-        unpack8(ldg128(x + p * x_ct + x_off + g * 8), f);
-        unpack8(ldg128(dy + p * dy_ct + dy_off + g * 8), d);
-        load8f(scale + g * 8, sc);
-        load8f(shift + g * 8, sh);
-        load8f(mean + g * 8, mu);
-        load8f(invstd + g * 8, is);
-        if (training) {
-            load8f(red + g * 8, r0);
-            load8f(red + c + g * 8, r1);
+    const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
+    const int group = blockIdx.y * gpb + g_local;
+    if (row >= rows || group >= groups) return;
+    float sc[8], sh[8], cb[8], cc[8];
+    load8f(scale + group * 8, sc);
+    load8f(shift + group * 8, sh);
+    if (training) {
+        float mu[8], is[8], r0[8], r1[8];
+        load8f(mean + group * 8, mu);
+        load8f(invstd + group * 8, is);
+        load8f(red + group * 8, r0);
+        load8f(red + c + group * 8, r1);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            cb[j] = -sc[j] * is[j] * r1[j] * inv_count;
+            cc[j] = -sc[j] * r0[j] * inv_count - cb[j] * mu[j];
         }
-        float m[8];
-        if (mask) {
-            unpack8(ldg128(mask + p * m_ct + m_off + g * 8), m);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) cb[j] = cc[j] = 0.f;
+    }
+    const int64_t p0 = static_cast<int64_t>(blockIdx.x) * rows;
+    const int64_t p1 = pixels;
+    const int64_t pstep = static_cast<int64_t>(gridDim.x) * rows;
+    (void)ppb;
+    const __nv_bfloat16* xb = x + x_off + group * 8;
+    const __nv_bfloat16* db = dy + dy_off + group * 8;
+    const __nv_bfloat16* mb = mask ? mask + m_off + group * 8 : nullptr;
+    __nv_bfloat16* ob = dx + dx_off + group * 8;
+#pragma unroll 2
+    for (int64_t p = p0 + row; p < p1; p += pstep) {
+        float f[8], d[8], m[8];
+        unpack8(ldcs128(xb + p * x_ct), f);
+        unpack8(ldcs128(db + p * dy_ct), d);
+        if (mb) {
+            unpack8(ldcs128(mb + p * m_ct), m);
         } else {
 #pragma unroll
             for (int j = 0; j < 8; ++j) m[j] = fmaf(f[j], sc[j], sh[j]);
@@ -265,11 +312,9 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const float dz = (relu && m[j] <= 0.f) ? 0.f : d[j];
-            float v = dz;
-            if (training) v = dz - r0[j] * inv_count - (f[j] - mu[j]) * is[j] * r1[j] * inv_count;
-            f[j] = v * sc[j];
+            f[j] = fmaf(sc[j], dz, fmaf(cb[j], f[j], cc[j]));
         }
-        st128(dx + p * dx_ct + dx_off + g * 8, pack8(f));
+        st128(ob + p * dx_ct, pack8(f));
     }
 }
 
@@ -374,11 +419,11 @@ int b200seg_bn_apply_add(const void* x, int x_c_total, int x_c_offset, void* y, 
     if (res && check_slice("bn_apply(res)", res, res_c_total, res_c_offset, c)) return 1;
     B200SEG_CHECK(scale && shift && pixels > 0, "bn_apply: bad arguments");
     B200SEG_CHECK((res_scale == nullptr) == (res_shift == nullptr), "bn_apply: residual scale and shift go together");
-    const int64_t total = pixels * (c / 8);
-    bn_apply_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    const ColGeom g = col_geom(c, pixels, 16);
+    bn_apply_kernel<<<dim3(g.gx, g.gy), kRedThreads, 0, static_cast<cudaStream_t>(stream)>>>(
         static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset,
-        c / 8, total, scale, shift, relu, static_cast<const __nv_bfloat16*>(res), res_c_total, res_c_offset, res_scale,
-        res_shift);
+        c / 8, pixels, g.pixels_per_block, g.gpb, g.rows, scale, shift, relu, static_cast<const __nv_bfloat16*>(res),
+        res_c_total, res_c_offset, res_scale, res_shift);
     B200SEG_LAUNCH_CHECK();
     return 0;
 }
@@ -457,11 +502,12 @@ int b200seg_bn_bwd_apply_masked(const void* dy, int dy_c_total, int dy_c_offset,
     if (check_slice("bn_bwd_apply(dx)", dx, dx_c_total, dx_c_offset, c)) return 1;
     if (mask && check_slice("bn_bwd_apply(mask)", mask, mask_c_total, mask_c_offset, c)) return 1;
     B200SEG_CHECK(scale && shift && save_mean && save_invstd && red && pixels > 0, "bn_bwd_apply: bad arguments");
-    const int64_t total = pixels * (c / 8);
-    bn_bwd_apply_kernel<<<elementwise_grid(total), 256, 0, st>>>(
+    const ColGeom g = col_geom(c, pixels, 16);
+    bn_bwd_apply_kernel<<<dim3(g.gx, g.gy), kRedThreads, 0, st>>>(
         static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, static_cast<const __nv_bfloat16*>(x), x_c_total,
-        x_c_offset, static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, c / 8, total,
-        static_cast<float>(1.0 / static_cast<double>(pixels)), scale, shift, save_mean, save_invstd, relu, training, red, c,
+        x_c_offset, static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, c / 8, pixels, g.pixels_per_block, g.gpb,
+        g.rows, static_cast<float>(1.0 / static_cast<double>(pixels)), scale, shift, save_mean, save_invstd, relu, training,
+        red, c,
         static_cast<const __nv_bfloat16*>(mask), mask_c_total, mask_c_offset);
     B200SEG_LAUNCH_CHECK();
     if (dgamma || dbeta) {

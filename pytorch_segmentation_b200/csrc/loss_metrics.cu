@@ -87,6 +87,63 @@ __global__ void __launch_bounds__(128) logits_up_bwd_kernel(const float* __restr
     }
 }
 
+// Same adjoint, tiled: a block owns 128 consecutive source pixels of one source row and four class planes at a time;
+// thread (x, j) gathers the window of source pixel x in class plane j + 4k.  Lanes walk neighbouring, overlapping
+// windows of the same dy rows (L1 serves the re-reads), the per-pixel x weights are computed once per thread, and
+// the bf16 NHWC result leaves through shared memory as one contiguous run.  Needs an x window of at most kWinMax
+// taps (up-scaling factors up to ~6); the host falls back to the kernel above otherwise.
+constexpr int kWinMax = 16;
+__global__ void __launch_bounds__(512) logits_up_bwd_tiled_kernel(const float* __restrict__ dy, int nc, int oh, int ow,
+                                                                   __nv_bfloat16* __restrict__ dx, int ct, int h, int w,
+                                                                   float sh, float sw, int ac) {
+    extern __shared__ __align__(16) unsigned char tile_raw[];
+    __nv_bfloat16* tile = reinterpret_cast<__nv_bfloat16*>(tile_raw);     // [128][ct]
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int sx = blockIdx.x * 128 + tx, sy = blockIdx.y, n = blockIdx.z;
+    int ylo, yhi, xlo = 0, xhi = -1;
+    bilinear_dst_range(sh, sy, h, oh, ac, ylo, yhi);
+    float wx[kWinMax];
+#pragma unroll
+    for (int k = 0; k < kWinMax; ++k) wx[k] = 0.f;
+    if (sx < w) {
+        bilinear_dst_range(sw, sx, w, ow, ac, xlo, xhi);
+#pragma unroll
+        for (int k = 0; k < kWinMax; ++k) {
+            const int ox = xlo + k;
+            if (ox <= xhi) {
+                const Lerp lx = bilinear_src(sw, ox, w, ac);
+                wx[k] = (lx.i0 == sx ? lx.w0 : 0.f) + (lx.i1 == sx ? lx.w1 : 0.f);
+            }
+        }
+    }
+    const int64_t plane = static_cast<int64_t>(oh) * ow;
+    for (int c = ty; c < ct; c += blockDim.y) {
+        float acc = 0.f;
+        if (c < nc && sx < w) {
+            const float* b = dy + (static_cast<int64_t>(n) * nc + c) * plane;
+            for (int oy = ylo; oy <= yhi; ++oy) {
+                const Lerp ly = bilinear_src(sh, oy, h, ac);
+                const float wy = (ly.i0 == sy ? ly.w0 : 0.f) + (ly.i1 == sy ? ly.w1 : 0.f);
+                if (wy == 0.f) continue;
+                const float* q = b + static_cast<int64_t>(oy) * ow + xlo;
+                float r = 0.f;
+#pragma unroll
+                for (int k = 0; k < kWinMax; ++k)
+                    if (xlo + k <= xhi) r = fmaf(wx[k], __ldg(q + k), r);
+                acc = fmaf(wy, r, acc);
+            }
+        }
+        tile[tx * ct + c] = __float2bfloat16(acc);
+    }
+    __syncthreads();
+    // the block's pixels are consecutive in NHWC: one contiguous run of npix * ct bf16
+    const int npix = min(128, w - blockIdx.x * 128);
+    const int vecs = npix * ct / 8;
+    uint4* dst = reinterpret_cast<uint4*>(dx + ((static_cast<int64_t>(n) * h + sy) * w + blockIdx.x * 128) * ct);
+    const uint4* src = reinterpret_cast<const uint4*>(tile);
+    for (int i = ty * 128 + tx; i < vecs; i += 128 * blockDim.y) dst[i] = src[i];
+}
+
 // generic NCHW fp32 bilinear resize (compute_loss when the logits and the targets differ in size)
 __global__ void __launch_bounds__(256) resize_nchw_fwd_kernel(const float* __restrict__ x, int h, int w,
                                                                float* __restrict__ y, int oh, int ow, int64_t total,
@@ -352,6 +409,14 @@ int b200seg_logits_upsample_bwd(const float* dy, int n, int nc, int oh, int ow, 
     const int grid = static_cast<int>(ceil_div64(total, 128));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     __nv_bfloat16* o = static_cast<__nv_bfloat16*>(dx);
+    // x window of a source pixel: at most 2/scale + 3 destination columns
+    const bool tiled = sw > 0.f && (2.f / sw + 6.f) <= static_cast<float>(kWinMax) && h <= 65535 && n <= 65535;
+    if (tiled) {
+        logits_up_bwd_tiled_kernel<<<dim3(ceil_div(w, 128), h, n), dim3(128, 4), 128 * c_total * 2, st>>>(
+            dy, nc, oh, ow, o, c_total, h, w, sh, sw, align_corners);
+        B200SEG_LAUNCH_CHECK();
+        return 0;
+    }
     if (c_total <= 8)
         logits_up_bwd_kernel<8><<<grid, 128, 0, st>>>(dy, nc, oh, ow, o, c_total, h, w, total, sh, sw, align_corners);
     else if (c_total <= 24)

@@ -37,16 +37,21 @@ __global__ void __launch_bounds__(256) linear_fwd_kernel(const float* __restrict
     }
 }
 
-// dx[n][c] = sum_k dy[n][k] * w[k][c];  one thread per input channel c (coalesced over c for every k)
+// dx[n][c] = sum_k dy[n][k] * w[k][c];  one thread per input channel c (coalesced over c for every k); the k range is
+// split over blockIdx.y (16 CTAs of 128 threads could not pull a 2 MB weight at speed) and partial sums meet in dx
+// (zeroed by the caller) through atomics.
+constexpr int kBwdDataKChunk = 16;
 __global__ void __launch_bounds__(128) linear_bwd_data_kernel(const float* __restrict__ dy, const float* __restrict__ w,
                                                                float* __restrict__ dx, int n, int c, int k) {
     const int cc = blockIdx.x * blockDim.x + threadIdx.x;
     if (cc >= c) return;
+    const int k_begin = blockIdx.y * kBwdDataKChunk;
+    const int k_end = min(k, k_begin + kBwdDataKChunk);
     for (int n0 = 0; n0 < n; n0 += kRowChunk) {
         float acc[kRowChunk];
 #pragma unroll
         for (int i = 0; i < kRowChunk; ++i) acc[i] = 0.f;
-        for (int kk = 0; kk < k; ++kk) {
+        for (int kk = k_begin; kk < k_end; ++kk) {
             const float wv = __ldg(w + static_cast<size_t>(kk) * c + cc);
 #pragma unroll
             for (int i = 0; i < kRowChunk; ++i)
@@ -54,7 +59,7 @@ __global__ void __launch_bounds__(128) linear_bwd_data_kernel(const float* __res
         }
 #pragma unroll
         for (int i = 0; i < kRowChunk; ++i)
-            if (n0 + i < n) dx[static_cast<size_t>(n0 + i) * c + cc] = acc[i];
+            if (n0 + i < n) atomicAdd(dx + static_cast<size_t>(n0 + i) * c + cc, acc[i]);
     }
 }
 
@@ -146,7 +151,7 @@ int b200seg_linear_f32_fwd(const float* x, const float* w, float* y, int n, int 
     using namespace b200seg;
     clear_error();
     B200SEG_CHECK(x && w && y && n > 0 && c > 0 && k > 0, "linear_f32_fwd: bad arguments");
-    linear_fwd_kernel<<<ceil_div(k * 32, 256), 256, 0, static_cast<cudaStream_t>(st)>>>(x, w, y, n, c, k);
+    linear_fwd_kernel<<<ceil_div(k * 32, 64), 64, 0, static_cast<cudaStream_t>(st)>>>(x, w, y, n, c, k);   // 2 warps per CTA: fills the SMs
     B200SEG_LAUNCH_CHECK();
     return 0;
 }
@@ -155,7 +160,9 @@ int b200seg_linear_f32_bwd_data(const float* dy, const float* w, float* dx, int 
     using namespace b200seg;
     clear_error();
     B200SEG_CHECK(dy && w && dx && n > 0 && c > 0 && k > 0, "linear_f32_bwd_data: bad arguments");
-    linear_bwd_data_kernel<<<ceil_div(c, 128), 128, 0, static_cast<cudaStream_t>(st)>>>(dy, w, dx, n, c, k);
+    B200SEG_CUDA(cudaMemsetAsync(dx, 0, sizeof(float) * static_cast<size_t>(n) * c, static_cast<cudaStream_t>(st)));
+    linear_bwd_data_kernel<<<dim3(ceil_div(c, 128), ceil_div(k, kBwdDataKChunk)), 128, 0, static_cast<cudaStream_t>(st)>>>(
+        dy, w, dx, n, c, k);
     B200SEG_LAUNCH_CHECK();
     return 0;
 }
