@@ -153,7 +153,7 @@ def run_b200(args):
     B = args.batch
     torch.manual_seed(1234)                       # identical initial weights on every rank
     model = P.DeepLabV3Plus(NC).to(dev).train()
-    opt = torch.optim.SGD(model.parameters(), lr=1e-3, momentum=0.9)
+    opt = P.optim.SGD(model.parameters(), lr=1e-3, momentum=0.9)       # one multi-tensor launch (b200seg_sgd_multi)
     bucketer = GradBucketer(model.parameters()) if world > 1 else None
 
     g = torch.Generator(device='cpu').manual_seed(100 + rank)
@@ -162,21 +162,22 @@ def run_b200(args):
     x_dev, t_dev = x_host.to(dev), t_host.to(dev)
     loss_host = torch.zeros((), dtype=torch.float32).pin_memory()
 
-    def step(x, t):
-        opt.zero_grad(set_to_none=True)
-        out = model(x)
-        loss = P.compute_loss(out, t, model)
-        loss.backward()
-        if bucketer is not None:
-            bucketer.finish()
-        opt.step()
-        return loss
+    use_graph = args.graph == 'on' or (args.graph == 'auto' and world == 1)
+    eager = P.TrainStep(model, opt, bucketer, graph=False)
+    step = P.TrainStep(model, opt, bucketer, graph=True) if use_graph else eager
 
     def step_e2e():
-        x = x_host.to(dev, non_blocking=True)
-        t = t_host.to(dev, non_blocking=True)
-        loss = step(x, t)
-        loss_host.copy_(loss.detach(), non_blocking=True)
+        # the public call with HOST buffers: pinned host -> device copies, the step, and the loss read back
+        if use_graph:
+            xs, ts = step.static_inputs
+            xs.copy_(x_host, non_blocking=True)
+            ts.copy_(t_host, non_blocking=True)
+            loss = step(xs, ts)
+        else:
+            x = x_host.to(dev, non_blocking=True)
+            t = t_host.to(dev, non_blocking=True)
+            loss = step(x, t)
+        loss_host.copy_(loss, non_blocking=True)
         torch.cuda.current_stream().synchronize()      # the user reads the loss every step (Trainer prints it)
         return loss_host
 
@@ -198,14 +199,22 @@ def run_b200(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms) / 1e3
 
-    for _ in range(args.warmup):
+    for _ in range(args.warmup + (4 if use_graph else 0)):      # graph mode: 3 eager calls + the capture come first
         step(x_dev, t_dev)
+    # host cost of enqueueing one eager step (Python + ctypes + allocator), for the record: it is what the graph removes
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    l0 = _lib.launches()
+    eager(x_dev, t_dev)
+    host_enqueue_ms = (time.perf_counter() - t0) * 1e3
+    eager_launches = _lib.launches() - l0
+    torch.cuda.synchronize()
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
     l0 = _lib.launches()
     secs = timed(lambda: step(x_dev, t_dev), args.steps)
-    launches = _lib.launches() - l0
+    launches = (step.launches_per_step * args.steps) if use_graph else (_lib.launches() - l0)
     clocks = sampler.stop() if sampler else None
     for _ in range(min(args.warmup, 2)):
         step_e2e()
@@ -214,11 +223,13 @@ def run_b200(args):
     # per-launch CUDA-event timing of the tcgen05 conv kernels over a few more steps (the events sit on the
     # launching stream; kept out of the throughput loop above so the headline has no instrumentation in it)
     E.PROFILE = []
+    E.OP_PROFILE = [] if args.detail else None
     prof_steps = min(args.steps, 3)
     for _ in range(prof_steps):
-        step(x_dev, t_dev)
+        eager(x_dev, t_dev)
     torch.cuda.synchronize()
     rec, E.PROFILE = E.PROFILE, None
+    op_rec, E.OP_PROFILE = E.OP_PROFILE, None
     agg = {}
     for tag, flops, e0, e1 in rec:
         a = agg.setdefault(tag, [0.0, 0.0, 0])
@@ -247,9 +258,11 @@ def run_b200(args):
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
             'config': {'workload': 'DeepLabV3+ 21-class 512x512 bf16 training, fwd+loss+bwd+SGD (BASELINE configs[3])',
                        'per_gpu_batch': B, 'global_batch': B * world, 'parallelism': 'dp%d' % world,
+                       'cuda_graph': bool(use_graph), 'host_enqueue_ms_per_eager_step': round(host_enqueue_ms, 2),
+                       'libb200seg_launches_per_step': eager_launches,
                        'l2': 'no explicit flush: one step streams several GB of activations (>> 126 MB L2)',
                        'backbone': 'ResNet-50 OS16 on libb200seg (tcgen05 convs incl. stride 2, fused BN/ReLU/residual, '
-                                   'max pool); only the 3-channel 7x7 stem conv is cuDNN (SURVEY.md 8f-1)'},
+                                   'max pool); 7x7 stem = patch gather + 1x1 tcgen05 GEMM; no cuDNN on the path'},
             'e2e': {'value': ips_e2e, 'unit': 'images/sec', 'h2d_bytes_per_step': x_host.numel() * 4 + t_host.numel() * 8,
                     'd2h_bytes_per_step': 4, 'ms_per_step': secs_e2e / args.steps * 1e3},
             'gpu_launches': launches,
@@ -265,6 +278,26 @@ def run_b200(args):
             line['cpu_baseline'] = {'value': ips_cpu, 'unit': 'images/sec', 'cores': threads, 'kind': 'port',
                                     'sample': 'oracle DeepLabV3+ 512x512 train step, batch %d, 1 warm-up + 2 timed steps '
                                               '(%.1f s/step)' % (CPU_SAMPLE_BATCH, dt)}
+        if args.detail:
+            with open(args.detail, 'w') as f:
+                ops, ops_by_shape = {}, {}
+                for tag, e0, e1 in op_rec or []:
+                    us = e0.elapsed_time(e1) * 1e3 / prof_steps
+                    for table, key in ((ops, tag.split(' ')[0]), (ops_by_shape, tag)):
+                        o = table.setdefault(key, [0.0, 0])
+                        o[0] += us
+                        o[1] += 1
+                counts = {t: v[2] // prof_steps for t, v in agg.items()}
+                for d in detail:
+                    d['per_step'] = counts.get(d['launch'])
+                conv_us = {k2: sum(v[1] for t, v in agg.items() if t.startswith(k2)) * 1e6 / prof_steps
+                           for k2 in ('conv_fprop', 'conv_dgrad', 'conv_wgrad')}
+                json.dump({'ms_per_step': line['ms_per_step'], 'conv_us_per_step': conv_us,
+                           'ops_us_per_step': {k2: [round(v[0], 1), v[1] // prof_steps]
+                                               for k2, v in sorted(ops.items(), key=lambda kv: -kv[1][0])},
+                           'ops_by_shape_us_per_step': {k2: [round(v[0], 1), v[1] // prof_steps]
+                                                        for k2, v in sorted(ops_by_shape.items(), key=lambda kv: -kv[1][0])},
+                           'kernels': detail}, f, indent=1)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -273,11 +306,14 @@ def run_b200(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=10)
+    ap.add_argument('--steps', type=int, default=40)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--batch', type=int, default=16, help='images per GPU per step')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--detail', default=None, help='write the per-launch CUDA-event timings of every conv to this file')
+    ap.add_argument('--graph', default='auto', choices=['auto', 'on', 'off'],
+                    help='replay the step from a CUDA graph (auto: on for 1 GPU)')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)

@@ -51,6 +51,47 @@ int b200seg_nhwc_to_nchw(const void* src, float* dst, int n, int c, int h, int w
 int b200seg_pack_weights(const float* w_oihw, int k, int c, int r, int s, void* w_fprop, int k_rows, void* w_dgrad,
                          int c_rows, int k_cols, b200seg_stream_t st);
 
+/* Patch gather for few-channel inputs — the 3-channel stems: ResNet-50 conv1 7x7 stride 2 behind
+ * models/deeplabv3plus.py:17 (external pytorch_modules.backbones.resnet50) and HRNet's ConvNormAct(3, 64, 3, 2)
+ * (models/hrnet.py:260).  fp32 NCHW image -> bf16 NHWC matrix with c_pad channels per output pixel:
+ *   col[n][oy][ox][(r*S + s)*C + c] = x[n][c][oy*stride + r - pad][ox*stride + s - pad]   (0 outside / beyond R*S*C)
+ * c_pad = R*S*C rounded up to a multiple of 8.  The convolution is then the 1x1 tcgen05 GEMM over col with the
+ * weight packed by b200seg_pack_weights_im2col ([k_rows][c_pad], same column order); its weight gradient (fp32
+ * [k][c_pad] from b200seg_conv_wgrad with r = s = 1) is scattered back to OIHW by b200seg_unpack_wgrad_im2col. */
+int b200seg_im2col_nchw(const float* x, int n, int c, int h, int w, int r, int s, int stride, int pad, void* col,
+                        int c_pad, b200seg_stream_t st);
+int b200seg_pack_weights_im2col(const float* w_oihw, int k, int c, int r, int s, void* w_fprop, int k_rows, int c_pad,
+                                b200seg_stream_t st);
+int b200seg_unpack_wgrad_im2col(const float* dw_col, int k, int c, int r, int s, int c_pad, float* dw_oihw,
+                                int accumulate, b200seg_stream_t st);
+
+/* All conv weights of a model re-packed in one or two launches (after an optimizer step every weight is stale at
+ * once): per tensor the same packings as b200seg_pack_weights, or — im2col != 0 — as b200seg_pack_weights_im2col. */
+typedef struct b200seg_pack_desc {
+    const float* w;          /* fp32 OIHW */
+    int32_t k, c, r, s;
+    void* w_fprop;           /* bf16 [r*s][k_rows][c]   (im2col: [k_rows][c_pad]) */
+    void* w_dgrad;           /* bf16 [r*s mirrored][c_rows][k_cols] or NULL */
+    int32_t k_rows, c_rows, k_cols;
+    int32_t im2col, c_pad;
+    int32_t reserved;
+} b200seg_pack_desc;
+int b200seg_pack_weights_multi(const b200seg_pack_desc* descs, int n, b200seg_stream_t st);
+
+/* ---- optimizer step (the update the reference's external Trainer runs after train.py:64's
+ * backward): torch.optim.SGD semantics over ALL parameters in one or two launches.
+ *   g' = grad_scale*g + weight_decay*p;  m = first_step ? g' : momentum*m + (1-dampening)*g';
+ *   p -= lr * (nesterov ? g' + momentum*m : m)        (momentum == 0: p -= lr*g', m may be NULL)
+ * grad_scale folds the 1/world_size of the data-parallel gradient average into the update. */
+typedef struct b200seg_sgd_desc {
+    float* p;
+    const float* g;
+    float* m;
+    int64_t numel;
+} b200seg_sgd_desc;
+int b200seg_sgd_multi(const b200seg_sgd_desc* descs, int n, float lr, float momentum, float dampening, float weight_decay,
+                      int nesterov, int first_step, float grad_scale, b200seg_stream_t st);
+
 /* ---- convolution: tcgen05 implicit GEMM ------------------------------------------------------------------ */
 /* One input of a "same"-padded convolution (stride 1 or 2): activation slice + packed weights + filter geometry. */
 typedef struct b200seg_conv_src {
@@ -134,6 +175,13 @@ int b200seg_bn_apply_add(const void* x, int x_c_total, int x_c_offset, void* y, 
 /* dx += dy * (y > 0): the identity branch's gradient joins the conv branch's at a residual block's input. */
 int b200seg_relu_bwd_add(void* dx, int dx_c_total, int dx_c_offset, const void* dy, int dy_c_total, int dy_c_offset,
                          const void* y, int y_c_total, int y_c_offset, int c, int64_t pixels, b200seg_stream_t st);
+/* dx = (dx + dy * [y > 0]) * [xin > 0] over bf16 NHWC slices; dy, y and xin are each optional (NULL).  The gradient
+ * join of a residual block (`out += residual; relu(out)`, models/hrnet.py:49-52,97-100 and the torchvision bottleneck
+ * behind models/deeplabv3plus.py:17) with the ReLU mask of the block INPUT applied on the way out, so the producing
+ * block's BatchNorm backward receives a pre-masked gradient. */
+int b200seg_grad_add_masked(void* dx, int dx_c_total, int dx_c_offset, const void* dy, int dy_c_total, int dy_c_offset,
+                            const void* y, int y_c_total, int y_c_offset, const void* xin, int xin_c_total,
+                            int xin_c_offset, int c, int64_t pixels, b200seg_stream_t st);
 /* eval mode (test.py:16, inference.py:24): scale/shift from the running statistics; feeds the conv epilogue so
  * Conv+BN+ReLU is one kernel.  save_mean/save_invstd (optional) receive the running mean and 1/sqrt(var+eps). */
 int b200seg_bn_eval_affine(int c, const float* gamma, const float* beta, const float* running_mean,
@@ -230,6 +278,11 @@ int b200seg_resize_nchw_bwd(const float* dy, int64_t planes, int oh, int ow, flo
 int b200seg_softmax_ce(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
                        float grad_scale, double* loss_sum, int64_t* valid_count, float* dlogits, int* status,
                        b200seg_stream_t st);
+/* Backward of the mean cross-entropy (loss.backward() of train.py:64 reaching utils/utils.py:21): recomputes the
+ * softmax from the saved logits and writes dlogits = (softmax - onehot) * (*grad_out) / (*valid_count), both scalars
+ * read on the device (no host sync, no separate scaling pass); ignored pixels get 0. */
+int b200seg_softmax_ce_bwd(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
+                           const float* grad_out, const int64_t* valid_count, float* dlogits, b200seg_stream_t st);
 /* outputs.max(1)[1] (test.py:31): NCHW fp32 -> int64 [n][hw], lowest index wins ties. */
 int b200seg_argmax(const float* logits, int n, int nc, int64_t hw, int64_t* pred, b200seg_stream_t st);
 /* cm[t*nc + p] += 1 over all pixels — superset of the tp/fn/fp loop at test.py:34-46 (tp = diag,

@@ -37,6 +37,18 @@ class WgradDesc(Structure):
                 ('workspace', c_void_p), ('workspace_bytes', c_size_t)]
 
 
+class PackDesc(Structure):
+    """struct b200seg_pack_desc"""
+    _fields_ = [('w', c_void_p), ('k', c_int32), ('c', c_int32), ('r', c_int32), ('s', c_int32),
+                ('w_fprop', c_void_p), ('w_dgrad', c_void_p), ('k_rows', c_int32), ('c_rows', c_int32),
+                ('k_cols', c_int32), ('im2col', c_int32), ('c_pad', c_int32), ('reserved', c_int32)]
+
+
+class SgdDesc(Structure):
+    """struct b200seg_sgd_desc"""
+    _fields_ = [('p', c_void_p), ('g', c_void_p), ('m', c_void_p), ('numel', c_int64)]
+
+
 _P = c_void_p
 _I = c_int
 _L = c_int64
@@ -51,6 +63,11 @@ PROTOTYPES = {
     'b200seg_nchw_to_nhwc': (c_int, [_P, _P, _I, _I, _I, _I, _I, _I, _P]),
     'b200seg_nhwc_to_nchw': (c_int, [_P, _P, _I, _I, _I, _I, _I, _I, _P]),
     'b200seg_pack_weights': (c_int, [_P, _I, _I, _I, _I, _P, _I, _P, _I, _I, _P]),
+    'b200seg_im2col_nchw': (c_int, [_P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _I, _P]),
+    'b200seg_pack_weights_im2col': (c_int, [_P, _I, _I, _I, _I, _P, _I, _I, _P]),
+    'b200seg_unpack_wgrad_im2col': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _P]),
+    'b200seg_pack_weights_multi': (c_int, [POINTER(PackDesc), _I, _P]),
+    'b200seg_sgd_multi': (c_int, [POINTER(SgdDesc), _I, _F, _F, _F, _F, _I, _I, _F, _P]),
     'b200seg_conv_fprop': (c_int, [_I, _I, _I, _I, POINTER(ConvSrc), POINTER(ConvOut), _P]),
     'b200seg_conv_dgrad': (c_int, [_I, _I, _I, _I, POINTER(ConvSrc), POINTER(ConvOut), _P]),
     'b200seg_conv_wgrad_workspace': (c_size_t, [POINTER(WgradDesc)]),
@@ -61,6 +78,7 @@ PROTOTYPES = {
     'b200seg_bn_apply': (c_int, [_P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _I, _P]),
     'b200seg_bn_apply_add': (c_int, [_P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _I, _P, _I, _I, _P, _P, _P]),
     'b200seg_relu_bwd_add': (c_int, [_P, _I, _I, _P, _I, _I, _P, _I, _I, _I, _L, _P]),
+    'b200seg_grad_add_masked': (c_int, [_P, _I, _I, _P, _I, _I, _P, _I, _I, _P, _I, _I, _I, _L, _P]),
     'b200seg_bn_bwd_reduce_masked': (c_int, [_P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _P, _P, _I, _P, _P, _I, _I, _P]),
     'b200seg_bn_bwd_apply_masked': (c_int, [_P, _I, _I, _P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _P, _P, _I, _I, _P, _P,
                                             _P, _I, _P, _I, _I, _P]),
@@ -85,6 +103,7 @@ PROTOTYPES = {
     'b200seg_resize_nchw_fwd': (c_int, [_P, _L, _I, _I, _P, _I, _I, _I, _P]),
     'b200seg_resize_nchw_bwd': (c_int, [_P, _L, _I, _I, _P, _I, _I, _I, _P]),
     'b200seg_softmax_ce': (c_int, [_P, _P, _I, _I, _L, _L, _F, _P, _P, _P, _P, _P]),
+    'b200seg_softmax_ce_bwd': (c_int, [_P, _P, _I, _I, _L, _L, _P, _P, _P, _P]),
     'b200seg_argmax': (c_int, [_P, _I, _I, _L, _P, _P]),
     'b200seg_confusion': (c_int, [_P, _P, _L, _I, _P, _P]),
     'b200seg_argmax_confusion': (c_int, [_P, _P, _I, _I, _L, _P, _P]),

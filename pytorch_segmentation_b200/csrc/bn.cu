@@ -338,6 +338,44 @@ __global__ void __launch_bounds__(256) relu_bwd_add_kernel(__nv_bfloat16* __rest
     }
 }
 
+// dx = (dx + dy * [y > 0]) * [xin > 0]; dy, y and xin are each optional.  The residual-block gradient join with the
+// ReLU mask of the block INPUT applied on the way out, so the producer block's BatchNorm backward gets a pre-masked
+// gradient and never reads its own output again.
+__global__ void __launch_bounds__(256) grad_add_masked_kernel(__nv_bfloat16* __restrict__ dx, int dx_ct, int dx_off,
+                                                               const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off,
+                                                               const __nv_bfloat16* __restrict__ y, int y_ct, int y_off,
+                                                               const __nv_bfloat16* __restrict__ xin, int xin_ct,
+                                                               int xin_off, int groups, int64_t total) {
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int g = static_cast<int>(i % groups);
+        const int64_t p = i / groups;
+        float a[8];
+        __nv_bfloat16* dst = dx + p * dx_ct + dx_off + g * 8;
+        unpack8(*reinterpret_cast<const uint4*>(dst), a);
+        if (dy) {
+            float d[8];
+            unpack8(ldcs128(dy + p * dy_ct + dy_off + g * 8), d);
+            if (y) {
+                float m[8];
+                unpack8(ldcs128(y + p * y_ct + y_off + g * 8), m);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) a[j] += m[j] > 0.f ? d[j] : 0.f;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) a[j] += d[j];
+            }
+        }
+        if (xin) {
+            float m[8];
+            unpack8(ldcs128(xin + p * xin_ct + xin_off + g * 8), m);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a[j] = m[j] > 0.f ? a[j] : 0.f;
+        }
+        st128(dst, pack8(a));
+    }
+}
+
 // dgamma = red1, dbeta = red0 (optionally accumulated into existing .grad)
 __global__ void bn_param_grad_kernel(const float* __restrict__ red, int c, float* dgamma, float* dbeta, int accumulate) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -446,6 +484,25 @@ int b200seg_relu_bwd_add(void* dx, int dx_c_total, int dx_c_offset, const void* 
     relu_bwd_add_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
         static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, static_cast<const __nv_bfloat16*>(dy), dy_c_total,
         dy_c_offset, static_cast<const __nv_bfloat16*>(y), y_c_total, y_c_offset, c / 8, total);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+
+int b200seg_grad_add_masked(void* dx, int dx_c_total, int dx_c_offset, const void* dy, int dy_c_total, int dy_c_offset,
+                            const void* y, int y_c_total, int y_c_offset, const void* xin, int xin_c_total,
+                            int xin_c_offset, int c, int64_t pixels, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    if (check_slice("grad_add_masked(dx)", dx, dx_c_total, dx_c_offset, c)) return 1;
+    if (dy && check_slice("grad_add_masked(dy)", dy, dy_c_total, dy_c_offset, c)) return 1;
+    if (y && check_slice("grad_add_masked(y)", y, y_c_total, y_c_offset, c)) return 1;
+    if (xin && check_slice("grad_add_masked(xin)", xin, xin_c_total, xin_c_offset, c)) return 1;
+    B200SEG_CHECK(pixels > 0 && (dy || xin) && (dy || !y), "grad_add_masked: bad arguments");
+    const int64_t total = pixels * (c / 8);
+    grad_add_masked_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, static_cast<const __nv_bfloat16*>(dy), dy_c_total,
+        dy_c_offset, static_cast<const __nv_bfloat16*>(y), y_c_total, y_c_offset, static_cast<const __nv_bfloat16*>(xin),
+        xin_c_total, xin_c_offset, c / 8, total);
     B200SEG_LAUNCH_CHECK();
     return 0;
 }

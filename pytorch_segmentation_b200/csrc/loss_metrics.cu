@@ -196,7 +196,10 @@ __global__ void __launch_bounds__(256) softmax_ce_kernel(const float* __restrict
                                                           int nc, int64_t hw, int64_t total, int64_t ignore_index,
                                                           float grad_scale, double* loss_sum,
                                                           unsigned long long* valid_count, float* __restrict__ dlogits,
-                                                          int* status) {
+                                                          int* status, const float* __restrict__ g_dev,
+                                                          const unsigned long long* __restrict__ count_dev) {
+    // backward form: the upstream gradient and the valid-pixel count live on the device (no host read)
+    if (g_dev) grad_scale *= __ldg(g_dev) / static_cast<float>(__ldg(count_dev));
     double lsum = 0.0;
     unsigned int lcount = 0;
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
@@ -219,7 +222,7 @@ __global__ void __launch_bounds__(256) softmax_ce_kernel(const float* __restrict
         }
         const bool ignored = (t == ignore_index);
         const bool bad = !ignored && (t < 0 || t >= nc);
-        if (bad) *status = 1;
+        if (bad && status) *status = 1;
         const bool valid = !ignored && !bad;
         float xt = 0.f;
         if (valid) {
@@ -245,7 +248,7 @@ __global__ void __launch_bounds__(256) softmax_ce_kernel(const float* __restrict
         scnt[warp] = lcount;
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (threadIdx.x == 0 && loss_sum) {
         double a = 0.0;
         unsigned long long b = 0;
         for (int k = 0; k < (blockDim.x >> 5); ++k) {
@@ -262,7 +265,10 @@ __global__ void __launch_bounds__(256) softmax_ce_generic_kernel(const float* __
                                                                   const int64_t* __restrict__ tgt, int nc, int64_t hw,
                                                                   int64_t total, int64_t ignore_index, float grad_scale,
                                                                   double* loss_sum, unsigned long long* valid_count,
-                                                                  float* __restrict__ dlogits, int* status) {
+                                                                  float* __restrict__ dlogits, int* status,
+                                                                  const float* __restrict__ g_dev,
+                                                                  const unsigned long long* __restrict__ count_dev) {
+    if (g_dev) grad_scale *= __ldg(g_dev) / static_cast<float>(__ldg(count_dev));
     double lsum = 0.0;
     unsigned int lcount = 0;
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
@@ -276,7 +282,7 @@ __global__ void __launch_bounds__(256) softmax_ce_generic_kernel(const float* __
         for (int c = 0; c < nc; ++c) s += __expf(q[c * hw] - m);
         const bool ignored = (t == ignore_index);
         const bool bad = !ignored && (t < 0 || t >= nc);
-        if (bad) *status = 1;
+        if (bad && status) *status = 1;
         const bool valid = !ignored && !bad;
         if (valid) {
             lsum += static_cast<double>(__logf(s) + m - q[t * hw]);
@@ -291,7 +297,7 @@ __global__ void __launch_bounds__(256) softmax_ce_generic_kernel(const float* __
     }
     lsum = warp_sum(lsum);
     lcount = __reduce_add_sync(0xffffffffu, lcount);
-    if ((threadIdx.x & 31) == 0) {
+    if ((threadIdx.x & 31) == 0 && loss_sum) {
         atomicAdd(loss_sum, lsum);
         if (valid_count) atomicAdd(valid_count, static_cast<unsigned long long>(lcount));
     }
@@ -455,30 +461,51 @@ int b200seg_resize_nchw_bwd(const float* dy, int64_t planes, int oh, int ow, flo
     return 0;
 }
 
+namespace b200seg {
+namespace {
+int launch_softmax_ce(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
+                      float grad_scale, double* loss_sum, int64_t* valid_count, float* dlogits, int* status,
+                      const float* g_dev, const int64_t* count_dev, cudaStream_t st) {
+    const int64_t total = static_cast<int64_t>(n) * hw;
+    const int grid = elementwise_grid(total);
+    unsigned long long* vc = reinterpret_cast<unsigned long long*>(valid_count);
+    const unsigned long long* cd = reinterpret_cast<const unsigned long long*>(count_dev);
+    if (nc <= 8)
+        softmax_ce_kernel<8><<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum, vc,
+                                                    dlogits, status, g_dev, cd);
+    else if (nc <= 24)
+        softmax_ce_kernel<24><<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum, vc,
+                                                     dlogits, status, g_dev, cd);
+    else if (nc <= 32)
+        softmax_ce_kernel<32><<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum, vc,
+                                                     dlogits, status, g_dev, cd);
+    else
+        softmax_ce_generic_kernel<<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum,
+                                                        vc, dlogits, status, g_dev, cd);
+    B200SEG_LAUNCH_CHECK();
+    return 0;
+}
+}  // namespace
+}  // namespace b200seg
+
 int b200seg_softmax_ce(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
                        float grad_scale, double* loss_sum, int64_t* valid_count, float* dlogits, int* status,
                        b200seg_stream_t stream) {
     using namespace b200seg;
     clear_error();
     B200SEG_CHECK(logits && targets && loss_sum && status && n > 0 && nc > 0 && hw > 0, "softmax_ce: bad arguments");
-    const int64_t total = static_cast<int64_t>(n) * hw;
-    const int grid = elementwise_grid(total);
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    unsigned long long* vc = reinterpret_cast<unsigned long long*>(valid_count);
-    if (nc <= 8)
-        softmax_ce_kernel<8><<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum, vc,
-                                                    dlogits, status);
-    else if (nc <= 24)
-        softmax_ce_kernel<24><<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum, vc,
-                                                     dlogits, status);
-    else if (nc <= 32)
-        softmax_ce_kernel<32><<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum, vc,
-                                                     dlogits, status);
-    else
-        softmax_ce_generic_kernel<<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum,
-                                                        vc, dlogits, status);
-    B200SEG_LAUNCH_CHECK();
-    return 0;
+    return launch_softmax_ce(logits, targets, n, nc, hw, ignore_index, grad_scale, loss_sum, valid_count, dlogits, status,
+                             nullptr, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+int b200seg_softmax_ce_bwd(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
+                           const float* grad_out, const int64_t* valid_count, float* dlogits, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(logits && targets && grad_out && valid_count && dlogits && n > 0 && nc > 0 && hw > 0,
+                  "softmax_ce_bwd: bad arguments");
+    return launch_softmax_ce(logits, targets, n, nc, hw, ignore_index, 1.0f, nullptr, nullptr, dlogits, nullptr, grad_out,
+                             valid_count, static_cast<cudaStream_t>(stream));
 }
 
 int b200seg_argmax(const float* logits, int n, int nc, int64_t hw, int64_t* pred, b200seg_stream_t stream) {

@@ -1,0 +1,213 @@
+// Multi-tensor kernels for the parameter side of a training step: the SGD(momentum) update of ALL
+// parameters and the bf16 re-packing of ALL conv weights, each in one or two launches instead of one per tensor.
+// The per-tensor descriptors travel BY VALUE in the kernel parameters (gradient pointers change from step to step
+// in eager mode, so there is no device-side table to keep in sync; a CUDA-graph capture records them as constants).
+// Both are pure HBM streams: fp32 p/g/m in, p/m out for the update (20 B per element), 4 B in / 4 B out for the pack.
+#include "common.cuh"
+#include "vec.cuh"
+
+#include <string.h>
+
+namespace b200seg {
+namespace {
+
+// ---------------------------------------------------------------------------------------------------------------
+// SGD with momentum — torch.optim.SGD semantics (the reference's external Trainer default, train.py:61-68):
+//   g' = grad_scale * g + weight_decay * p ;  m = first ? g' : momentum * m + (1 - dampening) * g'
+//   step = nesterov ? g' + momentum * m : m ;  p -= lr * step          (momentum == 0: step = g', m untouched)
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kSgdTensors = 96;
+constexpr int kSgdElemsPerBlock = 256 * 16;
+
+struct SgdChunk {
+    b200seg_sgd_desc t[kSgdTensors];
+    int blk_start[kSgdTensors + 1];
+    int n;
+    float lr, momentum, dampening, weight_decay, grad_scale;
+    int nesterov, first;
+};
+
+__device__ __forceinline__ float sgd_one(float p, float g, float* m, const SgdChunk& c) {
+    g = fmaf(c.weight_decay, p, c.grad_scale * g);
+    float step = g;
+    if (c.momentum != 0.f) {
+        const float mm = c.first ? g : fmaf(c.momentum, *m, (1.f - c.dampening) * g);
+        *m = mm;
+        step = c.nesterov ? fmaf(c.momentum, mm, g) : mm;
+    }
+    return fmaf(-c.lr, step, p);
+}
+
+__global__ void __launch_bounds__(256) sgd_multi_kernel(const __grid_constant__ SgdChunk c) {
+    // which tensor does this block belong to (block ranges are a prefix sum; n <= 96: binary search)
+    int lo = 0, hi = c.n - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (c.blk_start[mid] <= static_cast<int>(blockIdx.x)) lo = mid; else hi = mid - 1;
+    }
+    const b200seg_sgd_desc& t = c.t[lo];
+    const int64_t begin = static_cast<int64_t>(blockIdx.x - c.blk_start[lo]) * kSgdElemsPerBlock;
+    const int64_t end = begin + kSgdElemsPerBlock < t.numel ? begin + kSgdElemsPerBlock : t.numel;
+    float* p = t.p;
+    const float* g = t.g;
+    float* m = t.m;
+    const bool use_m = c.momentum != 0.f;
+    const bool aligned = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) |
+                           (use_m ? reinterpret_cast<uintptr_t>(m) : 0)) & 15) == 0;
+    if (aligned) {
+        const int64_t vend = begin + ((end - begin) & ~int64_t(3));
+        for (int64_t i = begin + threadIdx.x * 4; i < vend; i += 256 * 4) {
+            float4 pv = *reinterpret_cast<const float4*>(p + i);
+            const float4 gv = __ldcs(reinterpret_cast<const float4*>(g + i));
+            float4 mv = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (use_m && !c.first) mv = *reinterpret_cast<const float4*>(m + i);
+            pv.x = sgd_one(pv.x, gv.x, &mv.x, c);
+            pv.y = sgd_one(pv.y, gv.y, &mv.y, c);
+            pv.z = sgd_one(pv.z, gv.z, &mv.z, c);
+            pv.w = sgd_one(pv.w, gv.w, &mv.w, c);
+            *reinterpret_cast<float4*>(p + i) = pv;
+            if (use_m) *reinterpret_cast<float4*>(m + i) = mv;
+        }
+        for (int64_t i = vend + threadIdx.x; i < end; i += 256) {
+            float mv = (use_m && !c.first) ? m[i] : 0.f;
+            p[i] = sgd_one(p[i], g[i], &mv, c);
+            if (use_m) m[i] = mv;
+        }
+    } else {
+        for (int64_t i = begin + threadIdx.x; i < end; i += 256) {
+            float mv = (use_m && !c.first) ? m[i] : 0.f;
+            p[i] = sgd_one(p[i], g[i], &mv, c);
+            if (use_m) m[i] = mv;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// weight packing, all conv weights of a model in one go (same element mapping as pack_weights_kernel /
+// pack_weights_im2col_kernel in pack.cu / im2col.cu)
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kPackTensors = 48;
+constexpr int kPackElemsPerBlock = 256 * 8;
+
+struct PackChunk {
+    b200seg_pack_desc t[kPackTensors];
+    int blk_start[kPackTensors + 1];
+    int n;
+};
+
+__global__ void __launch_bounds__(256) pack_multi_kernel(const __grid_constant__ PackChunk c) {
+    int lo = 0, hi = c.n - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (c.blk_start[mid] <= static_cast<int>(blockIdx.x)) lo = mid; else hi = mid - 1;
+    }
+    const b200seg_pack_desc& t = c.t[lo];
+    const float* __restrict__ w = t.w;
+    const int taps = t.r * t.s;
+    const long long begin = static_cast<long long>(blockIdx.x - c.blk_start[lo]) * kPackElemsPerBlock;
+    __nv_bfloat16* wf = static_cast<__nv_bfloat16*>(t.w_fprop);
+    __nv_bfloat16* wd = static_cast<__nv_bfloat16*>(t.w_dgrad);
+    if (t.im2col) {
+        const long long total = static_cast<long long>(t.k_rows) * t.c_pad;
+        for (long long i = begin + threadIdx.x; i < begin + kPackElemsPerBlock && i < total; i += 256) {
+            const int j = static_cast<int>(i % t.c_pad), kk = static_cast<int>(i / t.c_pad);
+            float v = 0.f;
+            if (kk < t.k && j < taps * t.c) v = __ldg(w + (static_cast<size_t>(kk) * t.c + j % t.c) * taps + j / t.c);
+            wf[i] = __float2bfloat16(v);
+        }
+        return;
+    }
+    const long long total_f = wf ? static_cast<long long>(taps) * t.k_rows * t.c : 0;
+    for (long long i = begin + threadIdx.x; i < begin + kPackElemsPerBlock && i < total_f; i += 256) {
+        const int cc = static_cast<int>(i % t.c);
+        const int kk = static_cast<int>((i / t.c) % t.k_rows);
+        const int tap = static_cast<int>(i / (static_cast<long long>(t.c) * t.k_rows));
+        const float v = kk < t.k ? __ldg(w + (static_cast<size_t>(kk) * t.c + cc) * taps + tap) : 0.f;
+        wf[i] = __float2bfloat16(v);
+    }
+    const long long total_d = wd ? static_cast<long long>(taps) * t.c_rows * t.k_cols : 0;
+    for (long long i = begin + threadIdx.x; i < begin + kPackElemsPerBlock && i < total_d; i += 256) {
+        const int kk = static_cast<int>(i % t.k_cols);
+        const int cc = static_cast<int>((i / t.k_cols) % t.c_rows);
+        const int tap = static_cast<int>(i / (static_cast<long long>(t.k_cols) * t.c_rows));
+        const int src_tap = taps - 1 - tap;       // dgrad reads dY at the mirrored tap
+        const float v = (cc < t.c && kk < t.k) ? __ldg(w + (static_cast<size_t>(kk) * t.c + cc) * taps + src_tap) : 0.f;
+        wd[i] = __float2bfloat16(v);
+    }
+}
+
+}  // namespace
+}  // namespace b200seg
+
+extern "C" {
+
+int b200seg_sgd_multi(const b200seg_sgd_desc* descs, int n, float lr, float momentum, float dampening, float weight_decay,
+                      int nesterov, int first_step, float grad_scale, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(descs && n > 0, "sgd_multi: no tensors");
+    B200SEG_CHECK(!(nesterov && (momentum <= 0.f || dampening != 0.f)),
+                  "sgd_multi: Nesterov momentum requires a momentum and zero dampening");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    for (int base = 0; base < n;) {
+        SgdChunk c;
+        memset(&c, 0, sizeof(c));
+        c.lr = lr; c.momentum = momentum; c.dampening = dampening; c.weight_decay = weight_decay;
+        c.grad_scale = grad_scale; c.nesterov = nesterov; c.first = first_step;
+        int blocks = 0;
+        while (base < n && c.n < kSgdTensors) {
+            const b200seg_sgd_desc& d = descs[base];
+            B200SEG_CHECK(d.p && d.g && d.numel >= 0 && (momentum == 0.f || d.m), "sgd_multi: tensor %d has null pointers", base);
+            ++base;
+            if (d.numel == 0) continue;
+            c.t[c.n] = d;
+            c.blk_start[c.n] = blocks;
+            blocks += static_cast<int>(ceil_div64(d.numel, kSgdElemsPerBlock));
+            ++c.n;
+        }
+        c.blk_start[c.n] = blocks;
+        if (c.n == 0) continue;
+        sgd_multi_kernel<<<blocks, 256, 0, st>>>(c);
+        B200SEG_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+int b200seg_pack_weights_multi(const b200seg_pack_desc* descs, int n, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(descs && n > 0, "pack_weights_multi: no tensors");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    for (int base = 0; base < n;) {
+        PackChunk c;
+        memset(&c, 0, sizeof(c));
+        int blocks = 0;
+        while (base < n && c.n < kPackTensors) {
+            const b200seg_pack_desc& d = descs[base];
+            B200SEG_CHECK(d.w && d.w_fprop && d.k > 0 && d.c > 0 && d.r > 0 && d.s > 0 && d.k_rows >= d.k,
+                          "pack_weights_multi: tensor %d: bad descriptor", base);
+            long long total;
+            if (d.im2col) {
+                B200SEG_CHECK(d.c_pad % 8 == 0 && d.c_pad >= d.r * d.s * d.c, "pack_weights_multi: tensor %d: bad c_pad", base);
+                total = static_cast<long long>(d.k_rows) * d.c_pad;
+            } else {
+                B200SEG_CHECK(!d.w_dgrad || (d.c_rows >= d.c && d.k_cols >= d.k), "pack_weights_multi: tensor %d: bad dgrad dims",
+                              base);
+                total = static_cast<long long>(d.r) * d.s * d.k_rows * d.c;
+                const long long td = d.w_dgrad ? static_cast<long long>(d.r) * d.s * d.c_rows * d.k_cols : 0;
+                if (td > total) total = td;
+            }
+            c.t[c.n] = d;
+            c.blk_start[c.n] = blocks;
+            blocks += static_cast<int>(ceil_div64(total, kPackElemsPerBlock));
+            ++c.n;
+            ++base;
+        }
+        c.blk_start[c.n] = blocks;
+        pack_multi_kernel<<<blocks, 256, 0, st>>>(c);
+        B200SEG_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+}  // extern "C"

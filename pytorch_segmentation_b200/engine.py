@@ -97,39 +97,153 @@ def _round_up(a, b):
     return (a + b - 1) // b * b
 
 
+# bumped by TrainStep after every CUDA-graph replay (parameters change without their version counters moving)
+WEIGHT_EPOCH = 0
+
+
 class PackedWeight:
     """bf16 packings of an fp32 OIHW conv weight for fprop ([taps][k_rows][c]) and dgrad
-    ([taps mirrored][c_rows][k_cols]); refreshed when the parameter's version changes."""
-    __slots__ = ('k', 'c', 'r', 's', 'k_rows', 'c_rows', 'k_cols', 'wf', 'wd', 'key')
+    ([taps mirrored][c_rows][k_cols]); refreshed when the parameter's version changes.  The buffers are allocated
+    once per shape and rewritten in place (stream order makes that safe; a CUDA graph needs it)."""
+    __slots__ = ('k', 'c', 'r', 's', 'k_rows', 'c_rows', 'k_cols', 'wf', 'wd', 'key', '_shape')
+    im2col = False
 
     def __init__(self):
         self.key = None
+        self.wf = self.wd = self._shape = None
 
-    def update(self, w, need_dgrad=True):
+    def _key(self, w):
+        return (w.data_ptr(), w._version, tuple(w.shape), WEIGHT_EPOCH)
+
+    def fresh(self, w, need_dgrad=True):
+        return self.key == self._key(w) and (self.wd is not None or not need_dgrad)
+
+    def prepare(self, w, need_dgrad=True):
+        """Allocates the buffers for ``w`` if needed and returns (source tensor, filled PackDesc)."""
         _require_cuda(w, 'conv weight')
-        key = (w.data_ptr(), w._version, tuple(w.shape), need_dgrad)
-        if key == self.key:
-            return self
-        w = w.detach()
-        if w.dtype != torch.float32 or not w.is_contiguous():
-            w = w.float().contiguous()
-        k, c, r, s = w.shape
+        src = w.detach()
+        if src.dtype != torch.float32 or not src.is_contiguous():
+            src = src.float().contiguous()
+        k, c, r, s = src.shape
         if c % 8:
             raise ValueError('conv weight with %d input channels: need a multiple of 8' % c)
-        self.k, self.c, self.r, self.s = k, c, r, s
-        self.k_rows = _round_up(k, 8)
-        self.c_rows = _round_up(c, 8)
-        self.k_cols = _round_up(k, 8)
-        taps = r * s
-        self.wf = torch.empty((taps, self.k_rows, c), dtype=BF16, device=w.device)
-        keep_wd = need_dgrad or (self.key is not None and self.key[3])
-        self.wd = torch.empty((taps, self.c_rows, self.k_cols), dtype=BF16, device=w.device) if keep_wd else None
-        _lib.check(_lib.load().b200seg_pack_weights(w.data_ptr(), k, c, r, s, self.wf.data_ptr(), self.k_rows,
-                                                    self.wd.data_ptr() if keep_wd else None, self.c_rows, self.k_cols,
-                                                    _stream()), 'pack_weights')
+        if self._shape != (k, c, r, s, src.device):
+            self.k, self.c, self.r, self.s = k, c, r, s
+            self.k_rows, self.c_rows, self.k_cols = _round_up(k, 8), _round_up(c, 8), _round_up(k, 8)
+            self.wf = torch.empty((r * s, self.k_rows, c), dtype=BF16, device=src.device)
+            self.wd = None
+            self._shape = (k, c, r, s, src.device)
+        if need_dgrad and self.wd is None:
+            self.wd = torch.empty((r * s, self.c_rows, self.k_cols), dtype=BF16, device=src.device)
+        d = _lib.PackDesc(src.data_ptr(), k, c, r, s, self.wf.data_ptr(),
+                          self.wd.data_ptr() if self.wd is not None else None, self.k_rows, self.c_rows, self.k_cols,
+                          0, 0, 0)
+        return src, d
+
+    def update(self, w, need_dgrad=True):
+        if self.fresh(w, need_dgrad):
+            return self
+        src, d = self.prepare(w, need_dgrad)
+        _lib.check(_lib.load().b200seg_pack_weights(d.w, d.k, d.c, d.r, d.s, d.w_fprop, d.k_rows, d.w_dgrad, d.c_rows,
+                                                    d.k_cols, _stream()), 'pack_weights')
         _lib.count_launch()
-        self.key = (key[0], key[1], key[2], keep_wd)
+        self.key = self._key(w)
         return self
+
+
+class PackedIm2colWeight:
+    """bf16 [1][k_rows][c_pad] packing of an fp32 OIHW weight for the patch-gather path (few-channel stems): the
+    conv is a 1x1 GEMM over the gathered matrix, so this quacks like a PackedWeight with r = s = 1 and c = c_pad."""
+    __slots__ = ('k', 'c', 'r', 's', 'k_rows', 'wf', 'wd', 'key', 'cin', 'kr', 'ks', '_shape')
+    im2col = True
+
+    def __init__(self):
+        self.key = None
+        self.wf = self.wd = self._shape = None
+
+    def _key(self, w):
+        return (w.data_ptr(), w._version, tuple(w.shape), WEIGHT_EPOCH)
+
+    def fresh(self, w, need_dgrad=False):
+        return self.key == self._key(w)
+
+    def prepare(self, w, need_dgrad=False):
+        _require_cuda(w, 'conv weight')
+        src = w.detach()
+        if src.dtype != torch.float32 or not src.is_contiguous():
+            src = src.float().contiguous()
+        k, cin, kr, ks = src.shape
+        if self._shape != (k, cin, kr, ks, src.device):
+            self.k, self.cin, self.kr, self.ks = k, cin, kr, ks
+            self.r = self.s = 1
+            self.c = _round_up(cin * kr * ks, 8)
+            self.k_rows = _round_up(k, 8)
+            self.wf = torch.empty((1, self.k_rows, self.c), dtype=BF16, device=src.device)
+            self._shape = (k, cin, kr, ks, src.device)
+        d = _lib.PackDesc(src.data_ptr(), k, cin, kr, ks, self.wf.data_ptr(), None, self.k_rows, 0, 0, 1, self.c, 0)
+        return src, d
+
+    def update(self, w, need_dgrad=False):
+        if self.fresh(w):
+            return self
+        src, d = self.prepare(w)
+        _lib.check(_lib.load().b200seg_pack_weights_im2col(d.w, d.k, d.c, d.r, d.s, d.w_fprop, d.k_rows, d.c_pad,
+                                                           _stream()), 'pack_weights_im2col')
+        _lib.count_launch()
+        self.key = self._key(w)
+        return self
+
+
+def pack_all(entries, need_dgrad=True):
+    """entries: iterable of (PackedWeight | PackedIm2colWeight, weight parameter).  Re-packs every stale one in a
+    single multi-tensor launch (after an optimizer step that is all of them) — the per-layer ``update`` calls that
+    follow find fresh keys and do nothing."""
+    stale = [(pw, w) for pw, w in entries if not pw.fresh(w, need_dgrad)]
+    if not stale:
+        return 0
+    arr = (_lib.PackDesc * len(stale))()
+    keep = []
+    for i, (pw, w) in enumerate(stale):
+        src, arr[i] = pw.prepare(w, need_dgrad)
+        keep.append(src)
+    _lib.check(_lib.load().b200seg_pack_weights_multi(arr, len(stale), _stream()), 'pack_weights_multi')
+    _lib.count_launch((len(stale) + 47) // 48)
+    for pw, w in stale:
+        pw.key = pw._key(w)
+    return len(stale)
+
+
+def packed_entries(model):
+    """(packed, weight) pairs of every module under ``model`` that owns packed conv weights."""
+    out = []
+    for m in model.modules():
+        fn = getattr(m, '_packed_weights', None)
+        if fn is not None:
+            out.extend(fn())
+    return out
+
+
+def im2col(x, r, s, stride, pad):
+    """fp32 NCHW image -> Act [n, oh, ow, round_up(r*s*c, 8)] of gathered patches (bf16)."""
+    _require_cuda(x, 'im2col input')
+    if x.dim() != 4 or x.dtype != torch.float32 or not x.is_contiguous():
+        raise ValueError('im2col: expected a contiguous fp32 N x C x H x W tensor, got %s %s' % (tuple(x.shape), x.dtype))
+    n, c, h, w = x.shape
+    oh, ow = (h + 2 * pad - r) // stride + 1, (w + 2 * pad - s) // stride + 1
+    col = Act.empty(n, oh, ow, _round_up(r * s * c, 8), x.device)
+    _lib.check(_lib.load().b200seg_im2col_nchw(x.data_ptr(), n, c, h, w, r, s, stride, pad, col.ptr, col.c, _stream()),
+               'im2col')
+    _lib.count_launch()
+    return col
+
+
+def unpack_wgrad_im2col(dwcol, pw):
+    """fp32 [k, c_pad, 1, 1] gradient of the gathered-matrix GEMM -> fp32 OIHW gradient of the original filter."""
+    dw = torch.empty((pw.k, pw.cin, pw.kr, pw.ks), dtype=torch.float32, device=dwcol.device)
+    _lib.check(_lib.load().b200seg_unpack_wgrad_im2col(dwcol.data_ptr(), pw.k, pw.cin, pw.kr, pw.ks, pw.c, dw.data_ptr(), 0,
+                                                       _stream()), 'unpack_wgrad_im2col')
+    _lib.count_launch()
+    return dw
 
 
 # ------------------------------------------------------------------------------------------------
@@ -309,6 +423,15 @@ def relu_bwd_add(dx, dy, y):
     """dx += dy * (y > 0)"""
     _lib.check(_lib.load().b200seg_relu_bwd_add(dx.ptr, dx.ct, dx.c_off, dy.ptr, dy.ct, dy.c_off, y.ptr, y.ct, y.c_off,
                                                 dx.c, dx.pixels, _stream()), 'relu_bwd_add')
+    _lib.count_launch()
+
+
+def grad_add_masked(dx, dy=None, y=None, xin=None):
+    """dx = (dx + dy * [y > 0]) * [xin > 0]; dy, y, xin optional Acts."""
+    def trip(a):
+        return (a.ptr, a.ct, a.c_off) if a is not None else (None, 0, 0)
+    _lib.check(_lib.load().b200seg_grad_add_masked(dx.ptr, dx.ct, dx.c_off, *trip(dy), *trip(y), *trip(xin), dx.c, dx.pixels,
+                                                   _stream()), 'grad_add_masked')
     _lib.count_launch()
 
 
@@ -494,6 +617,19 @@ def softmax_ce(logits, targets, ignore_index=-100, want_grad=True):
     return acc, dl
 
 
+def softmax_ce_bwd(logits, targets, grad_out, count, ignore_index=-100):
+    """dlogits = (softmax - onehot) * grad_out / count, recomputed from the saved logits; ``grad_out`` (0-dim fp32)
+    and ``count`` (1-element int64) are read on the device."""
+    n, nc, h, w = logits.shape
+    assert grad_out.dtype == torch.float32 and count.dtype == torch.int64
+    dl = torch.empty_like(logits)
+    _lib.check(_lib.load().b200seg_softmax_ce_bwd(logits.data_ptr(), targets.data_ptr(), n, nc, h * w, ignore_index,
+                                                  grad_out.data_ptr(), count.data_ptr(), dl.data_ptr(), _stream()),
+               'softmax_ce_bwd')
+    _lib.count_launch()
+    return dl
+
+
 def argmax(logits):
     n, nc, h, w = logits.shape
     pred = torch.empty((n, h, w), dtype=torch.int64, device=logits.device)
@@ -519,3 +655,36 @@ def argmax_confusion(logits, targets, cm=None):
                                                     cm.data_ptr(), _stream()), 'argmax_confusion')
     _lib.count_launch()
     return cm
+
+
+# ------------------------------------------------------------------------------------------------
+# per-op CUDA-event timing (bench.py --detail): every wrapper above except the convs, which time themselves with
+# their nominal FLOPs.  OP_PROFILE is None in normal operation: the wrappers then add one global lookup per call.
+# ------------------------------------------------------------------------------------------------
+OP_PROFILE = None
+
+
+def _timed(name, fn):
+    def wrapper(*a, **kw):
+        if OP_PROFILE is None:
+            return fn(*a, **kw)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = fn(*a, **kw)
+        e1.record()
+        act = next((v for v in a if isinstance(v, Act)), None)
+        tag = name if act is None else '%s %dx%dx%dx%d%s' % (name, act.n, act.h, act.w, act.c,
+                                                            ' masked' if kw.get('mask') is not None else '')
+        OP_PROFILE.append((tag, e0, e1))
+        return out
+    wrapper.__name__, wrapper.__doc__ = fn.__name__, fn.__doc__
+    return wrapper
+
+
+for _name in ('as_act', 'grad_like', 'im2col', 'unpack_wgrad_im2col', 'bn_stats', 'bn_finalize', 'bn_eval_affine',
+              'bn_apply', 'bn_backward', 'relu_bwd_add', 'grad_add_masked', 'maxpool_fwd', 'maxpool_bwd', 'upsample_fwd', 'upsample_bwd',
+              'gap_fwd', 'sum_hw', 'broadcast_hw', 'linear_f32_fwd', 'linear_f32_bwd', 'bn_rows_fwd', 'bn_rows_bwd',
+              'channel_sum', 'logits_upsample_fwd', 'logits_upsample_bwd', 'resize_nchw_fwd', 'resize_nchw_bwd',
+              'softmax_ce', 'softmax_ce_bwd', 'argmax', 'confusion', 'argmax_confusion'):
+    globals()[_name] = _timed(_name, globals()[_name])
+del _name

@@ -27,11 +27,19 @@ class DeepLabV3Plus(nn.Module):
         initialize_weights(self.cls_conv)
         self.num_classes = num_classes
         self._cls_packed = E.PackedWeight()
+        self._pack_entries = None
 
     def head_tensors(self):
         return self.project.tensors() + self.aspp.tensors() + [self.cls_conv.weight, self.cls_conv.bias]
 
+    def _packed_weights(self):
+        return [(self._cls_packed, self.cls_conv.weight)]
+
     def forward(self, x):
+        # every conv weight that went stale (all of them after an optimizer step) is re-packed in one launch
+        if self._pack_entries is None:
+            self._pack_entries = E.packed_entries(self)
+        E.pack_all(self._pack_entries, need_dgrad=torch.is_grad_enabled())
         features = self.backbone(x)
         return self.head(features[1], features[-1])
 

@@ -50,6 +50,9 @@ class ConvNormAct(nn.Sequential):
     def bn(self):
         return self[1]
 
+    def _packed_weights(self):
+        return [(self._packed, self[0].weight)]
+
     def tensors(self):
         """The differentiable leaves in the order the heads pass them through autograd."""
         return [self[0].weight, self[1].weight, self[1].bias]

@@ -10,14 +10,15 @@ module tree (same state-dict keys as the oracle shim); the arithmetic below is l
   bandwidth kernel; backward is the two-pass BN backward, the tcgen05 wgrad and dgrad (the block-input gradient of a
   downsampling bottleneck — conv1's and the downsample conv's data gradients — is one accumulation in TMEM);
 * the 3x3 max pool is a gather kernel pair;
-* the 7x7 stride-2 stem convolution over 3 input channels is the ONE convolution left on the library (cuDNN through
-  ``F.conv2d``): 3 channels cannot feed a 64-wide K block.  DESIGN.md §7 lists it as not yet native.
+* the 7x7 stride-2 stem convolution over 3 input channels cannot feed a 64-wide K block tap by tap, so the fp32
+  NCHW image is gathered once into a bf16 patch matrix (147 -> 152 columns per output pixel; the same pass is the
+  fp32 -> bf16 / NCHW -> NHWC conversion of the input) and the stem becomes a 1x1 tcgen05 GEMM over it, its weight
+  gradient the tcgen05 wgrad over the same matrix.  No cuDNN anywhere on the path.
 
 Forward and backward are explicit kernel sequences inside one autograd node (no per-op autograd graph).
 """
 import torch
 import torch.nn as nn
-import torch.nn.functional as F
 import torchvision
 
 from . import engine as E
@@ -90,34 +91,43 @@ class _Block:
             E.bn_apply(raw3, out, v3, True, res=x)
         return out, (x, raw1, v1, a1, raw2, v2, a2, raw3, v3, rawd, vd, out)
 
-    def backward(self, rec, dout, training, grads, need_dx=True):
-        """dout: Act grad of the block output.  Fills grads[param] and returns the Act grad of the block input."""
+    def backward(self, rec, dout, training, grads, need_dx=True, dout_masked=False, mask_in=True):
+        """dout: Act grad of the block output — already multiplied by (out > 0) when ``dout_masked`` (it then came from
+        the next block's ``backward``), raw otherwise (a head's gradient).  Fills grads[param] and returns the Act grad
+        of the block input, multiplied by (x > 0) when ``mask_in`` (x is a ReLU output: the previous block's), so that
+        block's BatchNorm backward never re-reads its own output for the mask."""
         x, raw1, v1, a1, raw2, v2, a2, raw3, v3, rawd, vd, out = rec
         dev = x.t.device
 
-        def unit_bwd(u, dy, raw, vec, xin, mask=None):
+        def unit_bwd(u, dy, raw, vec, xin, relu=True, mask=None):
             draw = E.Act.empty(raw.n, raw.h, raw.w, raw.c, dev)
-            dgamma, dbeta = E.bn_backward(dy, raw, draw, vec, True, training, mask=mask)
+            dgamma, dbeta = E.bn_backward(dy, raw, draw, vec, relu, training, mask=mask)
             grads[u.conv.weight] = u.wgrad(draw, xin)
             grads[u.bn.weight], grads[u.bn.bias] = dgamma, dbeta
             return draw
 
-        draw3 = unit_bwd(self.u3, dout, raw3, v3, a2, mask=out)
+        # bn3 (and the downsample BN) sit under the block's final ReLU, whose mask is the sign of `out`
+        tail = dict(relu=False) if dout_masked else dict(relu=True, mask=out)
+        draw3 = unit_bwd(self.u3, dout, raw3, v3, a2, **tail)
         da2 = E.Act.empty(a2.n, a2.h, a2.w, a2.c, dev)
         E.conv_dgrad([self.u3.dgrad_src(draw3)], da2)
         draw2 = unit_bwd(self.u2, da2, raw2, v2, a1)
         da1 = E.Act.empty(a1.n, a1.h, a1.w, a1.c, dev)
         E.conv_dgrad([self.u2.dgrad_src(draw2)], da1)
         draw1 = unit_bwd(self.u1, da1, raw1, v1, x)
-        drawd = unit_bwd(self.ud, dout, rawd, vd, x, mask=out) if self.ud is not None else None
+        drawd = unit_bwd(self.ud, dout, rawd, vd, x, **tail) if self.ud is not None else None
         if not need_dx:
             return None
         dx = E.Act.empty(x.n, x.h, x.w, x.c, dev)
+        xin = x if mask_in else None
         if self.ud is not None:
             E.conv_dgrad([self.u1.dgrad_src(draw1), self.ud.dgrad_src(drawd)], dx)
+            if xin is not None:
+                E.grad_add_masked(dx, xin=xin)
         else:
             E.conv_dgrad([self.u1.dgrad_src(draw1)], dx)
-            E.relu_bwd_add(dx, dout, out)
+            # identity branch: + dout * (out > 0), the mask being already in dout when it is pre-masked
+            E.grad_add_masked(dx, dy=dout, y=None if dout_masked else out, xin=xin)
         return dx
 
 
@@ -132,6 +142,7 @@ class ResNet50Features(nn.Module):
         self.conv1, self.bn1, self.relu, self.maxpool = net.conv1, net.bn1, net.relu, net.maxpool
         self.layer1, self.layer2, self.layer3, self.layer4 = net.layer1, net.layer2, net.layer3, net.layer4
         self._plan = None
+        self._stem_packed = E.PackedIm2colWeight()
 
     def _build_plan(self):
         layers = [[_Block(b) for b in layer] for layer in (self.layer1, self.layer2, self.layer3, self.layer4)]
@@ -143,6 +154,10 @@ class ResNet50Features(nn.Module):
         self._plan = (layers, units, offs, off)
         return self._plan
 
+    def _packed_weights(self):
+        units = (self._plan or self._build_plan())[1]
+        return [(self._stem_packed, self.conv1.weight)] + [(u.packed, u.conv.weight) for u in units]
+
     def forward(self, x):
         params = list(self.parameters())
         feats = _ResNetFn.apply(self, x, *params)
@@ -153,17 +168,25 @@ class ResNet50Features(nn.Module):
         E._require_cuda(x, 'backbone input')
         layers, units, offs, total = self._plan or self._build_plan()
         dev = x.device
-        # stem: 7x7 stride-2 conv over 3 channels on the library (see module docstring), then our BN/ReLU/max-pool
-        xb = x.detach().to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
-        wb = self.conv1.weight.detach().to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
-        raw0_t = F.conv2d(xb, wb, None, 2, 3).contiguous(memory_format=torch.channels_last)
-        raw0 = E.Act(raw0_t.permute(0, 2, 3, 1))
+        # stem: patch gather of the image + 1x1 tcgen05 GEMM (see module docstring), then BN/ReLU/max-pool
+        conv1 = self.conv1
+        if conv1.bias is not None or conv1.groups != 1 or conv1.dilation != (1, 1):
+            raise NotImplementedError('backbone stem %r is outside the patch-gather path' % (conv1,))
+        xf = x.detach()
+        if xf.dtype != torch.float32 or not xf.is_contiguous():
+            xf = xf.float().contiguous()
+        col = E.im2col(xf, conv1.kernel_size[0], conv1.kernel_size[1], conv1.stride[0], conv1.padding[0])
+        pw0 = self._stem_packed.update(conv1.weight)
+        raw0 = E.Act.empty(col.n, col.h, col.w, conv1.out_channels, dev)
         bn = self.bn1
         if training:
+            stats0 = torch.zeros((2 * raw0.c,), dtype=torch.float32, device=dev)
+            E.conv_fprop([(col, pw0, 1)], raw0, stats=stats0)
             track = bn.track_running_stats and bn.running_mean is not None
-            v0 = E.bn_finalize(E.bn_stats(raw0), raw0.c, raw0.pixels, bn.weight, bn.bias, bn.eps, bn.momentum,
+            v0 = E.bn_finalize(stats0, raw0.c, raw0.pixels, bn.weight, bn.bias, bn.eps, bn.momentum,
                                bn.running_mean if track else None, bn.running_var if track else None)
         else:
+            E.conv_fprop([(col, pw0, 1)], raw0)
             v0 = E.bn_eval_affine(raw0.c, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
         a0 = E.Act.empty(raw0.n, raw0.h, raw0.w, raw0.c, dev)
         E.bn_apply(raw0, a0, v0, True)
@@ -191,27 +214,32 @@ class ResNet50Features(nn.Module):
                    if isinstance(m, nn.BatchNorm2d) and m.track_running_stats and m.num_batches_tracked is not None]
             if nbt:
                 torch._foreach_add_(nbt, 1)
-        saved = (xb, wb, raw0, v0, a0, idx, recs, training) if save else None
+        saved = (col, pw0, raw0, v0, a0, idx, recs, training) if save else None
         return feats, saved
 
     def run_backward(self, saved, gfeats):
         """gfeats: gradients of the five feature maps (None where unused).  -> {parameter: gradient}"""
-        xb, wb, raw0, v0, a0, idx, recs, training = saved
+        col, pw0, raw0, v0, a0, idx, recs, training = saved
         layers = self._plan[0]
         grads = {}
         d = None
+        masked = False       # whether d already carries the ReLU mask of the tensor it is the gradient of
         for li in (3, 2, 1, 0):
             g = gfeats[li + 1]
             if g is not None:
                 ga = E.as_act(g, 'backbone feature gradient')
                 if d is None:
-                    d = ga
+                    d, masked = ga, False
                 else:
-                    d.nchw().add_(ga.nchw())
+                    # d (masked) + external gradient (raw): mask the sum with the layer output's sign
+                    E.grad_add_masked(d, dy=ga, xin=recs[li][-1][-1])
             if d is None:
                 continue
             for bi in range(len(layers[li]) - 1, -1, -1):
-                d = layers[li][bi].backward(recs[li][bi], d, training, grads)
+                # the input of layer1's first block is the max-pool output, not a ReLU output: no mask there
+                d = layers[li][bi].backward(recs[li][bi], d, training, grads, dout_masked=masked,
+                                            mask_in=not (li == 0 and bi == 0))
+                masked = not (li == 0 and bi == 0)
         if d is not None:
             da0 = E.maxpool_bwd(d, idx, a0.h, a0.w)
             if gfeats[0] is not None:
@@ -222,9 +250,9 @@ class ResNet50Features(nn.Module):
             return grads
         draw0 = E.Act.empty(raw0.n, raw0.h, raw0.w, raw0.c, raw0.t.device)
         dgamma, dbeta = E.bn_backward(da0, raw0, draw0, v0, True, training)
-        gw = torch.ops.aten.convolution_backward(draw0.nchw(), xb, wb, None, [2, 2], [3, 3], [1, 1], False, [0, 0], 1,
-                                                 [False, True, False])[1]
-        grads[self.conv1.weight] = gw.float().contiguous()
+        # dW of the stem = the 1x1 wgrad over the gathered matrix, scattered back to OIHW
+        dwcol = E.conv_wgrad(draw0, col, raw0.c, 1, 1, 1)
+        grads[self.conv1.weight] = E.unpack_wgrad_im2col(dwcol, pw0)
         grads[self.bn1.weight], grads[self.bn1.bias] = dgamma, dbeta
         return grads
 
@@ -233,6 +261,8 @@ class _ResNetFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, mod, x, *params):
         save = any(ctx.needs_input_grad[2:])
+        # unused feature maps (the heads read two of the five) must reach backward as None, not as zero tensors
+        ctx.set_materialize_grads(False)
         feats, saved = mod.run_forward(x, mod.training, save)
         ctx.mod, ctx.saved, ctx.params = mod, saved, params
         outs = tuple(f.nchw() for f in feats)

@@ -23,21 +23,25 @@ class _CrossEntropyFn(torch.autograd.Function):
         if resized:          # utils/utils.py:18-20; identity (skipped) when the sizes match
             x = E.resize_nchw_fwd(x, th, tw, align_corners=True)
         need = ctx.needs_input_grad[0]
-        acc, dl = E.softmax_ce(x, targets.contiguous(), IGNORE_INDEX, want_grad=need)
-        count = acc[1:2].view(torch.int64).to(torch.float64)
-        loss = (acc[0:1] / count).to(torch.float32).reshape(())
+        targets = targets.contiguous()
+        # forward reads the logits once and writes nothing but three scalars; the gradient is recomputed in backward
+        # with the upstream gradient and the pixel count read on the device (one pass, no scaling pass)
+        acc, _ = E.softmax_ce(x, targets, IGNORE_INDEX, want_grad=False)
+        count_i = acc[1:2].view(torch.int64)
+        loss = (acc[0:1] / count_i.to(torch.float64)).to(torch.float32).reshape(())
         # an out-of-range target raises in the reference; here it poisons the loss (no host sync)
         bad = acc[2:3].view(torch.int32)[0] != 0
         loss = torch.where(bad, torch.full_like(loss, float('nan')), loss)
         if need:
-            ctx.save_for_backward(dl, count)
+            ctx.save_for_backward(x, targets, count_i)
             ctx.resized, ctx.in_hw, ctx.in_dtype = resized, (outputs.shape[2], outputs.shape[3]), outputs.dtype
         return loss
 
     @staticmethod
     def backward(ctx, g):
-        dl, count = ctx.saved_tensors
-        dl = dl * (g.to(torch.float32) / count.to(torch.float32))
+        x, targets, count_i = ctx.saved_tensors
+        g = g.detach().to(torch.float32).contiguous()
+        dl = E.softmax_ce_bwd(x, targets, g, count_i, IGNORE_INDEX)
         if ctx.resized:
             dl = E.resize_nchw_bwd(dl, ctx.in_hw[0], ctx.in_hw[1], align_corners=True)
         return dl.to(ctx.in_dtype), None

@@ -36,14 +36,18 @@ def test_struct_layouts_match_header(tmp_path):
     # compile the header with the host C compiler and compare struct sizes / key offsets with ctypes
     src = tmp_path / 'sz.c'
     src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "b200seg.h"\n'
-                   'int main(void){printf("%zu %zu %zu %zu %zu %zu\\n", sizeof(b200seg_conv_src), '
+                   'int main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(b200seg_conv_src), '
                    'sizeof(b200seg_conv_out), sizeof(b200seg_wgrad_desc), offsetof(b200seg_conv_src, w), '
-                   'offsetof(b200seg_conv_out, stats), offsetof(b200seg_wgrad_desc, workspace));return 0;}\n')
+                   'offsetof(b200seg_conv_out, stats), offsetof(b200seg_wgrad_desc, workspace), '
+                   'sizeof(b200seg_pack_desc), offsetof(b200seg_pack_desc, k_rows), sizeof(b200seg_sgd_desc), '
+                   'offsetof(b200seg_sgd_desc, numel));return 0;}\n')
     exe = tmp_path / 'sz'
     subprocess.check_call(['gcc', '-I', os.path.join(ROOT, 'include'), str(src), '-o', str(exe)])
     got = [int(v) for v in subprocess.check_output([str(exe)]).split()]
     want = [ctypes.sizeof(_lib.ConvSrc), ctypes.sizeof(_lib.ConvOut), ctypes.sizeof(_lib.WgradDesc),
-            _lib.ConvSrc.w.offset, _lib.ConvOut.stats.offset, _lib.WgradDesc.workspace.offset]
+            _lib.ConvSrc.w.offset, _lib.ConvOut.stats.offset, _lib.WgradDesc.workspace.offset,
+            ctypes.sizeof(_lib.PackDesc), _lib.PackDesc.k_rows.offset, ctypes.sizeof(_lib.SgdDesc),
+            _lib.SgdDesc.numel.offset]
     assert got == want
 
 

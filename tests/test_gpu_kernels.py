@@ -165,6 +165,103 @@ def test_conv_dgrad_mixed_3x3_s1_and_s2(E):
     assert rel_err(from_act(dxa), x.grad) < TOL
 
 
+@pytest.mark.parametrize('n,c,h,w,k,r,stride,pad', [(2, 3, 64, 96, 64, 7, 2, 3), (1, 3, 50, 38, 64, 3, 2, 1),
+                                                     (2, 3, 33, 200, 32, 7, 2, 3), (1, 4, 16, 16, 8, 3, 1, 1)])
+def test_patch_gather_stem_conv(E, n, c, h, w, k, r, stride, pad):
+    # few-channel stem: im2col gather (bit-exact vs unfold of the bf16-rounded image) + 1x1 GEMM fprop + wgrad
+    g = torch.Generator().manual_seed(n * 100 + h)
+    x = torch.randn(n, c, h, w, generator=g)
+    wt = torch.randn(k, c, r, r, generator=g) * 0.1
+    col = E.im2col(x.cuda(), r, r, stride, pad)
+    oh, ow = (h + 2 * pad - r) // stride + 1, (w + 2 * pad - r) // stride + 1
+    assert (col.n, col.h, col.w, col.c) == (n, oh, ow, (r * r * c + 7) // 8 * 8)
+    unf = F.unfold(bf16_round(x), r, padding=pad, stride=stride)            # [n, c*r*r, oh*ow], order (c, r, s)
+    unf = unf.view(n, c, r * r, oh, ow).permute(0, 3, 4, 2, 1).reshape(n, oh, ow, r * r * c)   # -> (tap, c)
+    got = col.t.float().cpu()
+    assert torch.equal(got[..., :r * r * c], unf)
+    assert float(got[..., r * r * c:].abs().max() if col.c > r * r * c else 0.0) == 0.0
+    pw = E.PackedIm2colWeight().update(wt.cuda())
+    y = E.Act.empty(n, oh, ow, k, 'cuda')
+    E.conv_fprop([(col, pw, 1)], y)
+    xr = bf16_round(x).requires_grad_(True)
+    wr = bf16_round(wt).requires_grad_(True)
+    ref = F.conv2d(xr, wr, None, stride, pad)
+    assert rel_err(from_act(y), ref) < TOL
+    gy = bf16_round(torch.randn(n, k, oh, ow, generator=g))
+    ref.backward(gy)
+    dwcol = E.conv_wgrad(nhwc(gy), col, k, 1, 1, 1)
+    dw = E.unpack_wgrad_im2col(dwcol, pw)
+    assert dw.shape == wt.shape
+    assert rel_err(dw, wr.grad) < TOL
+
+
+def test_pack_all_matches_single_tensor_packing(E):
+    g = torch.Generator().manual_seed(5)
+    shapes = [(64, 64, 1, 1), (256, 64, 3, 3), (21, 384, 3, 3), (128, 2048, 3, 3), (8, 8, 1, 1)]
+    ws = [torch.randn(*sh, generator=g).cuda() for sh in shapes]
+    stem = torch.randn(64, 3, 7, 7, generator=g).cuda()
+    single = [E.PackedWeight().update(w, need_dgrad=True) for w in ws]
+    single_stem = E.PackedIm2colWeight().update(stem)
+    multi = [E.PackedWeight() for _ in ws]
+    multi_stem = E.PackedIm2colWeight()
+    n = E.pack_all(list(zip(multi, ws)) + [(multi_stem, stem)], need_dgrad=True)
+    assert n == len(ws) + 1
+    for a, b in zip(single, multi):
+        assert torch.equal(a.wf, b.wf) and torch.equal(a.wd, b.wd)
+        assert (a.k, a.c, a.r, a.s, a.k_rows, a.c_rows, a.k_cols) == (b.k, b.c, b.r, b.s, b.k_rows, b.c_rows, b.k_cols)
+    assert torch.equal(single_stem.wf, multi_stem.wf)
+    # nothing stale: no launch; a version bump makes exactly that tensor stale again
+    assert E.pack_all(list(zip(multi, ws)) + [(multi_stem, stem)], need_dgrad=True) == 0
+    ws[1].mul_(2.0)
+    assert E.pack_all(list(zip(multi, ws)), need_dgrad=True) == 1
+    assert torch.equal(multi[1].wf, E.PackedWeight().update(ws[1]).wf)
+
+
+@pytest.mark.parametrize('momentum,nesterov,wd', [(0.9, False, 0.0), (0.9, True, 5e-4), (0.0, False, 1e-3)])
+def test_sgd_multi_matches_torch_sgd(E, momentum, nesterov, wd):
+    from pytorch_segmentation_b200 import optim
+    g = torch.Generator().manual_seed(11)
+    shapes = [(64, 3, 7, 7), (21,), (256, 64, 3, 3), (1,), (2048, 513), (7, 5, 3)] + [(16,)] * 120
+    ref = [torch.nn.Parameter(torch.randn(*sh, generator=g).cuda()) for sh in shapes]
+    ours = [torch.nn.Parameter(p.detach().clone()) for p in ref]
+    o_ref = torch.optim.SGD(ref, lr=0.05, momentum=momentum, nesterov=nesterov, weight_decay=wd)
+    o_ours = optim.SGD(ours, lr=0.05, momentum=momentum, nesterov=nesterov, weight_decay=wd)
+    for step in range(3):
+        for a, b in zip(ref, ours):
+            if step == 1 and a.numel() == 1:
+                a.grad = b.grad = None                   # a parameter without a gradient is skipped
+                continue
+            gr = torch.randn(a.shape, generator=g).cuda()
+            a.grad, b.grad = gr.clone(), gr.clone()
+        v0 = ours[2]._version
+        o_ref.step()
+        o_ours.step()
+        assert ours[2]._version > v0
+        for a, b in zip(ref, ours):
+            assert torch.allclose(a, b, rtol=1e-6, atol=1e-6)
+    if momentum:
+        assert torch.allclose(o_ref.state[ref[4]]['momentum_buffer'], o_ours.state[ours[4]]['momentum_buffer'],
+                              rtol=1e-6, atol=1e-6)
+
+
+def test_grad_add_masked(E):
+    g = torch.Generator().manual_seed(2)
+    n, h, w, c = 2, 9, 7, 24
+    dx, dy, y, xin = (bf16_round(torch.randn(n, c, h, w, generator=g)) for _ in range(4))
+    a = nhwc(dx)
+    E.grad_add_masked(a, dy=nhwc(dy), y=nhwc(y), xin=nhwc(xin))
+    assert rel_err(from_act(a), bf16_round((dx + dy * (y > 0)) * (xin > 0))) < 1e-6
+    a = nhwc(dx)
+    E.grad_add_masked(a, dy=nhwc(dy), xin=nhwc(xin))
+    assert rel_err(from_act(a), bf16_round((dx + dy) * (xin > 0))) < 1e-6
+    a = nhwc(dx)
+    E.grad_add_masked(a, xin=nhwc(xin))
+    assert torch.equal(from_act(a), dx * (xin > 0))
+    a = nhwc(dx)
+    E.grad_add_masked(a, dy=nhwc(dy), y=nhwc(y))
+    assert rel_err(from_act(a), bf16_round(dx + dy * (y > 0))) < 1e-6
+
+
 def test_conv_epilogue_scale_bias_relu_into_slice(E):
     g = torch.Generator().manual_seed(5)
     n, h, w, c, k = 2, 16, 16, 64, 128
@@ -401,6 +498,22 @@ def test_softmax_cross_entropy(E, nc):
     bad[1, 2, 3] = nc
     acc, _ = E.softmax_ce(logits.detach().cuda(), bad.cuda(), -100, False)
     assert int(acc[2:3].view(torch.int32)[0]) == 1
+
+
+@pytest.mark.parametrize('nc', [2, 21, 40])
+def test_softmax_cross_entropy_backward_recompute(E, nc):
+    # backward entry: dlogits = (softmax - onehot) * g / count with g and count read on the device
+    g = torch.Generator().manual_seed(100 + nc)
+    n, h, w = 2, 19, 31
+    logits = (torch.randn(n, nc, h, w, generator=g) * 3).requires_grad_(True)
+    tgt = torch.randint(0, nc, (n, h, w), generator=g)
+    tgt[1, 3, 2:9] = -100
+    (F.cross_entropy(logits, tgt) * 0.37).backward()
+    count = torch.tensor([int((tgt != -100).sum())], dtype=torch.int64, device='cuda')
+    gout = torch.tensor(0.37, dtype=torch.float32, device='cuda')
+    dl = E.softmax_ce_bwd(logits.detach().cuda(), tgt.cuda(), gout, count, -100)
+    assert rel_err(dl, logits.grad) < 1e-5
+    assert float(dl[1, :, 3, 2:9].abs().max()) == 0.0
 
 
 @pytest.mark.parametrize('nc', [2, 5, 21, 19, 64])

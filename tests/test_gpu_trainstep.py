@@ -1,0 +1,79 @@
+"""TrainStep: the CUDA-graph replay of the optimisation step is the same computation as the eager step
+(train.py:61-72 sequence: forward, compute_loss, backward, optimizer.step), and a model trained through replays
+evaluates with fresh weights afterwards."""
+import copy
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope='module')
+def P(lib):
+    import pytorch_segmentation_b200 as pkg
+    return pkg
+
+
+def _make(P, nc, seed):
+    torch.manual_seed(seed)
+    return P.DeepLabV3Plus(nc).cuda().train()
+
+
+def test_graph_step_matches_eager_step(P):
+    """Three copies of one model see the same batches: A and B step eagerly, C through TrainStep(graph=True).
+    A bf16 Conv-BN-ReLU stack trained on random data is chaotic (fp32 atomics reorder -> bf16 roundings flip ->
+    ReLU masks flip), so the run-to-run distance between the two EAGER copies is the yardstick for the graph copy."""
+    nc, n, h, w = 5, 4, 128, 128
+    m_a = _make(P, nc, 7)
+    m_b, m_c = copy.deepcopy(m_a), copy.deepcopy(m_a)
+    init = torch.cat([p.detach().flatten() for p in m_a.parameters()]).clone()
+    g = torch.Generator().manual_seed(3)
+    batches = [(torch.randn(n, 3, h, w, generator=g).cuda(), torch.randint(0, nc, (n, h, w), generator=g).cuda())
+               for _ in range(7)]
+    steps = []
+    for m, graph in ((m_a, False), (m_b, False), (m_c, True)):
+        steps.append(P.TrainStep(m, torch.optim.SGD(m.parameters(), lr=1e-3, momentum=0.9), graph=graph, warmup=3))
+    losses = [[], [], []]
+    for x, t in batches:
+        for i, s in enumerate(steps):            # graph copy: calls 1-3 eager, call 4 captures + replays, 5-7 replay
+            losses[i].append(float(s(x, t)))
+    assert steps[2].launches_per_step is not None and steps[2].launches_per_step > 100
+
+    def update(m):
+        return torch.cat([p.detach().flatten() for p in m.parameters()]) - init
+
+    ua, ub, uc = update(m_a), update(m_b), update(m_c)
+    floor = float((ua - ub).norm())
+    assert float(ua.norm()) > 0
+    assert float((ua - uc).norm()) <= max(3.0 * floor, 0.05 * float(ua.norm())), \
+        (float((ua - uc).norm()), floor, float(ua.norm()))
+    lfloor = max(abs(a - b) for a, b in zip(losses[0], losses[1]))
+    for a, c in zip(losses[0], losses[2]):
+        assert abs(a - c) <= max(3.0 * lfloor, 2e-2 * max(1.0, abs(a))), losses
+    # running statistics advanced in the replays as well
+    bn_a, bn_b, bn_c = m_a.aspp.project[1], m_b.aspp.project[1], m_c.aspp.project[1]
+    assert int(bn_c.num_batches_tracked) == int(bn_a.num_batches_tracked) == len(batches)
+    rfloor = float((bn_b.running_mean - bn_a.running_mean).abs().max())
+    assert float((bn_c.running_mean - bn_a.running_mean).abs().max()) <= max(3.0 * rfloor, 0.05)
+    assert float((bn_c.running_mean - torch.zeros_like(bn_c.running_mean)).abs().max()) > 0.0
+
+    # eval after graph training reads the CURRENT weights (the packed bf16 copies are refreshed): put C's state into
+    # an eager copy and compare the eval outputs
+    m_d = copy.deepcopy(m_a)
+    m_d.load_state_dict(m_c.state_dict())
+    m_c.eval()
+    m_d.eval()
+    with torch.no_grad():
+        x = batches[0][0]
+        yc, yd = m_c(x), m_d(x)
+    assert float((yc - yd).abs().max()) <= 1e-2 * max(float(yd.abs().max()), 1e-6)
+
+
+def test_graph_step_rejects_other_shapes(P):
+    m = _make(P, 3, 1)
+    s = P.TrainStep(m, torch.optim.SGD(m.parameters(), lr=1e-3), graph=True, warmup=1)
+    x, t = torch.randn(2, 3, 64, 64).cuda(), torch.randint(0, 3, (2, 64, 64)).cuda()
+    s(x, t)
+    with pytest.raises(ValueError):
+        s(torch.randn(2, 3, 96, 96).cuda(), torch.randint(0, 3, (2, 96, 96)).cuda())
