@@ -4,6 +4,7 @@
 // consecutive channel groups of one pixel (coalesced over the NHWC row), fp32 math, one atomic per channel per
 // block for the reductions.
 #include "common.cuh"
+#include "pdl.cuh"
 #include "vec.cuh"
 
 namespace b200seg {
@@ -69,6 +70,7 @@ __device__ __forceinline__ void block_col_reduce(float (&acc)[NV][8], int g_loca
 __global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(const __nv_bfloat16* __restrict__ x, int c_total, int c_off,
                                                                 int c, int64_t pixels, int64_t ppb, int gpb, int rows,
                                                                 float* __restrict__ stats) {
+    pdl_prologue();
     const int groups = c >> 3;
     const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
     const int group = blockIdx.y * gpb + g_local;
@@ -100,6 +102,7 @@ __global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(const __nv_bfloat
 __global__ void __launch_bounds__(kRedThreads) channel_sum_kernel(const __nv_bfloat16* __restrict__ x, int c_total,
                                                                    int c_off, int c, int64_t pixels, int64_t ppb, int gpb,
                                                                    int rows, float* __restrict__ out) {
+    pdl_prologue();
     const int groups = c >> 3;
     const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
     const int group = blockIdx.y * gpb + g_local;
@@ -127,6 +130,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ stats, int c, float
                                    const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
                                    float momentum, float* running_mean, float* running_var, float* scale, float* shift,
                                    float* save_mean, float* save_invstd) {
+    pdl_prologue();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= c) return;
     const float mean = stats[i] * inv_count;
@@ -147,6 +151,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ stats, int c, float
 __global__ void bn_eval_affine_kernel(int c, const float* __restrict__ gamma, const float* __restrict__ beta,
                                       const float* __restrict__ running_mean, const float* __restrict__ running_var,
                                       float eps, float* scale, float* shift, float* save_mean, float* save_invstd) {
+    pdl_prologue();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= c) return;
     const float invstd = rsqrtf(running_var[i] + eps);
@@ -165,6 +170,7 @@ __global__ void __launch_bounds__(kRedThreads) bn_apply_kernel(
     int64_t pixels, int64_t ppb, int gpb, int rows, const float* __restrict__ scale, const float* __restrict__ shift,
     int relu, const __nv_bfloat16* __restrict__ res, int r_ct, int r_off, const float* __restrict__ res_scale,
     const float* __restrict__ res_shift) {
+    pdl_prologue();
     const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
     const int group = blockIdx.y * gpb + g_local;
     if (row >= rows || group >= groups) return;
@@ -214,6 +220,7 @@ __global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(
     int c, int64_t pixels, int64_t ppb, int gpb, int rows, const float* __restrict__ scale, const float* __restrict__ shift,
     const float* __restrict__ mean, const float* __restrict__ invstd, int relu, float* __restrict__ red,
     const __nv_bfloat16* __restrict__ mask, int m_ct, int m_off) {
+    pdl_prologue();
     const int groups = c >> 3;
     const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
     const int group = blockIdx.y * gpb + g_local;
@@ -269,6 +276,7 @@ __global__ void __launch_bounds__(kRedThreads) bn_bwd_apply_kernel(
     float inv_count, const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
     const float* __restrict__ invstd, int relu, int training, const float* __restrict__ red, int c,
     const __nv_bfloat16* __restrict__ mask, int m_ct, int m_off) {
+    pdl_prologue();
     const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
     const int group = blockIdx.y * gpb + g_local;
     if (row >= rows || group >= groups) return;
@@ -323,6 +331,7 @@ __global__ void __launch_bounds__(256) relu_bwd_add_kernel(__nv_bfloat16* __rest
                                                             const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off,
                                                             const __nv_bfloat16* __restrict__ y, int y_ct, int y_off,
                                                             int groups, int64_t total) {
+    pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int g = static_cast<int>(i % groups);
@@ -346,6 +355,7 @@ __global__ void __launch_bounds__(256) grad_add_masked_kernel(__nv_bfloat16* __r
                                                                const __nv_bfloat16* __restrict__ y, int y_ct, int y_off,
                                                                const __nv_bfloat16* __restrict__ xin, int xin_ct,
                                                                int xin_off, int groups, int64_t total) {
+    pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int g = static_cast<int>(i % groups);
@@ -378,6 +388,7 @@ __global__ void __launch_bounds__(256) grad_add_masked_kernel(__nv_bfloat16* __r
 
 // dgamma = red1, dbeta = red0 (optionally accumulated into existing .grad)
 __global__ void bn_param_grad_kernel(const float* __restrict__ red, int c, float* dgamma, float* dbeta, int accumulate) {
+    pdl_prologue();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= c) return;
     if (dbeta) dbeta[i] = accumulate ? dbeta[i] + red[i] : red[i];
@@ -398,9 +409,8 @@ int b200seg_bn_stats(const void* x, int x_c_total, int x_c_offset, int c, int64_
     B200SEG_CHECK(stats && pixels > 0, "bn_stats: bad arguments");
     B200SEG_CUDA(cudaMemsetAsync(stats, 0, sizeof(float) * 2 * c, st));
     const ColGeom g = col_geom(c, pixels);
-    bn_stats_kernel<<<dim3(g.gx, g.gy), kRedThreads, 0, st>>>(static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, c,
-                                                             pixels, g.pixels_per_block, g.gpb, g.rows, stats);
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(bn_stats_kernel, dim3(g.gx, g.gy), kRedThreads, 0, st, static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, c,
+                                                             pixels, g.pixels_per_block, g.gpb, g.rows, stats));
     return 0;
 }
 
@@ -413,10 +423,9 @@ int b200seg_channel_sum(const void* x, int x_c_total, int x_c_offset, int c, int
     B200SEG_CHECK(out && pixels > 0, "channel_sum: bad arguments");
     if (!accumulate) B200SEG_CUDA(cudaMemsetAsync(out, 0, sizeof(float) * c, st));
     const ColGeom g = col_geom(c, pixels);
-    channel_sum_kernel<<<dim3(g.gx, g.gy), kRedThreads, 0, st>>>(static_cast<const __nv_bfloat16*>(x), x_c_total,
+    B200SEG_CUDA(launch_pdl(channel_sum_kernel, dim3(g.gx, g.gy), kRedThreads, 0, st, static_cast<const __nv_bfloat16*>(x), x_c_total,
                                                                 x_c_offset, c, pixels, g.pixels_per_block, g.gpb, g.rows,
-                                                                out);
-    B200SEG_LAUNCH_CHECK();
+                                                                out));
     return 0;
 }
 
@@ -427,10 +436,9 @@ int b200seg_bn_finalize(const float* stats, int c, int64_t count, const float* g
     clear_error();
     B200SEG_CHECK(stats && scale && shift && c > 0 && count > 0, "bn_finalize: bad arguments");
     const float unbias = count > 1 ? static_cast<float>(static_cast<double>(count) / static_cast<double>(count - 1)) : 1.f;
-    bn_finalize_kernel<<<ceil_div(c, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+    B200SEG_CUDA(launch_pdl(bn_finalize_kernel, ceil_div(c, 128), 128, 0, static_cast<cudaStream_t>(stream), 
         stats, c, static_cast<float>(1.0 / static_cast<double>(count)), unbias, gamma, beta, eps, momentum, running_mean,
-        running_var, scale, shift, save_mean, save_invstd);
-    B200SEG_LAUNCH_CHECK();
+        running_var, scale, shift, save_mean, save_invstd));
     return 0;
 }
 
@@ -440,9 +448,8 @@ int b200seg_bn_eval_affine(int c, const float* gamma, const float* beta, const f
     using namespace b200seg;
     clear_error();
     B200SEG_CHECK(running_mean && running_var && scale && shift && c > 0, "bn_eval_affine: bad arguments");
-    bn_eval_affine_kernel<<<ceil_div(c, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
-        c, gamma, beta, running_mean, running_var, eps, scale, shift, save_mean, save_invstd);
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(bn_eval_affine_kernel, ceil_div(c, 128), 128, 0, static_cast<cudaStream_t>(stream), 
+        c, gamma, beta, running_mean, running_var, eps, scale, shift, save_mean, save_invstd));
     return 0;
 }
 
@@ -458,11 +465,10 @@ int b200seg_bn_apply_add(const void* x, int x_c_total, int x_c_offset, void* y, 
     B200SEG_CHECK(scale && shift && pixels > 0, "bn_apply: bad arguments");
     B200SEG_CHECK((res_scale == nullptr) == (res_shift == nullptr), "bn_apply: residual scale and shift go together");
     const ColGeom g = col_geom(c, pixels, 16);
-    bn_apply_kernel<<<dim3(g.gx, g.gy), kRedThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+    B200SEG_CUDA(launch_pdl(bn_apply_kernel, dim3(g.gx, g.gy), kRedThreads, 0, static_cast<cudaStream_t>(stream), 
         static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset,
         c / 8, pixels, g.pixels_per_block, g.gpb, g.rows, scale, shift, relu, static_cast<const __nv_bfloat16*>(res),
-        res_c_total, res_c_offset, res_scale, res_shift);
-    B200SEG_LAUNCH_CHECK();
+        res_c_total, res_c_offset, res_scale, res_shift));
     return 0;
 }
 
@@ -481,10 +487,9 @@ int b200seg_relu_bwd_add(void* dx, int dx_c_total, int dx_c_offset, const void* 
     if (check_slice("relu_bwd_add(y)", y, y_c_total, y_c_offset, c)) return 1;
     B200SEG_CHECK(pixels > 0, "relu_bwd_add: bad arguments");
     const int64_t total = pixels * (c / 8);
-    relu_bwd_add_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    B200SEG_CUDA(launch_pdl(relu_bwd_add_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream), 
         static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, static_cast<const __nv_bfloat16*>(dy), dy_c_total,
-        dy_c_offset, static_cast<const __nv_bfloat16*>(y), y_c_total, y_c_offset, c / 8, total);
-    B200SEG_LAUNCH_CHECK();
+        dy_c_offset, static_cast<const __nv_bfloat16*>(y), y_c_total, y_c_offset, c / 8, total));
     return 0;
 }
 
@@ -499,11 +504,10 @@ int b200seg_grad_add_masked(void* dx, int dx_c_total, int dx_c_offset, const voi
     if (xin && check_slice("grad_add_masked(xin)", xin, xin_c_total, xin_c_offset, c)) return 1;
     B200SEG_CHECK(pixels > 0 && (dy || xin) && (dy || !y), "grad_add_masked: bad arguments");
     const int64_t total = pixels * (c / 8);
-    grad_add_masked_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    B200SEG_CUDA(launch_pdl(grad_add_masked_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream), 
         static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, static_cast<const __nv_bfloat16*>(dy), dy_c_total,
         dy_c_offset, static_cast<const __nv_bfloat16*>(y), y_c_total, y_c_offset, static_cast<const __nv_bfloat16*>(xin),
-        xin_c_total, xin_c_offset, c / 8, total);
-    B200SEG_LAUNCH_CHECK();
+        xin_c_total, xin_c_offset, c / 8, total));
     return 0;
 }
 
@@ -527,11 +531,10 @@ int b200seg_bn_bwd_reduce_masked(const void* dy, int dy_c_total, int dy_c_offset
     B200SEG_CHECK(scale && shift && save_mean && save_invstd && red && pixels > 0, "bn_bwd_reduce: bad arguments");
     B200SEG_CUDA(cudaMemsetAsync(red, 0, sizeof(float) * 2 * c, st));
     const ColGeom g = col_geom(c, pixels);
-    bn_bwd_reduce_kernel<<<dim3(g.gx, g.gy), kRedThreads, 0, st>>>(
+    B200SEG_CUDA(launch_pdl(bn_bwd_reduce_kernel, dim3(g.gx, g.gy), kRedThreads, 0, st, 
         static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, static_cast<const __nv_bfloat16*>(x), x_c_total,
         x_c_offset, c, pixels, g.pixels_per_block, g.gpb, g.rows, scale, shift, save_mean, save_invstd, relu, red,
-        static_cast<const __nv_bfloat16*>(mask), mask_c_total, mask_c_offset);
-    B200SEG_LAUNCH_CHECK();
+        static_cast<const __nv_bfloat16*>(mask), mask_c_total, mask_c_offset));
     return 0;
 }
 
@@ -560,16 +563,14 @@ int b200seg_bn_bwd_apply_masked(const void* dy, int dy_c_total, int dy_c_offset,
     if (mask && check_slice("bn_bwd_apply(mask)", mask, mask_c_total, mask_c_offset, c)) return 1;
     B200SEG_CHECK(scale && shift && save_mean && save_invstd && red && pixels > 0, "bn_bwd_apply: bad arguments");
     const ColGeom g = col_geom(c, pixels, 16);
-    bn_bwd_apply_kernel<<<dim3(g.gx, g.gy), kRedThreads, 0, st>>>(
+    B200SEG_CUDA(launch_pdl(bn_bwd_apply_kernel, dim3(g.gx, g.gy), kRedThreads, 0, st, 
         static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, static_cast<const __nv_bfloat16*>(x), x_c_total,
         x_c_offset, static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, c / 8, pixels, g.pixels_per_block, g.gpb,
         g.rows, static_cast<float>(1.0 / static_cast<double>(pixels)), scale, shift, save_mean, save_invstd, relu, training,
         red, c,
-        static_cast<const __nv_bfloat16*>(mask), mask_c_total, mask_c_offset);
-    B200SEG_LAUNCH_CHECK();
+        static_cast<const __nv_bfloat16*>(mask), mask_c_total, mask_c_offset));
     if (dgamma || dbeta) {
-        bn_param_grad_kernel<<<ceil_div(c, 128), 128, 0, st>>>(red, c, dgamma, dbeta, accumulate_param_grads);
-        B200SEG_LAUNCH_CHECK();
+        B200SEG_CUDA(launch_pdl(bn_param_grad_kernel, ceil_div(c, 128), 128, 0, st, red, c, dgamma, dbeta, accumulate_param_grads));
     }
     return 0;
 }

@@ -17,6 +17,7 @@
 // The same kernel is the data-gradient (x = dy, weights packed transposed with mirrored taps) and sums
 // several sources in TMEM (the ASPP branches' gradients w.r.t. their shared input).
 #include "common.cuh"
+#include "pdl.cuh"
 #include "ptx.cuh"
 
 #include <string.h>
@@ -147,6 +148,10 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // PDL: everything above (barrier init, TMEM allocation, descriptor prefetch) overlapped the previous kernel's
+    // tail; no global memory is touched before this point
+    pdl_launch_dependents();
+    pdl_wait();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -601,8 +606,7 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
     const int sms = sm_count();
     B200SEG_CHECK(sms > 0, "conv: cannot query SM count");
     const int grid = p.num_tiles < sms ? p.num_tiles : sms;
-    igemm_kernel<<<grid, kThreads, kSmemBytes, st>>>(p);
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(igemm_kernel, grid, kThreads, kSmemBytes, st, p));
     return 0;
 }
 

@@ -14,6 +14,7 @@
 // The M side is whichever of (dY, X) has more channels to tile by 128; the other is the N side (<= 256 per
 // tile).  For cls_conv (21 classes) that puts X's 384 channels on M and the padded 32 classes on N.
 #include "common.cuh"
+#include "pdl.cuh"
 #include "ptx.cuh"
 
 #include <string.h>
@@ -125,6 +126,10 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // PDL: everything above (barrier init, TMEM allocation, descriptor prefetch) overlapped the previous kernel's
+    // tail; no global memory is touched before this point
+    pdl_launch_dependents();
+    pdl_wait();
     const int n_boxes = p.bn / 64;
 
     if (warp == 0) {
@@ -225,6 +230,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
 // dw[k][c][r][s] (+)= sum_split ws[split][tap][m][n], (m, n) = (k, c) or (c, k)
 __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int k_out, int c, int taps,
                                     int splits, int m_pad, int n_pad, int m_is_c, int accumulate) {
+    pdl_prologue();
     const long long total = static_cast<long long>(k_out) * c * taps;
     const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
     if (i >= total) return;
@@ -423,14 +429,12 @@ int b200seg_conv_wgrad(const b200seg_wgrad_desc* d, b200seg_stream_t stream) {
     }
     const int taps = d->r * d->s;
     const int grid = pl.splits * taps * pl.tiles_m * pl.tiles_n;
-    wgrad_kernel<<<grid, kThreads, kSmemBytes, st>>>(p);
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(wgrad_kernel, grid, kThreads, kSmemBytes, st, p));
 
     const long long total = static_cast<long long>(d->k_out) * d->c * taps;
     const int rb = 256;
-    wgrad_reduce_kernel<<<static_cast<unsigned>((total + rb - 1) / rb), rb, 0, st>>>(
-        p.ws, d->dw, d->k_out, d->c, taps, pl.splits, pl.m_pad, pl.n_pad, pl.shift_m, d->accumulate);
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(wgrad_reduce_kernel, static_cast<unsigned>((total + rb - 1) / rb), rb, 0, st, 
+        p.ws, d->dw, d->k_out, d->c, taps, pl.splits, pl.m_pad, pl.n_pad, pl.shift_m, d->accumulate));
     return 0;
 }
 

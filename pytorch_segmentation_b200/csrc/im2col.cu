@@ -10,6 +10,7 @@
 // shared memory with loads coalesced along W, then written out as 16-byte chunks (8 col channels) by consecutive
 // threads — the col rows of neighbouring pixels are contiguous, so the stores are fully coalesced.
 #include "common.cuh"
+#include "pdl.cuh"
 #include "vec.cuh"
 
 namespace b200seg {
@@ -21,6 +22,7 @@ constexpr int kMaxCol = 512;     // LUT capacity (R*S*C rounded up)
 __global__ void __launch_bounds__(256) im2col_kernel(const float* __restrict__ x, int C, int H, int W, int R, int S,
                                                       int stride, int pad, int OH, int OW, int c_pad,
                                                       __nv_bfloat16* __restrict__ col) {
+    pdl_prologue();
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int cols = (kTW - 1) * stride + S;
     int* lut = reinterpret_cast<int*>(smem_raw);                                   // [c_pad]
@@ -66,6 +68,7 @@ __global__ void __launch_bounds__(256) im2col_kernel(const float* __restrict__ x
 // wf[kk][(r*S+s)*C + c] = w[kk][c][r][s]  (bf16, rows padded to c_pad, k padded to k_rows)
 __global__ void pack_weights_im2col_kernel(const float* __restrict__ w, int k, int C, int R, int S, int k_rows, int c_pad,
                                            __nv_bfloat16* __restrict__ wf) {
+    pdl_prologue();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= k_rows * c_pad) return;
     const int j = i % c_pad, kk = i / c_pad;
@@ -80,6 +83,7 @@ __global__ void pack_weights_im2col_kernel(const float* __restrict__ w, int k, i
 // dw[kk][c][r][s] (+)= dwcol[kk][(r*S+s)*C + c]
 __global__ void unpack_wgrad_im2col_kernel(const float* __restrict__ dwcol, int k, int C, int R, int S, int c_pad,
                                            float* __restrict__ dw, int accumulate) {
+    pdl_prologue();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= k * C * R * S) return;
     const int tap = i % (R * S), c = (i / (R * S)) % C, kk = i / (R * S * C);
@@ -108,9 +112,8 @@ int b200seg_im2col_nchw(const float* x, int n, int c, int h, int w, int r, int s
     B200SEG_CHECK(smem <= 48 * 1024, "im2col: window of %zu bytes exceeds shared memory", smem);
     B200SEG_CHECK(oh <= 65535 && n <= 65535, "im2col: grid too large");
     dim3 grid(ceil_div(ow, kTW), oh, n);
-    im2col_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(x, c, h, w, r, s, stride, pad, oh, ow, c_pad,
-                                                                         static_cast<__nv_bfloat16*>(col));
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(im2col_kernel, grid, 256, smem, static_cast<cudaStream_t>(stream), x, c, h, w, r, s, stride, pad, oh, ow, c_pad,
+                                                                         static_cast<__nv_bfloat16*>(col)));
     return 0;
 }
 
@@ -121,9 +124,8 @@ int b200seg_pack_weights_im2col(const float* w, int k, int c, int r, int s, void
     B200SEG_CHECK(w && wf, "pack_weights_im2col: null pointer");
     B200SEG_CHECK(k > 0 && k_rows >= k && c_pad % 8 == 0 && c_pad >= r * s * c, "pack_weights_im2col: bad sizes");
     const int total = k_rows * c_pad;
-    pack_weights_im2col_kernel<<<ceil_div(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        w, k, c, r, s, k_rows, c_pad, static_cast<__nv_bfloat16*>(wf));
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(pack_weights_im2col_kernel, ceil_div(total, 256), 256, 0, static_cast<cudaStream_t>(stream), 
+        w, k, c, r, s, k_rows, c_pad, static_cast<__nv_bfloat16*>(wf)));
     return 0;
 }
 
@@ -134,9 +136,8 @@ int b200seg_unpack_wgrad_im2col(const float* dwcol, int k, int c, int r, int s, 
     B200SEG_CHECK(dwcol && dw, "unpack_wgrad_im2col: null pointer");
     B200SEG_CHECK(k > 0 && c_pad >= r * s * c, "unpack_wgrad_im2col: bad sizes");
     const int total = k * c * r * s;
-    unpack_wgrad_im2col_kernel<<<ceil_div(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(dwcol, k, c, r, s, c_pad,
-                                                                                                   dw, accumulate);
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(unpack_wgrad_im2col_kernel, ceil_div(total, 256), 256, 0, static_cast<cudaStream_t>(stream), dwcol, k, c, r, s, c_pad,
+                                                                                                   dw, accumulate));
     return 0;
 }
 

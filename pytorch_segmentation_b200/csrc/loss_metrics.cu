@@ -3,6 +3,7 @@
 // per-pixel kernels put consecutive threads on consecutive pixels of one class plane (coalesced 128-byte rows)
 // and walk the class dimension in registers.
 #include "common.cuh"
+#include "pdl.cuh"
 #include "vec.cuh"
 
 namespace b200seg {
@@ -13,6 +14,7 @@ namespace {
 __global__ void __launch_bounds__(256) logits_up_fwd_kernel(const float* __restrict__ x, int ct, int h, int w, int nc,
                                                              float* __restrict__ y, int oh, int ow, int64_t total,
                                                              float sh, float sw, int ac) {
+    pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int ox = static_cast<int>(i % ow);
@@ -45,6 +47,7 @@ template <int NCMAX>
 __global__ void __launch_bounds__(128) logits_up_bwd_kernel(const float* __restrict__ dy, int nc, int oh, int ow,
                                                              __nv_bfloat16* __restrict__ dx, int ct, int h, int w,
                                                              int64_t total, float sh, float sw, int ac) {
+    pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int sx = static_cast<int>(i % w);
@@ -96,6 +99,7 @@ constexpr int kWinMax = 16;
 __global__ void __launch_bounds__(512) logits_up_bwd_tiled_kernel(const float* __restrict__ dy, int nc, int oh, int ow,
                                                                    __nv_bfloat16* __restrict__ dx, int ct, int h, int w,
                                                                    float sh, float sw, int ac) {
+    pdl_prologue();
     extern __shared__ __align__(16) unsigned char tile_raw[];
     __nv_bfloat16* tile = reinterpret_cast<__nv_bfloat16*>(tile_raw);     // [128][ct]
     const int tx = threadIdx.x, ty = threadIdx.y;
@@ -148,6 +152,7 @@ __global__ void __launch_bounds__(512) logits_up_bwd_tiled_kernel(const float* _
 __global__ void __launch_bounds__(256) resize_nchw_fwd_kernel(const float* __restrict__ x, int h, int w,
                                                                float* __restrict__ y, int oh, int ow, int64_t total,
                                                                float sh, float sw, int ac) {
+    pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int ox = static_cast<int>(i % ow);
@@ -164,6 +169,7 @@ __global__ void __launch_bounds__(256) resize_nchw_fwd_kernel(const float* __res
 __global__ void __launch_bounds__(256) resize_nchw_bwd_kernel(const float* __restrict__ dy, int oh, int ow,
                                                                float* __restrict__ dx, int h, int w, int64_t total,
                                                                float sh, float sw, int ac) {
+    pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int sx = static_cast<int>(i % w);
@@ -198,6 +204,7 @@ __global__ void __launch_bounds__(256) softmax_ce_kernel(const float* __restrict
                                                           unsigned long long* valid_count, float* __restrict__ dlogits,
                                                           int* status, const float* __restrict__ g_dev,
                                                           const unsigned long long* __restrict__ count_dev) {
+    pdl_prologue();
     // backward form: the upstream gradient and the valid-pixel count live on the device (no host read)
     if (g_dev) grad_scale *= __ldg(g_dev) / static_cast<float>(__ldg(count_dev));
     double lsum = 0.0;
@@ -268,6 +275,7 @@ __global__ void __launch_bounds__(256) softmax_ce_generic_kernel(const float* __
                                                                   float* __restrict__ dlogits, int* status,
                                                                   const float* __restrict__ g_dev,
                                                                   const unsigned long long* __restrict__ count_dev) {
+    pdl_prologue();
     if (g_dev) grad_scale *= __ldg(g_dev) / static_cast<float>(__ldg(count_dev));
     double lsum = 0.0;
     unsigned int lcount = 0;
@@ -320,6 +328,7 @@ __device__ __forceinline__ int argmax_planes(const float* q, int nc, int64_t hw)
 
 __global__ void __launch_bounds__(256) argmax_kernel(const float* __restrict__ logits, int nc, int64_t hw, int64_t total,
                                                       int64_t* __restrict__ pred) {
+    pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int64_t n = i / hw, p = i - n * hw;
@@ -338,6 +347,7 @@ __global__ void __launch_bounds__(kHistThreads) confusion_kernel(const float* __
                                                                   const int64_t* __restrict__ tgt, int nc, int64_t hw,
                                                                   int64_t total, int copies,
                                                                   unsigned long long* __restrict__ cm) {
+    pdl_prologue();
     extern __shared__ unsigned int hist[];
     const int bins = nc * nc;
     for (int b = threadIdx.x; b < bins * copies; b += blockDim.x) hist[b] = 0;
@@ -395,10 +405,9 @@ int b200seg_logits_upsample_fwd(const float* x, int c_total, int n, int h, int w
     B200SEG_CHECK(nc > 0 && nc <= c_total && c_total % 4 == 0, "logits_upsample_fwd: nc %d vs padded %d", nc, c_total);
     B200SEG_CHECK((reinterpret_cast<uintptr_t>(x) & 15) == 0, "logits_upsample_fwd: input not 16-byte aligned");
     const int64_t total = static_cast<int64_t>(n) * oh * ow;
-    logits_up_fwd_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    B200SEG_CUDA(launch_pdl(logits_up_fwd_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream), 
         x, c_total, h, w, nc, y, oh, ow, total, bilinear_scale(h, oh, align_corners), bilinear_scale(w, ow, align_corners),
-        align_corners);
-    B200SEG_LAUNCH_CHECK();
+        align_corners));
     return 0;
 }
 
@@ -418,20 +427,18 @@ int b200seg_logits_upsample_bwd(const float* dy, int n, int nc, int oh, int ow, 
     // x window of a source pixel: at most 2/scale + 3 destination columns
     const bool tiled = sw > 0.f && (2.f / sw + 6.f) <= static_cast<float>(kWinMax) && h <= 65535 && n <= 65535;
     if (tiled) {
-        logits_up_bwd_tiled_kernel<<<dim3(ceil_div(w, 128), h, n), dim3(128, 4), 128 * c_total * 2, st>>>(
-            dy, nc, oh, ow, o, c_total, h, w, sh, sw, align_corners);
-        B200SEG_LAUNCH_CHECK();
+        B200SEG_CUDA(launch_pdl(logits_up_bwd_tiled_kernel, dim3(ceil_div(w, 128), h, n), dim3(128, 4), 128 * c_total * 2, st, 
+            dy, nc, oh, ow, o, c_total, h, w, sh, sw, align_corners));
         return 0;
     }
     if (c_total <= 8)
-        logits_up_bwd_kernel<8><<<grid, 128, 0, st>>>(dy, nc, oh, ow, o, c_total, h, w, total, sh, sw, align_corners);
+        B200SEG_CUDA(launch_pdl(logits_up_bwd_kernel<8>, grid, 128, 0, st, dy, nc, oh, ow, o, c_total, h, w, total, sh, sw, align_corners));
     else if (c_total <= 24)
-        logits_up_bwd_kernel<24><<<grid, 128, 0, st>>>(dy, nc, oh, ow, o, c_total, h, w, total, sh, sw, align_corners);
+        B200SEG_CUDA(launch_pdl(logits_up_bwd_kernel<24>, grid, 128, 0, st, dy, nc, oh, ow, o, c_total, h, w, total, sh, sw, align_corners));
     else if (c_total <= 32)
-        logits_up_bwd_kernel<32><<<grid, 128, 0, st>>>(dy, nc, oh, ow, o, c_total, h, w, total, sh, sw, align_corners);
+        B200SEG_CUDA(launch_pdl(logits_up_bwd_kernel<32>, grid, 128, 0, st, dy, nc, oh, ow, o, c_total, h, w, total, sh, sw, align_corners));
     else
-        logits_up_bwd_kernel<64><<<grid, 128, 0, st>>>(dy, nc, oh, ow, o, c_total, h, w, total, sh, sw, align_corners);
-    B200SEG_LAUNCH_CHECK();
+        B200SEG_CUDA(launch_pdl(logits_up_bwd_kernel<64>, grid, 128, 0, st, dy, nc, oh, ow, o, c_total, h, w, total, sh, sw, align_corners));
     return 0;
 }
 
@@ -441,10 +448,9 @@ int b200seg_resize_nchw_fwd(const float* x, int64_t planes, int h, int w, float*
     clear_error();
     B200SEG_CHECK(x && y && planes > 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "resize_nchw_fwd: bad arguments");
     const int64_t total = planes * oh * ow;
-    resize_nchw_fwd_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    B200SEG_CUDA(launch_pdl(resize_nchw_fwd_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream), 
         x, h, w, y, oh, ow, total, bilinear_scale(h, oh, align_corners), bilinear_scale(w, ow, align_corners),
-        align_corners);
-    B200SEG_LAUNCH_CHECK();
+        align_corners));
     return 0;
 }
 
@@ -454,10 +460,9 @@ int b200seg_resize_nchw_bwd(const float* dy, int64_t planes, int oh, int ow, flo
     clear_error();
     B200SEG_CHECK(dy && dx && planes > 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "resize_nchw_bwd: bad arguments");
     const int64_t total = planes * h * w;
-    resize_nchw_bwd_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    B200SEG_CUDA(launch_pdl(resize_nchw_bwd_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream), 
         dy, oh, ow, dx, h, w, total, bilinear_scale(h, oh, align_corners), bilinear_scale(w, ow, align_corners),
-        align_corners);
-    B200SEG_LAUNCH_CHECK();
+        align_corners));
     return 0;
 }
 
@@ -471,18 +476,17 @@ int launch_softmax_ce(const float* logits, const int64_t* targets, int n, int nc
     unsigned long long* vc = reinterpret_cast<unsigned long long*>(valid_count);
     const unsigned long long* cd = reinterpret_cast<const unsigned long long*>(count_dev);
     if (nc <= 8)
-        softmax_ce_kernel<8><<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum, vc,
-                                                    dlogits, status, g_dev, cd);
+        B200SEG_CUDA(launch_pdl(softmax_ce_kernel<8>, grid, 256, 0, st, logits, targets, nc, hw, total, ignore_index, grad_scale,
+                                loss_sum, vc, dlogits, status, g_dev, cd));
     else if (nc <= 24)
-        softmax_ce_kernel<24><<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum, vc,
-                                                     dlogits, status, g_dev, cd);
+        B200SEG_CUDA(launch_pdl(softmax_ce_kernel<24>, grid, 256, 0, st, logits, targets, nc, hw, total, ignore_index, grad_scale,
+                                loss_sum, vc, dlogits, status, g_dev, cd));
     else if (nc <= 32)
-        softmax_ce_kernel<32><<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum, vc,
-                                                     dlogits, status, g_dev, cd);
+        B200SEG_CUDA(launch_pdl(softmax_ce_kernel<32>, grid, 256, 0, st, logits, targets, nc, hw, total, ignore_index, grad_scale,
+                                loss_sum, vc, dlogits, status, g_dev, cd));
     else
-        softmax_ce_generic_kernel<<<grid, 256, 0, st>>>(logits, targets, nc, hw, total, ignore_index, grad_scale, loss_sum,
-                                                        vc, dlogits, status, g_dev, cd);
-    B200SEG_LAUNCH_CHECK();
+        B200SEG_CUDA(launch_pdl(softmax_ce_generic_kernel, grid, 256, 0, st, logits, targets, nc, hw, total, ignore_index,
+                                grad_scale, loss_sum, vc, dlogits, status, g_dev, cd));
     return 0;
 }
 }  // namespace
@@ -513,8 +517,7 @@ int b200seg_argmax(const float* logits, int n, int nc, int64_t hw, int64_t* pred
     clear_error();
     B200SEG_CHECK(logits && pred && n > 0 && nc > 0 && hw > 0, "argmax: bad arguments");
     const int64_t total = static_cast<int64_t>(n) * hw;
-    argmax_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(logits, nc, hw, total, pred);
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(argmax_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream), logits, nc, hw, total, pred));
     return 0;
 }
 
@@ -527,9 +530,8 @@ int b200seg_confusion(const int64_t* pred, const int64_t* targets, int64_t count
     int copies, grid;
     size_t smem;
     if (hist_launch_geometry(nc, count, &copies, &smem, &grid)) return 1;
-    confusion_kernel<false><<<grid, kHistThreads, smem, static_cast<cudaStream_t>(stream)>>>(
-        nullptr, pred, targets, nc, 1, count, copies, reinterpret_cast<unsigned long long*>(cm));
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(confusion_kernel<false>, grid, kHistThreads, smem, static_cast<cudaStream_t>(stream), 
+        nullptr, pred, targets, nc, 1, count, copies, reinterpret_cast<unsigned long long*>(cm)));
     return 0;
 }
 
@@ -542,9 +544,8 @@ int b200seg_argmax_confusion(const float* logits, const int64_t* targets, int n,
     size_t smem;
     const int64_t total = static_cast<int64_t>(n) * hw;
     if (hist_launch_geometry(nc, total, &copies, &smem, &grid)) return 1;
-    confusion_kernel<true><<<grid, kHistThreads, smem, static_cast<cudaStream_t>(stream)>>>(
-        logits, nullptr, targets, nc, hw, total, copies, reinterpret_cast<unsigned long long*>(cm));
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(confusion_kernel<true>, grid, kHistThreads, smem, static_cast<cudaStream_t>(stream), 
+        logits, nullptr, targets, nc, hw, total, copies, reinterpret_cast<unsigned long long*>(cm)));
     return 0;
 }
 

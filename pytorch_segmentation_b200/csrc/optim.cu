@@ -4,6 +4,7 @@
 // in eager mode, so there is no device-side table to keep in sync; a CUDA-graph capture records them as constants).
 // Both are pure HBM streams: fp32 p/g/m in, p/m out for the update (20 B per element), 4 B in / 4 B out for the pack.
 #include "common.cuh"
+#include "pdl.cuh"
 #include "vec.cuh"
 
 #include <string.h>
@@ -39,6 +40,7 @@ __device__ __forceinline__ float sgd_one(float p, float g, float* m, const SgdCh
 }
 
 __global__ void __launch_bounds__(256) sgd_multi_kernel(const __grid_constant__ SgdChunk c) {
+    pdl_prologue();
     // which tensor does this block belong to (block ranges are a prefix sum; n <= 96: binary search)
     int lo = 0, hi = c.n - 1;
     while (lo < hi) {
@@ -96,6 +98,7 @@ struct PackChunk {
 };
 
 __global__ void __launch_bounds__(256) pack_multi_kernel(const __grid_constant__ PackChunk c) {
+    pdl_prologue();
     int lo = 0, hi = c.n - 1;
     while (lo < hi) {
         const int mid = (lo + hi + 1) >> 1;
@@ -167,8 +170,7 @@ int b200seg_sgd_multi(const b200seg_sgd_desc* descs, int n, float lr, float mome
         }
         c.blk_start[c.n] = blocks;
         if (c.n == 0) continue;
-        sgd_multi_kernel<<<blocks, 256, 0, st>>>(c);
-        B200SEG_LAUNCH_CHECK();
+        B200SEG_CUDA(launch_pdl(sgd_multi_kernel, blocks, 256, 0, st, c));
     }
     return 0;
 }
@@ -204,8 +206,7 @@ int b200seg_pack_weights_multi(const b200seg_pack_desc* descs, int n, b200seg_st
             ++base;
         }
         c.blk_start[c.n] = blocks;
-        pack_multi_kernel<<<blocks, 256, 0, st>>>(c);
-        B200SEG_LAUNCH_CHECK();
+        B200SEG_CUDA(launch_pdl(pack_multi_kernel, blocks, 256, 0, st, c));
     }
     return 0;
 }

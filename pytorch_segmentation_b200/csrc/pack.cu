@@ -1,5 +1,6 @@
 // Layout conversion at the drop-in boundary (fp32 NCHW <-> bf16 NHWC slices) and conv weight packing.
 #include "common.cuh"
+#include "pdl.cuh"
 #include "ptx.cuh"
 
 namespace b200seg {
@@ -9,6 +10,7 @@ namespace {
 // coalesced along channels (NHWC).
 __global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int c, int hw,
                                     int dst_c_total, int dst_c_offset) {
+    pdl_prologue();
     __shared__ float tile[32][33];
     const int n = blockIdx.z;
     const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
@@ -27,6 +29,7 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, __nv_bfloat16
 
 __global__ void nhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, int c, int hw,
                                     int src_c_total, int src_c_offset) {
+    pdl_prologue();
     __shared__ float tile[32][33];
     const int n = blockIdx.z;
     const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
@@ -46,6 +49,7 @@ __global__ void nhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float
 // One thread per packed element; both packings in one launch (grid.y selects which).
 __global__ void pack_weights_kernel(const float* __restrict__ w, int k, int c, int r, int s, __nv_bfloat16* wf,
                                     int k_rows, __nv_bfloat16* wd, int c_rows, int k_cols) {
+    pdl_prologue();
     const int taps = r * s;
     const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
     if (blockIdx.y == 0) {
@@ -84,9 +88,8 @@ int b200seg_nchw_to_nhwc(const float* src, void* dst, int n, int c, int h, int w
     B200SEG_CHECK(dst_c_offset + c <= dst_c_total, "nchw_to_nhwc: slice exceeds buffer");
     const int hw = h * w;
     dim3 grid(ceil_div(hw, 32), ceil_div(c, 32), n), block(32, 8);
-    nchw_to_nhwc_kernel<<<grid, block, 0, static_cast<cudaStream_t>(st)>>>(src, static_cast<__nv_bfloat16*>(dst), c, hw,
-                                                                             dst_c_total, dst_c_offset);
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(nchw_to_nhwc_kernel, grid, block, 0, static_cast<cudaStream_t>(st), src, static_cast<__nv_bfloat16*>(dst), c, hw,
+                                                                             dst_c_total, dst_c_offset));
     return 0;
 }
 
@@ -98,9 +101,8 @@ int b200seg_nhwc_to_nchw(const void* src, float* dst, int n, int c, int h, int w
     B200SEG_CHECK(src_c_offset + c <= src_c_total, "nhwc_to_nchw: slice exceeds buffer");
     const int hw = h * w;
     dim3 grid(ceil_div(hw, 32), ceil_div(c, 32), n), block(32, 8);
-    nhwc_to_nchw_kernel<<<grid, block, 0, static_cast<cudaStream_t>(st)>>>(static_cast<const __nv_bfloat16*>(src), dst, c,
-                                                                             hw, src_c_total, src_c_offset);
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(nhwc_to_nchw_kernel, grid, block, 0, static_cast<cudaStream_t>(st), static_cast<const __nv_bfloat16*>(src), dst, c,
+                                                                             hw, src_c_total, src_c_offset));
     return 0;
 }
 
@@ -117,10 +119,9 @@ int b200seg_pack_weights(const float* w_oihw, int k, int c, int r, int s, void* 
     const long long tmax = tf > td ? tf : td;
     if (tmax == 0) return 0;
     dim3 grid(static_cast<unsigned>((tmax + 255) / 256), 2);
-    pack_weights_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(st)>>>(
+    B200SEG_CUDA(launch_pdl(pack_weights_kernel, grid, 256, 0, static_cast<cudaStream_t>(st), 
         w_oihw, k, c, r, s, static_cast<__nv_bfloat16*>(w_fprop), k_rows, static_cast<__nv_bfloat16*>(w_dgrad), c_rows,
-        k_cols);
-    B200SEG_LAUNCH_CHECK();
+        k_cols));
     return 0;
 }
 

@@ -3,6 +3,7 @@
 // window position (0..8) of each maximum — first maximum in row-major window order, strict '>' like ATen — so the
 // backward is a gather over the <= 4 windows that contain an input pixel, with no atomics.
 #include "common.cuh"
+#include "pdl.cuh"
 #include "vec.cuh"
 
 namespace b200seg {
@@ -12,6 +13,7 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* _
                                                            int w, __nv_bfloat16* __restrict__ y, int y_ct, int y_off,
                                                            uint8_t* __restrict__ idx, int oh, int ow, int groups,
                                                            int64_t total) {
+    pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int g = static_cast<int>(i % groups);
@@ -59,6 +61,7 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const __nv_bfloat16* _
                                                            const uint8_t* __restrict__ idx, int oh, int ow,
                                                            __nv_bfloat16* __restrict__ dx, int dx_ct, int dx_off, int h,
                                                            int w, int groups, int64_t total) {
+    pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int g = static_cast<int>(i % groups);
@@ -110,10 +113,9 @@ int b200seg_maxpool3x3s2_fwd(const void* x, int x_c_total, int x_c_offset, int n
     B200SEG_CHECK((reinterpret_cast<uintptr_t>(idx) & 7) == 0, "maxpool_fwd: index buffer not 8-byte aligned");
     const int oh = (h + 1) / 2, ow = (w + 1) / 2;
     const int64_t total = static_cast<int64_t>(n) * oh * ow * (c / 8);
-    maxpool_fwd_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    B200SEG_CUDA(launch_pdl(maxpool_fwd_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream), 
         static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, h, w, static_cast<__nv_bfloat16*>(y), y_c_total,
-        y_c_offset, idx, oh, ow, c / 8, total);
-    B200SEG_LAUNCH_CHECK();
+        y_c_offset, idx, oh, ow, c / 8, total));
     return 0;
 }
 
@@ -126,10 +128,9 @@ int b200seg_maxpool3x3s2_bwd(const void* dy, int dy_c_total, int dy_c_offset, co
     B200SEG_CHECK(idx && n > 0 && h > 0 && w > 0, "maxpool_bwd: bad arguments");
     const int oh = (h + 1) / 2, ow = (w + 1) / 2;
     const int64_t total = static_cast<int64_t>(n) * h * w * (c / 8);
-    maxpool_bwd_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    B200SEG_CUDA(launch_pdl(maxpool_bwd_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream), 
         static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, idx, oh, ow, static_cast<__nv_bfloat16*>(dx),
-        dx_c_total, dx_c_offset, h, w, c / 8, total);
-    B200SEG_LAUNCH_CHECK();
+        dx_c_total, dx_c_offset, h, w, c / 8, total));
     return 0;
 }
 

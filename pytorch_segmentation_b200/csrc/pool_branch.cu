@@ -6,6 +6,7 @@
 // features, which is small against their mean, so bf16 rounding of the pooled vector is amplified ~10x
 // (DESIGN.md "precision").
 #include "common.cuh"
+#include "pdl.cuh"
 #include "vec.cuh"
 
 namespace b200seg {
@@ -16,6 +17,7 @@ constexpr int kRowChunk = 16;
 // y[n][k] = sum_c x[n][c] * w[k][c];  one warp per output channel k, lanes stride over c
 __global__ void __launch_bounds__(256) linear_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                           float* __restrict__ y, int n, int c, int k) {
+    pdl_prologue();
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= k) return;
     const float* wr = w + static_cast<size_t>(warp) * c;
@@ -43,6 +45,7 @@ __global__ void __launch_bounds__(256) linear_fwd_kernel(const float* __restrict
 constexpr int kBwdDataKChunk = 16;
 __global__ void __launch_bounds__(128) linear_bwd_data_kernel(const float* __restrict__ dy, const float* __restrict__ w,
                                                                float* __restrict__ dx, int n, int c, int k) {
+    pdl_prologue();
     const int cc = blockIdx.x * blockDim.x + threadIdx.x;
     if (cc >= c) return;
     const int k_begin = blockIdx.y * kBwdDataKChunk;
@@ -67,6 +70,7 @@ __global__ void __launch_bounds__(128) linear_bwd_data_kernel(const float* __res
 __global__ void __launch_bounds__(256) linear_bwd_weight_kernel(const float* __restrict__ dy, const float* __restrict__ x,
                                                                  float* __restrict__ dw, int n, int c, int k,
                                                                  int accumulate) {
+    pdl_prologue();
     const size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
     if (i >= static_cast<size_t>(k) * c) return;
     const int kk = static_cast<int>(i / c), cc = static_cast<int>(i % c);
@@ -80,6 +84,7 @@ __global__ void bn_rows_fwd_kernel(const float* __restrict__ x, int n, int k, co
                                    const float* __restrict__ beta, float eps, float momentum, float* running_mean,
                                    float* running_var, int training, int relu, float* __restrict__ y,
                                    float* __restrict__ save_mean, float* __restrict__ save_invstd) {
+    pdl_prologue();
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= k) return;
     float mean, invstd;
@@ -118,6 +123,7 @@ __global__ void bn_rows_bwd_kernel(const float* __restrict__ dy, const float* __
                                    const float* __restrict__ save_mean, const float* __restrict__ save_invstd, int training,
                                    int relu, float* __restrict__ dx, float* __restrict__ dgamma,
                                    float* __restrict__ dbeta) {
+    pdl_prologue();
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= k) return;
     const float mean = save_mean[j], invstd = save_invstd[j];
@@ -151,8 +157,8 @@ int b200seg_linear_f32_fwd(const float* x, const float* w, float* y, int n, int 
     using namespace b200seg;
     clear_error();
     B200SEG_CHECK(x && w && y && n > 0 && c > 0 && k > 0, "linear_f32_fwd: bad arguments");
-    linear_fwd_kernel<<<ceil_div(k * 32, 64), 64, 0, static_cast<cudaStream_t>(st)>>>(x, w, y, n, c, k);   // 2 warps per CTA: fills the SMs
-    B200SEG_LAUNCH_CHECK();
+    // 2 warps per CTA: fills the SMs
+    B200SEG_CUDA(launch_pdl(linear_fwd_kernel, ceil_div(k * 32, 64), 64, 0, static_cast<cudaStream_t>(st), x, w, y, n, c, k));
     return 0;
 }
 
@@ -161,9 +167,8 @@ int b200seg_linear_f32_bwd_data(const float* dy, const float* w, float* dx, int 
     clear_error();
     B200SEG_CHECK(dy && w && dx && n > 0 && c > 0 && k > 0, "linear_f32_bwd_data: bad arguments");
     B200SEG_CUDA(cudaMemsetAsync(dx, 0, sizeof(float) * static_cast<size_t>(n) * c, static_cast<cudaStream_t>(st)));
-    linear_bwd_data_kernel<<<dim3(ceil_div(c, 128), ceil_div(k, kBwdDataKChunk)), 128, 0, static_cast<cudaStream_t>(st)>>>(
-        dy, w, dx, n, c, k);
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(linear_bwd_data_kernel, dim3(ceil_div(c, 128), ceil_div(k, kBwdDataKChunk)), 128, 0,
+                            static_cast<cudaStream_t>(st), dy, w, dx, n, c, k));
     return 0;
 }
 
@@ -173,9 +178,8 @@ int b200seg_linear_f32_bwd_weight(const float* dy, const float* x, float* dw, in
     clear_error();
     B200SEG_CHECK(dy && x && dw && n > 0 && c > 0 && k > 0, "linear_f32_bwd_weight: bad arguments");
     const size_t total = static_cast<size_t>(k) * c;
-    linear_bwd_weight_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(st)>>>(
-        dy, x, dw, n, c, k, accumulate);
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(linear_bwd_weight_kernel, static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(st), 
+        dy, x, dw, n, c, k, accumulate));
     return 0;
 }
 
@@ -186,9 +190,8 @@ int b200seg_bn_rows_fwd(const float* x, int n, int k, const float* gamma, const 
     clear_error();
     B200SEG_CHECK(x && y && save_mean && save_invstd && n > 0 && k > 0, "bn_rows_fwd: bad arguments");
     B200SEG_CHECK(training || (running_mean && running_var), "bn_rows_fwd: eval mode needs running statistics");
-    bn_rows_fwd_kernel<<<ceil_div(k, 128), 128, 0, static_cast<cudaStream_t>(st)>>>(
-        x, n, k, gamma, beta, eps, momentum, running_mean, running_var, training, relu, y, save_mean, save_invstd);
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(bn_rows_fwd_kernel, ceil_div(k, 128), 128, 0, static_cast<cudaStream_t>(st), 
+        x, n, k, gamma, beta, eps, momentum, running_mean, running_var, training, relu, y, save_mean, save_invstd));
     return 0;
 }
 
@@ -199,9 +202,8 @@ int b200seg_bn_rows_bwd(const float* dy, const float* x, int n, int k, const flo
     clear_error();
     B200SEG_CHECK(dy && x && save_mean && save_invstd && dx && dgamma && dbeta && n > 0 && k > 0,
                   "bn_rows_bwd: bad arguments");
-    bn_rows_bwd_kernel<<<ceil_div(k, 128), 128, 0, static_cast<cudaStream_t>(st)>>>(
-        dy, x, n, k, gamma, beta, save_mean, save_invstd, training, relu, dx, dgamma, dbeta);
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(bn_rows_bwd_kernel, ceil_div(k, 128), 128, 0, static_cast<cudaStream_t>(st), 
+        dy, x, n, k, gamma, beta, save_mean, save_invstd, training, relu, dx, dgamma, dbeta));
     return 0;
 }
 

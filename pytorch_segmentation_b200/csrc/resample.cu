@@ -2,6 +2,7 @@
 // gather form, and the H*W reductions / broadcasts of the ASPP image-pooling branch.  HBM-bound: one thread per
 // (pixel, 8-channel group), 128-bit accesses, consecutive threads on consecutive channel groups.
 #include "common.cuh"
+#include "pdl.cuh"
 #include "vec.cuh"
 
 namespace b200seg {
@@ -11,6 +12,7 @@ __global__ void __launch_bounds__(256) upsample_fwd_kernel(const __nv_bfloat16* 
                                                             int w, __nv_bfloat16* __restrict__ y, int y_ct, int y_off,
                                                             int oh, int ow, int groups, int64_t total, float sh, float sw,
                                                             int ac) {
+    pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int g = static_cast<int>(i % groups);
@@ -38,6 +40,7 @@ __global__ void __launch_bounds__(256) upsample_bwd_kernel(const __nv_bfloat16* 
                                                             int oh, int ow, __nv_bfloat16* __restrict__ dx, int dx_ct,
                                                             int dx_off, int h, int w, int groups, int64_t total, float sh,
                                                             float sw, int ac) {
+    pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int g = static_cast<int>(i % groups);
@@ -75,6 +78,7 @@ __global__ void __launch_bounds__(256) upsample_bwd_kernel(const __nv_bfloat16* 
 // acc[n][c] += sum over a chunk of H*W (fp32 atomics), then a tiny kernel scales and rounds to bf16.
 __global__ void __launch_bounds__(256) reduce_hw_kernel(const __nv_bfloat16* __restrict__ x, int x_ct, int x_off, int hw,
                                                          int c, int gpb, int rows, int chunk, float* __restrict__ acc) {
+    pdl_prologue();
     __shared__ float red[256 * 8];
     const int groups = c >> 3;
     const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
@@ -110,6 +114,7 @@ __global__ void __launch_bounds__(256) reduce_hw_kernel(const __nv_bfloat16* __r
 }
 
 __global__ void scale_inplace_kernel(float* __restrict__ y, int64_t total, float scale) {
+    pdl_prologue();
     const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
     if (i < total) y[i] *= scale;
 }
@@ -118,6 +123,7 @@ __global__ void scale_inplace_kernel(float* __restrict__ y, int64_t total, float
 __global__ void __launch_bounds__(256) broadcast_hw_kernel(const float* __restrict__ v, int c, float scale,
                                                             __nv_bfloat16* __restrict__ y, int y_ct, int y_off, int hw,
                                                             int groups, int64_t total, int accumulate) {
+    pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int g = static_cast<int>(i % groups);
@@ -157,12 +163,10 @@ int reduce_hw(const char* what, const void* x, int x_c_total, int x_c_offset, in
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
     const int chunk = round_up(ceil_div(hw, splits), rows);
-    reduce_hw_kernel<<<dim3(ceil_div(hw, chunk), gy, n), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), x_c_total,
-                                                                      x_c_offset, hw, c, gpb, rows, chunk, y);
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(reduce_hw_kernel, dim3(ceil_div(hw, chunk), gy, n), 256, 0, st, static_cast<const __nv_bfloat16*>(x), x_c_total,
+                                                                      x_c_offset, hw, c, gpb, rows, chunk, y));
     if (scale != 1.f) {
-        scale_inplace_kernel<<<static_cast<unsigned>(ceil_div64(total, 256)), 256, 0, st>>>(y, total, scale);
-        B200SEG_LAUNCH_CHECK();
+        B200SEG_CUDA(launch_pdl(scale_inplace_kernel, static_cast<unsigned>(ceil_div64(total, 256)), 256, 0, st, y, total, scale));
     }
     return 0;
 }
@@ -180,11 +184,10 @@ int b200seg_upsample_fwd(const void* x, int x_c_total, int x_c_offset, int n, in
     if (check_slice("upsample_fwd(y)", y, y_c_total, y_c_offset, c)) return 1;
     B200SEG_CHECK(n > 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "upsample_fwd: bad shape");
     const int64_t total = static_cast<int64_t>(n) * oh * ow * (c / 8);
-    upsample_fwd_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    B200SEG_CUDA(launch_pdl(upsample_fwd_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream), 
         static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, h, w, static_cast<__nv_bfloat16*>(y), y_c_total,
         y_c_offset, oh, ow, c / 8, total, bilinear_scale(h, oh, align_corners), bilinear_scale(w, ow, align_corners),
-        align_corners);
-    B200SEG_LAUNCH_CHECK();
+        align_corners));
     return 0;
 }
 
@@ -196,11 +199,10 @@ int b200seg_upsample_bwd(const void* dy, int dy_c_total, int dy_c_offset, int n,
     if (check_slice("upsample_bwd(dx)", dx, dx_c_total, dx_c_offset, c)) return 1;
     B200SEG_CHECK(n > 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "upsample_bwd: bad shape");
     const int64_t total = static_cast<int64_t>(n) * h * w * (c / 8);
-    upsample_bwd_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    B200SEG_CUDA(launch_pdl(upsample_bwd_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream), 
         static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, oh, ow, static_cast<__nv_bfloat16*>(dx), dx_c_total,
         dx_c_offset, h, w, c / 8, total, bilinear_scale(h, oh, align_corners), bilinear_scale(w, ow, align_corners),
-        align_corners);
-    B200SEG_LAUNCH_CHECK();
+        align_corners));
     return 0;
 }
 
@@ -222,9 +224,8 @@ int b200seg_broadcast_hw(const float* v, int n, int c, float scale, void* y, int
     if (check_slice("broadcast_hw(y)", y, y_c_total, y_c_offset, c)) return 1;
     B200SEG_CHECK(v && n > 0 && hw > 0 && (reinterpret_cast<uintptr_t>(v) & 15) == 0, "broadcast_hw: bad arguments");
     const int64_t total = static_cast<int64_t>(n) * hw * (c / 8);
-    broadcast_hw_kernel<<<elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        v, c, scale, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset, hw, c / 8, total, accumulate);
-    B200SEG_LAUNCH_CHECK();
+    B200SEG_CUDA(launch_pdl(broadcast_hw_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream), 
+        v, c, scale, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset, hw, c / 8, total, accumulate));
     return 0;
 }
 
