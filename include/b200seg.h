@@ -65,6 +65,21 @@ int b200seg_pack_weights_im2col(const float* w_oihw, int k, int c, int r, int s,
 int b200seg_unpack_wgrad_im2col(const float* dw_col, int k, int c, int r, int s, int c_pad, float* dw_oihw,
                                 int accumulate, b200seg_stream_t st);
 
+/* Narrow-output 3x3 convolutions (cls_conv, models/deeplabv3plus.py:22,39 and models/unet.py:23,51: 384 -> 21 / 88 -> nc
+ * classes) restated so the wide input is read once instead of once per tap (see csrc/taps.cu):
+ *   fprop  Z = X * Wz (1x1 GEMM, N = r*s*ncp), then b200seg_tap_scatter_add: y[p][k] = bias[k] + sum_tap Z[p+off(tap)][tap*ncp+k]
+ *   bwd    b200seg_tap_gather: col[p][tap*c + ch] = x[p+off(tap)][ch]; dX = col * Wcol (1x1 GEMM); dWcol = col^T X (1x1 wgrad),
+ *          b200seg_unpack_wgrad_taps: dW[k][c][tap] = dWcol[mirror(tap)*ncp + k][c]
+ * b200seg_pack_weights_taps writes Wz [z_rows >= r*s*ncp][c] and Wcol [c_rows >= c][r*s*ncp] (bf16, either may be NULL). */
+int b200seg_tap_gather(const void* x, int x_c_total, int x_c_offset, int c, int n, int h, int w, int r, int s, int dil,
+                       void* col, int col_c_total, b200seg_stream_t st);
+int b200seg_tap_scatter_add(const void* z, int z_c_total, int ncp, int n, int h, int w, int r, int s, int dil,
+                            const float* bias, float* y, b200seg_stream_t st);
+int b200seg_pack_weights_taps(const float* w_oihw, int k, int c, int r, int s, int ncp, void* wz, int z_rows, void* wcol,
+                              int c_rows, b200seg_stream_t st);
+int b200seg_unpack_wgrad_taps(const float* dw_col, int k, int c, int r, int s, int ncp, float* dw_oihw, int accumulate,
+                              b200seg_stream_t st);
+
 /* All conv weights of a model re-packed in one or two launches (after an optimizer step every weight is stale at
  * once): per tensor the same packings as b200seg_pack_weights, or — im2col != 0 — as b200seg_pack_weights_im2col. */
 typedef struct b200seg_pack_desc {

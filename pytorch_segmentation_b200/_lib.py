@@ -66,6 +66,10 @@ PROTOTYPES = {
     'b200seg_im2col_nchw': (c_int, [_P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _I, _P]),
     'b200seg_pack_weights_im2col': (c_int, [_P, _I, _I, _I, _I, _P, _I, _I, _P]),
     'b200seg_unpack_wgrad_im2col': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _P]),
+    'b200seg_tap_gather': (c_int, [_P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P, _I, _P]),
+    'b200seg_tap_scatter_add': (c_int, [_P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
+    'b200seg_pack_weights_taps': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _P, _I, _P]),
+    'b200seg_unpack_wgrad_taps': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _P]),
     'b200seg_pack_weights_multi': (c_int, [POINTER(PackDesc), _I, _P]),
     'b200seg_sgd_multi': (c_int, [POINTER(SgdDesc), _I, _F, _F, _F, _F, _I, _I, _F, _P]),
     'b200seg_conv_fprop': (c_int, [_I, _I, _I, _I, POINTER(ConvSrc), POINTER(ConvOut), _P]),

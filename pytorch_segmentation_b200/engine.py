@@ -194,6 +194,85 @@ class PackedIm2colWeight:
         return self
 
 
+class _GemmView:
+    """What conv_fprop / conv_dgrad read from a packed weight, for a 1x1 GEMM over a re-arranged operand."""
+    __slots__ = ('wf', 'wd', 'k_rows', 'c_rows', 'k_cols', 'r', 's', 'k', 'c')
+
+    def __init__(self, wf=None, wd=None, k_rows=0, c_rows=0, k_cols=0, k=0, c=0):
+        self.wf, self.wd, self.k_rows, self.c_rows, self.k_cols, self.k, self.c = wf, wd, k_rows, c_rows, k_cols, k, c
+        self.r = self.s = 1
+
+
+class PackedTapWeight:
+    """Packings of a narrow-output 3x3 conv weight (cls_conv) for the taps-as-channels form (csrc/taps.cu):
+    ``fprop`` = Wz [taps*ncp][c] (the 1x1 GEMM that produces all per-tap partial class maps at once), ``dgrad`` =
+    Wcol [c][taps*ncp] (the 1x1 GEMM over the tap-gathered gradient)."""
+    __slots__ = ('k', 'c', 'r', 's', 'ncp', 'zc', 'wz', 'wcol', 'key', '_shape', 'fprop', 'dgrad')
+    MAX_COLS = 512
+
+    def __init__(self):
+        self.key = None
+        self.wz = self.wcol = self._shape = None
+
+    @staticmethod
+    def applies(conv):
+        k, c, r, s = conv.weight.shape
+        ncp = _round_up(k, 8)
+        return (r, s) == (3, 3) and conv.stride == (1, 1) and c % 8 == 0 and ncp <= 32 and c >= 4 * ncp
+
+    def update(self, w):
+        _require_cuda(w, 'conv weight')
+        key = (w.data_ptr(), w._version, tuple(w.shape), WEIGHT_EPOCH)
+        if key == self.key:
+            return self
+        src = w.detach()
+        if src.dtype != torch.float32 or not src.is_contiguous():
+            src = src.float().contiguous()
+        k, c, r, s = src.shape
+        if self._shape != (k, c, r, s, src.device):
+            self.k, self.c, self.r, self.s = k, c, r, s
+            self.ncp = _round_up(k, 8)
+            self.zc = r * s * self.ncp
+            self.wz = torch.empty((1, self.zc, c), dtype=BF16, device=src.device)
+            self.wcol = torch.empty((1, c, self.zc), dtype=BF16, device=src.device)
+            self.fprop = _GemmView(wf=self.wz, k_rows=self.zc, k=self.zc, c=c)
+            self.dgrad = _GemmView(wd=self.wcol, c_rows=c, k_cols=self.zc, k=self.zc, c=c)
+            self._shape = (k, c, r, s, src.device)
+        _lib.check(_lib.load().b200seg_pack_weights_taps(src.data_ptr(), k, c, r, s, self.ncp, self.wz.data_ptr(), self.zc,
+                                                         self.wcol.data_ptr(), c, _stream()), 'pack_weights_taps')
+        _lib.count_launch()
+        self.key = key
+        return self
+
+
+def tap_gather(x, r, s, dil):
+    """col[p][tap*c + ch] = x[p + off(tap)][ch] -> Act with r*s*c channels."""
+    col = Act.empty(x.n, x.h, x.w, r * s * x.c, x.t.device)
+    _lib.check(_lib.load().b200seg_tap_gather(x.ptr, x.ct, x.c_off, x.c, x.n, x.h, x.w, r, s, dil, col.ptr, col.ct,
+                                              _stream()), 'tap_gather')
+    _lib.count_launch()
+    return col
+
+
+def tap_scatter_add(z, ncp, r, s, dil, bias=None):
+    """y[p][k] = bias[k] + sum_tap z[p + off(tap)][tap*ncp + k] -> fp32 NHWC tensor [n, h, w, ncp]."""
+    assert z.c_off == 0 and z.c == z.ct
+    y = torch.empty((z.n, z.h, z.w, ncp), dtype=torch.float32, device=z.t.device)
+    _lib.check(_lib.load().b200seg_tap_scatter_add(z.ptr, z.ct, ncp, z.n, z.h, z.w, r, s, dil,
+                                                   bias.data_ptr() if bias is not None else None, y.data_ptr(), _stream()),
+               'tap_scatter_add')
+    _lib.count_launch()
+    return y
+
+
+def unpack_wgrad_taps(dwcol, pw):
+    dw = torch.empty((pw.k, pw.c, pw.r, pw.s), dtype=torch.float32, device=dwcol.device)
+    _lib.check(_lib.load().b200seg_unpack_wgrad_taps(dwcol.data_ptr(), pw.k, pw.c, pw.r, pw.s, pw.ncp, dw.data_ptr(), 0,
+                                                     _stream()), 'unpack_wgrad_taps')
+    _lib.count_launch()
+    return dw
+
+
 def pack_all(entries, need_dgrad=True):
     """entries: iterable of (PackedWeight | PackedIm2colWeight, weight parameter).  Re-packs every stale one in a
     single multi-tensor launch (after an optimizer step that is all of them) — the per-layer ``update`` calls that
@@ -681,7 +760,7 @@ def _timed(name, fn):
     return wrapper
 
 
-for _name in ('as_act', 'grad_like', 'im2col', 'unpack_wgrad_im2col', 'bn_stats', 'bn_finalize', 'bn_eval_affine',
+for _name in ('as_act', 'grad_like', 'im2col', 'unpack_wgrad_im2col', 'tap_gather', 'tap_scatter_add', 'unpack_wgrad_taps', 'bn_stats', 'bn_finalize', 'bn_eval_affine',
               'bn_apply', 'bn_backward', 'relu_bwd_add', 'grad_add_masked', 'maxpool_fwd', 'maxpool_bwd', 'upsample_fwd', 'upsample_bwd',
               'gap_fwd', 'sum_hw', 'broadcast_hw', 'linear_f32_fwd', 'linear_f32_bwd', 'bn_rows_fwd', 'bn_rows_bwd',
               'channel_sum', 'logits_upsample_fwd', 'logits_upsample_bwd', 'resize_nchw_fwd', 'resize_nchw_bwd',

@@ -26,14 +26,14 @@ class DeepLabV3Plus(nn.Module):
         initialize_weights(self.project)
         initialize_weights(self.cls_conv)
         self.num_classes = num_classes
-        self._cls_packed = E.PackedWeight()
+        self._cls_packed = make_cls_packed(self.cls_conv)
         self._pack_entries = None
 
     def head_tensors(self):
         return self.project.tensors() + self.aspp.tensors() + [self.cls_conv.weight, self.cls_conv.bias]
 
     def _packed_weights(self):
-        return [(self._cls_packed, self.cls_conv.weight)]
+        return [] if isinstance(self._cls_packed, E.PackedTapWeight) else [(self._cls_packed, self.cls_conv.weight)]
 
     def forward(self, x):
         # every conv weight that went stale (all of them after an optimizer step) is re-packed in one launch
@@ -48,15 +48,26 @@ class DeepLabV3Plus(nn.Module):
         return _DeepLabHeadFn.apply(self, low, high, *self.head_tensors())
 
 
+def make_cls_packed(conv):
+    """Narrow-output 3x3 convs take the taps-as-channels form (engine.PackedTapWeight, csrc/taps.cu)."""
+    return E.PackedTapWeight() if E.PackedTapWeight.applies(conv) else E.PackedWeight()
+
+
 def cls_conv_forward(conv, packed, x, save):
     """Plain 3x3 conv with bias, no BN/act (models/deeplabv3plus.py:22,39; models/unet.py:23,51):
     NHWC bf16 slice -> NHWC fp32 class map padded to a multiple of 8 channels."""
     nc = conv.out_channels
     ncp = (nc + 7) // 8 * 8
-    pw = packed.update(conv.weight, need_dgrad=save)
     bias = torch.zeros((ncp,), dtype=torch.float32, device=x.t.device)
     if conv.bias is not None:
         bias[:nc].copy_(conv.bias.detach())
+    if isinstance(packed, E.PackedTapWeight):
+        # the input is read once: one 1x1 GEMM produces the nine per-tap partial class maps, a gather sums them
+        pw = packed.update(conv.weight)
+        z = E.Act.empty(x.n, x.h, x.w, pw.zc, x.t.device)
+        E.conv_fprop([(x, pw.fprop, 1)], z)
+        return E.tap_scatter_add(z, ncp, pw.r, pw.s, conv.dilation[0], bias=bias)
+    pw = packed.update(conv.weight, need_dgrad=save)
     out = torch.empty((x.n, x.h, x.w, ncp), dtype=torch.float32, device=x.t.device)
     E.conv_fprop_f32([(x, pw, conv.dilation[0])], out, ncp, bias=bias)
     return out
@@ -65,8 +76,16 @@ def cls_conv_forward(conv, packed, x, save):
 def cls_conv_backward(conv, packed, x, dlr, dx):
     """dlr: Act grad of the padded class map (bf16).  Returns [dW, dbias]; writes dx if given."""
     nc = conv.out_channels
-    dw = E.conv_wgrad(dlr, x, nc, conv.kernel_size[0], conv.kernel_size[1], conv.dilation[0])
     db = E.channel_sum(dlr)[:nc]
+    if isinstance(packed, E.PackedTapWeight):
+        pw = packed.update(conv.weight)
+        col = E.tap_gather(dlr, pw.r, pw.s, conv.dilation[0])            # [p][tap*ncp + k] = dY[p + off(tap)][k]
+        dwcol = E.conv_wgrad(col, x, pw.zc, 1, 1, 1)
+        dw = E.unpack_wgrad_taps(dwcol, pw)
+        if dx is not None:
+            E.conv_dgrad([(col, pw.dgrad, 1)], dx)
+        return [dw, db]
+    dw = E.conv_wgrad(dlr, x, nc, conv.kernel_size[0], conv.kernel_size[1], conv.dilation[0])
     if dx is not None:
         E.conv_dgrad([(dlr, packed, conv.dilation[0])], dx)
     return [dw, db]

@@ -11,7 +11,7 @@ import torch.nn as nn
 from .. import engine as E
 from ..backbones import mobilenet_v2
 from ..modules import ConvNormAct, initialize_weights
-from .deeplabv3plus import cls_conv_backward, cls_conv_forward
+from .deeplabv3plus import cls_conv_backward, cls_conv_forward, make_cls_packed
 
 
 class UNet(nn.Module):
@@ -23,7 +23,7 @@ class UNet(nn.Module):
         initialize_weights(self.up_convs)
         initialize_weights(self.cls_conv)
         self.num_classes = num_classes
-        self._cls_packed = E.PackedWeight()
+        self._cls_packed = make_cls_packed(self.cls_conv)
         self._pack_entries = None
 
     def head_tensors(self):
@@ -33,7 +33,7 @@ class UNet(nn.Module):
         return ts + [self.cls_conv.weight, self.cls_conv.bias]
 
     def _packed_weights(self):
-        return [(self._cls_packed, self.cls_conv.weight)]
+        return [] if isinstance(self._cls_packed, E.PackedTapWeight) else [(self._cls_packed, self.cls_conv.weight)]
 
     def forward(self, x):
         # every conv weight that went stale (all of them after an optimizer step) is re-packed in one launch

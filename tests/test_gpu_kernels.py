@@ -262,6 +262,38 @@ def test_grad_add_masked(E):
     assert rel_err(from_act(a), bf16_round(dx + dy * (y > 0))) < 1e-6
 
 
+@pytest.mark.parametrize('n,h,w,c,k', [(2, 24, 40, 384, 21), (1, 17, 23, 88, 2), (2, 16, 16, 128, 19)])
+def test_narrow_output_conv_taps_form(E, n, h, w, c, k):
+    # cls_conv through the taps-as-channels form: Z GEMM + scatter-add forward; tap gather + 1x1 dgrad / wgrad backward
+    from pytorch_segmentation_b200.models.deeplabv3plus import cls_conv_backward, cls_conv_forward, make_cls_packed
+    g = torch.Generator().manual_seed(c + k)
+    conv = torch.nn.Conv2d(c, k, 3, padding=1).cuda()
+    with torch.no_grad():
+        conv.weight.copy_(bf16_round(torch.randn(k, c, 3, 3, generator=g) * 0.05))
+        conv.bias.copy_(torch.randn(k, generator=g))
+    packed = make_cls_packed(conv)
+    assert isinstance(packed, E.PackedTapWeight)
+    x = bf16_round(torch.randn(n, c, h, w, generator=g))
+    xa = nhwc(x)
+    y = cls_conv_forward(conv, packed, xa, True)                      # fp32 NHWC, padded to 8 channels
+    ncp = (k + 7) // 8 * 8
+    assert tuple(y.shape) == (n, h, w, ncp)
+    xr = x.clone().requires_grad_(True)
+    wr = conv.weight.detach().cpu().clone().requires_grad_(True)
+    ref = F.conv2d(xr, wr, conv.bias.detach().cpu(), padding=1)
+    assert rel_err(y[..., :k].permute(0, 3, 1, 2), ref) < TOL
+    assert float(y[..., k:].abs().max()) == 0.0 if ncp > k else True
+    gy = bf16_round(torch.randn(n, k, h, w, generator=g))
+    ref.backward(gy)
+    gyp = torch.zeros(n, ncp, h, w)
+    gyp[:, :k] = gy
+    dx = E.Act.empty(n, h, w, c, 'cuda')
+    dw, db = cls_conv_backward(conv, packed, xa, nhwc(gyp), dx)
+    assert rel_err(from_act(dx), xr.grad) < TOL
+    assert dw.shape == conv.weight.shape and rel_err(dw, wr.grad) < TOL
+    assert rel_err(db, gy.sum((0, 2, 3))) < TOL
+
+
 def test_conv_epilogue_scale_bias_relu_into_slice(E):
     g = torch.Generator().manual_seed(5)
     n, h, w, c, k = 2, 16, 16, 64, 128
