@@ -107,6 +107,11 @@ typedef struct b200seg_sgd_desc {
 int b200seg_sgd_multi(const b200seg_sgd_desc* descs, int n, float lr, float momentum, float dampening, float weight_decay,
                       int nesterov, int first_step, float grad_scale, b200seg_stream_t st);
 
+/* dst <- src for many fp32 tensors in one launch: the gradients of a bucket move into their slots of the flat
+ * all-reduce buffer (parallel.GradBucketer; the DDP exchange of train.py:108-119).  desc.p = destination, desc.g =
+ * source, desc.m unused. */
+int b200seg_copy_multi(const b200seg_sgd_desc* descs, int n, b200seg_stream_t st);
+
 /* ---- convolution: tcgen05 implicit GEMM ------------------------------------------------------------------ */
 /* One input of a "same"-padded convolution (stride 1 or 2): activation slice + packed weights + filter geometry. */
 typedef struct b200seg_conv_src {

@@ -72,6 +72,7 @@ PROTOTYPES = {
     'b200seg_unpack_wgrad_taps': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _P]),
     'b200seg_pack_weights_multi': (c_int, [POINTER(PackDesc), _I, _P]),
     'b200seg_sgd_multi': (c_int, [POINTER(SgdDesc), _I, _F, _F, _F, _F, _I, _I, _F, _P]),
+    'b200seg_copy_multi': (c_int, [POINTER(SgdDesc), _I, _P]),
     'b200seg_conv_fprop': (c_int, [_I, _I, _I, _I, POINTER(ConvSrc), POINTER(ConvOut), _P]),
     'b200seg_conv_dgrad': (c_int, [_I, _I, _I, _I, POINTER(ConvSrc), POINTER(ConvOut), _P]),
     'b200seg_conv_wgrad_workspace': (c_size_t, [POINTER(WgradDesc)]),

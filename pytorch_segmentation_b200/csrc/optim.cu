@@ -84,6 +84,36 @@ __global__ void __launch_bounds__(256) sgd_multi_kernel(const __grid_constant__ 
     }
 }
 
+// dst <- src for many fp32 tensors at once (gradients into their slots of a flat all-reduce bucket): descriptors are
+// b200seg_sgd_desc with p = destination, g = source, m unused
+struct CopyChunk {
+    b200seg_sgd_desc t[kSgdTensors];
+    int blk_start[kSgdTensors + 1];
+    int n;
+};
+
+__global__ void __launch_bounds__(256) copy_multi_kernel(const __grid_constant__ CopyChunk c) {
+    pdl_prologue();
+    int lo = 0, hi = c.n - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (c.blk_start[mid] <= static_cast<int>(blockIdx.x)) lo = mid; else hi = mid - 1;
+    }
+    const b200seg_sgd_desc& t = c.t[lo];
+    const int64_t begin = static_cast<int64_t>(blockIdx.x - c.blk_start[lo]) * kSgdElemsPerBlock;
+    const int64_t end = begin + kSgdElemsPerBlock < t.numel ? begin + kSgdElemsPerBlock : t.numel;
+    float* dst = t.p;
+    const float* src = t.g;
+    if (((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 15) == 0) {
+        const int64_t vend = begin + ((end - begin) & ~int64_t(3));
+        for (int64_t i = begin + threadIdx.x * 4; i < vend; i += 256 * 4)
+            *reinterpret_cast<float4*>(dst + i) = __ldcs(reinterpret_cast<const float4*>(src + i));
+        for (int64_t i = vend + threadIdx.x; i < end; i += 256) dst[i] = src[i];
+    } else {
+        for (int64_t i = begin + threadIdx.x; i < end; i += 256) dst[i] = src[i];
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // weight packing, all conv weights of a model in one go (same element mapping as pack_weights_kernel /
 // pack_weights_im2col_kernel in pack.cu / im2col.cu)
@@ -171,6 +201,32 @@ int b200seg_sgd_multi(const b200seg_sgd_desc* descs, int n, float lr, float mome
         c.blk_start[c.n] = blocks;
         if (c.n == 0) continue;
         B200SEG_CUDA(launch_pdl(sgd_multi_kernel, blocks, 256, 0, st, c));
+    }
+    return 0;
+}
+
+int b200seg_copy_multi(const b200seg_sgd_desc* descs, int n, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(descs && n > 0, "copy_multi: no tensors");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    for (int base = 0; base < n;) {
+        CopyChunk c;
+        memset(&c, 0, sizeof(c));
+        int blocks = 0;
+        while (base < n && c.n < kSgdTensors) {
+            const b200seg_sgd_desc& d = descs[base];
+            B200SEG_CHECK(d.p && d.g && d.numel >= 0, "copy_multi: tensor %d has null pointers", base);
+            ++base;
+            if (d.numel == 0) continue;
+            c.t[c.n] = d;
+            c.blk_start[c.n] = blocks;
+            blocks += static_cast<int>(ceil_div64(d.numel, kSgdElemsPerBlock));
+            ++c.n;
+        }
+        c.blk_start[c.n] = blocks;
+        if (c.n == 0) continue;
+        B200SEG_CUDA(launch_pdl(copy_multi_kernel, blocks, 256, 0, st, c));
     }
     return 0;
 }

@@ -55,6 +55,7 @@ class GradBucketer:
             self._buckets.append((flat, slots))
             self._pending.append(len(slots))
         self._ready = [0] * len(self._buckets)
+        self._moves = [[] for _ in self._buckets]
 
     @property
     def num_buckets(self):
@@ -70,13 +71,32 @@ class GradBucketer:
         flat = self._buckets[bi][0]
         view = flat[off:off + n].view_as(p)
         if p.grad.data_ptr() != view.data_ptr():
-            view.copy_(p.grad)
+            g = p.grad
+            if g.is_cuda and g.dtype == torch.float32 and g.is_contiguous():
+                self._moves[bi].append((view, g))       # moved by ONE multi-tensor launch when the bucket is complete
+            else:
+                view.copy_(g)
             p.grad = view
         self._ready[bi] += 1
         if self._ready[bi] == self._pending[bi]:
             self._launch(bi)
 
+    def _flush_moves(self, bi):
+        moves = self._moves[bi]
+        if not moves:
+            return
+        import ctypes
+        from . import _lib
+        arr = (_lib.SgdDesc * len(moves))()
+        for i, (dst, src) in enumerate(moves):
+            arr[i] = _lib.SgdDesc(dst.data_ptr(), src.data_ptr(), None, src.numel())
+        _lib.check(_lib.load().b200seg_copy_multi(arr, len(moves), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)),
+                   'copy_multi')
+        _lib.count_launch((len(moves) + 95) // 96)
+        self._moves[bi] = []
+
     def _launch(self, bi):
+        self._flush_moves(bi)
         if self.world > 1:
             self._handles.append((bi, dist.all_reduce(self._buckets[bi][0], op=dist.ReduceOp.SUM, group=self.group,
                                                       async_op=True)))
@@ -89,6 +109,8 @@ class GradBucketer:
             if self._ready[bi] != self._pending[bi] and self._ready[bi] >= 0 and self.enabled:
                 if bi not in launched and self._ready[bi] > 0:
                     self._launch(bi)
+        for bi in range(len(self._buckets)):
+            self._flush_moves(bi)
         for bi, h in self._handles:
             h.wait()
             if self.average and self.world > 1:

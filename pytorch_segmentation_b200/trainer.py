@@ -25,6 +25,8 @@ class TrainStep:
         self._graph = None
         self._x = self._t = self._loss = self._side = None
         self._calls = 0
+        self._stage = None
+        self._staged = False
         self.launches_per_step = None          # libb200seg launches recorded in the captured step
 
     # the eager step ------------------------------------------------------------------------------------------
@@ -84,6 +86,44 @@ class TrainStep:
         # caches that whatever they hold is stale for any later eager call (eval after training)
         E.WEIGHT_EPOCH += 1
         return self._loss
+
+    # host-side input pipeline -------------------------------------------------------------------------------
+    def prefetch(self, x_host, t_host):
+        """Starts the host -> device copy of a batch (pinned host tensors) on a copy stream; it overlaps whatever the
+        compute stream is doing.  ``step_prefetched()`` consumes it.  This is the DataLoader(pin_memory=True) +
+        ``.to(device, non_blocking=True)`` hand-off of train.py:28-31 made explicit and double-buffered."""
+        dev = next(self.model.parameters()).device
+        if self._stage is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+            self._stage = (torch.empty(x_host.shape, dtype=x_host.dtype, device=dev),
+                           torch.empty(t_host.shape, dtype=t_host.dtype, device=dev))
+            self._stage_free = torch.cuda.Event()
+            self._copy_done = torch.cuda.Event()
+            self._stage_free.record(torch.cuda.current_stream())
+        with torch.cuda.stream(self._copy_stream):
+            self._copy_stream.wait_event(self._stage_free)      # the previous batch has left the staging buffers
+            self._stage[0].copy_(x_host, non_blocking=True)
+            self._stage[1].copy_(t_host, non_blocking=True)
+            self._copy_done.record(self._copy_stream)
+        self._staged = True
+
+    def step_prefetched(self, next_batch=None):
+        """One step on the batch staged by ``prefetch``; ``next_batch=(x_host, t_host)`` starts the copy of the following
+        batch before this step's kernels are enqueued, so the copy runs under the step."""
+        if not getattr(self, '_staged', False):
+            raise RuntimeError('TrainStep.step_prefetched(): no batch staged — call prefetch(x_host, t_host) first')
+        cur = torch.cuda.current_stream()
+        cur.wait_event(self._copy_done)
+        if self._x is None:
+            self._x, self._t = torch.empty_like(self._stage[0]), torch.empty_like(self._stage[1])
+            self._side = torch.cuda.Stream()
+        self._x.copy_(self._stage[0], non_blocking=True)          # device -> device, ~30 us: frees the staging pair
+        self._t.copy_(self._stage[1], non_blocking=True)
+        self._stage_free.record(cur)
+        self._staged = False
+        if next_batch is not None:
+            self.prefetch(*next_batch)
+        return self(self._x, self._t)
 
     @property
     def static_inputs(self):

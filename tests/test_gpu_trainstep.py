@@ -77,3 +77,27 @@ def test_graph_step_rejects_other_shapes(P):
     s(x, t)
     with pytest.raises(ValueError):
         s(torch.randn(2, 3, 96, 96).cuda(), torch.randint(0, 3, (2, 96, 96)).cuda())
+
+
+def test_prefetched_step_equals_direct_step(P):
+    """prefetch()/step_prefetched(): the staged host batch is the one the step consumes (eval-mode forward is
+    deterministic, so the loss of a zero-lr step must match a direct call on the same data exactly)."""
+    nc, n, h, w = 3, 2, 64, 64
+    m = _make(P, nc, 5).eval()           # eval-mode BN: no batch statistics, no atomics -> bit-reproducible forward
+    s = P.TrainStep(m, P.optim.SGD(m.parameters(), lr=0.0), graph=False)
+    g = torch.Generator().manual_seed(9)
+    hosts = [(torch.randn(n, 3, h, w, generator=g).pin_memory(), torch.randint(0, nc, (n, h, w), generator=g).pin_memory())
+             for _ in range(3)]
+    with pytest.raises(RuntimeError):
+        s.step_prefetched()
+    s.prefetch(*hosts[0])
+    got = []
+    for i in range(3):
+        nxt = hosts[i + 1] if i + 1 < len(hosts) else None
+        got.append(float(s.step_prefetched(next_batch=nxt)))
+    m2 = _make(P, nc, 5).eval()
+    s2 = P.TrainStep(m2, P.optim.SGD(m2.parameters(), lr=0.0), graph=False)
+    want = [float(s2(x.cuda(), t.cuda())) for x, t in hosts]
+    for a, b in zip(got, want):
+        assert abs(a - b) <= 1e-4 * max(1.0, abs(b)), (got, want)
+    assert len(set(round(v, 3) for v in got)) > 1          # three different batches were consumed
