@@ -265,7 +265,11 @@ def tap_scatter_add(z, ncp, r, s, dil, bias=None):
     return y
 
 
-def unpack_wgrad_taps(dwcol, pw):
+def unpack_wgrad_taps(dwcol, pw, lane=False):
+    return on_wgrad_lane(_unpack_wgrad_taps, dwcol, pw, keep=(dwcol,)) if lane else _unpack_wgrad_taps(dwcol, pw)
+
+
+def _unpack_wgrad_taps(dwcol, pw):
     dw = torch.empty((pw.k, pw.c, pw.r, pw.s), dtype=torch.float32, device=dwcol.device)
     _lib.check(_lib.load().b200seg_unpack_wgrad_taps(dwcol.data_ptr(), pw.k, pw.c, pw.r, pw.s, pw.ncp, dw.data_ptr(), 0,
                                                      _stream()), 'unpack_wgrad_taps')
@@ -316,8 +320,13 @@ def im2col(x, r, s, stride, pad):
     return col
 
 
-def unpack_wgrad_im2col(dwcol, pw):
-    """fp32 [k, c_pad, 1, 1] gradient of the gathered-matrix GEMM -> fp32 OIHW gradient of the original filter."""
+def unpack_wgrad_im2col(dwcol, pw, lane=False):
+    """fp32 [k, c_pad, 1, 1] gradient of the gathered-matrix GEMM -> fp32 OIHW gradient of the original filter
+    (on the weight-gradient lane, behind the wgrad that produced ``dwcol``)."""
+    return on_wgrad_lane(_unpack_wgrad_im2col, dwcol, pw, keep=(dwcol,)) if lane else _unpack_wgrad_im2col(dwcol, pw)
+
+
+def _unpack_wgrad_im2col(dwcol, pw):
     dw = torch.empty((pw.k, pw.cin, pw.kr, pw.ks), dtype=torch.float32, device=dwcol.device)
     _lib.check(_lib.load().b200seg_unpack_wgrad_im2col(dwcol.data_ptr(), pw.k, pw.cin, pw.kr, pw.ks, pw.c, dw.data_ptr(), 0,
                                                        _stream()), 'unpack_wgrad_im2col')
@@ -397,8 +406,72 @@ def conv_dgrad(srcs, dx):
           dx.ptr, dx.ct, dx.c_off, dx.c, False, None, None, False, None)
 
 
-def conv_wgrad(dy, x, k_out, r, s, dil, dw=None, stride=1):
-    """dW fp32 OIHW [k_out, x.c, r, s] = sum_pixels dy (x) shifted x."""
+# ------------------------------------------------------------------------------------------------
+# the weight-gradient lane
+# ------------------------------------------------------------------------------------------------
+# In backward the critical path is  BN-backward -> dgrad -> BN-backward -> ...  (HBM-bound passes alternating with
+# tensor-core GEMMs); a layer's weight gradient hangs off that chain and nothing downstream needs it before the
+# optimizer.  conv_wgrad therefore runs on a second stream forked after the BN backward that produced its operand:
+# the tcgen05 wgrad of layer i overlaps the bandwidth-bound BN backward of layer i-1 (complementary resources), and
+# small GEMMs that leave SMs idle overlap each other.  Every autograd Function joins the lane before it returns.
+# Operands stay referenced until the join so the caching allocator cannot recycle them under the side stream.
+# B200SEG_WGRAD_LANE=0 turns it off (wgrad then runs in line).
+import os as _os
+
+_LANE_ON = _os.environ.get('B200SEG_WGRAD_LANE', '1') != '0'
+_lanes = {}
+
+
+class _Lane:
+    def __init__(self, device):
+        self.stream = torch.cuda.Stream(device=device)
+        self.keep = []
+        self.dirty = False
+
+
+def _lane(device):
+    if not _LANE_ON:
+        return None
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    ln = _lanes.get(key)
+    if ln is None:
+        ln = _lanes[key] = _Lane(device)
+    return ln
+
+
+def on_wgrad_lane(fn, *args, keep=()):
+    """Runs ``fn(*args)`` on the weight-gradient lane, ordered after everything enqueued so far on the current stream."""
+    dev = next((t.device for t in keep if isinstance(t, torch.Tensor)), None)
+    ln = _lane(dev) if dev is not None else None
+    if ln is None:
+        return fn(*args)
+    ln.stream.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(ln.stream):
+        out = fn(*args)
+    ln.keep.extend(keep)
+    ln.dirty = True
+    return out
+
+
+def join_wgrad_lane():
+    """The current stream waits for the weight-gradient lane; called before an autograd Function hands its gradients back."""
+    for ln in _lanes.values():
+        if ln.dirty:
+            torch.cuda.current_stream().wait_stream(ln.stream)
+            ln.keep.clear()
+            ln.dirty = False
+
+
+def conv_wgrad(dy, x, k_out, r, s, dil, dw=None, stride=1, lane=False):
+    """dW fp32 OIHW [k_out, x.c, r, s] = sum_pixels dy (x) shifted x.  ``lane=True`` (the models' backward passes)
+    enqueues it on the weight-gradient lane: the result may then be touched again only through ``on_wgrad_lane`` or
+    after ``join_wgrad_lane()``."""
+    if not lane:
+        return _conv_wgrad(dy, x, k_out, r, s, dil, dw, stride)
+    return on_wgrad_lane(_conv_wgrad, dy, x, k_out, r, s, dil, dw, stride, keep=(dy.t, x.t) + ((dw,) if dw is not None else ()))
+
+
+def _conv_wgrad(dy, x, k_out, r, s, dil, dw=None, stride=1):
     desc = WgradDesc()
     assert (x.n, x.h, x.w) == (dy.n, dy.h * stride, dy.w * stride), 'conv_wgrad: size mismatch'
     desc.n, desc.h, desc.w = dy.n, dy.h, dy.w

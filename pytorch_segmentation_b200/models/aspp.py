@@ -151,4 +151,5 @@ class _ASPPFn(torch.autograd.Function):
         g = E.Act.empty(da.n, da.h, da.w, ctx.mod.inplanes, dout.device)
         pgrads = ctx.mod.run_backward(ctx.rec, da, g)
         dx = E.grad_like(ctx.x, g) if ctx.needs_input_grad[1] else None
+        E.join_wgrad_lane()
         return (None, dx) + tuple(pgrads)

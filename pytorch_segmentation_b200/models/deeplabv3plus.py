@@ -73,19 +73,20 @@ def cls_conv_forward(conv, packed, x, save):
     return out
 
 
-def cls_conv_backward(conv, packed, x, dlr, dx):
-    """dlr: Act grad of the padded class map (bf16).  Returns [dW, dbias]; writes dx if given."""
+def cls_conv_backward(conv, packed, x, dlr, dx, lane=False):
+    """dlr: Act grad of the padded class map (bf16).  Returns [dW, dbias]; writes dx if given.  ``lane``: put the
+    weight gradient on the weight-gradient lane (the caller joins it)."""
     nc = conv.out_channels
     db = E.channel_sum(dlr)[:nc]
     if isinstance(packed, E.PackedTapWeight):
         pw = packed.update(conv.weight)
         col = E.tap_gather(dlr, pw.r, pw.s, conv.dilation[0])            # [p][tap*ncp + k] = dY[p + off(tap)][k]
-        dwcol = E.conv_wgrad(col, x, pw.zc, 1, 1, 1)
-        dw = E.unpack_wgrad_taps(dwcol, pw)
+        dwcol = E.conv_wgrad(col, x, pw.zc, 1, 1, 1, lane=lane)
+        dw = E.unpack_wgrad_taps(dwcol, pw, lane=lane)
         if dx is not None:
             E.conv_dgrad([(col, pw.dgrad, 1)], dx)
         return [dw, db]
-    dw = E.conv_wgrad(dlr, x, nc, conv.kernel_size[0], conv.kernel_size[1], conv.dilation[0])
+    dw = E.conv_wgrad(dlr, x, nc, conv.kernel_size[0], conv.kernel_size[1], conv.dilation[0], lane=lane)
     if dx is not None:
         E.conv_dgrad([(dlr, packed, conv.dilation[0])], dx)
     return [dw, db]
@@ -122,7 +123,7 @@ class _DeepLabHeadFn(torch.autograd.Function):
         dout = dout.contiguous().float()
         dlr = E.logits_upsample_bwd(dout, h4, w4, ncp, align_corners=True)
         ddec = E.Act.empty(n, h4, w4, 384, dev)
-        cls_grads = cls_conv_backward(m.cls_conv, m._cls_packed, dec, dlr, ddec)
+        cls_grads = cls_conv_backward(m.cls_conv, m._cls_packed, dec, dlr, ddec, lane=True)
         # project branch
         draw, proj_grads = m.project.run_backward_params(rec_proj, ddec.slice(256, 128))
         dlow = None
@@ -136,4 +137,5 @@ class _DeepLabHeadFn(torch.autograd.Function):
         g = E.Act.empty(n, h16, w16, 2048, dev) if ctx.needs_input_grad[2] else None
         aspp_grads = m.aspp.run_backward(rec_aspp, daspp, g)
         dhigh = E.grad_like(ctx.high, g) if g is not None else None
+        E.join_wgrad_lane()
         return (None, dlow, dhigh) + tuple(proj_grads + aspp_grads + cls_grads)

@@ -97,7 +97,7 @@ class _UNetHeadFn(torch.autograd.Function):
         dout = dout.contiguous().float()
         dlr = E.logits_upsample_bwd(dout, u.h, u.w, ncp, align_corners=True)
         du = E.Act.empty(n, u.h, u.w, u.c, dev)
-        cls_grads = cls_conv_backward(m.cls_conv, m._cls_packed, u, dlr, du)
+        cls_grads = cls_conv_backward(m.cls_conv, m._cls_packed, u, dlr, du, lane=True)
         dcat = E.Act.empty(n, cats[2].h, cats[2].w, cats[2].c, dev)
         E.upsample_bwd(du, dcat, align_corners=True)
         skip_inputs = (x4, x3, x2)
@@ -124,4 +124,5 @@ class _UNetHeadFn(torch.autograd.Function):
                 dcat = dx
         dx5 = E.grad_like(x5, dcat) if ctx.needs_input_grad[4] else None
         grads = pgrads[0] + pgrads[1] + pgrads[2] + cls_grads
+        E.join_wgrad_lane()
         return (None, dskips[2], dskips[1], dskips[0], dx5) + tuple(grads)

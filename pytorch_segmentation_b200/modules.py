@@ -98,7 +98,7 @@ class ConvNormAct(nn.Sequential):
         x, raw, vec, training = rec
         draw = E.Act.empty(raw.n, raw.h, raw.w, raw.c, raw.t.device)
         dgamma, dbeta = E.bn_backward(dout, raw, draw, vec, self.relu, training)
-        dw = E.conv_wgrad(draw, x, self[0].out_channels, self.ksize, self.ksize, self.dilation)
+        dw = E.conv_wgrad(draw, x, self[0].out_channels, self.ksize, self.ksize, self.dilation, lane=True)
         return draw, [dw, dgamma, dbeta]
 
     def dgrad_src(self, draw):
@@ -129,6 +129,7 @@ class _ConvNormActFn(torch.autograd.Function):
             g = E.Act.empty(da.n, da.h, da.w, mod[0].in_channels, dout.device)
             E.conv_dgrad([mod.dgrad_src(draw)], g)
             dx = E.grad_like(ctx.x, g)
+        E.join_wgrad_lane()
         return (None, dx) + tuple(pgrads)
 
 

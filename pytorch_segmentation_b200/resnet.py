@@ -57,7 +57,7 @@ class _Unit:
         return raw, vec
 
     def wgrad(self, draw, x):
-        return E.conv_wgrad(draw, x, self.cout, self.k, self.k, self.dil, stride=self.stride)
+        return E.conv_wgrad(draw, x, self.cout, self.k, self.k, self.dil, stride=self.stride, lane=True)
 
     def dgrad_src(self, draw):
         return (draw, self.packed, self.dil, self.stride)
@@ -251,8 +251,8 @@ class ResNet50Features(nn.Module):
         draw0 = E.Act.empty(raw0.n, raw0.h, raw0.w, raw0.c, raw0.t.device)
         dgamma, dbeta = E.bn_backward(da0, raw0, draw0, v0, True, training)
         # dW of the stem = the 1x1 wgrad over the gathered matrix, scattered back to OIHW
-        dwcol = E.conv_wgrad(draw0, col, raw0.c, 1, 1, 1)
-        grads[self.conv1.weight] = E.unpack_wgrad_im2col(dwcol, pw0)
+        dwcol = E.conv_wgrad(draw0, col, raw0.c, 1, 1, 1, lane=True)
+        grads[self.conv1.weight] = E.unpack_wgrad_im2col(dwcol, pw0, lane=True)
         grads[self.bn1.weight], grads[self.bn1.bias] = dgamma, dbeta
         return grads
 
@@ -271,6 +271,7 @@ class _ResNetFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, *gfeats):
         grads = ctx.mod.run_backward(ctx.saved, list(gfeats))
+        E.join_wgrad_lane()
         ctx.saved = None
         out = []
         for p, need in zip(ctx.params, ctx.needs_input_grad[2:]):
