@@ -219,6 +219,9 @@ def run_b200(args):
 
     # per-launch CUDA-event timing of the tcgen05 conv kernels over a few more steps (the events sit on the
     # launching stream; kept out of the throughput loop above so the headline has no instrumentation in it)
+    # per-launch timing runs with the weight-gradient lane off: concurrent kernels would share SMs with the launch
+    # being timed and understate it
+    lane_was, E._LANE_ON = E._LANE_ON, False
     E.PROFILE = []
     E.OP_PROFILE = [] if args.detail else None
     prof_steps = min(args.steps, 3)
@@ -227,6 +230,7 @@ def run_b200(args):
     torch.cuda.synchronize()
     rec, E.PROFILE = E.PROFILE, None
     op_rec, E.OP_PROFILE = E.OP_PROFILE, None
+    E._LANE_ON = lane_was
     agg = {}
     for tag, flops, e0, e1 in rec:
         a = agg.setdefault(tag, [0.0, 0.0, 0])

@@ -202,6 +202,13 @@ int b200seg_relu_bwd_add(void* dx, int dx_c_total, int dx_c_offset, const void* 
 int b200seg_grad_add_masked(void* dx, int dx_c_total, int dx_c_offset, const void* dy, int dy_c_total, int dy_c_offset,
                             const void* y, int y_c_total, int y_c_offset, const void* xin, int xin_c_total,
                             int xin_c_offset, int c, int64_t pixels, b200seg_stream_t st);
+/* y = relu?(x0 + ... + x_{n-1}), 1 <= n <= 4 bf16 NHWC slices: the multi-resolution fuse of an HRModule
+ * (models/hrnet.py:240-249) in one pass. */
+int b200seg_add_n_relu(int n_in, const void* const* x, const int* x_c_total, const int* x_c_offset, void* y, int y_c_total,
+                       int y_c_offset, int c, int64_t pixels, int relu, b200seg_stream_t st);
+/* dx = dy * [y > 0]: the gradient through a ReLU whose output y was stored (fuse ReLU, residual-block ReLU). */
+int b200seg_relu_bwd(const void* dy, int dy_c_total, int dy_c_offset, const void* y, int y_c_total, int y_c_offset,
+                     void* dx, int dx_c_total, int dx_c_offset, int c, int64_t pixels, b200seg_stream_t st);
 /* eval mode (test.py:16, inference.py:24): scale/shift from the running statistics; feeds the conv epilogue so
  * Conv+BN+ReLU is one kernel.  save_mean/save_invstd (optional) receive the running mean and 1/sqrt(var+eps). */
 int b200seg_bn_eval_affine(int c, const float* gamma, const float* beta, const float* running_mean,

@@ -17,6 +17,8 @@ CASES = {
     # BASELINE.json config 3: ASPP(2048, 256, [6,12,18]) on 32x32
     'aspp_full': dict(cin=2048, cout=256, rates=(6, 12, 18), n=2, h=32, w=32, seed=5),
     'aspp_small': dict(cin=128, cout=64, rates=(2, 4, 6), n=3, h=16, w=24, seed=6),
+    # BASELINE.json config 5 architecture (HRNet 19-class, W = 2H) at a size the CPU reference finishes in seconds
+    'hrnet_small': dict(kind='hrnet', nc=19, n=2, h=64, w=128, seed=8),
 }
 
 SAMPLE = 384

@@ -68,6 +68,37 @@ def model_case(ref, name):
     _save(name, out)
 
 
+def hrnet_case(ref, name):
+    """The UNMODIFIED reference HRNet (models/hrnet.py) on seeded inputs with the seeded state of
+    oracle/hrnet_restatement.make_state: eval logits, train logits / loss, gradients of a spread of parameters, and the
+    BN running statistics after one training step."""
+    from oracle import hrnet_restatement as H
+    c = CASES[name]
+    model = ref.HRNet(c['nc'])
+    model.load_state_dict(H.make_state(c['nc'], seed=c['seed']))
+    x, t = make_inputs(c)
+    out = {}
+    model.eval()
+    with torch.no_grad():
+        y = model(x)
+    out.update(summarize('eval_logits', y))
+    out['eval_loss'] = float(ref.compute_loss(y, t, model))
+    out['eval_argmax_sample'] = y.max(1)[1].flatten()[::97].numpy()
+    model.train()
+    y = model(x)
+    loss = ref.compute_loss(y, t, model)
+    loss.backward()
+    out.update(summarize('train_logits', y.detach()))
+    out['train_loss'] = float(loss)
+    names = [k for k, _ in model.named_parameters()]
+    for k in names[::max(1, len(names) // 24)] + ['final_layer.weight', 'final_layer.bias', 'stem.0.0.weight']:
+        out.update(summarize('grad:' + k, dict(model.named_parameters())[k].grad))
+    sd = model.state_dict()
+    for k in [k for k in sd if 'running_' in k][::16]:
+        out['stat:' + k] = sd[k].numpy()
+    _save(name, out)
+
+
 def aspp_case(ref, name):
     """ASPP standalone: SURVEY §8c fixture (i) and a small all-values variant."""
     c = CASES[name]
@@ -188,6 +219,7 @@ def main():
     model_case(ref, 'unet_320')
     model_case(ref, 'deeplab_small')
     model_case(ref, 'deeplab_512')
+    hrnet_case(ref, 'hrnet_small')
 
 
 if __name__ == '__main__':

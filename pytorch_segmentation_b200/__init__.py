@@ -4,11 +4,11 @@ model / loss / metric API.  See DESIGN.md and INTEGRATION.md at the repository r
 """
 from . import _lib
 from .evaluate import test
-from .models import ASPP, ASPPPooling, DeepLabV3Plus, UNet
+from .models import ASPP, ASPPPooling, DeepLabV3Plus, HRNet, UNet
 from .modules import ConvNormAct, initialize_weights
 from . import optim
 from .trainer import TrainStep
 from .utils.utils import compute_loss, compute_metrics
 
-__all__ = ['ASPP', 'ASPPPooling', 'DeepLabV3Plus', 'UNet', 'ConvNormAct', 'initialize_weights', 'compute_loss',
+__all__ = ['ASPP', 'ASPPPooling', 'DeepLabV3Plus', 'HRNet', 'UNet', 'ConvNormAct', 'initialize_weights', 'compute_loss',
            'compute_metrics', 'test', 'TrainStep', 'optim']

@@ -386,6 +386,59 @@ __global__ void __launch_bounds__(256) grad_add_masked_kernel(__nv_bfloat16* __r
     }
 }
 
+// y = relu?(x0 + x1 + ... ) over up to 4 bf16 NHWC slices — the multi-resolution fuse of an HRModule
+// (models/hrnet.py:240-249: y = y + fuse(x[j]) ...; relu(y))
+struct AddN {
+    const __nv_bfloat16* x[4];
+    int ct[4], off[4];
+    int n;
+};
+__global__ void __launch_bounds__(256) add_n_relu_kernel(const AddN a, __nv_bfloat16* __restrict__ y, int y_ct, int y_off,
+                                                          int groups, int64_t total, int relu) {
+    pdl_prologue();
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int g = static_cast<int>(i % groups);
+        const int64_t p = i / groups;
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (k < a.n) {
+                float f[8];
+                unpack8(ldcs128(a.x[k] + p * a.ct[k] + a.off[k] + g * 8), f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] += f[j];
+            }
+        }
+        if (relu) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] = fmaxf(acc[j], 0.f);
+        }
+        st128(y + p * y_ct + y_off + g * 8, pack8(acc));
+    }
+}
+
+// dx = dy * [y > 0]
+__global__ void __launch_bounds__(256) relu_bwd_kernel(const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off,
+                                                        const __nv_bfloat16* __restrict__ y, int y_ct, int y_off,
+                                                        __nv_bfloat16* __restrict__ dx, int dx_ct, int dx_off, int groups,
+                                                        int64_t total) {
+    pdl_prologue();
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int g = static_cast<int>(i % groups);
+        const int64_t p = i / groups;
+        float d[8], m[8];
+        unpack8(ldcs128(dy + p * dy_ct + dy_off + g * 8), d);
+        unpack8(ldcs128(y + p * y_ct + y_off + g * 8), m);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) d[j] = m[j] > 0.f ? d[j] : 0.f;
+        st128(dx + p * dx_ct + dx_off + g * 8, pack8(d));
+    }
+}
+
 // dgamma = red1, dbeta = red0 (optionally accumulated into existing .grad)
 __global__ void bn_param_grad_kernel(const float* __restrict__ red, int c, float* dgamma, float* dbeta, int accumulate) {
     pdl_prologue();
@@ -490,6 +543,46 @@ int b200seg_relu_bwd_add(void* dx, int dx_c_total, int dx_c_offset, const void* 
     B200SEG_CUDA(launch_pdl(relu_bwd_add_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream), 
         static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, static_cast<const __nv_bfloat16*>(dy), dy_c_total,
         dy_c_offset, static_cast<const __nv_bfloat16*>(y), y_c_total, y_c_offset, c / 8, total));
+    return 0;
+}
+
+int b200seg_add_n_relu(int n_in, const void* const* x, const int* x_c_total, const int* x_c_offset, void* y, int y_c_total,
+                       int y_c_offset, int c, int64_t pixels, int relu, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(n_in >= 1 && n_in <= 4 && x && x_c_total && x_c_offset && pixels > 0, "add_n_relu: 1..4 inputs");
+    if (check_slice("add_n_relu(y)", y, y_c_total, y_c_offset, c)) return 1;
+    AddN a;
+    a.n = n_in;
+    for (int i = 0; i < 4; ++i) {
+        a.x[i] = nullptr;
+        a.ct[i] = a.off[i] = 0;
+    }
+    for (int i = 0; i < n_in; ++i) {
+        if (check_slice("add_n_relu(x)", x[i], x_c_total[i], x_c_offset[i], c)) return 1;
+        a.x[i] = static_cast<const __nv_bfloat16*>(x[i]);
+        a.ct[i] = x_c_total[i];
+        a.off[i] = x_c_offset[i];
+    }
+    const int64_t total = pixels * (c / 8);
+    B200SEG_CUDA(launch_pdl(add_n_relu_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream), a,
+                            static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset, c / 8, total, relu));
+    return 0;
+}
+
+int b200seg_relu_bwd(const void* dy, int dy_c_total, int dy_c_offset, const void* y, int y_c_total, int y_c_offset,
+                     void* dx, int dx_c_total, int dx_c_offset, int c, int64_t pixels, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    if (check_slice("relu_bwd(dy)", dy, dy_c_total, dy_c_offset, c)) return 1;
+    if (check_slice("relu_bwd(y)", y, y_c_total, y_c_offset, c)) return 1;
+    if (check_slice("relu_bwd(dx)", dx, dx_c_total, dx_c_offset, c)) return 1;
+    B200SEG_CHECK(pixels > 0, "relu_bwd: bad arguments");
+    const int64_t total = pixels * (c / 8);
+    B200SEG_CUDA(launch_pdl(relu_bwd_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream),
+                            static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset,
+                            static_cast<const __nv_bfloat16*>(y), y_c_total, y_c_offset, static_cast<__nv_bfloat16*>(dx),
+                            dx_c_total, dx_c_offset, c / 8, total));
     return 0;
 }
 

@@ -587,6 +587,24 @@ def grad_add_masked(dx, dy=None, y=None, xin=None):
     _lib.count_launch()
 
 
+def add_n_relu(xs, y, relu=True):
+    """y = relu?(sum of 1..4 Acts)"""
+    n = len(xs)
+    ptrs = (ctypes.c_void_p * n)(*[a.ptr for a in xs])
+    cts = (ctypes.c_int * n)(*[a.ct for a in xs])
+    offs = (ctypes.c_int * n)(*[a.c_off for a in xs])
+    _lib.check(_lib.load().b200seg_add_n_relu(n, ptrs, cts, offs, y.ptr, y.ct, y.c_off, y.c, y.pixels, int(relu), _stream()),
+               'add_n_relu')
+    _lib.count_launch()
+
+
+def relu_bwd(dy, y, dx):
+    """dx = dy * [y > 0]"""
+    _lib.check(_lib.load().b200seg_relu_bwd(dy.ptr, dy.ct, dy.c_off, y.ptr, y.ct, y.c_off, dx.ptr, dx.ct, dx.c_off, dx.c,
+                                            dx.pixels, _stream()), 'relu_bwd')
+    _lib.count_launch()
+
+
 def maxpool_fwd(x):
     """3x3 stride-2 pad-1 max pool -> (y: Act, idx: uint8 tensor of window positions)"""
     oh, ow = (x.h + 1) // 2, (x.w + 1) // 2

@@ -21,13 +21,13 @@ _DEFAULT = object()
 
 class ConvNormAct(nn.Sequential):
     def __init__(self, inplanes, planes, ksize=3, stride=1, groups=1, dilation=1, activate=_DEFAULT):
-        if stride != 1 or groups != 1:
+        if stride not in (1, 2) or groups != 1 or (stride == 2 and dilation != 1):
             raise NotImplementedError(
-                'ConvNormAct(stride=%r, groups=%r): the sm_100a implicit-GEMM path covers the stride-1 dense convs of '
-                'the ASPP / DeepLabV3+ decoder / UNet up-blocks; there is no cuDNN fallback' % (stride, groups))
+                'ConvNormAct(stride=%r, groups=%r, dilation=%r): the sm_100a implicit-GEMM path covers dense convs of '
+                'stride 1 (any dilation) and stride 2; there is no cuDNN fallback' % (stride, groups, dilation))
         if ksize not in (1, 3):
             raise NotImplementedError('ConvNormAct(ksize=%r): only 1x1 and 3x3 filters' % (ksize,))
-        layers = [nn.Conv2d(inplanes, planes, ksize, stride=1, padding=((ksize - 1) // 2) * dilation,
+        layers = [nn.Conv2d(inplanes, planes, ksize, stride=stride, padding=((ksize - 1) // 2) * dilation,
                             dilation=dilation, bias=False),
                   nn.BatchNorm2d(planes)]
         if activate is _DEFAULT:
@@ -38,8 +38,13 @@ class ConvNormAct(nn.Sequential):
             layers.append(activate)
         super().__init__(*layers)
         self.relu = activate is not None
-        self.ksize, self.dilation = ksize, dilation
-        self._packed = E.PackedWeight()
+        self.ksize, self.dilation, self.stride = ksize, dilation, stride
+        # stride-1 convs over >= 8 channels are composed by the heads through run_forward / run_backward_params; stride 2
+        # (HRNet transitions and fuse layers, models/hrnet.py:213-224,320-324) and 3-channel stems (models/hrnet.py:260)
+        # go through the op-level node in ops.py
+        self._chain = stride == 1 and inplanes % 8 == 0
+        self._packed = E.PackedWeight() if self._chain else None
+        self._op_state = None
 
     # ---- parameter plumbing ---------------------------------------------------------------
     @property
@@ -51,7 +56,7 @@ class ConvNormAct(nn.Sequential):
         return self[1]
 
     def _packed_weights(self):
-        return [(self._packed, self[0].weight)]
+        return [(self._packed, self[0].weight)] if self._chain else []
 
     def tensors(self):
         """The differentiable leaves in the order the heads pass them through autograd."""
@@ -106,7 +111,12 @@ class ConvNormAct(nn.Sequential):
 
     # ---- standalone nn.Module use ---------------------------------------------------------------
     def forward(self, x):
-        return _ConvNormActFn.apply(self, x, *self.tensors())
+        if self._chain:
+            return _ConvNormActFn.apply(self, x, *self.tensors())
+        from . import ops
+        if self._op_state is None:
+            self._op_state = ops.ConvBNState(self[0])
+        return ops.conv_bn(x, self[0], self[1], self.relu, self._op_state)
 
 
 class _ConvNormActFn(torch.autograd.Function):

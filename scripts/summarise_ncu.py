@@ -3,8 +3,8 @@
 
   python scripts/summarise_ncu.py gpurun_out/launches_r01.csv [--steps N] > profiles/r01_launches.md
 
-The bench command profiled runs N identical steps (3 warm-up + 2 timed + 2 e2e warm-up + 2 e2e + 2 profiled
-= 11 by default); totals are divided by N.  ncu times are cold-cache and serialised: read SHARES.
+The bench command profiled runs N identical steps (3 warm-up + 1 enqueue-timing + 2 timed + 2 e2e warm-up + 2 e2e + 2 profiled
+= 12 by default); totals are divided by N.  ncu times are cold-cache and serialised: read SHARES.
 """
 import csv
 import re
@@ -14,7 +14,7 @@ from collections import defaultdict
 
 def main():
     path = sys.argv[1]
-    steps = 11
+    steps = 12
     if '--steps' in sys.argv:
         steps = int(sys.argv[sys.argv.index('--steps') + 1])
     rows = []

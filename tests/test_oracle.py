@@ -144,3 +144,65 @@ def test_restatement_equals_reference_live():
     fp = torch.tensor([2., 0., 3.])
     for a, b in zip(ref.compute_metrics(tp.clone(), fn.clone(), fp.clone()), R.compute_metrics(tp, fn, fp)):
         assert torch.equal(a, b)
+
+
+# ---------------------------------------------------------------------------------------------------
+# HRNet restatement (oracle/hrnet_restatement.py) vs the golden vectors from the unmodified reference and vs the live
+# reference
+# ---------------------------------------------------------------------------------------------------
+def _hrnet_run(training):
+    from oracle import hrnet_restatement as H
+    c = G.CASES['hrnet_small']
+    sd = H.make_state(c['nc'], seed=c['seed'])
+    for k, v in sd.items():
+        if v.is_floating_point() and 'running_' not in k:
+            v.requires_grad_(True)
+    x, t = G.make_inputs(c)
+    if not training:
+        with torch.no_grad():
+            y = H.hrnet(sd, x, training=False)
+        return sd, y, R.compute_loss(y, t)
+    y = H.hrnet(sd, x, training=True)
+    loss = R.compute_loss(y, t)
+    loss.backward()
+    return sd, y, loss
+
+
+def test_hrnet_restatement_golden():
+    gold = G.load('hrnet_small')
+    sd, y, loss = _hrnet_run(False)
+    assert G.summary_error(gold, 'eval_logits', y)[0] < FP32_TOL
+    assert abs(float(loss) - float(gold['eval_loss'])) < FP32_TOL * abs(float(gold['eval_loss']))
+    assert np.array_equal(y.max(1)[1].flatten()[::97].numpy(), gold['eval_argmax_sample'])
+    sd, y, loss = _hrnet_run(True)
+    assert G.summary_error(gold, 'train_logits', y.detach())[0] < FP32_TOL
+    assert abs(float(loss) - float(gold['train_loss'])) < FP32_TOL * abs(float(gold['train_loss']))
+    checked = 0
+    for k in gold:
+        if k.startswith('grad:') and k.endswith('/shape'):
+            name = k[len('grad:'):-len('/shape')]
+            assert G.summary_error(gold, 'grad:' + name, sd[name].grad)[0] < 5e-3, name
+            checked += 1
+        elif k.startswith('stat:'):
+            assert np.allclose(sd[k[len('stat:'):]].numpy(), gold[k], rtol=1e-4, atol=1e-6), k
+    assert checked >= 20
+
+
+@pytest.mark.skipif(not reference_loader.available(), reason='reference tree not present')
+def test_hrnet_restatement_equals_reference_live():
+    from oracle import hrnet_restatement as H
+    ref = reference_loader.load()
+    c = G.CASES['hrnet_small']
+    state = H.make_state(c['nc'], seed=c['seed'])
+    model = ref.HRNet(c['nc'])
+    model.load_state_dict(state)          # strict: the enumerated keys ARE the reference's
+    x = torch.randn(1, 3, 64, 64, generator=torch.Generator().manual_seed(1))
+    model.eval()
+    with torch.no_grad():
+        assert torch.allclose(model(x), H.hrnet({k: v.clone() for k, v in state.items()}, x), rtol=1e-4, atol=1e-4)
+    # the drop-in module exposes the same keys and shapes, so reference checkpoints load into it unchanged
+    from pytorch_segmentation_b200.models.hrnet import HRNet
+    mine = HRNet(c['nc'])
+    ours, theirs = mine.state_dict(), model.state_dict()
+    assert list(ours.keys()) == list(theirs.keys())
+    assert all(ours[k].shape == theirs[k].shape for k in ours)
