@@ -68,9 +68,15 @@ def test_no_cpu_fallback():
 
 def test_unsupported_convnormact_is_an_error_not_a_fallback():
     with pytest.raises(NotImplementedError):
-        P.ConvNormAct(8, 8, 3, 2)
+        P.ConvNormAct(8, 8, 3, 3)                      # stride 3
+    with pytest.raises(NotImplementedError):
+        P.ConvNormAct(8, 8, 3, 2, dilation=2)          # strided and dilated
+    with pytest.raises(NotImplementedError):
+        P.ConvNormAct(8, 8, 3, 1, groups=8)            # depthwise
     with pytest.raises(NotImplementedError):
         P.ConvNormAct(8, 8, 5)
+    assert P.ConvNormAct(8, 8, 3, 2)[0].stride == (2, 2)          # HRNet transitions / fuse layers (models/hrnet.py:213-224)
+    assert P.ConvNormAct(3, 64, 3, 2, activate=None)[0].in_channels == 3   # HRNet stem (models/hrnet.py:260)
     with pytest.raises(NotImplementedError):
         P.ConvNormAct(8, 8, activate=torch.nn.Sigmoid())
     P.ConvNormAct(8, 8, 1, activate=None)
