@@ -41,18 +41,22 @@ class SGD(torch.optim.Optimizer):
                 g = p.grad
                 if g is None:
                     continue
-                if not p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous():
-                    raise RuntimeError('pytorch_segmentation_b200.optim.SGD: parameters must be contiguous fp32 CUDA '
-                                       'tensors (got %s %s); there is no CPU fallback' % (p.device, p.dtype))
+                # the update is elementwise over the storage: any dense layout works (contiguous, or the channels_last
+                # conv weights of a torchvision backbone) as long as p, g and the momentum buffer share it
+                dense = p.is_contiguous() or (p.dim() == 4 and p.is_contiguous(memory_format=torch.channels_last))
+                if not p.is_cuda or p.dtype != torch.float32 or not dense:
+                    raise RuntimeError('pytorch_segmentation_b200.optim.SGD: parameters must be dense fp32 CUDA '
+                                       'tensors (got %s %s strides %s); there is no CPU fallback'
+                                       % (p.device, p.dtype, tuple(p.stride())))
                 if g.is_sparse or g.dtype != torch.float32:
                     raise RuntimeError('pytorch_segmentation_b200.optim.SGD: gradients must be dense fp32')
-                if not g.is_contiguous():
-                    g = g.contiguous()
+                if g.stride() != p.stride():
+                    g = torch.empty_like(p).copy_(g)
                 if momentum != 0.0:
                     st = self.state[p]
                     buf = st.get('momentum_buffer')
                     if buf is None:
-                        st['momentum_buffer'] = buf = torch.empty_like(p, memory_format=torch.contiguous_format)
+                        st['momentum_buffer'] = buf = torch.empty_like(p)          # preserves p's layout
                         without_buf.append((p, g, buf))
                     else:
                         with_buf.append((p, g, buf))

@@ -223,6 +223,9 @@ def test_sgd_multi_matches_torch_sgd(E, momentum, nesterov, wd):
     g = torch.Generator().manual_seed(11)
     shapes = [(64, 3, 7, 7), (21,), (256, 64, 3, 3), (1,), (2048, 513), (7, 5, 3)] + [(16,)] * 120
     ref = [torch.nn.Parameter(torch.randn(*sh, generator=g).cuda()) for sh in shapes]
+    # a channels_last conv weight (torchvision backbones under .to(memory_format=channels_last))
+    ref.append(torch.nn.Parameter(torch.randn(32, 16, 3, 3, generator=g).cuda().contiguous(memory_format=torch.channels_last)))
+    shapes.append((32, 16, 3, 3))
     ours = [torch.nn.Parameter(p.detach().clone()) for p in ref]
     o_ref = torch.optim.SGD(ref, lr=0.05, momentum=momentum, nesterov=nesterov, weight_decay=wd)
     o_ours = optim.SGD(ours, lr=0.05, momentum=momentum, nesterov=nesterov, weight_decay=wd)
