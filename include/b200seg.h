@@ -233,6 +233,12 @@ int b200seg_bn_bwd_reduce_masked(const void* dy, int dy_c_total, int dy_c_offset
                                  int x_c_offset, int c, int64_t pixels, const float* scale, const float* shift,
                                  const float* save_mean, const float* save_invstd, int relu, float* red, const void* mask,
                                  int mask_c_total, int mask_c_offset, b200seg_stream_t st);
+/* Same, ACCUMULATING into a `red` the caller zeroed (one memset for all BatchNorms of a backward pass instead of one
+ * per layer: a memset node between two kernels also breaks their programmatic-dependent-launch overlap). */
+int b200seg_bn_bwd_reduce_acc(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total, int x_c_offset,
+                              int c, int64_t pixels, const float* scale, const float* shift, const float* save_mean,
+                              const float* save_invstd, int relu, float* red, const void* mask, int mask_c_total,
+                              int mask_c_offset, b200seg_stream_t st);
 int b200seg_bn_bwd_apply_masked(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total,
                                 int x_c_offset, void* dx, int dx_c_total, int dx_c_offset, int c, int64_t pixels,
                                 const float* scale, const float* shift, const float* save_mean, const float* save_invstd,
@@ -305,6 +311,9 @@ int b200seg_resize_nchw_bwd(const float* dy, int64_t planes, int oh, int ow, flo
 int b200seg_softmax_ce(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
                        float grad_scale, double* loss_sum, int64_t* valid_count, float* dlogits, int* status,
                        b200seg_stream_t st);
+/* *loss = (float)(*loss_sum / *valid_count), NaN when *status != 0: the scalar tail of the mean reduction, on the device. */
+int b200seg_ce_finalize(const double* loss_sum, const int64_t* valid_count, const int* status, float* loss,
+                        b200seg_stream_t st);
 /* Backward of the mean cross-entropy (loss.backward() of train.py:64 reaching utils/utils.py:21): recomputes the
  * softmax from the saved logits and writes dlogits = (softmax - onehot) * (*grad_out) / (*valid_count), both scalars
  * read on the device (no host sync, no separate scaling pass); ignored pixels get 0. */

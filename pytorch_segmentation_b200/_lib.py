@@ -87,6 +87,7 @@ PROTOTYPES = {
     'b200seg_relu_bwd': (c_int, [_P, _I, _I, _P, _I, _I, _P, _I, _I, _I, _L, _P]),
     'b200seg_grad_add_masked': (c_int, [_P, _I, _I, _P, _I, _I, _P, _I, _I, _P, _I, _I, _I, _L, _P]),
     'b200seg_bn_bwd_reduce_masked': (c_int, [_P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _P, _P, _I, _P, _P, _I, _I, _P]),
+    'b200seg_bn_bwd_reduce_acc': (c_int, [_P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _P, _P, _I, _P, _P, _I, _I, _P]),
     'b200seg_bn_bwd_apply_masked': (c_int, [_P, _I, _I, _P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _P, _P, _I, _I, _P, _P,
                                             _P, _I, _P, _I, _I, _P]),
     'b200seg_bn_bwd_reduce': (c_int, [_P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _P, _P, _I, _P, _P]),
@@ -110,6 +111,7 @@ PROTOTYPES = {
     'b200seg_resize_nchw_fwd': (c_int, [_P, _L, _I, _I, _P, _I, _I, _I, _P]),
     'b200seg_resize_nchw_bwd': (c_int, [_P, _L, _I, _I, _P, _I, _I, _I, _P]),
     'b200seg_softmax_ce': (c_int, [_P, _P, _I, _I, _L, _L, _F, _P, _P, _P, _P, _P]),
+    'b200seg_ce_finalize': (c_int, [_P, _P, _P, _P, _P]),
     'b200seg_softmax_ce_bwd': (c_int, [_P, _P, _I, _I, _L, _L, _P, _P, _P, _P]),
     'b200seg_argmax': (c_int, [_P, _I, _I, _L, _P, _P]),
     'b200seg_confusion': (c_int, [_P, _P, _L, _I, _P, _P]),

@@ -241,7 +241,7 @@ __global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(
         const __nv_bfloat16* xb = x + x_off + group * 8;
         const __nv_bfloat16* db = dy + dy_off + group * 8;
         const __nv_bfloat16* mb = mask ? mask + m_off + group * 8 : nullptr;
-#pragma unroll 2
+#pragma unroll 4
         for (int64_t p = p0 + row; p < p1; p += pstep) {
             float f[8], d[8], m[8];
             unpack8(ldg128(xb + p * x_ct), f);
@@ -611,7 +611,7 @@ int b200seg_bn_bwd_reduce(const void* dy, int dy_c_total, int dy_c_offset, const
                                         save_mean, save_invstd, relu, red, nullptr, 0, 0, stream);
 }
 
-int b200seg_bn_bwd_reduce_masked(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total,
+static int bn_bwd_reduce_impl(bool zero_red, const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total,
                                  int x_c_offset, int c, int64_t pixels, const float* scale, const float* shift,
                                  const float* save_mean, const float* save_invstd, int relu, float* red, const void* mask,
                                  int mask_c_total, int mask_c_offset, b200seg_stream_t stream) {
@@ -622,13 +622,36 @@ int b200seg_bn_bwd_reduce_masked(const void* dy, int dy_c_total, int dy_c_offset
     if (check_slice("bn_bwd_reduce(x)", x, x_c_total, x_c_offset, c)) return 1;
     if (mask && check_slice("bn_bwd_reduce(mask)", mask, mask_c_total, mask_c_offset, c)) return 1;
     B200SEG_CHECK(scale && shift && save_mean && save_invstd && red && pixels > 0, "bn_bwd_reduce: bad arguments");
-    B200SEG_CUDA(cudaMemsetAsync(red, 0, sizeof(float) * 2 * c, st));
-    const ColGeom g = col_geom(c, pixels);
+    if (zero_red) B200SEG_CUDA(cudaMemsetAsync(red, 0, sizeof(float) * 2 * c, st));
+    // fewer, fatter CTAs than the streaming kernels: every CTA ends with one atomic per channel on the same 2c
+    // addresses, and those serialise in L2 (ncu: the reduce pass took longer than the apply pass that also writes)
+    static const int ctas = [] {
+        const char* e = getenv("B200SEG_BNRED_CTAS");
+        const int v = e ? atoi(e) : 2;
+        return v > 0 ? v : 2;
+    }();
+    const ColGeom g = col_geom(c, pixels, ctas);
     B200SEG_CUDA(launch_pdl(bn_bwd_reduce_kernel, dim3(g.gx, g.gy), kRedThreads, 0, st, 
         static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, static_cast<const __nv_bfloat16*>(x), x_c_total,
         x_c_offset, c, pixels, g.pixels_per_block, g.gpb, g.rows, scale, shift, save_mean, save_invstd, relu, red,
         static_cast<const __nv_bfloat16*>(mask), mask_c_total, mask_c_offset));
     return 0;
+}
+
+int b200seg_bn_bwd_reduce_masked(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total,
+                                 int x_c_offset, int c, int64_t pixels, const float* scale, const float* shift,
+                                 const float* save_mean, const float* save_invstd, int relu, float* red, const void* mask,
+                                 int mask_c_total, int mask_c_offset, b200seg_stream_t stream) {
+    return bn_bwd_reduce_impl(true, dy, dy_c_total, dy_c_offset, x, x_c_total, x_c_offset, c, pixels, scale, shift, save_mean,
+                              save_invstd, relu, red, mask, mask_c_total, mask_c_offset, stream);
+}
+
+int b200seg_bn_bwd_reduce_acc(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total, int x_c_offset,
+                              int c, int64_t pixels, const float* scale, const float* shift, const float* save_mean,
+                              const float* save_invstd, int relu, float* red, const void* mask, int mask_c_total,
+                              int mask_c_offset, b200seg_stream_t stream) {
+    return bn_bwd_reduce_impl(false, dy, dy_c_total, dy_c_offset, x, x_c_total, x_c_offset, c, pixels, scale, shift, save_mean,
+                              save_invstd, relu, red, mask, mask_c_total, mask_c_offset, stream);
 }
 
 int b200seg_bn_bwd_apply(const void* dy, int dy_c_total, int dy_c_offset, const void* x, int x_c_total, int x_c_offset,

@@ -468,6 +468,16 @@ int b200seg_resize_nchw_bwd(const float* dy, int64_t planes, int oh, int ow, flo
 
 namespace b200seg {
 namespace {
+// loss = sum / count as fp32 (NaN when a target was out of range): the scalar tail of nn.CrossEntropyLoss's mean
+__global__ void ce_finalize_kernel(const double* __restrict__ loss_sum, const unsigned long long* __restrict__ count,
+                                   const int* __restrict__ status, float* __restrict__ loss) {
+    pdl_prologue();
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        const double c = static_cast<double>(*count);
+        *loss = (*status != 0) ? __int_as_float(0x7fc00000) : static_cast<float>(*loss_sum / c);
+    }
+}
+
 int launch_softmax_ce(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
                       float grad_scale, double* loss_sum, int64_t* valid_count, float* dlogits, int* status,
                       const float* g_dev, const int64_t* count_dev, cudaStream_t st) {
@@ -500,6 +510,16 @@ int b200seg_softmax_ce(const float* logits, const int64_t* targets, int n, int n
     B200SEG_CHECK(logits && targets && loss_sum && status && n > 0 && nc > 0 && hw > 0, "softmax_ce: bad arguments");
     return launch_softmax_ce(logits, targets, n, nc, hw, ignore_index, grad_scale, loss_sum, valid_count, dlogits, status,
                              nullptr, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+int b200seg_ce_finalize(const double* loss_sum, const int64_t* valid_count, const int* status, float* loss,
+                        b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(loss_sum && valid_count && status && loss, "ce_finalize: null pointer");
+    B200SEG_CUDA(launch_pdl(ce_finalize_kernel, 1, 32, 0, static_cast<cudaStream_t>(stream), loss_sum,
+                            reinterpret_cast<const unsigned long long*>(valid_count), status, loss));
+    return 0;
 }
 
 int b200seg_softmax_ce_bwd(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,

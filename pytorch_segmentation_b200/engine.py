@@ -552,22 +552,25 @@ def bn_apply(x, y, vec, relu, res=None, res_vec=None):
     _lib.count_launch()
 
 
-def bn_backward(dy, x, dx, vec, relu, training, mask=None):
+def bn_backward(dy, x, dx, vec, relu, training, mask=None, red=None):
     """dy: grad of the BN(+ReLU) output, x: saved raw conv output, dx: receives the grad of x.  ``mask``: stored
-    block output whose sign is the ReLU mask (residual blocks); None recomputes it from x.  Returns (dgamma, dbeta)."""
+    block output whose sign is the ReLU mask (residual blocks); None recomputes it from x.  ``red``: a ZEROED fp32
+    [2c] slice of a per-backward arena (saves the per-layer memset).  Returns (dgamma, dbeta)."""
     c = x.c
     p = vec.data_ptr()
-    red = torch.empty((2 * c,), dtype=torch.float32, device=x.t.device)
     lib = _lib.load()
+    reduce_fn = lib.b200seg_bn_bwd_reduce_acc if red is not None else lib.b200seg_bn_bwd_reduce_masked
+    if red is None:
+        red = torch.empty((2 * c,), dtype=torch.float32, device=x.t.device)
     m = (mask.ptr, mask.ct, mask.c_off) if mask is not None else (None, 0, 0)
-    _lib.check(lib.b200seg_bn_bwd_reduce_masked(dy.ptr, dy.ct, dy.c_off, x.ptr, x.ct, x.c_off, c, x.pixels, p, p + 4 * c,
+    _lib.check(reduce_fn(dy.ptr, dy.ct, dy.c_off, x.ptr, x.ct, x.c_off, c, x.pixels, p, p + 4 * c,
                                                 p + 8 * c, p + 12 * c, int(relu), red.data_ptr(), m[0], m[1], m[2],
                                                 _stream()), 'bn_bwd_reduce')
     _lib.check(lib.b200seg_bn_bwd_apply_masked(dy.ptr, dy.ct, dy.c_off, x.ptr, x.ct, x.c_off, dx.ptr, dx.ct, dx.c_off, c,
                                                x.pixels, p, p + 4 * c, p + 8 * c, p + 12 * c, int(relu), int(training),
                                                red.data_ptr(), None, None, 0, m[0], m[1], m[2], _stream()),
                'bn_bwd_apply')
-    _lib.count_launch(3)      # memset + reduce + apply
+    _lib.count_launch(2)      # reduce + apply
     return red[c:], red[:c]
 
 
@@ -785,6 +788,15 @@ def softmax_ce(logits, targets, ignore_index=-100, want_grad=True):
                'softmax_ce')
     _lib.count_launch()
     return acc, dl
+
+
+def ce_finalize(acc):
+    """acc from ``softmax_ce`` -> 0-dim fp32 loss = sum / count (NaN if a target was out of range), one launch."""
+    loss = torch.empty((), dtype=torch.float32, device=acc.device)
+    p = acc.data_ptr()
+    _lib.check(_lib.load().b200seg_ce_finalize(p, p + 8, p + 16, loss.data_ptr(), _stream()), 'ce_finalize')
+    _lib.count_launch()
+    return loss
 
 
 def softmax_ce_bwd(logits, targets, grad_out, count, ignore_index=-100):

@@ -91,7 +91,7 @@ class _Block:
             E.bn_apply(raw3, out, v3, True, res=x)
         return out, (x, raw1, v1, a1, raw2, v2, a2, raw3, v3, rawd, vd, out)
 
-    def backward(self, rec, dout, training, grads, need_dx=True, dout_masked=False, mask_in=True):
+    def backward(self, rec, dout, training, grads, need_dx=True, dout_masked=False, mask_in=True, red_of=None):
         """dout: Act grad of the block output — already multiplied by (out > 0) when ``dout_masked`` (it then came from
         the next block's ``backward``), raw otherwise (a head's gradient).  Fills grads[param] and returns the Act grad
         of the block input, multiplied by (x > 0) when ``mask_in`` (x is a ReLU output: the previous block's), so that
@@ -101,7 +101,8 @@ class _Block:
 
         def unit_bwd(u, dy, raw, vec, xin, relu=True, mask=None):
             draw = E.Act.empty(raw.n, raw.h, raw.w, raw.c, dev)
-            dgamma, dbeta = E.bn_backward(dy, raw, draw, vec, relu, training, mask=mask)
+            dgamma, dbeta = E.bn_backward(dy, raw, draw, vec, relu, training, mask=mask,
+                                          red=red_of(u) if red_of is not None else None)
             grads[u.conv.weight] = u.wgrad(draw, xin)
             grads[u.bn.weight], grads[u.bn.bias] = dgamma, dbeta
             return draw
@@ -222,6 +223,14 @@ class ResNet50Features(nn.Module):
         col, pw0, raw0, v0, a0, idx, recs, training = saved
         layers = self._plan[0]
         grads = {}
+        # one zeroed arena for the per-channel reductions of every BatchNorm backward (same offsets as the forward stats)
+        units, offs, total = self._plan[1], self._plan[2], self._plan[3]
+        red_all = torch.zeros((total,), dtype=torch.float32, device=raw0.t.device)
+
+        def red_of(u):
+            o = offs[id(u)]
+            return red_all[o:o + 2 * u.cout]
+
         d = None
         masked = False       # whether d already carries the ReLU mask of the tensor it is the gradient of
         for li in (3, 2, 1, 0):
@@ -238,7 +247,7 @@ class ResNet50Features(nn.Module):
             for bi in range(len(layers[li]) - 1, -1, -1):
                 # the input of layer1's first block is the max-pool output, not a ReLU output: no mask there
                 d = layers[li][bi].backward(recs[li][bi], d, training, grads, dout_masked=masked,
-                                            mask_in=not (li == 0 and bi == 0))
+                                            mask_in=not (li == 0 and bi == 0), red_of=red_of)
                 masked = not (li == 0 and bi == 0)
         if d is not None:
             da0 = E.maxpool_bwd(d, idx, a0.h, a0.w)

@@ -28,10 +28,9 @@ class _CrossEntropyFn(torch.autograd.Function):
         # with the upstream gradient and the pixel count read on the device (one pass, no scaling pass)
         acc, _ = E.softmax_ce(x, targets, IGNORE_INDEX, want_grad=False)
         count_i = acc[1:2].view(torch.int64)
-        loss = (acc[0:1] / count_i.to(torch.float64)).to(torch.float32).reshape(())
-        # an out-of-range target raises in the reference; here it poisons the loss (no host sync)
-        bad = acc[2:3].view(torch.int32)[0] != 0
-        loss = torch.where(bad, torch.full_like(loss, float('nan')), loss)
+        # mean over the valid pixels; an out-of-range target raises in the reference, here it poisons the loss with NaN
+        # (no host sync)
+        loss = E.ce_finalize(acc)
         if need:
             ctx.save_for_backward(x, targets, count_i)
             ctx.resized, ctx.in_hw, ctx.in_dtype = resized, (outputs.shape[2], outputs.shape[3]), outputs.dtype

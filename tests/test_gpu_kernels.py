@@ -608,4 +608,4 @@ def test_errors_are_loud(E):
         E.as_act(torch.zeros(1, 3, 4, 4, device='cuda'))
     from pytorch_segmentation_b200 import ConvNormAct
     with pytest.raises(NotImplementedError):
-        ConvNormAct(8, 8, 3, 2)
+        ConvNormAct(8, 8, 3, 3)                   # stride 3 (stride 2 is the HRNet transition conv and is supported)
