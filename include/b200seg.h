@@ -311,6 +311,20 @@ int b200seg_resize_nchw_bwd(const float* dy, int64_t planes, int oh, int ow, flo
 int b200seg_softmax_ce(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
                        float grad_scale, double* loss_sum, int64_t* valid_count, float* dlogits, int* status,
                        b200seg_stream_t st);
+/* Cross-entropy straight from the head's LOW-RESOLUTION fp32 NHWC class map [n][h][w][c_total] (before the final bilinear
+ * of models/deeplabv3plus.py:40-43, unet.py:52-55, hrnet.py:400-404): the th x tw logits are interpolated on the fly
+ * (same arithmetic as b200seg_logits_upsample_fwd).  _fwd accumulates like b200seg_softmax_ce; _bwd writes the gradient
+ * of the class map itself (fp32, zeroed here) = upsample^T((softmax - onehot) * *grad_out / *valid_count) without the
+ * full-resolution gradient ever existing in HBM.  th >= h, tw >= w, nc <= 32. */
+int b200seg_lowres_ce_fwd(const float* lr, int n, int h, int w, int c_total, int nc, const int64_t* targets, int th, int tw,
+                          int align_corners, int64_t ignore_index, double* loss_sum, int64_t* valid_count, int* status,
+                          b200seg_stream_t st);
+int b200seg_lowres_ce_bwd(const float* lr, int n, int h, int w, int c_total, int nc, const int64_t* targets, int th, int tw,
+                          int align_corners, int64_t ignore_index, const float* grad_out, const int64_t* valid_count,
+                          float* dlr, b200seg_stream_t st);
+/* out[i] = bf16(a[i] + b[i]) (b bf16, may be NULL), count % 4 == 0: the fp32 class-map gradient of
+ * b200seg_lowres_ce_bwd as the bf16 NHWC slice b200seg_conv_dgrad / _wgrad consume. */
+int b200seg_cast_add_bf16(const float* a, const void* b, void* out, int64_t count, b200seg_stream_t st);
 /* *loss = (float)(*loss_sum / *valid_count), NaN when *status != 0: the scalar tail of the mean reduction, on the device. */
 int b200seg_ce_finalize(const double* loss_sum, const int64_t* valid_count, const int* status, float* loss,
                         b200seg_stream_t st);

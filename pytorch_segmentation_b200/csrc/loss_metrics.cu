@@ -466,8 +466,213 @@ int b200seg_resize_nchw_bwd(const float* dy, int64_t planes, int oh, int ow, flo
     return 0;
 }
 
+}  // extern "C"
+
 namespace b200seg {
 namespace {
+// ------------------------------------------------------------------------------------------------------------
+// Cross-entropy straight from the LOW-RESOLUTION class map (the head's fp32 NHWC [n][h][w][ct] output before its final
+// bilinear upsample, models/deeplabv3plus.py:40-43 / unet.py:52-55 / hrnet.py:400-404): the full-resolution logits are
+// interpolated on the fly, never read back from HBM (forward: 12.6 + 34 MB instead of 352 + 34 MB), and the backward
+// emits the gradient of the low-resolution map directly — softmax recomputed per pixel, scattered through the bilinear
+// weights into a shared-memory tile, flushed with fp32 atomics — instead of writing 352 MB of dlogits and reading them
+// again in the upsample adjoint.  One CTA = a 16 x 64 tile of target pixels; its source footprint (FH x FW low-res
+// pixels) is staged in shared memory.  Each thread owns 4 consecutive pixels of a row and pre-reduces their
+// contributions per source column in registers (they share 1-2 source columns), so the shared-memory atomics are a
+// quarter of the naive count.
+constexpr int kLrTH = 16, kLrTW = 64;
+
+template <int NCMAX, bool BWD>
+__global__ void __launch_bounds__(256, BWD ? 2 : 4) lowres_ce_kernel(const float* __restrict__ lr, int ct, int h, int w, int nc,
+                                                         const int64_t* __restrict__ tgt, int H, int W, float sh, float sw,
+                                                         int ac, int64_t ignore_index, double* loss_sum,
+                                                         unsigned long long* valid_count, int* status,
+                                                         float* __restrict__ dlr, const float* __restrict__ g_dev,
+                                                         const unsigned long long* __restrict__ count_dev, int FH, int FW) {
+    pdl_prologue();
+    extern __shared__ __align__(16) float lsm[];
+    float* L = lsm;                               // [FH][FW][ct] staged class map
+    float* G = lsm + FH * FW * ct;                // [FH][FW][ct] gradient accumulator (backward only)
+    const int n = blockIdx.z, ty0 = blockIdx.y * kLrTH, tx0 = blockIdx.x * kLrTW;
+    const int fy0 = bilinear_src(sh, ty0, h, ac).i0, fx0 = bilinear_src(sw, tx0, w, ac).i0;
+    const float* base = lr + static_cast<int64_t>(n) * h * w * ct;
+    const int cells = FH * FW;
+    for (int i = threadIdx.x; i < cells * (ct >> 2); i += blockDim.x) {
+        const int q = i % (ct >> 2), cell = i / (ct >> 2);
+        const int yy = fy0 + cell / FW, xx = fx0 + cell % FW;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (yy < h && xx < w) v = __ldg(reinterpret_cast<const float4*>(base + (static_cast<int64_t>(yy) * w + xx) * ct) + q);
+        reinterpret_cast<float4*>(L)[i] = v;
+        if (BWD) reinterpret_cast<float4*>(G)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    __syncthreads();
+    float gscale = 1.f;
+    if (BWD) gscale = __ldg(g_dev) / static_cast<float>(__ldg(count_dev));
+    const int ry = threadIdx.x >> 4, cg = threadIdx.x & 15;
+    const int oy = ty0 + ry;
+    double lsum = 0.0;
+    unsigned int lcount = 0;
+    if (oy < H) {
+        const Lerp ly = bilinear_src(sh, oy, h, ac);
+        const int y0 = ly.i0 - fy0, y1 = ly.i1 - fy0;
+        float acc0[NCMAX], acc1[NCMAX];
+        int cur = -1;
+        auto flush = [&]() {
+            if (cur < 0) return;
+            float* g00 = G + (y0 * FW + cur) * ct;
+            float* g10 = G + (y1 * FW + cur) * ct;
+#pragma unroll
+            for (int c = 0; c < NCMAX; ++c) {
+                if (c < nc) {
+                    atomicAdd(g00 + c, ly.w0 * acc0[c]);
+                    if (ly.w1 != 0.f) atomicAdd(g10 + c, ly.w1 * acc0[c]);
+                    if (cur + 1 < FW) {
+                        atomicAdd(g00 + ct + c, ly.w0 * acc1[c]);
+                        if (ly.w1 != 0.f) atomicAdd(g10 + ct + c, ly.w1 * acc1[c]);
+                    }
+                }
+            }
+        };
+#pragma unroll 1
+        for (int j = 0; j < 4; ++j) {
+            const int ox = tx0 + cg * 4 + j;
+            if (ox >= W) break;
+            const Lerp lx = bilinear_src(sw, ox, w, ac);
+            const int x0 = lx.i0 - fx0, x1 = lx.i1 - fx0;
+            const float* p00 = L + (y0 * FW + x0) * ct;
+            const float* p01 = L + (y0 * FW + x1) * ct;
+            const float* p10 = L + (y1 * FW + x0) * ct;
+            const float* p11 = L + (y1 * FW + x1) * ct;
+            float v[NCMAX];
+            float m = -INFINITY;
+#pragma unroll
+            for (int c = 0; c < NCMAX; ++c) {
+                // same expression as logits_up_fwd_kernel, so the loss is the loss of the logits the model returned
+                v[c] = c < nc ? ly.w0 * (lx.w0 * p00[c] + lx.w1 * p01[c]) + ly.w1 * (lx.w0 * p10[c] + lx.w1 * p11[c]) : -INFINITY;
+                m = fmaxf(m, v[c]);
+            }
+            float s = 0.f;
+#pragma unroll
+            for (int c = 0; c < NCMAX; ++c) {
+                v[c] = c < nc ? __expf(v[c] - m) : 0.f;
+                s += v[c];
+            }
+            const int64_t t = __ldcs(tgt + (static_cast<int64_t>(n) * H + oy) * W + ox);
+            const bool ignored = (t == ignore_index);
+            const bool bad = !ignored && (t < 0 || t >= nc);
+            if (bad && status) *status = 1;
+            const bool valid = !ignored && !bad;
+            if (!BWD) {
+                if (valid) {
+                    // log-softmax at the target: the interpolated logit is recomputed rather than indexed dynamically
+                    const int tc = static_cast<int>(t);
+                    const float xt = ly.w0 * (lx.w0 * p00[tc] + lx.w1 * p01[tc]) + ly.w1 * (lx.w0 * p10[tc] + lx.w1 * p11[tc]);
+                    lsum += static_cast<double>(__logf(s) + m - xt);
+                    ++lcount;
+                }
+                continue;
+            }
+            if (x0 != cur) {
+                flush();
+                cur = x0;
+#pragma unroll
+                for (int c = 0; c < NCMAX; ++c) acc0[c] = acc1[c] = 0.f;
+            }
+            const float inv = valid ? gscale / s : 0.f;
+            const float a0 = x1 == x0 ? lx.w0 + lx.w1 : lx.w0, a1 = x1 == x0 ? 0.f : lx.w1;
+#pragma unroll
+            for (int c = 0; c < NCMAX; ++c) {
+                const float d = v[c] * inv - ((valid && c == t) ? gscale : 0.f);
+                acc0[c] = fmaf(a0, d, acc0[c]);
+                acc1[c] = fmaf(a1, d, acc1[c]);
+            }
+        }
+        if (BWD) flush();
+    }
+    if (!BWD) {
+        lsum = warp_sum(lsum);
+        lcount = __reduce_add_sync(0xffffffffu, lcount);
+        __shared__ double ssum[8];
+        __shared__ unsigned int scnt[8];
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        if (lane == 0) {
+            ssum[warp] = lsum;
+            scnt[warp] = lcount;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double a = 0.0;
+            unsigned long long b = 0;
+            for (int k = 0; k < 8; ++k) {
+                a += ssum[k];
+                b += scnt[k];
+            }
+            atomicAdd(loss_sum, a);
+            atomicAdd(valid_count, b);
+        }
+        return;
+    }
+    __syncthreads();
+    float* out = dlr + static_cast<int64_t>(n) * h * w * ct;
+    for (int i = threadIdx.x; i < cells * ct; i += blockDim.x) {
+        const int c = i % ct, cell = i / ct;
+        const int yy = fy0 + cell / FW, xx = fx0 + cell % FW;
+        const float v = G[i];
+        if (c < nc && yy < h && xx < w && v != 0.f) atomicAdd(out + (static_cast<int64_t>(yy) * w + xx) * ct + c, v);
+    }
+}
+
+// out = bf16(a [+ b]) over n elements (n % 4 == 0): the fp32 class-map gradient becomes the bf16 slice the conv
+// backward consumes; b carries the gradient that reached the full-resolution logits some other way (may be null)
+__global__ void cast_add_bf16_kernel(const float4* __restrict__ a, const uint2* __restrict__ b, uint2* __restrict__ out,
+                                     int64_t n4) {
+    pdl_prologue();
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n4;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        float4 v = __ldg(a + i);
+        if (b) {
+            const uint2 r = __ldg(b + i);
+            const __nv_bfloat162 lo = *reinterpret_cast<const __nv_bfloat162*>(&r.x);
+            const __nv_bfloat162 hi = *reinterpret_cast<const __nv_bfloat162*>(&r.y);
+            v.x += __low2float(lo); v.y += __high2float(lo); v.z += __low2float(hi); v.w += __high2float(hi);
+        }
+        const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+        uint2 o;
+        o.x = *reinterpret_cast<const unsigned int*>(&lo);
+        o.y = *reinterpret_cast<const unsigned int*>(&hi);
+        out[i] = o;
+    }
+}
+
+int launch_lowres_ce(const float* lr, int n, int h, int w, int ct, int nc, const int64_t* targets, int H, int W,
+                     int align_corners, int64_t ignore_index, double* loss_sum, int64_t* valid_count, int* status, float* dlr,
+                     const float* g_dev, const int64_t* count_dev, cudaStream_t st) {
+    const float sh = bilinear_scale(h, H, align_corners), sw = bilinear_scale(w, W, align_corners);
+    // footprint of a 16 x 64 target tile in the class map (+1 for the second lerp tap, +1 for rounding)
+    const int FH = static_cast<int>(kLrTH * sh) + 3 < h ? static_cast<int>(kLrTH * sh) + 3 : h;
+    const int FW = static_cast<int>(kLrTW * sw) + 3 < w ? static_cast<int>(kLrTW * sw) + 3 : w;
+    const size_t smem = static_cast<size_t>(FH) * FW * ct * sizeof(float) * (dlr ? 2 : 1);
+    B200SEG_CHECK(smem <= 48 * 1024, "lowres_ce: class-map footprint of %zu bytes per tile exceeds shared memory", smem);
+    B200SEG_CHECK(n <= 65535 && ceil_div(H, kLrTH) <= 65535, "lowres_ce: grid too large");
+    dim3 grid(ceil_div(W, kLrTW), ceil_div(H, kLrTH), n);
+    unsigned long long* vc = reinterpret_cast<unsigned long long*>(valid_count);
+    const unsigned long long* cd = reinterpret_cast<const unsigned long long*>(count_dev);
+#define B200SEG_LRCE(NC, B)                                                                                              \
+    B200SEG_CUDA(launch_pdl(lowres_ce_kernel<NC, B>, grid, 256, smem, st, lr, ct, h, w, nc, targets, H, W, sh, sw,           \
+                            align_corners, ignore_index, loss_sum, vc, status, dlr, g_dev, cd, FH, FW))
+    if (dlr) {
+        if (nc <= 8) B200SEG_LRCE(8, true);
+        else if (nc <= 24) B200SEG_LRCE(24, true);
+        else B200SEG_LRCE(32, true);
+    } else {
+        if (nc <= 8) B200SEG_LRCE(8, false);
+        else if (nc <= 24) B200SEG_LRCE(24, false);
+        else B200SEG_LRCE(32, false);
+    }
+#undef B200SEG_LRCE
+    return 0;
+}
+
 // loss = sum / count as fp32 (NaN when a target was out of range): the scalar tail of nn.CrossEntropyLoss's mean
 __global__ void ce_finalize_kernel(const double* __restrict__ loss_sum, const unsigned long long* __restrict__ count,
                                    const int* __restrict__ status, float* __restrict__ loss) {
@@ -502,6 +707,8 @@ int launch_softmax_ce(const float* logits, const int64_t* targets, int n, int nc
 }  // namespace
 }  // namespace b200seg
 
+extern "C" {
+
 int b200seg_softmax_ce(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
                        float grad_scale, double* loss_sum, int64_t* valid_count, float* dlogits, int* status,
                        b200seg_stream_t stream) {
@@ -510,6 +717,49 @@ int b200seg_softmax_ce(const float* logits, const int64_t* targets, int n, int n
     B200SEG_CHECK(logits && targets && loss_sum && status && n > 0 && nc > 0 && hw > 0, "softmax_ce: bad arguments");
     return launch_softmax_ce(logits, targets, n, nc, hw, ignore_index, grad_scale, loss_sum, valid_count, dlogits, status,
                              nullptr, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+int b200seg_lowres_ce_fwd(const float* lr, int n, int h, int w, int c_total, int nc, const int64_t* targets, int th, int tw,
+                          int align_corners, int64_t ignore_index, double* loss_sum, int64_t* valid_count, int* status,
+                          b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(lr && targets && loss_sum && valid_count && status, "lowres_ce_fwd: null pointer");
+    B200SEG_CHECK(n > 0 && h > 0 && w > 0 && th >= h && tw >= w && nc > 0 && nc <= c_total && nc <= 32 && c_total % 4 == 0,
+                  "lowres_ce_fwd: bad geometry (class map %dx%d, targets %dx%d, nc %d of %d)", h, w, th, tw, nc, c_total);
+    B200SEG_CHECK((reinterpret_cast<uintptr_t>(lr) & 15) == 0, "lowres_ce_fwd: class map not 16-byte aligned");
+    return launch_lowres_ce(lr, n, h, w, c_total, nc, targets, th, tw, align_corners, ignore_index, loss_sum, valid_count,
+                            status, nullptr, nullptr, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+int b200seg_lowres_ce_bwd(const float* lr, int n, int h, int w, int c_total, int nc, const int64_t* targets, int th, int tw,
+                          int align_corners, int64_t ignore_index, const float* grad_out, const int64_t* valid_count,
+                          float* dlr, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(lr && targets && grad_out && valid_count && dlr, "lowres_ce_bwd: null pointer");
+    B200SEG_CHECK(n > 0 && h > 0 && w > 0 && th >= h && tw >= w && nc > 0 && nc <= c_total && nc <= 32 && c_total % 4 == 0,
+                  "lowres_ce_bwd: bad geometry (class map %dx%d, targets %dx%d, nc %d of %d)", h, w, th, tw, nc, c_total);
+    B200SEG_CHECK(((reinterpret_cast<uintptr_t>(lr) | reinterpret_cast<uintptr_t>(dlr)) & 15) == 0,
+                  "lowres_ce_bwd: pointers not 16-byte aligned");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    B200SEG_CUDA(cudaMemsetAsync(dlr, 0, sizeof(float) * static_cast<size_t>(n) * h * w * c_total, st));
+    return launch_lowres_ce(lr, n, h, w, c_total, nc, targets, th, tw, align_corners, ignore_index, nullptr, nullptr, nullptr,
+                            dlr, grad_out, valid_count, st);
+}
+
+int b200seg_cast_add_bf16(const float* a, const void* b, void* out, int64_t count, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(a && out && count > 0 && count % 4 == 0, "cast_add_bf16: null pointer or count %lld not a multiple of 4",
+                  static_cast<long long>(count));
+    B200SEG_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 7) == 0 &&
+                      (reinterpret_cast<uintptr_t>(b) & 7) == 0, "cast_add_bf16: misaligned pointer");
+    const int64_t n4 = count / 4;
+    const int blocks = static_cast<int>(n4 / 256 + 1 < 148 * 8 ? n4 / 256 + 1 : 148 * 8);
+    B200SEG_CUDA(launch_pdl(cast_add_bf16_kernel, blocks, 256, 0, static_cast<cudaStream_t>(stream),
+                            reinterpret_cast<const float4*>(a), static_cast<const uint2*>(b), static_cast<uint2*>(out), n4));
+    return 0;
 }
 
 int b200seg_ce_finalize(const double* loss_sum, const int64_t* valid_count, const int* status, float* loss,

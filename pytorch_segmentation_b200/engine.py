@@ -790,6 +790,78 @@ def softmax_ce(logits, targets, ignore_index=-100, want_grad=True):
     return acc, dl
 
 
+LOWRES_CE = _os.environ.get('B200SEG_LOWRES_CE', '1') != '0'   # loss through the class map (utils.compute_loss)
+
+
+def _lowres_geometry(lr, targets):
+    n, h, w, ct = lr.shape
+    assert lr.dtype == torch.float32 and lr.is_contiguous() and targets.dtype == torch.int64 and targets.is_contiguous()
+    assert targets.shape[0] == n
+    return n, h, w, ct, targets.shape[1], targets.shape[2]
+
+
+def lowres_ce_supported(lr_shape, nc, th, tw):
+    """The fused loss stages the class-map footprint of a 16 x 64 target tile (twice, in backward) in 48 KB."""
+    n, h, w, ct = lr_shape
+    if th < h or tw < w or nc > 32:
+        return False
+    fh, fw = min(16 * h // th + 3, h), min(64 * w // tw + 3, w)
+    return 2 * fh * fw * ct * 4 <= 48 * 1024
+
+
+def lowres_ce_fwd(lr, nc, targets, align_corners=True, ignore_index=-100):
+    """Loss accumulators (as ``softmax_ce``) of the bilinear upsample of the fp32 NHWC class map ``lr`` to the target
+    size, without the upsampled logits."""
+    n, h, w, ct, th, tw = _lowres_geometry(lr, targets)
+    acc = torch.zeros((3,), dtype=torch.float64, device=lr.device)
+    p = acc.data_ptr()
+    _lib.check(_lib.load().b200seg_lowres_ce_fwd(lr.data_ptr(), n, h, w, ct, nc, targets.data_ptr(), th, tw,
+                                                 int(align_corners), ignore_index, p, p + 8, p + 16, _stream()),
+               'lowres_ce_fwd')
+    _lib.count_launch()
+    return acc
+
+
+def lowres_ce_bwd(lr, nc, targets, grad_out, count, align_corners=True, ignore_index=-100):
+    """fp32 gradient of the class map: upsample^T((softmax - onehot) * grad_out / count)."""
+    n, h, w, ct, th, tw = _lowres_geometry(lr, targets)
+    assert grad_out.dtype == torch.float32 and count.dtype == torch.int64
+    dlr = torch.empty_like(lr)
+    _lib.check(_lib.load().b200seg_lowres_ce_bwd(lr.data_ptr(), n, h, w, ct, nc, targets.data_ptr(), th, tw,
+                                                 int(align_corners), ignore_index, grad_out.data_ptr(), count.data_ptr(),
+                                                 dlr.data_ptr(), _stream()), 'lowres_ce_bwd')
+    _lib.count_launch()
+    return dlr
+
+
+def class_map_grad(dlr_f32, extra=None):
+    """fp32 NHWC class-map gradient (+ an optional bf16 Act addend) -> the bf16 Act the classifier backward takes."""
+    n, h, w, ct = dlr_f32.shape
+    out = Act.empty(n, h, w, ct, dlr_f32.device)
+    _lib.check(_lib.load().b200seg_cast_add_bf16(dlr_f32.data_ptr(), extra.ptr if extra is not None else None, out.ptr,
+                                                 dlr_f32.numel(), _stream()), 'cast_add_bf16')
+    _lib.count_launch()
+    return out
+
+
+def class_map_backward(dout, dlr_direct, h, w, ncp, align_corners):
+    """Gradient of a head's class map as a bf16 Act from either / both of its consumers: the full-resolution logits
+    (``dout``, NCHW, through the upsample adjoint) and the class-map loss (``dlr_direct``, fp32 NHWC)."""
+    extra = None
+    if dout is not None:
+        extra = logits_upsample_bwd(dout.contiguous().float(), h, w, ncp, align_corners=align_corners)
+    if dlr_direct is None:
+        return extra
+    return class_map_grad(dlr_direct.contiguous(), extra)
+
+
+def attach_class_map(out, lr, nc, align_corners):
+    """Called by the model heads (read by utils.compute_loss): remember which class map ``out`` is the upsample of (and ``out``'s version, so an
+    in-place edit of the logits turns the shortcut off)."""
+    out._b200seg_class_map = (lr, nc, align_corners, out._version)
+    return out
+
+
 def ce_finalize(acc):
     """acc from ``softmax_ce`` -> 0-dim fp32 loss = sum / count (NaN if a target was out of range), one launch."""
     loss = torch.empty((), dtype=torch.float32, device=acc.device)

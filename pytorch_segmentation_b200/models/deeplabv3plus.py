@@ -45,7 +45,8 @@ class DeepLabV3Plus(nn.Module):
 
     def head(self, low, high):
         """features[1] (256 ch, stride 4) and features[-1] (2048 ch, stride 16) -> N x nc x 4H4 x 4W4 logits."""
-        return _DeepLabHeadFn.apply(self, low, high, *self.head_tensors())
+        out, lr = _DeepLabHeadFn.apply(self, low, high, *self.head_tensors())
+        return E.attach_class_map(out, lr, self.num_classes, True)
 
 
 def make_cls_packed(conv):
@@ -112,16 +113,16 @@ class _DeepLabHeadFn(torch.autograd.Function):
         if save:
             ctx.m, ctx.low, ctx.high = m, low, high
             ctx.rec = (rec_proj, rec_aspp, dec, (ha.h, ha.w), lr.shape[3])
-        return out
+            ctx.set_materialize_grads(False)
+        return out, lr
 
     @staticmethod
-    def backward(ctx, dout):
+    def backward(ctx, dout, dlr_direct):
         m = ctx.m
         rec_proj, rec_aspp, dec, (h16, w16), ncp = ctx.rec
-        dev = dout.device
         n, h4, w4 = dec.n, dec.h, dec.w
-        dout = dout.contiguous().float()
-        dlr = E.logits_upsample_bwd(dout, h4, w4, ncp, align_corners=True)
+        dev = dec.t.device
+        dlr = E.class_map_backward(dout, dlr_direct, h4, w4, ncp, True)
         ddec = E.Act.empty(n, h4, w4, 384, dev)
         cls_grads = cls_conv_backward(m.cls_conv, m._cls_packed, dec, dlr, ddec, lane=True)
         # project branch

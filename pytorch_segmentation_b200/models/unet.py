@@ -44,7 +44,8 @@ class UNet(nn.Module):
         return self.head(x2, x3, x4, x5)
 
     def head(self, x2, x3, x4, x5):
-        return _UNetHeadFn.apply(self, x2, x3, x4, x5, *self.head_tensors())
+        out, lr = _UNetHeadFn.apply(self, x2, x3, x4, x5, *self.head_tensors())
+        return E.attach_class_map(out, lr, self.num_classes, True)
 
 
 def _up2(x, out):
@@ -85,17 +86,17 @@ class _UNetHeadFn(torch.autograd.Function):
         if save:
             ctx.m, ctx.inputs = m, (x2, x3, x4, x5)
             ctx.rec = (recs, cats, u, lr.shape[3])
-        return out
+            ctx.set_materialize_grads(False)
+        return out, lr
 
     @staticmethod
-    def backward(ctx, dout):
+    def backward(ctx, dout, dlr_direct):
         m = ctx.m
         recs, cats, u, ncp = ctx.rec
         x2, x3, x4, x5 = ctx.inputs
-        dev = dout.device
+        dev = u.t.device
         n = u.n
-        dout = dout.contiguous().float()
-        dlr = E.logits_upsample_bwd(dout, u.h, u.w, ncp, align_corners=True)
+        dlr = E.class_map_backward(dout, dlr_direct, u.h, u.w, ncp, True)
         du = E.Act.empty(n, u.h, u.w, u.c, dev)
         cls_grads = cls_conv_backward(m.cls_conv, m._cls_packed, u, dlr, du, lane=True)
         dcat = E.Act.empty(n, cats[2].h, cats[2].w, cats[2].c, dev)

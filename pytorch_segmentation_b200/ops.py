@@ -198,15 +198,15 @@ class _ClassifyFn(torch.autograd.Function):
         out = E.logits_upsample_fwd(lr, conv.out_channels, xa.h * scale, xa.w * scale, align_corners=align_corners)
         if save:
             ctx.cfg = (xa, conv, packed, lr.shape[3], align_corners, x)
-        return out
+            ctx.set_materialize_grads(False)
+        return out, lr
 
     @staticmethod
-    def backward(ctx, dout):
+    def backward(ctx, dout, dlr_direct):
         from .models.deeplabv3plus import cls_conv_backward
         xa, conv, packed, ncp, ac, x = ctx.cfg
-        dout = dout.contiguous().float()
-        dlr = E.logits_upsample_bwd(dout, xa.h, xa.w, ncp, align_corners=ac)
-        dx = E.Act.empty(xa.n, xa.h, xa.w, xa.c, dout.device) if ctx.needs_input_grad[0] else None
+        dlr = E.class_map_backward(dout, dlr_direct, xa.h, xa.w, ncp, ac)
+        dx = E.Act.empty(xa.n, xa.h, xa.w, xa.c, xa.t.device) if ctx.needs_input_grad[0] else None
         dw, db = cls_conv_backward(conv, packed, xa, dlr, dx, lane=True)
         E.join_wgrad_lane()
         return (E.grad_like(x, dx) if dx is not None else None), dw, db, None, None, None, None
@@ -216,4 +216,5 @@ def classify(x, conv, packed, scale, align_corners):
     """nn.Conv2d (with bias, 1x1 or 3x3 'same') + bilinear x``scale`` -> fp32 NCHW logits."""
     if conv.bias is None:
         raise NotImplementedError('classifier conv without bias')
-    return _ClassifyFn.apply(x, conv.weight, conv.bias, conv, packed, int(scale), bool(align_corners))
+    out, lr = _ClassifyFn.apply(x, conv.weight, conv.bias, conv, packed, int(scale), bool(align_corners))
+    return E.attach_class_map(out, lr, conv.out_channels, bool(align_corners))

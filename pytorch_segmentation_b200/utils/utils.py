@@ -46,8 +46,33 @@ class _CrossEntropyFn(torch.autograd.Function):
         return dl.to(ctx.in_dtype), None
 
 
+class _ClassMapCrossEntropyFn(torch.autograd.Function):
+    """The same loss taken from the head's low-resolution fp32 class map: the logits the model returned are that map's
+    bilinear upsample, so loss and gradient are computed through the interpolation without reading the logits or
+    writing their gradient (csrc/loss_metrics.cu, lowres_ce_kernel)."""
+
+    @staticmethod
+    def forward(ctx, lr, targets, nc, align_corners):
+        acc = E.lowres_ce_fwd(lr.detach(), nc, targets, align_corners, IGNORE_INDEX)
+        if ctx.needs_input_grad[0]:
+            ctx.save_for_backward(lr.detach(), targets, acc[1:2].view(torch.int64))
+            ctx.nc, ctx.ac = nc, align_corners
+        return E.ce_finalize(acc)
+
+    @staticmethod
+    def backward(ctx, g):
+        lr, targets, count_i = ctx.saved_tensors
+        g = g.detach().to(torch.float32).contiguous()
+        return E.lowres_ce_bwd(lr, ctx.nc, targets, g, count_i, ctx.ac, IGNORE_INDEX), None, None, None
+
+
 def compute_loss(outputs, targets, model=None):
     """utils/utils.py:17-24: logits N x nc x h x w, int64 targets N x H x W -> 0-dim loss tensor."""
+    cm = getattr(outputs, '_b200seg_class_map', None)
+    if (cm is not None and cm[3] == outputs._version and targets.is_cuda and targets.dtype == torch.int64
+            and tuple(outputs.shape[2:]) == tuple(targets.shape[1:]) and E.LOWRES_CE
+            and E.lowres_ce_supported(cm[0].shape, cm[1], targets.shape[1], targets.shape[2])):
+        return _ClassMapCrossEntropyFn.apply(cm[0], targets.contiguous(), cm[1], cm[2])
     return _CrossEntropyFn.apply(outputs, targets)
 
 

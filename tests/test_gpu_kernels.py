@@ -609,3 +609,95 @@ def test_errors_are_loud(E):
     from pytorch_segmentation_b200 import ConvNormAct
     with pytest.raises(NotImplementedError):
         ConvNormAct(8, 8, 3, 3)                   # stride 3 (stride 2 is the HRNet transition conv and is supported)
+
+
+# ---- loss through the low-resolution class map (csrc/loss_metrics.cu lowres_ce_kernel) ----------------------------------
+LOWRES_CASES = [
+    # n, h, w, scale, nc, ct, align_corners
+    (2, 32, 40, 4, 21, 24, True),       # DeepLabV3+ head (models/deeplabv3plus.py:40-43); 160 wide = 2.5 tiles
+    (1, 23, 19, 4, 19, 24, False),      # HRNet head (models/hrnet.py:400-404), ragged
+    (3, 40, 48, 2, 2, 8, True),         # UNet head (models/unet.py:52-55)
+    (1, 9, 9, 4, 32, 32, True),         # widest class count
+]
+
+
+@pytest.mark.parametrize('n,h,w,scale,nc,ct,ac', LOWRES_CASES)
+def test_lowres_ce_matches_interpolate_cross_entropy(E, n, h, w, scale, nc, ct, ac):
+    g = torch.Generator().manual_seed(n * 100 + h)
+    H, W = h * scale, w * scale
+    lr = torch.zeros(n, h, w, ct)
+    lr[..., :nc] = torch.randn(n, h, w, nc, generator=g) * 3
+    t = torch.randint(0, nc, (n, H, W), generator=g)
+    t[torch.rand(n, H, W, generator=g) < 0.1] = -100                    # ignored pixels
+    ref_in = lr[..., :nc].permute(0, 3, 1, 2).contiguous().double().requires_grad_(True)
+    ref = F.cross_entropy(F.interpolate(ref_in, size=(H, W), mode='bilinear', align_corners=ac), t)
+    ref.backward()
+    upstream = torch.tensor(0.7, device='cuda')
+    lr_d, t_d = lr.cuda(), t.cuda()
+    acc = E.lowres_ce_fwd(lr_d, nc, t_d, ac)
+    loss = E.ce_finalize(acc)
+    assert int(acc[1:2].view(torch.int64)) == int((t != -100).sum())
+    assert abs(float(loss) - float(ref)) <= 2e-5 * abs(float(ref))
+    dlr = E.lowres_ce_bwd(lr_d, nc, t_d, upstream, acc[1:2].view(torch.int64), ac)
+    want = 0.7 * ref_in.grad.permute(0, 2, 3, 1).float()
+    assert rel_err(dlr[..., :nc], want) < 1e-4
+    assert float(dlr[..., nc:].abs().max()) == 0.0 if ct > nc else True
+    # the same numbers as the unfused path the model falls back to (upsampled logits -> softmax_ce)
+    logits = E.logits_upsample_fwd(lr_d, nc, H, W, align_corners=ac)
+    acc2, _ = E.softmax_ce(logits, t_d, want_grad=False)
+    assert abs(float(E.ce_finalize(acc2)) - float(loss)) <= 2e-6 * abs(float(loss))
+    # bf16 Act for the classifier backward, with and without a second gradient through the logits
+    a = E.class_map_grad(dlr)
+    assert rel_err(a.t.float(), dlr) < 4e-3
+    b = E.class_map_grad(dlr, a)
+    assert rel_err(b.t.float(), 2 * dlr) < 8e-3
+
+
+def test_lowres_ce_all_ignored_and_bad_target(E):
+    lr = torch.randn(1, 8, 8, 8, device='cuda')
+    t = torch.full((1, 32, 32), -100, dtype=torch.int64, device='cuda')
+    acc = E.lowres_ce_fwd(lr, 5, t, True)
+    assert torch.isnan(E.ce_finalize(acc))                             # 0 / 0, like nn.CrossEntropyLoss
+    t[0, 3, 3] = 7                                                       # out of range -> NaN, no host sync
+    assert torch.isnan(E.ce_finalize(E.lowres_ce_fwd(lr, 5, t, True)))
+    with pytest.raises(RuntimeError, match='lowres_ce'):
+        E.lowres_ce_fwd(torch.randn(1, 64, 64, 24, device='cuda'), 21, torch.zeros(1, 64, 64, dtype=torch.int64, device='cuda'))
+
+
+@pytest.mark.parametrize('kind', ['deeplabv3plus', 'unet'])
+def test_compute_loss_takes_the_class_map_shortcut_and_matches_the_logits_path(E, kind, monkeypatch):
+    import pytorch_segmentation_b200 as P
+    torch.manual_seed(0)
+    m = (P.DeepLabV3Plus(21) if kind == 'deeplabv3plus' else P.UNet(2)).cuda().eval()
+    nc = m.num_classes
+    x = torch.randn(2, 3, 128, 192, device='cuda')
+    t = torch.randint(0, nc, (2, 128, 192), device='cuda')
+    res = {}
+    for on in (True, False):
+        monkeypatch.setattr(E, 'LOWRES_CE', on)
+        m.zero_grad(set_to_none=True)
+        out = m(x)
+        assert hasattr(out, '_b200seg_class_map')
+        before = E._lib.launches()
+        loss = P.compute_loss(out, t)
+        res[on] = dict(loss=float(loss), launches=E._lib.launches() - before)
+        loss.backward()
+        res[on]['grads'] = {k: p.grad.clone() for k, p in m.named_parameters() if p.grad is not None}
+    assert res[True]['launches'] == 2 and res[False]['launches'] == 2
+    assert abs(res[True]['loss'] - res[False]['loss']) <= 1e-5 * abs(res[False]['loss'])
+    assert set(res[True]['grads']) == set(res[False]['grads'])
+    worst = max(float((res[True]['grads'][k] - g).norm()) / max(float(g.norm()), 1e-12) for k, g in res[False]['grads'].items())
+    assert worst < 2e-2, worst
+    # an in-place edit of the logits turns the shortcut off; so does a size mismatch with the targets
+    with torch.no_grad():
+        out = m(x)
+        out.mul_(2.0)
+        assert abs(float(P.compute_loss(out, t)) - res[False]['loss']) > 1e-3
+        small = P.compute_loss(m(x), t[:, ::2, ::2].contiguous())
+        assert torch.isfinite(small)
+    # a gradient through the logits AND the class-map loss: both reach the head
+    m.zero_grad(set_to_none=True)
+    monkeypatch.setattr(E, 'LOWRES_CE', True)
+    out = m(x)
+    (P.compute_loss(out, t) + 1e-3 * out.square().mean()).backward()
+    assert all(torch.isfinite(p.grad).all() for p in m.parameters() if p.grad is not None)
