@@ -474,122 +474,179 @@ namespace {
 // Cross-entropy straight from the LOW-RESOLUTION class map (the head's fp32 NHWC [n][h][w][ct] output before its final
 // bilinear upsample, models/deeplabv3plus.py:40-43 / unet.py:52-55 / hrnet.py:400-404): the full-resolution logits are
 // interpolated on the fly, never read back from HBM (forward: 12.6 + 34 MB instead of 352 + 34 MB), and the backward
-// emits the gradient of the low-resolution map directly — softmax recomputed per pixel, scattered through the bilinear
-// weights into a shared-memory tile, flushed with fp32 atomics — instead of writing 352 MB of dlogits and reading them
-// again in the upsample adjoint.  One CTA = a 16 x 64 tile of target pixels; its source footprint (FH x FW low-res
-// pixels) is staged in shared memory.  Each thread owns 4 consecutive pixels of a row and pre-reduces their
-// contributions per source column in registers (they share 1-2 source columns), so the shared-memory atomics are a
-// quarter of the naive count.
-constexpr int kLrTH = 16, kLrTW = 64;
+// emits the gradient of the class map directly instead of writing 352 MB of dlogits and reading them again in the
+// upsample adjoint.
+//
+// One CTA = a 32 x 128 tile of target pixels, its class-map footprint (FH x FW cells) staged in shared memory with an
+// odd cell stride.  One thread = a 4 x 4 patch of pixels: the patch reads an NCELL x NCELL window of cells (3 for an
+// upsample of x3 or more, 4 down to x1.5), so per class it loads 9-16 values for 16 pixels, and both the interpolation
+// and its adjoint are two small dense contractions with per-thread constant weight tables (zeros where a pixel does not
+// touch a cell) — no divergent indexing, no shared-memory float atomics (those are CAS loops on this architecture).
+// Passes over the classes: max, sum (+ target logit), and in backward a third that forms (softmax - onehot) * g / count,
+// contracts it to the patch's cell window, and exchanges the windows through shared memory: each footprint cell has a
+// K x K group of slots, one per patch whose window covers it (the covering patches are K or fewer consecutive patch
+// columns / rows, so a patch's slot is its distance from the first of them), and one thread per cell adds the group up
+// (a deterministic gather) into the staged tile, which is flushed with one coalesced fp32 atomic per element (tiles
+// overlap by the interpolation halo).
+constexpr int kCmP = 4, kCmPX = 32, kCmPY = 8;                 // patch edge, patches per tile in x / y
+constexpr int kCmTW = kCmP * kCmPX, kCmTH = kCmP * kCmPY;      // 128 x 32 target pixels per CTA
 
-template <int NCMAX, bool BWD>
-__global__ void __launch_bounds__(256, BWD ? 2 : 4) lowres_ce_kernel(const float* __restrict__ lr, int ct, int h, int w, int nc,
-                                                         const int64_t* __restrict__ tgt, int H, int W, float sh, float sw,
-                                                         int ac, int64_t ignore_index, double* loss_sum,
-                                                         unsigned long long* valid_count, int* status,
-                                                         float* __restrict__ dlr, const float* __restrict__ g_dev,
-                                                         const unsigned long long* __restrict__ count_dev, int FH, int FW) {
+// exchange geometry: K = most patch columns (rows) whose window can cover one cell, KS = floats per cell group
+template <int NCELL> struct CmExchange;
+template <> struct CmExchange<3> { static constexpr int K = 4, KS = 20; };    // 16 slots + 4 pad: conflict-free LDS.128
+template <> struct CmExchange<4> { static constexpr int K = 3, KS = 9; };
+
+template <int NCELL, bool BWD>
+__global__ void __launch_bounds__(256, 2) class_map_ce_kernel(const float* __restrict__ lr, int ct, int h, int w, int nc,
+                                                              const int64_t* __restrict__ tgt, int H, int W, float sh,
+                                                              float sw, int ac, int64_t ignore_index, double* loss_sum,
+                                                              unsigned long long* valid_count, int* status,
+                                                              float* __restrict__ dlr, const float* __restrict__ g_dev,
+                                                              const unsigned long long* __restrict__ count_dev, int FH,
+                                                              int FW, int nbuf) {
     pdl_prologue();
+    constexpr int P = kCmP, K = CmExchange<NCELL>::K, KS = CmExchange<NCELL>::KS;
     extern __shared__ __align__(16) float lsm[];
-    float* L = lsm;                               // [FH][FW][ct] staged class map
-    float* G = lsm + FH * FW * ct;                // [FH][FW][ct] gradient accumulator (backward only)
-    const int n = blockIdx.z, ty0 = blockIdx.y * kLrTH, tx0 = blockIdx.x * kLrTW;
+    __shared__ int bxs[kCmPX], bys[kCmPY];
+    __shared__ int xlo[160], ylo[64];                         // FW <= 160, FH <= 64 (checked by the launcher)
+    const int ctp = ct | 1;                                   // ct % 4 == 0 -> odd stride, conflict-free across cells
+    const int cells = FH * FW;
+    float* L = lsm;                                           // [cells][ctp]; in backward overwritten class by class with the gradient
+    float* T = lsm + ((cells * ctp + 3) & ~3);                // [nbuf][cells][KS] exchange slots (backward)
+    const int n = blockIdx.z, ty0 = blockIdx.y * kCmTH, tx0 = blockIdx.x * kCmTW;
     const int fy0 = bilinear_src(sh, ty0, h, ac).i0, fx0 = bilinear_src(sw, tx0, w, ac).i0;
     const float* base = lr + static_cast<int64_t>(n) * h * w * ct;
-    const int cells = FH * FW;
-    for (int i = threadIdx.x; i < cells * (ct >> 2); i += blockDim.x) {
-        const int q = i % (ct >> 2), cell = i / (ct >> 2);
+    const int ctq = ct >> 2;
+    for (int i = threadIdx.x; i < cells * ctq; i += blockDim.x) {
+        const int q = i % ctq, cell = i / ctq;
         const int yy = fy0 + cell / FW, xx = fx0 + cell % FW;
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
         if (yy < h && xx < w) v = __ldg(reinterpret_cast<const float4*>(base + (static_cast<int64_t>(yy) * w + xx) * ct) + q);
-        reinterpret_cast<float4*>(L)[i] = v;
-        if (BWD) reinterpret_cast<float4*>(G)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        float* d = L + cell * ctp + 4 * q;
+        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
     }
+    const int pxi = threadIdx.x & (kCmPX - 1), pyi = threadIdx.x / kCmPX;
+    // per-thread weight tables: WX[j][cell] = weight of cell (window-relative) in pixel column j of the patch
+    float WX[P][NCELL], WY[P][NCELL];
+    int bx, by;
+    {
+        const Lerp l0 = bilinear_src(sw, min(tx0 + pxi * P, W - 1), w, ac);
+        bx = l0.i0 - fx0;
+#pragma unroll
+        for (int j = 0; j < P; ++j) {
+            const Lerp l = bilinear_src(sw, min(tx0 + pxi * P + j, W - 1), w, ac);
+            const int r0 = l.i0 - fx0 - bx, r1 = l.i1 - fx0 - bx;
+#pragma unroll
+            for (int cx = 0; cx < NCELL; ++cx) WX[j][cx] = (cx == r0 ? l.w0 : 0.f) + (cx == r1 ? l.w1 : 0.f);
+        }
+        const Lerp m0 = bilinear_src(sh, min(ty0 + pyi * P, H - 1), h, ac);
+        by = m0.i0 - fy0;
+#pragma unroll
+        for (int i = 0; i < P; ++i) {
+            const Lerp l = bilinear_src(sh, min(ty0 + pyi * P + i, H - 1), h, ac);
+            const int r0 = l.i0 - fy0 - by, r1 = l.i1 - fy0 - by;
+#pragma unroll
+            for (int cy = 0; cy < NCELL; ++cy) WY[i][cy] = (cy == r0 ? l.w0 : 0.f) + (cy == r1 ? l.w1 : 0.f);
+        }
+    }
+    if (BWD) {
+        if (pyi == 0) bxs[pxi] = bx;
+        if (pxi == 0) bys[pyi] = by;
+    }
+    // window offsets into L (cells past the footprint edge carry zero weight; clamp them onto staged data)
+    int off[NCELL][NCELL];
+#pragma unroll
+    for (int cy = 0; cy < NCELL; ++cy)
+#pragma unroll
+        for (int cx = 0; cx < NCELL; ++cx) off[cy][cx] = (min(by + cy, FH - 1) * FW + min(bx + cx, FW - 1)) * ctp;
+    // targets of the patch: class code per pixel, 255 = not counted (ignored, out of range, outside the image)
+    unsigned int tcode[P];
+    bool bad = false;
+#pragma unroll
+    for (int i = 0; i < P; ++i) {
+        tcode[i] = 0;
+        const int oy = ty0 + pyi * P + i;
+#pragma unroll
+        for (int j = 0; j < P; ++j) {
+            const int ox = tx0 + pxi * P + j;
+            unsigned int code = 255u;
+            if (oy < H && ox < W) {
+                const int64_t t = __ldcs(tgt + (static_cast<int64_t>(n) * H + oy) * W + ox);
+                if (t != ignore_index) {
+                    if (t < 0 || t >= nc) bad = true;
+                    else code = static_cast<unsigned int>(t);
+                }
+            }
+            tcode[i] |= code << (8 * j);
+        }
+    }
+    if (!BWD && bad && status) *status = 1;
     __syncthreads();
-    float gscale = 1.f;
-    if (BWD) gscale = __ldg(g_dev) / static_cast<float>(__ldg(count_dev));
-    const int ry = threadIdx.x >> 4, cg = threadIdx.x & 15;
-    const int oy = ty0 + ry;
-    double lsum = 0.0;
-    unsigned int lcount = 0;
-    if (oy < H) {
-        const Lerp ly = bilinear_src(sh, oy, h, ac);
-        const int y0 = ly.i0 - fy0, y1 = ly.i1 - fy0;
-        float acc0[NCMAX], acc1[NCMAX];
-        int cur = -1;
-        auto flush = [&]() {
-            if (cur < 0) return;
-            float* g00 = G + (y0 * FW + cur) * ct;
-            float* g10 = G + (y1 * FW + cur) * ct;
+
+    // interpolated logits of the patch for class c: rows of the window contracted with WX, then with WY
+    auto patch_logits = [&](int c, float (&v)[P][P]) {
+        float Hrow[NCELL][P];
 #pragma unroll
-            for (int c = 0; c < NCMAX; ++c) {
-                if (c < nc) {
-                    atomicAdd(g00 + c, ly.w0 * acc0[c]);
-                    if (ly.w1 != 0.f) atomicAdd(g10 + c, ly.w1 * acc0[c]);
-                    if (cur + 1 < FW) {
-                        atomicAdd(g00 + ct + c, ly.w0 * acc1[c]);
-                        if (ly.w1 != 0.f) atomicAdd(g10 + ct + c, ly.w1 * acc1[c]);
-                    }
-                }
-            }
-        };
-#pragma unroll 1
-        for (int j = 0; j < 4; ++j) {
-            const int ox = tx0 + cg * 4 + j;
-            if (ox >= W) break;
-            const Lerp lx = bilinear_src(sw, ox, w, ac);
-            const int x0 = lx.i0 - fx0, x1 = lx.i1 - fx0;
-            const float* p00 = L + (y0 * FW + x0) * ct;
-            const float* p01 = L + (y0 * FW + x1) * ct;
-            const float* p10 = L + (y1 * FW + x0) * ct;
-            const float* p11 = L + (y1 * FW + x1) * ct;
-            float v[NCMAX];
-            float m = -INFINITY;
+        for (int cy = 0; cy < NCELL; ++cy) {
+            float C[NCELL];
 #pragma unroll
-            for (int c = 0; c < NCMAX; ++c) {
-                // same expression as logits_up_fwd_kernel, so the loss is the loss of the logits the model returned
-                v[c] = c < nc ? ly.w0 * (lx.w0 * p00[c] + lx.w1 * p01[c]) + ly.w1 * (lx.w0 * p10[c] + lx.w1 * p11[c]) : -INFINITY;
-                m = fmaxf(m, v[c]);
-            }
-            float s = 0.f;
+            for (int cx = 0; cx < NCELL; ++cx) C[cx] = L[off[cy][cx] + c];
 #pragma unroll
-            for (int c = 0; c < NCMAX; ++c) {
-                v[c] = c < nc ? __expf(v[c] - m) : 0.f;
-                s += v[c];
-            }
-            const int64_t t = __ldcs(tgt + (static_cast<int64_t>(n) * H + oy) * W + ox);
-            const bool ignored = (t == ignore_index);
-            const bool bad = !ignored && (t < 0 || t >= nc);
-            if (bad && status) *status = 1;
-            const bool valid = !ignored && !bad;
-            if (!BWD) {
-                if (valid) {
-                    // log-softmax at the target: the interpolated logit is recomputed rather than indexed dynamically
-                    const int tc = static_cast<int>(t);
-                    const float xt = ly.w0 * (lx.w0 * p00[tc] + lx.w1 * p01[tc]) + ly.w1 * (lx.w0 * p10[tc] + lx.w1 * p11[tc]);
-                    lsum += static_cast<double>(__logf(s) + m - xt);
-                    ++lcount;
-                }
-                continue;
-            }
-            if (x0 != cur) {
-                flush();
-                cur = x0;
+            for (int j = 0; j < P; ++j) {
+                float a = WX[j][0] * C[0];
 #pragma unroll
-                for (int c = 0; c < NCMAX; ++c) acc0[c] = acc1[c] = 0.f;
-            }
-            const float inv = valid ? gscale / s : 0.f;
-            const float a0 = x1 == x0 ? lx.w0 + lx.w1 : lx.w0, a1 = x1 == x0 ? 0.f : lx.w1;
-#pragma unroll
-            for (int c = 0; c < NCMAX; ++c) {
-                const float d = v[c] * inv - ((valid && c == t) ? gscale : 0.f);
-                acc0[c] = fmaf(a0, d, acc0[c]);
-                acc1[c] = fmaf(a1, d, acc1[c]);
+                for (int cx = 1; cx < NCELL; ++cx) a = fmaf(WX[j][cx], C[cx], a);
+                Hrow[cy][j] = a;
             }
         }
-        if (BWD) flush();
+#pragma unroll
+        for (int i = 0; i < P; ++i)
+#pragma unroll
+            for (int j = 0; j < P; ++j) {
+                float a = WY[i][0] * Hrow[0][j];
+#pragma unroll
+                for (int cy = 1; cy < NCELL; ++cy) a = fmaf(WY[i][cy], Hrow[cy][j], a);
+                v[i][j] = a;
+            }
+    };
+
+    float m[P][P], s[P][P], vt[P][P];
+#pragma unroll
+    for (int i = 0; i < P; ++i)
+#pragma unroll
+        for (int j = 0; j < P; ++j) m[i][j] = -INFINITY, s[i][j] = 0.f, vt[i][j] = 0.f;
+#pragma unroll 1
+    for (int c = 0; c < nc; ++c) {
+        float v[P][P];
+        patch_logits(c, v);
+#pragma unroll
+        for (int i = 0; i < P; ++i)
+#pragma unroll
+            for (int j = 0; j < P; ++j) m[i][j] = fmaxf(m[i][j], v[i][j]);
+    }
+#pragma unroll 1
+    for (int c = 0; c < nc; ++c) {
+        float v[P][P];
+        patch_logits(c, v);
+#pragma unroll
+        for (int i = 0; i < P; ++i)
+#pragma unroll
+            for (int j = 0; j < P; ++j) {
+                s[i][j] += __expf(v[i][j] - m[i][j]);
+                if (!BWD) vt[i][j] = (((tcode[i] >> (8 * j)) & 255u) == static_cast<unsigned int>(c)) ? v[i][j] : vt[i][j];
+            }
     }
     if (!BWD) {
+        double lsum = 0.0;
+        unsigned int lcount = 0;
+#pragma unroll
+        for (int i = 0; i < P; ++i)
+#pragma unroll
+            for (int j = 0; j < P; ++j)
+                if (((tcode[i] >> (8 * j)) & 255u) != 255u) {
+                    lsum += static_cast<double>(__logf(s[i][j]) + m[i][j] - vt[i][j]);
+                    ++lcount;
+                }
         lsum = warp_sum(lsum);
         lcount = __reduce_add_sync(0xffffffffu, lcount);
         __shared__ double ssum[8];
@@ -612,13 +669,96 @@ __global__ void __launch_bounds__(256, BWD ? 2 : 4) lowres_ce_kernel(const float
         }
         return;
     }
+
+    // ---- backward ----
+    // first patch column / row whose window covers footprint column X / row Y (window origins are monotonic)
+    for (int X = threadIdx.x; X < FW; X += blockDim.x) {
+        int lo = 0;
+        while (lo < kCmPX - 1 && bxs[lo] + NCELL <= X) ++lo;
+        xlo[X] = lo;
+    }
+    for (int Y = threadIdx.x; Y < FH; Y += blockDim.x) {
+        int lo = 0;
+        while (lo < kCmPY - 1 && bys[lo] + NCELL <= Y) ++lo;
+        ylo[Y] = lo;
+    }
+    for (int i = threadIdx.x; i < nbuf * cells * KS; i += blockDim.x) T[i] = 0.f;   // slots nobody owns stay zero
+    const float gscale = __ldg(g_dev) / static_cast<float>(__ldg(count_dev));
+#pragma unroll
+    for (int i = 0; i < P; ++i)
+#pragma unroll
+        for (int j = 0; j < P; ++j) s[i][j] = (((tcode[i] >> (8 * j)) & 255u) != 255u) ? gscale / s[i][j] : 0.f;
+    __syncthreads();
+    // this patch's slot for each cell of its window (-1: the cell lies outside the footprint, its weights are zero)
+    int wofs[NCELL][NCELL];
+#pragma unroll
+    for (int cy = 0; cy < NCELL; ++cy)
+#pragma unroll
+        for (int cx = 0; cx < NCELL; ++cx) {
+            wofs[cy][cx] = -1;
+            if (by + cy < FH && bx + cx < FW) {
+                const int ky = pyi - ylo[by + cy], kx = pxi - xlo[bx + cx];
+                if (ky >= 0 && ky < K && kx >= 0 && kx < K) wofs[cy][cx] = ((by + cy) * FW + bx + cx) * KS + ky * K + kx;
+            }
+        }
+    int buf = 0;
+#pragma unroll 1
+    for (int c = 0; c < nc; ++c) {
+        float v[P][P];
+        patch_logits(c, v);
+        float Hacc[P][NCELL];
+#pragma unroll
+        for (int i = 0; i < P; ++i) {
+#pragma unroll
+            for (int j = 0; j < P; ++j) {
+                const bool hit = ((tcode[i] >> (8 * j)) & 255u) == static_cast<unsigned int>(c);
+                v[i][j] = __expf(v[i][j] - m[i][j]) * s[i][j] - (hit ? gscale : 0.f);
+            }
+#pragma unroll
+            for (int cx = 0; cx < NCELL; ++cx) {
+                float a = WX[0][cx] * v[i][0];
+#pragma unroll
+                for (int j = 1; j < P; ++j) a = fmaf(WX[j][cx], v[i][j], a);
+                Hacc[i][cx] = a;
+            }
+        }
+        float* Tb = T + buf * cells * KS;
+#pragma unroll
+        for (int cy = 0; cy < NCELL; ++cy)
+#pragma unroll
+            for (int cx = 0; cx < NCELL; ++cx) {
+                float a = WY[0][cy] * Hacc[0][cx];
+#pragma unroll
+                for (int i = 1; i < P; ++i) a = fmaf(WY[i][cy], Hacc[i][cx], a);
+                if (wofs[cy][cx] >= 0) Tb[wofs[cy][cx]] = a;
+            }
+        __syncthreads();
+        for (int cell = threadIdx.x; cell < cells; cell += blockDim.x) {
+            float a;
+            if (NCELL == 3) {
+                const float4* q = reinterpret_cast<const float4*>(Tb + cell * KS);
+                const float4 a0 = q[0], a1 = q[1], a2 = q[2], a3 = q[3];
+                a = ((a0.x + a0.y) + (a0.z + a0.w)) + ((a1.x + a1.y) + (a1.z + a1.w)) +
+                    (((a2.x + a2.y) + (a2.z + a2.w)) + ((a3.x + a3.y) + (a3.z + a3.w)));
+            } else {
+                a = 0.f;
+#pragma unroll
+                for (int k = 0; k < K * K; ++k) a += Tb[cell * KS + k];
+            }
+            L[cell * ctp + c] = a;        // class c of the staged map is dead from here on: reuse it for the gradient
+        }
+        if (nbuf == 2) buf ^= 1;
+        else __syncthreads();
+    }
     __syncthreads();
     float* out = dlr + static_cast<int64_t>(n) * h * w * ct;
     for (int i = threadIdx.x; i < cells * ct; i += blockDim.x) {
         const int c = i % ct, cell = i / ct;
         const int yy = fy0 + cell / FW, xx = fx0 + cell % FW;
-        const float v = G[i];
-        if (c < nc && yy < h && xx < w && v != 0.f) atomicAdd(out + (static_cast<int64_t>(yy) * w + xx) * ct + c, v);
+        if (c < nc && yy < h && xx < w) {
+            const float v = L[cell * ctp + c];
+            if (v != 0.f) atomicAdd(out + (static_cast<int64_t>(yy) * w + xx) * ct + c, v);
+        }
     }
 }
 
@@ -648,26 +788,46 @@ int launch_lowres_ce(const float* lr, int n, int h, int w, int ct, int nc, const
                      int align_corners, int64_t ignore_index, double* loss_sum, int64_t* valid_count, int* status, float* dlr,
                      const float* g_dev, const int64_t* count_dev, cudaStream_t st) {
     const float sh = bilinear_scale(h, H, align_corners), sw = bilinear_scale(w, W, align_corners);
-    // footprint of a 16 x 64 target tile in the class map (+1 for the second lerp tap, +1 for rounding)
-    const int FH = static_cast<int>(kLrTH * sh) + 3 < h ? static_cast<int>(kLrTH * sh) + 3 : h;
-    const int FW = static_cast<int>(kLrTW * sw) + 3 < w ? static_cast<int>(kLrTW * sw) + 3 : w;
-    const size_t smem = static_cast<size_t>(FH) * FW * ct * sizeof(float) * (dlr ? 2 : 1);
-    B200SEG_CHECK(smem <= 48 * 1024, "lowres_ce: class-map footprint of %zu bytes per tile exceeds shared memory", smem);
-    B200SEG_CHECK(n <= 65535 && ceil_div(H, kLrTH) <= 65535, "lowres_ce: grid too large");
-    dim3 grid(ceil_div(W, kLrTW), ceil_div(H, kLrTH), n);
+    // cells a 4-pixel run can touch: floor(3 * scale) + 3
+    const float smax = sh > sw ? sh : sw;
+    const int ncell = static_cast<int>(3.f * smax) + 3;
+    B200SEG_CHECK(ncell <= 4, "lowres_ce: upsample factor below 1.5 (class map %dx%d, targets %dx%d)", h, w, H, W);
+    // footprint of a 32 x 128 target tile in the class map (+1 for the second lerp tap, +1 for rounding)
+    const int FH = static_cast<int>(kCmTH * sh) + 3 < h ? static_cast<int>(kCmTH * sh) + 3 : h;
+    const int FW = static_cast<int>(kCmTW * sw) + 3 < w ? static_cast<int>(kCmTW * sw) + 3 : w;
+    B200SEG_CHECK(FH <= 64 && FW <= 160, "lowres_ce: footprint %dx%d too large", FH, FW);
+    // patch columns covering one cell: window origins advance by >= floor(4 * scale) cells per patch
+    const float smin = sh < sw ? sh : sw;
+    const int kmax = ncell == 3 ? 4 : 3, ks = ncell == 3 ? 20 : 9;
+    B200SEG_CHECK(smin > 0.f && static_cast<int>((ncell - 1) / (4.f * smin)) + 2 <= kmax,
+                  "lowres_ce: upsample factor not supported (class map %dx%d, targets %dx%d)", h, w, H, W);
+    const size_t lbytes = sizeof(float) * ((static_cast<size_t>(FH) * FW * (ct | 1) + 3) & ~size_t(3));
+    const size_t tbytes = sizeof(float) * static_cast<size_t>(FH) * FW * ks;
+    const size_t limit = 110 * 1024;
+    int nbuf = dlr ? (lbytes + 2 * tbytes <= limit ? 2 : 1) : 0;
+    const size_t smem = lbytes + nbuf * tbytes;
+    B200SEG_CHECK(smem <= limit, "lowres_ce: class-map footprint of %zu bytes per tile exceeds shared memory", smem);
+    B200SEG_CHECK(n <= 65535 && ceil_div(H, kCmTH) <= 65535, "lowres_ce: grid too large");
+    dim3 grid(ceil_div(W, kCmTW), ceil_div(H, kCmTH), n);
     unsigned long long* vc = reinterpret_cast<unsigned long long*>(valid_count);
     const unsigned long long* cd = reinterpret_cast<const unsigned long long*>(count_dev);
-#define B200SEG_LRCE(NC, B)                                                                                              \
-    B200SEG_CUDA(launch_pdl(lowres_ce_kernel<NC, B>, grid, 256, smem, st, lr, ct, h, w, nc, targets, H, W, sh, sw,           \
-                            align_corners, ignore_index, loss_sum, vc, status, dlr, g_dev, cd, FH, FW))
+#define B200SEG_LRCE(NCELL, B)                                                                                             \
+    do {                                                                                                                   \
+        static bool attr_set = false;                                                                                      \
+        if (!attr_set) {                                                                                                   \
+            B200SEG_CUDA(cudaFuncSetAttribute(class_map_ce_kernel<NCELL, B>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+                                              110 * 1024));                                                                \
+            attr_set = true;                                                                                               \
+        }                                                                                                                  \
+        B200SEG_CUDA(launch_pdl(class_map_ce_kernel<NCELL, B>, grid, 256, smem, st, lr, ct, h, w, nc, targets, H, W, sh,   \
+                                sw, align_corners, ignore_index, loss_sum, vc, status, dlr, g_dev, cd, FH, FW, nbuf));     \
+    } while (0)
     if (dlr) {
-        if (nc <= 8) B200SEG_LRCE(8, true);
-        else if (nc <= 24) B200SEG_LRCE(24, true);
-        else B200SEG_LRCE(32, true);
+        if (ncell == 3) B200SEG_LRCE(3, true);
+        else B200SEG_LRCE(4, true);
     } else {
-        if (nc <= 8) B200SEG_LRCE(8, false);
-        else if (nc <= 24) B200SEG_LRCE(24, false);
-        else B200SEG_LRCE(32, false);
+        if (ncell == 3) B200SEG_LRCE(3, false);
+        else B200SEG_LRCE(4, false);
     }
 #undef B200SEG_LRCE
     return 0;

@@ -800,13 +800,20 @@ def _lowres_geometry(lr, targets):
     return n, h, w, ct, targets.shape[1], targets.shape[2]
 
 
-def lowres_ce_supported(lr_shape, nc, th, tw):
-    """The fused loss stages the class-map footprint of a 16 x 64 target tile (twice, in backward) in 48 KB."""
+def lowres_ce_supported(lr_shape, nc, th, tw, align_corners=True):
+    """Mirror of launch_lowres_ce's checks (csrc/loss_metrics.cu), slightly conservative: an upsample of x1.5 to ~x5
+    (a 4-pixel run touches <= 4 cells, <= 4 patch windows cover a cell) and the footprint of a 32 x 128 target tile plus
+    the exchange slots in 110 KB of shared memory.  Anything else takes the logits path."""
     n, h, w, ct = lr_shape
-    if th < h or tw < w or nc > 32:
+    if nc > 32 or th <= h or tw <= w or h < 2 or w < 2:
         return False
-    fh, fw = min(16 * h // th + 3, h), min(64 * w // tw + 3, w)
-    return 2 * fh * fw * ct * 4 <= 48 * 1024
+    sh, sw = ((h - 1) / (th - 1), (w - 1) / (tw - 1)) if align_corners else (h / th, w / tw)
+    ncell = int(3 * max(sh, sw) * (1 + 1e-6)) + 3
+    if ncell > 4 or int((ncell - 1) / (4 * min(sh, sw) * (1 - 1e-6))) + 2 > (4 if ncell == 3 else 3):
+        return False
+    fh, fw = min(int(32 * sh) + 3, h), min(int(128 * sw) + 3, w)
+    cells = fh * fw
+    return fh <= 64 and fw <= 160 and 4 * ((cells * (ct | 1) + 3) // 4 * 4 + cells * (20 if ncell == 3 else 9)) <= 110 * 1024
 
 
 def lowres_ce_fwd(lr, nc, targets, align_corners=True, ignore_index=-100):

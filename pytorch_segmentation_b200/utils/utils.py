@@ -71,7 +71,7 @@ def compute_loss(outputs, targets, model=None):
     cm = getattr(outputs, '_b200seg_class_map', None)
     if (cm is not None and cm[3] == outputs._version and targets.is_cuda and targets.dtype == torch.int64
             and tuple(outputs.shape[2:]) == tuple(targets.shape[1:]) and E.LOWRES_CE
-            and E.lowres_ce_supported(cm[0].shape, cm[1], targets.shape[1], targets.shape[2])):
+            and E.lowres_ce_supported(cm[0].shape, cm[1], targets.shape[1], targets.shape[2], cm[2])):
         return _ClassMapCrossEntropyFn.apply(cm[0], targets.contiguous(), cm[1], cm[2])
     return _CrossEntropyFn.apply(outputs, targets)
 

@@ -645,7 +645,7 @@ def test_lowres_ce_matches_interpolate_cross_entropy(E, n, h, w, scale, nc, ct, 
     # the same numbers as the unfused path the model falls back to (upsampled logits -> softmax_ce)
     logits = E.logits_upsample_fwd(lr_d, nc, H, W, align_corners=ac)
     acc2, _ = E.softmax_ce(logits, t_d, want_grad=False)
-    assert abs(float(E.ce_finalize(acc2)) - float(loss)) <= 2e-6 * abs(float(loss))
+    assert abs(float(E.ce_finalize(acc2)) - float(loss)) <= 1e-5 * abs(float(loss))
     # bf16 Act for the classifier backward, with and without a second gradient through the logits
     a = E.class_map_grad(dlr)
     assert rel_err(a.t.float(), dlr) < 4e-3
