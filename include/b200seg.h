@@ -64,6 +64,19 @@ int b200seg_pack_weights_im2col(const float* w_oihw, int k, int c, int r, int s,
                                 b200seg_stream_t st);
 int b200seg_unpack_wgrad_im2col(const float* dw_col, int k, int c, int r, int s, int c_pad, float* dw_oihw,
                                 int accumulate, b200seg_stream_t st);
+/* Space-to-depth form of a stride-2 r x s conv over c <= 4 channels (ResNet-50's 7x7 conv1, torchvision resnet.py via
+ * models/deeplabv3plus.py:17; HRNet's ConvNormAct(3, 64, 3, 2), models/hrnet.py:260) — replaces the gathered matrix:
+ * z[n][Y][X][(2b + b')*c + ch] = x[n][ch][2Y + b - pad][2X + b' - pad] (bf16, cs = 4c rounded up to 8 channels, 0 outside
+ * the image) on a (oh + ceil(r/2) - 1) x (ow + ceil(s/2) - 1) grid; the conv is then ceil(r/2) row taps over windows of
+ * ceil(s/2)*cs contiguous elements: an anchored window source of b200seg_conv_fprop / b200seg_conv_wgrad with
+ * x_rows, x_cols = that grid, x_c_total = cs, c = ceil(s/2)*cs, taps ceil(r/2) x 1. */
+int b200seg_space_to_depth_nchw(const float* x, int n, int c, int h, int w, int r, int s, int pad, void* z, int cs,
+                                b200seg_stream_t st);
+/* wp[a][kk][a'*cs + (2b + b')*c + ch] = w[kk][ch][2a + b][2a' + b'] (bf16 [ceil(r/2)][k_rows][ceil(s/2)*cs]) */
+int b200seg_pack_weights_s2d(const float* w, int k, int c, int r, int s, void* wp, int k_rows, int cs, b200seg_stream_t st);
+/* dw[kk][ch][r][s] (+)= dwin[kk][a'*cs + (2b + b')*c + ch][a] — dwin is b200seg_conv_wgrad's [k][ceil(s/2)*cs][ceil(r/2)][1] */
+int b200seg_unpack_wgrad_s2d(const float* dwin, int k, int c, int r, int s, int cs, float* dw, int accumulate,
+                             b200seg_stream_t st);
 
 /* Narrow-output 3x3 convolutions (cls_conv, models/deeplabv3plus.py:22,39 and models/unet.py:23,51: 384 -> 21 / 88 -> nc
  * classes) restated so the wide input is read once instead of once per tap (see csrc/taps.cu):
@@ -125,6 +138,13 @@ typedef struct b200seg_conv_src {
     int32_t dil;          /* dilation; padding is ((r-1)/2)*dil */
     int32_t stride;       /* 1 or 2 (2 needs dil == 1).  fprop: x is (stride*h) x (stride*w).  dgrad: x (= dY) is
                              (h/stride) x (w/stride) and the call's n,h,w is the dX grid */
+    int32_t x_rows, x_cols; /* 0, 0: regular source.  Otherwise an ANCHORED WINDOW source (fprop only, the single source
+                             of the call): x is an [n][x_rows][x_cols][x_c_total] buffer that carries its own padding
+                             and tap (i, j) of the r x s (r*s <= 9) filter reads, for output pixel (y, x), the c
+                             CONTIGUOUS elements that start at channel x_c_offset of buffer pixel (y + i, x + j).  c may
+                             exceed x_c_total: the window then runs on into the following pixels, so neighbouring
+                             windows overlap — how the space-to-depth stem (b200seg_space_to_depth_nchw) turns a
+                             strided few-channel conv into row taps over 64-element windows without a gathered matrix */
 } b200seg_conv_src;
 
 typedef struct b200seg_conv_out {
@@ -166,6 +186,8 @@ typedef struct b200seg_wgrad_desc {
     int32_t accumulate;   /* dw += result instead of dw = result */
     void* workspace;
     size_t workspace_bytes;
+    int32_t x_rows, x_cols; /* 0, 0: regular.  Otherwise x is an anchored window buffer as in b200seg_conv_src (dil = 1,
+                             stride = 1, r*s <= 9): dw[k][c][r][s] is the gradient of the window weights */
 } b200seg_wgrad_desc;
 
 size_t b200seg_conv_wgrad_workspace(const b200seg_wgrad_desc* d);

@@ -17,7 +17,7 @@ class ConvSrc(Structure):
     """struct b200seg_conv_src"""
     _fields_ = [('x', c_void_p), ('x_c_total', c_int32), ('x_c_offset', c_int32), ('c', c_int32),
                 ('w', c_void_p), ('w_rows', c_int32), ('r', c_int32), ('s', c_int32), ('dil', c_int32),
-                ('stride', c_int32)]
+                ('stride', c_int32), ('x_rows', c_int32), ('x_cols', c_int32)]
 
 
 class ConvOut(Structure):
@@ -34,7 +34,7 @@ class WgradDesc(Structure):
                 ('x', c_void_p), ('x_c_total', c_int32), ('x_c_offset', c_int32), ('c', c_int32),
                 ('r', c_int32), ('s', c_int32), ('dil', c_int32), ('stride', c_int32),
                 ('dw', c_void_p), ('k_out', c_int32), ('accumulate', c_int32),
-                ('workspace', c_void_p), ('workspace_bytes', c_size_t)]
+                ('workspace', c_void_p), ('workspace_bytes', c_size_t), ('x_rows', c_int32), ('x_cols', c_int32)]
 
 
 class PackDesc(Structure):
@@ -66,6 +66,9 @@ PROTOTYPES = {
     'b200seg_im2col_nchw': (c_int, [_P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _I, _P]),
     'b200seg_pack_weights_im2col': (c_int, [_P, _I, _I, _I, _I, _P, _I, _I, _P]),
     'b200seg_unpack_wgrad_im2col': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _P]),
+    'b200seg_space_to_depth_nchw': (c_int, [_P, _I, _I, _I, _I, _I, _I, _I, _P, _I, _P]),
+    'b200seg_pack_weights_s2d': (c_int, [_P, _I, _I, _I, _I, _P, _I, _I, _P]),
+    'b200seg_unpack_wgrad_s2d': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _P]),
     'b200seg_tap_gather': (c_int, [_P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P, _I, _P]),
     'b200seg_tap_scatter_add': (c_int, [_P, _I, _I, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     'b200seg_pack_weights_taps': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _P, _I, _P]),

@@ -79,6 +79,7 @@ struct __align__(64) IgemmParams {
     float* stats;
     long long* dbg;
     int dbg_slots;
+    int no_skip;             // anchored window sources: the buffer carries its own padding, every tap is in bounds
 };
 
 long long* g_dbg = nullptr;
@@ -106,6 +107,7 @@ __device__ __forceinline__ TileCoord decode_tile(const IgemmParams& p, int tile)
 }
 
 __device__ __forceinline__ bool tap_in_bounds(const IgemmParams& p, const TileCoord& t, int dy, int dx) {
+    if (p.no_skip) return true;
     return (t.y0 + dy < p.H) && (t.y0 + p.bh - 1 + dy >= 0) && (t.x0 + dx < p.W) && (t.x0 + p.bw - 1 + dx >= 0);
 }
 
@@ -492,12 +494,16 @@ struct OutPlan {
 };
 
 // Total pipeline iterations (TMA box pairs) the whole problem costs with a bw x bh x bi patch.
-long long patch_cost(int N, int H, int W, int bw, int bh, int bi, int nseg, const SegPlan* sp) {
+long long patch_cost(int N, int H, int W, int bw, int bh, int bi, int nseg, const SegPlan* sp, bool no_skip) {
     const int tx = ceil_div(W, bw), ty = ceil_div(H, bh), ti = ceil_div(N, bi);
     long long per_image = 0;
     for (int g = 0; g < nseg; ++g) {
         const IgemmSeg& seg = sp[g].seg;
         for (int tp = 0; tp < seg.ntaps; ++tp) {
+            if (no_skip) {
+                per_image += static_cast<long long>(ty) * tx * seg.cblks;
+                continue;
+            }
             const int dy = seg.dy[tp], dx = seg.dx[tp];
             // the in-bounds test is separable: count tile rows and tile columns that touch the image
             int ny = 0, nx = 0;
@@ -511,9 +517,10 @@ long long patch_cost(int N, int H, int W, int bw, int bh, int bi, int nseg, cons
 
 // Encodes the maps and launches the persistent kernel over an n x h x w output grid.
 int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPlan& op, const b200seg_conv_out* out,
-                   cudaStream_t st) {
+                   cudaStream_t st, bool no_skip = false) {
     IgemmParams p;
     memset(&p, 0, sizeof(p));
+    p.no_skip = no_skip ? 1 : 0;
     p.nseg = nseg;
     p.N = n;
     p.H = h;
@@ -537,7 +544,7 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
     {
         static std::mutex mu;
         static std::map<std::vector<int>, std::array<int, 3>> memo;
-        std::vector<int> key = {n, h, w, nseg};
+        std::vector<int> key = {n, h, w, nseg, p.no_skip};
         for (int i = 0; i < nseg; ++i) {
             key.push_back(p.seg[i].ntaps);
             key.push_back(p.seg[i].cblks);
@@ -554,7 +561,7 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
             for (int bi = 1; bi <= 128; bi *= 2) {
                 for (int bw = 1; bw * bi <= 128; bw *= 2) {
                     const int bh = 128 / (bw * bi);
-                    const long long c = patch_cost(n, h, w, bw, bh, bi, nseg, sp);
+                    const long long c = patch_cost(n, h, w, bw, bh, bi, nseg, sp, no_skip);
                     if (best < 0 || c < best || (c == best && bw > p.bw)) {
                         best = c;
                         p.bw = bw;
@@ -625,6 +632,21 @@ int check_common(int n, int h, int w, int n_src, const b200seg_conv_src* src, co
     for (int i = 0; i < n_src; ++i) {
         const b200seg_conv_src& s = src[i];
         B200SEG_CHECK(s.x && s.w, "conv: source %d has null pointers", i);
+        if (s.x_rows || s.x_cols) {
+            // anchored window source (include/b200seg.h): geometry checked here, the regular rules do not apply
+            B200SEG_CHECK(n_src == 1, "conv: an anchored window source must be the only source");
+            B200SEG_CHECK(s.r >= 1 && s.s >= 1 && s.r * s.s <= kMaxTaps && s.dil == 1 && s.stride == 1,
+                          "conv: anchored window source with %dx%d taps, dilation %d, stride %d", s.r, s.s, s.dil, s.stride);
+            B200SEG_CHECK(s.c > 0 && s.c % 8 == 0 && s.x_c_offset % 8 == 0 && s.x_c_total % 8 == 0,
+                          "conv: input channels (c=%d, offset=%d, total=%d) must be multiples of 8", s.c, s.x_c_offset,
+                          s.x_c_total);
+            const int span = ceil_div(s.x_c_offset + s.c, s.x_c_total);      // buffer pixels one window touches
+            B200SEG_CHECK(h + s.r - 1 <= s.x_rows && w + s.s - 1 + span - 1 <= s.x_cols,
+                          "conv: %dx%d outputs with %dx%d taps and %d-pixel windows exceed the %dx%d buffer", h, w, s.r,
+                          s.s, span, s.x_rows, s.x_cols);
+            B200SEG_CHECK(s.w_rows >= out->k, "conv: packed weight has %d rows < %d output channels", s.w_rows, out->k);
+            continue;
+        }
         B200SEG_CHECK((s.r == 1 && s.s == 1) || (s.r == 3 && s.s == 3), "conv: only 1x1 and 3x3 filters (got %dx%d)",
                       s.r, s.s);
         B200SEG_CHECK(s.dil >= 1 && s.dil <= 4096, "conv: dilation %d", s.dil);
@@ -674,6 +696,37 @@ int launch_fprop(int n, int h, int w, int n_src, const b200seg_conv_src* src, co
     SegPlan sp[kMaxSeg];
     memset(sp, 0, sizeof(sp));
     int nseg = 0;
+    if (src[0].x_rows || src[0].x_cols) {
+        // anchored window source: tap (r, q) of output pixel (y, x) reads the c contiguous elements that start at
+        // buffer pixel (y + r, x + q) — with c > x_c_total the view's innermost dimension runs on into the following
+        // pixels, i.e. neighbouring windows overlap in memory (the TMA unit only sees strides)
+        const b200seg_conv_src& s = src[0];
+        SegPlan& g = sp[nseg++];
+        const int span = ceil_div(s.x_c_offset + s.c, s.x_c_total);
+        g.a_base = static_cast<const char*>(s.x) + static_cast<size_t>(s.x_c_offset) * 2;
+        g.adims[0] = s.c;
+        g.adims[1] = s.x_cols - span + 1;
+        g.adims[2] = s.x_rows;
+        g.adims[3] = n;
+        g.astr[0] = static_cast<uint64_t>(s.x_c_total) * 2;
+        g.astr[1] = static_cast<uint64_t>(s.x_cols) * s.x_c_total * 2;
+        g.astr[2] = static_cast<uint64_t>(s.x_rows) * s.x_cols * s.x_c_total * 2;
+        g.w = s.w;
+        g.w_rows = s.w_rows;
+        g.c = s.c;
+        g.w_taps = s.r * s.s;
+        g.seg.cblks = ceil_div(s.c, kBK);
+        for (int r = 0; r < s.r; ++r)
+            for (int q = 0; q < s.s; ++q) {
+                const int t = g.seg.ntaps++;
+                g.seg.dy[t] = static_cast<short>(r);
+                g.seg.dx[t] = static_cast<short>(q);
+                g.seg.wtap[t] = static_cast<short>(r * s.s + q);
+            }
+        OutPlan wop;
+        plain_out(&wop, out, n, h, w);
+        return launch_planned(n, h, w, nseg, sp, wop, out, st, true);
+    }
     for (int i = 0; i < n_src; ++i) {
         const b200seg_conv_src& s = src[i];
         if (s.stride == 1) {
@@ -734,7 +787,10 @@ int launch_dgrad(int n, int h, int w, int n_src, const b200seg_conv_src* src, co
     clear_error();
     if (check_common(n, h, w, n_src, src, out)) return 1;
     bool any_s2 = false;
-    for (int i = 0; i < n_src; ++i) any_s2 |= src[i].stride == 2;
+    for (int i = 0; i < n_src; ++i) {
+        any_s2 |= src[i].stride == 2;
+        B200SEG_CHECK(!src[i].x_rows && !src[i].x_cols, "conv dgrad: anchored window sources are forward-only");
+    }
     if (!any_s2) return launch_fprop(n, h, w, n_src, src, out, st);     // same GEMM, mirrored weights
 
     B200SEG_CHECK(h % 2 == 0 && w % 2 == 0, "conv dgrad: stride 2 needs even dX size (got %dx%d)", h, w);

@@ -50,6 +50,7 @@ struct __align__(64) WgradParams {
     int splits, patches_per_split;
     int m_pad, n_pad;      // workspace matrix dims per (split, tap)
     float* ws;
+    int no_skip;           // anchored window X: the buffer carries its own padding, every (tap, patch) is in bounds
 };
 
 // Walks the pixel patches kp = begin, begin+1, ... with running (x, y, image) patch counters: the producer and the
@@ -72,6 +73,7 @@ struct PatchWalker {
         }
     }
     __device__ __forceinline__ bool in_bounds(const WgradParams& p, int dy, int dx) const {
+        if (p.no_skip) return true;
         const int x0 = px * p.bw, y0 = py * p.bh;
         return (y0 + dy < p.H) && (y0 + p.bh - 1 + dy >= 0) && (x0 + dx < p.W) && (x0 + p.bw - 1 + dx >= 0);
     }
@@ -258,9 +260,20 @@ struct WgradPlan {
 int plan_wgrad_uncached(const b200seg_wgrad_desc* d, WgradPlan* pl) {
     B200SEG_CHECK(d && d->dy && d->x && d->dw, "wgrad: null pointer");
     B200SEG_CHECK(d->n > 0 && d->h > 0 && d->w > 0, "wgrad: bad shape");
-    B200SEG_CHECK((d->r == 1 && d->s == 1) || (d->r == 3 && d->s == 3), "wgrad: only 1x1 and 3x3 filters");
-    B200SEG_CHECK(d->stride == 1 || (d->stride == 2 && d->dil == 1), "wgrad: stride %d / dilation %d not supported",
-                  d->stride, d->dil);
+    const bool anchored = d->x_rows || d->x_cols;
+    if (anchored) {
+        B200SEG_CHECK(d->r >= 1 && d->s >= 1 && d->r * d->s <= 9 && d->dil == 1 && d->stride == 1,
+                      "wgrad: anchored window input with %dx%d taps, dilation %d, stride %d", d->r, d->s, d->dil, d->stride);
+        B200SEG_CHECK(d->x_c_total > 0 && d->c > 0, "wgrad: bad window");
+        const int span = ceil_div(d->x_c_offset + d->c, d->x_c_total);
+        B200SEG_CHECK(d->h + d->r - 1 <= d->x_rows && d->w + d->s - 1 + span - 1 <= d->x_cols,
+                      "wgrad: %dx%d grid with %dx%d taps and %d-pixel windows exceeds the %dx%d buffer", d->h, d->w, d->r,
+                      d->s, span, d->x_rows, d->x_cols);
+    } else {
+        B200SEG_CHECK((d->r == 1 && d->s == 1) || (d->r == 3 && d->s == 3), "wgrad: only 1x1 and 3x3 filters");
+        B200SEG_CHECK(d->stride == 1 || (d->stride == 2 && d->dil == 1), "wgrad: stride %d / dilation %d not supported",
+                      d->stride, d->dil);
+    }
     B200SEG_CHECK(d->k % 8 == 0 && d->dy_c_offset % 8 == 0 && d->dy_c_total % 8 == 0 && d->c % 8 == 0 &&
                       d->x_c_offset % 8 == 0 && d->x_c_total % 8 == 0,
                   "wgrad: channel counts/offsets must be multiples of 8");
@@ -291,7 +304,7 @@ int plan_wgrad_uncached(const b200seg_wgrad_desc* d, WgradPlan* pl) {
                                 dx = dx >= 0 ? dx / 2 : -((-dx + 1) / 2);
                             }
                             const int y0 = y * bh, x0 = x * bw;
-                            if ((y0 + dy < d->h) && (y0 + bh - 1 + dy >= 0) && (x0 + dx < d->w) && (x0 + bw - 1 + dx >= 0))
+                            if (anchored || (y0 + dy < d->h) && (y0 + bh - 1 + dy >= 0) && (x0 + dx < d->w) && (x0 + bw - 1 + dx >= 0))
                                 ++cost;
                         }
             cost *= pi;
@@ -327,7 +340,8 @@ int plan_wgrad(const b200seg_wgrad_desc* d, WgradPlan* pl) {
     static std::mutex mu;
     static std::map<std::vector<int>, WgradPlan> memo;
     const std::vector<int> key = {d->n, d->h, d->w, d->k, d->c, d->r, d->s, d->dil, d->stride, d->k_out, d->dy_c_offset % 8,
-                                  d->dy_c_total % 8, d->x_c_offset % 8, d->x_c_total % 8};
+                                  d->dy_c_total % 8, d->x_c_offset % 8, d->x_c_total % 8, d->x_rows, d->x_cols,
+                                  d->x_c_total, d->x_c_offset};
     {
         std::lock_guard<std::mutex> lock(mu);
         auto it = memo.find(key);
@@ -398,10 +412,21 @@ int b200seg_conv_wgrad(const b200seg_wgrad_desc* d, b200seg_stream_t stream) {
                               (uint64_t)d->h * d->w * d->dy_c_total * 2};
     const char* ybase = static_cast<const char*>(d->dy) + (size_t)d->dy_c_offset * 2;
     if (encode_tmap_bf16(&p.y_map, ybase, 4, ydims, ystr, box)) return 1;
+    const bool anchored = d->x_rows || d->x_cols;
+    p.no_skip = anchored ? 1 : 0;
+    if (anchored) {
+        // window view: see launch_fprop in conv_igemm.cu
+        const int span = ceil_div(d->x_c_offset + d->c, d->x_c_total);
+        const uint64_t wdims[4] = {(uint64_t)d->c, (uint64_t)(d->x_cols - span + 1), (uint64_t)d->x_rows, (uint64_t)d->n};
+        const uint64_t wstr[3] = {(uint64_t)d->x_c_total * 2, (uint64_t)d->x_cols * d->x_c_total * 2,
+                                  (uint64_t)d->x_rows * d->x_cols * d->x_c_total * 2};
+        const char* wbase = static_cast<const char*>(d->x) + (size_t)d->x_c_offset * 2;
+        if (encode_tmap_bf16(&p.x_map[0], wbase, 4, wdims, wstr, box)) return 1;
+    }
     const uint64_t xdims[4] = {(uint64_t)d->c, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n};
     const uint64_t xstr[3] = {(uint64_t)cs * d->x_c_total * 2, (uint64_t)cs * wx * d->x_c_total * 2,
                               (uint64_t)hx * wx * d->x_c_total * 2};
-    for (int vy = 0; vy < cs; ++vy)
+    for (int vy = 0; vy < (anchored ? 0 : cs); ++vy)
         for (int vx = 0; vx < cs; ++vx) {
             const char* xbase = static_cast<const char*>(d->x) + ((size_t)vy * wx + vx) * d->x_c_total * 2 +
                                 (size_t)d->x_c_offset * 2;
@@ -411,7 +436,11 @@ int b200seg_conv_wgrad(const b200seg_wgrad_desc* d, b200seg_stream_t stream) {
         for (int s = 0; s < d->s; ++s) {
             const int oy = (r - d->r / 2) * d->dil, ox = (s - d->s / 2) * d->dil;
             const int t = r * d->s + s;
-            if (cs == 1) {
+            if (anchored) {
+                p.tap_map[t] = 0;
+                p.tap_dy[t] = static_cast<short>(r);
+                p.tap_dx[t] = static_cast<short>(s);
+            } else if (cs == 1) {
                 p.tap_map[t] = 0;
                 p.tap_dy[t] = static_cast<short>(oy);
                 p.tap_dx[t] = static_cast<short>(ox);

@@ -55,6 +55,17 @@ class Act:
         return v if (self.c_off == 0 and self.c == self.ct) else v[:, self.c_off:self.c_off + self.c]
 
 
+class WindowAct(Act):
+    """An anchored window source (include/b200seg.h, b200seg_conv_src.x_rows): ``c`` is the window length in elements
+    and may exceed the buffer's channels per pixel — the window runs on into the following pixels.  Only conv_fprop /
+    conv_wgrad take it."""
+    __slots__ = ()
+
+    def __init__(self, t, window):
+        assert t.dim() == 4 and t.dtype == BF16 and t.is_contiguous() and window % 8 == 0 and t.shape[3] % 8 == 0
+        self.t, self.c_off, self.c = t, 0, window
+
+
 def as_act(x, what='input'):
     """NCHW-shaped tensor (any float dtype / memory format) -> contiguous NHWC bf16 Act.
     bf16 channels_last input is a zero-copy view; fp32 NCHW goes through the layout kernel."""
@@ -194,6 +205,45 @@ class PackedIm2colWeight:
         return self
 
 
+class PackedS2DWeight:
+    """bf16 [ceil(r/2)][k_rows][ceil(s/2)*cs] packing of a stride-2 few-channel OIHW conv weight for the
+    space-to-depth form (csrc/im2col.cu): quacks like a PackedWeight with ceil(r/2) x 1 taps over windows of
+    ceil(s/2)*cs elements."""
+    __slots__ = ('k', 'c', 'r', 's', 'k_rows', 'wf', 'wd', 'key', 'cin', 'kr', 'ks', 'cs', '_shape')
+
+    def __init__(self):
+        self.key = None
+        self.wf = self.wd = self._shape = None
+
+    @staticmethod
+    def applies(conv):
+        return (conv.stride == (2, 2) and conv.in_channels <= 4 and conv.groups == 1 and conv.dilation == (1, 1)
+                and conv.bias is None and (conv.kernel_size[0] + 1) // 2 <= 9)
+
+    def update(self, w):
+        _require_cuda(w, 'conv weight')
+        key = (w.data_ptr(), w._version, tuple(w.shape), WEIGHT_EPOCH)
+        if key == self.key:
+            return self
+        src = w.detach()
+        if src.dtype != torch.float32 or not src.is_contiguous():
+            src = src.float().contiguous()
+        k, cin, kr, ks = src.shape
+        if self._shape != (k, cin, kr, ks, src.device):
+            self.k, self.cin, self.kr, self.ks = k, cin, kr, ks
+            self.cs = _round_up(4 * cin, 8)
+            self.r, self.s = (kr + 1) // 2, 1
+            self.c = (ks + 1) // 2 * self.cs
+            self.k_rows = _round_up(k, 8)
+            self.wf = torch.empty((self.r, self.k_rows, self.c), dtype=BF16, device=src.device)
+            self._shape = (k, cin, kr, ks, src.device)
+        _lib.check(_lib.load().b200seg_pack_weights_s2d(src.data_ptr(), k, cin, kr, ks, self.wf.data_ptr(), self.k_rows,
+                                                        self.cs, _stream()), 'pack_weights_s2d')
+        _lib.count_launch()
+        self.key = key
+        return self
+
+
 class _GemmView:
     """What conv_fprop / conv_dgrad read from a packed weight, for a 1x1 GEMM over a re-arranged operand."""
     __slots__ = ('wf', 'wd', 'k_rows', 'c_rows', 'k_cols', 'r', 's', 'k', 'c')
@@ -306,6 +356,34 @@ def packed_entries(model):
     return out
 
 
+def space_to_depth(x, r, s, pad):
+    """fp32 NCHW image (c <= 4) -> WindowAct over the bf16 space-to-depth tensor of the padded image: the operand of a
+    stride-2 r x s conv as ceil(r/2) row taps (csrc/im2col.cu)."""
+    _require_cuda(x, 'space_to_depth input')
+    if x.dim() != 4 or x.dtype != torch.float32 or not x.is_contiguous():
+        raise ValueError('space_to_depth: expected a contiguous fp32 N x C x H x W tensor, got %s %s' % (tuple(x.shape), x.dtype))
+    n, c, h, w = x.shape
+    oh, ow = (h + 2 * pad - r) // 2 + 1, (w + 2 * pad - s) // 2 + 1
+    cs = _round_up(4 * c, 8)
+    z = torch.empty((n, oh + (r + 1) // 2 - 1, ow + (s + 1) // 2 - 1, cs), dtype=BF16, device=x.device)
+    _lib.check(_lib.load().b200seg_space_to_depth_nchw(x.data_ptr(), n, c, h, w, r, s, pad, z.data_ptr(), cs, _stream()),
+               'space_to_depth')
+    _lib.count_launch()
+    return WindowAct(z, (s + 1) // 2 * cs), oh, ow
+
+
+def unpack_wgrad_s2d(dwin, pw, lane=False):
+    return on_wgrad_lane(_unpack_wgrad_s2d, dwin, pw, keep=(dwin,)) if lane else _unpack_wgrad_s2d(dwin, pw)
+
+
+def _unpack_wgrad_s2d(dwin, pw):
+    dw = torch.empty((pw.k, pw.cin, pw.kr, pw.ks), dtype=torch.float32, device=dwin.device)
+    _lib.check(_lib.load().b200seg_unpack_wgrad_s2d(dwin.data_ptr(), pw.k, pw.cin, pw.kr, pw.ks, pw.cs, dw.data_ptr(), 0,
+                                                    _stream()), 'unpack_wgrad_s2d')
+    _lib.count_launch()
+    return dw
+
+
 def im2col(x, r, s, stride, pad):
     """fp32 NCHW image -> Act [n, oh, ow, round_up(r*s*c, 8)] of gathered patches (bf16)."""
     _require_cuda(x, 'im2col input')
@@ -361,7 +439,8 @@ def _conv(fn, what, n, h, w, srcs, out_ptr, y_ct, y_off, k, out_fp32, scale, bia
 def _conv_launch(fn, what, n, h, w, srcs, out_ptr, y_ct, y_off, k, out_fp32, scale, bias, relu, stats):
     arr = (ConvSrc * len(srcs))()
     for i, (x, wptr, w_rows, r, s, dil, stride) in enumerate(srcs):
-        arr[i] = ConvSrc(x.ptr, x.ct, x.c_off, x.c, wptr, w_rows, r, s, dil, stride)
+        arr[i] = ConvSrc(x.ptr, x.ct, x.c_off, x.c, wptr, w_rows, r, s, dil, stride,
+                         *((x.h, x.w) if isinstance(x, WindowAct) else (0, 0)))
     out = ConvOut(out_ptr, y_ct, y_off, k, int(out_fp32),
                   scale.data_ptr() if scale is not None else None,
                   bias.data_ptr() if bias is not None else None, int(relu),
@@ -381,7 +460,8 @@ def conv_fprop(srcs, out, scale=None, bias=None, relu=False, stats=None):
     y = act(scale * sum conv + bias); a stride-2 source's x is twice the size of out."""
     srcs = [_src(t) for t in srcs]
     for x, pw, dil, stride in srcs:
-        assert (x.n, x.h, x.w) == (out.n, out.h * stride, out.w * stride), 'conv_fprop: input/output size mismatch'
+        assert isinstance(x, WindowAct) or (x.n, x.h, x.w) == (out.n, out.h * stride, out.w * stride), \
+            'conv_fprop: input/output size mismatch'
     _conv(_lib.load().b200seg_conv_fprop, 'conv_fprop', out.n, out.h, out.w,
           [(x, pw.wf.data_ptr(), pw.k_rows, pw.r, pw.s, dil, stride) for x, pw, dil, stride in srcs],
           out.ptr, out.ct, out.c_off, out.c, False, scale, bias, relu, stats)
@@ -473,7 +553,10 @@ def conv_wgrad(dy, x, k_out, r, s, dil, dw=None, stride=1, lane=False):
 
 def _conv_wgrad(dy, x, k_out, r, s, dil, dw=None, stride=1):
     desc = WgradDesc()
-    assert (x.n, x.h, x.w) == (dy.n, dy.h * stride, dy.w * stride), 'conv_wgrad: size mismatch'
+    if isinstance(x, WindowAct):
+        desc.x_rows, desc.x_cols = x.h, x.w
+    else:
+        assert (x.n, x.h, x.w) == (dy.n, dy.h * stride, dy.w * stride), 'conv_wgrad: size mismatch'
     desc.n, desc.h, desc.w = dy.n, dy.h, dy.w
     desc.dy, desc.dy_c_total, desc.dy_c_offset, desc.k = dy.ptr, dy.ct, dy.c_off, dy.c
     desc.x, desc.x_c_total, desc.x_c_offset, desc.c = x.ptr, x.ct, x.c_off, x.c

@@ -29,8 +29,10 @@ class ConvBNState:
             raise NotImplementedError('%r: stride / padding outside the tcgen05 path' % (conv,))
         if conv.stride == (2, 2) and conv.dilation != (1, 1):
             raise NotImplementedError('%r: stride 2 with dilation' % (conv,))
-        self.gather = conv.in_channels % 8 != 0          # few-channel stem: patch gather + 1x1 GEMM
-        self.packed = E.PackedIm2colWeight() if self.gather else E.PackedWeight()
+        # few-channel stem: stride 2 takes the space-to-depth form, stride 1 the patch gather + 1x1 GEMM
+        self.gather = conv.in_channels % 8 != 0
+        self.s2d = self.gather and E.PackedS2DWeight.applies(conv)
+        self.packed = (E.PackedS2DWeight() if self.s2d else E.PackedIm2colWeight()) if self.gather else E.PackedWeight()
 
 
 class _ConvBNFn(torch.autograd.Function):
@@ -49,14 +51,19 @@ class _ConvBNFn(torch.autograd.Function):
             xf = x.detach()
             if xf.dtype != torch.float32 or not xf.is_contiguous():
                 xf = xf.float().contiguous()
-            xa = E.im2col(xf, k, k, stride, conv.padding[0])
             pw = state.packed.update(weight)
+            if state.s2d:
+                xa, oh, ow = E.space_to_depth(xf, k, k, conv.padding[0])
+            else:
+                xa = E.im2col(xf, k, k, stride, conv.padding[0])
+                oh, ow = xa.h, xa.w
             src = (xa, pw, 1, 1)
         else:
             xa = E.as_act(x, 'conv_bn input')
             pw = state.packed.update(weight, need_dgrad=need_dx)
             src = (xa, pw, dil, stride)
-        oh, ow = (xa.h, xa.w) if state.gather else (xa.h // stride, xa.w // stride)
+        if not state.gather:
+            oh, ow = xa.h // stride, xa.w // stride
         res = E.as_act(residual, 'conv_bn residual') if residual is not None else None
         out = E.Act.empty(xa.n, oh, ow, cout, dev)
         track = bn.track_running_stats and bn.running_mean is not None
@@ -112,8 +119,8 @@ class _ConvBNFn(torch.autograd.Function):
             draw = E.Act.empty(raw.n, raw.h, raw.w, raw.c, dev)
             dgamma, dbeta = E.bn_backward(da, raw, draw, vec, relu, training)
         if state.gather:
-            dwcol = E.conv_wgrad(draw, xa, raw.c, 1, 1, 1, lane=True)
-            dw = E.unpack_wgrad_im2col(dwcol, pw, lane=True)
+            dwcol = E.conv_wgrad(draw, xa, raw.c, pw.r, pw.s, 1, lane=True)
+            dw = (E.unpack_wgrad_s2d if state.s2d else E.unpack_wgrad_im2col)(dwcol, pw, lane=True)
             dx = None                                    # the image gets no gradient
         else:
             dw = E.conv_wgrad(draw, xa, conv.out_channels, k, k, dil, stride=stride, lane=True)

@@ -143,7 +143,8 @@ class ResNet50Features(nn.Module):
         self.conv1, self.bn1, self.relu, self.maxpool = net.conv1, net.bn1, net.relu, net.maxpool
         self.layer1, self.layer2, self.layer3, self.layer4 = net.layer1, net.layer2, net.layer3, net.layer4
         self._plan = None
-        self._stem_packed = E.PackedIm2colWeight()
+        # stride-2 few-channel stem: space-to-depth form (no gathered matrix); anything else: patch gather
+        self._stem_packed = E.PackedS2DWeight() if E.PackedS2DWeight.applies(self.conv1) else E.PackedIm2colWeight()
 
     def _build_plan(self):
         layers = [[_Block(b) for b in layer] for layer in (self.layer1, self.layer2, self.layer3, self.layer4)]
@@ -157,7 +158,8 @@ class ResNet50Features(nn.Module):
 
     def _packed_weights(self):
         units = (self._plan or self._build_plan())[1]
-        return [(self._stem_packed, self.conv1.weight)] + [(u.packed, u.conv.weight) for u in units]
+        stem = [] if isinstance(self._stem_packed, E.PackedS2DWeight) else [(self._stem_packed, self.conv1.weight)]
+        return stem + [(u.packed, u.conv.weight) for u in units]
 
     def forward(self, x):
         params = list(self.parameters())
@@ -176,9 +178,13 @@ class ResNet50Features(nn.Module):
         xf = x.detach()
         if xf.dtype != torch.float32 or not xf.is_contiguous():
             xf = xf.float().contiguous()
-        col = E.im2col(xf, conv1.kernel_size[0], conv1.kernel_size[1], conv1.stride[0], conv1.padding[0])
         pw0 = self._stem_packed.update(conv1.weight)
-        raw0 = E.Act.empty(col.n, col.h, col.w, conv1.out_channels, dev)
+        if isinstance(pw0, E.PackedS2DWeight):
+            col, oh0, ow0 = E.space_to_depth(xf, conv1.kernel_size[0], conv1.kernel_size[1], conv1.padding[0])
+        else:
+            col = E.im2col(xf, conv1.kernel_size[0], conv1.kernel_size[1], conv1.stride[0], conv1.padding[0])
+            oh0, ow0 = col.h, col.w
+        raw0 = E.Act.empty(col.n, oh0, ow0, conv1.out_channels, dev)
         bn = self.bn1
         if training:
             stats0 = torch.zeros((2 * raw0.c,), dtype=torch.float32, device=dev)
@@ -260,8 +266,9 @@ class ResNet50Features(nn.Module):
         draw0 = E.Act.empty(raw0.n, raw0.h, raw0.w, raw0.c, raw0.t.device)
         dgamma, dbeta = E.bn_backward(da0, raw0, draw0, v0, True, training)
         # dW of the stem = the 1x1 wgrad over the gathered matrix, scattered back to OIHW
-        dwcol = E.conv_wgrad(draw0, col, raw0.c, 1, 1, 1, lane=True)
-        grads[self.conv1.weight] = E.unpack_wgrad_im2col(dwcol, pw0, lane=True)
+        dwcol = E.conv_wgrad(draw0, col, raw0.c, pw0.r, pw0.s, 1, lane=True)
+        unpack = E.unpack_wgrad_s2d if isinstance(pw0, E.PackedS2DWeight) else E.unpack_wgrad_im2col
+        grads[self.conv1.weight] = unpack(dwcol, pw0, lane=True)
         grads[self.bn1.weight], grads[self.bn1.bias] = dgamma, dbeta
         return grads
 

@@ -701,3 +701,61 @@ def test_compute_loss_takes_the_class_map_shortcut_and_matches_the_logits_path(E
     out = m(x)
     (P.compute_loss(out, t) + 1e-3 * out.square().mean()).backward()
     assert all(torch.isfinite(p.grad).all() for p in m.parameters() if p.grad is not None)
+
+
+# ---- space-to-depth stem: stride-2 few-channel conv as row taps over overlapping windows (csrc/im2col.cu) ---------------
+S2D_CASES = [
+    # n, c, h, w, k, r, pad
+    (2, 3, 64, 96, 64, 7, 3),           # ResNet-50 conv1 (torchvision resnet.py via models/deeplabv3plus.py:17)
+    (1, 3, 70, 54, 64, 7, 3),           # sizes that are not multiples of the tile
+    (2, 3, 32, 64, 64, 3, 1),           # HRNet stem conv (models/hrnet.py:260)
+    (1, 1, 33, 47, 16, 5, 2),           # odd image, single channel
+]
+
+
+@pytest.mark.parametrize('n,c,h,w,k,r,pad', S2D_CASES)
+def test_space_to_depth_stem_conv(E, n, c, h, w, k, r, pad):
+    g = torch.Generator().manual_seed(n * 100 + h + r)
+    x = torch.randn(n, c, h, w, generator=g)
+    wt = torch.randn(k, c, r, r, generator=g) * 0.1
+    win, oh, ow = E.space_to_depth(x.cuda(), r, r, pad)
+    assert (oh, ow) == ((h + 2 * pad - r) // 2 + 1, (w + 2 * pad - r) // 2 + 1)
+    a = (r + 1) // 2
+    cs = (4 * c + 7) // 8 * 8
+    assert tuple(win.t.shape) == (n, oh + a - 1, ow + a - 1, cs) and win.c == a * cs
+    # the transform is a bit-exact re-arrangement of the bf16-rounded padded image
+    zh, zw = oh + a - 1, ow + a - 1
+    xp = torch.zeros(n, c, 2 * zh, 2 * zw)
+    hh, ww = min(h, 2 * zh - pad), min(w, 2 * zw - pad)
+    xp[:, :, pad:pad + hh, pad:pad + ww] = bf16_round(x)[:, :, :hh, :ww]
+    want = xp.view(n, c, zh, 2, zw, 2).permute(0, 2, 4, 3, 5, 1).reshape(n, zh, zw, 4 * c)      # (b, b', ch)
+    got = win.t.float().cpu()
+    assert torch.equal(got[..., :4 * c], want)
+    assert cs == 4 * c or float(got[..., 4 * c:].abs().max()) == 0.0
+    pw = E.PackedS2DWeight().update(wt.cuda())
+    assert (pw.r, pw.s, pw.c) == (a, 1, a * cs)
+    y = E.Act.empty(n, oh, ow, k, 'cuda')
+    stats = torch.zeros(2 * k, device='cuda')
+    E.conv_fprop([(win, pw, 1)], y, stats=stats)
+    xr = bf16_round(x)
+    wr = bf16_round(wt).requires_grad_(True)
+    ref = F.conv2d(xr, wr, None, 2, pad)
+    assert rel_err(from_act(y), ref) < TOL
+    assert rel_err(stats[:k], from_act(y).sum((0, 2, 3))) < 1e-3
+    gy = bf16_round(torch.randn(n, k, oh, ow, generator=g))
+    ref.backward(gy)
+    dwin = E.conv_wgrad(nhwc(gy), win, k, pw.r, 1, 1)
+    dw = E.unpack_wgrad_s2d(dwin, pw)
+    assert dw.shape == wt.shape
+    assert rel_err(dw, wr.grad) < TOL
+
+
+def test_anchored_window_source_is_checked(E):
+    win, oh, ow = E.space_to_depth(torch.randn(1, 3, 32, 32, device='cuda'), 7, 7, 3)
+    pw = E.PackedS2DWeight().update(torch.randn(64, 3, 7, 7, device='cuda'))
+    with pytest.raises(RuntimeError, match='exceed'):
+        E.conv_fprop([(win, pw, 1)], E.Act.empty(1, oh + 1, ow, 64, 'cuda'))      # one output row too many
+    with pytest.raises(RuntimeError, match='forward-only'):
+        E._conv(E._lib.load().b200seg_conv_dgrad, 'conv_dgrad', 1, oh, ow,
+                [(win, pw.wf.data_ptr(), pw.k_rows, pw.r, pw.s, 1, 1)], E.Act.empty(1, oh, ow, 64, 'cuda').ptr, 64, 0, 64,
+                False, None, None, False, None)
