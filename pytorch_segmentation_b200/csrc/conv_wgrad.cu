@@ -17,6 +17,7 @@
 #include "pdl.cuh"
 #include "ptx.cuh"
 
+#include <stdlib.h>
 #include <string.h>
 
 #include <map>
@@ -50,6 +51,8 @@ struct __align__(64) WgradParams {
     int splits, patches_per_split;
     int m_pad, n_pad;      // workspace matrix dims per (split, tap)
     float* ws;
+    int tap_group;         // filter taps per CTA (>1 only with X on the N side): the taps' shifted X boxes sit side by
+                           // side as one N = tap_group * bn operand, so the dY boxes are loaded once per group
     int no_skip;           // anchored window X: the buffer carries its own padding, every (tap, patch) is in bounds
 };
 
@@ -98,13 +101,23 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
     const int m_tile = tile % p.tiles_m;
     tile /= p.tiles_m;
     const int taps = p.R * p.S;
-    const int tap = tile % taps;
-    const int split = tile / taps;
+    const int G = p.tap_group;
+    const int ngroups = (taps + G - 1) / G;
+    const int tap = (tile % ngroups) * G;          // first tap of this CTA's group
+    const int gt = min(G, taps - tap);             // taps in the group
+    const int split = tile / ngroups;
     const int dy = p.tap_dy[tap];
     const int dx = p.tap_dx[tap];
     const CUtensorMap* xm = &p.x_map[p.tap_map[tap]];
     const CUtensorMap* m_map = p.shift_m ? xm : &p.y_map;
     const CUtensorMap* n_map = p.shift_m ? &p.y_map : xm;
+    // a patch is skipped only when every tap of the group reads nothing but padding there (a tap that does is
+    // zero-filled by the TMA unit)
+    auto group_in_bounds = [&](const PatchWalker& w) {
+        for (int j = 0; j < gt; ++j)
+            if (w.in_bounds(p, p.tap_dy[tap + j], p.tap_dx[tap + j])) return true;
+        return false;
+    };
     const int kp_begin = split * p.patches_per_split;
     const int kp_end = min(kp_begin + p.patches_per_split, p.patches);
 
@@ -138,22 +151,29 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            const uint32_t tx_bytes = kABytes + n_boxes * kBoxBytes;
+            const uint32_t tx_bytes = kABytes + gt * n_boxes * kBoxBytes;
             const int mdx = p.shift_m ? dx : 0, mdy = p.shift_m ? dy : 0;
             const int ndx = p.shift_m ? 0 : dx, ndy = p.shift_m ? 0 : dy;
             PatchWalker pw;
             pw.init(p, kp_begin);
             for (int kp = kp_begin; kp < kp_end; ++kp, pw.next(p)) {
-                if (!pw.in_bounds(p, dy, dx)) continue;
+                if (!group_in_bounds(pw)) continue;
                 const int x0 = pw.px * p.bw, y0 = pw.py * p.bh, n0 = pw.pn * p.bi;
                 mbar_wait(&empty[stage], phase ^ 1);
                 uint8_t* sa = smem + stage * kStageBytes;
                 mbar_arrive_expect_tx(&full[stage], tx_bytes);
                 for (int b = 0; b < 2; ++b)
                     tma_load_4d(sa + b * kBoxBytes, m_map, &full[stage], m_tile * kBM + b * 64, x0 + mdx, y0 + mdy, n0);
-                for (int b = 0; b < n_boxes; ++b)
-                    tma_load_4d(sa + kABytes + b * kBoxBytes, n_map, &full[stage], n_tile * p.bn + b * 64, x0 + ndx,
-                                y0 + ndy, n0);
+                if (G == 1) {
+                    for (int b = 0; b < n_boxes; ++b)
+                        tma_load_4d(sa + kABytes + b * kBoxBytes, n_map, &full[stage], n_tile * p.bn + b * 64, x0 + ndx,
+                                    y0 + ndy, n0);
+                } else {
+                    for (int j = 0; j < gt; ++j)
+                        for (int b = 0; b < n_boxes; ++b)
+                            tma_load_4d(sa + kABytes + (j * n_boxes + b) * kBoxBytes, &p.x_map[p.tap_map[tap + j]],
+                                        &full[stage], b * 64, x0 + p.tap_dx[tap + j], y0 + p.tap_dy[tap + j], n0);
+                }
                 if (++stage == kStages) {
                     stage = 0;
                     phase ^= 1;
@@ -162,14 +182,14 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            const uint32_t idesc = umma_idesc_bf16(kBM, p.bn, 1, 1);
+            const uint32_t idesc = umma_idesc_bf16(kBM, gt * p.bn, 1, 1);
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
             PatchWalker pw;
             pw.init(p, kp_begin);
             for (int kp = kp_begin; kp < kp_end; ++kp, pw.next(p)) {
-                if (!pw.in_bounds(p, dy, dx)) continue;
+                if (!group_in_bounds(pw)) continue;
                 mbar_wait(&full[stage], phase);
                 tc_fence_after();
                 const uint32_t sa = smem_u32(smem + stage * kStageBytes);
@@ -198,26 +218,29 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
         bool any = false;
         PatchWalker pw;
         pw.init(p, kp_begin);
-        for (int kp = kp_begin; kp < kp_end && !any; ++kp, pw.next(p)) any = pw.in_bounds(p, dy, dx);
+        for (int kp = kp_begin; kp < kp_end && !any; ++kp, pw.next(p)) any = group_in_bounds(pw);
         const int q = warp & 3;
         const int row = q * 32 + lane;
         mbar_wait(tfull, 0);
         tc_fence_after();
-        float* dst = p.ws + ((static_cast<size_t>(split) * taps + tap) * p.m_pad + (m_tile * kBM + row)) * p.n_pad +
-                     n_tile * p.bn;
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-        for (int ch = 0; ch < p.bn; ch += 32) {
-            uint32_t v[32];
-            if (any) {
-                tmem_ld_32x32(taddr + ch, v);
-                tmem_ld_wait();
-            } else {
+        for (int g = 0; g < gt; ++g) {
+            // tap g of the group: accumulator columns [g * bn, (g + 1) * bn) -> its own plane of the workspace
+            float* dst = p.ws + ((static_cast<size_t>(split) * taps + tap + g) * p.m_pad + (m_tile * kBM + row)) * p.n_pad +
+                         n_tile * p.bn;
+            for (int ch = 0; ch < p.bn; ch += 32) {
+                uint32_t v[32];
+                if (any) {
+                    tmem_ld_32x32(taddr + g * p.bn + ch, v);
+                    tmem_ld_wait();
+                } else {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = 0;
+                    for (int j = 0; j < 32; ++j) v[j] = 0;
+                }
+#pragma unroll
+                for (int j = 0; j < 32; j += 4)
+                    *reinterpret_cast<uint4*>(dst + ch + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
             }
-#pragma unroll
-            for (int j = 0; j < 32; j += 4)
-                *reinterpret_cast<uint4*>(dst + ch + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
         }
     }
 
@@ -252,8 +275,16 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restr
     *d = accumulate ? (*d + acc) : acc;
 }
 
+bool tap_grouping_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("B200SEG_WGRAD_TAPGROUP");
+        return !(e && e[0] == '0');
+    }();
+    return on;
+}
+
 struct WgradPlan {
-    int shift_m, bw, bh, bi, patches_x, patches_y, patches_i, tiles_m, tiles_n, bn, splits, pps, m_pad, n_pad;
+    int shift_m, bw, bh, bi, patches_x, patches_y, patches_i, tiles_m, tiles_n, bn, splits, pps, m_pad, n_pad, tap_group;
     size_t ws_bytes;
 };
 
@@ -321,7 +352,15 @@ int plan_wgrad_uncached(const b200seg_wgrad_desc* d, WgradPlan* pl) {
     }
     B200SEG_CHECK(best > 0, "wgrad: no patch shape");
     const int patches = pl->patches_x * pl->patches_y * pl->patches_i;
-    const int base_tiles = d->r * d->s * pl->tiles_m * pl->tiles_n;
+    // tap groups: with X on the N side and a single narrow n-tile, several taps share one CTA (and one load of dY)
+    const int taps = d->r * d->s;
+    pl->tap_group = 1;
+    if (!pl->shift_m && pl->tiles_n == 1 && taps > 1 && pl->bn <= kMaxBN / 2 && tap_grouping_enabled()) {
+        const int gmax = kMaxBN / pl->bn;
+        const int ngroups = ceil_div(taps, gmax);
+        pl->tap_group = ceil_div(taps, ngroups);
+    }
+    const int base_tiles = ceil_div(taps, pl->tap_group) * pl->tiles_m * pl->tiles_n;
     int sms = sm_count();
     if (sms <= 0) sms = 148;
     int splits = sms / base_tiles;
@@ -396,6 +435,7 @@ int b200seg_conv_wgrad(const b200seg_wgrad_desc* d, b200seg_stream_t stream) {
     p.tiles_m = pl.tiles_m;
     p.tiles_n = pl.tiles_n;
     p.bn = pl.bn;
+    p.tap_group = pl.tap_group;
     p.splits = pl.splits;
     p.patches_per_split = pl.pps;
     p.m_pad = pl.m_pad;
@@ -457,7 +497,7 @@ int b200seg_conv_wgrad(const b200seg_wgrad_desc* d, b200seg_stream_t stream) {
         attr_set = true;
     }
     const int taps = d->r * d->s;
-    const int grid = pl.splits * taps * pl.tiles_m * pl.tiles_n;
+    const int grid = pl.splits * ceil_div(taps, pl.tap_group) * pl.tiles_m * pl.tiles_n;
     B200SEG_CUDA(launch_pdl(wgrad_kernel, grid, kThreads, kSmemBytes, st, p));
 
     const long long total = static_cast<long long>(d->k_out) * d->c * taps;
