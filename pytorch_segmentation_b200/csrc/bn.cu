@@ -334,8 +334,8 @@ __global__ void __launch_bounds__(256) relu_bwd_add_kernel(__nv_bfloat16* __rest
     pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int g = static_cast<int>(i % groups);
-        const int64_t p = i / groups;
+        int g;
+        const int64_t p = divmod_small(i, groups, total, g);
         float a[8], d[8], m[8];
         __nv_bfloat16* dst = dx + p * dx_ct + dx_off + g * 8;
         unpack8(*reinterpret_cast<const uint4*>(dst), a);
@@ -358,8 +358,8 @@ __global__ void __launch_bounds__(256) grad_add_masked_kernel(__nv_bfloat16* __r
     pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int g = static_cast<int>(i % groups);
-        const int64_t p = i / groups;
+        int g;
+        const int64_t p = divmod_small(i, groups, total, g);
         float a[8];
         __nv_bfloat16* dst = dx + p * dx_ct + dx_off + g * 8;
         unpack8(*reinterpret_cast<const uint4*>(dst), a);
@@ -398,8 +398,8 @@ __global__ void __launch_bounds__(256) add_n_relu_kernel(const AddN a, __nv_bflo
     pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int g = static_cast<int>(i % groups);
-        const int64_t p = i / groups;
+        int g;
+        const int64_t p = divmod_small(i, groups, total, g);
         float acc[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] = 0.f;
@@ -428,8 +428,8 @@ __global__ void __launch_bounds__(256) relu_bwd_kernel(const __nv_bfloat16* __re
     pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int g = static_cast<int>(i % groups);
-        const int64_t p = i / groups;
+        int g;
+        const int64_t p = divmod_small(i, groups, total, g);
         float d[8], m[8];
         unpack8(ldcs128(dy + p * dy_ct + dy_off + g * 8), d);
         unpack8(ldcs128(y + p * y_ct + y_off + g * 8), m);

@@ -16,12 +16,9 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const __nv_bfloat16* _
     pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int g = static_cast<int>(i % groups);
-        int64_t p = i / groups;
-        const int ox = static_cast<int>(p % ow);
-        p /= ow;
-        const int oy = static_cast<int>(p % oh);
-        const int64_t n = p / oh;
+        const Idx4 id = decode4(i, groups, ow, oh, total);
+        const int g = id.g, ox = id.x, oy = id.y;
+        const int64_t n = id.n;
         float best[8];
         int bi[8];
 #pragma unroll
@@ -64,34 +61,43 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const __nv_bfloat16* _
     pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int g = static_cast<int>(i % groups);
-        int64_t p = i / groups;
-        const int ix = static_cast<int>(p % w);
-        p /= w;
-        const int iy = static_cast<int>(p % h);
-        const int64_t n = p / h;
+        const Idx4 id = decode4(i, groups, w, h, total);
+        const int g = id.g, ix = id.x, iy = id.y;
+        const int64_t n = id.n;
         float acc[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-        // windows o with 2o-1 <= i <= 2o+1: o = i/2 (tap 1) for even i; o = (i-1)/2 (tap 2) and (i+1)/2 (tap 0) for odd i
+        // windows o with 2o-1 <= i <= 2o+1: o = i/2 (tap 1) for even i; o = (i-1)/2 (tap 2) and (i+1)/2 (tap 0) for odd i.
+        // All (up to four) window reads are issued before any is consumed: the dependent-latency chain of the looped
+        // form kept this kernel at a quarter of the HBM rate.
         const int oy0 = iy >> 1, oy1 = (iy + 1) >> 1;
         const int ox0 = ix >> 1, ox1 = (ix + 1) >> 1;
-        for (int oy = oy0; oy <= oy1; ++oy) {
-            if (oy >= oh) continue;
-            const int r = iy - (2 * oy - 1);
-            for (int ox = ox0; ox <= ox1; ++ox) {
-                if (ox >= ow) continue;
-                const int s = ix - (2 * ox - 1);
-                const int tap = r * 3 + s;
-                const int64_t op = (n * oh + oy) * ow + ox;
-                const uint2 packed = __ldg(reinterpret_cast<const uint2*>(idx + (op * groups + g) * 8));
-                float d[8];
-                unpack8(ldg128(dy + op * dy_ct + dy_off + g * 8), d);
+        uint2 packed[4];
+        uint4 dv[4];
+        int tapv[4];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const int sel = ((j < 4 ? packed.x : packed.y) >> ((j & 3) * 8)) & 0xff;
-                    if (sel == tap) acc[j] += d[j];
+        for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+                const int oy = a ? oy1 : oy0, ox = b ? ox1 : ox0;
+                const bool ok = (a == 0 || oy1 != oy0) && (b == 0 || ox1 != ox0) && oy < oh && ox < ow;
+                tapv[a * 2 + b] = ok ? (iy - (2 * oy - 1)) * 3 + (ix - (2 * ox - 1)) : -1;
+                packed[a * 2 + b] = make_uint2(0u, 0u);
+                dv[a * 2 + b] = make_uint4(0u, 0u, 0u, 0u);
+                if (ok) {
+                    const int64_t op = (n * oh + oy) * ow + ox;
+                    packed[a * 2 + b] = __ldg(reinterpret_cast<const uint2*>(idx + (op * groups + g) * 8));
+                    dv[a * 2 + b] = ldg128(dy + op * dy_ct + dy_off + g * 8);
                 }
+            }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            float d[8];
+            unpack8(dv[q], d);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int sel = ((j < 4 ? packed[q].x : packed[q].y) >> ((j & 3) * 8)) & 0xff;
+                if (sel == tapv[q]) acc[j] += d[j];
             }
         }
         st128(dx + ((n * h + iy) * w + ix) * dx_ct + dx_off + g * 8, pack8(acc));

@@ -14,18 +14,19 @@ namespace {
 
 constexpr int kRowChunk = 16;
 
-// y[n][k] = sum_c x[n][c] * w[k][c];  one warp per output channel k, lanes stride over c
+// y[n][k] = sum_c x[n][c] * w[k][c];  one CTA (8 warps) per output channel k, threads stride over c — a warp per
+// channel walked c = 2048 in 64 dependent-latency steps; here it is 8, and the partial sums meet in shared memory
 __global__ void __launch_bounds__(256) linear_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                           float* __restrict__ y, int n, int c, int k) {
     pdl_prologue();
-    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (warp >= k) return;
-    const float* wr = w + static_cast<size_t>(warp) * c;
+    __shared__ float red[8][kRowChunk];
+    const int kk = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const float* wr = w + static_cast<size_t>(kk) * c;
     for (int n0 = 0; n0 < n; n0 += kRowChunk) {
         float acc[kRowChunk];
 #pragma unroll
         for (int i = 0; i < kRowChunk; ++i) acc[i] = 0.f;
-        for (int cc = lane; cc < c; cc += 32) {
+        for (int cc = threadIdx.x; cc < c; cc += 256) {
             const float wv = __ldg(wr + cc);
 #pragma unroll
             for (int i = 0; i < kRowChunk; ++i)
@@ -34,8 +35,16 @@ __global__ void __launch_bounds__(256) linear_fwd_kernel(const float* __restrict
 #pragma unroll
         for (int i = 0; i < kRowChunk; ++i) {
             const float s = warp_sum(acc[i]);
-            if (lane == 0 && n0 + i < n) y[static_cast<size_t>(n0 + i) * k + warp] = s;
+            if (lane == 0) red[warp][i] = s;
         }
+        __syncthreads();
+        if (threadIdx.x < kRowChunk && n0 + threadIdx.x < n) {
+            float s = 0.f;
+#pragma unroll
+            for (int r = 0; r < 8; ++r) s += red[r][threadIdx.x];
+            y[static_cast<size_t>(n0 + threadIdx.x) * k + kk] = s;
+        }
+        __syncthreads();
     }
 }
 
@@ -157,8 +166,7 @@ int b200seg_linear_f32_fwd(const float* x, const float* w, float* y, int n, int 
     using namespace b200seg;
     clear_error();
     B200SEG_CHECK(x && w && y && n > 0 && c > 0 && k > 0, "linear_f32_fwd: bad arguments");
-    // 2 warps per CTA: fills the SMs
-    B200SEG_CUDA(launch_pdl(linear_fwd_kernel, ceil_div(k * 32, 64), 64, 0, static_cast<cudaStream_t>(st), x, w, y, n, c, k));
+    B200SEG_CUDA(launch_pdl(linear_fwd_kernel, k, 256, 0, static_cast<cudaStream_t>(st), x, w, y, n, c, k));
     return 0;
 }
 

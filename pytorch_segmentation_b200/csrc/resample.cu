@@ -15,12 +15,8 @@ __global__ void __launch_bounds__(256) upsample_fwd_kernel(const __nv_bfloat16* 
     pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int g = static_cast<int>(i % groups);
-        int64_t p = i / groups;
-        const int ox = static_cast<int>(p % ow);
-        p /= ow;
-        const int oy = static_cast<int>(p % oh);
-        const int n = static_cast<int>(p / oh);
+        const Idx4 id = decode4(i, groups, ow, oh, total);
+        const int g = id.g, ox = id.x, oy = id.y, n = id.n;
         const Lerp ly = bilinear_src(sh, oy, h, ac), lx = bilinear_src(sw, ox, w, ac);
         const __nv_bfloat16* b = x + (static_cast<int64_t>(n) * h * w) * x_ct + x_off + g * 8;
         float v00[8], v01[8], v10[8], v11[8], o[8];
@@ -43,12 +39,8 @@ __global__ void __launch_bounds__(256) upsample_bwd_kernel(const __nv_bfloat16* 
     pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int g = static_cast<int>(i % groups);
-        int64_t p = i / groups;
-        const int sx = static_cast<int>(p % w);
-        p /= w;
-        const int sy = static_cast<int>(p % h);
-        const int n = static_cast<int>(p / h);
+        const Idx4 id = decode4(i, groups, w, h, total);
+        const int g = id.g, sx = id.x, sy = id.y, n = id.n;
         int ylo, yhi, xlo, xhi;
         bilinear_dst_range(sh, sy, h, oh, ac, ylo, yhi);
         bilinear_dst_range(sw, sx, w, ow, ac, xlo, xhi);
@@ -56,19 +48,56 @@ __global__ void __launch_bounds__(256) upsample_bwd_kernel(const __nv_bfloat16* 
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] = 0.f;
         const __nv_bfloat16* b = dy + (static_cast<int64_t>(n) * oh * ow) * dy_ct + dy_off + g * 8;
-        for (int oy = ylo; oy <= yhi; ++oy) {
-            const Lerp ly = bilinear_src(sh, oy, h, ac);
-            const float wy = (ly.i0 == sy ? ly.w0 : 0.f) + (ly.i1 == sy ? ly.w1 : 0.f);
-            if (wy == 0.f) continue;
-            for (int ox = xlo; ox <= xhi; ++ox) {
-                const Lerp lx = bilinear_src(sw, ox, w, ac);
-                const float wx = (lx.i0 == sx ? lx.w0 : 0.f) + (lx.i1 == sx ? lx.w1 : 0.f);
-                if (wx == 0.f) continue;
-                float f[8];
-                unpack8(ldg128(b + (static_cast<int64_t>(oy) * ow + ox) * dy_ct), f);
-                const float wt = wy * wx;
+        // the range is a superset: trim the columns that do not read sx, then up to x4.5 a source column feeds <= 10
+        auto col_weight = [&](int ox) {
+            const Lerp lx = bilinear_src(sw, ox, w, ac);
+            return (lx.i0 == sx ? lx.w0 : 0.f) + (lx.i1 == sx ? lx.w1 : 0.f);
+        };
+        while (xlo < xhi && col_weight(xlo) == 0.f) ++xlo;
+        while (xhi > xlo && col_weight(xhi) == 0.f) --xhi;
+        constexpr int kSpan = 10;
+        if (xhi - xlo < kSpan) {
+            // column weights once per element; per destination row all loads are issued before they are consumed
+            float wxs[kSpan];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) acc[j] = fmaf(wt, f[j], acc[j]);
+            for (int k = 0; k < kSpan; ++k) {
+                const int ox = xlo + k;
+                const Lerp lx = bilinear_src(sw, min(ox, ow - 1), w, ac);
+                wxs[k] = ox <= xhi ? (lx.i0 == sx ? lx.w0 : 0.f) + (lx.i1 == sx ? lx.w1 : 0.f) : 0.f;
+            }
+            for (int oy = ylo; oy <= yhi; ++oy) {
+                const Lerp ly = bilinear_src(sh, oy, h, ac);
+                const float wy = (ly.i0 == sy ? ly.w0 : 0.f) + (ly.i1 == sy ? ly.w1 : 0.f);
+                if (wy == 0.f) continue;
+                const __nv_bfloat16* rowp = b + (static_cast<int64_t>(oy) * ow + xlo) * dy_ct;
+                uint4 v[kSpan];
+#pragma unroll
+                for (int k = 0; k < kSpan; ++k)
+                    v[k] = wxs[k] != 0.f ? ldg128(rowp + static_cast<int64_t>(k) * dy_ct) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+                for (int k = 0; k < kSpan; ++k) {
+                    float f[8];
+                    unpack8(v[k], f);
+                    const float wt = wy * wxs[k];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[j] = fmaf(wt, f[j], acc[j]);
+                }
+            }
+        } else {
+            for (int oy = ylo; oy <= yhi; ++oy) {
+                const Lerp ly = bilinear_src(sh, oy, h, ac);
+                const float wy = (ly.i0 == sy ? ly.w0 : 0.f) + (ly.i1 == sy ? ly.w1 : 0.f);
+                if (wy == 0.f) continue;
+                for (int ox = xlo; ox <= xhi; ++ox) {
+                    const Lerp lx = bilinear_src(sw, ox, w, ac);
+                    const float wx = (lx.i0 == sx ? lx.w0 : 0.f) + (lx.i1 == sx ? lx.w1 : 0.f);
+                    if (wx == 0.f) continue;
+                    float f[8];
+                    unpack8(ldg128(b + (static_cast<int64_t>(oy) * ow + ox) * dy_ct), f);
+                    const float wt = wy * wx;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[j] = fmaf(wt, f[j], acc[j]);
+                }
             }
         }
         st128(dx + ((static_cast<int64_t>(n) * h + sy) * w + sx) * dx_ct + dx_off + g * 8, pack8(acc));

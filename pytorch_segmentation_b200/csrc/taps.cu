@@ -27,11 +27,10 @@ __global__ void __launch_bounds__(256) tap_gather_kernel(const __nv_bfloat16* __
     const int per_pixel = R * S * groups;
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int64_t p = i / per_pixel;
-        const int q = static_cast<int>(i - p * per_pixel);
+        int q, px, py;
+        const int64_t p = divmod_small(i, per_pixel, total, q);
         const int tap = q / groups, g = q - tap * groups;
-        const int px = static_cast<int>(p % W);
-        const int py = static_cast<int>((p / W) % H);
+        divmod_small(divmod_small(p, W, total, px), H, total, py);
         const int sy = py + (tap / S - R / 2) * dil, sx = px + (tap % S - S / 2) * dil;
         uint4 v = make_uint4(0u, 0u, 0u, 0u);
         if (sy >= 0 && sy < H && sx >= 0 && sx < W) {
@@ -50,10 +49,9 @@ __global__ void __launch_bounds__(256) tap_scatter_add_kernel(const __nv_bfloat1
     const int groups = ncp >> 3;
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int64_t p = i / groups;
-        const int g = static_cast<int>(i - p * groups);
-        const int px = static_cast<int>(p % W);
-        const int py = static_cast<int>((p / W) % H);
+        int g, px, py;
+        const int64_t p = divmod_small(i, groups, total, g);
+        divmod_small(divmod_small(p, W, total, px), H, total, py);
         float acc[8];
         if (bias) {
             load8f(bias + g * 8, acc);

@@ -54,6 +54,44 @@ __host__ __device__ __forceinline__ float bilinear_scale(int in, int out, int al
     if (align_corners) return out > 1 ? static_cast<float>(in - 1) / static_cast<float>(out - 1) : 0.f;
     return static_cast<float>(in) / static_cast<float>(out);
 }
+// (group, x, y, n) of flat element i of an [n][H][W][groups] enumeration.  64-bit division is a ~100-instruction
+// subroutine on this machine and three of them per element made the gather kernels ALU-bound; every shape the
+// models produce fits 32 bits (uniform branch).
+struct Idx4 {
+    int g, x, y, n;
+};
+__device__ __forceinline__ Idx4 decode4(int64_t i, int groups, int W, int H, int64_t total) {
+    Idx4 r;
+    if (total < (int64_t(1) << 31)) {
+        const unsigned u = static_cast<unsigned>(i);
+        const unsigned p = u / static_cast<unsigned>(groups);
+        r.g = static_cast<int>(u - p * groups);
+        const unsigned q = p / static_cast<unsigned>(W);
+        r.x = static_cast<int>(p - q * W);
+        const unsigned n = q / static_cast<unsigned>(H);
+        r.y = static_cast<int>(q - n * H);
+        r.n = static_cast<int>(n);
+    } else {
+        r.g = static_cast<int>(i % groups);
+        int64_t p = i / groups;
+        r.x = static_cast<int>(p % W);
+        p /= W;
+        r.y = static_cast<int>(p % H);
+        r.n = static_cast<int>(p / H);
+    }
+    return r;
+}
+// i = q * d + rem, with 32-bit arithmetic when `total` (an upper bound of i) allows
+__device__ __forceinline__ int64_t divmod_small(int64_t i, int d, int64_t total, int& rem) {
+    if (total < (int64_t(1) << 31)) {
+        const unsigned u = static_cast<unsigned>(i), q = u / static_cast<unsigned>(d);
+        rem = static_cast<int>(u - q * d);
+        return q;
+    }
+    const int64_t q = i / d;
+    rem = static_cast<int>(i - q * d);
+    return q;
+}
 struct Lerp {
     int i0, i1;
     float w0, w1;
