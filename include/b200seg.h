@@ -207,6 +207,14 @@ int b200seg_bn_finalize(const float* stats, int c, int64_t count, const float* g
 /* y = relu?(x*scale + shift) from one NHWC slice into another (BN apply + nn.ReLU + concat placement). */
 int b200seg_bn_apply(const void* x, int x_c_total, int x_c_offset, void* y, int y_c_total, int y_c_offset, int c,
                      int64_t pixels, const float* scale, const float* shift, int relu, b200seg_stream_t st);
+/* b200seg_bn_finalize + b200seg_bn_apply_add in one launch (train mode): scale / shift come straight from the conv
+ * epilogue's stats[2c] (count = pixels); vec[4c] receives scale, shift, mean, invstd for the backward and the running
+ * statistics move exactly as in b200seg_bn_finalize.  res / res_scale / res_shift as in b200seg_bn_apply_add. */
+int b200seg_bn_apply_train(const void* x, int x_c_total, int x_c_offset, void* y, int y_c_total, int y_c_offset, int c,
+                           int64_t pixels, const float* stats, const float* gamma, const float* beta, float eps,
+                           float momentum, float* running_mean, float* running_var, float* vec, int relu, const void* res,
+                           int res_c_total, int res_c_offset, const float* res_scale, const float* res_shift,
+                           b200seg_stream_t st);
 /* Residual form used by the ResNet bottlenecks of the backbone (pytorch_modules.backbones.resnet50, called at
  * models/deeplabv3plus.py:17-19,29): y = relu?(x*scale + shift + r) with r = res (identity) or res*res_scale +
  * res_shift (the downsample conv's raw output and its BN); res == NULL reduces to b200seg_bn_apply. */

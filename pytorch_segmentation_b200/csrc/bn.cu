@@ -162,6 +162,17 @@ __global__ void bn_eval_affine_kernel(int c, const float* __restrict__ gamma, co
     if (save_invstd) save_invstd[i] = invstd;
 }
 
+// Training-mode inputs of bn_apply_kernel when it also does bn_finalize's job (stats == nullptr: plain apply)
+struct BnTrain {
+    const float* stats;      // [2c] per-channel sum and sum of squares from the conv epilogue
+    const float* gamma;
+    const float* beta;
+    float inv_count, unbias, eps, momentum;
+    float* running_mean;
+    float* running_var;
+    float* vec;              // [4c] out: scale, shift, mean, invstd
+};
+
 // Elementwise kernels over a [pixels][c] slice use the column geometry too: a thread owns one 8-channel group for
 // its whole pixel range, so the per-channel parameters live in registers (reloading them per element made these
 // kernels L1-bound at ~65 % of HBM bandwidth).
@@ -169,14 +180,47 @@ __global__ void __launch_bounds__(kRedThreads) bn_apply_kernel(
     const __nv_bfloat16* __restrict__ x, int x_ct, int x_off, __nv_bfloat16* __restrict__ y, int y_ct, int y_off, int groups,
     int64_t pixels, int64_t ppb, int gpb, int rows, const float* __restrict__ scale, const float* __restrict__ shift,
     int relu, const __nv_bfloat16* __restrict__ res, int r_ct, int r_off, const float* __restrict__ res_scale,
-    const float* __restrict__ res_shift) {
+    const float* __restrict__ res_shift, const BnTrain tr) {
     pdl_prologue();
     const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
     const int group = blockIdx.y * gpb + g_local;
     if (row >= rows || group >= groups) return;
     float sc[8], sh[8], rsc[8], rsh[8];
-    load8f(scale + group * 8, sc);
-    load8f(shift + group * 8, sh);
+    if (tr.stats) {
+        // training mode without a separate finalize launch: every thread derives its 8 channels' scale / shift from
+        // the conv epilogue's sums (bn_finalize_kernel's arithmetic); the first block row also publishes them for the
+        // backward and moves the running statistics
+        const int c = groups * 8;
+        float s1[8], s2[8], gm[8], bt[8], mean[8], invstd[8], var[8];
+        load8f(tr.stats + group * 8, s1);
+        load8f(tr.stats + c + group * 8, s2);
+        load8f(tr.gamma + group * 8, gm);
+        load8f(tr.beta + group * 8, bt);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            mean[j] = s1[j] * tr.inv_count;
+            var[j] = fmaxf(fmaf(-mean[j], mean[j], s2[j] * tr.inv_count), 0.f);
+            invstd[j] = rsqrtf(var[j] + tr.eps);
+            sc[j] = gm[j] * invstd[j];
+            sh[j] = fmaf(-mean[j], sc[j], bt[j]);
+        }
+        if (blockIdx.x == 0 && row == 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int ch = group * 8 + j;
+                tr.vec[ch] = sc[j];
+                tr.vec[c + ch] = sh[j];
+                tr.vec[2 * c + ch] = mean[j];
+                tr.vec[3 * c + ch] = invstd[j];
+                if (tr.running_mean) tr.running_mean[ch] = fmaf(tr.momentum, mean[j] - tr.running_mean[ch], tr.running_mean[ch]);
+                if (tr.running_var)
+                    tr.running_var[ch] = fmaf(tr.momentum, var[j] * tr.unbias - tr.running_var[ch], tr.running_var[ch]);
+            }
+        }
+    } else {
+        load8f(scale + group * 8, sc);
+        load8f(shift + group * 8, sh);
+    }
     const bool res_affine = res != nullptr && res_scale != nullptr;
     if (res_affine) {
         load8f(res_scale + group * 8, rsc);
@@ -521,7 +565,41 @@ int b200seg_bn_apply_add(const void* x, int x_c_total, int x_c_offset, void* y, 
     B200SEG_CUDA(launch_pdl(bn_apply_kernel, dim3(g.gx, g.gy), kRedThreads, 0, static_cast<cudaStream_t>(stream), 
         static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset,
         c / 8, pixels, g.pixels_per_block, g.gpb, g.rows, scale, shift, relu, static_cast<const __nv_bfloat16*>(res),
-        res_c_total, res_c_offset, res_scale, res_shift));
+        res_c_total, res_c_offset, res_scale, res_shift, BnTrain{}));
+    return 0;
+}
+
+int b200seg_bn_apply_train(const void* x, int x_c_total, int x_c_offset, void* y, int y_c_total, int y_c_offset, int c,
+                           int64_t pixels, const float* stats, const float* gamma, const float* beta, float eps,
+                           float momentum, float* running_mean, float* running_var, float* vec, int relu, const void* res,
+                           int res_c_total, int res_c_offset, const float* res_scale, const float* res_shift,
+                           b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    if (check_slice("bn_apply_train(x)", x, x_c_total, x_c_offset, c)) return 1;
+    if (check_slice("bn_apply_train(y)", y, y_c_total, y_c_offset, c)) return 1;
+    if (res && check_slice("bn_apply_train(res)", res, res_c_total, res_c_offset, c)) return 1;
+    B200SEG_CHECK(stats && gamma && beta && vec && pixels > 0, "bn_apply_train: bad arguments");
+    B200SEG_CHECK((res_scale == nullptr) == (res_shift == nullptr), "bn_apply_train: residual scale and shift go together");
+    B200SEG_CHECK(((reinterpret_cast<uintptr_t>(stats) | reinterpret_cast<uintptr_t>(gamma) | reinterpret_cast<uintptr_t>(beta)) & 15) == 0,
+                  "bn_apply_train: statistics / affine parameters must be 16-byte aligned");
+    BnTrain tr;
+    tr.stats = stats;
+    tr.gamma = gamma;
+    tr.beta = beta;
+    tr.inv_count = static_cast<float>(1.0 / static_cast<double>(pixels));
+    tr.unbias = pixels > 1 ? static_cast<float>(static_cast<double>(pixels) / static_cast<double>(pixels - 1)) : 1.f;
+    tr.eps = eps;
+    tr.momentum = momentum;
+    tr.running_mean = running_mean;
+    tr.running_var = running_var;
+    tr.vec = vec;
+    const ColGeom g = col_geom(c, pixels, 16);
+    B200SEG_CUDA(launch_pdl(bn_apply_kernel, dim3(g.gx, g.gy), kRedThreads, 0, static_cast<cudaStream_t>(stream),
+        static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset,
+        c / 8, pixels, g.pixels_per_block, g.gpb, g.rows, static_cast<const float*>(nullptr),
+        static_cast<const float*>(nullptr), relu, static_cast<const __nv_bfloat16*>(res), res_c_total, res_c_offset,
+        res_scale, res_shift, tr));
     return 0;
 }
 

@@ -610,6 +610,34 @@ def bn_finalize(stats, c, count, gamma, beta, eps, momentum, running_mean, runni
     return vec
 
 
+def bn_finalize_lazy(stats, c, count, gamma, beta, eps, momentum, running_mean, running_var):
+    """Like ``bn_finalize`` but defers the work to the ``bn_apply`` that follows (one launch less per layer): the
+    returned vec is unfilled and carries what is needed to fill it.  ``bn_resolve`` forces it."""
+    ok = (gamma.dtype == torch.float32 and beta.dtype == torch.float32 and gamma.is_contiguous() and beta.is_contiguous()
+          and gamma.data_ptr() % 16 == 0 and beta.data_ptr() % 16 == 0 and stats.data_ptr() % 16 == 0 and c % 8 == 0)
+    if not ok:
+        return bn_finalize(stats, c, count, gamma, beta, eps, momentum, running_mean, running_var)
+    vec = torch.empty((4, c), dtype=torch.float32, device=stats.device)
+    vec._b200seg_pending = (stats, c, count, gamma, beta, eps, momentum, running_mean, running_var)
+    return vec
+
+
+def bn_resolve(vec):
+    """Fill a vec from ``bn_finalize_lazy`` that no ``bn_apply`` consumed yet (the downsample BN of a bottleneck is applied
+    inside another layer's pass)."""
+    pend = getattr(vec, '_b200seg_pending', None)
+    if pend is not None:
+        stats, c, count, gamma, beta, eps, momentum, rm, rv = pend
+        p = vec.data_ptr()
+        _lib.check(_lib.load().b200seg_bn_finalize(
+            stats.data_ptr(), c, count, gamma.data_ptr(), beta.data_ptr(), eps, momentum,
+            rm.data_ptr() if rm is not None else None, rv.data_ptr() if rv is not None else None,
+            p, p + 4 * c, p + 8 * c, p + 12 * c, _stream()), 'bn_finalize')
+        _lib.count_launch()
+        vec._b200seg_pending = None
+    return vec
+
+
 def bn_eval_affine(c, gamma, beta, running_mean, running_var, eps):
     vec = torch.empty((4, c), dtype=torch.float32, device=gamma.device)
     p = vec.data_ptr()
@@ -624,6 +652,21 @@ def bn_apply(x, y, vec, relu, res=None, res_vec=None):
     """y = relu?(x*scale + shift [+ res | + res*res_scale + res_shift])"""
     c = x.c
     p = vec.data_ptr()
+    if res_vec is not None:
+        bn_resolve(res_vec)
+    pend = getattr(vec, '_b200seg_pending', None)
+    if pend is not None:
+        stats, pc, count, gamma, beta, eps, momentum, rm, rv = pend
+        assert pc == c and count == x.pixels, 'bn_apply: statistics of another tensor'
+        rp = res_vec.data_ptr() if res_vec is not None else None
+        _lib.check(_lib.load().b200seg_bn_apply_train(
+            x.ptr, x.ct, x.c_off, y.ptr, y.ct, y.c_off, c, x.pixels, stats.data_ptr(), gamma.data_ptr(), beta.data_ptr(),
+            eps, momentum, rm.data_ptr() if rm is not None else None, rv.data_ptr() if rv is not None else None, p,
+            int(relu), res.ptr if res is not None else None, res.ct if res is not None else 0,
+            res.c_off if res is not None else 0, rp, rp + 4 * c if rp is not None else None, _stream()), 'bn_apply_train')
+        vec._b200seg_pending = None
+        _lib.count_launch()
+        return
     if res is None:
         _lib.check(_lib.load().b200seg_bn_apply(x.ptr, x.ct, x.c_off, y.ptr, y.ct, y.c_off, c, x.pixels, p, p + 4 * c,
                                                 int(relu), _stream()), 'bn_apply')

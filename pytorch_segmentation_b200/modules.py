@@ -81,7 +81,7 @@ class ConvNormAct(nn.Sequential):
             stats = torch.zeros((2 * k,), dtype=torch.float32, device=dev)
             E.conv_fprop([(x, pw, self.dilation)], raw, stats=stats)
             track = bn.track_running_stats and bn.running_mean is not None
-            vec = E.bn_finalize(stats, k, x.pixels, bn.weight, bn.bias, bn.eps, bn.momentum,
+            vec = E.bn_finalize_lazy(stats, k, x.pixels, bn.weight, bn.bias, bn.eps, bn.momentum,
                                 bn.running_mean if track else None, bn.running_var if track else None)
             if track and bn.num_batches_tracked is not None:
                 bn.num_batches_tracked.add_(1)

@@ -76,7 +76,7 @@ class _ConvBNFn(torch.autograd.Function):
                                  % ([xa.n, cout, oh, ow],))
             stats = torch.zeros((2 * cout,), dtype=torch.float32, device=dev)
             E.conv_fprop([src], raw, stats=stats)
-            vec = E.bn_finalize(stats, cout, raw.pixels, gamma, beta, bn.eps, bn.momentum,
+            vec = E.bn_finalize_lazy(stats, cout, raw.pixels, gamma, beta, bn.eps, bn.momentum,
                                 bn.running_mean if track else None, bn.running_var if track else None)
             if track and bn.num_batches_tracked is not None:
                 bn.num_batches_tracked.add_(1)

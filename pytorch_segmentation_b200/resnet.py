@@ -49,7 +49,7 @@ class _Unit:
         if training:
             E.conv_fprop([(x, pw, self.dil, self.stride)], raw, stats=stats)
             track = bn.track_running_stats and bn.running_mean is not None
-            vec = E.bn_finalize(stats, self.cout, raw.pixels, bn.weight, bn.bias, bn.eps, bn.momentum,
+            vec = E.bn_finalize_lazy(stats, self.cout, raw.pixels, bn.weight, bn.bias, bn.eps, bn.momentum,
                                 bn.running_mean if track else None, bn.running_var if track else None)
         else:
             E.conv_fprop([(x, pw, self.dil, self.stride)], raw)
@@ -190,7 +190,7 @@ class ResNet50Features(nn.Module):
             stats0 = torch.zeros((2 * raw0.c,), dtype=torch.float32, device=dev)
             E.conv_fprop([(col, pw0, 1)], raw0, stats=stats0)
             track = bn.track_running_stats and bn.running_mean is not None
-            v0 = E.bn_finalize(stats0, raw0.c, raw0.pixels, bn.weight, bn.bias, bn.eps, bn.momentum,
+            v0 = E.bn_finalize_lazy(stats0, raw0.c, raw0.pixels, bn.weight, bn.bias, bn.eps, bn.momentum,
                                bn.running_mean if track else None, bn.running_var if track else None)
         else:
             E.conv_fprop([(col, pw0, 1)], raw0)

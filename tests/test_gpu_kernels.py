@@ -759,3 +759,30 @@ def test_anchored_window_source_is_checked(E):
         E._conv(E._lib.load().b200seg_conv_dgrad, 'conv_dgrad', 1, oh, ow,
                 [(win, pw.wf.data_ptr(), pw.k_rows, pw.r, pw.s, 1, 1)], E.Act.empty(1, oh, ow, 64, 'cuda').ptr, 64, 0, 64,
                 False, None, None, False, None)
+
+
+def test_bn_apply_train_equals_finalize_then_apply(E):
+    # the fused launch (lazy finalize consumed by bn_apply) against the two-launch form, residual variants included
+    g = torch.Generator().manual_seed(11)
+    n, h, w, c = 2, 12, 20, 64
+    x = nhwc(torch.randn(n, c, h, w, generator=g) * 2 + 0.5)
+    res = nhwc(torch.randn(n, c, h, w, generator=g))
+    gamma, beta = (1 + 0.1 * torch.randn(c, generator=g)).cuda(), (0.1 * torch.randn(c, generator=g)).cuda()
+    stats = E.bn_stats(x)
+    for use_res, res_affine in ((False, False), (True, False), (True, True)):
+        rm1, rv1 = torch.zeros(c, device='cuda'), torch.ones(c, device='cuda')
+        rm2, rv2 = rm1.clone(), rv1.clone()
+        rvec = E.bn_finalize(E.bn_stats(res), c, res.pixels, gamma, beta, 1e-5, 0.1, None, None) if res_affine else None
+        v1 = E.bn_finalize(stats, c, x.pixels, gamma, beta, 1e-5, 0.1, rm1, rv1)
+        y1 = E.Act.empty(n, h, w, c, 'cuda')
+        E.bn_apply(x, y1, v1, True, res=res if use_res else None, res_vec=rvec)
+        v2 = E.bn_finalize_lazy(stats, c, x.pixels, gamma, beta, 1e-5, 0.1, rm2, rv2)
+        assert getattr(v2, '_b200seg_pending', None) is not None
+        before = E._lib.launches()
+        y2 = E.Act.empty(n, h, w, c, 'cuda')
+        E.bn_apply(x, y2, v2, True, res=res if use_res else None, res_vec=rvec)
+        assert E._lib.launches() - before == 1 and v2._b200seg_pending is None
+        assert torch.equal(y1.t, y2.t) and torch.equal(v1, v2) and torch.equal(rm1, rm2) and torch.equal(rv1, rv2)
+    # a lazy vec nobody applied resolves to the same numbers on demand
+    v3 = E.bn_resolve(E.bn_finalize_lazy(stats, c, x.pixels, gamma, beta, 1e-5, 0.1, None, None))
+    assert torch.equal(v3[0], v1[0]) and torch.equal(v3[3], v1[3])
