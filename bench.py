@@ -163,7 +163,7 @@ def run_b200(args):
     x_dev, t_dev = x_host.to(dev), t_host.to(dev)
     loss_host = torch.zeros((), dtype=torch.float32).pin_memory()
 
-    use_graph = args.graph == 'on' or (args.graph == 'auto' and world == 1)
+    use_graph = args.graph in ('on', 'auto')
     eager = P.TrainStep(model, opt, bucketer, graph=False)
     step = P.TrainStep(model, opt, bucketer, graph=True) if use_graph else eager
 
@@ -301,6 +301,14 @@ def run_b200(args):
                            'kernels': detail}, f, indent=1)
         print(json.dumps(line), flush=True)
     if world > 1:
+        torch.cuda.synchronize()
+        dist.barrier()
+        if use_graph:
+            # a captured step holds NCCL kernels: tearing the communicator down under a live graph (or the graph
+            # after the communicator) can block at interpreter exit, so the ranks leave together right here
+            sys.stdout.flush()
+            sys.stderr.flush()
+            os._exit(0)
         dist.destroy_process_group()
 
 
@@ -314,7 +322,7 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--detail', default=None, help='write the per-launch CUDA-event timings of every conv to this file')
     ap.add_argument('--graph', default='auto', choices=['auto', 'on', 'off'],
-                    help='replay the step from a CUDA graph (auto: on for 1 GPU)')
+                    help='replay the step from a CUDA graph (auto = on; the bucketed NCCL all-reduces are captured with it)')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)
