@@ -113,10 +113,19 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
     const CUtensorMap* n_map = p.shift_m ? &p.y_map : xm;
     // a patch is skipped only when every tap of the group reads nothing but padding there (a tap that does is
     // zero-filled by the TMA unit)
+    int gdy[4], gdx[4];                            // the group's shifts in registers: the walkers below are single
+#pragma unroll                                     // threads on the critical path
+    for (int j = 0; j < 4; ++j) {
+        gdy[j] = p.tap_dy[min(tap + j, taps - 1)];
+        gdx[j] = p.tap_dx[min(tap + j, taps - 1)];
+    }
     auto group_in_bounds = [&](const PatchWalker& w) {
-        for (int j = 0; j < gt; ++j)
-            if (w.in_bounds(p, p.tap_dy[tap + j], p.tap_dx[tap + j])) return true;
-        return false;
+        if (p.no_skip) return true;
+        bool any_tap = w.in_bounds(p, dy, dx);
+#pragma unroll
+        for (int j = 1; j < 4; ++j)
+            if (j < gt) any_tap |= w.in_bounds(p, gdy[j], gdx[j]);
+        return any_tap;
     };
     const int kp_begin = split * p.patches_per_split;
     const int kp_end = min(kp_begin + p.patches_per_split, p.patches);
@@ -169,10 +178,12 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
                         tma_load_4d(sa + kABytes + b * kBoxBytes, n_map, &full[stage], n_tile * p.bn + b * 64, x0 + ndx,
                                     y0 + ndy, n0);
                 } else {
-                    for (int j = 0; j < gt; ++j)
-                        for (int b = 0; b < n_boxes; ++b)
-                            tma_load_4d(sa + kABytes + (j * n_boxes + b) * kBoxBytes, &p.x_map[p.tap_map[tap + j]],
-                                        &full[stage], b * 64, x0 + p.tap_dx[tap + j], y0 + p.tap_dy[tap + j], n0);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        if (j < gt)
+                            for (int b = 0; b < n_boxes; ++b)
+                                tma_load_4d(sa + kABytes + (j * n_boxes + b) * kBoxBytes, &p.x_map[p.tap_map[tap + j]],
+                                            &full[stage], b * 64, x0 + gdx[j], y0 + gdy[j], n0);
                 }
                 if (++stage == kStages) {
                     stage = 0;
