@@ -59,11 +59,12 @@ class WindowAct(Act):
     """An anchored window source (include/b200seg.h, b200seg_conv_src.x_rows): ``c`` is the window length in elements
     and may exceed the buffer's channels per pixel — the window runs on into the following pixels.  Only conv_fprop /
     conv_wgrad take it."""
-    __slots__ = ()
+    __slots__ = ('algo_k',)
 
-    def __init__(self, t, window):
+    def __init__(self, t, window, algo_k=None):
         assert t.dim() == 4 and t.dtype == BF16 and t.is_contiguous() and window % 8 == 0 and t.shape[3] % 8 == 0
         self.t, self.c_off, self.c = t, 0, window
+        self.algo_k = algo_k        # real multiply-adds per output element and output channel (profiling only)
 
 
 def as_act(x, what='input'):
@@ -369,7 +370,7 @@ def space_to_depth(x, r, s, pad):
     _lib.check(_lib.load().b200seg_space_to_depth_nchw(x.data_ptr(), n, c, h, w, r, s, pad, z.data_ptr(), cs, _stream()),
                'space_to_depth')
     _lib.count_launch()
-    return WindowAct(z, (s + 1) // 2 * cs), oh, ow
+    return WindowAct(z, (s + 1) // 2 * cs, algo_k=r * s * c), oh, ow
 
 
 def unpack_wgrad_s2d(dwin, pw, lane=False):
@@ -424,7 +425,7 @@ def _conv(fn, what, n, h, w, srcs, out_ptr, y_ct, y_off, k, out_fp32, scale, bia
     if PROFILE is not None:
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         # nominal dense flops: fprop counts output pixels; a stride-2 dgrad source has h*w/4 dY pixels
-        flops = 2.0 * n * h * w * k * sum(x.c * r * s / (st * st if what == 'conv_dgrad' else 1)
+        flops = 2.0 * n * h * w * k * sum((getattr(x, 'algo_k', None) or x.c * r * s) / (st * st if what == 'conv_dgrad' else 1)
                                           for x, _, _, r, s, _, st in srcs)
         tag = '%s %dx%dx%d k%d %s' % (what, n, h, w, k, '+'.join('c%d r%d d%d%s' % (x.c, r, d, ' s2' if st == 2 else '')
                                                               for x, _, _, r, _, d, st in srcs))
@@ -581,7 +582,7 @@ def _conv_wgrad(dy, x, k_out, r, s, dil, dw=None, stride=1):
         ev1.record()
         PROFILE.append(('conv_wgrad %dx%dx%d k%d c%d r%d d%d%s' % (dy.n, dy.h, dy.w, dy.c, x.c, r, dil,
                                                                    ' s2' if stride == 2 else ''),
-                        2.0 * dy.pixels * dy.c * x.c * r * s, ev0, ev1))
+                        2.0 * dy.pixels * dy.c * (getattr(x, 'algo_k', None) or x.c * r * s), ev0, ev1))
     _lib.count_launch(2)
     return dw
 
