@@ -143,6 +143,13 @@ def run_b200(args):
     world = int(os.environ.get('WORLD_SIZE', '1'))
     if not torch.cuda.is_available():
         raise RuntimeError('bench.py: no CUDA device — the B200 arm has no CPU fallback (use --impl reference)')
+    if world > 1:
+        # the gradient all-reduce runs under backward: give NCCL a few SMs of its own instead of letting it push the
+        # one-CTA-per-SM conv kernels into a second wave (csrc/common.cu gemm_sm_count)
+        if args.sm_reserve:
+            os.environ.setdefault('B200SEG_SM_RESERVE', str(args.sm_reserve))
+        if args.nccl_ctas:
+            os.environ.setdefault('NCCL_MAX_CTAS', str(args.nccl_ctas))
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     if world > 1:
@@ -155,7 +162,7 @@ def run_b200(args):
     model = P.DeepLabV3Plus(NC).to(dev).train()
     # one multi-tensor launch (b200seg_sgd_multi); the 1/world of the gradient average is folded into the update
     opt = P.optim.SGD(model.parameters(), lr=1e-3, momentum=0.9, grad_scale=1.0 / world)
-    bucketer = GradBucketer(model.parameters(), average=False) if world > 1 else None
+    bucketer = GradBucketer(model.parameters(), bucket_mb=args.bucket_mb, average=False).attach() if world > 1 else None
 
     g = torch.Generator(device='cpu').manual_seed(100 + rank)
     x_host = torch.randn(B, 3, H, W, generator=g).pin_memory()
@@ -321,6 +328,9 @@ def main():
     ap.add_argument('--batch', type=int, default=16, help='images per GPU per step')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--detail', default=None, help='write the per-launch CUDA-event timings of every conv to this file')
+    ap.add_argument('--bucket-mb', type=float, default=64.0, help='N > 1: gradient all-reduce bucket size')
+    ap.add_argument('--sm-reserve', type=int, default=0, help='N > 1: SMs the conv kernels leave to NCCL')
+    ap.add_argument('--nccl-ctas', type=int, default=0, help='N > 1: NCCL_MAX_CTAS (0 = NCCL default)')
     ap.add_argument('--graph', default='auto', choices=['auto', 'on', 'off'],
                     help='replay the step from a CUDA graph (auto = on; the bucketed NCCL all-reduces are captured with it)')
     args = ap.parse_args()

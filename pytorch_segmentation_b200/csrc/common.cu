@@ -31,6 +31,19 @@ int sm_count() {
     return cached[dev];
 }
 
+// SMs the tensor-core kernels size their grids for.  They hold one CTA per SM (227 KB of shared memory) and stride
+// their tiles statically, so a co-running kernel that takes a few SMs (NCCL's all-reduce under data parallelism)
+// would push the last CTAs into a second wave and nearly double the launch; B200SEG_SM_RESERVE=<n> leaves n SMs free.
+int gemm_sm_count() {
+    static const int reserve = [] {
+        const char* e = getenv("B200SEG_SM_RESERVE");
+        const int v = e ? atoi(e) : 0;
+        return v > 0 && v < 64 ? v : 0;
+    }();
+    const int n = sm_count();
+    return n > reserve ? n - reserve : n;
+}
+
 // cuTensorMapEncodeTiled is a driver-API symbol; fetch it through the runtime so the library does not link
 // against libcuda.so (absent on build machines without a driver).
 static PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {

@@ -39,6 +39,7 @@ int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_
 int check_slice(const char* what, const void* p, int c_total, int c_off, int c);
 // grid size for a 256-thread grid-stride elementwise kernel over `total` items (capped at 16 CTAs per SM)
 int elementwise_grid(int64_t total);
+int gemm_sm_count();
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }

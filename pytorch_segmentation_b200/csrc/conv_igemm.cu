@@ -610,7 +610,7 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
         B200SEG_CUDA(cudaFuncSetAttribute(igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         attr_set = true;
     }
-    const int sms = sm_count();
+    const int sms = gemm_sm_count();
     B200SEG_CHECK(sms > 0, "conv: cannot query SM count");
     const int grid = p.num_tiles < sms ? p.num_tiles : sms;
     B200SEG_CUDA(launch_pdl(igemm_kernel, grid, kThreads, kSmemBytes, st, p));

@@ -372,7 +372,7 @@ int plan_wgrad_uncached(const b200seg_wgrad_desc* d, WgradPlan* pl) {
         pl->tap_group = ceil_div(taps, ngroups);
     }
     const int base_tiles = ceil_div(taps, pl->tap_group) * pl->tiles_m * pl->tiles_n;
-    int sms = sm_count();
+    int sms = gemm_sm_count();
     if (sms <= 0) sms = 148;
     int splits = sms / base_tiles;
     if (splits < 1) splits = 1;

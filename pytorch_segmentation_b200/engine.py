@@ -590,6 +590,28 @@ def _conv_wgrad(dy, x, k_out, r, s, dil, dw=None, stride=1):
 # ------------------------------------------------------------------------------------------------
 # batch norm
 # ------------------------------------------------------------------------------------------------
+# ------------------------------------------------------------------------------------------------
+# early gradient delivery (data parallelism)
+# ------------------------------------------------------------------------------------------------
+# A hand-sequenced autograd node (the whole ResNet-50 is one) returns its parameter gradients when its backward ends,
+# so a bucketed all-reduce driven by per-parameter hooks would see the whole backbone at once, at the very end of
+# backward, and run exposed.  A node calls ``deliver_grads`` whenever a stage's gradients are complete; with a sink
+# installed (parallel.GradBucketer.attach) they move into their all-reduce buckets right then and the collectives run
+# under the rest of backward.  Without a sink this is a no-op.
+GRAD_SINK = None
+
+
+def deliver_grads(grads, params):
+    """grads: {parameter: gradient tensor}; params: the parameters whose gradients are final.  The sink may replace
+    entries of ``grads`` (by views of its flat buffers)."""
+    if GRAD_SINK is None:
+        return
+    ready = [p for p in params if grads.get(p) is not None]
+    if ready:
+        join_wgrad_lane()            # weight gradients live on the side stream until joined
+        GRAD_SINK(grads, ready)
+
+
 def bn_stats(x):
     stats = torch.empty((2 * x.c,), dtype=torch.float32, device=x.t.device)
     _lib.check(_lib.load().b200seg_bn_stats(x.ptr, x.ct, x.c_off, x.c, x.pixels, stats.data_ptr(), _stream()),

@@ -29,6 +29,43 @@ class GradBucketer:
         self._build(bucket_mb, first_bucket_mb)
         self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
         self.enabled = True         # set False on non-final micro-steps of gradient accumulation
+        self._early = set()         # parameters whose gradient reached its slot before autograd delivered it
+
+    def attach(self):
+        """Become the engine's early-gradient sink (engine.deliver_grads): hand-sequenced nodes such as the ResNet-50
+        backbone then feed their buckets stage by stage instead of all at once when their backward ends."""
+        from . import engine as E
+        E.GRAD_SINK = self._deliver
+        return self
+
+    def detach(self):
+        from . import engine as E
+        if E.GRAD_SINK == self._deliver:
+            E.GRAD_SINK = None
+
+    def _deliver(self, grads, params):
+        if not self.enabled:
+            return
+        for p in params:
+            slot = self._slot.get(id(p))
+            g = grads[p]
+            # only a fresh gradient can bypass AccumulateGrad's add; anything else takes the ordinary hook path
+            if (slot is None or p.grad is not None or id(p) in self._early or g.dtype != p.dtype
+                    or g.numel() != p.numel()):
+                continue
+            bi, off, n = slot
+            view = self._buckets[bi][0][off:off + n].view_as(p)
+            if g.is_cuda and g.dtype == torch.float32:
+                self._moves[bi].append((view, g.contiguous()))
+            else:
+                view.copy_(g.reshape(p.shape))
+            # the node returns None for this parameter: .grad is set here, AccumulateGrad and its hook never run
+            p.grad = view
+            grads[p] = None
+            self._early.add(id(p))
+            self._ready[bi] += 1
+            if self._ready[bi] == self._pending[bi]:
+                self._launch(bi)
 
     def _build(self, bucket_mb, first_bucket_mb):
         cap = int(first_bucket_mb * (1 << 20))
@@ -70,6 +107,12 @@ class GradBucketer:
         bi, off, n = self._slot[id(p)]
         flat = self._buckets[bi][0]
         view = flat[off:off + n].view_as(p)
+        if id(p) in self._early:
+            # delivered by its node ahead of autograd (which still runs this hook, with an undefined gradient, when
+            # the node returns None): the slot is filled and counted, .grad must simply still be that slot
+            if p.grad is None or p.grad.data_ptr() != view.data_ptr():
+                raise RuntimeError('GradBucketer: a gradient delivered early was replaced before the step finished')
+            return
         if p.grad.data_ptr() != view.data_ptr():
             g = p.grad
             if g.is_cuda and g.dtype == torch.float32 and g.is_contiguous():
@@ -117,6 +160,7 @@ class GradBucketer:
                 self._buckets[bi][0].div_(self.world)
         self._handles = []
         self._ready = [0] * len(self._buckets)
+        self._early.clear()
 
     def zero_grad(self):
         """Zero the flat buffers in place (gradients stay views of them)."""
@@ -124,6 +168,7 @@ class GradBucketer:
             flat.zero_()
 
     def remove(self):
+        self.detach()
         for h in self._hooks:
             h.remove()
         self._hooks = []

@@ -255,6 +255,8 @@ class ResNet50Features(nn.Module):
                 d = layers[li][bi].backward(recs[li][bi], d, training, grads, dout_masked=masked,
                                             mask_in=not (li == 0 and bi == 0), red_of=red_of)
                 masked = not (li == 0 and bi == 0)
+            # this stage's gradients are final: a data-parallel sink starts their all-reduce under the remaining stages
+            E.deliver_grads(grads, [p for blk in layers[li] for u in blk.units() for p in u.params()])
         if d is not None:
             da0 = E.maxpool_bwd(d, idx, a0.h, a0.w)
             if gfeats[0] is not None:

@@ -104,3 +104,36 @@ def test_bucketer_layout_reverse_order_and_sizes():
         assert float(flat.sum()) == flat.numel()
         for p, off, n in slots:
             assert p.grad.data_ptr() == flat[off:off + n].data_ptr()
+
+
+def test_bucketer_early_delivery_feeds_buckets_before_autograd():
+    from pytorch_segmentation_b200 import engine as E
+    ps = [torch.nn.Parameter(torch.zeros(n)) for n in (4, 6, 300000, 8)]
+    b = GradBucketer(ps, bucket_mb=1.0, first_bucket_mb=1.0).attach()
+    try:
+        assert E.GRAD_SINK is not None
+        launched = []
+        b._launch = lambda bi, _orig=b._launch: (launched.append(bi), _orig(bi))[1]
+        # a hand-sequenced node finished the stage that owns ps[2] and ps[3] (reverse order: they fill bucket 0 / 1 first)
+        grads = {ps[3]: torch.full((8,), 2.0), ps[2]: torch.full((300000,), 3.0), ps[1]: None}
+        E.deliver_grads(grads, [ps[3], ps[2], ps[1]])
+        assert grads[ps[3]] is None and grads[ps[2]] is None          # the node returns None for them
+        assert ps[3].grad is not None and float(ps[3].grad.sum()) == 16.0 and float(ps[2].grad[5]) == 3.0
+        assert len(launched) >= 1                                       # a complete bucket went out immediately
+        b._on_grad(ps[3])                                               # autograd still runs the hook: a no-op
+        # the rest arrives through autograd's hooks as usual
+        for p in ps[:2]:
+            p.grad = torch.ones_like(p)
+            b._on_grad(p)
+        b.finish()
+        assert sorted(set(launched)) == list(range(b.num_buckets))
+        for flat, slots in b._buckets:
+            for p, off, n in slots:
+                assert p.grad.data_ptr() == flat[off:off + n].data_ptr()
+        # a parameter that already holds a gradient (accumulation) is not delivered early
+        grads = {ps[0]: torch.ones(4)}
+        E.deliver_grads(grads, [ps[0]])
+        assert grads[ps[0]] is not None
+    finally:
+        b.remove()
+    assert E.GRAD_SINK is None
