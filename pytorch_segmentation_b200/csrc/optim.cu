@@ -119,8 +119,16 @@ __global__ void __launch_bounds__(256) copy_multi_kernel(const __grid_constant__
 // pack_weights_im2col_kernel in pack.cu / im2col.cu)
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int kPackTensors = 48;
-constexpr int kPackTile = 32;            // a block packs a 32 (k) x 32 (c) x taps tile of one weight
+constexpr int kPackTile = 32;            // a block packs a TK (k) x 32 (c) x taps tile of one weight
 constexpr int kPackMaxTaps = 9;
+constexpr int kPackSmemFloats = kPackTile * (kPackTile * kPackMaxTaps + 1);
+// k rows per tile: as many as fit the staging buffer (32 for 3x3, 256 for 1x1 — a 32 x 32 tile of a 1x1 weight is 4
+// elements per thread, and 12 M of the model's 39 M conv weights are 1x1)
+__host__ __device__ inline int pack_tile_k(int taps) {
+    const int rows = kPackSmemFloats / (kPackTile * taps + 1);
+    const int tk = rows / kPackTile * kPackTile;
+    return tk > 256 ? 256 : tk;
+}
 
 struct PackChunk {
     b200seg_pack_desc t[kPackTensors];
@@ -134,7 +142,7 @@ struct PackChunk {
 // (wf[tap][k][c..c+31], wd[tap'][c][k..k+31]).
 __global__ void __launch_bounds__(256) pack_multi_kernel(const __grid_constant__ PackChunk c) {
     pdl_prologue();
-    __shared__ float tile[kPackTile][kPackTile * kPackMaxTaps + 1];
+    __shared__ __align__(16) float tile[kPackSmemFloats];
     int lo = 0, hi = c.n - 1;
     while (lo < hi) {
         const int mid = (lo + hi + 1) >> 1;
@@ -158,36 +166,66 @@ __global__ void __launch_bounds__(256) pack_multi_kernel(const __grid_constant__
         }
         return;
     }
-    const int rows_k = t.k_rows > t.k_cols ? t.k_rows : t.k_cols;     // both are k rounded up to 8
+    const int tk = pack_tile_k(taps);
     const int tiles_c = (t.c_rows + kPackTile - 1) / kPackTile;
-    const int k0 = (local / tiles_c) * kPackTile, c0 = (local % tiles_c) * kPackTile;
+    const int k0 = (local / tiles_c) * tk, c0 = (local % tiles_c) * kPackTile;
     const int run = kPackTile * taps;                                  // contiguous floats per k row of the tile
-    for (int i = threadIdx.x; i < kPackTile * run; i += 256) {
-        const int kk = i / run, j = i - kk * run;                      // j = cc * taps + tap
-        const int cc = j / taps;
-        float v = 0.f;
-        if (k0 + kk < t.k && c0 + cc < t.c) v = __ldg(w + (static_cast<size_t>(k0 + kk) * t.c + c0) * taps + j);
-        tile[kk][j] = v;
+    const int pitch = run + 1;
+    // stage: float4 loads when every k row of the tile starts 16-byte aligned and lies inside the tensor
+    const bool vec = ((static_cast<long long>(t.c) * taps) & 3) == 0 && c0 + kPackTile <= t.c &&
+                     (reinterpret_cast<uintptr_t>(w) & 15) == 0;
+    if (vec) {
+        const int run4 = run >> 2;
+        for (int i = threadIdx.x; i < tk * run4; i += 256) {
+            const int kk = i / run4, j = (i - kk * run4) << 2;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (k0 + kk < t.k) v = __ldg(reinterpret_cast<const float4*>(w + (static_cast<size_t>(k0 + kk) * t.c + c0) * taps + j));
+            float* d = tile + kk * pitch + j;
+            d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+        }
+    } else {
+        for (int i = threadIdx.x; i < tk * run; i += 256) {
+            const int kk = i / run, j = i - kk * run;                  // j = cc * taps + tap
+            const int cc = j / taps;
+            float v = 0.f;
+            if (k0 + kk < t.k && c0 + cc < t.c) v = __ldg(w + (static_cast<size_t>(k0 + kk) * t.c + c0) * taps + j);
+            tile[kk * pitch + j] = v;
+        }
     }
     __syncthreads();
-    // fprop packing: [tap][k_rows][c], 32 consecutive c per (tap, k)
+    // fprop packing: [tap][k_rows][c], 32 consecutive c per (tap, k): a thread writes a bf16 pair
     if (wf) {
-        for (int i = threadIdx.x; i < taps * kPackTile * kPackTile; i += 256) {
-            const int cc = i % kPackTile, kk = (i / kPackTile) % kPackTile, tap = i / (kPackTile * kPackTile);
-            if (k0 + kk < t.k_rows && c0 + cc < t.c)
-                wf[(static_cast<size_t>(tap) * t.k_rows + k0 + kk) * t.c + c0 + cc] = __float2bfloat16(tile[kk][cc * taps + tap]);
+        const bool pair = (t.c & 1) == 0;
+        for (int i = threadIdx.x; i < taps * tk * (kPackTile / 2); i += 256) {
+            const int cc = (i % (kPackTile / 2)) * 2, kk = (i / (kPackTile / 2)) % tk, tap = i / ((kPackTile / 2) * tk);
+            if (k0 + kk >= t.k_rows || c0 + cc >= t.c) continue;
+            __nv_bfloat16* d = wf + (static_cast<size_t>(tap) * t.k_rows + k0 + kk) * t.c + c0 + cc;
+            const float a = tile[kk * pitch + cc * taps + tap], b = tile[kk * pitch + (cc + 1) * taps + tap];
+            if (pair && c0 + cc + 1 < t.c) {
+                *reinterpret_cast<__nv_bfloat162*>(d) = __floats2bfloat162_rn(a, b);
+            } else {
+                d[0] = __float2bfloat16(a);
+                if (c0 + cc + 1 < t.c) d[1] = __float2bfloat16(b);
+            }
         }
     }
-    // dgrad packing: [tap mirrored][c_rows][k_cols], 32 consecutive k per (tap, c)
+    // dgrad packing: [tap mirrored][c_rows][k_cols], consecutive k per (tap, c): a bf16 pair per thread
     if (wd) {
-        for (int i = threadIdx.x; i < taps * kPackTile * kPackTile; i += 256) {
-            const int kk = i % kPackTile, cc = (i / kPackTile) % kPackTile, tap = i / (kPackTile * kPackTile);
-            if (c0 + cc < t.c_rows && k0 + kk < t.k_cols)
-                wd[(static_cast<size_t>(taps - 1 - tap) * t.c_rows + c0 + cc) * t.k_cols + k0 + kk] =
-                    __float2bfloat16(tile[kk][cc * taps + tap]);
+        const bool pair = (t.k_cols & 1) == 0;
+        const int hk = tk / 2;
+        for (int i = threadIdx.x; i < taps * kPackTile * hk; i += 256) {
+            const int kk = (i % hk) * 2, cc = (i / hk) % kPackTile, tap = i / (hk * kPackTile);
+            if (c0 + cc >= t.c_rows || k0 + kk >= t.k_cols) continue;
+            __nv_bfloat16* d = wd + (static_cast<size_t>(taps - 1 - tap) * t.c_rows + c0 + cc) * t.k_cols + k0 + kk;
+            const float a = tile[kk * pitch + cc * taps + tap], b = tile[(kk + 1) * pitch + cc * taps + tap];
+            if (pair && k0 + kk + 1 < t.k_cols) {
+                *reinterpret_cast<__nv_bfloat162*>(d) = __floats2bfloat162_rn(a, b);
+            } else {
+                d[0] = __float2bfloat16(a);
+                if (k0 + kk + 1 < t.k_cols) d[1] = __float2bfloat16(b);
+            }
         }
     }
-    (void)rows_k;
 }
 
 }  // namespace
@@ -281,7 +319,7 @@ int b200seg_pack_weights_multi(const b200seg_pack_desc* descs, int n, b200seg_st
                     dd.k_cols = d.k_rows;
                 }
                 c.t[c.n] = dd;
-                nblk = ceil_div(krows, kPackTile) * ceil_div(crows, kPackTile);
+                nblk = ceil_div(krows, pack_tile_k(d.r * d.s)) * ceil_div(crows, kPackTile);
                 c.blk_start[c.n] = blocks;
                 blocks += nblk;
                 ++c.n;
