@@ -209,12 +209,14 @@ int b200seg_bn_apply(const void* x, int x_c_total, int x_c_offset, void* y, int 
                      int64_t pixels, const float* scale, const float* shift, int relu, b200seg_stream_t st);
 /* b200seg_bn_finalize + b200seg_bn_apply_add in one launch (train mode): scale / shift come straight from the conv
  * epilogue's stats[2c] (count = pixels); vec[4c] receives scale, shift, mean, invstd for the backward and the running
- * statistics move exactly as in b200seg_bn_finalize.  res / res_scale / res_shift as in b200seg_bn_apply_add. */
+ * statistics move exactly as in b200seg_bn_finalize.  res / res_scale / res_shift as in b200seg_bn_apply_add.
+ * mask_bits (optional, [pixels][c/8] bytes): bit j of byte (p, g) = (y[p][8g + j] > 0) — the ReLU mask of the output in
+ * 1/16 of its bytes, read by b200seg_grad_add_masked_bits in backward instead of the output itself. */
 int b200seg_bn_apply_train(const void* x, int x_c_total, int x_c_offset, void* y, int y_c_total, int y_c_offset, int c,
                            int64_t pixels, const float* stats, const float* gamma, const float* beta, float eps,
                            float momentum, float* running_mean, float* running_var, float* vec, int relu, const void* res,
                            int res_c_total, int res_c_offset, const float* res_scale, const float* res_shift,
-                           b200seg_stream_t st);
+                           uint8_t* mask_bits, b200seg_stream_t st);
 /* Residual form used by the ResNet bottlenecks of the backbone (pytorch_modules.backbones.resnet50, called at
  * models/deeplabv3plus.py:17-19,29): y = relu?(x*scale + shift + r) with r = res (identity) or res*res_scale +
  * res_shift (the downsample conv's raw output and its BN); res == NULL reduces to b200seg_bn_apply. */
@@ -232,6 +234,10 @@ int b200seg_relu_bwd_add(void* dx, int dx_c_total, int dx_c_offset, const void* 
 int b200seg_grad_add_masked(void* dx, int dx_c_total, int dx_c_offset, const void* dy, int dy_c_total, int dy_c_offset,
                             const void* y, int y_c_total, int y_c_offset, const void* xin, int xin_c_total,
                             int xin_c_offset, int c, int64_t pixels, b200seg_stream_t st);
+/* Same with the block-input mask given as bits (b200seg_bn_apply_train's mask_bits of that tensor). */
+int b200seg_grad_add_masked_bits(void* dx, int dx_c_total, int dx_c_offset, const void* dy, int dy_c_total, int dy_c_offset,
+                                 const void* y, int y_c_total, int y_c_offset, const uint8_t* xin_bits, int c, int64_t pixels,
+                                 b200seg_stream_t st);
 /* y = relu?(x0 + ... + x_{n-1}), 1 <= n <= 4 bf16 NHWC slices: the multi-resolution fuse of an HRModule
  * (models/hrnet.py:240-249) in one pass. */
 int b200seg_add_n_relu(int n_in, const void* const* x, const int* x_c_total, const int* x_c_offset, void* y, int y_c_total,

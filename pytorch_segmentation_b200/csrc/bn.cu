@@ -171,6 +171,8 @@ struct BnTrain {
     float* running_mean;
     float* running_var;
     float* vec;              // [4c] out: scale, shift, mean, invstd
+    unsigned char* bits;     // optional [pixels][c/8]: bit j of a byte = (y[8g + j] > 0), the ReLU mask of the output in
+                             // 1/16 of its bytes — what the residual gradient join reads instead of the output itself
 };
 
 // Elementwise kernels over a [pixels][c] slice use the column geometry too: a thread owns one 8-channel group for
@@ -255,6 +257,12 @@ __global__ void __launch_bounds__(kRedThreads) bn_apply_kernel(
             for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
         }
         st128(yb + p * y_ct, pack8(f));
+        if (tr.bits) {
+            unsigned int m = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) m |= (f[j] > 0.f ? 1u : 0u) << j;
+            tr.bits[p * groups + group] = static_cast<unsigned char>(m);
+        }
     }
 }
 
@@ -398,7 +406,8 @@ __global__ void __launch_bounds__(256) grad_add_masked_kernel(__nv_bfloat16* __r
                                                                const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off,
                                                                const __nv_bfloat16* __restrict__ y, int y_ct, int y_off,
                                                                const __nv_bfloat16* __restrict__ xin, int xin_ct,
-                                                               int xin_off, int groups, int64_t total) {
+                                                               int xin_off, const unsigned char* __restrict__ xin_bits,
+                                                               int groups, int64_t total) {
     pdl_prologue();
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
@@ -420,7 +429,11 @@ __global__ void __launch_bounds__(256) grad_add_masked_kernel(__nv_bfloat16* __r
                 for (int j = 0; j < 8; ++j) a[j] += d[j];
             }
         }
-        if (xin) {
+        if (xin_bits) {
+            const unsigned int m = __ldg(xin_bits + i);          // dense [pixels][groups]: element i
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a[j] = (m >> j) & 1u ? a[j] : 0.f;
+        } else if (xin) {
             float m[8];
             unpack8(ldcs128(xin + p * xin_ct + xin_off + g * 8), m);
 #pragma unroll
@@ -573,7 +586,7 @@ int b200seg_bn_apply_train(const void* x, int x_c_total, int x_c_offset, void* y
                            int64_t pixels, const float* stats, const float* gamma, const float* beta, float eps,
                            float momentum, float* running_mean, float* running_var, float* vec, int relu, const void* res,
                            int res_c_total, int res_c_offset, const float* res_scale, const float* res_shift,
-                           b200seg_stream_t stream) {
+                           uint8_t* mask_bits, b200seg_stream_t stream) {
     using namespace b200seg;
     clear_error();
     if (check_slice("bn_apply_train(x)", x, x_c_total, x_c_offset, c)) return 1;
@@ -594,6 +607,7 @@ int b200seg_bn_apply_train(const void* x, int x_c_total, int x_c_offset, void* y
     tr.running_mean = running_mean;
     tr.running_var = running_var;
     tr.vec = vec;
+    tr.bits = mask_bits;
     const ColGeom g = col_geom(c, pixels, 16);
     B200SEG_CUDA(launch_pdl(bn_apply_kernel, dim3(g.gx, g.gy), kRedThreads, 0, static_cast<cudaStream_t>(stream),
         static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset,
@@ -678,7 +692,24 @@ int b200seg_grad_add_masked(void* dx, int dx_c_total, int dx_c_offset, const voi
     B200SEG_CUDA(launch_pdl(grad_add_masked_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream), 
         static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, static_cast<const __nv_bfloat16*>(dy), dy_c_total,
         dy_c_offset, static_cast<const __nv_bfloat16*>(y), y_c_total, y_c_offset, static_cast<const __nv_bfloat16*>(xin),
-        xin_c_total, xin_c_offset, c / 8, total));
+        xin_c_total, xin_c_offset, static_cast<const unsigned char*>(nullptr), c / 8, total));
+    return 0;
+}
+
+int b200seg_grad_add_masked_bits(void* dx, int dx_c_total, int dx_c_offset, const void* dy, int dy_c_total, int dy_c_offset,
+                                 const void* y, int y_c_total, int y_c_offset, const uint8_t* xin_bits, int c, int64_t pixels,
+                                 b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    if (check_slice("grad_add_masked_bits(dx)", dx, dx_c_total, dx_c_offset, c)) return 1;
+    if (dy && check_slice("grad_add_masked_bits(dy)", dy, dy_c_total, dy_c_offset, c)) return 1;
+    if (y && check_slice("grad_add_masked_bits(y)", y, y_c_total, y_c_offset, c)) return 1;
+    B200SEG_CHECK(pixels > 0 && xin_bits && (dy || !y), "grad_add_masked_bits: bad arguments");
+    const int64_t total = pixels * (c / 8);
+    B200SEG_CUDA(launch_pdl(grad_add_masked_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream),
+        static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, static_cast<const __nv_bfloat16*>(dy), dy_c_total,
+        dy_c_offset, static_cast<const __nv_bfloat16*>(y), y_c_total, y_c_offset, static_cast<const __nv_bfloat16*>(nullptr),
+        0, 0, xin_bits, c / 8, total));
     return 0;
 }
 

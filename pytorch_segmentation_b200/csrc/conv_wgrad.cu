@@ -82,6 +82,10 @@ struct PatchWalker {
     }
 };
 
+// kGrouped = false is the one-tap-per-CTA kernel; the grouped code lives in its own instantiation so the single-thread
+// producer / MMA loops of the common case stay as small as they were (sharing one body cost the multi-tap launches
+// 5-20 %).
+template <bool kGrouped>
 __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constant__ WgradParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -101,7 +105,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
     const int m_tile = tile % p.tiles_m;
     tile /= p.tiles_m;
     const int taps = p.R * p.S;
-    const int G = p.tap_group;
+    const int G = kGrouped ? p.tap_group : 1;
     const int ngroups = (taps + G - 1) / G;
     const int tap = (tile % ngroups) * G;          // first tap of this CTA's group
     const int gt = min(G, taps - tap);             // taps in the group
@@ -116,17 +120,20 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
     int gdy[4], gdx[4];                            // the group's shifts in registers: the walkers below are single
 #pragma unroll                                     // threads on the critical path
     for (int j = 0; j < 4; ++j) {
-        gdy[j] = p.tap_dy[min(tap + j, taps - 1)];
-        gdx[j] = p.tap_dx[min(tap + j, taps - 1)];
+        gdy[j] = kGrouped ? p.tap_dy[min(tap + j, taps - 1)] : dy;
+        gdx[j] = kGrouped ? p.tap_dx[min(tap + j, taps - 1)] : dx;
     }
-    auto group_in_bounds = [&](const PatchWalker& w) {
-        if (p.no_skip) return true;
-        bool any_tap = w.in_bounds(p, dy, dx);
-#pragma unroll
-        for (int j = 1; j < 4; ++j)
-            if (j < gt) any_tap |= w.in_bounds(p, gdy[j], gdx[j]);
-        return any_tap;
-    };
+    // (a by-reference lambda over the __grid_constant__ parameter block made every p.* read in the single-thread
+    // walkers a generic load: 10-20 % on the multi-tap launches; the geometry is copied to registers instead)
+    const int gH = p.H, gW = p.W, gbw = p.bw, gbh = p.bh;
+    const bool no_skip = p.no_skip != 0;
+#define B200SEG_TAP_IN(w, ddy, ddx)                                                                                   \
+    (((w).py * gbh + (ddy) < gH) && ((w).py * gbh + gbh - 1 + (ddy) >= 0) && ((w).px * gbw + (ddx) < gW) &&           \
+     ((w).px * gbw + gbw - 1 + (ddx) >= 0))
+#define group_in_bounds(w)                                                                                            \
+    (kGrouped ? (no_skip || B200SEG_TAP_IN(w, dy, dx) || (gt > 1 && B200SEG_TAP_IN(w, gdy[1], gdx[1])) ||             \
+                 (gt > 2 && B200SEG_TAP_IN(w, gdy[2], gdx[2])) || (gt > 3 && B200SEG_TAP_IN(w, gdy[3], gdx[3])))      \
+              : (w).in_bounds(p, dy, dx))
     const int kp_begin = split * p.patches_per_split;
     const int kp_end = min(kp_begin + p.patches_per_split, p.patches);
 
@@ -173,7 +180,7 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
                 mbar_arrive_expect_tx(&full[stage], tx_bytes);
                 for (int b = 0; b < 2; ++b)
                     tma_load_4d(sa + b * kBoxBytes, m_map, &full[stage], m_tile * kBM + b * 64, x0 + mdx, y0 + mdy, n0);
-                if (G == 1) {
+                if (!kGrouped) {
                     for (int b = 0; b < n_boxes; ++b)
                         tma_load_4d(sa + kABytes + b * kBoxBytes, n_map, &full[stage], n_tile * p.bn + b * 64, x0 + ndx,
                                     y0 + ndy, n0);
@@ -261,6 +268,8 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
         tc_fence_after();
         tmem_dealloc(tmem_base, kMaxBN);
     }
+#undef group_in_bounds
+#undef B200SEG_TAP_IN
 }
 
 // dw[k][c][r][s] (+)= sum_split ws[split][tap][m][n], (m, n) = (k, c) or (c, k)
@@ -366,7 +375,7 @@ int plan_wgrad_uncached(const b200seg_wgrad_desc* d, WgradPlan* pl) {
     // tap groups: with X on the N side and a single narrow n-tile, several taps share one CTA (and one load of dY)
     const int taps = d->r * d->s;
     pl->tap_group = 1;
-    if (!pl->shift_m && pl->tiles_n == 1 && taps > 1 && pl->bn <= kMaxBN / 2 && tap_grouping_enabled()) {
+    if (!pl->shift_m && pl->tiles_n == 1 && taps > 1 && pl->bn <= kMaxBN / 4 && tap_grouping_enabled()) {   // measured: pairs of 128-wide taps do not pay
         const int gmax = kMaxBN / pl->bn;
         const int ngroups = ceil_div(taps, gmax);
         pl->tap_group = ceil_div(taps, ngroups);
@@ -504,12 +513,16 @@ int b200seg_conv_wgrad(const b200seg_wgrad_desc* d, b200seg_stream_t stream) {
 
     static bool attr_set = false;
     if (!attr_set) {
-        B200SEG_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        B200SEG_CUDA(cudaFuncSetAttribute(wgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        B200SEG_CUDA(cudaFuncSetAttribute(wgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         attr_set = true;
     }
     const int taps = d->r * d->s;
     const int grid = pl.splits * ceil_div(taps, pl.tap_group) * pl.tiles_m * pl.tiles_n;
-    B200SEG_CUDA(launch_pdl(wgrad_kernel, grid, kThreads, kSmemBytes, st, p));
+    if (pl.tap_group > 1)
+        B200SEG_CUDA(launch_pdl(wgrad_kernel<true>, grid, kThreads, kSmemBytes, st, p));
+    else
+        B200SEG_CUDA(launch_pdl(wgrad_kernel<false>, grid, kThreads, kSmemBytes, st, p));
 
     const long long total = static_cast<long long>(d->k_out) * d->c * taps;
     const int rb = 256;

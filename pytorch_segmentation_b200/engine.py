@@ -26,11 +26,12 @@ def _require_cuda(t, what):
 
 class Act:
     """A channel slice [c_off, c_off + c) of an NHWC bf16 buffer ``t`` of shape [n, h, w, c_total]."""
-    __slots__ = ('t', 'c_off', 'c')
+    __slots__ = ('t', 'c_off', 'c', 'bits')
 
     def __init__(self, t, c_off=0, c=None):
         assert t.dim() == 4 and t.dtype == BF16 and t.is_contiguous(), (t.shape, t.dtype, t.stride())
         self.t, self.c_off = t, c_off
+        self.bits = None          # optional uint8 [pixels, c/8] sign mask written by bn_apply(want_bits=True)
         self.c = t.shape[3] - c_off if c is None else c
         assert self.c_off % 8 == 0 and self.c % 8 == 0 and t.shape[3] % 8 == 0, \
             'channel counts and offsets must be multiples of 8 (got c=%d off=%d total=%d)' % (self.c, c_off, t.shape[3])
@@ -599,6 +600,7 @@ def _conv_wgrad(dy, x, k_out, r, s, dil, dw=None, stride=1):
 # installed (parallel.GradBucketer.attach) they move into their all-reduce buckets right then and the collectives run
 # under the rest of backward.  Without a sink this is a no-op.
 GRAD_SINK = None
+MASK_BITS = _os.environ.get('B200SEG_MASK_BITS', '1') != '0'      # ReLU masks of block outputs as bits (bn_apply / grad_add_masked)
 
 
 def deliver_grads(grads, params):
@@ -671,8 +673,9 @@ def bn_eval_affine(c, gamma, beta, running_mean, running_var, eps):
     return vec
 
 
-def bn_apply(x, y, vec, relu, res=None, res_vec=None):
-    """y = relu?(x*scale + shift [+ res | + res*res_scale + res_shift])"""
+def bn_apply(x, y, vec, relu, res=None, res_vec=None, want_bits=False):
+    """y = relu?(x*scale + shift [+ res | + res*res_scale + res_shift]).  ``want_bits``: also leave the sign mask of y as
+    bits in ``y.bits`` (train-mode fused path, full-buffer outputs only) for ``grad_add_masked``."""
     c = x.c
     p = vec.data_ptr()
     if res_vec is not None:
@@ -682,11 +685,16 @@ def bn_apply(x, y, vec, relu, res=None, res_vec=None):
         stats, pc, count, gamma, beta, eps, momentum, rm, rv = pend
         assert pc == c and count == x.pixels, 'bn_apply: statistics of another tensor'
         rp = res_vec.data_ptr() if res_vec is not None else None
+        bits = None
+        if want_bits and MASK_BITS and y.c_off == 0 and y.c == y.ct:
+            bits = torch.empty((y.pixels, c // 8), dtype=torch.uint8, device=y.t.device)
         _lib.check(_lib.load().b200seg_bn_apply_train(
             x.ptr, x.ct, x.c_off, y.ptr, y.ct, y.c_off, c, x.pixels, stats.data_ptr(), gamma.data_ptr(), beta.data_ptr(),
             eps, momentum, rm.data_ptr() if rm is not None else None, rv.data_ptr() if rv is not None else None, p,
             int(relu), res.ptr if res is not None else None, res.ct if res is not None else 0,
-            res.c_off if res is not None else 0, rp, rp + 4 * c if rp is not None else None, _stream()), 'bn_apply_train')
+            res.c_off if res is not None else 0, rp, rp + 4 * c if rp is not None else None,
+            bits.data_ptr() if bits is not None else None, _stream()), 'bn_apply_train')
+        y.bits = bits
         vec._b200seg_pending = None
         _lib.count_launch()
         return
@@ -734,6 +742,12 @@ def grad_add_masked(dx, dy=None, y=None, xin=None):
     """dx = (dx + dy * [y > 0]) * [xin > 0]; dy, y, xin optional Acts."""
     def trip(a):
         return (a.ptr, a.ct, a.c_off) if a is not None else (None, 0, 0)
+    if xin is not None and xin.bits is not None and xin.c_off == 0 and xin.c == dx.c:
+        _lib.check(_lib.load().b200seg_grad_add_masked_bits(dx.ptr, dx.ct, dx.c_off, *trip(dy), *trip(y),
+                                                            xin.bits.data_ptr(), dx.c, dx.pixels, _stream()),
+                   'grad_add_masked_bits')
+        _lib.count_launch()
+        return
     _lib.check(_lib.load().b200seg_grad_add_masked(dx.ptr, dx.ct, dx.c_off, *trip(dy), *trip(y), *trip(xin), dx.c, dx.pixels,
                                                    _stream()), 'grad_add_masked')
     _lib.count_launch()

@@ -85,10 +85,10 @@ class _Block:
         out = E.Act.empty(raw3.n, raw3.h, raw3.w, raw3.c, dev)
         if self.ud is not None:
             rawd, vd = self.ud.forward_raw(x, training, stats_of(self.ud))
-            E.bn_apply(raw3, out, v3, True, res=rawd, res_vec=vd)
+            E.bn_apply(raw3, out, v3, True, res=rawd, res_vec=vd, want_bits=training)
         else:
             rawd = vd = None
-            E.bn_apply(raw3, out, v3, True, res=x)
+            E.bn_apply(raw3, out, v3, True, res=x, want_bits=training)
         return out, (x, raw1, v1, a1, raw2, v2, a2, raw3, v3, rawd, vd, out)
 
     def backward(self, rec, dout, training, grads, need_dx=True, dout_masked=False, mask_in=True, red_of=None):

@@ -786,3 +786,28 @@ def test_bn_apply_train_equals_finalize_then_apply(E):
     # a lazy vec nobody applied resolves to the same numbers on demand
     v3 = E.bn_resolve(E.bn_finalize_lazy(stats, c, x.pixels, gamma, beta, 1e-5, 0.1, None, None))
     assert torch.equal(v3[0], v1[0]) and torch.equal(v3[3], v1[3])
+
+
+def test_relu_mask_bits_drive_the_gradient_join(E):
+    # bn_apply(want_bits) leaves (y > 0) as one byte per 8 channels; grad_add_masked reads it instead of y
+    g = torch.Generator().manual_seed(12)
+    n, h, w, c = 2, 9, 14, 48
+    x = nhwc(torch.randn(n, c, h, w, generator=g))
+    res = nhwc(torch.randn(n, c, h, w, generator=g))
+    gamma, beta = (1 + 0.1 * torch.randn(c, generator=g)).cuda(), (0.1 * torch.randn(c, generator=g)).cuda()
+    vec = E.bn_finalize_lazy(E.bn_stats(x), c, x.pixels, gamma, beta, 1e-5, 0.1, None, None)
+    y = E.Act.empty(n, h, w, c, 'cuda')
+    E.bn_apply(x, y, vec, True, res=res, want_bits=True)
+    assert y.bits is not None and tuple(y.bits.shape) == (n * h * w, c // 8)
+    want = (y.t.float() > 0).view(-1, c // 8, 8).to(torch.int32)
+    want = (want << torch.arange(8, device='cuda', dtype=torch.int32)).sum(-1).to(torch.uint8)
+    assert torch.equal(y.bits, want)
+    dx0 = nhwc(torch.randn(n, c, h, w, generator=g))
+    dy = nhwc(torch.randn(n, c, h, w, generator=g))
+    for use_dy in (True, False):
+        a, b = E.Act(dx0.t.clone()), E.Act(dx0.t.clone())
+        plain = E.Act(y.t)                                      # same tensor without the bits: reads y itself
+        before = E._lib.launches()
+        E.grad_add_masked(a, dy=dy if use_dy else None, xin=y)
+        E.grad_add_masked(b, dy=dy if use_dy else None, xin=plain)
+        assert E._lib.launches() - before == 2 and torch.equal(a.t, b.t)
