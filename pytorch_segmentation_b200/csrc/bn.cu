@@ -178,7 +178,11 @@ struct BnTrain {
 // Elementwise kernels over a [pixels][c] slice use the column geometry too: a thread owns one 8-channel group for
 // its whole pixel range, so the per-channel parameters live in registers (reloading them per element made these
 // kernels L1-bound at ~65 % of HBM bandwidth).
-__global__ void __launch_bounds__(kRedThreads) bn_apply_kernel(
+// kResAffine: the residual carries its own BN affine (downsample branch); kBits: also write the sign mask.  Separate
+// instantiations keep the common ones at 64 registers or fewer (4 resident CTAs per SM): at 73 the 134 MB passes ran
+// 113 us instead of 85.
+template <bool kResAffine, bool kBits>
+__global__ void __launch_bounds__(kRedThreads, 4) bn_apply_kernel(
     const __nv_bfloat16* __restrict__ x, int x_ct, int x_off, __nv_bfloat16* __restrict__ y, int y_ct, int y_off, int groups,
     int64_t pixels, int64_t ppb, int gpb, int rows, const float* __restrict__ scale, const float* __restrict__ shift,
     int relu, const __nv_bfloat16* __restrict__ res, int r_ct, int r_off, const float* __restrict__ res_scale,
@@ -192,39 +196,45 @@ __global__ void __launch_bounds__(kRedThreads) bn_apply_kernel(
         // training mode without a separate finalize launch: every thread derives its 8 channels' scale / shift from
         // the conv epilogue's sums (bn_finalize_kernel's arithmetic); the first block row also publishes them for the
         // backward and moves the running statistics
+        // (four channels at a time: the whole prologue live at once took the kernel past 64 registers and cost it a
+        // resident CTA per SM)
         const int c = groups * 8;
-        float s1[8], s2[8], gm[8], bt[8], mean[8], invstd[8], var[8];
-        load8f(tr.stats + group * 8, s1);
-        load8f(tr.stats + c + group * 8, s2);
-        load8f(tr.gamma + group * 8, gm);
-        load8f(tr.beta + group * 8, bt);
+        const bool publish = blockIdx.x == 0 && row == 0;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            mean[j] = s1[j] * tr.inv_count;
-            var[j] = fmaxf(fmaf(-mean[j], mean[j], s2[j] * tr.inv_count), 0.f);
-            invstd[j] = rsqrtf(var[j] + tr.eps);
-            sc[j] = gm[j] * invstd[j];
-            sh[j] = fmaf(-mean[j], sc[j], bt[j]);
-        }
-        if (blockIdx.x == 0 && row == 0) {
+        for (int hv = 0; hv < 2; ++hv) {
+            const int ch0 = group * 8 + hv * 4;
+            const float4 s1 = __ldg(reinterpret_cast<const float4*>(tr.stats + ch0));
+            const float4 s2 = __ldg(reinterpret_cast<const float4*>(tr.stats + c + ch0));
+            const float4 gm = __ldg(reinterpret_cast<const float4*>(tr.gamma + ch0));
+            const float4 bt = __ldg(reinterpret_cast<const float4*>(tr.beta + ch0));
+            const float s1v[4] = {s1.x, s1.y, s1.z, s1.w}, s2v[4] = {s2.x, s2.y, s2.z, s2.w};
+            const float gmv[4] = {gm.x, gm.y, gm.z, gm.w}, btv[4] = {bt.x, bt.y, bt.z, bt.w};
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int ch = group * 8 + j;
-                tr.vec[ch] = sc[j];
-                tr.vec[c + ch] = sh[j];
-                tr.vec[2 * c + ch] = mean[j];
-                tr.vec[3 * c + ch] = invstd[j];
-                if (tr.running_mean) tr.running_mean[ch] = fmaf(tr.momentum, mean[j] - tr.running_mean[ch], tr.running_mean[ch]);
-                if (tr.running_var)
-                    tr.running_var[ch] = fmaf(tr.momentum, var[j] * tr.unbias - tr.running_var[ch], tr.running_var[ch]);
+            for (int j = 0; j < 4; ++j) {
+                const float mean = s1v[j] * tr.inv_count;
+                const float var = fmaxf(fmaf(-mean, mean, s2v[j] * tr.inv_count), 0.f);
+                const float invstd = rsqrtf(var + tr.eps);
+                const float scj = gmv[j] * invstd, shj = fmaf(-mean, scj, btv[j]);
+                sc[hv * 4 + j] = scj;
+                sh[hv * 4 + j] = shj;
+                if (publish) {
+                    const int ch = ch0 + j;
+                    tr.vec[ch] = scj;
+                    tr.vec[c + ch] = shj;
+                    tr.vec[2 * c + ch] = mean;
+                    tr.vec[3 * c + ch] = invstd;
+                    if (tr.running_mean) tr.running_mean[ch] = fmaf(tr.momentum, mean - tr.running_mean[ch], tr.running_mean[ch]);
+                    if (tr.running_var)
+                        tr.running_var[ch] = fmaf(tr.momentum, var * tr.unbias - tr.running_var[ch], tr.running_var[ch]);
+                }
             }
         }
     } else {
         load8f(scale + group * 8, sc);
         load8f(shift + group * 8, sh);
     }
-    const bool res_affine = res != nullptr && res_scale != nullptr;
-    if (res_affine) {
+    const bool res_affine = kResAffine;
+    if (kResAffine) {
         load8f(res_scale + group * 8, rsc);
         load8f(res_shift + group * 8, rsh);
     }
@@ -235,6 +245,9 @@ __global__ void __launch_bounds__(kRedThreads) bn_apply_kernel(
     const __nv_bfloat16* xb = x + x_off + group * 8;
     const __nv_bfloat16* rb = res ? res + r_off + group * 8 : nullptr;
     __nv_bfloat16* yb = y + y_off + group * 8;
+    // a char store may alias anything: without the restrict copy the next iteration's loads could not move above it
+    // and the pass ran 35 % slower
+    unsigned char* __restrict__ bits = kBits ? tr.bits : nullptr;
 #pragma unroll 2
     for (int64_t p = p0 + row; p < p1; p += pstep) {
         float f[8];
@@ -245,7 +258,7 @@ __global__ void __launch_bounds__(kRedThreads) bn_apply_kernel(
             // residual branch: the identity, or the downsample conv's raw output with its own BN affine
             float r[8];
             unpack8(ldcs128(rb + p * r_ct), r);
-            if (res_affine) {
+            if (kResAffine) {
 #pragma unroll
                 for (int j = 0; j < 8; ++j) r[j] = fmaf(r[j], rsc[j], rsh[j]);
             }
@@ -257,11 +270,11 @@ __global__ void __launch_bounds__(kRedThreads) bn_apply_kernel(
             for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
         }
         st128(yb + p * y_ct, pack8(f));
-        if (tr.bits) {
+        if (kBits) {
             unsigned int m = 0;
 #pragma unroll
             for (int j = 0; j < 8; ++j) m |= (f[j] > 0.f ? 1u : 0u) << j;
-            tr.bits[p * groups + group] = static_cast<unsigned char>(m);
+            bits[p * groups + group] = static_cast<unsigned char>(m);
         }
     }
 }
@@ -575,10 +588,12 @@ int b200seg_bn_apply_add(const void* x, int x_c_total, int x_c_offset, void* y, 
     B200SEG_CHECK(scale && shift && pixels > 0, "bn_apply: bad arguments");
     B200SEG_CHECK((res_scale == nullptr) == (res_shift == nullptr), "bn_apply: residual scale and shift go together");
     const ColGeom g = col_geom(c, pixels, 16);
-    B200SEG_CUDA(launch_pdl(bn_apply_kernel, dim3(g.gx, g.gy), kRedThreads, 0, static_cast<cudaStream_t>(stream), 
-        static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset,
-        c / 8, pixels, g.pixels_per_block, g.gpb, g.rows, scale, shift, relu, static_cast<const __nv_bfloat16*>(res),
+#define B200SEG_BN_APPLY(RA, BITS)     B200SEG_CUDA(launch_pdl(bn_apply_kernel<RA, BITS>, dim3(g.gx, g.gy), kRedThreads, 0, static_cast<cudaStream_t>(stream),  \
+        static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset, \
+        c / 8, pixels, g.pixels_per_block, g.gpb, g.rows, scale, shift, relu, static_cast<const __nv_bfloat16*>(res), \
         res_c_total, res_c_offset, res_scale, res_shift, BnTrain{}));
+    if (res && res_scale) B200SEG_BN_APPLY(true, false) else B200SEG_BN_APPLY(false, false)
+#undef B200SEG_BN_APPLY
     return 0;
 }
 
@@ -609,11 +624,15 @@ int b200seg_bn_apply_train(const void* x, int x_c_total, int x_c_offset, void* y
     tr.vec = vec;
     tr.bits = mask_bits;
     const ColGeom g = col_geom(c, pixels, 16);
-    B200SEG_CUDA(launch_pdl(bn_apply_kernel, dim3(g.gx, g.gy), kRedThreads, 0, static_cast<cudaStream_t>(stream),
-        static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset,
-        c / 8, pixels, g.pixels_per_block, g.gpb, g.rows, static_cast<const float*>(nullptr),
-        static_cast<const float*>(nullptr), relu, static_cast<const __nv_bfloat16*>(res), res_c_total, res_c_offset,
+#define B200SEG_BN_APPLY(RA, BITS)     B200SEG_CUDA(launch_pdl(bn_apply_kernel<RA, BITS>, dim3(g.gx, g.gy), kRedThreads, 0, static_cast<cudaStream_t>(stream), \
+        static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset, \
+        c / 8, pixels, g.pixels_per_block, g.gpb, g.rows, static_cast<const float*>(nullptr), \
+        static_cast<const float*>(nullptr), relu, static_cast<const __nv_bfloat16*>(res), res_c_total, res_c_offset, \
         res_scale, res_shift, tr));
+    const bool ra = res && res_scale;
+    if (ra && mask_bits) B200SEG_BN_APPLY(true, true) else if (ra) B200SEG_BN_APPLY(true, false)
+    else if (mask_bits) B200SEG_BN_APPLY(false, true) else B200SEG_BN_APPLY(false, false)
+#undef B200SEG_BN_APPLY
     return 0;
 }
 
