@@ -280,7 +280,7 @@ __global__ void __launch_bounds__(kRedThreads, 4) bn_apply_kernel(
 }
 
 // red[0..c) = sum dz', red[c..2c) = sum dz' * xhat   with dz' = dy * (y > 0 if relu)
-__global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(
+__global__ void __launch_bounds__(kRedThreads, 4) bn_bwd_reduce_kernel(
     const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off, const __nv_bfloat16* __restrict__ x, int x_ct, int x_off,
     int c, int64_t pixels, int64_t ppb, int gpb, int rows, const float* __restrict__ scale, const float* __restrict__ shift,
     const float* __restrict__ mean, const float* __restrict__ invstd, int relu, float* __restrict__ red,
@@ -293,11 +293,9 @@ __global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[0][j] = acc[1][j] = 0.f;
     if (row < rows && group < groups) {
-        float sc[8], sh[8], mu[8], is[8];
+        float sc[8], sh[8];
         load8f(scale + group * 8, sc);
         load8f(shift + group * 8, sh);
-        load8f(mean + group * 8, mu);
-        load8f(invstd + group * 8, is);
         // strided sweep: all CTAs move through the tensor together (measured faster than one contiguous chunk per CTA)
         const int64_t p0 = static_cast<int64_t>(blockIdx.x) * rows;
         const int64_t p1 = pixels;
@@ -306,7 +304,7 @@ __global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(
         const __nv_bfloat16* xb = x + x_off + group * 8;
         const __nv_bfloat16* db = dy + dy_off + group * 8;
         const __nv_bfloat16* mb = mask ? mask + m_off + group * 8 : nullptr;
-#pragma unroll 4
+#pragma unroll 2
         for (int64_t p = p0 + row; p < p1; p += pstep) {
             float f[8], d[8], m[8];
             unpack8(ldg128(xb + p * x_ct), f);
@@ -325,7 +323,11 @@ __global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(
                 acc[1][j] = fmaf(dz, f[j], acc[1][j]);      // sum dz * x; centred and scaled once below
             }
         }
-        // sum dz * xhat = invstd * (sum dz*x - mean * sum dz), per thread (a few hundred terms: no cancellation issue)
+        // sum dz * xhat = invstd * (sum dz*x - mean * sum dz), per thread (a few hundred terms: no cancellation issue);
+        // mean / invstd are loaded only now: live across the sweep they cost the kernel its fourth resident CTA
+        float mu[8], is[8];
+        load8f(mean + group * 8, mu);
+        load8f(invstd + group * 8, is);
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[1][j] = is[j] * (acc[1][j] - mu[j] * acc[0][j]);
     }
@@ -335,7 +337,7 @@ __global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(
 // dx = scale * (dz' - red0/M - xhat * red1/M)   (training)   or   scale * dz'   (eval: statistics are constants)
 // rewritten per channel as dx = A * dz' + B * x + C with A = scale, B = -scale*invstd*red1/M (xhat = (x-mean)*invstd),
 // C = -scale*red0/M - B*mean (all per-channel registers).
-__global__ void __launch_bounds__(kRedThreads) bn_bwd_apply_kernel(
+__global__ void __launch_bounds__(kRedThreads, 4) bn_bwd_apply_kernel(
     const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off, const __nv_bfloat16* __restrict__ x, int x_ct, int x_off,
     __nv_bfloat16* __restrict__ dx, int dx_ct, int dx_off, int groups, int64_t pixels, int64_t ppb, int gpb, int rows,
     float inv_count, const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
@@ -371,7 +373,7 @@ __global__ void __launch_bounds__(kRedThreads) bn_bwd_apply_kernel(
     const __nv_bfloat16* db = dy + dy_off + group * 8;
     const __nv_bfloat16* mb = mask ? mask + m_off + group * 8 : nullptr;
     __nv_bfloat16* ob = dx + dx_off + group * 8;
-#pragma unroll 2
+#pragma unroll 1
     for (int64_t p = p0 + row; p < p1; p += pstep) {
         float f[8], d[8], m[8];
         unpack8(ldcs128(xb + p * x_ct), f);
@@ -751,12 +753,12 @@ static int bn_bwd_reduce_impl(bool zero_red, const void* dy, int dy_c_total, int
     if (mask && check_slice("bn_bwd_reduce(mask)", mask, mask_c_total, mask_c_offset, c)) return 1;
     B200SEG_CHECK(scale && shift && save_mean && save_invstd && red && pixels > 0, "bn_bwd_reduce: bad arguments");
     if (zero_red) B200SEG_CUDA(cudaMemsetAsync(red, 0, sizeof(float) * 2 * c, st));
-    // fewer, fatter CTAs than the streaming kernels: every CTA ends with one atomic per channel on the same 2c
-    // addresses, and those serialise in L2 (ncu: the reduce pass took longer than the apply pass that also writes)
+    // one wave of 4 resident CTAs per SM (the kernel is held to 64 registers for that: at 99 registers only two fit and
+    // the pass ran 1.59 ms per step instead of 1.28); more CTAs than that only add atomics on the same 2c addresses
     static const int ctas = [] {
         const char* e = getenv("B200SEG_BNRED_CTAS");
-        const int v = e ? atoi(e) : 2;
-        return v > 0 ? v : 2;
+        const int v = e ? atoi(e) : 4;
+        return v > 0 ? v : 4;
     }();
     const ColGeom g = col_geom(c, pixels, ctas);
     B200SEG_CUDA(launch_pdl(bn_bwd_reduce_kernel, dim3(g.gx, g.gy), kRedThreads, 0, st, 
