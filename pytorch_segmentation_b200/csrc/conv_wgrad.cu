@@ -287,8 +287,19 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restr
     const int tap = static_cast<int>(i / (static_cast<long long>(n_dim) * m_dim));
     const size_t plane = static_cast<size_t>(m_pad) * n_pad;
     const float* src = ws + (static_cast<size_t>(tap) * m_pad + m) * n_pad + n;
+    // up to 148 partials per element: eight loads in flight per thread (the adds keep their fixed order); one load
+    // per trip made the small-weight launches pure latency chains of 16-32 us
     float acc = 0.f;
-    for (int s = 0; s < splits; ++s) acc += src[static_cast<size_t>(s) * taps * plane];
+    const size_t sstride = static_cast<size_t>(taps) * plane;
+    int s = 0;
+    for (; s + 8 <= splits; s += 8) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = __ldcs(src + static_cast<size_t>(s + u) * sstride);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) acc += v[u];
+    }
+    for (; s < splits; ++s) acc += __ldcs(src + static_cast<size_t>(s) * sstride);
     const int kk = m_is_c ? n : m;
     const int cc = m_is_c ? m : n;
     float* d = dw + (static_cast<size_t>(kk) * c + cc) * taps + tap;
