@@ -137,3 +137,15 @@ def test_bucketer_early_delivery_feeds_buckets_before_autograd():
     finally:
         b.remove()
     assert E.GRAD_SINK is None
+
+
+def test_class_map_loss_predicate_covers_the_heads_and_rejects_the_rest():
+    from pytorch_segmentation_b200 import engine as E
+    ok = E.lowres_ce_supported
+    assert ok((16, 128, 128, 24), 21, 512, 512, True)            # DeepLabV3+ x4, align_corners (deeplabv3plus.py:40-43)
+    assert ok((4, 160, 160, 8), 2, 320, 320, True)               # UNet x2 (unet.py:52-55)
+    assert ok((8, 128, 256, 24), 19, 512, 1024, False)           # HRNet x4, half-pixel centres (hrnet.py:400-404)
+    assert not ok((1, 64, 64, 24), 21, 64, 64, True)             # no upsample: the logits path
+    assert not ok((1, 16, 16, 24), 21, 128, 128, True)           # x8: more than four patch windows per cell
+    assert not ok((1, 64, 64, 40), 33, 256, 256, True)           # more than 32 classes
+    assert not ok((1, 1, 64, 24), 21, 4, 256, True)              # degenerate class map
