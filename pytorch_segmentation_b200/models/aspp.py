@@ -39,6 +39,8 @@ class ASPPPooling(nn.Module):
         if training and bn.track_running_stats and bn.num_batches_tracked is not None:
             bn.num_batches_tracked.add_(1)
         E.broadcast_hw(z, out)
+        E.capture(conv.weight, 'raw', raw)
+        E.capture(conv.weight, 'out', z)
         return (g, raw, bn_save, training, x.h * x.w) if save else None
 
     def run_backward(self, rec, dout, dx, accumulate):

@@ -86,6 +86,8 @@ class ConvNormAct(nn.Sequential):
             if track and bn.num_batches_tracked is not None:
                 bn.num_batches_tracked.add_(1)
             E.bn_apply(raw, out, vec, self.relu)
+            E.capture(conv.weight, 'raw', raw)
+            E.capture(conv.weight, 'out', out)
             return (x, raw, vec, True) if save else None
         vec = E.bn_eval_affine(k, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
         if not save:

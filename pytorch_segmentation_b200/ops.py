@@ -81,6 +81,8 @@ class _ConvBNFn(torch.autograd.Function):
             if track and bn.num_batches_tracked is not None:
                 bn.num_batches_tracked.add_(1)
             E.bn_apply(raw, out, vec, relu, res=res)
+            E.capture(conv.weight, 'raw', raw)
+            E.capture(conv.weight, 'out', out)
         else:
             if not track:
                 raise RuntimeError('eval-mode BatchNorm without running statistics')

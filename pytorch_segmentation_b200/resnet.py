@@ -54,6 +54,7 @@ class _Unit:
         else:
             E.conv_fprop([(x, pw, self.dil, self.stride)], raw)
             vec = E.bn_eval_affine(self.cout, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
+        E.capture(self.conv.weight, 'raw', raw)
         return raw, vec
 
     def wgrad(self, draw, x):
@@ -89,6 +90,10 @@ class _Block:
         else:
             rawd = vd = None
             E.bn_apply(raw3, out, v3, True, res=x, want_bits=training)
+        if E.CAPTURE is not None:
+            E.capture(self.u1.conv.weight, 'out', a1)
+            E.capture(self.u2.conv.weight, 'out', a2)
+            E.capture(self.u3.conv.weight, 'out', out)
         return out, (x, raw1, v1, a1, raw2, v2, a2, raw3, v3, rawd, vd, out)
 
     def backward(self, rec, dout, training, grads, need_dx=True, dout_masked=False, mask_in=True, red_of=None):
@@ -197,6 +202,8 @@ class ResNet50Features(nn.Module):
             v0 = E.bn_eval_affine(raw0.c, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
         a0 = E.Act.empty(raw0.n, raw0.h, raw0.w, raw0.c, dev)
         E.bn_apply(raw0, a0, v0, True)
+        E.capture(conv1.weight, 'raw', raw0)
+        E.capture(conv1.weight, 'out', a0)
         p0, idx = E.maxpool_fwd(a0)
 
         stats_all = torch.zeros((total,), dtype=torch.float32, device=dev) if training else None

@@ -206,3 +206,39 @@ def test_hrnet_restatement_equals_reference_live():
     ours, theirs = mine.state_dict(), model.state_dict()
     assert list(ours.keys()) == list(theirs.keys())
     assert all(ours[k].shape == theirs[k].shape for k in ours)
+
+
+def test_mask_matched_substitution_machinery():
+    """oracle/restatement.py ``substituted`` / ``hook_backbone`` (used by tests/test_gpu_gradparity.py): recording the
+    oracle's own boundary tensors and substituting them back is the identity (same logits, same gradients, bit for
+    bit); substituting bf16-rounded values moves the logits by rounding noise only and keeps the fp32 autograd graph
+    intact (every parameter still receives a gradient)."""
+    n, nc, h, w, seed = 2, 5, 64, 64, 3
+    x, t = G.make_inputs(dict(n=n, nc=nc, h=h, w=w, seed=seed))
+
+    def run(values, record=False):
+        oracle = R.OracleModel('deeplabv3plus', nc, seed=seed).train()
+        handles = R.hook_backbone(oracle.backbone, values, prefix='backbone.', record=record)
+        with R.substituted(values, record=record):
+            y = oracle(x)
+            loss = R.compute_loss(y, t)
+        loss.backward()
+        for hd in handles:
+            hd.remove()
+        grads = {'backbone.' + k: p.grad for k, p in oracle.backbone.named_parameters()}
+        grads.update({k: v.grad for k, v in oracle.sd.items() if v.requires_grad})
+        return y.detach(), grads
+
+    vals = {}
+    y0, g0 = run(vals, record=True)
+    assert sum(k.endswith('.raw') for k in vals) == 53 + 7            # ResNet-50 convs + project, 5 ASPP branches, ASPP project
+    assert 'backbone.layer4.2.conv3.weight.out' in vals and 'backbone.conv1.weight.out' in vals
+    y1, g1 = run(vals)
+    assert torch.equal(y0, y1)
+    for k in g0:
+        assert torch.equal(g0[k], g1[k]), k
+    rounded = {k: v.to(torch.bfloat16).float() for k, v in vals.items()}
+    y2, g2 = run(rounded)
+    err = float((y2 - y0).abs().max()) / float(y0.abs().max())
+    assert 0 < err < 5e-2, err
+    assert all(g is not None and bool(torch.isfinite(g).all()) for g in g2.values())
