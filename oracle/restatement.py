@@ -76,13 +76,31 @@ def _subst(key, y):
     return y + (v.to(y.dtype).reshape(y.shape) - y).detach()
 
 
-def hook_backbone(backbone, values, prefix='backbone.', record=False):
+def hook_backbone(backbone, values, prefix='backbone.', record=False, grad_log=None):
     """Forward hooks on a torchvision ResNet (through the shim) that substitute the stored conv results
     ('<prefix><conv name>.raw') and the stored stem / bottleneck outputs ('<prefix><conv name>.out': conv1 -> the
     ReLU output that feeds the max pool; block.conv1/conv2 -> the ReLU outputs inside the block; block.conv3 -> the
-    block output).  Returns the hook handles."""
+    block output).  Returns the hook handles.
+
+    ``grad_log`` (a dict) switches on the backward re-synchronisation at block boundaries: where ``values`` holds
+    '<prefix><block>.conv3.weight.gout' — the gradient the CUDA run stored (bf16) on entry to that block's backward,
+    possibly pre-multiplied by the ReLU mask of the block output — the oracle's own gradient of the block output is
+    logged (masked the same way) under that key and REPLACED by the stored one, so bf16 gradient-storage noise does
+    not accumulate from block to block and every block's backward is checked on the gradient its CUDA counterpart
+    actually received.  The logged gradients are compared with the stored ones by the caller, which closes the chain."""
     import torch.nn as nn
     handles = []
+
+    def resync(key, out):
+        g_stored = values.get(key) if grad_log is not None else None
+        if g_stored is None or not out.requires_grad:
+            return
+        mask = (out.detach() > 0).to(out.dtype)
+
+        def on_grad(g):
+            grad_log[key] = (g.detach() * mask, g_stored.to(g.dtype) * mask)
+            return g_stored.to(g.dtype)
+        out.register_hook(on_grad)
 
     def sub(key):
         def hook(_m, _i, out):
@@ -96,22 +114,48 @@ def hook_backbone(backbone, values, prefix='backbone.', record=False):
             return out + (v.to(out.dtype) - out).detach()
         return hook
 
+    def sub_input(key):
+        def pre(_m, inp):
+            if record:
+                values[key] = inp[0].detach().clone()
+                return None
+            v = values.get(key)
+            if v is None:
+                return None
+            assert v.shape == inp[0].shape, (key, tuple(v.shape), tuple(inp[0].shape))
+            return (inp[0] + (v.to(inp[0].dtype) - inp[0]).detach(),)
+        return pre
+
     for name, m in backbone.named_modules():
         if isinstance(m, nn.Conv2d):
             handles.append(m.register_forward_hook(sub(prefix + name + '.weight.raw')))
+            # inside a Bottleneck, conv2 reads relu(bn1(conv1 x)) and conv3 reads relu(bn2(conv2 .)): the stored ReLU outputs
+            for nxt, prv in (('.conv2', '.conv1'), ('.conv3', '.conv2')):
+                if name.endswith(nxt):
+                    handles.append(m.register_forward_pre_hook(sub_input(prefix + name[:-len(nxt)] + prv + '.weight.out')))
         if hasattr(m, 'conv3') and hasattr(m, 'bn3'):          # Bottleneck: its output
-            handles.append(m.register_forward_hook(sub(prefix + name + '.conv3.weight.out')))
+            def block_hook(_m, _i, out, key=prefix + name + '.conv3.weight'):
+                new = sub(key + '.out')(_m, _i, out)
+                new = out if new is None else new
+                resync(key + '.gout', new)
+                return new
+            handles.append(m.register_forward_hook(block_hook))
     if hasattr(backbone, 'maxpool'):
-        def pre(_m, inp):
-            if record:
-                values[prefix + 'conv1.weight.out'] = inp[0].detach().clone()
-                return None
-            v = values.get(prefix + 'conv1.weight.out')
-            if v is None:
-                return None
-            return (inp[0] + (v.to(inp[0].dtype) - inp[0]).detach(),)
-        handles.append(backbone.maxpool.register_forward_pre_hook(pre))
+        handles.append(backbone.maxpool.register_forward_pre_hook(sub_input(prefix + 'conv1.weight.out')))
     return handles
+
+
+def round_conv_weights_to_bf16_(model):
+    """In place: every conv weight of an ``OracleModel`` (4-D tensors of ``sd`` and of the backbone) becomes its nearest
+    bf16-representable fp32 value.  The CUDA path multiplies bf16 packings of the fp32 master weights; with
+    representable masters the packing is exact, so a weight rounding error — one fixed perturbation applied at every
+    pixel, which per-channel sums over pixels (BatchNorm bias / scale gradients) do not average away — is not part of
+    the comparison."""
+    with torch.no_grad():
+        for v in list(model.sd.values()) + list(model.backbone.parameters()):
+            if v.dim() == 4:
+                v.copy_(v.to(torch.bfloat16).float())
+    return model
 
 
 # ----------------------------------------------------------------------------------------------

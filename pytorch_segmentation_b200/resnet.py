@@ -103,6 +103,7 @@ class _Block:
         block's BatchNorm backward never re-reads its own output for the mask."""
         x, raw1, v1, a1, raw2, v2, a2, raw3, v3, rawd, vd, out = rec
         dev = x.t.device
+        E.capture(self.u3.conv.weight, 'gout', dout)       # parity tests: the stored gradient that enters this block
 
         def unit_bwd(u, dy, raw, vec, xin, relu=True, mask=None):
             draw = E.Act.empty(raw.n, raw.h, raw.w, raw.c, dev)

