@@ -117,8 +117,26 @@ typedef struct b200seg_sgd_desc {
     float* m;
     int64_t numel;
 } b200seg_sgd_desc;
+/* hyper: NULL, or a DEVICE vector {lr, momentum, dampening, weight_decay, grad_scale} read by the kernel in place of the
+ * by-value arguments — a captured CUDA graph then follows a learning-rate schedule (the host refreshes the vector before
+ * each replay).  Whether momentum / nesterov / first_step apply is fixed by the by-value arguments. */
 int b200seg_sgd_multi(const b200seg_sgd_desc* descs, int n, float lr, float momentum, float dampening, float weight_decay,
-                      int nesterov, int first_step, float grad_scale, b200seg_stream_t st);
+                      int nesterov, int first_step, float grad_scale, const float* hyper, b200seg_stream_t st);
+
+/* Adam / AdamW for all parameters in one launch per 64 tensors (train.py:96 ``--adam``; torch.optim.Adam(W), amsgrad off):
+ *   g' = grad_scale*g (+ weight_decay*p if !decoupled);  decoupled: p *= 1 - lr*weight_decay
+ *   m += (1-beta1)*(g'-m);  v = beta2*v + (1-beta2)*g'^2;  p -= (lr/bc1) * m / (sqrt(v)/sqrt_bc2 + eps)
+ * hyper = DEVICE vector {lr, beta1, beta2, eps, weight_decay, grad_scale, bc1 = 1-beta1^t, sqrt_bc2 = sqrt(1-beta2^t)}.
+ * first_step: m and v are not read (treated as zero). */
+typedef struct b200seg_adam_desc {
+    float* p;
+    const float* g;
+    float* m;
+    float* v;
+    int64_t numel;
+} b200seg_adam_desc;
+int b200seg_adam_multi(const b200seg_adam_desc* descs, int n, const float* hyper, int decoupled, int first_step,
+                       b200seg_stream_t st);
 
 /* dst <- src for many fp32 tensors in one launch: the gradients of a bucket move into their slots of the flat
  * all-reduce buffer (parallel.GradBucketer; the DDP exchange of train.py:108-119).  desc.p = destination, desc.g =
@@ -340,11 +358,19 @@ int b200seg_resize_nchw_fwd(const float* x, int64_t planes, int h, int w, float*
                             b200seg_stream_t st);
 int b200seg_resize_nchw_bwd(const float* dy, int64_t planes, int oh, int ow, float* dx, int h, int w, int align_corners,
                             b200seg_stream_t st);
-/* nn.CrossEntropyLoss() of utils/utils.py:12,21 on NCHW fp32 logits and int64 targets: accumulates
+/* Target masks: int64 is what the reference's post_fetch_fn hands on (``segs.long()``, utils/datasets.py:213); uint8 is
+ * what BasicDataset.__getitem__ yields before that cast (utils/datasets.py:161-194) and int32 a common intermediate —
+ * every function below that takes ``targets`` reads any of the three directly (target_kind), so the 8x wider copy need
+ * never exist (33.5 MB -> 4.2 MB per 16 x 512 x 512 batch, host -> device transfer included). */
+#define B200SEG_TARGET_I64 0
+#define B200SEG_TARGET_I32 1
+#define B200SEG_TARGET_U8 2
+
+/* nn.CrossEntropyLoss() of utils/utils.py:12,21 on NCHW fp32 logits and integer targets: accumulates
  * sum_pixels -log softmax[target] into *loss_sum (fp64; caller zeroes it and divides by the pixel count) and
  * writes dlogits = (softmax - onehot) * grad_scale when dlogits != NULL.  Targets outside [0, nc) other than
  * ignore_index set *status = 1. */
-int b200seg_softmax_ce(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
+int b200seg_softmax_ce(const float* logits, const void* targets, int target_kind, int n, int nc, int64_t hw, int64_t ignore_index,
                        float grad_scale, double* loss_sum, int64_t* valid_count, float* dlogits, int* status,
                        b200seg_stream_t st);
 /* Cross-entropy straight from the head's LOW-RESOLUTION fp32 NHWC class map [n][h][w][c_total] (before the final bilinear
@@ -352,10 +378,10 @@ int b200seg_softmax_ce(const float* logits, const int64_t* targets, int n, int n
  * (same arithmetic as b200seg_logits_upsample_fwd).  _fwd accumulates like b200seg_softmax_ce; _bwd writes the gradient
  * of the class map itself (fp32, zeroed here) = upsample^T((softmax - onehot) * *grad_out / *valid_count) without the
  * full-resolution gradient ever existing in HBM.  th >= h, tw >= w, nc <= 32. */
-int b200seg_lowres_ce_fwd(const float* lr, int n, int h, int w, int c_total, int nc, const int64_t* targets, int th, int tw,
+int b200seg_lowres_ce_fwd(const float* lr, int n, int h, int w, int c_total, int nc, const void* targets, int target_kind, int th, int tw,
                           int align_corners, int64_t ignore_index, double* loss_sum, int64_t* valid_count, int* status,
                           b200seg_stream_t st);
-int b200seg_lowres_ce_bwd(const float* lr, int n, int h, int w, int c_total, int nc, const int64_t* targets, int th, int tw,
+int b200seg_lowres_ce_bwd(const float* lr, int n, int h, int w, int c_total, int nc, const void* targets, int target_kind, int th, int tw,
                           int align_corners, int64_t ignore_index, const float* grad_out, const int64_t* valid_count,
                           float* dlr, b200seg_stream_t st);
 /* out[i] = bf16(a[i] + b[i]) (b bf16, may be NULL), count % 4 == 0: the fp32 class-map gradient of
@@ -367,17 +393,39 @@ int b200seg_ce_finalize(const double* loss_sum, const int64_t* valid_count, cons
 /* Backward of the mean cross-entropy (loss.backward() of train.py:64 reaching utils/utils.py:21): recomputes the
  * softmax from the saved logits and writes dlogits = (softmax - onehot) * (*grad_out) / (*valid_count), both scalars
  * read on the device (no host sync, no separate scaling pass); ignored pixels get 0. */
-int b200seg_softmax_ce_bwd(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
+int b200seg_softmax_ce_bwd(const float* logits, const void* targets, int target_kind, int n, int nc, int64_t hw, int64_t ignore_index,
                            const float* grad_out, const int64_t* valid_count, float* dlogits, b200seg_stream_t st);
 /* outputs.max(1)[1] (test.py:31): NCHW fp32 -> int64 [n][hw], lowest index wins ties. */
 int b200seg_argmax(const float* logits, int n, int nc, int64_t hw, int64_t* pred, b200seg_stream_t st);
 /* cm[t*nc + p] += 1 over all pixels — superset of the tp/fn/fp loop at test.py:34-46 (tp = diag,
  * fn = row sum - diag, fp = column sum - diag).  Labels outside [0, nc) are skipped. */
-int b200seg_confusion(const int64_t* pred, const int64_t* targets, int64_t count, int nc, int64_t* cm,
+int b200seg_confusion(const int64_t* pred, const void* targets, int target_kind, int64_t count, int nc, int64_t* cm,
                       b200seg_stream_t st);
 /* argmax + confusion in one pass over the logits (never materialises the prediction). */
-int b200seg_argmax_confusion(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t* cm,
+int b200seg_argmax_confusion(const float* logits, const void* targets, int target_kind, int n, int nc, int64_t hw, int64_t* cm,
                              b200seg_stream_t st);
+/* Evaluation from the head's LOW-RESOLUTION class map (test.py:28-46 applied to models/deeplabv3plus.py:40-43's output):
+ * prediction = argmax_c bilinear(lr)[c] at every one of the th x tw target pixels, cm[t*nc + p] += 1 — without reading
+ * (or needing) the full-resolution logits.  The interpolation is the instruction sequence b200seg_logits_upsample_fwd
+ * stores, so the result is bit-identical to b200seg_argmax_confusion over those logits.  Ties: lowest class index (the
+ * first maximum, like outputs.max(1)[1]); the first NaN beats everything.  pred (int64 [n][th][tw]) and cm/targets
+ * are each optional (one of them must be given). */
+int b200seg_class_map_confusion(const float* lr, int n, int h, int w, int c_total, int nc, const void* targets,
+                                int target_kind, int th, int tw, int align_corners, int64_t* cm, int64_t* pred,
+                                b200seg_stream_t st);
+
+/* ---- input side: the reference's post_fetch_fn (utils/datasets.py:199-213) on the device --------------
+ * imgs.float(); imgs -= mean; imgs /= std  with uint8 images as BasicDataset yields them (utils/datasets.py:161-194).
+ * layout: 0 = NCHW uint8 (the reference's batches), 1 = NHWC uint8 (what cv2 decodes to).  mean / std: c host floats.
+ * Arithmetic is (float(x) - mean) / std with IEEE subtraction and division: bit-identical to the reference's fp32 ops. */
+/* -> fp32 NCHW, exactly the tensor post_fetch_fn returns (any model / backbone) */
+int b200seg_input_u8_normalize(const uint8_t* x, int layout, int n, int c, int h, int w, const float* mean, const float* std,
+                               float* y, b200seg_stream_t st);
+/* -> the bf16 space-to-depth operand of a stride-2 r x s stem conv (see b200seg_space_to_depth_nchw): normalisation,
+ * fp32 -> bf16 rounding, NCHW -> NHWC and the 2x2 space-to-depth in ONE pass over the 1-byte pixels (12.6 MB in, 34 MB
+ * out for 16 x 3 x 512 x 512 instead of an 50 MB fp32 intermediate written and read back).  Padding lanes hold 0. */
+int b200seg_input_u8_s2d(const uint8_t* x, int layout, int n, int c, int h, int w, int r, int s, int pad, const float* mean,
+                         const float* std, void* z, int cs, b200seg_stream_t st);
 
 #ifdef __cplusplus
 }

@@ -49,6 +49,11 @@ class SgdDesc(Structure):
     _fields_ = [('p', c_void_p), ('g', c_void_p), ('m', c_void_p), ('numel', c_int64)]
 
 
+class AdamDesc(Structure):
+    """struct b200seg_adam_desc"""
+    _fields_ = [('p', c_void_p), ('g', c_void_p), ('m', c_void_p), ('v', c_void_p), ('numel', c_int64)]
+
+
 _P = c_void_p
 _I = c_int
 _L = c_int64
@@ -74,7 +79,8 @@ PROTOTYPES = {
     'b200seg_pack_weights_taps': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _P, _I, _P]),
     'b200seg_unpack_wgrad_taps': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _P]),
     'b200seg_pack_weights_multi': (c_int, [POINTER(PackDesc), _I, _P]),
-    'b200seg_sgd_multi': (c_int, [POINTER(SgdDesc), _I, _F, _F, _F, _F, _I, _I, _F, _P]),
+    'b200seg_sgd_multi': (c_int, [POINTER(SgdDesc), _I, _F, _F, _F, _F, _I, _I, _F, _P, _P]),
+    'b200seg_adam_multi': (c_int, [POINTER(AdamDesc), _I, _P, _I, _I, _P]),
     'b200seg_copy_multi': (c_int, [POINTER(SgdDesc), _I, _P]),
     'b200seg_conv_fprop': (c_int, [_I, _I, _I, _I, POINTER(ConvSrc), POINTER(ConvOut), _P]),
     'b200seg_conv_dgrad': (c_int, [_I, _I, _I, _I, POINTER(ConvSrc), POINTER(ConvOut), _P]),
@@ -115,15 +121,18 @@ PROTOTYPES = {
     'b200seg_logits_upsample_bwd': (c_int, [_P, _I, _I, _I, _I, _P, _I, _I, _I, _I, _P]),
     'b200seg_resize_nchw_fwd': (c_int, [_P, _L, _I, _I, _P, _I, _I, _I, _P]),
     'b200seg_resize_nchw_bwd': (c_int, [_P, _L, _I, _I, _P, _I, _I, _I, _P]),
-    'b200seg_softmax_ce': (c_int, [_P, _P, _I, _I, _L, _L, _F, _P, _P, _P, _P, _P]),
-    'b200seg_lowres_ce_fwd': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _L, _P, _P, _P, _P]),
-    'b200seg_lowres_ce_bwd': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _L, _P, _P, _P, _P]),
+    'b200seg_softmax_ce': (c_int, [_P, _P, _I, _I, _I, _L, _L, _F, _P, _P, _P, _P, _P]),
+    'b200seg_lowres_ce_fwd': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _L, _P, _P, _P, _P]),
+    'b200seg_lowres_ce_bwd': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _L, _P, _P, _P, _P]),
     'b200seg_cast_add_bf16': (c_int, [_P, _P, _P, _L, _P]),
     'b200seg_ce_finalize': (c_int, [_P, _P, _P, _P, _P]),
-    'b200seg_softmax_ce_bwd': (c_int, [_P, _P, _I, _I, _L, _L, _P, _P, _P, _P]),
+    'b200seg_softmax_ce_bwd': (c_int, [_P, _P, _I, _I, _I, _L, _L, _P, _P, _P, _P]),
     'b200seg_argmax': (c_int, [_P, _I, _I, _L, _P, _P]),
-    'b200seg_confusion': (c_int, [_P, _P, _L, _I, _P, _P]),
-    'b200seg_argmax_confusion': (c_int, [_P, _P, _I, _I, _L, _P, _P]),
+    'b200seg_confusion': (c_int, [_P, _P, _I, _L, _I, _P, _P]),
+    'b200seg_argmax_confusion': (c_int, [_P, _P, _I, _I, _I, _L, _P, _P]),
+    'b200seg_class_map_confusion': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _P, _P, _P]),
+    'b200seg_input_u8_normalize': (c_int, [_P, _I, _I, _I, _I, _I, POINTER(c_float), POINTER(c_float), _P, _P]),
+    'b200seg_input_u8_s2d': (c_int, [_P, _I, _I, _I, _I, _I, _I, _I, _I, POINTER(c_float), POINTER(c_float), _P, _I, _P]),
 }
 
 _lib = None

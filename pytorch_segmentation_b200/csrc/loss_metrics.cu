@@ -9,6 +9,25 @@
 namespace b200seg {
 namespace {
 
+// Targets at the boundary are int64 (what the reference's post_fetch_fn hands on: ``segs.long()``, utils/datasets.py:213)
+// or the uint8 / int32 masks the dataset holds before that cast (utils/datasets.py:161-194) — B200SEG_TARGET_*: reading the
+// narrow type directly saves the 8x wider copy (33.5 MB -> 4.2 MB per 16 x 512 x 512 batch, host -> device included).
+__device__ __forceinline__ int64_t load_target(const void* t, int kind, int64_t i) {
+    if (kind == B200SEG_TARGET_I64) return __ldcs(static_cast<const long long*>(t) + i);
+    if (kind == B200SEG_TARGET_I32) return __ldcs(static_cast<const int*>(t) + i);
+    return __ldcs(static_cast<const unsigned char*>(t) + i);
+}
+
+// One bilinear tap set, the same instruction sequence wherever full-resolution logits are formed from the class map
+// (logits_up_fwd_kernel writes them, class_map_confusion_kernel takes their argmax without writing them): explicit
+// round-to-nearest intrinsics, so the compiler cannot contract the two sites differently and the fused eval path is
+// bit-identical to argmax over the written logits.
+__device__ __forceinline__ float lerp2d(float wy0, float wy1, float wx0, float wx1, float a, float b, float c, float d) {
+    const float top = __fmaf_rn(wx1, b, __fmul_rn(wx0, a));
+    const float bot = __fmaf_rn(wx1, d, __fmul_rn(wx0, c));
+    return __fmaf_rn(wy1, bot, __fmul_rn(wy0, top));
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // final bilinear of the class map: NHWC fp32 [n][h][w][ct] -> NCHW fp32 [n][nc][oh][ow]
 __global__ void __launch_bounds__(256) logits_up_fwd_kernel(const float* __restrict__ x, int ct, int h, int w, int nc,
@@ -31,10 +50,10 @@ __global__ void __launch_bounds__(256) logits_up_fwd_kernel(const float* __restr
         const int64_t plane = static_cast<int64_t>(oh) * ow;
         for (int c4 = 0; c4 * 4 < nc; ++c4) {
             const float4 a = __ldg(p00 + c4), bb = __ldg(p01 + c4), cc = __ldg(p10 + c4), d = __ldg(p11 + c4);
-            const float v[4] = {ly.w0 * (lx.w0 * a.x + lx.w1 * bb.x) + ly.w1 * (lx.w0 * cc.x + lx.w1 * d.x),
-                                ly.w0 * (lx.w0 * a.y + lx.w1 * bb.y) + ly.w1 * (lx.w0 * cc.y + lx.w1 * d.y),
-                                ly.w0 * (lx.w0 * a.z + lx.w1 * bb.z) + ly.w1 * (lx.w0 * cc.z + lx.w1 * d.z),
-                                ly.w0 * (lx.w0 * a.w + lx.w1 * bb.w) + ly.w1 * (lx.w0 * cc.w + lx.w1 * d.w)};
+            const float v[4] = {lerp2d(ly.w0, ly.w1, lx.w0, lx.w1, a.x, bb.x, cc.x, d.x),
+                                lerp2d(ly.w0, ly.w1, lx.w0, lx.w1, a.y, bb.y, cc.y, d.y),
+                                lerp2d(ly.w0, ly.w1, lx.w0, lx.w1, a.z, bb.z, cc.z, d.z),
+                                lerp2d(ly.w0, ly.w1, lx.w0, lx.w1, a.w, bb.w, cc.w, d.w)};
 #pragma unroll
             for (int j = 0; j < 4; ++j)
                 if (c4 * 4 + j < nc) __stcs(out + (c4 * 4 + j) * plane, v[j]);
@@ -198,7 +217,7 @@ __global__ void __launch_bounds__(256) resize_nchw_bwd_kernel(const float* __res
 // ------------------------------------------------------------------------------------------------------------
 // softmax cross-entropy, one thread per pixel, class vector in registers
 template <int NCMAX>
-__global__ void __launch_bounds__(256) softmax_ce_kernel(const float* __restrict__ logits, const int64_t* __restrict__ tgt,
+__global__ void __launch_bounds__(256) softmax_ce_kernel(const float* __restrict__ logits, const void* __restrict__ tgt, int tk,
                                                           int nc, int64_t hw, int64_t total, int64_t ignore_index,
                                                           float grad_scale, double* loss_sum,
                                                           unsigned long long* valid_count, float* __restrict__ dlogits,
@@ -213,7 +232,7 @@ __global__ void __launch_bounds__(256) softmax_ce_kernel(const float* __restrict
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int64_t n = i / hw, p = i - n * hw;
         const float* q = logits + n * nc * hw + p;
-        const int64_t t = __ldcs(tgt + i);
+        const int64_t t = load_target(tgt, tk, i);
         float v[NCMAX];
         float m = -INFINITY;
 #pragma unroll
@@ -269,7 +288,7 @@ __global__ void __launch_bounds__(256) softmax_ce_kernel(const float* __restrict
 
 // any class count: three passes over the class dimension (max, sum, gradient)
 __global__ void __launch_bounds__(256) softmax_ce_generic_kernel(const float* __restrict__ logits,
-                                                                  const int64_t* __restrict__ tgt, int nc, int64_t hw,
+                                                                  const void* __restrict__ tgt, int tk, int nc, int64_t hw,
                                                                   int64_t total, int64_t ignore_index, float grad_scale,
                                                                   double* loss_sum, unsigned long long* valid_count,
                                                                   float* __restrict__ dlogits, int* status,
@@ -283,7 +302,7 @@ __global__ void __launch_bounds__(256) softmax_ce_generic_kernel(const float* __
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const int64_t n = i / hw, p = i - n * hw;
         const float* q = logits + n * nc * hw + p;
-        const int64_t t = tgt[i];
+        const int64_t t = load_target(tgt, tk, i);
         float m = -INFINITY;
         for (int c = 0; c < nc; ++c) m = fmaxf(m, q[c * hw]);
         float s = 0.f;
@@ -344,7 +363,7 @@ constexpr int kHistWarps = kHistThreads / 32;
 template <bool FUSED_ARGMAX>
 __global__ void __launch_bounds__(kHistThreads) confusion_kernel(const float* __restrict__ logits,
                                                                   const int64_t* __restrict__ pred,
-                                                                  const int64_t* __restrict__ tgt, int nc, int64_t hw,
+                                                                  const void* __restrict__ tgt, int tk, int nc, int64_t hw,
                                                                   int64_t total, int copies,
                                                                   unsigned long long* __restrict__ cm) {
     pdl_prologue();
@@ -355,7 +374,7 @@ __global__ void __launch_bounds__(kHistThreads) confusion_kernel(const float* __
     unsigned int* mine = hist + ((threadIdx.x >> 5) % copies) * bins;
     for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const int64_t t = __ldcs(tgt + i);
+        const int64_t t = load_target(tgt, tk, i);
         int64_t pr;
         if (FUSED_ARGMAX) {
             const int64_t n = i / hw, p = i - n * hw;
@@ -390,6 +409,70 @@ int hist_launch_geometry(int nc, int64_t total, int* copies, size_t* smem, int* 
     if (blocks < 1) blocks = 1;
     *grid = static_cast<int>(blocks);
     return 0;
+}
+
+
+// Evaluation straight from the LOW-RESOLUTION class map (test.py:28-46 on the output of models/deeplabv3plus.py:40-43):
+// prediction = argmax over classes of the bilinear upsample, confusion histogram against the targets — the
+// full-resolution logits (352 MB for 16 x 21 x 512 x 512) are neither read nor needed: 11 MB class map + targets in.
+// One thread per target pixel: its four source cells' class vectors come from L1/L2 (every cell serves ~16 pixels),
+// the interpolation is lerp2d — the very instruction sequence logits_up_fwd_kernel stores — so the prediction is
+// BIT-IDENTICAL to argmax over the written logits.  Tie rule (= argmax_planes = ``outputs.max(1)[1]``'s first
+// maximum): strict '>' in ascending class order, lowest index wins; the first NaN wins over everything.
+__global__ void __launch_bounds__(kHistThreads) class_map_confusion_kernel(const float* __restrict__ x, int ct, int h, int w,
+                                                                            int nc, const void* __restrict__ tgt, int tk,
+                                                                            int oh, int ow, int64_t total, float sh, float sw,
+                                                                            int ac, int copies,
+                                                                            unsigned long long* __restrict__ cm,
+                                                                            int64_t* __restrict__ pred_out) {
+    pdl_prologue();
+    extern __shared__ unsigned int hist[];
+    const int bins = nc * nc;
+    for (int b = threadIdx.x; b < bins * copies; b += blockDim.x) hist[b] = 0;
+    __syncthreads();
+    unsigned int* mine = hist + ((threadIdx.x >> 5) % copies) * bins;
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int ox = static_cast<int>(i % ow);
+        const int64_t p = i / ow;
+        const int oy = static_cast<int>(p % oh);
+        const int n = static_cast<int>(p / oh);
+        const Lerp ly = bilinear_src(sh, oy, h, ac), lx = bilinear_src(sw, ox, w, ac);
+        const float* b = x + static_cast<int64_t>(n) * h * w * ct;
+        const float4* p00 = reinterpret_cast<const float4*>(b + (static_cast<int64_t>(ly.i0) * w + lx.i0) * ct);
+        const float4* p01 = reinterpret_cast<const float4*>(b + (static_cast<int64_t>(ly.i0) * w + lx.i1) * ct);
+        const float4* p10 = reinterpret_cast<const float4*>(b + (static_cast<int64_t>(ly.i1) * w + lx.i0) * ct);
+        const float4* p11 = reinterpret_cast<const float4*>(b + (static_cast<int64_t>(ly.i1) * w + lx.i1) * ct);
+        float best = -INFINITY;
+        int bi = 0;
+        for (int c4 = 0; c4 * 4 < nc; ++c4) {
+            const float4 a = __ldg(p00 + c4), bb = __ldg(p01 + c4), cc = __ldg(p10 + c4), d = __ldg(p11 + c4);
+            const float v[4] = {lerp2d(ly.w0, ly.w1, lx.w0, lx.w1, a.x, bb.x, cc.x, d.x),
+                                lerp2d(ly.w0, ly.w1, lx.w0, lx.w1, a.y, bb.y, cc.y, d.y),
+                                lerp2d(ly.w0, ly.w1, lx.w0, lx.w1, a.z, bb.z, cc.z, d.z),
+                                lerp2d(ly.w0, ly.w1, lx.w0, lx.w1, a.w, bb.w, cc.w, d.w)};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int c = c4 * 4 + j;
+                if (c < nc && (v[j] > best || (v[j] != v[j] && best == best))) {
+                    best = v[j];
+                    bi = c;
+                }
+            }
+        }
+        if (pred_out) pred_out[i] = bi;
+        if (tgt) {
+            const int64_t t = load_target(tgt, tk, i);
+            if (t >= 0 && t < nc) atomicAdd(mine + static_cast<int>(t) * nc + bi, 1u);
+        }
+    }
+    __syncthreads();
+    if (cm)
+        for (int b = threadIdx.x; b < bins; b += blockDim.x) {
+            unsigned long long sacc = 0;
+            for (int k = 0; k < copies; ++k) sacc += hist[k * bins + b];
+            if (sacc) atomicAdd(cm + b, sacc);
+        }
 }
 
 }  // namespace
@@ -498,7 +581,7 @@ template <> struct CmExchange<4> { static constexpr int K = 3, KS = 9; };
 
 template <int NCELL, bool BWD>
 __global__ void __launch_bounds__(256, 2) class_map_ce_kernel(const float* __restrict__ lr, int ct, int h, int w, int nc,
-                                                              const int64_t* __restrict__ tgt, int H, int W, float sh,
+                                                              const void* __restrict__ tgt, int tk, int H, int W, float sh,
                                                               float sw, int ac, int64_t ignore_index, double* loss_sum,
                                                               unsigned long long* valid_count, int* status,
                                                               float* __restrict__ dlr, const float* __restrict__ g_dev,
@@ -571,7 +654,7 @@ __global__ void __launch_bounds__(256, 2) class_map_ce_kernel(const float* __res
             const int ox = tx0 + pxi * P + j;
             unsigned int code = 255u;
             if (oy < H && ox < W) {
-                const int64_t t = __ldcs(tgt + (static_cast<int64_t>(n) * H + oy) * W + ox);
+                const int64_t t = load_target(tgt, tk, (static_cast<int64_t>(n) * H + oy) * W + ox);
                 if (t != ignore_index) {
                     if (t < 0 || t >= nc) bad = true;
                     else code = static_cast<unsigned int>(t);
@@ -784,7 +867,7 @@ __global__ void cast_add_bf16_kernel(const float4* __restrict__ a, const uint2* 
     }
 }
 
-int launch_lowres_ce(const float* lr, int n, int h, int w, int ct, int nc, const int64_t* targets, int H, int W,
+int launch_lowres_ce(const float* lr, int n, int h, int w, int ct, int nc, const void* targets, int tk, int H, int W,
                      int align_corners, int64_t ignore_index, double* loss_sum, int64_t* valid_count, int* status, float* dlr,
                      const float* g_dev, const int64_t* count_dev, cudaStream_t st) {
     const float sh = bilinear_scale(h, H, align_corners), sw = bilinear_scale(w, W, align_corners);
@@ -819,7 +902,7 @@ int launch_lowres_ce(const float* lr, int n, int h, int w, int ct, int nc, const
                                               110 * 1024));                                                                \
             attr_set = true;                                                                                               \
         }                                                                                                                  \
-        B200SEG_CUDA(launch_pdl(class_map_ce_kernel<NCELL, B>, grid, 256, smem, st, lr, ct, h, w, nc, targets, H, W, sh,   \
+        B200SEG_CUDA(launch_pdl(class_map_ce_kernel<NCELL, B>, grid, 256, smem, st, lr, ct, h, w, nc, targets, tk, H, W, sh,\
                                 sw, align_corners, ignore_index, loss_sum, vc, status, dlr, g_dev, cd, FH, FW, nbuf));     \
     } while (0)
     if (dlr) {
@@ -843,7 +926,7 @@ __global__ void ce_finalize_kernel(const double* __restrict__ loss_sum, const un
     }
 }
 
-int launch_softmax_ce(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
+int launch_softmax_ce(const float* logits, const void* targets, int tk, int n, int nc, int64_t hw, int64_t ignore_index,
                       float grad_scale, double* loss_sum, int64_t* valid_count, float* dlogits, int* status,
                       const float* g_dev, const int64_t* count_dev, cudaStream_t st) {
     const int64_t total = static_cast<int64_t>(n) * hw;
@@ -851,16 +934,16 @@ int launch_softmax_ce(const float* logits, const int64_t* targets, int n, int nc
     unsigned long long* vc = reinterpret_cast<unsigned long long*>(valid_count);
     const unsigned long long* cd = reinterpret_cast<const unsigned long long*>(count_dev);
     if (nc <= 8)
-        B200SEG_CUDA(launch_pdl(softmax_ce_kernel<8>, grid, 256, 0, st, logits, targets, nc, hw, total, ignore_index, grad_scale,
+        B200SEG_CUDA(launch_pdl(softmax_ce_kernel<8>, grid, 256, 0, st, logits, targets, tk, nc, hw, total, ignore_index, grad_scale,
                                 loss_sum, vc, dlogits, status, g_dev, cd));
     else if (nc <= 24)
-        B200SEG_CUDA(launch_pdl(softmax_ce_kernel<24>, grid, 256, 0, st, logits, targets, nc, hw, total, ignore_index, grad_scale,
+        B200SEG_CUDA(launch_pdl(softmax_ce_kernel<24>, grid, 256, 0, st, logits, targets, tk, nc, hw, total, ignore_index, grad_scale,
                                 loss_sum, vc, dlogits, status, g_dev, cd));
     else if (nc <= 32)
-        B200SEG_CUDA(launch_pdl(softmax_ce_kernel<32>, grid, 256, 0, st, logits, targets, nc, hw, total, ignore_index, grad_scale,
+        B200SEG_CUDA(launch_pdl(softmax_ce_kernel<32>, grid, 256, 0, st, logits, targets, tk, nc, hw, total, ignore_index, grad_scale,
                                 loss_sum, vc, dlogits, status, g_dev, cd));
     else
-        B200SEG_CUDA(launch_pdl(softmax_ce_generic_kernel, grid, 256, 0, st, logits, targets, nc, hw, total, ignore_index,
+        B200SEG_CUDA(launch_pdl(softmax_ce_generic_kernel, grid, 256, 0, st, logits, targets, tk, nc, hw, total, ignore_index,
                                 grad_scale, loss_sum, vc, dlogits, status, g_dev, cd));
     return 0;
 }
@@ -869,18 +952,23 @@ int launch_softmax_ce(const float* logits, const int64_t* targets, int n, int nc
 
 extern "C" {
 
-int b200seg_softmax_ce(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
-                       float grad_scale, double* loss_sum, int64_t* valid_count, float* dlogits, int* status,
-                       b200seg_stream_t stream) {
+#define B200SEG_CHECK_TK(what)                                                                                       \
+    B200SEG_CHECK(target_kind == B200SEG_TARGET_I64 || target_kind == B200SEG_TARGET_I32 || target_kind == B200SEG_TARGET_U8, \
+                  what ": target_kind %d", target_kind)
+
+int b200seg_softmax_ce(const float* logits, const void* targets, int target_kind, int n, int nc, int64_t hw,
+                       int64_t ignore_index, float grad_scale, double* loss_sum, int64_t* valid_count, float* dlogits,
+                       int* status, b200seg_stream_t stream) {
     using namespace b200seg;
     clear_error();
     B200SEG_CHECK(logits && targets && loss_sum && status && n > 0 && nc > 0 && hw > 0, "softmax_ce: bad arguments");
-    return launch_softmax_ce(logits, targets, n, nc, hw, ignore_index, grad_scale, loss_sum, valid_count, dlogits, status,
+    B200SEG_CHECK_TK("softmax_ce");
+    return launch_softmax_ce(logits, targets, target_kind, n, nc, hw, ignore_index, grad_scale, loss_sum, valid_count, dlogits, status,
                              nullptr, nullptr, static_cast<cudaStream_t>(stream));
 }
 
-int b200seg_lowres_ce_fwd(const float* lr, int n, int h, int w, int c_total, int nc, const int64_t* targets, int th, int tw,
-                          int align_corners, int64_t ignore_index, double* loss_sum, int64_t* valid_count, int* status,
+int b200seg_lowres_ce_fwd(const float* lr, int n, int h, int w, int c_total, int nc, const void* targets, int target_kind,
+                          int th, int tw, int align_corners, int64_t ignore_index, double* loss_sum, int64_t* valid_count, int* status,
                           b200seg_stream_t stream) {
     using namespace b200seg;
     clear_error();
@@ -888,12 +976,13 @@ int b200seg_lowres_ce_fwd(const float* lr, int n, int h, int w, int c_total, int
     B200SEG_CHECK(n > 0 && h > 0 && w > 0 && th >= h && tw >= w && nc > 0 && nc <= c_total && nc <= 32 && c_total % 4 == 0,
                   "lowres_ce_fwd: bad geometry (class map %dx%d, targets %dx%d, nc %d of %d)", h, w, th, tw, nc, c_total);
     B200SEG_CHECK((reinterpret_cast<uintptr_t>(lr) & 15) == 0, "lowres_ce_fwd: class map not 16-byte aligned");
-    return launch_lowres_ce(lr, n, h, w, c_total, nc, targets, th, tw, align_corners, ignore_index, loss_sum, valid_count,
+    B200SEG_CHECK_TK("lowres_ce_fwd");
+    return launch_lowres_ce(lr, n, h, w, c_total, nc, targets, target_kind, th, tw, align_corners, ignore_index, loss_sum, valid_count,
                             status, nullptr, nullptr, nullptr, static_cast<cudaStream_t>(stream));
 }
 
-int b200seg_lowres_ce_bwd(const float* lr, int n, int h, int w, int c_total, int nc, const int64_t* targets, int th, int tw,
-                          int align_corners, int64_t ignore_index, const float* grad_out, const int64_t* valid_count,
+int b200seg_lowres_ce_bwd(const float* lr, int n, int h, int w, int c_total, int nc, const void* targets, int target_kind,
+                          int th, int tw, int align_corners, int64_t ignore_index, const float* grad_out, const int64_t* valid_count,
                           float* dlr, b200seg_stream_t stream) {
     using namespace b200seg;
     clear_error();
@@ -902,9 +991,10 @@ int b200seg_lowres_ce_bwd(const float* lr, int n, int h, int w, int c_total, int
                   "lowres_ce_bwd: bad geometry (class map %dx%d, targets %dx%d, nc %d of %d)", h, w, th, tw, nc, c_total);
     B200SEG_CHECK(((reinterpret_cast<uintptr_t>(lr) | reinterpret_cast<uintptr_t>(dlr)) & 15) == 0,
                   "lowres_ce_bwd: pointers not 16-byte aligned");
+    B200SEG_CHECK_TK("lowres_ce_bwd");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     B200SEG_CUDA(cudaMemsetAsync(dlr, 0, sizeof(float) * static_cast<size_t>(n) * h * w * c_total, st));
-    return launch_lowres_ce(lr, n, h, w, c_total, nc, targets, th, tw, align_corners, ignore_index, nullptr, nullptr, nullptr,
+    return launch_lowres_ce(lr, n, h, w, c_total, nc, targets, target_kind, th, tw, align_corners, ignore_index, nullptr, nullptr, nullptr,
                             dlr, grad_out, valid_count, st);
 }
 
@@ -932,13 +1022,14 @@ int b200seg_ce_finalize(const double* loss_sum, const int64_t* valid_count, cons
     return 0;
 }
 
-int b200seg_softmax_ce_bwd(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t ignore_index,
-                           const float* grad_out, const int64_t* valid_count, float* dlogits, b200seg_stream_t stream) {
+int b200seg_softmax_ce_bwd(const float* logits, const void* targets, int target_kind, int n, int nc, int64_t hw,
+                           int64_t ignore_index, const float* grad_out, const int64_t* valid_count, float* dlogits, b200seg_stream_t stream) {
     using namespace b200seg;
     clear_error();
     B200SEG_CHECK(logits && targets && grad_out && valid_count && dlogits && n > 0 && nc > 0 && hw > 0,
                   "softmax_ce_bwd: bad arguments");
-    return launch_softmax_ce(logits, targets, n, nc, hw, ignore_index, 1.0f, nullptr, nullptr, dlogits, nullptr, grad_out,
+    B200SEG_CHECK_TK("softmax_ce_bwd");
+    return launch_softmax_ce(logits, targets, target_kind, n, nc, hw, ignore_index, 1.0f, nullptr, nullptr, dlogits, nullptr, grad_out,
                              valid_count, static_cast<cudaStream_t>(stream));
 }
 
@@ -951,31 +1042,54 @@ int b200seg_argmax(const float* logits, int n, int nc, int64_t hw, int64_t* pred
     return 0;
 }
 
-int b200seg_confusion(const int64_t* pred, const int64_t* targets, int64_t count, int nc, int64_t* cm,
+int b200seg_confusion(const int64_t* pred, const void* targets, int target_kind, int64_t count, int nc, int64_t* cm,
                       b200seg_stream_t stream) {
     using namespace b200seg;
     clear_error();
     B200SEG_CHECK(pred && targets && cm && count >= 0, "confusion: bad arguments");
+    B200SEG_CHECK_TK("confusion");
     if (count == 0) return 0;
     int copies, grid;
     size_t smem;
     if (hist_launch_geometry(nc, count, &copies, &smem, &grid)) return 1;
     B200SEG_CUDA(launch_pdl(confusion_kernel<false>, grid, kHistThreads, smem, static_cast<cudaStream_t>(stream), 
-        nullptr, pred, targets, nc, 1, count, copies, reinterpret_cast<unsigned long long*>(cm)));
+        nullptr, pred, targets, target_kind, nc, 1, count, copies, reinterpret_cast<unsigned long long*>(cm)));
     return 0;
 }
 
-int b200seg_argmax_confusion(const float* logits, const int64_t* targets, int n, int nc, int64_t hw, int64_t* cm,
-                             b200seg_stream_t stream) {
+int b200seg_argmax_confusion(const float* logits, const void* targets, int target_kind, int n, int nc, int64_t hw,
+                             int64_t* cm, b200seg_stream_t stream) {
     using namespace b200seg;
     clear_error();
     B200SEG_CHECK(logits && targets && cm && n > 0 && hw > 0, "argmax_confusion: bad arguments");
+    B200SEG_CHECK_TK("argmax_confusion");
     int copies, grid;
     size_t smem;
     const int64_t total = static_cast<int64_t>(n) * hw;
     if (hist_launch_geometry(nc, total, &copies, &smem, &grid)) return 1;
     B200SEG_CUDA(launch_pdl(confusion_kernel<true>, grid, kHistThreads, smem, static_cast<cudaStream_t>(stream), 
-        logits, nullptr, targets, nc, hw, total, copies, reinterpret_cast<unsigned long long*>(cm)));
+        logits, nullptr, targets, target_kind, nc, hw, total, copies, reinterpret_cast<unsigned long long*>(cm)));
+    return 0;
+}
+
+int b200seg_class_map_confusion(const float* lr, int n, int h, int w, int c_total, int nc, const void* targets,
+                                int target_kind, int th, int tw, int align_corners, int64_t* cm, int64_t* pred,
+                                b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(lr && (pred || (targets && cm)), "class_map_confusion: null pointer");
+    B200SEG_CHECK(n > 0 && h > 0 && w > 0 && th > 0 && tw > 0 && nc > 0 && nc <= c_total && c_total % 4 == 0,
+                  "class_map_confusion: bad geometry (class map %dx%d, targets %dx%d, nc %d of %d)", h, w, th, tw, nc, c_total);
+    B200SEG_CHECK((reinterpret_cast<uintptr_t>(lr) & 15) == 0, "class_map_confusion: class map not 16-byte aligned");
+    if (targets) B200SEG_CHECK_TK("class_map_confusion");
+    int copies, grid;
+    size_t smem;
+    const int64_t total = static_cast<int64_t>(n) * th * tw;
+    if (hist_launch_geometry(nc, total, &copies, &smem, &grid)) return 1;
+    const float sh = bilinear_scale(h, th, align_corners), sw = bilinear_scale(w, tw, align_corners);
+    B200SEG_CUDA(launch_pdl(class_map_confusion_kernel, grid, kHistThreads, smem, static_cast<cudaStream_t>(stream), lr,
+                            c_total, h, w, nc, cm ? targets : nullptr, target_kind, th, tw, total, sh, sw, align_corners,
+                            copies, reinterpret_cast<unsigned long long*>(cm), pred));
     return 0;
 }
 

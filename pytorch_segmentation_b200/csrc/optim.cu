@@ -26,17 +26,23 @@ struct SgdChunk {
     int n;
     float lr, momentum, dampening, weight_decay, grad_scale;
     int nesterov, first;
+    const float* hyper;      // optional device vector {lr, momentum, dampening, weight_decay, grad_scale}: read at run
+                             // time, so a CUDA-graph replay sees the values of the moment (LR schedules)
 };
 
-__device__ __forceinline__ float sgd_one(float p, float g, float* m, const SgdChunk& c) {
-    g = fmaf(c.weight_decay, p, c.grad_scale * g);
+struct SgdHyper {
+    float lr, momentum, dampening, weight_decay, grad_scale;
+};
+
+__device__ __forceinline__ float sgd_one(float p, float g, float* m, const SgdHyper& h, bool use_m, bool first, bool nesterov) {
+    g = fmaf(h.weight_decay, p, h.grad_scale * g);
     float step = g;
-    if (c.momentum != 0.f) {
-        const float mm = c.first ? g : fmaf(c.momentum, *m, (1.f - c.dampening) * g);
+    if (use_m) {
+        const float mm = first ? g : fmaf(h.momentum, *m, (1.f - h.dampening) * g);
         *m = mm;
-        step = c.nesterov ? fmaf(c.momentum, mm, g) : mm;
+        step = nesterov ? fmaf(h.momentum, mm, g) : mm;
     }
-    return fmaf(-c.lr, step, p);
+    return fmaf(-h.lr, step, p);
 }
 
 __global__ void __launch_bounds__(256) sgd_multi_kernel(const __grid_constant__ SgdChunk c) {
@@ -53,7 +59,17 @@ __global__ void __launch_bounds__(256) sgd_multi_kernel(const __grid_constant__ 
     float* p = t.p;
     const float* g = t.g;
     float* m = t.m;
+    // whether a momentum buffer exists is structural (fixed at launch / capture); the VALUES may come from the device
     const bool use_m = c.momentum != 0.f;
+    const bool first = c.first != 0, nesterov = c.nesterov != 0;
+    SgdHyper h = {c.lr, c.momentum, c.dampening, c.weight_decay, c.grad_scale};
+    if (c.hyper) {
+        h.lr = __ldg(c.hyper + 0);
+        h.momentum = __ldg(c.hyper + 1);
+        h.dampening = __ldg(c.hyper + 2);
+        h.weight_decay = __ldg(c.hyper + 3);
+        h.grad_scale = __ldg(c.hyper + 4);
+    }
     const bool aligned = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) |
                            (use_m ? reinterpret_cast<uintptr_t>(m) : 0)) & 15) == 0;
     if (aligned) {
@@ -63,24 +79,105 @@ __global__ void __launch_bounds__(256) sgd_multi_kernel(const __grid_constant__ 
             const float4 gv = __ldcs(reinterpret_cast<const float4*>(g + i));
             float4 mv = make_float4(0.f, 0.f, 0.f, 0.f);
             if (use_m && !c.first) mv = *reinterpret_cast<const float4*>(m + i);
-            pv.x = sgd_one(pv.x, gv.x, &mv.x, c);
-            pv.y = sgd_one(pv.y, gv.y, &mv.y, c);
-            pv.z = sgd_one(pv.z, gv.z, &mv.z, c);
-            pv.w = sgd_one(pv.w, gv.w, &mv.w, c);
+            pv.x = sgd_one(pv.x, gv.x, &mv.x, h, use_m, first, nesterov);
+            pv.y = sgd_one(pv.y, gv.y, &mv.y, h, use_m, first, nesterov);
+            pv.z = sgd_one(pv.z, gv.z, &mv.z, h, use_m, first, nesterov);
+            pv.w = sgd_one(pv.w, gv.w, &mv.w, h, use_m, first, nesterov);
             *reinterpret_cast<float4*>(p + i) = pv;
             if (use_m) *reinterpret_cast<float4*>(m + i) = mv;
         }
         for (int64_t i = vend + threadIdx.x; i < end; i += 256) {
             float mv = (use_m && !c.first) ? m[i] : 0.f;
-            p[i] = sgd_one(p[i], g[i], &mv, c);
+            p[i] = sgd_one(p[i], g[i], &mv, h, use_m, first, nesterov);
             if (use_m) m[i] = mv;
         }
     } else {
         for (int64_t i = begin + threadIdx.x; i < end; i += 256) {
             float mv = (use_m && !c.first) ? m[i] : 0.f;
-            p[i] = sgd_one(p[i], g[i], &mv, c);
+            p[i] = sgd_one(p[i], g[i], &mv, h, use_m, first, nesterov);
             if (use_m) m[i] = mv;
         }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Adam / AdamW — torch.optim.Adam(W) semantics, amsgrad off (the reference's ``--adam`` switch, train.py:96, handed to
+// the external Trainer):
+//   g' = grad_scale * g  (+ weight_decay * p when the decay is coupled: Adam)
+//   decoupled (AdamW):  p *= 1 - lr * weight_decay
+//   m = m + (1 - beta1) * (g' - m) ;  v = beta2 * v + (1 - beta2) * g'^2
+//   p -= (lr / bc1) * m / (sqrt(v) / sqrt(bc2) + eps)          bc_i = 1 - beta_i^step  (host-computed)
+// hyper = {lr, beta1, beta2, eps, weight_decay, grad_scale, bc1, sqrt(bc2)} lives in DEVICE memory so a CUDA-graph
+// replay sees this step's learning rate and bias corrections.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kAdamTensors = 64;
+
+struct AdamChunk {
+    b200seg_adam_desc t[kAdamTensors];
+    int blk_start[kAdamTensors + 1];
+    int n;
+    int decoupled, first;
+    const float* hyper;
+};
+
+struct AdamHyper {
+    float lr, beta1, beta2, eps, wd, gs, bc1, sbc2;
+};
+
+__device__ __forceinline__ float adam_one(float p, float g, float* m, float* v, const AdamHyper& h, bool decoupled) {
+    g *= h.gs;
+    if (decoupled) p = p * (1.f - h.lr * h.wd);
+    else g = fmaf(h.wd, p, g);
+    const float mm = fmaf(1.f - h.beta1, g - *m, *m);
+    const float vv = fmaf(h.beta2, *v, (1.f - h.beta2) * g * g);
+    *m = mm;
+    *v = vv;
+    const float denom = __fdiv_rn(__fsqrt_rn(vv), h.sbc2) + h.eps;
+    return p - __fdiv_rn(h.lr, h.bc1) * __fdiv_rn(mm, denom);
+}
+
+__global__ void __launch_bounds__(256) adam_multi_kernel(const __grid_constant__ AdamChunk c) {
+    pdl_prologue();
+    int lo = 0, hi = c.n - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (c.blk_start[mid] <= static_cast<int>(blockIdx.x)) lo = mid; else hi = mid - 1;
+    }
+    const b200seg_adam_desc& t = c.t[lo];
+    const int64_t begin = static_cast<int64_t>(blockIdx.x - c.blk_start[lo]) * kSgdElemsPerBlock;
+    const int64_t end = begin + kSgdElemsPerBlock < t.numel ? begin + kSgdElemsPerBlock : t.numel;
+    AdamHyper h;
+    h.lr = __ldg(c.hyper + 0); h.beta1 = __ldg(c.hyper + 1); h.beta2 = __ldg(c.hyper + 2); h.eps = __ldg(c.hyper + 3);
+    h.wd = __ldg(c.hyper + 4); h.gs = __ldg(c.hyper + 5); h.bc1 = __ldg(c.hyper + 6); h.sbc2 = __ldg(c.hyper + 7);
+    const bool dec = c.decoupled != 0, first = c.first != 0;
+    float* p = t.p;
+    const float* g = t.g;
+    float* m = t.m;
+    float* v = t.v;
+    const bool aligned = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) |
+                           reinterpret_cast<uintptr_t>(v)) & 15) == 0;
+    const int64_t vend = aligned ? begin + ((end - begin) & ~int64_t(3)) : begin;
+    for (int64_t i = begin + threadIdx.x * 4; i < vend; i += 256 * 4) {
+        float4 pv = *reinterpret_cast<const float4*>(p + i);
+        const float4 gv = __ldcs(reinterpret_cast<const float4*>(g + i));
+        float4 mv = make_float4(0.f, 0.f, 0.f, 0.f), vv = mv;
+        if (!first) {
+            mv = *reinterpret_cast<const float4*>(m + i);
+            vv = *reinterpret_cast<const float4*>(v + i);
+        }
+        pv.x = adam_one(pv.x, gv.x, &mv.x, &vv.x, h, dec);
+        pv.y = adam_one(pv.y, gv.y, &mv.y, &vv.y, h, dec);
+        pv.z = adam_one(pv.z, gv.z, &mv.z, &vv.z, h, dec);
+        pv.w = adam_one(pv.w, gv.w, &mv.w, &vv.w, h, dec);
+        *reinterpret_cast<float4*>(p + i) = pv;
+        *reinterpret_cast<float4*>(m + i) = mv;
+        *reinterpret_cast<float4*>(v + i) = vv;
+    }
+    for (int64_t i = vend + threadIdx.x; i < end; i += 256) {
+        float mv = first ? 0.f : m[i], vv = first ? 0.f : v[i];
+        p[i] = adam_one(p[i], g[i], &mv, &vv, h, dec);
+        m[i] = mv;
+        v[i] = vv;
     }
 }
 
@@ -234,7 +331,7 @@ __global__ void __launch_bounds__(256) pack_multi_kernel(const __grid_constant__
 extern "C" {
 
 int b200seg_sgd_multi(const b200seg_sgd_desc* descs, int n, float lr, float momentum, float dampening, float weight_decay,
-                      int nesterov, int first_step, float grad_scale, b200seg_stream_t stream) {
+                      int nesterov, int first_step, float grad_scale, const float* hyper, b200seg_stream_t stream) {
     using namespace b200seg;
     clear_error();
     B200SEG_CHECK(descs && n > 0, "sgd_multi: no tensors");
@@ -246,6 +343,7 @@ int b200seg_sgd_multi(const b200seg_sgd_desc* descs, int n, float lr, float mome
         memset(&c, 0, sizeof(c));
         c.lr = lr; c.momentum = momentum; c.dampening = dampening; c.weight_decay = weight_decay;
         c.grad_scale = grad_scale; c.nesterov = nesterov; c.first = first_step;
+        c.hyper = hyper;
         int blocks = 0;
         while (base < n && c.n < kSgdTensors) {
             const b200seg_sgd_desc& d = descs[base];
@@ -260,6 +358,37 @@ int b200seg_sgd_multi(const b200seg_sgd_desc* descs, int n, float lr, float mome
         c.blk_start[c.n] = blocks;
         if (c.n == 0) continue;
         B200SEG_CUDA(launch_pdl(sgd_multi_kernel, blocks, 256, 0, st, c));
+    }
+    return 0;
+}
+
+int b200seg_adam_multi(const b200seg_adam_desc* descs, int n, const float* hyper, int decoupled, int first_step,
+                       b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(descs && n > 0, "adam_multi: no tensors");
+    B200SEG_CHECK(hyper, "adam_multi: the hyper-parameter vector lives in device memory (8 floats)");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    for (int base = 0; base < n;) {
+        AdamChunk c;
+        memset(&c, 0, sizeof(c));
+        c.decoupled = decoupled;
+        c.first = first_step;
+        c.hyper = hyper;
+        int blocks = 0;
+        while (base < n && c.n < kAdamTensors) {
+            const b200seg_adam_desc& d = descs[base];
+            B200SEG_CHECK(d.p && d.g && d.m && d.v && d.numel >= 0, "adam_multi: tensor %d has null pointers", base);
+            ++base;
+            if (d.numel == 0) continue;
+            c.t[c.n] = d;
+            c.blk_start[c.n] = blocks;
+            blocks += static_cast<int>(ceil_div64(d.numel, kSgdElemsPerBlock));
+            ++c.n;
+        }
+        c.blk_start[c.n] = blocks;
+        if (c.n == 0) continue;
+        B200SEG_CUDA(launch_pdl(adam_multi_kernel, blocks, 256, 0, st, c));
     }
     return 0;
 }

@@ -391,6 +391,57 @@ def space_to_depth(x, r, s, pad):
     return WindowAct(z, (s + 1) // 2 * cs, algo_k=r * s * c), oh, ow
 
 
+# utils/datasets.py:201-205 — the reference's normalisation constants (ImageNet mean / std on the 0..255 scale)
+INPUT_MEAN = (123.675, 116.28, 103.53)
+INPUT_STD = (58.395, 57.12, 57.375)
+
+
+def _norm_args(c, mean, std):
+    mean = tuple(INPUT_MEAN if mean is None else mean)
+    std = tuple(INPUT_STD if std is None else std)
+    if len(mean) != c or len(std) != c:
+        raise ValueError('normalisation constants for %d channels, image has %d' % (len(mean), c))
+    return (ctypes.c_float * c)(*mean), (ctypes.c_float * c)(*std)
+
+
+def _u8_image(x, what):
+    _require_cuda(x, what)
+    if x.dim() != 4 or x.dtype != torch.uint8:
+        raise ValueError('%s: expected an N x C x H x W uint8 tensor, got %s %s' % (what, tuple(x.shape), x.dtype))
+    if x.is_contiguous():
+        return x, 0
+    if x.permute(0, 2, 3, 1).is_contiguous():
+        return x, 1          # channels_last uint8 (what cv2 decodes to): read in place
+    return x.contiguous(), 0
+
+
+def normalize_u8(x, mean=None, std=None):
+    """uint8 N x C x H x W (NCHW or channels_last) -> fp32 NCHW (x - mean) / std: post_fetch_fn of utils/datasets.py:199-206
+    on the device, bit-identical to the reference's three fp32 tensor ops."""
+    x, layout = _u8_image(x, 'normalize_u8')
+    n, c, h, w = x.shape
+    m, s = _norm_args(c, mean, std)
+    y = torch.empty((n, c, h, w), dtype=torch.float32, device=x.device)
+    _lib.check(_lib.load().b200seg_input_u8_normalize(x.data_ptr(), layout, n, c, h, w, m, s, y.data_ptr(), _stream()),
+               'input_u8_normalize')
+    _lib.count_launch()
+    return y
+
+
+def space_to_depth_u8(x, r, s, pad, mean=None, std=None):
+    """uint8 image batch -> the stem's WindowAct in one pass: normalise + bf16 + NHWC + 2x2 space-to-depth (csrc/input.cu)."""
+    x, layout = _u8_image(x, 'space_to_depth_u8')
+    n, c, h, w = x.shape
+    m, sd = _norm_args(c, mean, std)
+    oh, ow = (h + 2 * pad - r) // 2 + 1, (w + 2 * pad - s) // 2 + 1
+    cs = _round_up(4 * c, 8)
+    z = torch.empty((n, oh + (r + 1) // 2 - 1, ow + (s + 1) // 2 - 1, cs), dtype=BF16, device=x.device)
+    _lib.check(_lib.load().b200seg_input_u8_s2d(x.data_ptr(), layout, n, c, h, w, r, s, pad, m, sd, z.data_ptr(), cs,
+                                                _stream()), 'input_u8_s2d')
+    _lib.count_launch()
+    return WindowAct(z, (s + 1) // 2 * cs, algo_k=r * s * c), oh, ow
+
+
 def unpack_wgrad_s2d(dwin, pw, lane=False):
     return on_wgrad_lane(_unpack_wgrad_s2d, dwin, pw, keep=(dwin,)) if lane else _unpack_wgrad_s2d(dwin, pw)
 
@@ -955,6 +1006,21 @@ def resize_nchw_bwd(dy, h, w, align_corners=True):
     return dx
 
 
+_TARGET_KINDS = {torch.int64: 0, torch.int32: 1, torch.uint8: 2}      # B200SEG_TARGET_* (include/b200seg.h)
+
+
+def target_kind(targets):
+    """Masks are read as they are: int64 (post_fetch_fn's ``segs.long()``, utils/datasets.py:213) or the dataset's own
+    uint8 (utils/datasets.py:161-194) / int32 — no widening copy."""
+    k = _TARGET_KINDS.get(targets.dtype)
+    if k is None:
+        raise RuntimeError('targets must be int64, int32 or uint8 (got %s)' % targets.dtype)
+    _require_cuda(targets, 'targets')
+    if not targets.is_contiguous():
+        raise RuntimeError('targets must be contiguous')
+    return k
+
+
 def softmax_ce(logits, targets, ignore_index=-100, want_grad=True):
     """logits NCHW fp32, targets int64 [n, h, w].  Returns (acc, dlogits): ``acc`` is a 3-element fp64
     device tensor (sum of -log p[target], number of valid pixels as int64 bits, status flag as int32
@@ -963,7 +1029,7 @@ def softmax_ce(logits, targets, ignore_index=-100, want_grad=True):
     acc = torch.zeros((3,), dtype=torch.float64, device=logits.device)
     dl = torch.empty_like(logits) if want_grad else None
     p = acc.data_ptr()
-    _lib.check(_lib.load().b200seg_softmax_ce(logits.data_ptr(), targets.data_ptr(), n, nc, h * w, ignore_index, 1.0,
+    _lib.check(_lib.load().b200seg_softmax_ce(logits.data_ptr(), targets.data_ptr(), target_kind(targets), n, nc, h * w, ignore_index, 1.0,
                                               p, p + 8, dl.data_ptr() if want_grad else None, p + 16, _stream()),
                'softmax_ce')
     _lib.count_launch()
@@ -975,7 +1041,7 @@ LOWRES_CE = _os.environ.get('B200SEG_LOWRES_CE', '1') != '0'   # loss through th
 
 def _lowres_geometry(lr, targets):
     n, h, w, ct = lr.shape
-    assert lr.dtype == torch.float32 and lr.is_contiguous() and targets.dtype == torch.int64 and targets.is_contiguous()
+    assert lr.dtype == torch.float32 and lr.is_contiguous() and targets.dtype in _TARGET_KINDS and targets.is_contiguous()
     assert targets.shape[0] == n
     return n, h, w, ct, targets.shape[1], targets.shape[2]
 
@@ -1002,7 +1068,7 @@ def lowres_ce_fwd(lr, nc, targets, align_corners=True, ignore_index=-100):
     n, h, w, ct, th, tw = _lowres_geometry(lr, targets)
     acc = torch.zeros((3,), dtype=torch.float64, device=lr.device)
     p = acc.data_ptr()
-    _lib.check(_lib.load().b200seg_lowres_ce_fwd(lr.data_ptr(), n, h, w, ct, nc, targets.data_ptr(), th, tw,
+    _lib.check(_lib.load().b200seg_lowres_ce_fwd(lr.data_ptr(), n, h, w, ct, nc, targets.data_ptr(), target_kind(targets), th, tw,
                                                  int(align_corners), ignore_index, p, p + 8, p + 16, _stream()),
                'lowres_ce_fwd')
     _lib.count_launch()
@@ -1014,7 +1080,7 @@ def lowres_ce_bwd(lr, nc, targets, grad_out, count, align_corners=True, ignore_i
     n, h, w, ct, th, tw = _lowres_geometry(lr, targets)
     assert grad_out.dtype == torch.float32 and count.dtype == torch.int64
     dlr = torch.empty_like(lr)
-    _lib.check(_lib.load().b200seg_lowres_ce_bwd(lr.data_ptr(), n, h, w, ct, nc, targets.data_ptr(), th, tw,
+    _lib.check(_lib.load().b200seg_lowres_ce_bwd(lr.data_ptr(), n, h, w, ct, nc, targets.data_ptr(), target_kind(targets), th, tw,
                                                  int(align_corners), ignore_index, grad_out.data_ptr(), count.data_ptr(),
                                                  dlr.data_ptr(), _stream()), 'lowres_ce_bwd')
     _lib.count_launch()
@@ -1064,7 +1130,7 @@ def softmax_ce_bwd(logits, targets, grad_out, count, ignore_index=-100):
     n, nc, h, w = logits.shape
     assert grad_out.dtype == torch.float32 and count.dtype == torch.int64
     dl = torch.empty_like(logits)
-    _lib.check(_lib.load().b200seg_softmax_ce_bwd(logits.data_ptr(), targets.data_ptr(), n, nc, h * w, ignore_index,
+    _lib.check(_lib.load().b200seg_softmax_ce_bwd(logits.data_ptr(), targets.data_ptr(), target_kind(targets), n, nc, h * w, ignore_index,
                                                   grad_out.data_ptr(), count.data_ptr(), dl.data_ptr(), _stream()),
                'softmax_ce_bwd')
     _lib.count_launch()
@@ -1079,23 +1145,53 @@ def argmax(logits):
     return pred
 
 
-def confusion(pred, targets, nc, cm=None):
+def _check_cm(cm, nc, device):
+    """The kernels index the matrix with nc: a matrix of another size would be written out of bounds / mis-binned."""
     if cm is None:
-        cm = torch.zeros((nc, nc), dtype=torch.int64, device=pred.device)
-    _lib.check(_lib.load().b200seg_confusion(pred.data_ptr(), targets.data_ptr(), pred.numel(), nc, cm.data_ptr(),
-                                             _stream()), 'confusion')
+        return torch.zeros((nc, nc), dtype=torch.int64, device=device)
+    if tuple(cm.shape) != (nc, nc) or cm.dtype != torch.int64 or not cm.is_contiguous() or not cm.is_cuda:
+        raise ValueError('confusion matrix must be a contiguous CUDA int64 %d x %d tensor (got %s %s)'
+                         % (nc, nc, tuple(cm.shape), cm.dtype))
+    return cm
+
+
+def confusion(pred, targets, nc, cm=None):
+    cm = _check_cm(cm, nc, pred.device)
+    if pred.numel() != targets.numel():
+        raise ValueError('confusion: %d predictions vs %d targets' % (pred.numel(), targets.numel()))
+    _lib.check(_lib.load().b200seg_confusion(pred.data_ptr(), targets.data_ptr(), target_kind(targets), pred.numel(), nc,
+                                             cm.data_ptr(), _stream()), 'confusion')
     _lib.count_launch()
     return cm
 
 
 def argmax_confusion(logits, targets, cm=None):
     n, nc, h, w = logits.shape
-    if cm is None:
-        cm = torch.zeros((nc, nc), dtype=torch.int64, device=logits.device)
-    _lib.check(_lib.load().b200seg_argmax_confusion(logits.data_ptr(), targets.data_ptr(), n, nc, h * w,
+    cm = _check_cm(cm, nc, logits.device)
+    if targets.numel() != n * h * w:
+        raise ValueError('argmax_confusion: logits %s vs targets %s' % (tuple(logits.shape), tuple(targets.shape)))
+    _lib.check(_lib.load().b200seg_argmax_confusion(logits.data_ptr(), targets.data_ptr(), target_kind(targets), n, nc, h * w,
                                                     cm.data_ptr(), _stream()), 'argmax_confusion')
     _lib.count_launch()
     return cm
+
+
+def class_map_confusion(lr, nc, targets, align_corners=True, cm=None, want_pred=False):
+    """Evaluation from a head's low-resolution fp32 NHWC class map (the tag ``attach_class_map`` leaves on the logits):
+    argmax of its bilinear upsample to the target size + confusion histogram, without reading the full-resolution logits.
+    Bit-identical to ``argmax_confusion`` over the logits the head wrote (same interpolation instructions; ties -> lowest
+    class index).  Returns (cm, pred or None)."""
+    n, h, w, ct = lr.shape
+    assert lr.dtype == torch.float32 and lr.is_contiguous() and targets.shape[0] == n
+    th, tw = targets.shape[1], targets.shape[2]
+    cm = _check_cm(cm, nc, lr.device)
+    pred = torch.empty((n, th, tw), dtype=torch.int64, device=lr.device) if want_pred else None
+    _lib.check(_lib.load().b200seg_class_map_confusion(lr.data_ptr(), n, h, w, ct, nc, targets.data_ptr(), target_kind(targets),
+                                                       th, tw, int(align_corners), cm.data_ptr(),
+                                                       pred.data_ptr() if pred is not None else None, _stream()),
+               'class_map_confusion')
+    _lib.count_launch()
+    return cm, pred
 
 
 # ------------------------------------------------------------------------------------------------

@@ -49,10 +49,16 @@ class _ConvBNFn(torch.autograd.Function):
         E._require_cuda(x, 'conv_bn input')
         if state.gather:
             xf = x.detach()
-            if xf.dtype != torch.float32 or not xf.is_contiguous():
+            norm = getattr(x, '_b200seg_norm', (None, None))
+            u8 = xf.dtype == torch.uint8        # utils.post_fetch_fn: 1-byte pixels, normalised by the kernel that reads them
+            if u8 and not state.s2d:
+                xf = E.normalize_u8(xf, *norm)
+            elif not u8 and (xf.dtype != torch.float32 or not xf.is_contiguous()):
                 xf = xf.float().contiguous()
             pw = state.packed.update(weight)
-            if state.s2d:
+            if state.s2d and u8:
+                xa, oh, ow = E.space_to_depth_u8(xf, k, k, conv.padding[0], *norm)
+            elif state.s2d:
                 xa, oh, ow = E.space_to_depth(xf, k, k, conv.padding[0])
             else:
                 xa = E.im2col(xf, k, k, stride, conv.padding[0])

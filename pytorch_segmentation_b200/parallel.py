@@ -8,6 +8,10 @@ buffer, re-points ``param.grad`` at that slot, and â€” when the bucket is full â
 asynchronous ``all_reduce`` (NCCL over NVLink/NVSwitch on GPUs, gloo in the CPU tests) while backward
 keeps running.  ``finish()`` waits for the outstanding buckets and averages.
 
+Every rank must produce gradients for the SAME set of parameters in every step (as with DDP without
+``find_unused_parameters``): ``finish()`` launches the partially filled buckets, and ranks that disagree on which
+buckets those are would wait on each other forever.  ``sync_initial_state()`` is DDP's construction-time broadcast.
+
 There is no collective on the data path itself: images are independent through every kernel
 (train-mode BatchNorm statistics stay per-GPU, as in the reference, which shows no SyncBN).
 """
@@ -30,6 +34,31 @@ class GradBucketer:
         self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
         self.enabled = True         # set False on non-final micro-steps of gradient accumulation
         self._early = set()         # parameters whose gradient reached its slot before autograd delivered it
+
+    def sync_initial_state(self, module=None, src=0):
+        """Broadcast every parameter (and, given the module, every buffer: BatchNorm running statistics) from rank ``src``
+        â€” what DistributedDataParallel does at construction.  Without it each rank trains from its own random
+        initialisation unless the caller seeded them identically, and rank 0's checkpoint is not the collectively
+        trained model.  Tensors travel flattened per dtype (a handful of collectives).  Returns self."""
+        if self.world <= 1:
+            return self
+        tensors = list(self.params)
+        if module is not None:
+            seen = {id(p) for p in tensors}
+            tensors += [p for p in module.parameters() if id(p) not in seen]
+            tensors += [b for b in module.buffers()]
+        by_dtype = {}
+        for t in tensors:
+            by_dtype.setdefault((t.dtype, t.device), []).append(t)
+        with torch.no_grad():
+            for group in by_dtype.values():
+                flat = torch.cat([t.detach().reshape(-1) for t in group])
+                dist.broadcast(flat, src=src, group=self.group)
+                off = 0
+                for t in group:
+                    t.copy_(flat[off:off + t.numel()].view_as(t))
+                    off += t.numel()
+        return self
 
     def attach(self):
         """Become the engine's early-gradient sink (engine.deliver_grads): hand-sequenced nodes such as the ResNet-50

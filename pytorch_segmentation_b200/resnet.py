@@ -182,10 +182,16 @@ class ResNet50Features(nn.Module):
         if conv1.bias is not None or conv1.groups != 1 or conv1.dilation != (1, 1):
             raise NotImplementedError('backbone stem %r is outside the patch-gather path' % (conv1,))
         xf = x.detach()
-        if xf.dtype != torch.float32 or not xf.is_contiguous():
-            xf = xf.float().contiguous()
         pw0 = self._stem_packed.update(conv1.weight)
-        if isinstance(pw0, E.PackedS2DWeight):
+        u8 = xf.dtype == torch.uint8          # utils.post_fetch_fn: 1-byte pixels, normalised by the first kernel that reads them
+        if u8 and not isinstance(pw0, E.PackedS2DWeight):
+            xf = E.normalize_u8(xf, *getattr(x, '_b200seg_norm', (None, None)))
+        elif not u8 and (xf.dtype != torch.float32 or not xf.is_contiguous()):
+            xf = xf.float().contiguous()
+        if isinstance(pw0, E.PackedS2DWeight) and u8:
+            col, oh0, ow0 = E.space_to_depth_u8(xf, conv1.kernel_size[0], conv1.kernel_size[1], conv1.padding[0],
+                                                *getattr(x, '_b200seg_norm', (None, None)))
+        elif isinstance(pw0, E.PackedS2DWeight):
             col, oh0, ow0 = E.space_to_depth(xf, conv1.kernel_size[0], conv1.kernel_size[1], conv1.padding[0])
         else:
             col = E.im2col(xf, conv1.kernel_size[0], conv1.kernel_size[1], conv1.stride[0], conv1.padding[0])
@@ -309,6 +315,33 @@ class _ResNetFn(torch.autograd.Function):
         return (None, None) + tuple(out)
 
 
+def load_pretrained(module, arch, filename):
+    """``pretrained=True`` (models/deeplabv3plus.py:17, models/unet.py:17): the reference's backbones start from ImageNet
+    weights.  There is no network here, so the torchvision checkpoint is taken from a local file — ``$B200SEG_PRETRAINED_DIR``
+    or the torch hub cache (``<hub>/checkpoints/<filename>``) — and when none exists the backbone stays randomly
+    initialised WITH A WARNING (never silently)."""
+    import os
+    import warnings
+    dirs = [os.environ.get('B200SEG_PRETRAINED_DIR'), os.path.join(torch.hub.get_dir(), 'checkpoints')]
+    for d in dirs:
+        path = os.path.join(d, filename) if d else None
+        if path and os.path.exists(path):
+            state = torch.load(path, map_location='cpu', weights_only=True)
+            own = module.state_dict()
+            missing = [k for k in own if k not in state]
+            if missing:
+                raise RuntimeError('%s: %s lacks %d tensors (e.g. %s)' % (arch, path, len(missing), missing[0]))
+            module.load_state_dict({k: state[k] for k in own})
+            return True
+    warnings.warn('%s(pretrained=True): no local ImageNet checkpoint (%s under $B200SEG_PRETRAINED_DIR or %s) and no '
+                  'network — the backbone is RANDOMLY INITIALISED, unlike the reference\'s' % (arch, filename, dirs[1]),
+                  RuntimeWarning, stacklevel=3)
+    return False
+
+
 def resnet50(pretrained=False, replace_stride_with_dilation=None, **kw):
-    """Drop-in for ``pytorch_modules.backbones.resnet50`` (``pretrained`` ignored: no network, random init)."""
-    return ResNet50Features(replace_stride_with_dilation)
+    """Drop-in for ``pytorch_modules.backbones.resnet50`` (models/deeplabv3plus.py:17-19)."""
+    net = ResNet50Features(replace_stride_with_dilation)
+    if pretrained:
+        load_pretrained(net, 'resnet50', 'resnet50-0676ba61.pth')
+    return net

@@ -9,6 +9,19 @@ replayed with one launch per step — streams and graphs, no tracing compiler.
 
 Every kernel in the graph is the same libb200seg launch the eager path makes (the capture simply records them);
 buffers come from the graph's private pool of the PyTorch caching allocator.
+
+Gradient accumulation (``--accumulate``, train.py:94, default 2, implemented by the reference's external ``Trainer``):
+``TrainStep(accumulate=k)`` runs forward + backward on every call and the gradient exchange + optimizer step on every
+k-th; the data-parallel all-reduce is skipped on the other k-1 (``GradBucketer.enabled``), as DDP's ``no_sync`` would.
+Each micro-batch's loss is divided by k before backward (the step then descends the mean over the k micro-batches; the
+external Trainer's own scaling is unknown — ``average_accumulated=False`` leaves the losses unscaled).  Under a CUDA
+graph the k micro-steps and the update are ONE captured graph over k static input slots: calls 1..k-1 only stage their
+micro-batch (and return None), call k replays.
+
+What a captured step freezes, and what it does not: shapes, the set of parameters with gradients, momentum / nesterov
+on-off and the accumulate count are structural — changing one needs a new TrainStep.  Learning rate, momentum value,
+weight decay, Adam's betas / step count are read by the optimizer kernels from a device vector that is refreshed from
+``optimizer.param_groups`` before every replay (optim._HyperMixin), so LR schedulers work unchanged.
 """
 import torch
 
@@ -18,27 +31,50 @@ from .utils.utils import compute_loss
 
 
 class TrainStep:
-    def __init__(self, model, optimizer, bucketer=None, graph=False, loss_fn=compute_loss, warmup=3):
+    def __init__(self, model, optimizer, bucketer=None, graph=False, loss_fn=compute_loss, warmup=3, accumulate=1,
+                 average_accumulated=True):
         self.model, self.optimizer, self.bucketer, self.loss_fn = model, optimizer, bucketer, loss_fn
         self.use_graph = bool(graph)
+        self.accumulate = int(accumulate)
+        if self.accumulate < 1:
+            raise ValueError('TrainStep(accumulate=%r): need >= 1' % (accumulate,))
+        if self.use_graph and warmup < 1:
+            # a step captured before any eager one would record the optimizer's first-step path (momentum buffers
+            # initialised from the gradient on EVERY replay) and, with freshly packed weights, no weight re-packing
+            raise ValueError('TrainStep(graph=True) needs warmup >= 1 eager step before the capture')
         self.warmup = warmup
+        self.loss_scale = 1.0 / self.accumulate if average_accumulated else 1.0
         self._graph = None
         self._x = self._t = self._loss = self._side = None
         self._calls = 0
+        self._micro = 0                        # micro-batches taken since the last optimizer step
+        self._xs = self._ts = None             # graph mode with accumulate > 1: the k static input slots
         self._stage = None
         self._staged = False
         self.launches_per_step = None          # libb200seg launches recorded in the captured step
 
     # the eager step ------------------------------------------------------------------------------------------
-    def _step(self, x, t):
-        self.optimizer.zero_grad(set_to_none=True)
+    def _micro_step(self, x, t, first, last):
+        """forward + loss + backward of one micro-batch; zeroes the gradients before the first, exchanges and applies
+        them after the last."""
+        if first:
+            self.optimizer.zero_grad(set_to_none=True)
+        if self.bucketer is not None:
+            self.bucketer.enabled = last           # accumulate locally, all-reduce the sum once (DDP no_sync)
         out = self.model(x)
         loss = self.loss_fn(out, t, self.model)
-        loss.backward()
-        if self.bucketer is not None:
-            self.bucketer.finish()
-        self.optimizer.step()
+        (loss * self.loss_scale if self.loss_scale != 1.0 else loss).backward()
+        if last:
+            if self.bucketer is not None:
+                self.bucketer.finish()
+            self.optimizer.step()
         return loss.detach()
+
+    def _step(self, x, t):
+        first, last = self._micro == 0, self._micro == self.accumulate - 1
+        loss = self._micro_step(x, t, first, last)
+        self._micro = 0 if last else self._micro + 1
+        return loss
 
     # capture ----------------------------------------------------------------------------------------------------
     def _set_inputs(self, x, t):
@@ -55,12 +91,21 @@ class TrainStep:
 
     def _capture(self):
         torch.cuda.synchronize()
+        # every packed bf16 weight copy counts as stale from here, so the capture records the re-packing launch whatever
+        # the caches held (a graph without it would replay on frozen weights)
+        E.WEIGHT_EPOCH += 1
         g = torch.cuda.CUDAGraph()
         l0 = _lib.launches()
+        k = self.accumulate
         with torch.cuda.graph(g):
-            self._loss = self._step(self._x, self._t)
+            if k == 1:
+                self._loss = self._micro_step(self._x, self._t, True, True)
+            else:
+                losses = [self._micro_step(self._xs[i], self._ts[i], i == 0, i == k - 1) for i in range(k)]
+                self._loss = torch.stack(losses).mean()
         self.launches_per_step = _lib.launches() - l0
         self._graph = g
+        self._fresh_capture = True
 
     def __call__(self, x, t):
         """x: N x 3 x H x W images, t: N x H x W int64 masks, both on the model's device.  Returns the (detached)
@@ -71,8 +116,10 @@ class TrainStep:
         that and every later call replays it."""
         if not self.use_graph:
             return self._step(x, t)
+        if self.accumulate > 1 and (self._graph is not None or self._calls >= self.warmup * self.accumulate):
+            return self._graph_accumulate(x, t)
         self._set_inputs(x, t)
-        if self._graph is None and self._calls < self.warmup:
+        if self._graph is None and self._calls < self.warmup * self.accumulate:
             self._calls += 1
             self._side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(self._side):
@@ -81,11 +128,42 @@ class TrainStep:
             return loss
         if self._graph is None:
             self._capture()
+        return self._replay()
+
+    def _replay(self):
+        # the optimizer kernels read their hyper-parameters from a device vector whose pinned host mirror the graph copies
+        # in on every replay: bring the mirror up to date with param_groups (LR schedule, Adam step count).  The capture
+        # call's own step() has just done that.
+        if getattr(self, '_fresh_capture', False):
+            self._fresh_capture = False
+        elif hasattr(self.optimizer, 'refresh_hyper'):
+            self.optimizer.refresh_hyper()
         self._graph.replay()
         # a replay updates the parameters without bumping their Python-side version counters: tell the packed-weight
         # caches that whatever they hold is stale for any later eager call (eval after training)
         E.WEIGHT_EPOCH += 1
         return self._loss
+
+    def _graph_accumulate(self, x, t):
+        """accumulate > 1 under a graph: stage micro-batch i into its static slot; the k-th call replays the one graph
+        that holds all k forward/backward passes and the update.  Returns None on staging calls, the mean loss of the k
+        micro-batches on the k-th."""
+        k = self.accumulate
+        if self._xs is None:
+            self._xs = [torch.empty_like(x) for _ in range(k)]
+            self._ts = [torch.empty_like(t) for _ in range(k)]
+        if x.shape != self._xs[0].shape or t.shape != self._ts[0].shape:
+            raise ValueError('TrainStep(graph=True) is bound to inputs %s / %s, got %s / %s'
+                             % (tuple(self._xs[0].shape), tuple(self._ts[0].shape), tuple(x.shape), tuple(t.shape)))
+        self._xs[self._micro].copy_(x, non_blocking=True)
+        self._ts[self._micro].copy_(t, non_blocking=True)
+        if self._micro < k - 1:
+            self._micro += 1
+            return None
+        self._micro = 0
+        if self._graph is None:
+            self._capture()
+        return self._replay()
 
     # host-side input pipeline -------------------------------------------------------------------------------
     def prefetch(self, x_host, t_host):

@@ -13,8 +13,8 @@ class _CrossEntropyFn(torch.autograd.Function):
     def forward(ctx, outputs, targets):
         E._require_cuda(outputs, 'compute_loss(outputs)')
         E._require_cuda(targets, 'compute_loss(targets)')
-        if targets.dtype != torch.int64:
-            raise RuntimeError('compute_loss: expected int64 targets, got %s' % targets.dtype)
+        if targets.dtype not in (torch.int64, torch.int32, torch.uint8):
+            raise RuntimeError('compute_loss: expected int64 (or int32 / uint8) targets, got %s' % targets.dtype)
         x = outputs.detach()
         if x.dtype != torch.float32 or not x.is_contiguous():
             x = x.float().contiguous()
@@ -69,11 +69,39 @@ class _ClassMapCrossEntropyFn(torch.autograd.Function):
 def compute_loss(outputs, targets, model=None):
     """utils/utils.py:17-24: logits N x nc x h x w, int64 targets N x H x W -> 0-dim loss tensor."""
     cm = getattr(outputs, '_b200seg_class_map', None)
-    if (cm is not None and cm[3] == outputs._version and targets.is_cuda and targets.dtype == torch.int64
+    if (cm is not None and cm[3] == outputs._version and targets.is_cuda
+            and targets.dtype in (torch.int64, torch.int32, torch.uint8)
             and tuple(outputs.shape[2:]) == tuple(targets.shape[1:]) and E.LOWRES_CE
             and E.lowres_ce_supported(cm[0].shape, cm[1], targets.shape[1], targets.shape[2], cm[2])):
         return _ClassMapCrossEntropyFn.apply(cm[0], targets.contiguous(), cm[1], cm[2])
     return _CrossEntropyFn.apply(outputs, targets)
+
+
+def post_fetch_fn(batch, mean=None, std=None):
+    """Drop-in for ``BasicDataset.post_fetch_fn`` (utils/datasets.py:199-213) on device-resident batches:
+    ``(uint8 N x 3 x H x W images, uint8 N x H x W masks)`` -> ``(images, masks)`` ready for ``model(images)`` /
+    ``compute_loss(outputs, masks, model)``.
+
+    The reference computes ``imgs.float(); imgs -= mean; imgs /= std`` and ``segs.long()``: 4-byte pixels and 8-byte
+    labels.  Here both stay 1-byte: the images are returned as they are, tagged with the normalisation constants, and
+    the first kernel that touches them — the stem's space-to-depth pass for DeepLabV3+ / HRNet
+    (``engine.space_to_depth_u8``), ``engine.normalize_u8`` for any other backbone — applies the same fp32 arithmetic;
+    loss and metric kernels read uint8 masks directly.  ``multi_scale`` resizing (utils/datasets.py:206-212, nearest
+    ``F.interpolate`` of the float images) is not part of this path.  float images pass through unchanged."""
+    imgs, segs = batch
+    if imgs.dtype == torch.uint8:
+        imgs._b200seg_norm = (tuple(E.INPUT_MEAN if mean is None else mean), tuple(E.INPUT_STD if std is None else std))
+    return imgs, segs
+
+
+def model_input(x):
+    """What a model's forward does with its input first: uint8 images (``post_fetch_fn`` above) become the normalised
+    fp32 NCHW tensor of the reference; floats pass through.  (DeepLabV3+'s stem bypasses this and fuses the
+    normalisation into its space-to-depth pass.)"""
+    if x.dtype == torch.uint8:
+        mean, std = getattr(x, '_b200seg_norm', (None, None))
+        return E.normalize_u8(x, mean, std)
+    return x
 
 
 def compute_metrics(tp, fn, fp):

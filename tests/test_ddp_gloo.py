@@ -149,3 +149,31 @@ def test_early_gradient_delivery_world2(tmp_path):
         for rank in range(world):
             for a, b in zip(r[rank]['grads'][it], want):
                 assert torch.allclose(a, b, rtol=1e-5, atol=1e-6)
+
+
+def _sync_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    from pytorch_segmentation_b200.parallel import GradBucketer
+    torch.manual_seed(1000 + rank)                            # DIFFERENT weights and statistics on every rank
+    model = torch.nn.Sequential(torch.nn.Conv2d(3, 8, 3), torch.nn.BatchNorm2d(8), torch.nn.Conv2d(8, 4, 1))
+    model[1].running_mean.normal_()
+    model[1].num_batches_tracked.fill_(rank + 5)
+    model[2].weight.requires_grad_(False)                     # a frozen parameter is not in the bucketer but must sync too
+    before = {k: v.clone() for k, v in model.state_dict().items()}
+    GradBucketer(model.parameters(), bucket_mb=0.01).sync_initial_state(model)
+    torch.save({'before': before, 'after': {k: v.clone() for k, v in model.state_dict().items()}},
+               os.path.join(out, 's%d.pt' % rank))
+    dist.destroy_process_group()
+
+
+def test_sync_initial_state_world2(tmp_path):
+    """GradBucketer.sync_initial_state = DDP's construction-time broadcast: every rank ends up with rank 0's parameters
+    AND buffers (BN running statistics, num_batches_tracked), whatever it was initialised with."""
+    world, port = 2, _free_port()
+    mp.spawn(_sync_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    r = [torch.load(os.path.join(str(tmp_path), 's%d.pt' % i)) for i in range(world)]
+    assert any(not torch.equal(r[0]['before'][k], r[1]['before'][k]) for k in r[0]['before'])
+    for k, v in r[0]['before'].items():
+        assert torch.equal(r[0]['after'][k], v), k            # rank 0 keeps its state
+        assert torch.equal(r[1]['after'][k], v), k            # rank 1 receives it

@@ -1,0 +1,317 @@
+"""Round-2 rows of SURVEY.md §8: the input side (f4: uint8 images / masks straight into the kernels), the fused evaluation
+from the class map (a9 / a13), Adam / AdamW and gradient accumulation (f3), and the graph step's hyper-parameter plumbing.
+
+Bit-exact where the arithmetic is integer or a fixed fp32 op sequence (normalisation, space-to-depth, argmax, confusion),
+tolerances stated where fp32 accumulation order differs (optimizer updates, losses)."""
+import copy
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+MEAN = (123.675, 116.28, 103.53)      # utils/datasets.py:201-205
+STD = (58.395, 57.12, 57.375)
+
+
+@pytest.fixture(scope='module')
+def P(lib):
+    import pytorch_segmentation_b200 as pkg
+    return pkg
+
+
+@pytest.fixture(scope='module')
+def E(lib):
+    from pytorch_segmentation_b200 import engine
+    return engine
+
+
+def _post_fetch_reference(imgs_u8):
+    """utils/datasets.py:199-205, the reference's three fp32 tensor ops (on the CPU)."""
+    imgs = imgs_u8.cpu().float()
+    imgs -= torch.FloatTensor(list(MEAN)).reshape(1, 3, 1, 1)
+    imgs /= torch.FloatTensor(list(STD)).reshape(1, 3, 1, 1)
+    return imgs
+
+
+# ---------------------------------------------------------------------------------------------------
+# f4: input side
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('n,h,w', [(2, 64, 96), (3, 37, 53), (16, 512, 512)])
+def test_normalize_u8_bit_exact(E, n, h, w):
+    g = torch.Generator().manual_seed(n * h + w)
+    x = torch.randint(0, 256, (n, 3, h, w), generator=g, dtype=torch.uint8)
+    want = _post_fetch_reference(x)
+    got = E.normalize_u8(x.cuda())
+    assert got.dtype == torch.float32 and torch.equal(got.cpu(), want)
+    # channels_last uint8 (an NHWC buffer, what cv2 decodes to) is read in place
+    xl = x.cuda().contiguous(memory_format=torch.channels_last)
+    assert torch.equal(E.normalize_u8(xl).cpu(), want)
+
+
+@pytest.mark.parametrize('n,h,w,r,pad', [(2, 64, 96, 7, 3), (2, 62, 70, 3, 1), (16, 512, 512, 7, 3)])
+def test_space_to_depth_u8_equals_normalise_then_fp32_path(E, n, h, w, r, pad):
+    """One pass over 1-byte pixels == post_fetch_fn followed by the fp32 space-to-depth pass, bit for bit (bf16)."""
+    g = torch.Generator().manual_seed(h + w)
+    x = torch.randint(0, 256, (n, 3, h, w), generator=g, dtype=torch.uint8)
+    ref, oh, ow = E.space_to_depth(_post_fetch_reference(x).cuda(), r, r, pad)
+    for xin in (x.cuda(), x.cuda().contiguous(memory_format=torch.channels_last)):
+        got, oh2, ow2 = E.space_to_depth_u8(xin, r, r, pad)
+        assert (oh2, ow2) == (oh, ow) and got.c == ref.c
+        assert torch.equal(got.t.view(torch.int16), ref.t.view(torch.int16))
+
+
+def test_models_take_uint8_batches(P):
+    """post_fetch_fn drop-in: uint8 images + uint8 masks give the logits / loss of the float + int64 path exactly
+    (eval mode: no batch-statistics atomics, so the forward is bit-reproducible)."""
+    from pytorch_segmentation_b200.utils.utils import post_fetch_fn
+    g = torch.Generator().manual_seed(5)
+    x8 = torch.randint(0, 256, (2, 3, 128, 160), generator=g, dtype=torch.uint8)
+    t8 = torch.randint(0, 7, (2, 128, 160), generator=g, dtype=torch.uint8)
+    xf = _post_fetch_reference(x8).cuda()
+    for ctor in (P.DeepLabV3Plus, P.UNet, lambda nc: P.HRNet(nc)):
+        torch.manual_seed(3)
+        m = ctor(7).cuda().eval()
+        imgs, segs = post_fetch_fn((x8.cuda(), t8.cuda()))
+        with torch.no_grad():
+            y8 = m(imgs)
+            l8 = P.compute_loss(y8, segs, m)
+            yf = m(xf)
+            lf = P.compute_loss(yf, t8.cuda().long(), m)
+        assert torch.equal(y8, yf), ctor
+        assert abs(float(l8) - float(lf)) <= 1e-6 * abs(float(lf))
+
+
+@pytest.mark.parametrize('dtype', [torch.uint8, torch.int32])
+def test_narrow_targets_equal_int64(P, E, dtype):
+    g = torch.Generator().manual_seed(11)
+    n, nc, h, w = 2, 21, 96, 128
+    logits = torch.randn(n, nc, h, w, generator=g).cuda()
+    t64 = torch.randint(0, nc, (n, h, w), generator=g).cuda()
+    tn = t64.to(dtype)
+    # logits path
+    la, lb = logits.clone().requires_grad_(True), logits.clone().requires_grad_(True)
+    a, b = P.compute_loss(la, t64, None), P.compute_loss(lb, tn, None)
+    a.backward()
+    b.backward()
+    assert abs(float(a) - float(b)) <= 1e-6 * abs(float(a)) and torch.equal(la.grad, lb.grad)
+    assert torch.equal(E.argmax_confusion(logits, t64), E.argmax_confusion(logits, tn))
+    pred = E.argmax(logits)
+    assert torch.equal(E.confusion(pred.reshape(-1), t64.reshape(-1), nc), E.confusion(pred.reshape(-1), tn.reshape(-1), nc))
+    # class-map path
+    lr = torch.randn(n, h // 4, w // 4, 24, generator=g).cuda()
+    acc64, accn = E.lowres_ce_fwd(lr, nc, t64), E.lowres_ce_fwd(lr, nc, tn)
+    assert abs(float(acc64[0]) - float(accn[0])) <= 1e-9 * abs(float(acc64[0]))
+    assert torch.equal(acc64[1:2].view(torch.int64), accn[1:2].view(torch.int64))
+    with pytest.raises(RuntimeError):
+        P.compute_loss(logits, t64.to(torch.int16), None)
+
+
+# ---------------------------------------------------------------------------------------------------
+# a9 / a13: evaluation from the class map
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('n,h,w,up,nc,ct', [(2, 37, 41, 4, 21, 24), (3, 40, 24, 2, 2, 8), (16, 128, 128, 4, 21, 24)])
+def test_class_map_confusion_bit_exact(E, n, h, w, up, nc, ct):
+    g = torch.Generator().manual_seed(n + h)
+    lr = torch.randn(n, h, w, ct, generator=g).cuda()
+    tgt = torch.randint(0, nc, (n, h * up, w * up), generator=g).cuda()
+    logits = E.logits_upsample_fwd(lr, nc, h * up, w * up)
+    want_cm = E.argmax_confusion(logits, tgt)
+    cm, pred = E.class_map_confusion(lr, nc, tgt, True, want_pred=True)
+    assert torch.equal(pred, E.argmax(logits))
+    assert torch.equal(pred, logits.max(1)[1])               # outputs.max(1)[1] of test.py:31
+    assert torch.equal(cm, want_cm) and int(cm.sum()) == tgt.numel()
+    # accumulates into a caller's matrix; wrong-sized matrices are refused
+    cm2, _ = E.class_map_confusion(lr, nc, tgt.to(torch.uint8), True, cm=cm.clone())
+    assert torch.equal(cm2, 2 * want_cm)
+    with pytest.raises(ValueError):
+        E.class_map_confusion(lr, nc, tgt, True, cm=torch.zeros((nc + 1, nc + 1), dtype=torch.int64, device='cuda'))
+
+
+def test_class_map_confusion_tie_rule(E):
+    """Ties go to the LOWEST class index (the first maximum, like ``outputs.max(1)[1]`` on the written logits): integer
+    class maps interpolate to exact ties at every cell centre and along every edge between equal cells."""
+    n, h, w, nc, ct = 2, 9, 11, 5, 8
+    g = torch.Generator().manual_seed(0)
+    lr = torch.randint(0, 2, (n, h, w, ct), generator=g).float().cuda()       # values in {0, 1}: ties everywhere
+    tgt = torch.randint(0, nc, (n, h * 4, w * 4), generator=g).cuda()
+    logits = E.logits_upsample_fwd(lr, nc, h * 4, w * 4)
+    cm, pred = E.class_map_confusion(lr, nc, tgt, True, want_pred=True)
+    assert torch.equal(pred, logits.max(1)[1]) and torch.equal(pred, E.argmax(logits))
+    ties = (logits == logits.max(1, keepdim=True)[0]).sum(1) > 1
+    assert float(ties.float().mean()) > 0.2                      # the case really is exercised
+    first = (logits == logits.max(1, keepdim=True)[0]).float().argmax(1)
+    assert torch.equal(pred, first)
+    zero = torch.zeros(n, h, w, ct, device='cuda')
+    _, p0 = E.class_map_confusion(zero, nc, tgt, True, want_pred=True)
+    assert int(p0.abs().sum()) == 0                              # all classes tie -> class 0
+
+
+def test_test_loop_uses_the_class_map(P, E, monkeypatch):
+    """test(model, fetcher) (test.py:14-73) on a DeepLabV3+ head: the prediction comes from the class map (no pass over
+    the logits) and mIoU equals the logits path's bit for bit."""
+    torch.manual_seed(2)
+    nc = 6
+    m = P.DeepLabV3Plus(nc).cuda().eval()
+    g = torch.Generator().manual_seed(4)
+    batches = [(torch.randn(2, 3, 128, 128, generator=g).cuda(), torch.randint(0, nc, (2, 128, 128), generator=g).cuda())
+               for _ in range(2)]
+
+    class F:
+        def __init__(self, b):
+            self.b = b
+            self.loader = type('L', (), {})()
+            self.loader.dataset = type('D', (), {'classes': ['c%d' % i for i in range(nc)]})()
+
+        def __iter__(self):
+            return iter(self.b)
+
+    calls = {'cm': 0, 'logits': 0}
+    real_cm, real_lg = E.class_map_confusion, E.argmax_confusion
+    monkeypatch.setattr(E, 'class_map_confusion', lambda *a, **k: (calls.__setitem__('cm', calls['cm'] + 1), real_cm(*a, **k))[1])
+    monkeypatch.setattr(E, 'argmax_confusion', lambda *a, **k: (calls.__setitem__('logits', calls['logits'] + 1), real_lg(*a, **k))[1])
+    miou_fused = P.test(m, F(batches), verbose=False)
+    assert calls == {'cm': 2, 'logits': 0}
+    monkeypatch.setattr(E, 'LOWRES_CE', False)
+
+    class Untag(torch.nn.Module):
+        def __init__(self, inner):
+            super().__init__()
+            self.inner = inner
+
+        def forward(self, x):
+            return self.inner(x).clone()                      # a fresh tensor carries no class-map tag
+
+    miou_logits = P.test(Untag(m), F(batches), verbose=False)
+    assert calls['logits'] == 2
+    assert miou_fused == miou_logits
+    with pytest.raises(ValueError):
+        bad = F(batches)
+        bad.loader.dataset.classes = ['a', 'b']
+        P.test(m, bad, verbose=False)
+
+
+# ---------------------------------------------------------------------------------------------------
+# f3: Adam / AdamW, hyper-parameters under the graph, accumulation
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('name,kw', [('AdamW', dict(lr=3e-3, weight_decay=0.05)), ('Adam', dict(lr=3e-3, weight_decay=0.01)),
+                                     ('AdamW', dict(lr=1e-2, betas=(0.8, 0.95), eps=1e-6, weight_decay=0.0))])
+def test_adam_multi_matches_torch(P, name, kw):
+    g = torch.Generator().manual_seed(1)
+    shapes = [(64, 3, 7, 7), (256,), (33, 17), (1,), (2048, 256, 1, 1), (5, 8, 3, 3)]
+    ps = [torch.randn(s, generator=g).cuda() for s in shapes]
+    ps[0] = ps[0].contiguous(memory_format=torch.channels_last)
+    a = [p.clone().requires_grad_(True) for p in ps]
+    b = [p.clone().requires_grad_(True) for p in ps]
+    oa = getattr(P.optim, name)(a, **kw)
+    ob = getattr(torch.optim, name)(b, **kw)
+    for step in range(5):
+        if step == 3:                                  # a schedule moving the learning rate
+            for o in (oa, ob):
+                o.param_groups[0]['lr'] *= 0.5
+        for x, y in zip(a, b):
+            gr = torch.randn(x.shape, generator=g).cuda()
+            x.grad = gr.clone().contiguous(memory_format=torch.channels_last) if x.dim() == 4 and x.shape == (64, 3, 7, 7) else gr.clone()
+            y.grad = x.grad.clone()
+        oa.step()
+        ob.step()
+        for x, y in zip(a, b):
+            assert float((x - y).abs().max()) <= 2e-6 * max(1.0, float(y.abs().max())), (name, step, tuple(x.shape))
+    sa, sb = oa.state_dict()['state'], ob.state_dict()['state']
+    assert set(sa[0]) >= {'step', 'exp_avg', 'exp_avg_sq'} and float(sa[0]['step']) == float(sb[0]['step']) == 5
+    assert float((sa[4]['exp_avg_sq'] - sb[4]['exp_avg_sq']).abs().max()) <= 1e-6 * float(sb[4]['exp_avg_sq'].abs().max())
+
+
+def _params(m):
+    return torch.cat([p.detach().flatten() for p in m.parameters()]).clone()
+
+
+def test_graph_replay_follows_param_groups(P):
+    """The captured step reads lr / momentum / weight decay from the device at replay time: lr = 0 freezes the
+    parameters exactly, restoring it resumes training, and the momentum path is the steady-state one (a step captured
+    on the first-step path would reset the momentum buffer every replay)."""
+    torch.manual_seed(5)
+    m = P.DeepLabV3Plus(4).cuda().train()
+    opt = P.optim.SGD(m.parameters(), lr=1e-2, momentum=0.9)
+    s = P.TrainStep(m, opt, graph=True, warmup=1)
+    with pytest.raises(ValueError):
+        P.TrainStep(m, opt, graph=True, warmup=0)
+    x, t = torch.randn(2, 3, 64, 64).cuda(), torch.randint(0, 4, (2, 64, 64)).cuda()
+    s(x, t)                     # eager warm-up
+    s(x, t)                     # capture + replay
+    p0 = _params(m)
+    s(x, t)
+    p1 = _params(m)
+    assert float((p1 - p0).abs().max()) > 0
+    opt.param_groups[0]['lr'] = 0.0
+    s(x, t)
+    p2 = _params(m)
+    assert torch.equal(p2, p1)                          # the replay saw lr = 0
+    buf = opt.state[m.cls_conv.weight]['momentum_buffer'].clone()
+    s(x, t)
+    buf2 = opt.state[m.cls_conv.weight]['momentum_buffer']
+    assert not torch.equal(buf, buf2)                   # momentum keeps integrating: m = 0.9 m + g, not m = g
+    grad = m.cls_conv.weight.grad
+    assert float((buf2 - (0.9 * buf + grad)).abs().max()) <= 1e-5 * max(1.0, float(buf2.abs().max()))
+    opt.param_groups[0]['lr'] = 1e-2
+    s(x, t)
+    assert float((_params(m) - p2).abs().max()) > 0
+    # eval after the replays reads the CURRENT weights (packed bf16 copies refreshed): a fresh model given the same
+    # state dict must produce the same logits
+    m.eval()
+    fresh = P.DeepLabV3Plus(4).cuda().eval()
+    fresh.load_state_dict(m.state_dict())
+    with torch.no_grad():
+        assert torch.equal(m(x), fresh(x))
+
+
+def test_adamw_under_graph_advances_its_step_count(P):
+    torch.manual_seed(6)
+    m = P.DeepLabV3Plus(3).cuda().train()
+    m2 = copy.deepcopy(m)
+    kw = dict(lr=1e-3, weight_decay=0.01)
+    sg = P.TrainStep(m, P.optim.AdamW(m.parameters(), **kw), graph=True, warmup=1)
+    se = P.TrainStep(m2, P.optim.AdamW(m2.parameters(), **kw), graph=False)
+    x, t = torch.randn(2, 3, 64, 64).cuda(), torch.randint(0, 3, (2, 64, 64)).cuda()
+    init = _params(m)
+    for _ in range(5):
+        sg(x, t)
+        se(x, t)
+    assert int(sg.optimizer.param_groups[0]['_b200seg_step']) == int(se.optimizer.param_groups[0]['_b200seg_step']) == 5
+    ug, ue = _params(m) - init, _params(m2) - init
+    # Adam's early steps move every weight by ~lr whatever the gradient scale: the two runs agree to the run-to-run noise
+    assert float((ug - ue).norm()) <= 0.05 * float(ue.norm()), (float((ug - ue).norm()), float(ue.norm()))
+
+
+@pytest.mark.parametrize('graph', [False, True])
+def test_gradient_accumulation(P, graph):
+    """accumulate=2 (train.py:94's default): the optimizer steps on every second call with the mean of the two
+    micro-batches' gradients; compared with the same sequence written out by hand on a copy of the model."""
+    torch.manual_seed(8)
+    nc = 4
+    m = P.DeepLabV3Plus(nc).cuda().train()
+    m_ref = copy.deepcopy(m)
+    opt = P.optim.SGD(m.parameters(), lr=1e-2, momentum=0.9)
+    opt_ref = P.optim.SGD(m_ref.parameters(), lr=1e-2, momentum=0.9)
+    s = P.TrainStep(m, opt, graph=graph, warmup=1, accumulate=2)
+    g = torch.Generator().manual_seed(1)
+    data = [(torch.randn(2, 3, 64, 64, generator=g).cuda(), torch.randint(0, nc, (2, 64, 64), generator=g).cuda())
+            for _ in range(8)]
+    init = _params(m)
+    for i in range(0, 8, 2):
+        before = _params(m)
+        r1 = s(*data[i])
+        assert torch.equal(_params(m), before), 'no update on the first micro-batch'
+        r2 = s(*data[i + 1])
+        assert float((_params(m) - before).abs().max()) > 0
+        assert r2 is not None and bool(torch.isfinite(r2))
+        if graph and i >= 2:
+            assert r1 is None                                  # staging call of the captured 2-micro-step graph
+        opt_ref.zero_grad(set_to_none=True)
+        for x, t in data[i:i + 2]:
+            (P.compute_loss(m_ref(x), t, m_ref) * 0.5).backward()
+        opt_ref.step()
+    u, u_ref = _params(m) - init, _params(m_ref) - init
+    assert float((u - u_ref).norm()) <= 0.05 * float(u_ref.norm()), (float((u - u_ref).norm()), float(u_ref.norm()))
+    bn = m.aspp.project[1]
+    assert int(bn.num_batches_tracked) == 8
