@@ -126,7 +126,8 @@ int b200seg_sgd_multi(const b200seg_sgd_desc* descs, int n, float lr, float mome
 /* Adam / AdamW for all parameters in one launch per 64 tensors (train.py:96 ``--adam``; torch.optim.Adam(W), amsgrad off):
  *   g' = grad_scale*g (+ weight_decay*p if !decoupled);  decoupled: p *= 1 - lr*weight_decay
  *   m += (1-beta1)*(g'-m);  v = beta2*v + (1-beta2)*g'^2;  p -= (lr/bc1) * m / (sqrt(v)/sqrt_bc2 + eps)
- * hyper = DEVICE vector {lr, beta1, beta2, eps, weight_decay, grad_scale, bc1 = 1-beta1^t, sqrt_bc2 = sqrt(1-beta2^t)}.
+ * hyper = DEVICE vector of 11 floats {lr, beta1, beta2, eps, weight_decay, grad_scale, lr/(1-beta1^t), sqrt(1-beta2^t),
+ * 1-beta1, 1-beta2, 1-lr*weight_decay} (derived entries formed by the host in double precision).
  * first_step: m and v are not read (treated as zero). */
 typedef struct b200seg_adam_desc {
     float* p;
@@ -358,6 +359,12 @@ int b200seg_resize_nchw_fwd(const float* x, int64_t planes, int h, int w, float*
                             b200seg_stream_t st);
 int b200seg_resize_nchw_bwd(const float* dy, int64_t planes, int oh, int ow, float* dx, int h, int w, int align_corners,
                             b200seg_stream_t st);
+/* Measurement aids (bench.py roofline.flops_executed): pipeline iterations of the launches made by this thread's last
+ * b200seg_conv_fprop / _dgrad call — run, and what the same tiling runs with no all-padding (tap, tile) skipped; the
+ * same pair for a weight-gradient descriptor.  nominal FLOPs x run / dense = FLOPs the tensor pipe was asked for. */
+int b200seg_conv_last_plan(int64_t* iters_run, int64_t* iters_dense);
+int b200seg_conv_wgrad_plan_info(const b200seg_wgrad_desc* d, int64_t* iters_run, int64_t* iters_dense);
+
 /* Target masks: int64 is what the reference's post_fetch_fn hands on (``segs.long()``, utils/datasets.py:213); uint8 is
  * what BasicDataset.__getitem__ yields before that cast (utils/datasets.py:161-194) and int32 a common intermediate —
  * every function below that takes ``targets`` reads any of the three directly (target_kind), so the 8x wider copy need

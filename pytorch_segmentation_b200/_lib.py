@@ -85,6 +85,8 @@ PROTOTYPES = {
     'b200seg_conv_fprop': (c_int, [_I, _I, _I, _I, POINTER(ConvSrc), POINTER(ConvOut), _P]),
     'b200seg_conv_dgrad': (c_int, [_I, _I, _I, _I, POINTER(ConvSrc), POINTER(ConvOut), _P]),
     'b200seg_conv_wgrad_workspace': (c_size_t, [POINTER(WgradDesc)]),
+    'b200seg_conv_last_plan': (c_int, [POINTER(c_int64), POINTER(c_int64)]),
+    'b200seg_conv_wgrad_plan_info': (c_int, [POINTER(WgradDesc), POINTER(c_int64), POINTER(c_int64)]),
     'b200seg_conv_wgrad': (c_int, [POINTER(WgradDesc), _P]),
     'b200seg_bn_stats': (c_int, [_P, _I, _I, _I, _L, _P, _P]),
     'b200seg_bn_finalize': (c_int, [_P, _I, _L, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P]),

@@ -14,7 +14,7 @@ import torch
 import torch.nn as nn
 import torchvision
 
-from .resnet import load_pretrained, resnet50  # noqa: F401  (re-exported: models/deeplabv3plus.py imports it from here)
+from .resnet import find_pretrained, load_pretrained, resnet50  # noqa: F401  (re-exported: models/deeplabv3plus.py imports it from here)
 from .utils.utils import model_input
 
 
@@ -40,10 +40,8 @@ class _MobileNetV2Features(nn.Module):
 
 
 def mobilenet_v2(pretrained=False, **kw):
-    net = _MobileNetV2Features(torchvision.models.mobilenet_v2(weights=None))
-    if pretrained:
-        # the torchvision checkpoint is keyed features.<i>...: load it into an unsplit copy, the stages share its modules
-        full = torchvision.models.mobilenet_v2(weights=None)
-        if load_pretrained(full, 'mobilenet_v2', 'mobilenet_v2-b0353104.pth'):
-            net = _MobileNetV2Features(full)
-    return net.to(memory_format=torch.channels_last)
+    full = torchvision.models.mobilenet_v2(weights=None)
+    if pretrained and find_pretrained('mobilenet_v2', 'mobilenet_v2-b0353104.pth'):
+        # the torchvision checkpoint is keyed features.<i>...: load it into the unsplit net, the stages share its modules
+        load_pretrained(full, 'mobilenet_v2', 'mobilenet_v2-b0353104.pth')
+    return _MobileNetV2Features(full).to(memory_format=torch.channels_last)

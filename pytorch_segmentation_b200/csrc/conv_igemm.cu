@@ -85,6 +85,11 @@ struct __align__(64) IgemmParams {
 long long* g_dbg = nullptr;
 int g_dbg_slots = 0;
 
+// Pipeline iterations ((tap, 64-channel block, tile) triples) of the launches made by the last conv_fprop / conv_dgrad
+// call of this thread: those actually run, and what the same tiling would run with no all-padding tap skipped.  Their
+// ratio turns nominal FLOPs (padding taps counted) into executed FLOPs (bench.py, roofline.frac_executed).
+thread_local long long g_iters_run = 0, g_iters_dense = 0;
+
 __device__ __forceinline__ long long gtime() {
     long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -543,7 +548,7 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
     long long best = -1;
     {
         static std::mutex mu;
-        static std::map<std::vector<int>, std::array<int, 3>> memo;
+        static std::map<std::vector<int>, std::array<long long, 5>> memo;
         std::vector<int> key = {n, h, w, nseg, p.no_skip};
         for (int i = 0; i < nseg; ++i) {
             key.push_back(p.seg[i].ntaps);
@@ -553,10 +558,12 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
         std::lock_guard<std::mutex> lock(mu);
         auto it = memo.find(key);
         if (it != memo.end()) {
-            p.bw = it->second[0];
-            p.bh = it->second[1];
-            p.bi = it->second[2];
+            p.bw = static_cast<int>(it->second[0]);
+            p.bh = static_cast<int>(it->second[1]);
+            p.bi = static_cast<int>(it->second[2]);
             best = 1;
+            g_iters_run += it->second[3];
+            g_iters_dense += it->second[4];
         } else {
             for (int bi = 1; bi <= 128; bi *= 2) {
                 for (int bw = 1; bw * bi <= 128; bw *= 2) {
@@ -570,7 +577,12 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
                     }
                 }
             }
-            if (best > 0) memo[key] = {p.bw, p.bh, p.bi};
+            if (best > 0) {
+                const long long dense = patch_cost(n, h, w, p.bw, p.bh, p.bi, nseg, sp, true);
+                memo[key] = {p.bw, p.bh, p.bi, best, dense};
+                g_iters_run += best;
+                g_iters_dense += dense;
+            }
         }
     }
     B200SEG_CHECK(best > 0, "conv: no tile shape for %dx%dx%d", n, h, w);
@@ -879,13 +891,21 @@ int b200seg_debug_timing(int64_t* buf, int slots) {
     return 0;
 }
 
+int b200seg_conv_last_plan(int64_t* iters_run, int64_t* iters_dense) {
+    if (iters_run) *iters_run = b200seg::g_iters_run;
+    if (iters_dense) *iters_dense = b200seg::g_iters_dense;
+    return 0;
+}
+
 int b200seg_conv_fprop(int n, int h, int w, int n_src, const b200seg_conv_src* src, const b200seg_conv_out* out,
                        b200seg_stream_t st) {
+    b200seg::g_iters_run = b200seg::g_iters_dense = 0;
     return b200seg::launch_fprop(n, h, w, n_src, src, out, static_cast<cudaStream_t>(st));
 }
 
 int b200seg_conv_dgrad(int n, int h, int w, int n_src, const b200seg_conv_src* src, const b200seg_conv_out* out,
                        b200seg_stream_t st) {
+    b200seg::g_iters_run = b200seg::g_iters_dense = 0;
     return b200seg::launch_dgrad(n, h, w, n_src, src, out, static_cast<cudaStream_t>(st));
 }
 

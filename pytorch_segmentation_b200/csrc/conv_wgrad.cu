@@ -317,6 +317,7 @@ bool tap_grouping_enabled() {
 struct WgradPlan {
     int shift_m, bw, bh, bi, patches_x, patches_y, patches_i, tiles_m, tiles_n, bn, splits, pps, m_pad, n_pad, tap_group;
     size_t ws_bytes;
+    long long iters_run, iters_dense;      // (tap, patch) pairs with / without the all-padding ones skipped
 };
 
 int plan_wgrad_uncached(const b200seg_wgrad_desc* d, WgradPlan* pl) {
@@ -383,6 +384,8 @@ int plan_wgrad_uncached(const b200seg_wgrad_desc* d, WgradPlan* pl) {
     }
     B200SEG_CHECK(best > 0, "wgrad: no patch shape");
     const int patches = pl->patches_x * pl->patches_y * pl->patches_i;
+    pl->iters_run = best;
+    pl->iters_dense = static_cast<long long>(patches) * d->r * d->s;
     // tap groups: with X on the N side and a single narrow n-tile, several taps share one CTA (and one load of dY)
     const int taps = d->r * d->s;
     pl->tap_group = 1;
@@ -430,6 +433,16 @@ int plan_wgrad(const b200seg_wgrad_desc* d, WgradPlan* pl) {
 }  // namespace b200seg
 
 extern "C" {
+
+int b200seg_conv_wgrad_plan_info(const b200seg_wgrad_desc* d, int64_t* iters_run, int64_t* iters_dense) {
+    b200seg::clear_error();
+    b200seg::WgradPlan pl;
+    memset(&pl, 0, sizeof(pl));
+    if (b200seg::plan_wgrad(d, &pl)) return 1;
+    if (iters_run) *iters_run = pl.iters_run;
+    if (iters_dense) *iters_dense = pl.iters_dense;
+    return 0;
+}
 
 size_t b200seg_conv_wgrad_workspace(const b200seg_wgrad_desc* d) {
     b200seg::WgradPlan pl;

@@ -106,9 +106,10 @@ __global__ void __launch_bounds__(256) sgd_multi_kernel(const __grid_constant__ 
 //   g' = grad_scale * g  (+ weight_decay * p when the decay is coupled: Adam)
 //   decoupled (AdamW):  p *= 1 - lr * weight_decay
 //   m = m + (1 - beta1) * (g' - m) ;  v = beta2 * v + (1 - beta2) * g'^2
-//   p -= (lr / bc1) * m / (sqrt(v) / sqrt(bc2) + eps)          bc_i = 1 - beta_i^step  (host-computed)
-// hyper = {lr, beta1, beta2, eps, weight_decay, grad_scale, bc1, sqrt(bc2)} lives in DEVICE memory so a CUDA-graph
-// replay sees this step's learning rate and bias corrections.
+//   p -= (lr / bc1) * m / (sqrt(v) / sqrt(bc2) + eps)          bc_i = 1 - beta_i^step
+// hyper = {lr, beta1, beta2, eps, weight_decay, grad_scale, lr/bc1, sqrt(bc2), 1-beta1, 1-beta2, 1-lr*weight_decay}
+// lives in DEVICE memory so a CUDA-graph replay sees this step's learning rate and bias corrections; the derived
+// entries are formed on the host in double precision like torch.optim's Python scalars (1 - 0.999 in fp32 is off by 1e-5).
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int kAdamTensors = 64;
 
@@ -121,19 +122,19 @@ struct AdamChunk {
 };
 
 struct AdamHyper {
-    float lr, beta1, beta2, eps, wd, gs, bc1, sbc2;
+    float lr, beta1, beta2, eps, wd, gs, step_size, sbc2, omb1, omb2, decay;
 };
 
 __device__ __forceinline__ float adam_one(float p, float g, float* m, float* v, const AdamHyper& h, bool decoupled) {
     g *= h.gs;
-    if (decoupled) p = p * (1.f - h.lr * h.wd);
+    if (decoupled) p = p * h.decay;
     else g = fmaf(h.wd, p, g);
-    const float mm = fmaf(1.f - h.beta1, g - *m, *m);
-    const float vv = fmaf(h.beta2, *v, (1.f - h.beta2) * g * g);
+    const float mm = fmaf(h.omb1, g - *m, *m);
+    const float vv = fmaf(h.beta2, *v, h.omb2 * g * g);
     *m = mm;
     *v = vv;
     const float denom = __fdiv_rn(__fsqrt_rn(vv), h.sbc2) + h.eps;
-    return p - __fdiv_rn(h.lr, h.bc1) * __fdiv_rn(mm, denom);
+    return p - h.step_size * __fdiv_rn(mm, denom);
 }
 
 __global__ void __launch_bounds__(256) adam_multi_kernel(const __grid_constant__ AdamChunk c) {
@@ -148,7 +149,8 @@ __global__ void __launch_bounds__(256) adam_multi_kernel(const __grid_constant__
     const int64_t end = begin + kSgdElemsPerBlock < t.numel ? begin + kSgdElemsPerBlock : t.numel;
     AdamHyper h;
     h.lr = __ldg(c.hyper + 0); h.beta1 = __ldg(c.hyper + 1); h.beta2 = __ldg(c.hyper + 2); h.eps = __ldg(c.hyper + 3);
-    h.wd = __ldg(c.hyper + 4); h.gs = __ldg(c.hyper + 5); h.bc1 = __ldg(c.hyper + 6); h.sbc2 = __ldg(c.hyper + 7);
+    h.wd = __ldg(c.hyper + 4); h.gs = __ldg(c.hyper + 5); h.step_size = __ldg(c.hyper + 6); h.sbc2 = __ldg(c.hyper + 7);
+    h.omb1 = __ldg(c.hyper + 8); h.omb2 = __ldg(c.hyper + 9); h.decay = __ldg(c.hyper + 10);
     const bool dec = c.decoupled != 0, first = c.first != 0;
     float* p = t.p;
     const float* g = t.g;
@@ -367,7 +369,7 @@ int b200seg_adam_multi(const b200seg_adam_desc* descs, int n, const float* hyper
     using namespace b200seg;
     clear_error();
     B200SEG_CHECK(descs && n > 0, "adam_multi: no tensors");
-    B200SEG_CHECK(hyper, "adam_multi: the hyper-parameter vector lives in device memory (8 floats)");
+    B200SEG_CHECK(hyper, "adam_multi: the hyper-parameter vector lives in device memory (11 floats)");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     for (int base = 0; base < n;) {
         AdamChunk c;

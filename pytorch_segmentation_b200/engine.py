@@ -501,7 +501,15 @@ def _conv(fn, what, n, h, w, srcs, out_ptr, y_ct, y_off, k, out_fp32, scale, bia
         ev0.record()
         _conv_launch(fn, what, n, h, w, srcs, out_ptr, y_ct, y_off, k, out_fp32, scale, bias, relu, stats)
         ev1.record()
-        PROFILE.append((tag, flops, ev0, ev1))
+        run, dense = ctypes.c_int64(0), ctypes.c_int64(0)
+        _lib.load().b200seg_conv_last_plan(ctypes.byref(run), ctypes.byref(dense))
+        # algorithmic bytes: every input slice once + the output slice + every packed weight once
+        nbytes = n * h * w * k * (4 if out_fp32 else 2)
+        for x, _, w_rows, r, s, _, st in srcs:
+            px = x.pixels if not isinstance(x, WindowAct) else x.t.numel() // max(x.ct, 1)
+            nbytes += 2 * px * min(x.c, x.ct) + 2 * r * s * w_rows * x.c
+        PROFILE.append((tag, flops, ev0, ev1, {'bytes': float(nbytes),
+                                               'run_share': run.value / dense.value if dense.value else 1.0}))
         return
     _conv_launch(fn, what, n, h, w, srcs, out_ptr, y_ct, y_off, k, out_fp32, scale, bias, relu, stats)
 
@@ -649,9 +657,14 @@ def _conv_wgrad(dy, x, k_out, r, s, dil, dw=None, stride=1):
     _lib.check(lib.b200seg_conv_wgrad(ctypes.byref(desc), _stream()), 'conv_wgrad')
     if PROFILE is not None:
         ev1.record()
+        run, dense = ctypes.c_int64(0), ctypes.c_int64(0)
+        lib.b200seg_conv_wgrad_plan_info(ctypes.byref(desc), ctypes.byref(run), ctypes.byref(dense))
+        px = x.pixels if not isinstance(x, WindowAct) else x.t.numel() // max(x.ct, 1)
         PROFILE.append(('conv_wgrad %dx%dx%d k%d c%d r%d d%d%s' % (dy.n, dy.h, dy.w, dy.c, x.c, r, dil,
                                                                    ' s2' if stride == 2 else ''),
-                        2.0 * dy.pixels * dy.c * (getattr(x, 'algo_k', None) or x.c * r * s), ev0, ev1))
+                        2.0 * dy.pixels * dy.c * (getattr(x, 'algo_k', None) or x.c * r * s), ev0, ev1,
+                        {'bytes': 2.0 * dy.pixels * dy.c + 2.0 * px * min(x.c, x.ct) + 4.0 * k_out * x.c * r * s,
+                         'run_share': run.value / dense.value if dense.value else 1.0}))
     _lib.count_launch(2)
     return dw
 
@@ -1201,6 +1214,21 @@ def class_map_confusion(lr, nc, targets, align_corners=True, cm=None, want_pred=
 OP_PROFILE = None
 
 
+def _act_bytes(a):
+    return 2.0 * a.pixels * a.c if isinstance(a, Act) else 0.0
+
+
+# algorithmic HBM bytes of the BatchNorm-family passes ("BN apply: 2 x tensor bytes"; backward = the two
+# passes' reads of dy and x plus the dx write; the residual join reads what it is given and rewrites dx)
+_OP_BYTES = {
+    'bn_apply': lambda a, kw: _act_bytes(a[0]) * (2 + (kw.get('res') is not None or (len(a) > 4 and a[4] is not None))),
+    'bn_backward': lambda a, kw: _act_bytes(a[1]) * 5,
+    'grad_add_masked': lambda a, kw: _act_bytes(a[0]) * (2 + sum(1 for v in list(a[1:3]) + [kw.get('dy'), kw.get('y')]
+                                                                 if v is not None)
+                                                         + (1.0 / 16 if (kw.get('xin') if 'xin' in kw else (a[3] if len(a) > 3 else None)) is not None else 0)),
+}
+
+
 def _timed(name, fn):
     def wrapper(*a, **kw):
         if OP_PROFILE is None:
@@ -1212,7 +1240,8 @@ def _timed(name, fn):
         act = next((v for v in a if isinstance(v, Act)), None)
         tag = name if act is None else '%s %dx%dx%dx%d%s' % (name, act.n, act.h, act.w, act.c,
                                                             ' masked' if kw.get('mask') is not None else '')
-        OP_PROFILE.append((tag, e0, e1))
+        nbytes = _OP_BYTES[name](a, kw) if name in _OP_BYTES else 0.0
+        OP_PROFILE.append((tag, e0, e1, nbytes))
         return out
     wrapper.__name__, wrapper.__doc__ = fn.__name__, fn.__doc__
     return wrapper

@@ -38,7 +38,7 @@ def _check_param(name, p, g):
 
 class _HyperMixin:
     """Per param-group device vector of hyper-parameters + its pinned host mirror."""
-    HYPER_LEN = 8
+    HYPER_LEN = 12
 
     def _hyper(self, gi, device):
         store = self.__dict__.setdefault('_hyper_store', {})
@@ -155,8 +155,10 @@ class Adam(_HyperMixin, torch.optim.Optimizer):
                     st['step'] += 1
         t = max(int(group.get('_b200seg_step', 0)), 1)
         b1, b2 = group['betas']
-        return [float(group['lr']), float(b1), float(b2), float(group['eps']), float(group['weight_decay']),
-                float(group.get('grad_scale', 1.0)), 1.0 - b1 ** t, math.sqrt(1.0 - b2 ** t)]
+        lr, wd = float(group['lr']), float(group['weight_decay'])
+        # derived scalars in double precision, as torch.optim forms them in Python before they meet an fp32 tensor
+        return [lr, float(b1), float(b2), float(group['eps']), wd, float(group.get('grad_scale', 1.0)),
+                lr / (1.0 - b1 ** t), math.sqrt(1.0 - b2 ** t), 1.0 - b1, 1.0 - b2, 1.0 - lr * wd]
 
     @torch.no_grad()
     def step(self, closure=None):

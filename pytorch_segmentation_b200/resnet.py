@@ -320,23 +320,31 @@ def load_pretrained(module, arch, filename):
     weights.  There is no network here, so the torchvision checkpoint is taken from a local file — ``$B200SEG_PRETRAINED_DIR``
     or the torch hub cache (``<hub>/checkpoints/<filename>``) — and when none exists the backbone stays randomly
     initialised WITH A WARNING (never silently)."""
+    path = find_pretrained(arch, filename)
+    if path is None:
+        return False
+    state = torch.load(path, map_location='cpu', weights_only=True)
+    own = module.state_dict()
+    missing = [k for k in own if k not in state]
+    if missing:
+        raise RuntimeError('%s: %s lacks %d tensors (e.g. %s)' % (arch, path, len(missing), missing[0]))
+    module.load_state_dict({k: state[k] for k in own})
+    return True
+
+
+def find_pretrained(arch, filename):
+    """Path of the local checkpoint, or None after warning that the backbone stays randomly initialised."""
     import os
     import warnings
     dirs = [os.environ.get('B200SEG_PRETRAINED_DIR'), os.path.join(torch.hub.get_dir(), 'checkpoints')]
     for d in dirs:
         path = os.path.join(d, filename) if d else None
         if path and os.path.exists(path):
-            state = torch.load(path, map_location='cpu', weights_only=True)
-            own = module.state_dict()
-            missing = [k for k in own if k not in state]
-            if missing:
-                raise RuntimeError('%s: %s lacks %d tensors (e.g. %s)' % (arch, path, len(missing), missing[0]))
-            module.load_state_dict({k: state[k] for k in own})
-            return True
+            return path
     warnings.warn('%s(pretrained=True): no local ImageNet checkpoint (%s under $B200SEG_PRETRAINED_DIR or %s) and no '
                   'network — the backbone is RANDOMLY INITIALISED, unlike the reference\'s' % (arch, filename, dirs[1]),
-                  RuntimeWarning, stacklevel=3)
-    return False
+                  RuntimeWarning, stacklevel=4)
+    return None
 
 
 def resnet50(pretrained=False, replace_stride_with_dilation=None, **kw):

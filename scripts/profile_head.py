@@ -58,7 +58,8 @@ def main():
     torch.cuda.synchronize()
     torch.cuda.cudart().cudaProfilerStop()
     rec, E.PROFILE = E.PROFILE, None
-    rows = [{'tag': tag, 'flops': flops, 'us_events': e0.elapsed_time(e1) * 1e3} for tag, flops, e0, e1 in rec]
+    rows = [{'tag': r[0], 'flops': r[1], 'us_events': r[2].elapsed_time(r[3]) * 1e3, 'run_share': r[4]['run_share'],
+             'bytes': r[4]['bytes']} for r in rec]
     if args.tags:
         json.dump(rows, open(args.tags, 'w'), indent=1)
     print('head step: loss %.5f, %d tcgen05 conv launches' % (float(loss), len(rows)))
