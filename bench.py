@@ -1,21 +1,33 @@
 #!/usr/bin/env python
-"""bench.py — train images/sec @512x512 of DeepLabV3+ (21 classes, bf16) on N B200s (BASELINE.json metric).
+"""bench.py — the BASELINE.json configurations of the pytorch_segmentation hot path on N B200s.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--batch B]
+  python bench.py [--config train|infer|aspp|hrnet|unet|unet_cpu] [--gpus N] [--steps K] [--warmup W]
+                  [--impl b200|reference] [--batch B]
 
-One step = forward + compute_loss + backward (+ bucketed gradient all-reduce for N > 1) + SGD update on one
-synthetic batch of B images per GPU (random-init weights, randn images, randint masks; per-rank seeds).
+  --config train (default; BASELINE configs[3], the headline): DeepLabV3+ 21-class 512x512 bf16 training.  One step =
+      forward + compute_loss + backward (+ bucketed gradient all-reduce for N > 1) + SGD update on one synthetic batch
+      of B images per GPU (random-init weights; per-rank seeds).  metric: train images/sec.
+  --config infer  (configs[1]): DeepLabV3+ 21-class 512x512 bf16 inference batch 16 incl. the mIoU confusion histogram
+      of test.py:28-46 (fused evaluation from the class map).
+  --config aspp   (configs[2]): the ASPP block isolated (2048-ch input, rates 6/12/18), forward + backward; the
+      fprop / dgrad / wgrad launches are listed separately in ``kernels``.
+  --config hrnet  (configs[4]): HRNet 19-class 1024x512 bf16 training, per-GPU batch 8.
+  --config unet   (configs[0] on the GPU): UNet 2-class 320x320 batch 4 training step.
+  --config unet_cpu (configs[0] as stated: CPU): the oracle's UNet 2-class 320x320 batch 4 fwd+bwd on the host cores.
+
 Launched by the driver as one process per GPU (torch.distributed.run) for N > 1.  Rank 0 prints ONE JSON line.
 
   value     whole-job images/sec with the step's inputs already resident in HBM
-  e2e       the same through the public API with HOST buffers: pinned-host -> device copies of the images and
-            masks and a device -> host read of the loss inside the timed region, every step
+  e2e       the same through the public API with HOST buffers: pinned-host -> device copies of the uint8 images and
+            masks (utils.post_fetch_fn drop-in: 1-byte pixels and labels) and a device -> host read of the loss inside the
+            timed region, every step
   roofline  the dominant kernel (tcgen05 implicit-GEMM conv, all fprop/dgrad launches of the step): nominal dense
             FLOPs (2*N*P*Q*K*C*R*S, padding taps counted — SURVEY.md §8d) / CUDA-event time, vs the measured bf16
-            peak in MEASURED_PEAKS.json
+            peak in MEASURED_PEAKS.json; ``flops_executed`` / ``frac_executed`` leave out the all-padding (tap, tile)
+            pairs the kernel skips; ``roofline_bn`` is the same for the HBM-bound BatchNorm family
   cpu_baseline / --impl reference
             the CPU oracle (oracle/restatement.py: the reference's own PyTorch calls, fp32) on the host cores on a
-            bounded sample (batch 2 per step) of the same workload
+            bounded sample of the same workload
 """
 import argparse
 import json
@@ -111,9 +123,56 @@ def cpu_reference_run(steps, warmup, batch=CPU_SAMPLE_BATCH):
     return batch / dt, dt, threads
 
 
+def cpu_model():
+    try:
+        for line in open('/proc/cpuinfo'):
+            if line.startswith('model name'):
+                return line.split(':', 1)[1].strip()
+    except OSError:
+        pass
+    return 'unknown'
+
+
+def cpu_unet_run(steps, warmup=1):
+    """BASELINE.md §4 "config 1 exactly": UNet(2).train(), randn(4,3,320,320) (seed 0), randint(0,2,(4,320,320)) (seed 1),
+    random init (seed 2), fwd + compute_loss + bwd, fp32, all host threads.  Returns (best s/step, median s/step, threads)."""
+    from oracle import restatement as R
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    model = R.OracleModel('unet', 2, seed=2).train()
+    x = torch.randn(4, 3, 320, 320, generator=torch.Generator().manual_seed(0))
+    t = torch.randint(0, 2, (4, 320, 320), generator=torch.Generator().manual_seed(1))
+    times = []
+    for i in range(warmup + steps):
+        model.zero_grad()
+        t0 = time.perf_counter()
+        loss = R.compute_loss(model(x), t)
+        loss.backward()
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    times.sort()
+    return times[0], times[len(times) // 2], threads
+
+
 def run_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
+        return
+    if args.config in ('unet', 'unet_cpu'):
+        steps = max(5, min(args.steps, 20))
+        best, med, threads = cpu_unet_run(steps, 1)
+        ips = 4 / med
+        line = {'impl': 'reference', 'metric': 'UNet 2-class 320x320 batch 4 fwd+bwd images/sec', 'value': ips,
+                'unit': 'images/sec', 'n_gpus': args.gpus, 'steps': steps, 'warmup': 1, 'ms_per_step': med * 1e3,
+                'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+                'config': {'workload': 'UNet 2-class 320x320 batch 4 fwd+compute_loss+bwd (BASELINE configs[0]); CPU oracle '
+                                       'port of the reference model code, fp32', 'per_step_batch': 4},
+                'cpu_baseline': {'value': ips, 'unit': 'images/sec', 'cores': threads, 'kind': 'port', 'cpu': cpu_model(),
+                                 'best_s_per_step': best, 'median_s_per_step': med,
+                                 'sample': 'config 1 exactly (BASELINE.md §4), 1 warm-up + %d timed steps; value = median' % steps},
+                'e2e': {'value': ips, 'unit': 'images/sec', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+                'gpu_launches': 0}
+        print(json.dumps(line), flush=True)
         return
     steps, warmup = max(1, min(args.steps, 20)), max(1, min(args.warmup, 2))
     ips, dt, threads = cpu_reference_run(steps, warmup)
@@ -124,7 +183,8 @@ def run_reference(args):
             'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
             'config': {'workload': 'DeepLabV3+ 21-class 512x512 training (configs[3]); CPU oracle port of the '
                                    'reference model code, fp32', 'per_step_batch': CPU_SAMPLE_BATCH},
-            'cpu_baseline': {'value': ips, 'unit': 'images/sec', 'cores': threads, 'kind': 'port', 'sample': sample},
+            'cpu_baseline': {'value': ips, 'unit': 'images/sec', 'cores': threads, 'kind': 'port', 'sample': sample,
+                             'cpu': cpu_model()},
             'e2e': {'value': ips, 'unit': 'images/sec', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
     print(json.dumps(line), flush=True)
@@ -162,11 +222,15 @@ def run_b200(args):
     model = P.DeepLabV3Plus(NC).to(dev).train()
     # one multi-tensor launch (b200seg_sgd_multi); the 1/world of the gradient average is folded into the update
     opt = P.optim.SGD(model.parameters(), lr=1e-3, momentum=0.9, grad_scale=1.0 / world)
-    bucketer = GradBucketer(model.parameters(), bucket_mb=args.bucket_mb, average=False).attach() if world > 1 else None
+    bucketer = (GradBucketer(model.parameters(), bucket_mb=args.bucket_mb, average=False).attach().sync_initial_state(model)
+                if world > 1 else None)
 
+    # inputs as the reference's dataset yields them (utils/datasets.py:161-194): uint8 images, uint8 masks.  The
+    # normalisation of post_fetch_fn (utils/datasets.py:199-205) runs on the device inside the stem's space-to-depth
+    # pass, the loss reads the 1-byte masks directly (utils.post_fetch_fn drop-in)
     g = torch.Generator(device='cpu').manual_seed(100 + rank)
-    x_host = torch.randn(B, 3, H, W, generator=g).pin_memory()
-    t_host = torch.randint(0, NC, (B, H, W), generator=g).pin_memory()
+    x_host = torch.randint(0, 256, (B, 3, H, W), generator=g, dtype=torch.uint8).pin_memory()
+    t_host = torch.randint(0, NC, (B, H, W), generator=g, dtype=torch.uint8).pin_memory()
     x_dev, t_dev = x_host.to(dev), t_host.to(dev)
     loss_host = torch.zeros((), dtype=torch.float32).pin_memory()
 
@@ -230,7 +294,7 @@ def run_b200(args):
     # being timed and understate it
     lane_was, E._LANE_ON = E._LANE_ON, False
     E.PROFILE = []
-    E.OP_PROFILE = [] if args.detail else None
+    E.OP_PROFILE = []
     prof_steps = min(args.steps, 3)
     for _ in range(prof_steps):
         eager(x_dev, t_dev)
@@ -238,24 +302,45 @@ def run_b200(args):
     rec, E.PROFILE = E.PROFILE, None
     op_rec, E.OP_PROFILE = E.OP_PROFILE, None
     E._LANE_ON = lane_was
+    # data parallel: every rank must hold the same parameters after the same number of averaged updates
+    sync_diff = None
+    if world > 1:
+        chk = torch.stack([p.detach().double().sum() for p in model.parameters()])
+        hi, lo = chk.clone(), chk.clone()
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        sync_diff = float((hi - lo).abs().max())
     agg = {}
-    for tag, flops, e0, e1 in rec:
-        a = agg.setdefault(tag, [0.0, 0.0, 0])
+    for tag, flops, e0, e1, info in rec:
+        a = agg.setdefault(tag, [0.0, 0.0, 0, 0.0, 0.0])
         a[0] += flops
         a[1] += e0.elapsed_time(e1) * 1e-3
         a[2] += 1
+        a[3] += flops * info['run_share']           # FLOPs of the (tap, tile) pairs actually run
+        a[4] += info['bytes']
     pk = peaks()
     igemm = [(t, v) for t, v in agg.items() if t.startswith('conv_fprop') or t.startswith('conv_dgrad')]
-    ig_flops, ig_secs, ig_n = (sum(v[i] for _, v in igemm) for i in range(3))
+    ig_flops, ig_secs, ig_n, ig_exec, ig_bytes = (sum(v[i] for _, v in igemm) for i in range(5))
     peak_tf = pk['bf16_tflops_sustained'] or pk['bf16_tflops']
     achieved = ig_flops / ig_secs / 1e12 if ig_secs > 0 else 0.0
     detail = sorted(({'launch': t, 'tflops': round(v[0] / v[1] / 1e12, 1), 'us': round(v[1] / v[2] * 1e6, 1),
-                      'frac': round(v[0] / v[1] / 1e12 / peak_tf, 3)} for t, v in agg.items() if v[1] > 0),
-                    key=lambda d: -d['us'])
-    traffic = None
+                      'frac': round(v[0] / v[1] / 1e12 / peak_tf, 3),
+                      'frac_executed': round(v[3] / v[1] / 1e12 / peak_tf, 3),
+                      'skipped_tap_share': round(1.0 - v[3] / v[0], 3) if v[0] else 0.0}
+                     for t, v in agg.items() if v[1] > 0), key=lambda d: -d['us'])
+    # the BatchNorm family (apply / backward / residual-gradient join): HBM-bound, algorithmic bytes per SURVEY §8d
+    bn_bytes = bn_secs = 0.0
+    bn_n = 0
+    for tag, e0, e1, nbytes in op_rec or []:
+        if nbytes > 0:
+            bn_bytes += nbytes
+            bn_secs += e0.elapsed_time(e1) * 1e-3
+            bn_n += 1
+    traffic = traffic_src = None
     tpath = os.path.join(ROOT, 'profiles', 'igemm_traffic.json')
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get('dram_bytes_per_launch')
+        tj = json.load(open(tpath))
+        traffic, traffic_src = tj.get('dram_bytes_per_launch'), tj.get('source')
 
     if rank == 0:
         ips = world * B * args.steps / secs
@@ -264,32 +349,55 @@ def run_b200(args):
             'metric': METRIC, 'value': ips, 'unit': 'images/sec', 'n_gpus': world, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': secs / args.steps * 1e3, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
-            'config': {'workload': 'DeepLabV3+ 21-class 512x512 bf16 training, fwd+loss+bwd+SGD (BASELINE configs[3])',
+            'config': {'workload': 'DeepLabV3+ 21-class 512x512 bf16 training, fwd+loss+bwd+SGD (BASELINE configs[3]); uint8 images '
+                                   'and masks as the dataset yields them, post_fetch_fn normalisation fused into the stem pass',
                        'per_gpu_batch': B, 'global_batch': B * world, 'parallelism': 'dp%d' % world,
                        'cuda_graph': bool(use_graph), 'host_enqueue_ms_per_eager_step': round(host_enqueue_ms, 2),
                        'libb200seg_launches_per_step': eager_launches,
                        'l2': 'no explicit flush: one step streams several GB of activations (>> 126 MB L2)',
                        'backbone': 'ResNet-50 OS16 on libb200seg (tcgen05 convs incl. stride 2, fused BN/ReLU/residual, '
                                    'max pool); 7x7/2 stem = 4 row taps over the space-to-depth image (tcgen05); no cuDNN on the path'},
-            'e2e': {'value': ips_e2e, 'unit': 'images/sec', 'h2d_bytes_per_step': x_host.numel() * 4 + t_host.numel() * 8,
+            'e2e': {'value': ips_e2e, 'unit': 'images/sec', 'h2d_bytes_per_step': x_host.numel() * x_host.element_size() + t_host.numel() * t_host.element_size(),
                     'd2h_bytes_per_step': 4, 'ms_per_step': secs_e2e / args.steps * 1e3},
             'gpu_launches': launches,
             'clocks': clocks,
             'roofline': {'bound': 'tensor', 'achieved': achieved, 'peak': peak_tf, 'unit': 'TFLOP/s',
-                         'frac': achieved / peak_tf if peak_tf else None, 'traffic': traffic,
+                         'frac': achieved / peak_tf if peak_tf else None,
+                         'flops_executed_per_step': ig_exec / max(prof_steps, 1),
+                         'frac_executed': ig_exec / ig_secs / 1e12 / peak_tf if ig_secs > 0 and peak_tf else None,
+                         'skipped_tap_share': 1.0 - ig_exec / ig_flops if ig_flops else None,
+                         'traffic': traffic, 'traffic_source': traffic_src,
+                         'algorithmic_bytes': ig_bytes / max(ig_n, 1),
                          'kernel': 'igemm_kernel (tcgen05 implicit-GEMM fprop+dgrad, %d launches/step)' % (ig_n // max(prof_steps, 1)),
-                         'flops_per_step': ig_flops / max(prof_steps, 1), 'peak_source': pk['source'] + ', sustained'},
+                         'flops_per_step': ig_flops / max(prof_steps, 1), 'peak_source': pk['source'] + ', sustained',
+                         'note': 'frac counts padding taps (SURVEY 8d nominal FLOPs); frac_executed leaves out the all-padding '
+                                 '(tap, tile) pairs the kernel skips (ASPP d=12/18 skip 44 % / 61 %), so per-launch frac > 1 is '
+                                 'nominal work not done, not time saved by magic; durations are eager per-launch CUDA events '
+                                 '(launch gaps included), traffic / algorithmic_bytes are per launch averaged over the step'},
+            'roofline_bn': {'bound': 'hbm', 'achieved': bn_bytes / bn_secs / 1e9 if bn_secs > 0 else None, 'peak': pk['hbm_gbs'],
+                            'unit': 'GB/s', 'frac': bn_bytes / bn_secs / 1e9 / pk['hbm_gbs'] if bn_secs > 0 and pk['hbm_gbs'] else None,
+                            'kernel': 'bn_apply / bn_bwd_reduce+apply / grad_add_masked (%d calls/step)' % (bn_n // max(prof_steps, 1)),
+                            'algorithmic_bytes_per_step': bn_bytes / max(prof_steps, 1),
+                            'ms_per_step': bn_secs / max(prof_steps, 1) * 1e3,
+                            'bytes_rule': 'apply 2x tensor (+1 with a residual), backward 2x(dy+x)+dx, join dx r/w + operands'},
             'kernels': detail[:12],
         }
+        if sync_diff is not None:
+            line['param_sync_max_abs_diff'] = sync_diff
         if world == 1 and not args.no_cpu_baseline:
             ips_cpu, dt, threads = cpu_reference_run(16, 1)      # ~10 s of host work
-            line['cpu_baseline'] = {'value': ips_cpu, 'unit': 'images/sec', 'cores': threads, 'kind': 'port',
+            ub, um, _ = cpu_unet_run(6, 1)                        # BASELINE.md §4 "config 1 exactly", ~5 s
+            line['cpu_baseline'] = {'value': ips_cpu, 'unit': 'images/sec', 'cores': threads, 'kind': 'port', 'cpu': cpu_model(),
                                     'sample': 'oracle DeepLabV3+ 512x512 train step, batch %d, 1 warm-up + 16 timed steps '
-                                              '(%.2f s/step)' % (CPU_SAMPLE_BATCH, dt)}
+                                              '(%.2f s/step)' % (CPU_SAMPLE_BATCH, dt),
+                                    'config1_unet2_b4_320': {'best_s_per_step': ub, 'median_s_per_step': um,
+                                                             'images_per_sec_best': 4 / ub, 'images_per_sec_median': 4 / um,
+                                                             'what': 'UNet(2) batch 4 320x320 fwd+compute_loss+bwd, fp32, '
+                                                                     '1 warm-up + 6 timed (BASELINE.md §4)'}}
         if args.detail:
             with open(args.detail, 'w') as f:
                 ops, ops_by_shape = {}, {}
-                for tag, e0, e1 in op_rec or []:
+                for tag, e0, e1, _nb in op_rec or []:
                     us = e0.elapsed_time(e1) * 1e3 / prof_steps
                     for table, key in ((ops, tag.split(' ')[0]), (ops_by_shape, tag)):
                         o = table.setdefault(key, [0.0, 0])
@@ -308,15 +416,214 @@ def run_b200(args):
                            'kernels': detail}, f, indent=1)
         print(json.dumps(line), flush=True)
     if world > 1:
-        torch.cuda.synchronize()
-        dist.barrier()
-        if use_graph:
-            # a captured step holds NCCL kernels: tearing the communicator down under a live graph (or the graph
-            # after the communicator) can block at interpreter exit, so the ranks leave together right here
-            sys.stdout.flush()
-            sys.stderr.flush()
+        _teardown(step, eager, bucketer)
+
+
+def _teardown(*objs):
+    """Leave a multi-rank run cleanly: the captured graphs (which hold NCCL kernels) go first, then the communicator.  A
+    watchdog ends the process if the teardown has not finished in 30 s (round 1 saw communicator teardown block under a
+    live graph): the JSON line is out by then, so the only effect is the exit path."""
+    torch.cuda.synchronize()
+    dist.barrier()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    done = threading.Event()
+
+    def watchdog():
+        if not done.wait(30.0):
             os._exit(0)
-        dist.destroy_process_group()
+    threading.Thread(target=watchdog, daemon=True).start()
+    for o in objs:
+        if o is None:
+            continue
+        for name in ('_graph', '_loss'):
+            if hasattr(o, name):
+                setattr(o, name, None)
+        if hasattr(o, 'remove'):
+            o.remove()
+    import gc
+    gc.collect()
+    torch.cuda.synchronize()
+    dist.destroy_process_group()
+    done.set()
+
+
+# -----------------------------------------------------------------------------------------------------------
+# the other BASELINE.json configurations (same contract, one JSON line)
+# -----------------------------------------------------------------------------------------------------------
+OTHER = {
+    # name: (model, classes, H, W, per-GPU batch, train?, metric, workload)
+    'infer': ('deeplab', 21, 512, 512, 16, False, 'inference images/sec @512x512 (DeepLabV3+ 21-class, bf16)',
+              'DeepLabV3+ 21-class 512x512 bf16 inference batch 16 + mIoU confusion histogram (BASELINE configs[1])'),
+    'hrnet': ('hrnet', 19, 512, 1024, 8, True, 'train images/sec @1024x512 (HRNet 19-class, bf16)',
+              'HRNet 19-class 1024x512 bf16 training, fwd+loss+bwd+SGD (BASELINE configs[4])'),
+    'unet': ('unet', 2, 320, 320, 4, True, 'train images/sec @320x320 (UNet 2-class, bf16)',
+             'UNet 2-class 320x320 batch 4 fwd+loss+bwd+SGD on the GPU (BASELINE configs[0] shapes; MobileNetV2 encoder on '
+             'torchvision/cuDNN — outside SURVEY §8 — head on libb200seg)'),
+    'aspp': ('aspp', 21, 32, 32, 16, True, 'ASPP block fwd+bwd images/sec (2048-ch 32x32 input, rates 6/12/18, bf16)',
+             'ASPP(2048, 256, [6, 12, 18]) isolated, forward + backward, batch 16 (BASELINE configs[2])'),
+}
+
+
+def run_other(args):
+    import pytorch_segmentation_b200 as P
+    from pytorch_segmentation_b200 import _lib, engine as E
+    from pytorch_segmentation_b200.parallel import GradBucketer
+    kind, nc, h, w, batch, train, metric, workload = OTHER[args.config]
+    B = args.batch if args.batch_given else batch
+    rank, local, world = (int(os.environ.get(k, d)) for k, d in (('RANK', '0'), ('LOCAL_RANK', '0'), ('WORLD_SIZE', '1')))
+    if not torch.cuda.is_available():
+        raise RuntimeError('bench.py: no CUDA device — the B200 arm has no CPU fallback (use --impl reference)')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=dev)
+    _lib.load()
+    torch.manual_seed(1234)
+    g = torch.Generator(device='cpu').manual_seed(100 + rank)
+    bucketer = step = None
+    if kind == 'aspp':
+        model = P.ASPP(2048, 256, [6, 12, 18]).to(dev).train()
+        x_host = torch.randn(B, h, w, 2048, generator=g).to(torch.bfloat16).pin_memory()
+        gy = torch.randn(B, h, w, 256, generator=g).to(torch.bfloat16).to(dev).permute(0, 3, 1, 2)
+        x_dev = x_host.to(dev).permute(0, 3, 1, 2).requires_grad_(True)
+        t_host = None
+
+        def fn(x=None):
+            xin = x_dev if x is None else x
+            xin.grad = None
+            model.zero_grad(set_to_none=True)
+            E.pack_all(E.packed_entries(model))
+            y = model(xin)
+            y.backward(gy)
+            return y
+
+        def fn_e2e():
+            xx = x_host.to(dev, non_blocking=True).permute(0, 3, 1, 2).requires_grad_(True)
+            y = fn(xx)
+            return y.detach().float().abs().mean()
+        h2d = x_host.numel() * 2
+    else:
+        cls = {'deeplab': P.DeepLabV3Plus, 'hrnet': P.HRNet, 'unet': P.UNet}[kind]
+        model = cls(nc).to(dev)
+        x_host = torch.randint(0, 256, (B, 3, h, w), generator=g, dtype=torch.uint8).pin_memory()
+        t_host = torch.randint(0, nc, (B, h, w), generator=g, dtype=torch.uint8).pin_memory()
+        x_dev, t_dev = x_host.to(dev), t_host.to(dev)
+        h2d = x_host.numel() + t_host.numel()
+        if train:
+            model.train()
+            opt = P.optim.SGD(model.parameters(), lr=1e-3, momentum=0.9, grad_scale=1.0 / world)
+            if world > 1:
+                bucketer = GradBucketer(model.parameters(), bucket_mb=args.bucket_mb, average=False).attach().sync_initial_state(model)
+            step = P.TrainStep(model, opt, bucketer, graph=args.graph in ('on', 'auto'))
+            eager = P.TrainStep(model, opt, bucketer, graph=False)
+
+            def fn():
+                return step(x_dev, t_dev)
+
+            def fn_e2e():
+                return step.step_prefetched(next_batch=(x_host, t_host))
+        else:
+            model.eval()
+            cm = torch.zeros((nc, nc), dtype=torch.int64, device=dev)
+
+            def infer(x, t):
+                with torch.no_grad():
+                    y = model(x)
+                    tag = y._b200seg_class_map                # test.py:28-46 through evaluate.test's fused path
+                    E.class_map_confusion(tag[0], nc, t, tag[2], cm)
+                return y
+
+            def fn():
+                return infer(x_dev, t_dev)
+
+            def fn_e2e():
+                infer(x_host.to(dev, non_blocking=True), t_host.to(dev, non_blocking=True))
+                return cm.sum()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(f, k):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k):
+            f()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms) / 1e3
+
+    out_host = torch.zeros((), dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        out_host.copy_(fn_e2e().float(), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for _ in range(args.warmup + (4 if step is not None and step.use_graph else 0)):
+        fn()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    l0 = _lib.launches()
+    secs = timed(fn, args.steps)
+    launches = step.launches_per_step * args.steps if step is not None and step.use_graph else _lib.launches() - l0
+    clocks = sampler.stop() if sampler else None
+    if step is not None:
+        step.prefetch(x_host, t_host)
+    for _ in range(2):
+        e2e_step()
+    secs_e2e = timed(e2e_step, args.steps)
+    # per-launch CUDA-event timing of the tcgen05 convs (eager, weight-gradient lane off)
+    lane_was, E._LANE_ON = E._LANE_ON, False
+    E.PROFILE = []
+    prof_fn = (lambda: eager(x_dev, t_dev)) if step is not None else fn
+    for _ in range(2):
+        prof_fn()
+    torch.cuda.synchronize()
+    rec, E.PROFILE = E.PROFILE, None
+    E._LANE_ON = lane_was
+    pk = peaks()
+    peak_tf = pk['bf16_tflops_sustained'] or pk['bf16_tflops']
+    agg = {}
+    for tag, flops, e0, e1, info in rec:
+        a = agg.setdefault(tag, [0.0, 0.0, 0, 0.0])
+        a[0] += flops
+        a[1] += e0.elapsed_time(e1) * 1e-3
+        a[2] += 1
+        a[3] += flops * info['run_share']
+    ig = [v for t, v in agg.items() if t.startswith('conv_fprop') or t.startswith('conv_dgrad')]
+    fl, sc, nn, ex = (sum(v[i] for v in ig) for i in range(4))
+    detail = sorted(({'launch': t, 'tflops': round(v[0] / v[1] / 1e12, 1), 'us': round(v[1] / v[2] * 1e6, 1),
+                      'frac': round(v[0] / v[1] / 1e12 / peak_tf, 3), 'frac_executed': round(v[3] / v[1] / 1e12 / peak_tf, 3)}
+                     for t, v in agg.items() if v[1] > 0), key=lambda d: -d['us'])
+    if rank == 0:
+        line = {'metric': metric, 'value': world * B * args.steps / secs, 'unit': 'images/sec', 'n_gpus': world,
+                'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': secs / args.steps * 1e3, 'higher_is_better': True,
+                'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
+                'config': {'workload': workload, 'per_gpu_batch': B, 'global_batch': B * world, 'parallelism': 'dp%d' % world,
+                           'cuda_graph': bool(step is not None and step.use_graph),
+                           'l2': 'no explicit flush: one step streams far more than the 126 MB L2' if kind != 'aspp' else
+                                 'inputs + weights (67 + 47 MB) exceed what stays in the 126 MB L2 across a step'},
+                'e2e': {'value': world * B * args.steps / secs_e2e, 'unit': 'images/sec', 'h2d_bytes_per_step': h2d,
+                        'd2h_bytes_per_step': 4, 'ms_per_step': secs_e2e / args.steps * 1e3},
+                'gpu_launches': launches, 'clocks': clocks,
+                'roofline': {'bound': 'tensor', 'achieved': fl / sc / 1e12 if sc > 0 else None, 'peak': peak_tf,
+                             'unit': 'TFLOP/s', 'frac': fl / sc / 1e12 / peak_tf if sc > 0 else None,
+                             'frac_executed': ex / sc / 1e12 / peak_tf if sc > 0 else None, 'traffic': None,
+                             'kernel': 'igemm_kernel (tcgen05 implicit-GEMM fprop+dgrad, %d launches/step)' % (nn // 2),
+                             'peak_source': pk['source'] + ', sustained'},
+                'kernels': detail[:12]}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        _teardown(step, eager if step is not None else None, bucketer)
 
 
 def main():
@@ -325,7 +632,9 @@ def main():
     ap.add_argument('--steps', type=int, default=40)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--batch', type=int, default=16, help='images per GPU per step')
+    ap.add_argument('--batch', type=int, default=None, help='images per GPU per step (default: the configuration\'s)')
+    ap.add_argument('--config', default='train', choices=['train', 'infer', 'aspp', 'hrnet', 'unet', 'unet_cpu'],
+                    help='which BASELINE.json configuration (default: configs[3], the headline training step)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--detail', default=None, help='write the per-launch CUDA-event timings of every conv to this file')
     ap.add_argument('--bucket-mb', type=float, default=64.0, help='N > 1: gradient all-reduce bucket size')
@@ -334,11 +643,14 @@ def main():
     ap.add_argument('--graph', default='auto', choices=['auto', 'on', 'off'],
                     help='replay the step from a CUDA graph (auto = on; the bucketed NCCL all-reduces are captured with it)')
     args = ap.parse_args()
-    if args.impl == 'reference':
+    args.batch_given = args.batch is not None
+    if args.batch is None:
+        args.batch = 16
+    if args.impl == 'reference' or args.config == 'unet_cpu':
         run_reference(args)
     else:
         args.warmup = max(args.warmup, 3)
-        run_b200(args)
+        (run_b200 if args.config == 'train' else run_other)(args)
 
 
 if __name__ == '__main__':

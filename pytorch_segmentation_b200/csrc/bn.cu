@@ -7,10 +7,21 @@
 #include "pdl.cuh"
 #include "vec.cuh"
 
+#include <stdlib.h>
+
 namespace b200seg {
 namespace {
 
 constexpr int kRedThreads = 256;
+
+// pixels per thread per trip of the streaming BatchNorm passes (1, 2 or 4): B200SEG_BN_K sets all three kernels,
+// B200SEG_BN_K_APPLY / _BWD / _RED one of them (A/B runs: scripts/bench_bandwidth.py)
+int bn_env_k(const char* name, int dflt) {
+    const char* e = getenv(name);
+    if (!e) e = getenv("B200SEG_BN_K");
+    const int v = e ? atoi(e) : dflt;
+    return v == 1 || v == 2 || v == 4 ? v : dflt;
+}
 
 // Geometry of a column reduction over a [pixels][c] slice: G = c/8 channel groups; a block covers
 // `gpb` groups (<= 256) and 256/gpb pixel rows per iteration.
@@ -181,44 +192,51 @@ struct BnTrain {
 // kResAffine: the residual carries its own BN affine (downsample branch); kBits: also write the sign mask.  Separate
 // instantiations keep the common ones at 64 registers or fewer (4 resident CTAs per SM): at 73 the 134 MB passes ran
 // 113 us instead of 85.
-template <bool kResAffine, bool kBits>
+// K: pixels per thread per trip, their loads all issued before the first is consumed.  A streaming pass needs
+// bandwidth x latency bytes in flight (6.5 TB/s x ~1 us = 44 KB per SM); one 16-byte load per thread at 1024 resident
+// threads is 16 KB, which is what held these passes at ~3 TB/s.  The per-channel parameters live in SHARED memory
+// (one LDS.128 pair per vector per trip, far below the LDS rate): in registers they left no room for K loads at four
+// resident CTAs per SM.
+// (volatile: the compiler would otherwise hoist the rows back into registers for the whole sweep and spill the loads)
+__device__ __forceinline__ void lds8(const float* p, float (&f)[8]) {
+    const unsigned a = static_cast<unsigned>(__cvta_generic_to_shared(p));
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(f[0]), "=f"(f[1]), "=f"(f[2]), "=f"(f[3]) : "r"(a));
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(f[4]), "=f"(f[5]), "=f"(f[6]), "=f"(f[7]) : "r"(a + 16));
+}
+
+// kRes: 0 = no residual, 1 = identity residual, 2 = residual with its own BN affine (downsample branch); compile-time so
+// the K staged residual loads cost registers only where a residual exists
+template <int kRes, bool kBits, int K>
 __global__ void __launch_bounds__(kRedThreads, 4) bn_apply_kernel(
     const __nv_bfloat16* __restrict__ x, int x_ct, int x_off, __nv_bfloat16* __restrict__ y, int y_ct, int y_off, int groups,
     int64_t pixels, int64_t ppb, int gpb, int rows, const float* __restrict__ scale, const float* __restrict__ shift,
     int relu, const __nv_bfloat16* __restrict__ res, int r_ct, int r_off, const float* __restrict__ res_scale,
     const float* __restrict__ res_shift, const BnTrain tr) {
     pdl_prologue();
+    extern __shared__ __align__(16) float bn_sp[];      // [2 or 4][gpb * 8]: scale, shift (, residual scale, shift)
+    const int cw = gpb * 8;
     const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
     const int group = blockIdx.y * gpb + g_local;
-    if (row >= rows || group >= groups) return;
-    float sc[8], sh[8], rsc[8], rsh[8];
-    if (tr.stats) {
-        // training mode without a separate finalize launch: every thread derives its 8 channels' scale / shift from
-        // the conv epilogue's sums (bn_finalize_kernel's arithmetic); the first block row also publishes them for the
-        // backward and moves the running statistics
-        // (four channels at a time: the whole prologue live at once took the kernel past 64 registers and cost it a
-        // resident CTA per SM)
-        const int c = groups * 8;
-        const bool publish = blockIdx.x == 0 && row == 0;
+    if (threadIdx.x < gpb && group < groups) {
+        // one thread per channel group fills the block's parameter rows
+        float* dsc = bn_sp + threadIdx.x * 8;
+        float* dsh = bn_sp + cw + threadIdx.x * 8;
+        if (tr.stats) {
+            // training mode without a separate finalize launch: scale / shift from the conv epilogue's sums
+            // (bn_finalize_kernel's arithmetic); block row 0 also publishes them for the backward and moves the running
+            // statistics
+            const int c = groups * 8;
+            const bool publish = blockIdx.x == 0;
 #pragma unroll
-        for (int hv = 0; hv < 2; ++hv) {
-            const int ch0 = group * 8 + hv * 4;
-            const float4 s1 = __ldg(reinterpret_cast<const float4*>(tr.stats + ch0));
-            const float4 s2 = __ldg(reinterpret_cast<const float4*>(tr.stats + c + ch0));
-            const float4 gm = __ldg(reinterpret_cast<const float4*>(tr.gamma + ch0));
-            const float4 bt = __ldg(reinterpret_cast<const float4*>(tr.beta + ch0));
-            const float s1v[4] = {s1.x, s1.y, s1.z, s1.w}, s2v[4] = {s2.x, s2.y, s2.z, s2.w};
-            const float gmv[4] = {gm.x, gm.y, gm.z, gm.w}, btv[4] = {bt.x, bt.y, bt.z, bt.w};
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float mean = s1v[j] * tr.inv_count;
-                const float var = fmaxf(fmaf(-mean, mean, s2v[j] * tr.inv_count), 0.f);
+            for (int j = 0; j < 8; ++j) {
+                const int ch = group * 8 + j;
+                const float mean = __ldg(tr.stats + ch) * tr.inv_count;
+                const float var = fmaxf(fmaf(-mean, mean, __ldg(tr.stats + c + ch) * tr.inv_count), 0.f);
                 const float invstd = rsqrtf(var + tr.eps);
-                const float scj = gmv[j] * invstd, shj = fmaf(-mean, scj, btv[j]);
-                sc[hv * 4 + j] = scj;
-                sh[hv * 4 + j] = shj;
+                const float scj = __ldg(tr.gamma + ch) * invstd, shj = fmaf(-mean, scj, __ldg(tr.beta + ch));
+                dsc[j] = scj;
+                dsh[j] = shj;
                 if (publish) {
-                    const int ch = ch0 + j;
                     tr.vec[ch] = scj;
                     tr.vec[c + ch] = shj;
                     tr.vec[2 * c + ch] = mean;
@@ -228,74 +246,119 @@ __global__ void __launch_bounds__(kRedThreads, 4) bn_apply_kernel(
                         tr.running_var[ch] = fmaf(tr.momentum, var * tr.unbias - tr.running_var[ch], tr.running_var[ch]);
                 }
             }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                dsc[j] = __ldg(scale + group * 8 + j);
+                dsh[j] = __ldg(shift + group * 8 + j);
+            }
         }
-    } else {
-        load8f(scale + group * 8, sc);
-        load8f(shift + group * 8, sh);
+        if (kRes == 2) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                bn_sp[2 * cw + threadIdx.x * 8 + j] = __ldg(res_scale + group * 8 + j);
+                bn_sp[3 * cw + threadIdx.x * 8 + j] = __ldg(res_shift + group * 8 + j);
+            }
+        }
     }
-    const bool res_affine = kResAffine;
-    if (kResAffine) {
-        load8f(res_scale + group * 8, rsc);
-        load8f(res_shift + group * 8, rsh);
-    }
+    __syncthreads();
+    if (row >= rows || group >= groups) return;
+    const float* psc = bn_sp + g_local * 8;
+    const float* psh = psc + cw;
     const int64_t p0 = static_cast<int64_t>(blockIdx.x) * rows;
     const int64_t p1 = pixels;
     const int64_t pstep = static_cast<int64_t>(gridDim.x) * rows;
     (void)ppb;
     const __nv_bfloat16* xb = x + x_off + group * 8;
-    const __nv_bfloat16* rb = res ? res + r_off + group * 8 : nullptr;
+    const __nv_bfloat16* rb = kRes ? res + r_off + group * 8 : nullptr;
     __nv_bfloat16* yb = y + y_off + group * 8;
     // a char store may alias anything: without the restrict copy the next iteration's loads could not move above it
-    // and the pass ran 35 % slower
     unsigned char* __restrict__ bits = kBits ? tr.bits : nullptr;
-#pragma unroll 2
-    for (int64_t p = p0 + row; p < p1; p += pstep) {
-        float f[8];
-        unpack8(ldcs128(xb + p * x_ct), f);
+    // running pointers and a 32-bit trip count instead of 64-bit index products per access (registers)
+    const int64_t first = p0 + row;
+    const int cnt = first < p1 ? static_cast<int>((p1 - first + pstep - 1) / pstep) : 0;
+    const int xs = static_cast<int>(pstep * x_ct), rs = static_cast<int>(pstep * r_ct), ys = static_cast<int>(pstep * y_ct),
+              bs = static_cast<int>(pstep * groups);        // launcher-checked to fit 32 bits
+    const __nv_bfloat16* xp = xb + first * x_ct;
+    const __nv_bfloat16* rp = kRes ? rb + first * r_ct : nullptr;
+    __nv_bfloat16* yp = yb + first * y_ct;
+    unsigned char* bp = kBits ? bits + first * groups + group : nullptr;
+#pragma unroll 1
+    for (int i = 0; i < cnt; i += K, xp += K * xs, yp += K * ys) {
+        if (kRes) rp += (i ? K * rs : 0);
+        if (kBits) bp += (i ? K * bs : 0);
+        uint4 xv[K], rv[kRes ? K : 1];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]);
-        if (rb) {
-            // residual branch: the identity, or the downsample conv's raw output with its own BN affine
-            float r[8];
-            unpack8(ldcs128(rb + p * r_ct), r);
-            if (kResAffine) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) r[j] = fmaf(r[j], rsc[j], rsh[j]);
+        for (int k = 0; k < K; ++k) {
+            if (i + k < cnt) {
+                xv[k] = ldcs128(xp + k * xs);
+                if (kRes) rv[k] = ldcs128(rp + k * rs);
             }
-#pragma unroll
-            for (int j = 0; j < 8; ++j) f[j] += r[j];
         }
-        if (relu) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
-        }
-        st128(yb + p * y_ct, pack8(f));
-        if (kBits) {
-            unsigned int m = 0;
+        for (int k = 0; k < K; ++k) {
+            if (i + k >= cnt) break;
+            float f[8], sc[8], sh[8];
+            lds8(psc, sc);
+            lds8(psh, sh);
+            unpack8(xv[k], f);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) m |= (f[j] > 0.f ? 1u : 0u) << j;
-            bits[p * groups + group] = static_cast<unsigned char>(m);
+            for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]);
+            if (kRes) {
+                // residual branch: the identity, or the downsample conv's raw output with its own BN affine
+                float r[8];
+                unpack8(rv[k], r);
+                if (kRes == 2) {
+                    float rsc[8], rsh[8];
+                    lds8(psc + 2 * cw, rsc);
+                    lds8(psc + 3 * cw, rsh);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) r[j] = fmaf(r[j], rsc[j], rsh[j]);
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] += r[j];
+            }
+            if (relu) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+            }
+            st128(yp + k * ys, pack8(f));
+            if (kBits) {
+                unsigned int m = 0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) m |= (f[j] > 0.f ? 1u : 0u) << j;
+                bp[k * bs] = static_cast<unsigned char>(m);
+            }
         }
     }
 }
 
 // red[0..c) = sum dz', red[c..2c) = sum dz' * xhat   with dz' = dy * (y > 0 if relu)
+template <int K, bool kMask>
 __global__ void __launch_bounds__(kRedThreads, 4) bn_bwd_reduce_kernel(
     const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off, const __nv_bfloat16* __restrict__ x, int x_ct, int x_off,
     int c, int64_t pixels, int64_t ppb, int gpb, int rows, const float* __restrict__ scale, const float* __restrict__ shift,
     const float* __restrict__ mean, const float* __restrict__ invstd, int relu, float* __restrict__ red,
     const __nv_bfloat16* __restrict__ mask, int m_ct, int m_off) {
     pdl_prologue();
+    extern __shared__ __align__(16) float bn_sp[];      // [2][gpb * 8]: scale, shift (the ReLU mask is recomputed from x)
+    const int cw = gpb * 8;
     const int groups = c >> 3;
     const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
     const int group = blockIdx.y * gpb + g_local;
+    if (threadIdx.x < gpb && group < groups) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            bn_sp[threadIdx.x * 8 + j] = __ldg(scale + group * 8 + j);
+            bn_sp[cw + threadIdx.x * 8 + j] = __ldg(shift + group * 8 + j);
+        }
+    }
+    __syncthreads();
     float acc[2][8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[0][j] = acc[1][j] = 0.f;
     if (row < rows && group < groups) {
-        float sc[8], sh[8];
-        load8f(scale + group * 8, sc);
-        load8f(shift + group * 8, sh);
+        const float* psc = bn_sp + g_local * 8;
         // strided sweep: all CTAs move through the tensor together (measured faster than one contiguous chunk per CTA)
         const int64_t p0 = static_cast<int64_t>(blockIdx.x) * rows;
         const int64_t p1 = pixels;
@@ -303,28 +366,50 @@ __global__ void __launch_bounds__(kRedThreads, 4) bn_bwd_reduce_kernel(
         (void)ppb;
         const __nv_bfloat16* xb = x + x_off + group * 8;
         const __nv_bfloat16* db = dy + dy_off + group * 8;
-        const __nv_bfloat16* mb = mask ? mask + m_off + group * 8 : nullptr;
-#pragma unroll 2
-        for (int64_t p = p0 + row; p < p1; p += pstep) {
-            float f[8], d[8], m[8];
-            unpack8(ldg128(xb + p * x_ct), f);
-            unpack8(ldg128(db + p * dy_ct), d);
-            if (mb) {
-                // ReLU mask from the stored block output (BN output + residual), not recomputable from x alone
-                unpack8(ldg128(mb + p * m_ct), m);
-            } else {
+        const __nv_bfloat16* mb = kMask ? mask + m_off + group * 8 : nullptr;
+        const int64_t first = p0 + row;
+        const int cnt = first < p1 ? static_cast<int>((p1 - first + pstep - 1) / pstep) : 0;
+        const int xs = static_cast<int>(pstep * x_ct), ds = static_cast<int>(pstep * dy_ct), ms = static_cast<int>(pstep * m_ct);
+        const __nv_bfloat16* xp = xb + first * x_ct;
+        const __nv_bfloat16* dp = db + first * dy_ct;
+        const __nv_bfloat16* mp = kMask ? mb + first * m_ct : nullptr;
+#pragma unroll 1
+        for (int i = 0; i < cnt; i += K, xp += K * xs, dp += K * ds) {
+            if (kMask) mp += (i ? K * ms : 0);
+            uint4 xv[K], dv[K], mv[kMask ? K : 1];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) m[j] = fmaf(f[j], sc[j], sh[j]);
+            for (int k = 0; k < K; ++k) {
+                if (i + k < cnt) {
+                    xv[k] = ldg128(xp + k * xs);
+                    dv[k] = ldg128(dp + k * ds);
+                    // ReLU mask from the stored block output (BN output + residual), not recomputable from x alone
+                    if (kMask) mv[k] = ldg128(mp + k * ms);
+                }
             }
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const float dz = (relu && m[j] <= 0.f) ? 0.f : d[j];
-                acc[0][j] += dz;
-                acc[1][j] = fmaf(dz, f[j], acc[1][j]);      // sum dz * x; centred and scaled once below
+            for (int k = 0; k < K; ++k) {
+                if (i + k >= cnt) break;
+                float f[8], d[8], m[8];
+                unpack8(xv[k], f);
+                unpack8(dv[k], d);
+                if (kMask) {
+                    unpack8(mv[k], m);
+                } else if (relu) {
+                    float sc[8], sh[8];
+                    lds8(psc, sc);
+                    lds8(psc + cw, sh);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) m[j] = fmaf(f[j], sc[j], sh[j]);
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float dz = (relu && m[j] <= 0.f) ? 0.f : d[j];
+                    acc[0][j] += dz;
+                    acc[1][j] = fmaf(dz, f[j], acc[1][j]);      // sum dz * x; centred and scaled once below
+                }
             }
         }
-        // sum dz * xhat = invstd * (sum dz*x - mean * sum dz), per thread (a few hundred terms: no cancellation issue);
-        // mean / invstd are loaded only now: live across the sweep they cost the kernel its fourth resident CTA
+        // sum dz * xhat = invstd * (sum dz*x - mean * sum dz), per thread (a few hundred terms: no cancellation issue)
         float mu[8], is[8];
         load8f(mean + group * 8, mu);
         load8f(invstd + group * 8, is);
@@ -336,7 +421,8 @@ __global__ void __launch_bounds__(kRedThreads, 4) bn_bwd_reduce_kernel(
 
 // dx = scale * (dz' - red0/M - xhat * red1/M)   (training)   or   scale * dz'   (eval: statistics are constants)
 // rewritten per channel as dx = A * dz' + B * x + C with A = scale, B = -scale*invstd*red1/M (xhat = (x-mean)*invstd),
-// C = -scale*red0/M - B*mean (all per-channel registers).
+// C = -scale*red0/M - B*mean (per-channel rows in shared memory).
+template <int K, bool kMask>
 __global__ void __launch_bounds__(kRedThreads, 4) bn_bwd_apply_kernel(
     const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off, const __nv_bfloat16* __restrict__ x, int x_ct, int x_off,
     __nv_bfloat16* __restrict__ dx, int dx_ct, int dx_off, int groups, int64_t pixels, int64_t ppb, int gpb, int rows,
@@ -344,52 +430,82 @@ __global__ void __launch_bounds__(kRedThreads, 4) bn_bwd_apply_kernel(
     const float* __restrict__ invstd, int relu, int training, const float* __restrict__ red, int c,
     const __nv_bfloat16* __restrict__ mask, int m_ct, int m_off) {
     pdl_prologue();
+    extern __shared__ __align__(16) float bn_sp[];      // [4][gpb * 8]: scale, shift, B, C
+    const int cw = gpb * 8;
     const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
     const int group = blockIdx.y * gpb + g_local;
-    if (row >= rows || group >= groups) return;
-    float sc[8], sh[8], cb[8], cc[8];
-    load8f(scale + group * 8, sc);
-    load8f(shift + group * 8, sh);
-    if (training) {
-        float mu[8], is[8], r0[8], r1[8];
-        load8f(mean + group * 8, mu);
-        load8f(invstd + group * 8, is);
-        load8f(red + group * 8, r0);
-        load8f(red + c + group * 8, r1);
+    if (threadIdx.x < gpb && group < groups) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            cb[j] = -sc[j] * is[j] * r1[j] * inv_count;
-            cc[j] = -sc[j] * r0[j] * inv_count - cb[j] * mu[j];
+            const int ch = group * 8 + j;
+            const float scj = __ldg(scale + ch);
+            float cb = 0.f, cc = 0.f;
+            if (training) {
+                cb = -scj * __ldg(invstd + ch) * __ldg(red + c + ch) * inv_count;
+                cc = -scj * __ldg(red + ch) * inv_count - cb * __ldg(mean + ch);
+            }
+            bn_sp[threadIdx.x * 8 + j] = scj;
+            bn_sp[cw + threadIdx.x * 8 + j] = __ldg(shift + ch);
+            bn_sp[2 * cw + threadIdx.x * 8 + j] = cb;
+            bn_sp[3 * cw + threadIdx.x * 8 + j] = cc;
         }
-    } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) cb[j] = cc[j] = 0.f;
     }
+    __syncthreads();
+    if (row >= rows || group >= groups) return;
+    const float* psc = bn_sp + g_local * 8;
     const int64_t p0 = static_cast<int64_t>(blockIdx.x) * rows;
     const int64_t p1 = pixels;
     const int64_t pstep = static_cast<int64_t>(gridDim.x) * rows;
     (void)ppb;
     const __nv_bfloat16* xb = x + x_off + group * 8;
     const __nv_bfloat16* db = dy + dy_off + group * 8;
-    const __nv_bfloat16* mb = mask ? mask + m_off + group * 8 : nullptr;
+    const __nv_bfloat16* mb = kMask ? mask + m_off + group * 8 : nullptr;
     __nv_bfloat16* ob = dx + dx_off + group * 8;
+    const int64_t first = p0 + row;
+    const int cnt = first < p1 ? static_cast<int>((p1 - first + pstep - 1) / pstep) : 0;
+    const int xs = static_cast<int>(pstep * x_ct), ds = static_cast<int>(pstep * dy_ct), ms = static_cast<int>(pstep * m_ct),
+              os = static_cast<int>(pstep * dx_ct);
+    const __nv_bfloat16* xp = xb + first * x_ct;
+    const __nv_bfloat16* dp = db + first * dy_ct;
+    const __nv_bfloat16* mp = kMask ? mb + first * m_ct : nullptr;
+    __nv_bfloat16* op = ob + first * dx_ct;
 #pragma unroll 1
-    for (int64_t p = p0 + row; p < p1; p += pstep) {
-        float f[8], d[8], m[8];
-        unpack8(ldcs128(xb + p * x_ct), f);
-        unpack8(ldcs128(db + p * dy_ct), d);
-        if (mb) {
-            unpack8(ldcs128(mb + p * m_ct), m);
-        } else {
+    for (int i = 0; i < cnt; i += K, xp += K * xs, dp += K * ds, op += K * os) {
+        if (kMask) mp += (i ? K * ms : 0);
+        uint4 xv[K], dv[K], mv[kMask ? K : 1];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) m[j] = fmaf(f[j], sc[j], sh[j]);
+        for (int k = 0; k < K; ++k) {
+            if (i + k < cnt) {
+                xv[k] = ldcs128(xp + k * xs);
+                dv[k] = ldcs128(dp + k * ds);
+                if (kMask) mv[k] = ldcs128(mp + k * ms);
+            }
         }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const float dz = (relu && m[j] <= 0.f) ? 0.f : d[j];
-            f[j] = fmaf(sc[j], dz, fmaf(cb[j], f[j], cc[j]));
+        for (int k = 0; k < K; ++k) {
+            if (i + k >= cnt) break;
+            float f[8], d[8], m[8], sc[8];
+            unpack8(xv[k], f);
+            unpack8(dv[k], d);
+            lds8(psc, sc);
+            if (kMask) {
+                unpack8(mv[k], m);
+            } else if (relu) {
+                float sh[8];
+                lds8(psc + cw, sh);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) m[j] = fmaf(f[j], sc[j], sh[j]);
+            }
+            float cb[8], cc[8];
+            lds8(psc + 2 * cw, cb);
+            lds8(psc + 3 * cw, cc);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float dz = (relu && m[j] <= 0.f) ? 0.f : d[j];
+                f[j] = fmaf(sc[j], dz, fmaf(cb[j], f[j], cc[j]));
+            }
+            st128(op + k * os, pack8(f));
         }
-        st128(ob + p * dx_ct, pack8(f));
     }
 }
 
@@ -590,12 +706,22 @@ int b200seg_bn_apply_add(const void* x, int x_c_total, int x_c_offset, void* y, 
     B200SEG_CHECK(scale && shift && pixels > 0, "bn_apply: bad arguments");
     B200SEG_CHECK((res_scale == nullptr) == (res_shift == nullptr), "bn_apply: residual scale and shift go together");
     const ColGeom g = col_geom(c, pixels, 16);
-#define B200SEG_BN_APPLY(RA, BITS)     B200SEG_CUDA(launch_pdl(bn_apply_kernel<RA, BITS>, dim3(g.gx, g.gy), kRedThreads, 0, static_cast<cudaStream_t>(stream),  \
+    static const int kk = bn_env_k("B200SEG_BN_K_APPLY", 4);
+#define B200SEG_BN_APPLY_K(RA, BITS, K)     B200SEG_CUDA(launch_pdl(bn_apply_kernel<RA, BITS, K>, dim3(g.gx, g.gy), kRedThreads, sizeof(float) * 8 * g.gpb * ((RA) == 2 ? 4 : 2), static_cast<cudaStream_t>(stream),  \
         static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset, \
         c / 8, pixels, g.pixels_per_block, g.gpb, g.rows, scale, shift, relu, static_cast<const __nv_bfloat16*>(res), \
         res_c_total, res_c_offset, res_scale, res_shift, BnTrain{}));
-    if (res && res_scale) B200SEG_BN_APPLY(true, false) else B200SEG_BN_APPLY(false, false)
+    /* loads in flight per thread = K x streams: 4 without a residual, 2 x 2 with one, 1 x 2 with an affine residual (its */ \
+    /* two extra parameter rows leave no registers for more at four resident CTAs per SM) */
+#define B200SEG_BN_APPLY(RA, BITS)                                                                         \
+    {                                                                                                      \
+        const int ke = (RA) == 0 ? kk : ((RA) == 1 ? (kk >= 2 ? 2 : 1) : 1);                               \
+        if (ke == 4) B200SEG_BN_APPLY_K(RA, BITS, 4) else if (ke == 2) B200SEG_BN_APPLY_K(RA, BITS, 2)     \
+        else B200SEG_BN_APPLY_K(RA, BITS, 1)                                                               \
+    }
+    if (res && res_scale) B200SEG_BN_APPLY(2, false) else if (res) B200SEG_BN_APPLY(1, false) else B200SEG_BN_APPLY(0, false)
 #undef B200SEG_BN_APPLY
+#undef B200SEG_BN_APPLY_K
     return 0;
 }
 
@@ -626,15 +752,26 @@ int b200seg_bn_apply_train(const void* x, int x_c_total, int x_c_offset, void* y
     tr.vec = vec;
     tr.bits = mask_bits;
     const ColGeom g = col_geom(c, pixels, 16);
-#define B200SEG_BN_APPLY(RA, BITS)     B200SEG_CUDA(launch_pdl(bn_apply_kernel<RA, BITS>, dim3(g.gx, g.gy), kRedThreads, 0, static_cast<cudaStream_t>(stream), \
+    static const int kk = bn_env_k("B200SEG_BN_K_APPLY", 4);
+#define B200SEG_BN_APPLY_K(RA, BITS, K)     B200SEG_CUDA(launch_pdl(bn_apply_kernel<RA, BITS, K>, dim3(g.gx, g.gy), kRedThreads, sizeof(float) * 8 * g.gpb * ((RA) == 2 ? 4 : 2), static_cast<cudaStream_t>(stream), \
         static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset, \
         c / 8, pixels, g.pixels_per_block, g.gpb, g.rows, static_cast<const float*>(nullptr), \
         static_cast<const float*>(nullptr), relu, static_cast<const __nv_bfloat16*>(res), res_c_total, res_c_offset, \
         res_scale, res_shift, tr));
-    const bool ra = res && res_scale;
-    if (ra && mask_bits) B200SEG_BN_APPLY(true, true) else if (ra) B200SEG_BN_APPLY(true, false)
-    else if (mask_bits) B200SEG_BN_APPLY(false, true) else B200SEG_BN_APPLY(false, false)
+    /* loads in flight per thread = K x streams: 4 without a residual, 2 x 2 with one, 1 x 2 with an affine residual (its */ \
+    /* two extra parameter rows leave no registers for more at four resident CTAs per SM) */
+#define B200SEG_BN_APPLY(RA, BITS)                                                                         \
+    {                                                                                                      \
+        const int ke = (RA) == 0 ? kk : ((RA) == 1 ? (kk >= 2 ? 2 : 1) : 1);                               \
+        if (ke == 4) B200SEG_BN_APPLY_K(RA, BITS, 4) else if (ke == 2) B200SEG_BN_APPLY_K(RA, BITS, 2)     \
+        else B200SEG_BN_APPLY_K(RA, BITS, 1)                                                               \
+    }
+    const int ra = res ? (res_scale ? 2 : 1) : 0;
+    if (ra == 2 && mask_bits) B200SEG_BN_APPLY(2, true) else if (ra == 2) B200SEG_BN_APPLY(2, false)
+    else if (ra == 1 && mask_bits) B200SEG_BN_APPLY(1, true) else if (ra == 1) B200SEG_BN_APPLY(1, false)
+    else if (mask_bits) B200SEG_BN_APPLY(0, true) else B200SEG_BN_APPLY(0, false)
 #undef B200SEG_BN_APPLY
+#undef B200SEG_BN_APPLY_K
     return 0;
 }
 
@@ -761,10 +898,16 @@ static int bn_bwd_reduce_impl(bool zero_red, const void* dy, int dy_c_total, int
         return v > 0 ? v : 4;
     }();
     const ColGeom g = col_geom(c, pixels, ctas);
-    B200SEG_CUDA(launch_pdl(bn_bwd_reduce_kernel, dim3(g.gx, g.gy), kRedThreads, 0, st, 
-        static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, static_cast<const __nv_bfloat16*>(x), x_c_total,
-        x_c_offset, c, pixels, g.pixels_per_block, g.gpb, g.rows, scale, shift, save_mean, save_invstd, relu, red,
+    static const int kk = bn_env_k("B200SEG_BN_K_RED", 2);
+#define B200SEG_BN_RED_(K, M)                                                                                                  \
+    B200SEG_CUDA(launch_pdl(bn_bwd_reduce_kernel<K, M>, dim3(g.gx, g.gy), kRedThreads, sizeof(float) * 16 * g.gpb, st,                                  \
+        static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, static_cast<const __nv_bfloat16*>(x), x_c_total,     \
+        x_c_offset, c, pixels, g.pixels_per_block, g.gpb, g.rows, scale, shift, save_mean, save_invstd, relu, red,           \
         static_cast<const __nv_bfloat16*>(mask), mask_c_total, mask_c_offset));
+#define B200SEG_BN_RED(K) { if (mask) B200SEG_BN_RED_(K, true) else B200SEG_BN_RED_(K, false) }
+    if (kk == 4) B200SEG_BN_RED(4) else if (kk == 2) B200SEG_BN_RED(2) else B200SEG_BN_RED(1)
+#undef B200SEG_BN_RED
+#undef B200SEG_BN_RED_
     return 0;
 }
 
@@ -809,12 +952,17 @@ int b200seg_bn_bwd_apply_masked(const void* dy, int dy_c_total, int dy_c_offset,
     if (mask && check_slice("bn_bwd_apply(mask)", mask, mask_c_total, mask_c_offset, c)) return 1;
     B200SEG_CHECK(scale && shift && save_mean && save_invstd && red && pixels > 0, "bn_bwd_apply: bad arguments");
     const ColGeom g = col_geom(c, pixels, 16);
-    B200SEG_CUDA(launch_pdl(bn_bwd_apply_kernel, dim3(g.gx, g.gy), kRedThreads, 0, st, 
-        static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, static_cast<const __nv_bfloat16*>(x), x_c_total,
-        x_c_offset, static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, c / 8, pixels, g.pixels_per_block, g.gpb,
-        g.rows, static_cast<float>(1.0 / static_cast<double>(pixels)), scale, shift, save_mean, save_invstd, relu, training,
-        red, c,
-        static_cast<const __nv_bfloat16*>(mask), mask_c_total, mask_c_offset));
+    static const int kk = bn_env_k("B200SEG_BN_K_BWD", 2);
+#define B200SEG_BN_BWD_(K, M)                                                                                                  \
+    B200SEG_CUDA(launch_pdl(bn_bwd_apply_kernel<K, M>, dim3(g.gx, g.gy), kRedThreads, sizeof(float) * 32 * g.gpb, st,                                  \
+        static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, static_cast<const __nv_bfloat16*>(x), x_c_total,     \
+        x_c_offset, static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, c / 8, pixels, g.pixels_per_block, g.gpb,      \
+        g.rows, static_cast<float>(1.0 / static_cast<double>(pixels)), scale, shift, save_mean, save_invstd, relu, training, \
+        red, c, static_cast<const __nv_bfloat16*>(mask), mask_c_total, mask_c_offset));
+#define B200SEG_BN_BWD(K) { if (mask) B200SEG_BN_BWD_(K, true) else B200SEG_BN_BWD_(K, false) }
+    if (kk == 4) B200SEG_BN_BWD(4) else if (kk == 2) B200SEG_BN_BWD(2) else B200SEG_BN_BWD(1)
+#undef B200SEG_BN_BWD
+#undef B200SEG_BN_BWD_
     if (dgamma || dbeta) {
         B200SEG_CUDA(launch_pdl(bn_param_grad_kernel, ceil_div(c, 128), 128, 0, st, red, c, dgamma, dbeta, accumulate_param_grads));
     }
