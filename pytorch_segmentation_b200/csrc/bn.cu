@@ -31,10 +31,13 @@ struct ColGeom {
     int gx;
 };
 
-ColGeom col_geom(int c, int64_t pixels, int ctas_per_sm = 8) {
+// max_gpb: widest channel span of one block.  A REDUCTION ends with one atomic per channel per block, so total atomics =
+// blocks x channels-per-block: spanning 32 groups (a warp reads 512 contiguous bytes of a pixel) instead of the whole
+// row cuts them 4-8x on the 1024 / 2048-channel tensors and lets the grid's second dimension cover the rest.
+ColGeom col_geom(int c, int64_t pixels, int ctas_per_sm = 8, int max_gpb = kRedThreads) {
     ColGeom g;
     g.groups = c / 8;
-    g.gpb = g.groups < kRedThreads ? g.groups : kRedThreads;
+    g.gpb = g.groups < max_gpb ? g.groups : max_gpb;
     g.rows = kRedThreads / g.gpb;
     g.gy = ceil_div(g.groups, g.gpb);
     int sms = sm_count();
@@ -897,7 +900,12 @@ static int bn_bwd_reduce_impl(bool zero_red, const void* dy, int dy_c_total, int
         const int v = e ? atoi(e) : 4;
         return v > 0 ? v : 4;
     }();
-    const ColGeom g = col_geom(c, pixels, ctas);
+    static const int red_gpb = [] {
+        const char* e = getenv("B200SEG_BNRED_GPB");
+        const int v = e ? atoi(e) : 32;
+        return v >= 8 && v <= 256 ? v : 32;
+    }();
+    const ColGeom g = col_geom(c, pixels, ctas, red_gpb);
     static const int kk = bn_env_k("B200SEG_BN_K_RED", 2);
 #define B200SEG_BN_RED_(K, M)                                                                                                  \
     B200SEG_CUDA(launch_pdl(bn_bwd_reduce_kernel<K, M>, dim3(g.gx, g.gy), kRedThreads, sizeof(float) * 16 * g.gpb, st,                                  \
@@ -952,7 +960,7 @@ int b200seg_bn_bwd_apply_masked(const void* dy, int dy_c_total, int dy_c_offset,
     if (mask && check_slice("bn_bwd_apply(mask)", mask, mask_c_total, mask_c_offset, c)) return 1;
     B200SEG_CHECK(scale && shift && save_mean && save_invstd && red && pixels > 0, "bn_bwd_apply: bad arguments");
     const ColGeom g = col_geom(c, pixels, 16);
-    static const int kk = bn_env_k("B200SEG_BN_K_BWD", 2);
+    static const int kk = bn_env_k("B200SEG_BN_K_BWD", 1);
 #define B200SEG_BN_BWD_(K, M)                                                                                                  \
     B200SEG_CUDA(launch_pdl(bn_bwd_apply_kernel<K, M>, dim3(g.gx, g.gy), kRedThreads, sizeof(float) * 32 * g.gpb, st,                                  \
         static_cast<const __nv_bfloat16*>(dy), dy_c_total, dy_c_offset, static_cast<const __nv_bfloat16*>(x), x_c_total,     \

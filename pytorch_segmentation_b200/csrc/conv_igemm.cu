@@ -22,7 +22,10 @@
 
 #include <string.h>
 
+#include <stdlib.h>
+
 #include <array>
+#include <atomic>
 #include <map>
 #include <mutex>
 #include <vector>
@@ -80,6 +83,7 @@ struct __align__(64) IgemmParams {
     long long* dbg;
     int dbg_slots;
     int no_skip;             // anchored window sources: the buffer carries its own padding, every tap is in bounds
+    int* sched;              // dynamic tile scheduler: {next tile - gridDim.x, CTAs done}; nullptr = static striding
 };
 
 long long* g_dbg = nullptr;
@@ -101,9 +105,12 @@ struct TileCoord {
 };
 
 __device__ __forceinline__ TileCoord decode_tile(const IgemmParams& p, int tile) {
+    // n_tile is the SLOWEST index: a CTA's consecutive tiles (static stride or dynamic) then share their output-channel
+    // block, so the per-channel BN statistics it carries in registers are flushed once per block, not once per tile
     TileCoord t;
-    t.n_tile = tile % p.tiles_n;
-    int m = tile / p.tiles_n;
+    const int m_tiles = p.tiles_x * p.tiles_y * p.tiles_i;
+    t.n_tile = tile / m_tiles;
+    int m = tile - t.n_tile * m_tiles;
     t.x0 = (m % p.tiles_x) * p.bw;
     m /= p.tiles_x;
     t.y0 = (m % p.tiles_y) * p.bh;
@@ -125,7 +132,10 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     uint64_t* empty = bars + kStages;         // [kStages] MMA -> TMA
     uint64_t* tfull = bars + 2 * kStages;     // [2] MMA -> epilogue
     uint64_t* tempty = bars + 2 * kStages + 2;   // [2] epilogue -> MMA
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+    uint64_t* sfull = bars + 2 * kStages + 4;    // [2] scheduler (the producer thread) -> MMA + epilogue: a tile id is posted
+    uint64_t* sempty = bars + 2 * kStages + 6;   // [2] MMA + epilogue warps -> scheduler: the slot was read
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 8);
+    volatile int* sched_tile = reinterpret_cast<volatile int*>(tmem_slot + 1);      // [2] posted tile ids (-1 = no more)
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
@@ -144,6 +154,8 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tfull[i], 1);
             mbar_init(&tempty[i], p.out_fp32 ? 4 : 8);
+            mbar_init(&sfull[i], 1);
+            mbar_init(&sempty[i], p.out_fp32 ? 5 : 9);      // the MMA thread + one lane per epilogue warp
         }
         fence_barrier_init();
     }
@@ -166,7 +178,24 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
             int stage = 0;
             uint32_t phase = 0;
             const uint32_t tx_bytes = kABytes + p.bn * kBK * 2;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+            // This thread is also the CTA's TILE SCHEDULER.  The first tile is blockIdx.x; every later one comes from a
+            // global counter (atomicAdd) instead of a static stride, so a CTA that starts late or runs on a shared SM
+            // (weight-gradient kernels on the side stream, NCCL under data parallelism) simply takes fewer tiles instead
+            // of holding the launch's tail.  Tile ids reach the MMA and epilogue warps through a two-slot mailbox.
+            int slot = 0;
+            uint32_t sphase = 0;
+            int tile = blockIdx.x;
+            for (;;) {
+                mbar_wait(&sempty[slot], sphase ^ 1);
+                sched_tile[slot] = tile < p.num_tiles ? tile : -1;
+                mbar_arrive(&sfull[slot]);
+                if (++slot == 2) {
+                    slot = 0;
+                    sphase ^= 1;
+                }
+                if (tile >= p.num_tiles) break;
+                // the next id is requested before this tile's loads are issued: the atomic's latency hides under them
+                const int next = p.sched ? atomicAdd(p.sched, 1) + static_cast<int>(gridDim.x) : tile + static_cast<int>(gridDim.x);
                 const TileCoord t = decode_tile(p, tile);
                 for (int sg = 0; sg < p.nseg; ++sg) {
                     const IgemmSeg& seg = p.seg[sg];
@@ -187,6 +216,16 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
                         }
                     }
                 }
+                tile = next;
+            }
+            if (p.sched) {
+                // the last CTA to run out of tiles leaves the counters zeroed for the next launch that uses this slot
+                __threadfence();
+                if (atomicAdd(p.sched + 1, 1) == static_cast<int>(gridDim.x) - 1) {
+                    p.sched[0] = 0;
+                    p.sched[1] = 0;
+                    __threadfence();
+                }
             }
         }
     } else if (warp == 1) {
@@ -196,7 +235,17 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
             int stage = 0;
             uint32_t phase = 0;
             int lt = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++lt) {
+            int slot = 0;
+            uint32_t sphase = 0;
+            for (;; ++lt) {
+                mbar_wait(&sfull[slot], sphase);
+                const int tile = sched_tile[slot];
+                mbar_arrive(&sempty[slot]);
+                if (++slot == 2) {
+                    slot = 0;
+                    sphase ^= 1;
+                }
+                if (tile < 0) break;
                 const TileCoord t = decode_tile(p, tile);
                 int kiters = 0;
                 for (int sg = 0; sg < p.nseg; ++sg) {
@@ -281,7 +330,18 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
                 named_bar_sync(1, kEpiThreads);      // red[] is read before the next slab is staged over it
             };
             int lt = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++lt) {
+            int slot = 0;
+            uint32_t sphase = 0;
+            for (;; ++lt) {
+                mbar_wait(&sfull[slot], sphase);
+                const int tile = sched_tile[slot];
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sempty[slot]);
+                if (++slot == 2) {
+                    slot = 0;
+                    sphase ^= 1;
+                }
+                if (tile < 0) break;
                 const TileCoord t = decode_tile(p, tile);
                 const int acc = lt & 1;
                 const uint32_t acc_phase = (lt >> 1) & 1;
@@ -408,7 +468,18 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
         } else if (warp < 8) {
             // fp32 class map (cls_conv): direct stores, four warps
             int lt = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++lt) {
+            int slot = 0;
+            uint32_t sphase = 0;
+            for (;; ++lt) {
+                mbar_wait(&sfull[slot], sphase);
+                const int tile = sched_tile[slot];
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sempty[slot]);
+                if (++slot == 2) {
+                    slot = 0;
+                    sphase ^= 1;
+                }
+                if (tile < 0) break;
                 const TileCoord t = decode_tile(p, tile);
                 const int acc = lt & 1;
                 const uint32_t acc_phase = (lt >> 1) & 1;
@@ -473,6 +544,32 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
         tc_fence_after();
         tmem_dealloc(tmem_base, kTmemCols);
     }
+}
+
+// Dynamic tile scheduler state: a ring of {tile counter, done counter} pairs, one pair per launch (a launch leaves its
+// pair zeroed; consecutive launches, which programmatic dependent launch lets overlap, never share one).  Allocated on
+// first use — which must not be inside a stream capture (trainer.TrainStep runs eager steps before it captures).
+constexpr int kSchedSlots = 2048;
+int* sched_slot() {
+    static int* ring = nullptr;
+    static std::once_flag once;
+    static std::atomic<unsigned> seq{0};
+    static const bool on = [] {
+        const char* e = getenv("B200SEG_IGEMM_DYNAMIC");
+        return !(e && e[0] == '0');
+    }();
+    if (!on) return nullptr;
+    std::call_once(once, [] {
+        int* p = nullptr;
+        if (cudaMalloc(&p, sizeof(int) * 2 * kSchedSlots) == cudaSuccess && cudaMemset(p, 0, sizeof(int) * 2 * kSchedSlots) == cudaSuccess) {
+            cudaDeviceSynchronize();
+            ring = p;
+        } else {
+            cudaGetLastError();
+        }
+    });
+    if (!ring) return nullptr;
+    return ring + 2 * (seq.fetch_add(1) % kSchedSlots);
 }
 
 int ilog2(int v) {
@@ -625,6 +722,7 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
     const int sms = gemm_sm_count();
     B200SEG_CHECK(sms > 0, "conv: cannot query SM count");
     const int grid = p.num_tiles < sms ? p.num_tiles : sms;
+    p.sched = p.num_tiles > grid ? sched_slot() : nullptr;       // a single wave has nothing to schedule
     B200SEG_CUDA(launch_pdl(igemm_kernel, grid, kThreads, kSmemBytes, st, p));
     return 0;
 }

@@ -8,8 +8,11 @@
 // M-side tensor (2 boxes = 128 rows of D) and of the N-side tensor (bn/64 boxes), the X boxes shifted by the
 // tap offset with out-of-bounds pixels zero-filled (that is the padding).  Patches whose shifted window is
 // entirely padding are skipped.  The reduction is split across CTAs (split-K) when taps x tiles alone do not
-// fill the GPU; partials go to a caller-provided fp32 workspace and a second kernel reduces them in a fixed
-// order (deterministic) while scattering into the OIHW fp32 gradient.
+// fill the GPU.  The split CTAs of one output tile form a thread-block CLUSTER (2, 4 or 8 CTAs): each drains its TMEM
+// accumulator into its own shared memory, and after a cluster barrier CTA r sums column slice r of all ranks through
+// distributed shared memory in rank order (deterministic) — on chip, no workspace round trip.  With splits <= cluster
+// size the sums go straight into the OIHW fp32 gradient from the epilogue; only beyond that do per-cluster partials go
+// to a caller-provided fp32 workspace for a (now 2-8x smaller) fixed-order second-stage reduce.
 //
 // The M side is whichever of (dY, X) has more channels to tile by 128; the other is the N side (<= 256 per
 // tile).  For cls_conv (21 classes) that puts X's 384 channels on M and the padded 32 classes on N.
@@ -54,7 +57,20 @@ struct __align__(64) WgradParams {
     int tap_group;         // filter taps per CTA (>1 only with X on the N side): the taps' shifted X boxes sit side by
                            // side as one N = tap_group * bn operand, so the dY boxes are loaded once per group
     int no_skip;           // anchored window X: the buffer carries its own padding, every (tap, patch) is in bounds
+    int cs;                // cluster size along the split dimension (1 = no cluster); splits = splits_hi * cs
+    int direct;            // 1: this launch's sums are final — write dw (fp32 OIHW) from the epilogue, no workspace
+    float* dw;
+    int k_out, c_in, accumulate;
 };
+
+// final element (m, n) of filter tap `tap` -> dw[k][c][tap] (+)= v        (m, n) = (c, k) with X on the M side, else (k, c)
+__device__ __forceinline__ void wgrad_store_final(const WgradParams& p, int taps, int tap, int m, int n, float v) {
+    const int kk = p.shift_m ? n : m, cc = p.shift_m ? m : n;
+    if (kk < p.k_out && cc < p.c_in) {
+        float* d = p.dw + (static_cast<size_t>(kk) * p.c_in + cc) * taps + tap;
+        *d = p.accumulate ? *d + v : v;
+    }
+}
 
 // Walks the pixel patches kp = begin, begin+1, ... with running (x, y, image) patch counters: the producer and the
 // MMA issuer are single threads, so a division per pipeline stage would sit on the critical path.
@@ -98,8 +114,9 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
-    // tile decode: n_tile fastest, then m_tile, tap, split
-    int tile = blockIdx.x;
+    // tile decode: cluster rank (low part of the split index) fastest, then n_tile, m_tile, tap, split (high part)
+    const int rank = p.cs > 1 ? static_cast<int>(blockIdx.x % p.cs) : 0;
+    int tile = blockIdx.x / p.cs;
     const int n_tile = tile % p.tiles_n;
     tile /= p.tiles_n;
     const int m_tile = tile % p.tiles_m;
@@ -109,7 +126,8 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
     const int ngroups = (taps + G - 1) / G;
     const int tap = (tile % ngroups) * G;          // first tap of this CTA's group
     const int gt = min(G, taps - tap);             // taps in the group
-    const int split = tile / ngroups;
+    const int split_hi = tile / ngroups;
+    const int split = split_hi * p.cs + rank;
     const int dy = p.tap_dy[tap];
     const int dx = p.tap_dx[tap];
     const CUtensorMap* xm = &p.x_map[p.tap_map[tap]];
@@ -242,24 +260,95 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
         mbar_wait(tfull, 0);
         tc_fence_after();
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-        for (int g = 0; g < gt; ++g) {
-            // tap g of the group: accumulator columns [g * bn, (g + 1) * bn) -> its own plane of the workspace
-            float* dst = p.ws + ((static_cast<size_t>(split) * taps + tap + g) * p.m_pad + (m_tile * kBM + row)) * p.n_pad +
-                         n_tile * p.bn;
-            for (int ch = 0; ch < p.bn; ch += 32) {
+        if (p.cs > 1) {
+            // stage the accumulator tile in this CTA's shared memory (the pipeline stages are idle: every MMA has
+            // completed), column-major [col][128 rows] so lanes write consecutive words; the cluster reduces it below
+            float* stage_buf = reinterpret_cast<float*>(smem);
+            for (int col = 0; col < gt * p.bn; col += 32) {
                 uint32_t v[32];
                 if (any) {
-                    tmem_ld_32x32(taddr + g * p.bn + ch, v);
+                    tmem_ld_32x32(taddr + col, v);
                     tmem_ld_wait();
                 } else {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = 0;
                 }
 #pragma unroll
-                for (int j = 0; j < 32; j += 4)
-                    *reinterpret_cast<uint4*>(dst + ch + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                for (int j = 0; j < 32; ++j) stage_buf[(col + j) * kBM + row] = __uint_as_float(v[j]);
+            }
+        } else if (p.direct) {
+            // a single split: the accumulator IS the gradient
+            for (int g = 0; g < gt; ++g)
+                for (int ch = 0; ch < p.bn; ch += 32) {
+                    uint32_t v[32];
+                    if (any) {
+                        tmem_ld_32x32(taddr + g * p.bn + ch, v);
+                        tmem_ld_wait();
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = 0;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        wgrad_store_final(p, taps, tap + g, m_tile * kBM + row, n_tile * p.bn + ch + j, __uint_as_float(v[j]));
+                }
+        } else {
+            for (int g = 0; g < gt; ++g) {
+                // tap g of the group: accumulator columns [g * bn, (g + 1) * bn) -> its own plane of the workspace
+                float* dst = p.ws + ((static_cast<size_t>(split) * taps + tap + g) * p.m_pad + (m_tile * kBM + row)) * p.n_pad +
+                             n_tile * p.bn;
+                for (int ch = 0; ch < p.bn; ch += 32) {
+                    uint32_t v[32];
+                    if (any) {
+                        tmem_ld_32x32(taddr + g * p.bn + ch, v);
+                        tmem_ld_wait();
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = 0;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4)
+                        *reinterpret_cast<uint4*>(dst + ch + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                }
             }
         }
+    }
+
+    if (p.cs > 1) {
+        // ---- split-K reduction on chip: CTA `rank` owns accumulator columns [rank * wc, (rank + 1) * wc) and adds them
+        // up over the cluster's ranks in rank order through distributed shared memory
+        __syncwarp();
+        cluster_sync_all();
+        if (warp >= 4) {
+            const int row = (warp & 3) * 32 + lane;
+            const int wtot = gt * p.bn, wc = wtot / p.cs;           // bn is a multiple of 64, cs of {2, 4, 8}
+            const uint32_t local = smem_u32(smem);
+            uint32_t peer[8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r) peer[r] = r < p.cs ? dsmem_addr(local, r) : 0u;
+            for (int col = rank * wc; col < (rank + 1) * wc; col += 4) {
+                float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    if (r < p.cs) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) acc[j] += dsmem_ld_f32(peer[r] + ((col + j) * kBM + row) * 4);
+                    }
+                }
+                const int g = col / p.bn, ch = col - g * p.bn;      // 4 consecutive columns never straddle a tap
+                if (p.direct) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        wgrad_store_final(p, taps, tap + g, m_tile * kBM + row, n_tile * p.bn + ch + j, acc[j]);
+                } else {
+                    float* dst = p.ws + ((static_cast<size_t>(split_hi) * taps + tap + g) * p.m_pad + (m_tile * kBM + row)) * p.n_pad +
+                                 n_tile * p.bn + ch;
+                    *reinterpret_cast<float4*>(dst) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+                }
+            }
+        }
+        __syncwarp();
+        cluster_sync_all();          // nobody leaves while a peer still reads its shared memory
     }
 
     tc_fence_before();
@@ -306,6 +395,24 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restr
     *d = accumulate ? (*d + acc) : acc;
 }
 
+bool cluster_reduce_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("B200SEG_WGRAD_CLUSTER");
+        return !(e && e[0] == '0');
+    }();
+    return on;
+}
+
+bool direct_write_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("B200SEG_WGRAD_DIRECT");
+        return !(e && e[0] == '0');
+    }();
+    return on;
+}
+
+int cluster_capacity(int cs);
+
 bool tap_grouping_enabled() {
     static const bool on = [] {
         const char* e = getenv("B200SEG_WGRAD_TAPGROUP");
@@ -314,8 +421,49 @@ bool tap_grouping_enabled() {
     return on;
 }
 
+void set_wgrad_attrs() {
+    static std::once_flag once;
+    std::call_once(once, [] {
+        cudaFuncSetAttribute(wgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+        cudaFuncSetAttribute(wgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+    });
+}
+
+// co-resident clusters of `cs` CTAs of this kernel (one CTA per SM: ~193 KB of shared memory) — asked of the driver once
+int cluster_capacity(int cs) {
+    static std::mutex mu;
+    static std::map<int, int> memo;
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = memo.find(cs);
+    if (it != memo.end()) return it->second;
+    set_wgrad_attrs();
+    int sms = gemm_sm_count();
+    if (sms <= 0) sms = 148;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(static_cast<unsigned>(sms / cs * cs));
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = kSmemBytes;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cs;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, wgrad_kernel<false>, &cfg) != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        n = sms / cs * 3 / 4;          // conservative guess: GPCs of ~18 SMs leave a remainder per cluster size
+    }
+    const int lim = sms / cs;
+    if (n > lim) n = lim;
+    memo[cs] = n;
+    return n;
+}
+
 struct WgradPlan {
     int shift_m, bw, bh, bi, patches_x, patches_y, patches_i, tiles_m, tiles_n, bn, splits, pps, m_pad, n_pad, tap_group;
+    int cs, splits_hi, direct;             // cluster size along the splits, workspace planes, epilogue writes dw itself
     size_t ws_bytes;
     long long iters_run, iters_dense;      // (tap, patch) pairs with / without the all-padding ones skipped
 };
@@ -397,13 +545,38 @@ int plan_wgrad_uncached(const b200seg_wgrad_desc* d, WgradPlan* pl) {
     const int base_tiles = ceil_div(taps, pl->tap_group) * pl->tiles_m * pl->tiles_n;
     int sms = gemm_sm_count();
     if (sms <= 0) sms = 148;
-    int splits = sms / base_tiles;
-    if (splits < 1) splits = 1;
+    int want = sms / base_tiles;                    // splits that fill the GPU once
+    if (want < 1) want = 1;
     const int max_splits = patches / 8 > 0 ? patches / 8 : 1;
-    if (splits > max_splits) splits = max_splits;
+    if (want > max_splits) want = max_splits;
+    // Cluster size along the splits: clusters are placed inside one GPC, so fewer CTAs are co-resident the larger the
+    // cluster (cluster_capacity asks the driver); take the largest cluster that keeps >= 80 % of the CTAs a plain launch
+    // would have — the on-chip reduction is worth more than the last few SMs on these HBM-bound launches
+    pl->cs = 1;
+    pl->splits_hi = want;
+    if (want >= 2 && cluster_reduce_enabled()) {
+        for (int cs = 8; cs >= 2; cs /= 2) {
+            if (cs > want) continue;
+            const int cap = cluster_capacity(cs);                  // co-resident clusters of this size
+            int hi = cap / base_tiles;
+            if (hi > want / cs) hi = want / cs;
+            if (hi < 1) continue;
+            if (static_cast<long long>(base_tiles) * hi * cs * 10 >= static_cast<long long>(base_tiles) * want * 8) {
+                pl->cs = cs;
+                pl->splits_hi = hi;
+                break;
+            }
+        }
+    }
+    int splits = pl->splits_hi * pl->cs;
     pl->pps = ceil_div(patches, splits);
-    pl->splits = ceil_div(patches, pl->pps);
-    pl->ws_bytes = static_cast<size_t>(pl->splits) * d->r * d->s * pl->m_pad * pl->n_pad * sizeof(float);
+    if (pl->cs == 1) {
+        splits = ceil_div(patches, pl->pps);        // drop empty tail splits
+        pl->splits_hi = splits;
+    }
+    pl->splits = splits;
+    pl->direct = pl->splits_hi == 1 && direct_write_enabled() ? 1 : 0;
+    pl->ws_bytes = pl->direct ? 256 : static_cast<size_t>(pl->splits_hi) * d->r * d->s * pl->m_pad * pl->n_pad * sizeof(float);
     return 0;
 }
 
@@ -535,23 +708,26 @@ int b200seg_conv_wgrad(const b200seg_wgrad_desc* d, b200seg_stream_t stream) {
             }
         }
 
-    static bool attr_set = false;
-    if (!attr_set) {
-        B200SEG_CUDA(cudaFuncSetAttribute(wgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        B200SEG_CUDA(cudaFuncSetAttribute(wgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        attr_set = true;
-    }
+    set_wgrad_attrs();
+    p.cs = pl.cs;
+    p.direct = pl.direct;
+    p.dw = static_cast<float*>(d->dw);
+    p.k_out = d->k_out;
+    p.c_in = d->c;
+    p.accumulate = d->accumulate;
+    p.splits = pl.splits;
     const int taps = d->r * d->s;
     const int grid = pl.splits * ceil_div(taps, pl.tap_group) * pl.tiles_m * pl.tiles_n;
     if (pl.tap_group > 1)
-        B200SEG_CUDA(launch_pdl(wgrad_kernel<true>, grid, kThreads, kSmemBytes, st, p));
+        B200SEG_CUDA(launch_pdl_cluster(wgrad_kernel<true>, grid, kThreads, kSmemBytes, st, pl.cs, p));
     else
-        B200SEG_CUDA(launch_pdl(wgrad_kernel<false>, grid, kThreads, kSmemBytes, st, p));
+        B200SEG_CUDA(launch_pdl_cluster(wgrad_kernel<false>, grid, kThreads, kSmemBytes, st, pl.cs, p));
+    if (pl.direct) return 0;
 
     const long long total = static_cast<long long>(d->k_out) * d->c * taps;
     const int rb = 256;
-    B200SEG_CUDA(launch_pdl(wgrad_reduce_kernel, static_cast<unsigned>((total + rb - 1) / rb), rb, 0, st, 
-        p.ws, d->dw, d->k_out, d->c, taps, pl.splits, pl.m_pad, pl.n_pad, pl.shift_m, d->accumulate));
+    B200SEG_CUDA(launch_pdl(wgrad_reduce_kernel, static_cast<unsigned>((total + rb - 1) / rb), rb, 0, st,
+        p.ws, d->dw, d->k_out, d->c, taps, pl.splits_hi, pl.m_pad, pl.n_pad, pl.shift_m, d->accumulate));
     return 0;
 }
 

@@ -61,7 +61,6 @@ def main():
     peak_tf, peak_gb = pk['bf16_tflops_sustained'], pk['hbm_gbs']
     flush = torch.zeros(64 << 20, dtype=torch.float32, device='cuda')      # 256 MB, read (not written): clean lines
     cases = {'head': HEAD, 'backbone': BACKBONE, 'all': HEAD + BACKBONE}[args.set]
-    has_stride = 'stride' in E.conv_fprop.__code__.co_varnames
 
     def timed(fn):
         for _ in range(3):
@@ -90,8 +89,6 @@ def main():
     out = []
     print('%-16s %-6s %9s %9s %6s %8s %6s' % ('conv', 'pass', 'us', 'TFLOP/s', 'frac', 'GB/s', 'frac'))
     for name, n, h, w, c, k, ks, dil, stride in cases:
-        if stride != 1 and not has_stride:
-            continue
         oh, ow = h // stride, w // stride
         x = E.Act(torch.randn(n, h, w, c, device='cuda').to(torch.bfloat16))
         wt = torch.randn(k, c, ks, ks, device='cuda') * (2.0 / (c * ks * ks)) ** 0.5
@@ -100,15 +97,14 @@ def main():
         dy = E.Act(torch.randn(n, oh, ow, k, device='cuda').to(torch.bfloat16))
         dx = E.Act.empty(n, h, w, c, 'cuda')
         stats = torch.zeros(2 * k, device='cuda')
-        kw = {'stride': stride} if has_stride else {}
         flops = 2.0 * n * oh * ow * k * c * ks * ks
         byts = {'fprop0': 2.0 * (x.t.numel() + y.t.numel() + wt.numel()), 'fprop': 2.0 * (x.t.numel() + y.t.numel() + wt.numel()),
                 'dgrad': 2.0 * (x.t.numel() + y.t.numel() + wt.numel()),
                 'wgrad': 2.0 * (x.t.numel() + y.t.numel()) + 4.0 * wt.numel()}
-        fns = {'fprop0': lambda: E.conv_fprop([(x, pw, dil)], y, **kw),
-               'fprop': lambda: E.conv_fprop([(x, pw, dil)], y, stats=stats, **kw),
-               'dgrad': lambda: E.conv_dgrad([(dy, pw, dil)], dx, **kw),
-               'wgrad': lambda: E.conv_wgrad(dy, x, k, ks, ks, dil, **kw)}
+        fns = {'fprop0': lambda: E.conv_fprop([(x, pw, dil, stride)], y),
+               'fprop': lambda: E.conv_fprop([(x, pw, dil, stride)], y, stats=stats),
+               'dgrad': lambda: E.conv_dgrad([(dy, pw, dil, stride)], dx),
+               'wgrad': lambda: E.conv_wgrad(dy, x, k, ks, ks, dil, stride=stride)}
         for what, fn in fns.items():
             us = timed(fn)
             tf, gb = flops / us / 1e6, byts[what] / us / 1e3

@@ -6,7 +6,7 @@ import torch
 from pytorch_segmentation_b200 import _lib, engine as E
 lib = _lib.load()
 names = ['ld_issue->ld_done', 'bar1', 'cvt+sts', 'fence', 'bar2', 'tma+wait', 'stats', 'next']
-for (n, h, w, c, k, with_stats) in [(16, 128, 128, 64, 256, 0), (16, 128, 128, 64, 256, 1), (16, 32, 32, 1280, 256, 0)]:
+for (n, h, w, c, k, with_stats) in [(16, 128, 128, 64, 256, 1), (16, 32, 32, 256, 1024, 1), (16, 32, 32, 1024, 256, 1), (16, 64, 64, 128, 512, 1)]:
     x = E.Act(torch.randn(n, h, w, c, device='cuda').to(torch.bfloat16))
     pw = E.PackedWeight().update(torch.randn(k, c, 1, 1, device='cuda') * 0.05, need_dgrad=False)
     y = E.Act.empty(n, h, w, k, 'cuda')
