@@ -222,7 +222,7 @@ def run_b200(args):
     model = P.DeepLabV3Plus(NC).to(dev).train()
     # one multi-tensor launch (b200seg_sgd_multi); the 1/world of the gradient average is folded into the update
     opt = P.optim.SGD(model.parameters(), lr=1e-3, momentum=0.9, grad_scale=1.0 / world)
-    bucketer = (GradBucketer(model.parameters(), bucket_mb=args.bucket_mb, average=False).attach().sync_initial_state(model)
+    bucketer = (GradBucketer(model.parameters(), bucket_mb=args.bucket_mb, average=False, last_bucket_mb=args.last_bucket_mb).attach().sync_initial_state(model)
                 if world > 1 else None)
 
     # inputs as the reference's dataset yields them (utils/datasets.py:161-194): uint8 images, uint8 masks.  The
@@ -298,6 +298,8 @@ def run_b200(args):
     lane_was, E._LANE_ON = E._LANE_ON, False
     E.PROFILE = []
     E.OP_PROFILE = []
+    if bucketer is not None:
+        bucketer.profile = []
     prof_steps = min(args.steps, 3)
     for _ in range(prof_steps):
         # the host needs about as long to enqueue an eager step as the GPU to run it; a ~40 ms spin kernel ahead of each
@@ -309,7 +311,10 @@ def run_b200(args):
     op_rec, E.OP_PROFILE = E.OP_PROFILE, None
     E._LANE_ON = lane_was
     # data parallel: every rank must hold the same parameters after the same number of averaged updates
-    sync_diff = None
+    sync_diff = exposed_ms = None
+    if bucketer is not None:
+        ev, bucketer.profile = bucketer.profile, None
+        exposed_ms = sum(a.elapsed_time(b) for a, b in ev) / max(len(ev), 1)
     if world > 1:
         chk = torch.stack([p.detach().double().sum() for p in model.parameters()])
         hi, lo = chk.clone(), chk.clone()
@@ -391,6 +396,9 @@ def run_b200(args):
         }
         if sync_diff is not None:
             line['param_sync_max_abs_diff'] = sync_diff
+            # CUDA events around GradBucketer.finish()'s waits in the eager profiling steps: the part of the gradient
+            # all-reduce that backward did not hide (rank 0; no nsys on this image)
+            line['allreduce_exposed_ms_per_step'] = exposed_ms
         if world == 1 and not args.no_cpu_baseline:
             ips_cpu, dt, threads = cpu_reference_run(16, 1)      # ~10 s of host work
             ub, um, _ = cpu_unet_run(6, 1)                        # BASELINE.md §4 "config 1 exactly", ~5 s
@@ -522,7 +530,7 @@ def run_other(args):
             model.train()
             opt = P.optim.SGD(model.parameters(), lr=1e-3, momentum=0.9, grad_scale=1.0 / world)
             if world > 1:
-                bucketer = GradBucketer(model.parameters(), bucket_mb=args.bucket_mb, average=False).attach().sync_initial_state(model)
+                bucketer = GradBucketer(model.parameters(), bucket_mb=args.bucket_mb, average=False, last_bucket_mb=args.last_bucket_mb).attach().sync_initial_state(model)
             step = P.TrainStep(model, opt, bucketer, graph=args.graph in ('on', 'auto'))
             eager = P.TrainStep(model, opt, bucketer, graph=False)
 
@@ -646,6 +654,7 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--detail', default=None, help='write the per-launch CUDA-event timings of every conv to this file')
     ap.add_argument('--bucket-mb', type=float, default=64.0, help='N > 1: gradient all-reduce bucket size')
+    ap.add_argument('--last-bucket-mb', type=float, default=4.0, help='N > 1: cap of the bucket that completes last (exposed)')
     ap.add_argument('--sm-reserve', type=int, default=0, help='N > 1: SMs the conv kernels leave to NCCL')
     ap.add_argument('--nccl-ctas', type=int, default=0, help='N > 1: NCCL_MAX_CTAS (0 = NCCL default)')
     ap.add_argument('--graph', default='auto', choices=['auto', 'on', 'off'],

@@ -257,6 +257,16 @@ int b200seg_grad_add_masked(void* dx, int dx_c_total, int dx_c_offset, const voi
 int b200seg_grad_add_masked_bits(void* dx, int dx_c_total, int dx_c_offset, const void* dy, int dy_c_total, int dy_c_offset,
                                  const void* y, int y_c_total, int y_c_offset, const uint8_t* xin_bits, int c, int64_t pixels,
                                  b200seg_stream_t st);
+/* The same join fused with the FIRST pass of the BatchNorm backward that consumes its result: the joined gradient of a
+ * block input is the (pre-masked) output gradient of the ResNet block before it, whose bn3 — and downsample BN, if any —
+ * backward begins by reducing it against the saved raw conv output.  dx <- (dx + dy) * mask(xin_bits);
+ * red3[0..c) += sum dx, red3[c..2c) += invstd3 * (sum dx*x3 - mean3 * sum dx), likewise (xd, meand, invstdd, redd) when
+ * xd != NULL.  The caller then runs b200seg_bn_bwd_apply_masked only (no b200seg_bn_bwd_reduce_*) for those layers.
+ * red3 / redd must be zeroed (or carry a partial sum).  dy optional. */
+int b200seg_grad_join_reduce(void* dx, int dx_c_total, int dx_c_offset, const void* dy, int dy_c_total, int dy_c_offset,
+                             const uint8_t* xin_bits, int c, int64_t pixels, const void* x3, int x3_c_total, int x3_c_offset,
+                             const float* mean3, const float* invstd3, float* red3, const void* xd, int xd_c_total,
+                             int xd_c_offset, const float* meand, const float* invstdd, float* redd, b200seg_stream_t st);
 /* y = relu?(x0 + ... + x_{n-1}), 1 <= n <= 4 bf16 NHWC slices: the multi-resolution fuse of an HRModule
  * (models/hrnet.py:240-249) in one pass. */
 int b200seg_add_n_relu(int n_in, const void* const* x, const int* x_c_total, const int* x_c_offset, void* y, int y_c_total,

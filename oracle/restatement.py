@@ -76,11 +76,39 @@ def _subst(key, y):
     return y + (v.to(y.dtype).reshape(y.shape) - y).detach()
 
 
+def _relu_adopt(pre, key, values, record=False):
+    """ReLU whose VALUE and MASK are the stored ones: forward value = values[key] (the bf16 tensor the CUDA run wrote),
+    backward d/d(pre) = [values[key] > 0].  An fp32 oracle's own mask differs from the kernels' on the handful of
+    elements whose pre-activation is within fp32 round-off of zero (different operation order inside BatchNorm); on a
+    12 x 12 map one such flip moves a weight-gradient entry by several per cent.  Without a stored value: plain ReLU."""
+    if record:
+        y = F.relu(pre)
+        values[key] = y.detach().clone()
+        return y
+    v = values.get(key) if values is not None else None
+    if v is None:
+        return F.relu(pre)
+    assert v.numel() == pre.numel(), (key, tuple(v.shape), tuple(pre.shape))
+    v = v.to(pre.dtype).reshape(pre.shape)
+    y = pre * (v > 0).to(pre.dtype)
+    return y + (v - y).detach()
+
+
+class _Restore:
+    def __init__(self, fn):
+        self.fn = fn
+
+    def remove(self):
+        self.fn()
+
+
 def hook_backbone(backbone, values, prefix='backbone.', record=False, grad_log=None):
-    """Forward hooks on a torchvision ResNet (through the shim) that substitute the stored conv results
-    ('<prefix><conv name>.raw') and the stored stem / bottleneck outputs ('<prefix><conv name>.out': conv1 -> the
-    ReLU output that feeds the max pool; block.conv1/conv2 -> the ReLU outputs inside the block; block.conv3 -> the
-    block output).  Returns the hook handles.
+    """Makes a torchvision ResNet (through the shim) consume what the CUDA run stored: forward hooks substitute the conv
+    results ('<prefix><conv name>.weight.raw'), and every ReLU takes value and mask from the stored activation
+    ('<prefix><conv name>.weight.out': conv1 -> the stem output that feeds the max pool; block.conv1 / conv2 -> the ReLU
+    outputs inside the block; block.conv3 -> the block output) — the Bottleneck forward is restated here for that
+    (torchvision/models/resnet.py Bottleneck.forward: conv1-bn1-relu, conv2-bn2-relu, conv3-bn3, + identity or
+    downsample(x), relu).  Returns handles with ``.remove()``.
 
     ``grad_log`` (a dict) switches on the backward re-synchronisation at block boundaries: where ``values`` holds
     '<prefix><block>.conv3.weight.gout' — the gradient the CUDA run stored (bf16) on entry to that block's backward,
@@ -111,37 +139,56 @@ def hook_backbone(backbone, values, prefix='backbone.', record=False, grad_log=N
             if v is None:
                 return None
             assert v.shape == out.shape, (key, tuple(v.shape), tuple(out.shape))
-            return out + (v.to(out.dtype) - out).detach()
+            new = out + (v.to(out.dtype) - out).detach()
+            # re-synchronisation inside the blocks as well: '<conv>.weight.graw' is the gradient of this raw conv output
+            # the CUDA run stored (the BatchNorm backward's result, bf16) — logged against the oracle's and then used in
+            # its place, so every dgrad / wgrad / BN backward is checked on exactly the operands its kernel had
+            g_stored = values.get(key[:-len('.raw')] + '.graw') if grad_log is not None else None
+            if g_stored is not None and new.requires_grad:
+                def on_grad(g, gkey=key[:-len('.raw')] + '.graw'):
+                    grad_log[gkey] = (g.detach(), g_stored.to(g.dtype))
+                    return g_stored.to(g.dtype)
+                new.register_hook(on_grad)
+            return new
         return hook
 
-    def sub_input(key):
-        def pre(_m, inp):
-            if record:
-                values[key] = inp[0].detach().clone()
-                return None
-            v = values.get(key)
-            if v is None:
-                return None
-            assert v.shape == inp[0].shape, (key, tuple(v.shape), tuple(inp[0].shape))
-            return (inp[0] + (v.to(inp[0].dtype) - inp[0]).detach(),)
-        return pre
+    def patch_forward(mod, fn):
+        had = 'forward' in mod.__dict__
+        old = mod.__dict__.get('forward')
+        mod.forward = fn
+
+        def undo():
+            if had:
+                mod.forward = old
+            else:
+                del mod.forward
+        handles.append(_Restore(undo))
 
     for name, m in backbone.named_modules():
         if isinstance(m, nn.Conv2d):
             handles.append(m.register_forward_hook(sub(prefix + name + '.weight.raw')))
-            # inside a Bottleneck, conv2 reads relu(bn1(conv1 x)) and conv3 reads relu(bn2(conv2 .)): the stored ReLU outputs
-            for nxt, prv in (('.conv2', '.conv1'), ('.conv3', '.conv2')):
-                if name.endswith(nxt):
-                    handles.append(m.register_forward_pre_hook(sub_input(prefix + name[:-len(nxt)] + prv + '.weight.out')))
-        if hasattr(m, 'conv3') and hasattr(m, 'bn3'):          # Bottleneck: its output
-            def block_hook(_m, _i, out, key=prefix + name + '.conv3.weight'):
-                new = sub(key + '.out')(_m, _i, out)
-                new = out if new is None else new
-                resync(key + '.gout', new)
-                return new
-            handles.append(m.register_forward_hook(block_hook))
-    if hasattr(backbone, 'maxpool'):
-        handles.append(backbone.maxpool.register_forward_pre_hook(sub_input(prefix + 'conv1.weight.out')))
+        if hasattr(m, 'conv3') and hasattr(m, 'bn3'):          # Bottleneck
+            def block_forward(x, blk=m, key=prefix + name):
+                out = _relu_adopt(blk.bn1(blk.conv1(x)), key + '.conv1.weight.out', values, record)
+                out = _relu_adopt(blk.bn2(blk.conv2(out)), key + '.conv2.weight.out', values, record)
+                out = blk.bn3(blk.conv3(out))
+                identity = x if blk.downsample is None else blk.downsample(x)
+                out = _relu_adopt(out + identity, key + '.conv3.weight.out', values, record)
+                resync(key + '.conv3.weight.gout', out)
+                return out
+            patch_forward(m, block_forward)
+    if hasattr(backbone, 'relu') and hasattr(backbone, 'maxpool'):
+        # the stem's ReLU (the shim computes relu(bn1(conv1 x)) with this module): stored value and mask
+        old_relu = backbone.relu
+
+        class _StemReLU(nn.Module):
+            def forward(self, pre):
+                return _relu_adopt(pre, prefix + 'conv1.weight.out', values, record)
+        backbone.relu = _StemReLU()
+
+        def undo_relu():
+            backbone.relu = old_relu
+        handles.append(_Restore(undo_relu))
     return handles
 
 
@@ -175,6 +222,8 @@ def conv_norm_act(sd, prefix, x, ksize, dilation=1, training=False, relu=True):
         sd[prefix + '.1.num_batches_tracked'] += 1
     y = F.batch_norm(y, sd[prefix + '.1.running_mean'], sd[prefix + '.1.running_var'],
                      sd[prefix + '.1.weight'], sd[prefix + '.1.bias'], training, BN_MOMENTUM, BN_EPS)
+    if relu and _SUBST is not None:
+        return _relu_adopt(y, prefix + '.0.weight.out', _SUBST, _RECORD)      # stored value AND mask
     return _subst(prefix + '.0.weight.out', F.relu(y) if relu else y)
 
 

@@ -94,6 +94,7 @@ PROTOTYPES = {
     'b200seg_bn_apply': (c_int, [_P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _I, _P]),
     'b200seg_bn_apply_train': (c_int, [_P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _P, _F, _F, _P, _P, _P, _I, _P, _I, _I, _P, _P, _P, _P]),
     'b200seg_grad_add_masked_bits': (c_int, [_P, _I, _I, _P, _I, _I, _P, _I, _I, _P, _I, _L, _P]),
+    'b200seg_grad_join_reduce': (c_int, [_P, _I, _I, _P, _I, _I, _P, _I, _L, _P, _I, _I, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P]),
     'b200seg_bn_apply_add': (c_int, [_P, _I, _I, _P, _I, _I, _I, _L, _P, _P, _I, _P, _I, _I, _P, _P, _P]),
     'b200seg_relu_bwd_add': (c_int, [_P, _I, _I, _P, _I, _I, _P, _I, _I, _I, _L, _P]),
     'b200seg_add_n_relu': (c_int, [_I, POINTER(c_void_p), POINTER(c_int), POINTER(c_int), _P, _I, _I, _I, _L, _I, _P]),

@@ -577,6 +577,88 @@ __global__ void __launch_bounds__(256) grad_add_masked_kernel(__nv_bfloat16* __r
     }
 }
 
+// The residual-block gradient join FUSED with the first pass of the next BatchNorm backward in line.  In a ResNet
+// backward the joined gradient d = (dx + dy) * [xin > 0] of a block input IS the (pre-masked) output gradient of the block
+// before it, whose bn3 backward — and its downsample BN's, if it has one — starts by reducing sum d and sum d * xhat over
+// all pixels.  Doing that here, while d is in registers, saves that pass one read of d per block and a launch:
+//   dx <- d ;  red3[0..c) += sum d,  red3[c..2c) += invstd3 * (sum d*x3 - mean3 * sum d) ;  same for (xd, redd) if kDs
+// Column geometry of the reductions (a thread owns 8 channels for its pixel rows); xin's mask comes as bits.
+template <bool kDs>
+__global__ void __launch_bounds__(kRedThreads, 4) grad_join_reduce_kernel(
+    __nv_bfloat16* __restrict__ dx, int dx_ct, int dx_off, const __nv_bfloat16* __restrict__ dy, int dy_ct, int dy_off,
+    const unsigned char* __restrict__ bits, const __nv_bfloat16* __restrict__ x3, int x3_ct, int x3_off,
+    const float* __restrict__ mean3, const float* __restrict__ invstd3, float* __restrict__ red3,
+    const __nv_bfloat16* __restrict__ xd, int xd_ct, int xd_off, const float* __restrict__ meand,
+    const float* __restrict__ invstdd, float* __restrict__ redd, int c, int64_t pixels, int gpb, int rows) {
+    pdl_prologue();
+    const int groups = c >> 3;
+    const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
+    const int group = blockIdx.y * gpb + g_local;
+    float a0[8], a3[8], ad[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a0[j] = a3[j] = ad[j] = 0.f;
+    if (row < rows && group < groups) {
+        const int64_t pstep = static_cast<int64_t>(gridDim.x) * rows;
+        __nv_bfloat16* ob = dx + dx_off + group * 8;
+        const __nv_bfloat16* db = dy ? dy + dy_off + group * 8 : nullptr;
+        const __nv_bfloat16* x3b = x3 + x3_off + group * 8;
+        const __nv_bfloat16* xdb = kDs ? xd + xd_off + group * 8 : nullptr;
+#pragma unroll 1
+        for (int64_t p = static_cast<int64_t>(blockIdx.x) * rows + row; p < pixels; p += pstep) {
+            const uint4 v = *reinterpret_cast<const uint4*>(ob + p * dx_ct);
+            const uint4 x3v = ldcs128(x3b + p * x3_ct);
+            uint4 dv = make_uint4(0u, 0u, 0u, 0u), xdv = dv;
+            if (db) dv = ldcs128(db + p * dy_ct);
+            if (kDs) xdv = ldcs128(xdb + p * xd_ct);
+            const unsigned int m = __ldg(bits + p * groups + group);
+            float a[8], d[8], f[8];
+            unpack8(v, a);
+            unpack8(dv, d);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a[j] = (m >> j) & 1u ? a[j] + d[j] : 0.f;
+            const uint4 packed = pack8(a);
+            st128(ob + p * dx_ct, packed);
+            // the sums are those of the gradient AS STORED (bf16), which is what the apply pass will read
+            unpack8(packed, a);
+            unpack8(x3v, f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                a0[j] += a[j];
+                a3[j] = fmaf(a[j], f[j], a3[j]);
+            }
+            if (kDs) {
+                unpack8(xdv, f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) ad[j] = fmaf(a[j], f[j], ad[j]);
+            }
+        }
+    }
+    float acc[2][8];
+    {
+        float mu[8], is[8];
+        if (row < rows && group < groups) {
+            load8f(mean3 + group * 8, mu);
+            load8f(invstd3 + group * 8, is);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            acc[0][j] = a0[j];
+            acc[1][j] = (row < rows && group < groups) ? is[j] * (a3[j] - mu[j] * a0[j]) : 0.f;
+        }
+    }
+    block_col_reduce<2>(acc, g_local, row, gpb, rows, group, groups, c, red3);
+    if (kDs) {
+        float mu[8], is[8];
+        if (row < rows && group < groups) {
+            load8f(meand + group * 8, mu);
+            load8f(invstdd + group * 8, is);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[1][j] = (row < rows && group < groups) ? is[j] * (ad[j] - mu[j] * a0[j]) : 0.f;
+        block_col_reduce<2>(acc, g_local, row, gpb, rows, group, groups, c, redd);
+    }
+}
+
 // y = relu?(x0 + x1 + ... ) over up to 4 bf16 NHWC slices — the multi-resolution fuse of an HRModule
 // (models/hrnet.py:240-249: y = y + fuse(x[j]) ...; relu(y))
 struct AddN {
@@ -871,6 +953,31 @@ int b200seg_grad_add_masked_bits(void* dx, int dx_c_total, int dx_c_offset, cons
         static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, static_cast<const __nv_bfloat16*>(dy), dy_c_total,
         dy_c_offset, static_cast<const __nv_bfloat16*>(y), y_c_total, y_c_offset, static_cast<const __nv_bfloat16*>(nullptr),
         0, 0, xin_bits, c / 8, total));
+    return 0;
+}
+
+int b200seg_grad_join_reduce(void* dx, int dx_c_total, int dx_c_offset, const void* dy, int dy_c_total, int dy_c_offset,
+                             const uint8_t* xin_bits, int c, int64_t pixels, const void* x3, int x3_c_total, int x3_c_offset,
+                             const float* mean3, const float* invstd3, float* red3, const void* xd, int xd_c_total,
+                             int xd_c_offset, const float* meand, const float* invstdd, float* redd,
+                             b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    if (check_slice("grad_join_reduce(dx)", dx, dx_c_total, dx_c_offset, c)) return 1;
+    if (dy && check_slice("grad_join_reduce(dy)", dy, dy_c_total, dy_c_offset, c)) return 1;
+    if (check_slice("grad_join_reduce(x3)", x3, x3_c_total, x3_c_offset, c)) return 1;
+    if (xd && check_slice("grad_join_reduce(xd)", xd, xd_c_total, xd_c_offset, c)) return 1;
+    B200SEG_CHECK(pixels > 0 && xin_bits && mean3 && invstd3 && red3, "grad_join_reduce: bad arguments");
+    B200SEG_CHECK(!xd || (meand && invstdd && redd), "grad_join_reduce: downsample statistics missing");
+    const ColGeom g = col_geom(c, pixels, 4, 32);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define B200SEG_JOIN(DS)                                                                                                  \
+    B200SEG_CUDA(launch_pdl(grad_join_reduce_kernel<DS>, dim3(g.gx, g.gy), kRedThreads, 0, st,                            \
+        static_cast<__nv_bfloat16*>(dx), dx_c_total, dx_c_offset, static_cast<const __nv_bfloat16*>(dy), dy_c_total,      \
+        dy_c_offset, xin_bits, static_cast<const __nv_bfloat16*>(x3), x3_c_total, x3_c_offset, mean3, invstd3, red3,      \
+        static_cast<const __nv_bfloat16*>(xd), xd_c_total, xd_c_offset, meand, invstdd, redd, c, pixels, g.gpb, g.rows));
+    if (xd) B200SEG_JOIN(true) else B200SEG_JOIN(false)
+#undef B200SEG_JOIN
     return 0;
 }
 

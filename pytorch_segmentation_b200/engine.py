@@ -790,7 +790,7 @@ def bn_apply(x, y, vec, relu, res=None, res_vec=None, want_bits=False):
     _lib.count_launch()
 
 
-def bn_backward(dy, x, dx, vec, relu, training, mask=None, red=None):
+def bn_backward(dy, x, dx, vec, relu, training, mask=None, red=None, reduced=False):
     """dy: grad of the BN(+ReLU) output, x: saved raw conv output, dx: receives the grad of x.  ``mask``: stored
     block output whose sign is the ReLU mask (residual blocks); None recomputes it from x.  ``red``: a ZEROED fp32
     [2c] slice of a per-backward arena (saves the per-layer memset).  Returns (dgamma, dbeta)."""
@@ -801,14 +801,14 @@ def bn_backward(dy, x, dx, vec, relu, training, mask=None, red=None):
     if red is None:
         red = torch.empty((2 * c,), dtype=torch.float32, device=x.t.device)
     m = (mask.ptr, mask.ct, mask.c_off) if mask is not None else (None, 0, 0)
-    _lib.check(reduce_fn(dy.ptr, dy.ct, dy.c_off, x.ptr, x.ct, x.c_off, c, x.pixels, p, p + 4 * c,
-                                                p + 8 * c, p + 12 * c, int(relu), red.data_ptr(), m[0], m[1], m[2],
-                                                _stream()), 'bn_bwd_reduce')
+    if not reduced:        # ``reduced``: ``red`` already holds the sums (grad_join_reduce did the first pass)
+        _lib.check(reduce_fn(dy.ptr, dy.ct, dy.c_off, x.ptr, x.ct, x.c_off, c, x.pixels, p, p + 4 * c,
+                             p + 8 * c, p + 12 * c, int(relu), red.data_ptr(), m[0], m[1], m[2], _stream()), 'bn_bwd_reduce')
     _lib.check(lib.b200seg_bn_bwd_apply_masked(dy.ptr, dy.ct, dy.c_off, x.ptr, x.ct, x.c_off, dx.ptr, dx.ct, dx.c_off, c,
                                                x.pixels, p, p + 4 * c, p + 8 * c, p + 12 * c, int(relu), int(training),
                                                red.data_ptr(), None, None, 0, m[0], m[1], m[2], _stream()),
                'bn_bwd_apply')
-    _lib.count_launch(2)      # reduce + apply
+    _lib.count_launch(1 if reduced else 2)      # reduce + apply
     return red[c:], red[:c]
 
 
@@ -831,6 +831,33 @@ def grad_add_masked(dx, dy=None, y=None, xin=None):
         return
     _lib.check(_lib.load().b200seg_grad_add_masked(dx.ptr, dx.ct, dx.c_off, *trip(dy), *trip(y), *trip(xin), dx.c, dx.pixels,
                                                    _stream()), 'grad_add_masked')
+    _lib.count_launch()
+
+
+JOIN_REDUCE = _os.environ.get('B200SEG_JOIN_REDUCE', '1') != '0'      # resnet.py: fuse the join with the next BN reduce
+
+
+def grad_join_reduce(dx, dy, xin, t3, td=None):
+    """dx = (dx + dy) * [xin > 0] (dy optional, xin's mask as bits) AND the first pass of the BatchNorm backward(s) that
+    consume dx as their output gradient: t3 / td = (raw conv output Act, vec[4, c], zeroed red[2c]) of the previous
+    block's bn3 / downsample BN.  Afterwards ``bn_backward(..., red=red, reduced=True)`` runs the apply pass only."""
+    c = dx.c
+    assert xin.bits is not None and xin.c_off == 0 and xin.c == c
+
+    def trip(a):
+        return (a.ptr, a.ct, a.c_off) if a is not None else (None, 0, 0)
+
+    def target(t):
+        if t is None:
+            return (None, 0, 0, None, None, None)
+        x, vec, red = t
+        bn_resolve(vec)
+        assert x.c == c and x.pixels == dx.pixels
+        p = vec.data_ptr()
+        return (x.ptr, x.ct, x.c_off, p + 8 * c, p + 12 * c, red.data_ptr())
+
+    _lib.check(_lib.load().b200seg_grad_join_reduce(dx.ptr, dx.ct, dx.c_off, *trip(dy), xin.bits.data_ptr(), c, dx.pixels,
+                                                    *target(t3), *target(td), _stream()), 'grad_join_reduce')
     _lib.count_launch()
 
 
@@ -983,13 +1010,35 @@ def channel_sum(x):
 # ------------------------------------------------------------------------------------------------
 # class map, loss, metrics
 # ------------------------------------------------------------------------------------------------
-def logits_upsample_fwd(x_nhwc_f32, nc, oh, ow, align_corners=True):
+# trainer.TrainStep sets this around the model's forward: the step's loss is taken from the class map (compute_loss's
+# shortcut), so the 352 MB of full-resolution logits the head would write are never read.  The head then returns the
+# logits tensor ALLOCATED BUT UNWRITTEN, marked deferred in its class-map tag; compute_loss fills it first
+# (``materialize_logits``) if for any reason it has to take the logits path after all.
+DEFER_LOGITS = False
+_deferred = set()
+
+
+def logits_upsample_fwd(x_nhwc_f32, nc, oh, ow, align_corners=True, out=None):
     n, h, w, ct = x_nhwc_f32.shape
-    y = torch.empty((n, nc, oh, ow), dtype=torch.float32, device=x_nhwc_f32.device)
+    y = out if out is not None else torch.empty((n, nc, oh, ow), dtype=torch.float32, device=x_nhwc_f32.device)
+    if (out is None and DEFER_LOGITS and LOWRES_CE
+            and lowres_ce_supported(x_nhwc_f32.shape, nc, oh, ow, align_corners)):
+        _deferred.add(y.data_ptr())
+        return y
     _lib.check(_lib.load().b200seg_logits_upsample_fwd(x_nhwc_f32.data_ptr(), ct, n, h, w, nc, y.data_ptr(), oh, ow,
                                                        int(align_corners), _stream()), 'logits_upsample_fwd')
     _lib.count_launch()
     return y
+
+
+def materialize_logits(out):
+    """Write the logits a head deferred (see DEFER_LOGITS); no-op for ordinary outputs."""
+    tag = getattr(out, '_b200seg_class_map', None)
+    if tag is not None and len(tag) > 4 and tag[4]:
+        lr, nc, ac = tag[0], tag[1], tag[2]
+        logits_upsample_fwd(lr, nc, out.shape[2], out.shape[3], ac, out=out.detach())
+        out._b200seg_class_map = tag[:4] + (False,)
+    return out
 
 
 def logits_upsample_bwd(dy_nchw_f32, h, w, ct, align_corners=True):
@@ -1124,7 +1173,10 @@ def class_map_backward(dout, dlr_direct, h, w, ncp, align_corners):
 def attach_class_map(out, lr, nc, align_corners):
     """Called by the model heads (read by utils.compute_loss): remember which class map ``out`` is the upsample of (and ``out``'s version, so an
     in-place edit of the logits turns the shortcut off)."""
-    out._b200seg_class_map = (lr, nc, align_corners, out._version)
+    deferred = out.data_ptr() in _deferred
+    if deferred:
+        _deferred.discard(out.data_ptr())
+    out._b200seg_class_map = (lr, nc, align_corners, out._version, deferred)
     return out
 
 
@@ -1222,7 +1274,8 @@ def _act_bytes(a):
 # passes' reads of dy and x plus the dx write; the residual join reads what it is given and rewrites dx)
 _OP_BYTES = {
     'bn_apply': lambda a, kw: _act_bytes(a[0]) * (2 + (kw.get('res') is not None or (len(a) > 4 and a[4] is not None))),
-    'bn_backward': lambda a, kw: _act_bytes(a[1]) * 5,
+    'bn_backward': lambda a, kw: _act_bytes(a[1]) * (3 if kw.get('reduced') else 5),
+    'grad_join_reduce': lambda a, kw: _act_bytes(a[0]) * (2 + (a[1] is not None) + 1.0 / 16 + 1 + ((a[4] if len(a) > 4 else kw.get('td')) is not None)),
     'grad_add_masked': lambda a, kw: _act_bytes(a[0]) * (2 + sum(1 for v in list(a[1:3]) + [kw.get('dy'), kw.get('y')]
                                                                  if v is not None)
                                                          + (1.0 / 16 if (kw.get('xin') if 'xin' in kw else (a[3] if len(a) > 3 else None)) is not None else 0)),
@@ -1248,7 +1301,7 @@ def _timed(name, fn):
 
 
 for _name in ('as_act', 'grad_like', 'im2col', 'unpack_wgrad_im2col', 'tap_gather', 'tap_scatter_add', 'unpack_wgrad_taps', 'bn_stats', 'bn_finalize', 'bn_eval_affine',
-              'bn_apply', 'bn_backward', 'relu_bwd_add', 'grad_add_masked', 'maxpool_fwd', 'maxpool_bwd', 'upsample_fwd', 'upsample_bwd',
+              'bn_apply', 'bn_backward', 'relu_bwd_add', 'grad_add_masked', 'grad_join_reduce', 'maxpool_fwd', 'maxpool_bwd', 'upsample_fwd', 'upsample_bwd',
               'gap_fwd', 'sum_hw', 'broadcast_hw', 'linear_f32_fwd', 'linear_f32_bwd', 'bn_rows_fwd', 'bn_rows_bwd',
               'channel_sum', 'logits_upsample_fwd', 'logits_upsample_bwd', 'resize_nchw_fwd', 'resize_nchw_bwd',
               'softmax_ce', 'softmax_ce_bwd', 'argmax', 'confusion', 'argmax_confusion'):

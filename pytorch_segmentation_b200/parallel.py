@@ -20,7 +20,7 @@ import torch.distributed as dist
 
 
 class GradBucketer:
-    def __init__(self, params, bucket_mb=25.0, first_bucket_mb=1.0, process_group=None, average=True):
+    def __init__(self, params, bucket_mb=25.0, first_bucket_mb=1.0, process_group=None, average=True, last_bucket_mb=4.0):
         self.params = [p for p in params if p.requires_grad]
         self.group = process_group
         self.average = average
@@ -30,7 +30,7 @@ class GradBucketer:
         self._pending = []
         self._ready = []
         self._handles = []
-        self._build(bucket_mb, first_bucket_mb)
+        self._build(bucket_mb, first_bucket_mb, last_bucket_mb)
         self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
         self.enabled = True         # set False on non-final micro-steps of gradient accumulation
         self._early = set()         # parameters whose gradient reached its slot before autograd delivered it
@@ -96,7 +96,7 @@ class GradBucketer:
             if self._ready[bi] == self._pending[bi]:
                 self._launch(bi)
 
-    def _build(self, bucket_mb, first_bucket_mb):
+    def _build(self, bucket_mb, first_bucket_mb, last_bucket_mb=0.0):
         cap = int(first_bucket_mb * (1 << 20))
         cur, cur_bytes = [], 0
         groups = []
@@ -110,6 +110,17 @@ class GradBucketer:
             cur_bytes += nbytes
         if cur:
             groups.append(cur)
+        # The bucket that completes LAST (the first-registered parameters: the stem and the first backbone stage) starts
+        # its all-reduce when backward is over, i.e. fully exposed: keep it small, so what is exposed is a few MB and the
+        # rest of that tail travels with the previous bucket, under the last stage's backward.
+        if last_bucket_mb and groups:
+            tail, cap, nbytes = groups[-1], int(last_bucket_mb * (1 << 20)), 0
+            cut = len(tail)
+            while cut > 1 and nbytes + tail[cut - 1].numel() * tail[cut - 1].element_size() <= cap:
+                cut -= 1
+                nbytes += tail[cut].numel() * tail[cut].element_size()
+            if 0 < cut < len(tail):
+                groups[-1:] = [tail[:cut], tail[cut:]]
         for bi, g in enumerate(groups):
             total = sum(p.numel() for p in g)
             flat = torch.zeros((total,), dtype=g[0].dtype, device=g[0].device)
@@ -183,8 +194,16 @@ class GradBucketer:
                     self._launch(bi)
         for bi in range(len(self._buckets)):
             self._flush_moves(bi)
+        prof = getattr(self, 'profile', None)
+        if prof is not None:
+            # exposed collective time: how long the compute stream stalls here for all-reduces still in flight
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
         for bi, h in self._handles:
             h.wait()
+        if prof is not None:
+            e1.record()
+            prof.append((e0, e1))
             if self.average and self.world > 1:
                 self._buckets[bi][0].div_(self.world)
         self._handles = []

@@ -96,25 +96,38 @@ class _Block:
             E.capture(self.u3.conv.weight, 'out', out)
         return out, (x, raw1, v1, a1, raw2, v2, a2, raw3, v3, rawd, vd, out)
 
-    def backward(self, rec, dout, training, grads, need_dx=True, dout_masked=False, mask_in=True, red_of=None):
+    def join_target(self, rec, red_of):
+        """What a later block's gradient join needs to do this block's first BatchNorm-backward pass for it
+        (engine.grad_join_reduce): (raw3, v3, red3) and, with a downsample branch, (rawd, vd, redd)."""
+        x, raw1, v1, a1, raw2, v2, a2, raw3, v3, rawd, vd, out = rec
+        t3 = (raw3, v3, red_of(self.u3))
+        td = (rawd, vd, red_of(self.ud)) if self.ud is not None else None
+        return t3, td
+
+    def backward(self, rec, dout, training, grads, need_dx=True, dout_masked=False, mask_in=True, red_of=None,
+                 red_done=False, join_to=None):
         """dout: Act grad of the block output — already multiplied by (out > 0) when ``dout_masked`` (it then came from
         the next block's ``backward``), raw otherwise (a head's gradient).  Fills grads[param] and returns the Act grad
         of the block input, multiplied by (x > 0) when ``mask_in`` (x is a ReLU output: the previous block's), so that
         block's BatchNorm backward never re-reads its own output for the mask."""
         x, raw1, v1, a1, raw2, v2, a2, raw3, v3, rawd, vd, out = rec
         dev = x.t.device
+        self.fused_join = False
         E.capture(self.u3.conv.weight, 'gout', dout)       # parity tests: the stored gradient that enters this block
 
-        def unit_bwd(u, dy, raw, vec, xin, relu=True, mask=None):
+        def unit_bwd(u, dy, raw, vec, xin, relu=True, mask=None, reduced=False):
             draw = E.Act.empty(raw.n, raw.h, raw.w, raw.c, dev)
             dgamma, dbeta = E.bn_backward(dy, raw, draw, vec, relu, training, mask=mask,
-                                          red=red_of(u) if red_of is not None else None)
+                                          red=red_of(u) if red_of is not None else None, reduced=reduced)
+            E.capture(u.conv.weight, 'graw', draw)         # parity tests: the stored gradient of the raw conv output
             grads[u.conv.weight] = u.wgrad(draw, xin)
             grads[u.bn.weight], grads[u.bn.bias] = dgamma, dbeta
             return draw
 
         # bn3 (and the downsample BN) sit under the block's final ReLU, whose mask is the sign of `out`
-        tail = dict(relu=False) if dout_masked else dict(relu=True, mask=out)
+        # ``red_done``: the join that produced dout already reduced it against raw3 (and rawd) into the arena
+        assert not red_done or (dout_masked and training and red_of is not None)
+        tail = dict(relu=False, reduced=red_done) if dout_masked else dict(relu=True, mask=out)
         draw3 = unit_bwd(self.u3, dout, raw3, v3, a2, **tail)
         da2 = E.Act.empty(a2.n, a2.h, a2.w, a2.c, dev)
         E.conv_dgrad([self.u3.dgrad_src(draw3)], da2)
@@ -127,14 +140,22 @@ class _Block:
             return None
         dx = E.Act.empty(x.n, x.h, x.w, x.c, dev)
         xin = x if mask_in else None
+        # ``join_to`` = (t3, td) of the block whose output x is: the join then also does that block's first BN-backward pass
+        fuse = join_to is not None and xin is not None and xin.bits is not None and (self.ud is not None or dout_masked)
         if self.ud is not None:
             E.conv_dgrad([self.u1.dgrad_src(draw1), self.ud.dgrad_src(drawd)], dx)
-            if xin is not None:
+            if fuse:
+                E.grad_join_reduce(dx, None, xin, *join_to)
+            elif xin is not None:
                 E.grad_add_masked(dx, xin=xin)
         else:
             E.conv_dgrad([self.u1.dgrad_src(draw1)], dx)
             # identity branch: + dout * (out > 0), the mask being already in dout when it is pre-masked
-            E.grad_add_masked(dx, dy=dout, y=None if dout_masked else out, xin=xin)
+            if fuse:
+                E.grad_join_reduce(dx, dout, xin, *join_to)
+            else:
+                E.grad_add_masked(dx, dy=dout, y=None if dout_masked else out, xin=xin)
+        self.fused_join = fuse
         return dx
 
 
@@ -253,6 +274,8 @@ class ResNet50Features(nn.Module):
 
         d = None
         masked = False       # whether d already carries the ReLU mask of the tensor it is the gradient of
+        red_done = False     # whether d was already reduced against the next block's raw3 / rawd (fused join)
+        fuse_ok = E.JOIN_REDUCE and training
         for li in (3, 2, 1, 0):
             g = gfeats[li + 1]
             if g is not None:
@@ -260,15 +283,32 @@ class ResNet50Features(nn.Module):
                 if d is None:
                     d, masked = ga, False
                 else:
-                    # d (masked) + external gradient (raw): mask the sum with the layer output's sign
-                    E.grad_add_masked(d, dy=ga, xin=recs[li][-1][-1])
+                    # d (masked) + external gradient (raw): mask the sum with the layer output's sign.  This join is the
+                    # last word on d, so it is the one that may carry the reduction for the layer's last block
+                    out_last = recs[li][-1][-1]
+                    if fuse_ok and out_last.bits is not None:
+                        E.grad_join_reduce(d, ga, out_last, *layers[li][-1].join_target(recs[li][-1], red_of))
+                        red_done = True
+                    else:
+                        E.grad_add_masked(d, dy=ga, xin=out_last)
             if d is None:
                 continue
             for bi in range(len(layers[li]) - 1, -1, -1):
+                # the block this one's input gradient goes to (None: the max-pool output, or a layer boundary where an
+                # external feature gradient still has to be added — handled above)
+                prev = None
+                if fuse_ok:
+                    if bi > 0:
+                        prev = (li, bi - 1)
+                    elif li > 0 and gfeats[li] is None:
+                        prev = (li - 1, len(layers[li - 1]) - 1)
+                join_to = layers[prev[0]][prev[1]].join_target(recs[prev[0]][prev[1]], red_of) if prev is not None else None
                 # the input of layer1's first block is the max-pool output, not a ReLU output: no mask there
-                d = layers[li][bi].backward(recs[li][bi], d, training, grads, dout_masked=masked,
-                                            mask_in=not (li == 0 and bi == 0), red_of=red_of)
+                blk = layers[li][bi]
+                d = blk.backward(recs[li][bi], d, training, grads, dout_masked=masked,
+                                 mask_in=not (li == 0 and bi == 0), red_of=red_of, red_done=red_done, join_to=join_to)
                 masked = not (li == 0 and bi == 0)
+                red_done = blk.fused_join
             # this stage's gradients are final: a data-parallel sink starts their all-reduce under the remaining stages
             E.deliver_grads(grads, [p for blk in layers[li] for u in blk.units() for p in u.params()])
         if d is not None:
@@ -281,6 +321,7 @@ class ResNet50Features(nn.Module):
             return grads
         draw0 = E.Act.empty(raw0.n, raw0.h, raw0.w, raw0.c, raw0.t.device)
         dgamma, dbeta = E.bn_backward(da0, raw0, draw0, v0, True, training)
+        E.capture(self.conv1.weight, 'graw', draw0)
         # dW of the stem = the 1x1 wgrad over the gathered matrix, scattered back to OIHW
         dwcol = E.conv_wgrad(draw0, col, raw0.c, pw0.r, pw0.s, 1, lane=True)
         unpack = E.unpack_wgrad_s2d if isinstance(pw0, E.PackedS2DWeight) else E.unpack_wgrad_im2col

@@ -61,7 +61,14 @@ class TrainStep:
             self.optimizer.zero_grad(set_to_none=True)
         if self.bucketer is not None:
             self.bucketer.enabled = last           # accumulate locally, all-reduce the sum once (DDP no_sync)
-        out = self.model(x)
+        # the step's logits are consumed by compute_loss alone, which takes loss and gradient from the head's class map:
+        # let the head skip writing them (engine.DEFER_LOGITS; compute_loss materialises them if it cannot)
+        defer = self.loss_fn is compute_loss and tuple(t.shape[1:]) == tuple(x.shape[2:])
+        E.DEFER_LOGITS = defer
+        try:
+            out = self.model(x)
+        finally:
+            E.DEFER_LOGITS = False
         loss = self.loss_fn(out, t, self.model)
         (loss * self.loss_scale if self.loss_scale != 1.0 else loss).backward()
         if last:

@@ -74,6 +74,7 @@ def compute_loss(outputs, targets, model=None):
             and tuple(outputs.shape[2:]) == tuple(targets.shape[1:]) and E.LOWRES_CE
             and E.lowres_ce_supported(cm[0].shape, cm[1], targets.shape[1], targets.shape[2], cm[2])):
         return _ClassMapCrossEntropyFn.apply(cm[0], targets.contiguous(), cm[1], cm[2])
+    E.materialize_logits(outputs)           # a head may have deferred writing them (engine.DEFER_LOGITS)
     return _CrossEntropyFn.apply(outputs, targets)
 
 

@@ -345,3 +345,42 @@ def test_gradient_accumulation(P):
     assert s_d.launches_per_step is not None and s_d.launches_per_step > 800      # two forward/backward passes in one graph
     for m in (m_a, m_c, m_d):
         assert int(m.aspp.project[1].num_batches_tracked) == 8
+
+
+def test_trainstep_defers_the_logits_and_loss_is_unchanged(P, E):
+    """TrainStep lets the head skip writing the full-resolution logits (its loss comes from the class map); the loss is
+    the same as the plain model(x) -> compute_loss sequence, and a loss that cannot use the class map gets them
+    materialised first."""
+    torch.manual_seed(4)
+    m = P.DeepLabV3Plus(5).cuda().eval()            # eval: deterministic forward
+    x, t = torch.randn(2, 3, 128, 128).cuda(), torch.randint(0, 5, (2, 128, 128)).cuda()
+    with torch.no_grad():
+        want = float(P.compute_loss(m(x), t, m))
+        E.DEFER_LOGITS = True
+        try:
+            y = m(x)
+        finally:
+            E.DEFER_LOGITS = False
+        assert y._b200seg_class_map[4] is True      # allocated, not written
+        got = float(P.compute_loss(y, t, m))
+        assert abs(got - want) <= 1e-6 * abs(want)
+        # half-size targets: compute_loss resizes the logits (utils/utils.py:18-20) -> needs them -> fills them in
+        E.DEFER_LOGITS = True
+        try:
+            y2 = m(x)
+        finally:
+            E.DEFER_LOGITS = False
+        t_half = t[:, ::2, ::2].contiguous()
+        got2 = float(P.compute_loss(y2, t_half, m))
+        want2 = float(P.compute_loss(m(x), t_half, m))
+        assert y2._b200seg_class_map[4] is False and torch.equal(y2, m(x))
+        assert abs(got2 - want2) <= 1e-6 * abs(want2)
+    s = P.TrainStep(m.train(), P.optim.SGD(m.parameters(), lr=0.0), graph=False)
+    before = _lib_launches()
+    s(x, t)
+    assert E.DEFER_LOGITS is False
+
+
+def _lib_launches():
+    from pytorch_segmentation_b200 import _lib
+    return _lib.launches()
