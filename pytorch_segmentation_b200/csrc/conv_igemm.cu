@@ -84,6 +84,7 @@ struct __align__(64) IgemmParams {
     int dbg_slots;
     int no_skip;             // anchored window sources: the buffer carries its own padding, every tap is in bounds
     int* sched;              // dynamic tile scheduler: {next tile - gridDim.x, CTAs done}; nullptr = static striding
+    int n_fast;              // A/B switch (B200SEG_IGEMM_NFAST=1, static striding only): n_tile as the fastest tile index
 };
 
 long long* g_dbg = nullptr;
@@ -109,8 +110,14 @@ __device__ __forceinline__ TileCoord decode_tile(const IgemmParams& p, int tile)
     // block, so the per-channel BN statistics it carries in registers are flushed once per block, not once per tile
     TileCoord t;
     const int m_tiles = p.tiles_x * p.tiles_y * p.tiles_i;
-    t.n_tile = tile / m_tiles;
-    int m = tile - t.n_tile * m_tiles;
+    int m;
+    if (p.n_fast) {
+        t.n_tile = tile % p.tiles_n;
+        m = tile / p.tiles_n;
+    } else {
+        t.n_tile = tile / m_tiles;
+        m = tile - t.n_tile * m_tiles;
+    }
     t.x0 = (m % p.tiles_x) * p.bw;
     m /= p.tiles_x;
     t.y0 = (m % p.tiles_y) * p.bh;
@@ -723,6 +730,11 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
     B200SEG_CHECK(sms > 0, "conv: cannot query SM count");
     const int grid = p.num_tiles < sms ? p.num_tiles : sms;
     p.sched = p.num_tiles > grid ? sched_slot() : nullptr;       // a single wave has nothing to schedule
+    static const bool n_fast = [] {
+        const char* e = getenv("B200SEG_IGEMM_NFAST");
+        return e && e[0] == '1';
+    }();
+    p.n_fast = n_fast && !p.sched ? 1 : 0;
     B200SEG_CUDA(launch_pdl(igemm_kernel, grid, kThreads, kSmemBytes, st, p));
     return 0;
 }

@@ -3,8 +3,8 @@
 
   python scripts/summarise_ncu.py gpurun_out/launches_r01.csv [--steps N] > profiles/r01_launches.md
 
-The bench command profiled runs N identical steps (3 warm-up + 1 enqueue-timing + 2 timed + 2 e2e warm-up + 2 e2e + 2 profiled
-= 12 by default); totals are divided by N.  ncu times are cold-cache and serialised: read SHARES.
+The bench command profiled runs N identical steps (3 warm-up + 2 enqueue-timing + 2 timed + 2 e2e warm-up + 2 e2e + 2 profiled
+= 13 by default); totals are divided by N.  The spin kernels bench.py puts ahead of its profiled steps are left out.  ncu times are cold-cache and serialised: read SHARES.
 """
 import csv
 import re
@@ -14,7 +14,7 @@ from collections import defaultdict
 
 def main():
     path = sys.argv[1]
-    steps = 12
+    steps = 13
     if '--steps' in sys.argv:
         steps = int(sys.argv[sys.argv.index('--steps') + 1])
     rows = []
@@ -27,6 +27,8 @@ def main():
         v = float(r['Metric Value'].replace(',', ''))
         unit = r['Metric Unit']
         us = v / 1e3 if unit in ('ns', 'nsecond') else v * {'us': 1, 'usecond': 1, 'ms': 1e3, 'msecond': 1e3}.get(unit, 1)
+        if 'spin_kernel' in r['Kernel Name']:
+            continue
         rows.append((r['Kernel Name'], us))
     agg = defaultdict(lambda: [0.0, 0])
     for name, us in rows:
