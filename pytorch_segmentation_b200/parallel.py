@@ -201,11 +201,11 @@ class GradBucketer:
             e0.record()
         for bi, h in self._handles:
             h.wait()
+            if self.average and self.world > 1:
+                self._buckets[bi][0].div_(self.world)
         if prof is not None:
             e1.record()
             prof.append((e0, e1))
-            if self.average and self.world > 1:
-                self._buckets[bi][0].div_(self.world)
         self._handles = []
         self._ready = [0] * len(self._buckets)
         self._early.clear()
