@@ -555,7 +555,12 @@ int plan_wgrad_uncached(const b200seg_wgrad_desc* d, WgradPlan* pl) {
     pl->cs = 1;
     pl->splits_hi = want;
     if (want >= 2 && cluster_reduce_enabled()) {
-        for (int cs = 8; cs >= 2; cs /= 2) {
+        static const int max_cs = [] {
+            const char* e = getenv("B200SEG_WGRAD_MAXCS");
+            const int v = e ? atoi(e) : 8;
+            return v == 2 || v == 4 || v == 8 ? v : 8;
+        }();
+        for (int cs = max_cs; cs >= 2; cs /= 2) {
             if (cs > want) continue;
             const int cap = cluster_capacity(cs);                  // co-resident clusters of this size
             int hi = cap / base_tiles;

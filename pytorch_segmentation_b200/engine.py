@@ -335,7 +335,7 @@ def tap_scatter_add(z, ncp, r, s, dil, bias=None):
 
 
 def unpack_wgrad_taps(dwcol, pw, lane=False):
-    return on_wgrad_lane(_unpack_wgrad_taps, dwcol, pw, keep=(dwcol,)) if lane else _unpack_wgrad_taps(dwcol, pw)
+    return on_wgrad_lane(_unpack_wgrad_taps, dwcol, pw, keep=(dwcol,), chain=True) if lane else _unpack_wgrad_taps(dwcol, pw)
 
 
 def _unpack_wgrad_taps(dwcol, pw):
@@ -443,7 +443,7 @@ def space_to_depth_u8(x, r, s, pad, mean=None, std=None):
 
 
 def unpack_wgrad_s2d(dwin, pw, lane=False):
-    return on_wgrad_lane(_unpack_wgrad_s2d, dwin, pw, keep=(dwin,)) if lane else _unpack_wgrad_s2d(dwin, pw)
+    return on_wgrad_lane(_unpack_wgrad_s2d, dwin, pw, keep=(dwin,), chain=True) if lane else _unpack_wgrad_s2d(dwin, pw)
 
 
 def _unpack_wgrad_s2d(dwin, pw):
@@ -471,7 +471,7 @@ def im2col(x, r, s, stride, pad):
 def unpack_wgrad_im2col(dwcol, pw, lane=False):
     """fp32 [k, c_pad, 1, 1] gradient of the gathered-matrix GEMM -> fp32 OIHW gradient of the original filter
     (on the weight-gradient lane, behind the wgrad that produced ``dwcol``)."""
-    return on_wgrad_lane(_unpack_wgrad_im2col, dwcol, pw, keep=(dwcol,)) if lane else _unpack_wgrad_im2col(dwcol, pw)
+    return on_wgrad_lane(_unpack_wgrad_im2col, dwcol, pw, keep=(dwcol,), chain=True) if lane else _unpack_wgrad_im2col(dwcol, pw)
 
 
 def _unpack_wgrad_im2col(dwcol, pw):
@@ -578,6 +578,10 @@ import os as _os
 
 _LANE_ON = _os.environ.get('B200SEG_WGRAD_LANE', '1') != '0'
 _lanes = {}
+# Several lanes, taken round-robin: weight-gradient kernels hold one CTA per SM, and a launch rarely fills the GPU evenly
+# (128 CTAs of an 8-cluster launch leave 20 SMs idle; the corner-tap CTAs of a dilated 3x3 finish in a quarter of the
+# centre tap's time) — with the next wgrad on another stream its CTAs take those SMs instead of waiting for the tail.
+_N_LANES = max(1, int(_os.environ.get('B200SEG_WGRAD_LANES', '1')))      # measured: 1 / 2 / 3 / 4 lanes = 11.66 / 11.64 / 11.64 / 11.64 ms per step: one is enough
 
 
 class _Lane:
@@ -587,22 +591,38 @@ class _Lane:
         self.dirty = False
 
 
-def _lane(device):
+class _LaneSet:
+    def __init__(self, device):
+        self.lanes = [_Lane(device) for _ in range(_N_LANES)]
+        self.next = 0
+        self.last = self.lanes[0]
+
+    def take(self, chain=False):
+        """The next lane in turn; ``chain``: the lane the previous call used (an op that consumes its result)."""
+        if not chain:
+            self.last = self.lanes[self.next]
+            self.next = (self.next + 1) % len(self.lanes)
+        return self.last
+
+
+def _laneset(device):
     if not _LANE_ON:
         return None
     key = device.index if device.index is not None else torch.cuda.current_device()
-    ln = _lanes.get(key)
-    if ln is None:
-        ln = _lanes[key] = _Lane(device)
-    return ln
+    ls = _lanes.get(key)
+    if ls is None:
+        ls = _lanes[key] = _LaneSet(device)
+    return ls
 
 
-def on_wgrad_lane(fn, *args, keep=()):
-    """Runs ``fn(*args)`` on the weight-gradient lane, ordered after everything enqueued so far on the current stream."""
+def on_wgrad_lane(fn, *args, keep=(), chain=False):
+    """Runs ``fn(*args)`` on a weight-gradient lane, ordered after everything enqueued so far on the current stream.
+    ``chain=True``: on the same lane as the previous call (its input is that call's output)."""
     dev = next((t.device for t in keep if isinstance(t, torch.Tensor)), None)
-    ln = _lane(dev) if dev is not None else None
-    if ln is None:
+    ls = _laneset(dev) if dev is not None else None
+    if ls is None:
         return fn(*args)
+    ln = ls.take(chain)
     ln.stream.wait_stream(torch.cuda.current_stream())
     with torch.cuda.stream(ln.stream):
         out = fn(*args)
@@ -612,12 +632,13 @@ def on_wgrad_lane(fn, *args, keep=()):
 
 
 def join_wgrad_lane():
-    """The current stream waits for the weight-gradient lane; called before an autograd Function hands its gradients back."""
-    for ln in _lanes.values():
-        if ln.dirty:
-            torch.cuda.current_stream().wait_stream(ln.stream)
-            ln.keep.clear()
-            ln.dirty = False
+    """The current stream waits for the weight-gradient lanes; called before an autograd Function hands its gradients back."""
+    for ls in _lanes.values():
+        for ln in ls.lanes:
+            if ln.dirty:
+                torch.cuda.current_stream().wait_stream(ln.stream)
+                ln.keep.clear()
+                ln.dirty = False
 
 
 def conv_wgrad(dy, x, k_out, r, s, dil, dw=None, stride=1, lane=False):
@@ -693,16 +714,20 @@ def deliver_grads(grads, params):
     ready = [p for p in params if grads.get(p) is not None]
     if not ready:
         return
-    ln = _lane(ready[0].device) if (SINK_ON_LANE and ready[0].is_cuda) else None
-    if ln is None:
-        join_wgrad_lane()            # weight gradients live on the side stream until joined
+    ls = _laneset(ready[0].device) if (SINK_ON_LANE and ready[0].is_cuda) else None
+    if ls is None:
+        join_wgrad_lane()            # weight gradients live on the side streams until joined
         GRAD_SINK(grads, ready)
         return
-    # The weight gradients of this stage are still being computed on the weight-gradient lane.  Joining the lane here
-    # would stall the compute stream at every stage boundary (measured: most of the 0.5 ms a step lost at 8 GPUs);
-    # instead the sink — the bucket copy and the all-reduce launch — runs ON the lane, behind those wgrads, and only the
-    # lane waits (for the BN parameter gradients the compute stream produced).  The node joins the lane before it returns.
+    # The weight gradients of this stage are still being computed on the weight-gradient lanes.  Joining them here
+    # would stall the compute stream at every stage boundary; instead the sink — the bucket copy and the all-reduce
+    # launch — runs ON a lane, behind those wgrads, and only that lane waits (for the other lanes and for the BN
+    # parameter gradients the compute stream produced).  The node joins the lanes before it returns.
+    ln = ls.lanes[0]
     ln.stream.wait_stream(torch.cuda.current_stream())
+    for other in ls.lanes[1:]:
+        if other.dirty:
+            ln.stream.wait_stream(other.stream)
     with torch.cuda.stream(ln.stream):
         GRAD_SINK(grads, ready)
     ln.dirty = True
