@@ -174,6 +174,19 @@ def run_reference(args):
                 'gpu_launches': 0}
         print(json.dumps(line), flush=True)
         return
+    if args.config in ('infer', 'aspp', 'hrnet'):
+        ips, dt, threads, batch, what = cpu_other_run(args.config, max(2, min(args.steps, 10)))
+        metric = OTHER[args.config][6]
+        line = {'impl': 'reference', 'metric': metric, 'value': ips, 'unit': 'images/sec', 'n_gpus': args.gpus,
+                'steps': max(2, min(args.steps, 10)), 'warmup': 1, 'ms_per_step': dt * 1e3, 'higher_is_better': True,
+                'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+                'config': {'workload': what, 'per_step_batch': batch},
+                'cpu_baseline': {'value': ips, 'unit': 'images/sec', 'cores': threads, 'kind': 'port', 'cpu': cpu_model(),
+                                 'sample': 'batch %d per step (bounded sample), 1 warm-up' % batch},
+                'e2e': {'value': ips, 'unit': 'images/sec', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+                'gpu_launches': 0}
+        print(json.dumps(line), flush=True)
+        return
     steps, warmup = max(1, min(args.steps, 20)), max(1, min(args.warmup, 2))
     ips, dt, threads = cpu_reference_run(steps, warmup)
     sample = 'batch %d per step, %d timed steps (bounded sample of the per-GPU batch-%d step)' % (
@@ -188,6 +201,63 @@ def run_reference(args):
             'e2e': {'value': ips, 'unit': 'images/sec', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
     print(json.dumps(line), flush=True)
+
+
+def cpu_other_run(config, steps):
+    """The oracle's CPU leg of the configurations other than training / UNet: a bounded batch of the same workload.
+    Returns (images/sec, seconds per step, threads, batch, workload text)."""
+    from oracle import restatement as R
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    g = torch.Generator().manual_seed(0)
+    if config == 'infer':
+        batch = 2
+        model = R.OracleModel('deeplabv3plus', NC, seed=0).eval()
+        x, t = torch.randn(batch, 3, H, W, generator=g), torch.randint(0, NC, (batch, H, W), generator=g)
+
+        def step():
+            with torch.no_grad():
+                y = model(x)
+                return R.confusion_matrix(y.max(1)[1], t, NC)
+        what = 'DeepLabV3+ 21-class 512x512 inference + confusion histogram (configs[1]); CPU oracle, fp32'
+    elif config == 'aspp':
+        batch = 2
+        sd = {}
+        full = R.OracleModel('deeplabv3plus', NC, seed=0)
+        sd = {k: v for k, v in full.sd.items() if k.startswith('aspp.')}
+        x = torch.randn(batch, 2048, 32, 32, generator=g).requires_grad_(True)
+        gy = torch.randn(batch, 256, 32, 32, generator=g)
+
+        def step():
+            x.grad = None
+            for v in sd.values():
+                v.grad = None
+            y = R.aspp(sd, 'aspp', x, R.DEEPLAB_RATES, True)
+            y.backward(gy)
+            return y
+        what = 'ASPP(2048, 256, [6, 12, 18]) forward + backward (configs[2]); CPU oracle, fp32'
+    else:
+        from oracle import hrnet_restatement as HR
+        batch = 1
+        sd = HR.make_state(19, seed=0)
+        for k, v in sd.items():
+            if v.is_floating_point() and 'running_' not in k:
+                v.requires_grad_(True)
+        x, t = torch.randn(batch, 3, 512, 1024, generator=g), torch.randint(0, 19, (batch, 512, 1024), generator=g)
+
+        def step():
+            for v in sd.values():
+                v.grad = None
+            loss = R.compute_loss(HR.hrnet(sd, x, training=True), t)
+            loss.backward()
+            return loss
+        what = 'HRNet 19-class 1024x512 training step fwd+loss+bwd (configs[4]); CPU oracle, fp32'
+    step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / steps
+    return batch / dt, dt, threads, batch, what
 
 
 # -----------------------------------------------------------------------------------------------------------

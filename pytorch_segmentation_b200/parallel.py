@@ -15,8 +15,14 @@ buckets those are would wait on each other forever.  ``sync_initial_state()`` is
 There is no collective on the data path itself: images are independent through every kernel
 (train-mode BatchNorm statistics stay per-GPU, as in the reference, which shows no SyncBN).
 """
+import os
+
 import torch
 import torch.distributed as dist
+
+# diagnosis only (bench A/B): bucket the gradients but skip the collective, to separate the bucketing's own cost from the
+# all-reduce's contention with backward — the ranks then train independently
+_SKIP_ALLREDUCE = os.environ.get('B200SEG_SKIP_ALLREDUCE', '0') == '1'
 
 
 class GradBucketer:
@@ -180,7 +186,7 @@ class GradBucketer:
 
     def _launch(self, bi):
         self._flush_moves(bi)
-        if self.world > 1:
+        if self.world > 1 and not _SKIP_ALLREDUCE:
             self._handles.append((bi, dist.all_reduce(self._buckets[bi][0], op=dist.ReduceOp.SUM, group=self.group,
                                                       async_op=True)))
 
