@@ -360,6 +360,13 @@ def run_b200(args):
         step_e2e()
     secs_e2e = timed(step_e2e, args.steps)
     torch.cuda.synchronize()
+    # the same step called eagerly, as the reference's external Trainer would (no graph): host-bound by the Python +
+    # ctypes enqueue cost the graph removes
+    eager_ips = None
+    if use_graph:
+        eager(x_dev, t_dev)
+        k_eager = max(3, min(args.steps, 10))
+        eager_ips = world * B * k_eager / timed(lambda: eager(x_dev, t_dev), k_eager)
 
     # per-launch CUDA-event timing of the tcgen05 conv kernels over a few more steps (the events sit on the
     # launching stream; kept out of the throughput loop above so the headline has no instrumentation in it)
@@ -434,6 +441,7 @@ def run_b200(args):
                                    'and masks as the dataset yields them, post_fetch_fn normalisation fused into the stem pass',
                        'per_gpu_batch': B, 'global_batch': B * world, 'parallelism': 'dp%d' % world,
                        'cuda_graph': bool(use_graph), 'host_enqueue_ms_per_eager_step': round(host_enqueue_ms, 2),
+                       'eager_images_per_sec': round(eager_ips, 1) if eager_ips else None,
                        'libb200seg_launches_per_step': eager_launches,
                        'l2': 'no explicit flush: one step streams several GB of activations (>> 126 MB L2)',
                        'backbone': 'ResNet-50 OS16 on libb200seg (tcgen05 convs incl. stride 2, fused BN/ReLU/residual, '

@@ -15,7 +15,27 @@ The walk below follows the reference's module tree by state-dict prefix:
 import torch
 import torch.nn.functional as F
 
+from . import restatement as _R
+
 BN_EPS, BN_MOMENTUM = 1e-5, 0.1     # nn.BatchNorm2d defaults; hrnet.py:14 passes momentum=0.1 explicitly
+
+# Mask-matched mode (tests/test_gpu_gradparity.py): under ``restatement.substituted(values, grad_log=...)`` every conv
+# result, BatchNorm / ReLU / residual output and fused branch sum takes the VALUE (and ReLU mask) the CUDA run stored,
+# and the backward is re-synchronised at every stored gradient of a raw conv output.  Keys are the reference's
+# state-dict names of the conv weight + '.raw' / '.out' / '.graw'; the fused sums are 'sum_relu.<n>' in forward order.
+# Outside that context the helpers below are the identity / a plain ReLU.
+_SEQ = [0]
+
+
+def _conv(sd, wkey, x, stride=1, pad=0):
+    y = _R._subst(wkey + '.raw', F.conv2d(x, sd[wkey], None, stride, pad))
+    return _R._resync(wkey + '.graw', y)
+
+
+def _act(wkey, y, relu):
+    if relu and _R._SUBST is not None:
+        return _R._relu_adopt(y, wkey + '.out', _R._SUBST, _R._RECORD)
+    return _R._subst(wkey + '.out', F.relu(y) if relu else y)
 
 
 def _bn(sd, p, y, training):
@@ -27,30 +47,30 @@ def _bn(sd, p, y, training):
 
 def _cna(sd, p, x, ksize, stride, relu, training):
     """ConvNormAct under prefix p: conv = p.0, bn = p.1 (oracle/shim/pytorch_modules/nn)."""
-    y = F.conv2d(x, sd[p + '.0.weight'], None, stride, (ksize - 1) // 2)
-    y = _bn(sd, p + '.1', y, training)
-    return F.relu(y) if relu else y
+    y = _conv(sd, p + '.0.weight', x, stride, (ksize - 1) // 2)
+    return _act(p + '.0.weight', _bn(sd, p + '.1', y, training), relu)
 
 
 def _shortcut(sd, p, x, training):
     if (p + '.downsample.0.weight') not in sd:
         return x
-    return _bn(sd, p + '.downsample.1', F.conv2d(x, sd[p + '.downsample.0.weight']), training)
+    k = p + '.downsample.0.weight'
+    return _act(k, _bn(sd, p + '.downsample.1', _conv(sd, k, x), training), False)
 
 
 def basic_block(sd, p, x, training):
     """hrnet.py:39-56"""
-    y = F.relu(_bn(sd, p + '.bn1', F.conv2d(x, sd[p + '.conv1.weight'], None, 1, 1), training))
-    y = _bn(sd, p + '.bn2', F.conv2d(y, sd[p + '.conv2.weight'], None, 1, 1), training)
-    return F.relu(y + _shortcut(sd, p, x, training))
+    y = _act(p + '.conv1.weight', _bn(sd, p + '.bn1', _conv(sd, p + '.conv1.weight', x, 1, 1), training), True)
+    y = _bn(sd, p + '.bn2', _conv(sd, p + '.conv2.weight', y, 1, 1), training)
+    return _act(p + '.conv2.weight', y + _shortcut(sd, p, x, training), True)
 
 
 def bottleneck(sd, p, x, training):
     """hrnet.py:83-103"""
-    y = F.relu(_bn(sd, p + '.bn1', F.conv2d(x, sd[p + '.conv1.weight']), training))
-    y = F.relu(_bn(sd, p + '.bn2', F.conv2d(y, sd[p + '.conv2.weight'], None, 1, 1), training))
-    y = _bn(sd, p + '.bn3', F.conv2d(y, sd[p + '.conv3.weight']), training)
-    return F.relu(y + _shortcut(sd, p, x, training))
+    y = _act(p + '.conv1.weight', _bn(sd, p + '.bn1', _conv(sd, p + '.conv1.weight', x), training), True)
+    y = _act(p + '.conv2.weight', _bn(sd, p + '.bn2', _conv(sd, p + '.conv2.weight', y, 1, 1), training), True)
+    y = _bn(sd, p + '.bn3', _conv(sd, p + '.conv3.weight', y), training)
+    return _act(p + '.conv3.weight', y + _shortcut(sd, p, x, training), True)
 
 
 def _count(sd, prefix):
@@ -86,12 +106,14 @@ def hr_module(sd, p, xs, multi_scale_output, training):
                     last = k == i - j - 1
                     t = _cna(sd, '%s.%d' % (q, k) if last else '%s.%d.0' % (q, k), t, 3, 2, not last, training)
             y = t if y is None else y + t
-        outs.append(F.relu(y))
+        outs.append(_act('sum_relu.%d' % _SEQ[0], y, True))
+        _SEQ[0] += 1
     return outs
 
 
 def hrnet(sd, x, branches=(2, 3, 4), training=False):
     """hrnet.py:373-406.  ``sd`` is mutated in training mode (BN running statistics), like the module."""
+    _SEQ[0] = 0
     x = _cna(sd, 'stem.0', x, 3, 2, False, training)
     x = _cna(sd, 'stem.1', x, 3, 2, True, training)
     for i in range(_count(sd, 'stem.2')):

@@ -47,20 +47,53 @@ _SUBST = None
 _RECORD = False
 
 
-class substituted:
-    """``record=True`` fills ``values`` with the oracle's own tensors at the same keys instead (CPU self-tests)."""
+_GRAD_LOG = None
 
-    def __init__(self, values, record=False):
-        self.values, self.record = values, record
+
+class substituted:
+    """``record=True`` fills ``values`` with the oracle's own tensors at the same keys instead (CPU self-tests).
+    ``grad_log`` (a dict) switches on the backward re-synchronisation of ``_resync`` for the functional restatements."""
+
+    def __init__(self, values, record=False, grad_log=None):
+        self.values, self.record, self.grad_log = values, record, grad_log
 
     def __enter__(self):
-        global _SUBST, _RECORD
-        self._prev, _SUBST, _RECORD = (_SUBST, _RECORD), self.values, self.record
+        global _SUBST, _RECORD, _GRAD_LOG
+        self._prev = (_SUBST, _RECORD, _GRAD_LOG)
+        _SUBST, _RECORD, _GRAD_LOG = self.values, self.record, self.grad_log
         return self
 
     def __exit__(self, *exc):
-        global _SUBST, _RECORD
-        _SUBST, _RECORD = self._prev
+        global _SUBST, _RECORD, _GRAD_LOG
+        _SUBST, _RECORD, _GRAD_LOG = self._prev
+
+
+def _resync(key, y):
+    """Backward re-synchronisation at a tensor whose gradient the CUDA run stored (bf16) under ``key``: when backward
+    reaches ``y`` the oracle's own gradient is logged beside the stored one (the caller compares the pair: one
+    kernel-step of error) and REPLACED by the stored one, so storage noise does not accumulate from layer to layer and
+    every layer's backward is checked on the gradient its CUDA counterpart actually received."""
+    if _SUBST is None or not y.requires_grad:
+        return y
+    if _RECORD:                       # CPU self-tests: the oracle's own gradient becomes the "stored" one
+        vals = _SUBST
+        y = y.view_as(y)
+        y.register_hook(lambda g: vals.__setitem__(key, g.detach().clone()))
+        return y
+    if _GRAD_LOG is None:
+        return y
+    g_stored = _SUBST.get(key)
+    if g_stored is None:
+        return y
+    log = _GRAD_LOG
+
+    def on_grad(g):
+        gs = g_stored.to(g.dtype).reshape(g.shape)
+        log[key] = (g.detach().clone(), gs)
+        return gs
+    y = y.view_as(y)
+    y.register_hook(on_grad)
+    return y
 
 
 def _subst(key, y):

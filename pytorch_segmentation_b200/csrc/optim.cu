@@ -238,33 +238,14 @@ struct PackChunk {
 // OIHW is [k][c][tap] with the taps contiguous, both packings want them outermost.  Reading one element per packed
 // element strides the loads by `taps` floats (9x sector over-fetch: 335 us for DeepLabV3+'s 39 M weights); instead a
 // block stages a 32 x 32 x taps tile through shared memory: 288-float contiguous runs in, 64-byte runs out
-// (wf[tap][k][c..c+31], wd[tap'][c][k..k+31]).
-__global__ void __launch_bounds__(256) pack_multi_kernel(const __grid_constant__ PackChunk c) {
-    pdl_prologue();
-    __shared__ __align__(16) float tile[kPackSmemFloats];
-    int lo = 0, hi = c.n - 1;
-    while (lo < hi) {
-        const int mid = (lo + hi + 1) >> 1;
-        if (c.blk_start[mid] <= static_cast<int>(blockIdx.x)) lo = mid; else hi = mid - 1;
-    }
-    const b200seg_pack_desc& t = c.t[lo];
+// (wf[tap][k][c..c+31], wd[tap'][c][k..k+31]).  kTaps = 1 / 9 make every index split a compile-time constant (the
+// run-time divisions of the generic form, three per packed pair, were half of this kernel's time); 0 = any r x s.
+template <int kTaps>
+__device__ __forceinline__ void pack_tile(const b200seg_pack_desc& t, int local, float* tile) {
     const float* __restrict__ w = t.w;
-    const int taps = t.r * t.s;
-    const int local = blockIdx.x - c.blk_start[lo];
+    const int taps = kTaps > 0 ? kTaps : t.r * t.s;
     __nv_bfloat16* wf = static_cast<__nv_bfloat16*>(t.w_fprop);
     __nv_bfloat16* wd = static_cast<__nv_bfloat16*>(t.w_dgrad);
-    if (t.im2col) {
-        // patch-gather packing of a few-channel stem: tiny, one element per thread
-        const long long total = static_cast<long long>(t.k_rows) * t.c_pad;
-        for (long long i = static_cast<long long>(local) * 2048 + threadIdx.x; i < static_cast<long long>(local + 1) * 2048 && i < total;
-             i += 256) {
-            const int j = static_cast<int>(i % t.c_pad), kk = static_cast<int>(i / t.c_pad);
-            float v = 0.f;
-            if (kk < t.k && j < taps * t.c) v = __ldg(w + (static_cast<size_t>(kk) * t.c + j % t.c) * taps + j / t.c);
-            wf[i] = __float2bfloat16(v);
-        }
-        return;
-    }
     const int tk = pack_tile_k(taps);
     const int tiles_c = (t.c_rows + kPackTile - 1) / kPackTile;
     const int k0 = (local / tiles_c) * tk, c0 = (local % tiles_c) * kPackTile;
@@ -275,10 +256,12 @@ __global__ void __launch_bounds__(256) pack_multi_kernel(const __grid_constant__
                      (reinterpret_cast<uintptr_t>(w) & 15) == 0;
     if (vec) {
         const int run4 = run >> 2;
+        const float* base = w + (static_cast<size_t>(k0) * t.c + c0) * taps;
+        const size_t k_pitch = static_cast<size_t>(t.c) * taps;
         for (int i = threadIdx.x; i < tk * run4; i += 256) {
             const int kk = i / run4, j = (i - kk * run4) << 2;
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (k0 + kk < t.k) v = __ldg(reinterpret_cast<const float4*>(w + (static_cast<size_t>(k0 + kk) * t.c + c0) * taps + j));
+            if (k0 + kk < t.k) v = __ldcs(reinterpret_cast<const float4*>(base + kk * k_pitch + j));
             float* d = tile + kk * pitch + j;
             d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
         }
@@ -295,8 +278,9 @@ __global__ void __launch_bounds__(256) pack_multi_kernel(const __grid_constant__
     // fprop packing: [tap][k_rows][c], 32 consecutive c per (tap, k): a thread writes a bf16 pair
     if (wf) {
         const bool pair = (t.c & 1) == 0;
-        for (int i = threadIdx.x; i < taps * tk * (kPackTile / 2); i += 256) {
-            const int cc = (i % (kPackTile / 2)) * 2, kk = (i / (kPackTile / 2)) % tk, tap = i / ((kPackTile / 2) * tk);
+        constexpr int kHalf = kPackTile / 2;
+        for (int i = threadIdx.x; i < taps * tk * kHalf; i += 256) {
+            const int cc = (i % kHalf) * 2, kk = (i / kHalf) % tk, tap = i / (kHalf * tk);
             if (k0 + kk >= t.k_rows || c0 + cc >= t.c) continue;
             __nv_bfloat16* d = wf + (static_cast<size_t>(tap) * t.k_rows + k0 + kk) * t.c + c0 + cc;
             const float a = tile[kk * pitch + cc * taps + tap], b = tile[kk * pitch + (cc + 1) * taps + tap];
@@ -325,6 +309,37 @@ __global__ void __launch_bounds__(256) pack_multi_kernel(const __grid_constant__
             }
         }
     }
+}
+
+__global__ void __launch_bounds__(256) pack_multi_kernel(const __grid_constant__ PackChunk c) {
+    pdl_prologue();
+    __shared__ __align__(16) float tile[kPackSmemFloats];
+    int lo = 0, hi = c.n - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (c.blk_start[mid] <= static_cast<int>(blockIdx.x)) lo = mid; else hi = mid - 1;
+    }
+    const b200seg_pack_desc& t = c.t[lo];
+    const int local = blockIdx.x - c.blk_start[lo];
+    if (t.im2col) {
+        // patch-gather packing of a few-channel stem: tiny, one element per thread
+        const float* __restrict__ w = t.w;
+        const int taps = t.r * t.s;
+        __nv_bfloat16* wf = static_cast<__nv_bfloat16*>(t.w_fprop);
+        const long long total = static_cast<long long>(t.k_rows) * t.c_pad;
+        for (long long i = static_cast<long long>(local) * 2048 + threadIdx.x; i < static_cast<long long>(local + 1) * 2048 && i < total;
+             i += 256) {
+            const int j = static_cast<int>(i % t.c_pad), kk = static_cast<int>(i / t.c_pad);
+            float v = 0.f;
+            if (kk < t.k && j < taps * t.c) v = __ldg(w + (static_cast<size_t>(kk) * t.c + j % t.c) * taps + j / t.c);
+            wf[i] = __float2bfloat16(v);
+        }
+        return;
+    }
+    const int taps = t.r * t.s;
+    if (taps == 9) pack_tile<9>(t, local, tile);
+    else if (taps == 1) pack_tile<1>(t, local, tile);
+    else pack_tile<0>(t, local, tile);
 }
 
 }  // namespace

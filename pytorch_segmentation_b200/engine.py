@@ -14,8 +14,25 @@ from ._lib import ConvOut, ConvSrc, WgradDesc
 BF16 = torch.bfloat16
 
 
+# torch.cuda.current_stream() costs ~4 us of Python per call (device-index resolution, a Stream object) and an eager
+# training step asks ~500 times; the raw handle is one C call.
+_raw_stream = torch._C._cuda_getCurrentRawStream
+_cur_device = torch._C._cuda_getDevice
+_stream_objs = {}
+
+
 def _stream():
-    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return ctypes.c_void_p(_raw_stream(_cur_device()))
+
+
+def current_stream():
+    """torch.cuda.current_stream(), with the Stream objects cached by (device, raw handle)."""
+    dev = _cur_device()
+    key = (dev, _raw_stream(dev))
+    st = _stream_objs.get(key)
+    if st is None:
+        st = _stream_objs[key] = torch.cuda.current_stream()
+    return st
 
 
 def _require_cuda(t, what):
@@ -118,6 +135,14 @@ def capture(param, kind, value):
     if CAPTURE is not None:
         t = value.nchw() if isinstance(value, Act) else value
         CAPTURE[(id(param), kind)] = t.detach().float().clone()
+
+
+def capture_seq(family, value):
+    """The same for tensors no parameter names (the fused sums of HRNet's branches): keyed by call order within
+    ``family`` — CAPTURE[('seq', family)] is the list, in the order the forward produced them."""
+    if CAPTURE is not None:
+        t = value.nchw() if isinstance(value, Act) else value
+        CAPTURE.setdefault(('seq', family), []).append(t.detach().float().clone())
 
 
 # ------------------------------------------------------------------------------------------------
@@ -623,9 +648,13 @@ def on_wgrad_lane(fn, *args, keep=(), chain=False):
     if ls is None:
         return fn(*args)
     ln = ls.take(chain)
-    ln.stream.wait_stream(torch.cuda.current_stream())
-    with torch.cuda.stream(ln.stream):
+    cur = current_stream()
+    ln.stream.wait_stream(cur)
+    torch.cuda.set_stream(ln.stream)          # (the torch.cuda.stream() context manager costs ~10 us per use)
+    try:
         out = fn(*args)
+    finally:
+        torch.cuda.set_stream(cur)
     ln.keep.extend(keep)
     ln.dirty = True
     return out
@@ -636,7 +665,7 @@ def join_wgrad_lane():
     for ls in _lanes.values():
         for ln in ls.lanes:
             if ln.dirty:
-                torch.cuda.current_stream().wait_stream(ln.stream)
+                current_stream().wait_stream(ln.stream)
                 ln.keep.clear()
                 ln.dirty = False
 
@@ -724,7 +753,7 @@ def deliver_grads(grads, params):
     # launch — runs ON a lane, behind those wgrads, and only that lane waits (for the other lanes and for the BN
     # parameter gradients the compute stream produced).  The node joins the lanes before it returns.
     ln = ls.lanes[0]
-    ln.stream.wait_stream(torch.cuda.current_stream())
+    ln.stream.wait_stream(current_stream())
     for other in ls.lanes[1:]:
         if other.dirty:
             ln.stream.wait_stream(other.stream)

@@ -105,6 +105,7 @@ class ConvNormAct(nn.Sequential):
         x, raw, vec, training = rec
         draw = E.Act.empty(raw.n, raw.h, raw.w, raw.c, raw.t.device)
         dgamma, dbeta = E.bn_backward(dout, raw, draw, vec, self.relu, training)
+        E.capture(self[0].weight, 'graw', draw)          # parity tests: the stored gradient of the raw conv output
         dw = E.conv_wgrad(draw, x, self[0].out_channels, self.ksize, self.ksize, self.dilation, lane=True)
         return draw, [dw, dgamma, dbeta]
 

@@ -126,6 +126,7 @@ class _ConvBNFn(torch.autograd.Function):
         else:
             draw = E.Act.empty(raw.n, raw.h, raw.w, raw.c, dev)
             dgamma, dbeta = E.bn_backward(da, raw, draw, vec, relu, training)
+        E.capture(conv.weight, 'graw', draw)             # parity tests: the stored gradient of the raw conv output
         if state.gather:
             dwcol = E.conv_wgrad(draw, xa, raw.c, pw.r, pw.s, 1, lane=True)
             dw = (E.unpack_wgrad_s2d if state.s2d else E.unpack_wgrad_im2col)(dwcol, pw, lane=True)
@@ -185,6 +186,7 @@ class _SumReLUFn(torch.autograd.Function):
             cur = [tgt] + rest
         ctx.y = y if relu else None
         ctx.xs = xs
+        E.capture_seq('sum_relu', y)
         return y.nchw()
 
     @staticmethod

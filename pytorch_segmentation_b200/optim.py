@@ -19,6 +19,7 @@ import math
 import torch
 
 from . import _lib
+from . import engine as _engine
 
 
 def _dense(p):
@@ -89,7 +90,7 @@ class SGD(_HyperMixin, torch.optim.Optimizer):
             with torch.enable_grad():
                 loss = closure()
         lib = _lib.load()
-        stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        stream = _engine._stream()
         for gi, group in enumerate(self.param_groups):
             momentum = float(group['momentum'])
             with_buf, without_buf = [], []
@@ -167,7 +168,7 @@ class Adam(_HyperMixin, torch.optim.Optimizer):
             with torch.enable_grad():
                 loss = closure()
         lib = _lib.load()
-        stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        stream = _engine._stream()
         for gi, group in enumerate(self.param_groups):
             old, new = [], []
             for p in group['params']:

@@ -174,12 +174,11 @@ class GradBucketer:
         moves = self._moves[bi]
         if not moves:
             return
-        import ctypes
-        from . import _lib
+        from . import _lib, engine as _engine
         arr = (_lib.SgdDesc * len(moves))()
         for i, (dst, src) in enumerate(moves):
             arr[i] = _lib.SgdDesc(dst.data_ptr(), src.data_ptr(), None, src.numel())
-        _lib.check(_lib.load().b200seg_copy_multi(arr, len(moves), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)),
+        _lib.check(_lib.load().b200seg_copy_multi(arr, len(moves), _engine._stream()),
                    'copy_multi')
         _lib.count_launch((len(moves) + 95) // 96)
         self._moves[bi] = []

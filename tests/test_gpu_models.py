@@ -222,10 +222,10 @@ def test_argmax_agreement(P):
 @pytest.mark.parametrize('name', ['deeplab_small', 'unet_320', 'deeplab_512'])
 def test_whole_model_matches_reference_golden(P, name):
     """Drop-in API end to end: model(x) on N x 3 x H x W float input returns N x nc x H x W fp32 logits.
-    Eval mode is compared with the reference's golden logits.  In train mode the random-init bf16 backbone
-    (torchvision under autocast — outside the hot path) is chaotic at N=2 (the library bf16 pipeline itself
-    is ~45 % away from fp32 there), so only the API contract and the loss are checked; gradient parity of
-    the hot path is covered by the head tests above on identical features."""
+    Eval mode is compared with the reference's golden logits.  In train mode a random-init bf16 ResNet-50 is chaotic
+    at N=2 against an independent fp32 run (batch statistics over a few hundred pixels amplify every rounding; any bf16
+    pipeline is ~45 % away from fp32 there), so only the API contract and the loss are checked here; composed-gradient
+    parity of the whole model is proven against the mask-matched oracle in tests/test_gpu_gradparity.py."""
     c = G.CASES[name]
     gold = G.load(name)
     oracle = R.OracleModel(c['kind'], c['nc'], seed=c['seed'])

@@ -242,3 +242,51 @@ def test_mask_matched_substitution_machinery():
     err = float((y2 - y0).abs().max()) / float(y0.abs().max())
     assert 0 < err < 5e-2, err
     assert all(g is not None and bool(torch.isfinite(g).all()) for g in g2.values())
+
+
+def test_hrnet_mask_matched_machinery():
+    """oracle/hrnet_restatement.py under ``restatement.substituted``: recording the oracle's own boundary tensors and
+    gradients, then substituting them back with the backward re-synchronisation on, is the identity — same logits, same
+    parameter gradients, and every logged (own, stored) gradient pair equal; the number of boundaries is the number of
+    convs in front of a BatchNorm."""
+    from oracle import hrnet_restatement as H
+    nc, seed = 5, 2
+    g = torch.Generator().manual_seed(seed)
+    x, t = torch.randn(2, 3, 64, 64, generator=g), torch.randint(0, nc, (2, 64, 64), generator=g)
+
+    def run(values, record=False, grad_log=None):
+        sd = H.make_state(nc, seed=seed)
+        for v in sd.values():
+            if v.is_floating_point():
+                v.requires_grad_(True)
+        for k in sd:
+            if 'running_' in k:
+                sd[k] = sd[k].detach()
+        ctx = R.substituted(values, record=record, grad_log=grad_log) if values is not None else None
+        if ctx is not None:
+            with ctx:
+                y = H.hrnet(sd, x, training=True)
+                loss = R.compute_loss(y, t)
+                loss.backward()
+        else:
+            y = H.hrnet(sd, x, training=True)
+            R.compute_loss(y, t).backward()
+        return y.detach(), {k: v.grad for k, v in sd.items() if v.requires_grad}
+
+    y0, g0 = run(None)
+    values = {}
+    y1, g1 = run(values, record=True)
+    assert torch.equal(y0, y1)
+    convs = [k for k in g0 if k.endswith('.weight') and g0[k].dim() == 4 and k != 'final_layer.weight']
+    assert len([k for k in values if k.endswith('.raw')]) == len(convs)
+    assert len([k for k in values if k.endswith('.graw')]) == len(convs)
+    assert len([k for k in values if k.startswith('sum_relu.')]) == 2 + 3 + 1
+    log = {}
+    y2, g2 = run(values, grad_log=log)
+    assert len(log) == len(convs)
+    assert torch.allclose(y0, y2, rtol=1e-5, atol=1e-6)
+    for k, (own, stored) in log.items():
+        assert torch.allclose(own, stored, rtol=1e-4, atol=1e-7 + 1e-5 * float(stored.abs().max())), k
+    for k in g0:
+        assert g2[k] is not None, k
+        assert torch.allclose(g0[k], g2[k], rtol=1e-3, atol=1e-5 * float(g0[k].abs().max()) + 1e-9), k
