@@ -366,6 +366,11 @@ def run_b200(args):
     if use_graph:
         eager(x_dev, t_dev)
         k_eager = max(3, min(args.steps, 10))
+        eager(x_dev, t_dev)                             # the pool has regrown by now: a steady-state eager step
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        eager(x_dev, t_dev)
+        host_enqueue_ms = (time.perf_counter() - t0) * 1e3
         eager_ips = world * B * k_eager / timed(lambda: eager(x_dev, t_dev), k_eager)
 
     # per-launch CUDA-event timing of the tcgen05 conv kernels over a few more steps (the events sit on the

@@ -444,6 +444,13 @@ int b200seg_input_u8_normalize(const uint8_t* x, int layout, int n, int c, int h
 int b200seg_input_u8_s2d(const uint8_t* x, int layout, int n, int c, int h, int w, int r, int s, int pad, const float* mean,
                          const float* std, void* z, int cs, b200seg_stream_t st);
 
+/* multi_scale of post_fetch_fn (utils/datasets.py:206-212): F.interpolate(imgs, (oh, ow)) — mode 'nearest' — applied to
+ * the 1-byte planes BEFORE the normalisation (nearest sampling commutes with a per-pixel map, so the float result is the
+ * reference's bit for bit).  x: [planes][h][w] uint8 (planes = n*c for NCHW images, n for masks), y: [planes][oh][ow].
+ * Source index = min(int(floorf(dst * float(in)/out)), in - 1), ATen's fp32 arithmetic. */
+int b200seg_resize_nearest_u8(const uint8_t* x, int64_t planes, int h, int w, uint8_t* y, int oh, int ow,
+                              b200seg_stream_t st);
+
 #ifdef __cplusplus
 }
 #endif

@@ -136,6 +136,7 @@ PROTOTYPES = {
     'b200seg_class_map_confusion': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _P, _P, _P]),
     'b200seg_input_u8_normalize': (c_int, [_P, _I, _I, _I, _I, _I, POINTER(c_float), POINTER(c_float), _P, _P]),
     'b200seg_input_u8_s2d': (c_int, [_P, _I, _I, _I, _I, _I, _I, _I, _I, POINTER(c_float), POINTER(c_float), _P, _I, _P]),
+    'b200seg_resize_nearest_u8': (c_int, [_P, _L, _I, _I, _P, _I, _I, _P]),
 }
 
 _lib = None

@@ -82,6 +82,37 @@ __global__ void __launch_bounds__(256) input_u8_s2d_kernel(const uint8_t* __rest
     if (cs == 16) out[1] = *reinterpret_cast<const uint4*>(v + 8);
 }
 
+// multi_scale (utils/datasets.py:206-212): F.interpolate(imgs, (h, w)), mode 'nearest', on the 1-byte planes — nearest
+// sampling commutes with the per-pixel normalisation, so resizing the uint8 image first gives the reference's float
+// result bit for bit.  Source index as ATen computes it (UpSample.h nearest_neighbor_compute_source_index):
+// min(int(floorf(dst * float(in) / out)), in - 1) in fp32.  One thread per 4 output bytes of a row.
+__global__ void __launch_bounds__(256) resize_nearest_u8_kernel(const uint8_t* __restrict__ x, int H, int W,
+                                                                 uint8_t* __restrict__ y, int OH, int OW, int ow4,
+                                                                 float sh, float sw, int64_t total) {
+    pdl_prologue();
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        const int q = static_cast<int>(i % ow4);
+        const int64_t row = i / ow4;                     // plane * OH + oy
+        const int oy = static_cast<int>(row % OH);
+        const int64_t plane = row / OH;
+        const int iy = min(static_cast<int>(floorf(oy * sh)), H - 1);
+        const uint8_t* src = x + (plane * H + iy) * W;
+        uint8_t* dst = y + row * OW + q * 4;
+        uint8_t v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int ox = q * 4 + k;
+            v[k] = ox < OW ? __ldg(src + min(static_cast<int>(floorf(ox * sw)), W - 1)) : 0;
+        }
+        if (q * 4 + 4 <= OW && (reinterpret_cast<uintptr_t>(dst) & 3) == 0) {
+            *reinterpret_cast<uchar4*>(dst) = make_uchar4(v[0], v[1], v[2], v[3]);
+        } else {
+            for (int k = 0; k < 4 && q * 4 + k < OW; ++k) dst[k] = v[k];
+        }
+    }
+}
+
 int fill_norm(Norm4* nm, int c, const float* mean, const float* std, const char* what) {
     B200SEG_CHECK(mean && std, "%s: null mean / std", what);
     for (int i = 0; i < 4; ++i) {
@@ -134,6 +165,21 @@ int b200seg_input_u8_s2d(const uint8_t* x, int layout, int n, int c, int h, int 
     B200SEG_CUDA(launch_pdl(input_u8_s2d_kernel, static_cast<unsigned>((total + 255) / 256), 256, 0,
                             static_cast<cudaStream_t>(stream), x, layout, c, h, w, pad, zh, zw, cs, nm,
                             static_cast<__nv_bfloat16*>(z), total));
+    return 0;
+}
+
+int b200seg_resize_nearest_u8(const uint8_t* x, int64_t planes, int h, int w, uint8_t* y, int oh, int ow,
+                              b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(x && y, "resize_nearest_u8: null pointer");
+    B200SEG_CHECK(planes > 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "resize_nearest_u8: bad geometry");
+    const int ow4 = (ow + 3) / 4;
+    const int64_t total = planes * oh * ow4;
+    // ATen: scale = float(in) / out, computed in fp32
+    const float sh = static_cast<float>(h) / static_cast<float>(oh), sw = static_cast<float>(w) / static_cast<float>(ow);
+    B200SEG_CUDA(launch_pdl(resize_nearest_u8_kernel, elementwise_grid(total), 256, 0, static_cast<cudaStream_t>(stream),
+                            x, h, w, y, oh, ow, ow4, sh, sw, total));
     return 0;
 }
 

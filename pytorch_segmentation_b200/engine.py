@@ -453,6 +453,21 @@ def normalize_u8(x, mean=None, std=None):
     return y
 
 
+def resize_nearest_u8(x, oh, ow):
+    """uint8 [..., H, W] (contiguous) -> [..., oh, ow], F.interpolate(mode='nearest') indexing (csrc/input.cu)."""
+    _require_cuda(x, 'resize_nearest_u8 input')
+    if x.dtype != torch.uint8 or x.dim() < 2:
+        raise ValueError('resize_nearest_u8: expected a uint8 tensor [..., H, W], got %s %s' % (x.dtype, tuple(x.shape)))
+    x = x.contiguous()
+    h, w = x.shape[-2:]
+    y = torch.empty(tuple(x.shape[:-2]) + (int(oh), int(ow)), dtype=torch.uint8, device=x.device)
+    planes = x.numel() // (h * w)
+    _lib.check(_lib.load().b200seg_resize_nearest_u8(x.data_ptr(), planes, h, w, y.data_ptr(), int(oh), int(ow), _stream()),
+               'resize_nearest_u8')
+    _lib.count_launch()
+    return y
+
+
 def space_to_depth_u8(x, r, s, pad, mean=None, std=None):
     """uint8 image batch -> the stem's WindowAct in one pass: normalise + bf16 + NHWC + 2x2 space-to-depth (csrc/input.cu)."""
     x, layout = _u8_image(x, 'space_to_depth_u8')

@@ -1,4 +1,6 @@
 """Loss and metric functions of the hot path — drop-ins for utils/utils.py:17-24 and :51-65."""
+import random
+
 import torch
 
 from .. import engine as E
@@ -78,7 +80,7 @@ def compute_loss(outputs, targets, model=None):
     return _CrossEntropyFn.apply(outputs, targets)
 
 
-def post_fetch_fn(batch, mean=None, std=None):
+def post_fetch_fn(batch, mean=None, std=None, multi_scale=False, resize_masks=False):
     """Drop-in for ``BasicDataset.post_fetch_fn`` (utils/datasets.py:199-213) on device-resident batches:
     ``(uint8 N x 3 x H x W images, uint8 N x H x W masks)`` -> ``(images, masks)`` ready for ``model(images)`` /
     ``compute_loss(outputs, masks, model)``.
@@ -87,9 +89,27 @@ def post_fetch_fn(batch, mean=None, std=None):
     labels.  Here both stay 1-byte: the images are returned as they are, tagged with the normalisation constants, and
     the first kernel that touches them — the stem's space-to-depth pass for DeepLabV3+ / HRNet
     (``engine.space_to_depth_u8``), ``engine.normalize_u8`` for any other backbone — applies the same fp32 arithmetic;
-    loss and metric kernels read uint8 masks directly.  ``multi_scale`` resizing (utils/datasets.py:206-212, nearest
-    ``F.interpolate`` of the float images) is not part of this path.  float images pass through unchanged."""
+    loss and metric kernels read uint8 masks directly.  float images pass through unchanged.
+
+    ``multi_scale`` (utils/datasets.py:206-212): one ``random.uniform(0.7, 1.5)`` draw per batch (the same call on the
+    same ``random`` state as the reference), sizes rounded down to multiples of 32, nearest ``F.interpolate`` — done on
+    the 1-byte images, which commutes with the normalisation bit for bit.  Like the reference it resizes the images only
+    (its masks keep their size, which its own loss then rejects); ``resize_masks=True`` resizes the masks the same way."""
     imgs, segs = batch
+    if multi_scale:
+        h, w = imgs.shape[2], imgs.shape[3]
+        scale = random.uniform(0.7, 1.5)
+        h, w = int(h * scale / 32) * 32, int(w * scale / 32) * 32
+        if imgs.dtype == torch.uint8 and imgs.is_cuda:
+            imgs = E.resize_nearest_u8(imgs, h, w)
+            if resize_masks and segs.dtype == torch.uint8:
+                segs = E.resize_nearest_u8(segs, h, w)
+            elif resize_masks:
+                segs = torch.nn.functional.interpolate(segs[:, None].float(), (h, w))[:, 0].to(segs.dtype)
+        else:
+            imgs = torch.nn.functional.interpolate(imgs.float(), (h, w))
+            if resize_masks:
+                segs = torch.nn.functional.interpolate(segs[:, None].float(), (h, w))[:, 0].to(segs.dtype)
     if imgs.dtype == torch.uint8:
         imgs._b200seg_norm = (tuple(E.INPUT_MEAN if mean is None else mean), tuple(E.INPUT_STD if std is None else std))
     return imgs, segs

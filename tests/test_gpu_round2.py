@@ -49,6 +49,44 @@ def test_normalize_u8_bit_exact(E, n, h, w):
     assert torch.equal(E.normalize_u8(xl).cpu(), want)
 
 
+@pytest.mark.parametrize('n,h,w,oh,ow', [(2, 64, 96, 96, 64), (3, 37, 53, 64, 33), (2, 224, 224, 160, 320),
+                                          (16, 512, 512, 736, 384)])
+def test_resize_nearest_u8_matches_interpolate(E, n, h, w, oh, ow):
+    """multi_scale of post_fetch_fn (utils/datasets.py:206-212): F.interpolate(imgs, (h, w)) — nearest — after the
+    normalisation == the uint8 nearest resize before it, bit for bit."""
+    g = torch.Generator().manual_seed(h * w + oh)
+    x = torch.randint(0, 256, (n, 3, h, w), generator=g, dtype=torch.uint8)
+    want = torch.nn.functional.interpolate(_post_fetch_reference(x), (oh, ow))
+    y = E.resize_nearest_u8(x.cuda(), oh, ow)
+    assert y.dtype == torch.uint8 and list(y.shape) == [n, 3, oh, ow]
+    assert torch.equal(E.normalize_u8(y).cpu(), want)
+    m = torch.randint(0, 21, (n, h, w), generator=g, dtype=torch.uint8)
+    want_m = torch.nn.functional.interpolate(m[:, None].float(), (oh, ow))[:, 0].to(torch.uint8)
+    assert torch.equal(E.resize_nearest_u8(m.cuda(), oh, ow).cpu(), want_m)
+
+
+def test_post_fetch_fn_multi_scale_follows_the_reference_draw(P):
+    """Same ``random`` state => the same scale draw and output size as the reference's post_fetch_fn, same pixels."""
+    import random
+    from pytorch_segmentation_b200.utils.utils import model_input, post_fetch_fn
+    g = torch.Generator().manual_seed(5)
+    x = torch.randint(0, 256, (2, 3, 224, 224), generator=g, dtype=torch.uint8)
+    t = torch.randint(0, 21, (2, 224, 224), generator=g, dtype=torch.uint8)
+    for seed in (0, 1, 2, 3):
+        random.seed(seed)
+        scale = random.uniform(0.7, 1.5)                              # utils/datasets.py:209-211
+        h = w = int(224 * scale / 32) * 32
+        want = torch.nn.functional.interpolate(_post_fetch_reference(x), (h, w))
+        random.seed(seed)
+        imgs, segs = post_fetch_fn((x.cuda(), t.cuda()), multi_scale=True)
+        assert imgs.dtype == torch.uint8 and list(imgs.shape) == [2, 3, h, w]
+        assert list(segs.shape) == [2, 224, 224]                      # the reference leaves the masks alone
+        assert torch.equal(model_input(imgs).cpu(), want)
+        random.seed(seed)
+        imgs, segs = post_fetch_fn((x.cuda(), t.cuda()), multi_scale=True, resize_masks=True)
+        assert list(segs.shape) == [2, h, w]
+
+
 @pytest.mark.parametrize('n,h,w,r,pad', [(2, 64, 96, 7, 3), (2, 62, 70, 3, 1), (16, 512, 512, 7, 3)])
 def test_space_to_depth_u8_equals_normalise_then_fp32_path(E, n, h, w, r, pad):
     """One pass over 1-byte pixels == post_fetch_fn followed by the fp32 space-to-depth pass, bit for bit (bf16)."""
