@@ -401,6 +401,15 @@ int b200seg_lowres_ce_fwd(const float* lr, int n, int h, int w, int c_total, int
 int b200seg_lowres_ce_bwd(const float* lr, int n, int h, int w, int c_total, int nc, const void* targets, int target_kind, int th, int tw,
                           int align_corners, int64_t ignore_index, const float* grad_out, const int64_t* valid_count,
                           float* dlr, b200seg_stream_t st);
+/* Training: both of the above in ONE pass over the target tiles (three interpolations of the logits per class instead
+ * of five).  The mean's 1/count is not known until every tile is done, so dlr receives the UNSCALED gradient
+ * upsample^T(softmax - onehot); b200seg_scale_by_ratio then multiplies it by *grad_out / *valid_count in place (both read
+ * on the device).  Accumulators as b200seg_lowres_ce_fwd (zeroed by the caller); dlr is zeroed here. */
+int b200seg_lowres_ce_fused(const float* lr, int n, int h, int w, int c_total, int nc, const void* targets, int target_kind,
+                            int th, int tw, int align_corners, int64_t ignore_index, double* loss_sum, int64_t* valid_count,
+                            int* status, float* dlr, b200seg_stream_t st);
+int b200seg_scale_by_ratio(float* y, int64_t count, const float* grad_out, const int64_t* valid_count, b200seg_stream_t st);
+
 /* out[i] = bf16(a[i] + b[i]) (b bf16, may be NULL), count % 4 == 0: the fp32 class-map gradient of
  * b200seg_lowres_ce_bwd as the bf16 NHWC slice b200seg_conv_dgrad / _wgrad consume. */
 int b200seg_cast_add_bf16(const float* a, const void* b, void* out, int64_t count, b200seg_stream_t st);

@@ -127,6 +127,8 @@ PROTOTYPES = {
     'b200seg_softmax_ce': (c_int, [_P, _P, _I, _I, _I, _L, _L, _F, _P, _P, _P, _P, _P]),
     'b200seg_lowres_ce_fwd': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _L, _P, _P, _P, _P]),
     'b200seg_lowres_ce_bwd': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _L, _P, _P, _P, _P]),
+    'b200seg_lowres_ce_fused': (c_int, [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _L, _P, _P, _P, _P, _P]),
+    'b200seg_scale_by_ratio': (c_int, [_P, _L, _P, _P, _P]),
     'b200seg_cast_add_bf16': (c_int, [_P, _P, _P, _L, _P]),
     'b200seg_ce_finalize': (c_int, [_P, _P, _P, _P, _P]),
     'b200seg_softmax_ce_bwd': (c_int, [_P, _P, _I, _I, _I, _L, _L, _P, _P, _P, _P]),

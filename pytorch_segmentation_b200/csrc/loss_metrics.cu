@@ -579,7 +579,10 @@ template <int NCELL> struct CmExchange;
 template <> struct CmExchange<3> { static constexpr int K = 4, KS = 20; };    // 16 slots + 4 pad: conflict-free LDS.128
 template <> struct CmExchange<4> { static constexpr int K = 3, KS = 9; };
 
-template <int NCELL, bool BWD>
+// MODE: 0 = loss accumulators only, 1 = gradient only (scaled by *g_dev / *count_dev), 2 = both in one pass over the
+// tile with the gradient left UNSCALED (the pixel count is only known when every tile is done; the caller scales) — a
+// training step then interpolates the logits three times per class instead of five.
+template <int NCELL, int MODE>
 __global__ void __launch_bounds__(256, 2) class_map_ce_kernel(const float* __restrict__ lr, int ct, int h, int w, int nc,
                                                               const void* __restrict__ tgt, int tk, int H, int W, float sh,
                                                               float sw, int ac, int64_t ignore_index, double* loss_sum,
@@ -588,6 +591,7 @@ __global__ void __launch_bounds__(256, 2) class_map_ce_kernel(const float* __res
                                                               const unsigned long long* __restrict__ count_dev, int FH,
                                                               int FW, int nbuf) {
     pdl_prologue();
+    constexpr bool BWD = MODE != 0, FWD = MODE != 1;
     constexpr int P = kCmP, K = CmExchange<NCELL>::K, KS = CmExchange<NCELL>::KS;
     extern __shared__ __align__(16) float lsm[];
     __shared__ int bxs[kCmPX], bys[kCmPY];
@@ -663,7 +667,7 @@ __global__ void __launch_bounds__(256, 2) class_map_ce_kernel(const float* __res
             tcode[i] |= code << (8 * j);
         }
     }
-    if (!BWD && bad && status) *status = 1;
+    if (FWD && bad && status) *status = 1;
     __syncthreads();
 
     // interpolated logits of the patch for class c: rows of the window contracted with WX, then with WY
@@ -716,10 +720,10 @@ __global__ void __launch_bounds__(256, 2) class_map_ce_kernel(const float* __res
 #pragma unroll
             for (int j = 0; j < P; ++j) {
                 s[i][j] += __expf(v[i][j] - m[i][j]);
-                if (!BWD) vt[i][j] = (((tcode[i] >> (8 * j)) & 255u) == static_cast<unsigned int>(c)) ? v[i][j] : vt[i][j];
+                if (FWD) vt[i][j] = (((tcode[i] >> (8 * j)) & 255u) == static_cast<unsigned int>(c)) ? v[i][j] : vt[i][j];
             }
     }
-    if (!BWD) {
+    if (FWD) {
         double lsum = 0.0;
         unsigned int lcount = 0;
 #pragma unroll
@@ -750,7 +754,7 @@ __global__ void __launch_bounds__(256, 2) class_map_ce_kernel(const float* __res
             atomicAdd(loss_sum, a);
             atomicAdd(valid_count, b);
         }
-        return;
+        if (!BWD) return;
     }
 
     // ---- backward ----
@@ -766,7 +770,7 @@ __global__ void __launch_bounds__(256, 2) class_map_ce_kernel(const float* __res
         ylo[Y] = lo;
     }
     for (int i = threadIdx.x; i < nbuf * cells * KS; i += blockDim.x) T[i] = 0.f;   // slots nobody owns stay zero
-    const float gscale = __ldg(g_dev) / static_cast<float>(__ldg(count_dev));
+    const float gscale = MODE == 2 ? 1.f : __ldg(g_dev) / static_cast<float>(__ldg(count_dev));
 #pragma unroll
     for (int i = 0; i < P; ++i)
 #pragma unroll
@@ -867,9 +871,25 @@ __global__ void cast_add_bf16_kernel(const float4* __restrict__ a, const uint2* 
     }
 }
 
+// y *= *g / *count, in place: the scale the fused loss + gradient pass could not know (mean over the valid pixels times
+// the upstream gradient), both read on the device
+__global__ void scale_by_ratio_kernel(float4* __restrict__ y, int64_t n4, const float* __restrict__ g,
+                                      const unsigned long long* __restrict__ count) {
+    pdl_prologue();
+    const float sc = __ldg(g) / static_cast<float>(__ldg(count));
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n4;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+        float4 v = y[i];
+        v.x *= sc; v.y *= sc; v.z *= sc; v.w *= sc;
+        y[i] = v;
+    }
+}
+
 int launch_lowres_ce(const float* lr, int n, int h, int w, int ct, int nc, const void* targets, int tk, int H, int W,
                      int align_corners, int64_t ignore_index, double* loss_sum, int64_t* valid_count, int* status, float* dlr,
                      const float* g_dev, const int64_t* count_dev, cudaStream_t st) {
+    // dlr == nullptr: loss only; dlr with g_dev: gradient only; dlr without g_dev: both, gradient unscaled
+    const int mode = !dlr ? 0 : (g_dev ? 1 : 2);
     const float sh = bilinear_scale(h, H, align_corners), sw = bilinear_scale(w, W, align_corners);
     // cells a 4-pixel run can touch: floor(3 * scale) + 3
     const float smax = sh > sw ? sh : sw;
@@ -905,12 +925,15 @@ int launch_lowres_ce(const float* lr, int n, int h, int w, int ct, int nc, const
         B200SEG_CUDA(launch_pdl(class_map_ce_kernel<NCELL, B>, grid, 256, smem, st, lr, ct, h, w, nc, targets, tk, H, W, sh,\
                                 sw, align_corners, ignore_index, loss_sum, vc, status, dlr, g_dev, cd, FH, FW, nbuf));     \
     } while (0)
-    if (dlr) {
-        if (ncell == 3) B200SEG_LRCE(3, true);
-        else B200SEG_LRCE(4, true);
+    if (mode == 1) {
+        if (ncell == 3) B200SEG_LRCE(3, 1);
+        else B200SEG_LRCE(4, 1);
+    } else if (mode == 2) {
+        if (ncell == 3) B200SEG_LRCE(3, 2);
+        else B200SEG_LRCE(4, 2);
     } else {
-        if (ncell == 3) B200SEG_LRCE(3, false);
-        else B200SEG_LRCE(4, false);
+        if (ncell == 3) B200SEG_LRCE(3, 0);
+        else B200SEG_LRCE(4, 0);
     }
 #undef B200SEG_LRCE
     return 0;
@@ -996,6 +1019,34 @@ int b200seg_lowres_ce_bwd(const float* lr, int n, int h, int w, int c_total, int
     B200SEG_CUDA(cudaMemsetAsync(dlr, 0, sizeof(float) * static_cast<size_t>(n) * h * w * c_total, st));
     return launch_lowres_ce(lr, n, h, w, c_total, nc, targets, target_kind, th, tw, align_corners, ignore_index, nullptr, nullptr, nullptr,
                             dlr, grad_out, valid_count, st);
+}
+
+int b200seg_lowres_ce_fused(const float* lr, int n, int h, int w, int c_total, int nc, const void* targets, int target_kind,
+                            int th, int tw, int align_corners, int64_t ignore_index, double* loss_sum, int64_t* valid_count,
+                            int* status, float* dlr, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(lr && targets && loss_sum && valid_count && status && dlr, "lowres_ce_fused: null pointer");
+    B200SEG_CHECK(n > 0 && h > 0 && w > 0 && th >= h && tw >= w && nc > 0 && nc <= c_total && nc <= 32 && c_total % 4 == 0,
+                  "lowres_ce_fused: bad geometry (class map %dx%d, targets %dx%d, nc %d of %d)", h, w, th, tw, nc, c_total);
+    B200SEG_CHECK(((reinterpret_cast<uintptr_t>(lr) | reinterpret_cast<uintptr_t>(dlr)) & 15) == 0,
+                  "lowres_ce_fused: pointers not 16-byte aligned");
+    B200SEG_CHECK_TK("lowres_ce_fused");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    B200SEG_CUDA(cudaMemsetAsync(dlr, 0, sizeof(float) * static_cast<size_t>(n) * h * w * c_total, st));
+    return launch_lowres_ce(lr, n, h, w, c_total, nc, targets, target_kind, th, tw, align_corners, ignore_index, loss_sum, valid_count,
+                            status, dlr, nullptr, nullptr, st);
+}
+
+int b200seg_scale_by_ratio(float* y, int64_t count, const float* grad_out, const int64_t* valid_count, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(y && grad_out && valid_count && count > 0 && count % 4 == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0,
+                  "scale_by_ratio: null / misaligned pointer or count %lld not a multiple of 4", static_cast<long long>(count));
+    B200SEG_CUDA(launch_pdl(scale_by_ratio_kernel, elementwise_grid(count / 4), 256, 0, static_cast<cudaStream_t>(stream),
+                            reinterpret_cast<float4*>(y), count / 4, grad_out,
+                            reinterpret_cast<const unsigned long long*>(valid_count)));
+    return 0;
 }
 
 int b200seg_cast_add_bf16(const float* a, const void* b, void* out, int64_t count, b200seg_stream_t stream) {

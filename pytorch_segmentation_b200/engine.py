@@ -1181,6 +1181,8 @@ def softmax_ce(logits, targets, ignore_index=-100, want_grad=True):
 
 
 LOWRES_CE = _os.environ.get('B200SEG_LOWRES_CE', '1') != '0'   # loss through the class map (utils.compute_loss)
+# one fused loss + gradient launch when the class map needs a gradient (A/B: B200SEG_FUSED_CE=0 recomputes in backward)
+FUSED_CE = _os.environ.get('B200SEG_FUSED_CE', '1') != '0'
 
 
 def _lowres_geometry(lr, targets):
@@ -1227,6 +1229,29 @@ def lowres_ce_bwd(lr, nc, targets, grad_out, count, align_corners=True, ignore_i
     _lib.check(_lib.load().b200seg_lowres_ce_bwd(lr.data_ptr(), n, h, w, ct, nc, targets.data_ptr(), target_kind(targets), th, tw,
                                                  int(align_corners), ignore_index, grad_out.data_ptr(), count.data_ptr(),
                                                  dlr.data_ptr(), _stream()), 'lowres_ce_bwd')
+    _lib.count_launch()
+    return dlr
+
+
+def lowres_ce_fused(lr, nc, targets, align_corners=True, ignore_index=-100):
+    """Training: loss accumulators AND the unscaled class-map gradient upsample^T(softmax - onehot) in one launch
+    (``lowres_ce_scale`` applies grad_out / count once both are known)."""
+    n, h, w, ct, th, tw = _lowres_geometry(lr, targets)
+    acc = torch.zeros((3,), dtype=torch.float64, device=lr.device)
+    dlr = torch.empty_like(lr)
+    p = acc.data_ptr()
+    _lib.check(_lib.load().b200seg_lowres_ce_fused(lr.data_ptr(), n, h, w, ct, nc, targets.data_ptr(), target_kind(targets), th, tw,
+                                                   int(align_corners), ignore_index, p, p + 8, p + 16, dlr.data_ptr(),
+                                                   _stream()), 'lowres_ce_fused')
+    _lib.count_launch()
+    return acc, dlr
+
+
+def lowres_ce_scale(dlr, grad_out, count):
+    """dlr *= grad_out / count, in place; both scalars read on the device."""
+    assert grad_out.dtype == torch.float32 and count.dtype == torch.int64 and dlr.dtype == torch.float32
+    _lib.check(_lib.load().b200seg_scale_by_ratio(dlr.data_ptr(), dlr.numel(), grad_out.data_ptr(), count.data_ptr(), _stream()),
+               'scale_by_ratio')
     _lib.count_launch()
     return dlr
 

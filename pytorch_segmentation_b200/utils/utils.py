@@ -55,16 +55,28 @@ class _ClassMapCrossEntropyFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, lr, targets, nc, align_corners):
+        if ctx.needs_input_grad[0] and E.FUSED_CE:
+            # training: loss and (unscaled) class-map gradient from ONE pass over the target tiles; backward only scales
+            acc, dlr = E.lowres_ce_fused(lr.detach(), nc, targets, align_corners, IGNORE_INDEX)
+            ctx.save_for_backward(dlr, acc[1:2].view(torch.int64))
+            ctx.fused = True
+            return E.ce_finalize(acc)
         acc = E.lowres_ce_fwd(lr.detach(), nc, targets, align_corners, IGNORE_INDEX)
         if ctx.needs_input_grad[0]:
             ctx.save_for_backward(lr.detach(), targets, acc[1:2].view(torch.int64))
-            ctx.nc, ctx.ac = nc, align_corners
+            ctx.nc, ctx.ac, ctx.fused = nc, align_corners, False
         return E.ce_finalize(acc)
 
     @staticmethod
     def backward(ctx, g):
-        lr, targets, count_i = ctx.saved_tensors
         g = g.detach().to(torch.float32).contiguous()
+        if ctx.fused:
+            dlr, count_i = ctx.saved_tensors
+            if getattr(ctx, 'scaled', False):
+                raise RuntimeError('compute_loss: backward through the class-map loss a second time')
+            ctx.scaled = True                   # the saved gradient is scaled in place
+            return E.lowres_ce_scale(dlr, g, count_i), None, None, None
+        lr, targets, count_i = ctx.saved_tensors
         return E.lowres_ce_bwd(lr, ctx.nc, targets, g, count_i, ctx.ac, IGNORE_INDEX), None, None, None
 
 

@@ -422,3 +422,30 @@ def test_trainstep_defers_the_logits_and_loss_is_unchanged(P, E):
 def _lib_launches():
     from pytorch_segmentation_b200 import _lib
     return _lib.launches()
+
+
+@pytest.mark.parametrize('n,nc,h,w,up,dtype', [(2, 21, 32, 40, 4, torch.int64), (3, 2, 80, 80, 2, torch.uint8),
+                                               (16, 21, 128, 128, 4, torch.uint8)])
+def test_fused_class_map_loss_and_gradient(P, E, monkeypatch, n, nc, h, w, up, dtype):
+    """Training takes loss and class-map gradient from one launch (gradient unscaled, then * g / count in place): the
+    same loss bit for bit and the same gradient to fp32 round-off as the two-launch form, ignored pixels included."""
+    from pytorch_segmentation_b200.utils.utils import _ClassMapCrossEntropyFn
+    g = torch.Generator().manual_seed(n * h + nc)
+    ct = (nc + 7) // 8 * 8
+    lr = torch.randn(n, h, w, ct, generator=g).cuda()
+    t = torch.randint(0, nc, (n, h * up, w * up), generator=g)
+    if dtype == torch.int64:
+        t[0, :7, :] = -100
+    t = t.to(dtype).cuda()
+    assert E.lowres_ce_supported(lr.shape, nc, h * up, w * up, True)
+    out = {}
+    for fused in (False, True):
+        monkeypatch.setattr(E, 'FUSED_CE', fused)
+        x = lr.clone().requires_grad_(True)
+        loss = _ClassMapCrossEntropyFn.apply(x, t, nc, True)
+        (loss * 3.0).backward()
+        out[fused] = (loss.detach().clone(), x.grad.clone())
+    assert torch.equal(out[True][0], out[False][0])
+    ref = out[False][1]
+    assert float((out[True][1] - ref).abs().max()) <= 2e-6 * float(ref.abs().max())
+    assert float(out[True][1][..., nc:].abs().max() if ct > nc else 0.0) == 0.0
