@@ -8,5 +8,5 @@ $CMD > gpurun_out/bench_${R}_short.log 2> gpurun_out/bench_${R}_short.err && \
 timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 16000 --csv \
     --log-file gpurun_out/launches_${R}.csv $CMD > gpurun_out/ncu_list_${R}.log 2>&1
 echo "launch list rc=$?"; wc -l gpurun_out/launches_${R}.csv
-python scripts/summarise_ncu.py gpurun_out/launches_${R}.csv --steps 12 > gpurun_out/launches_${R}.md; head -40 gpurun_out/launches_${R}.md
+python scripts/summarise_ncu.py gpurun_out/launches_${R}.csv --steps 13 > gpurun_out/launches_${R}.md; head -40 gpurun_out/launches_${R}.md
 gzip -f gpurun_out/launches_${R}.csv
