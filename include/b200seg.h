@@ -212,6 +212,17 @@ typedef struct b200seg_wgrad_desc {
 size_t b200seg_conv_wgrad_workspace(const b200seg_wgrad_desc* d);
 /* dW[k][c][r][s] = sum_pixels dy[p][k] * x[p + tap][c]  (conv backward-weights of the same convs). */
 int b200seg_conv_wgrad(const b200seg_wgrad_desc* d, b200seg_stream_t st);
+/* The same weight gradient for callers that cannot allocate device memory (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * d->workspace / d->workspace_bytes are ignored: the split-K scratch is a static device array inside the
+ * library of B200SEG_NOALLOC_WGRAD_MAX_BYTES bytes (held by every GPU that loads the library until the process exits),
+ * and the call makes no cudaMalloc / cudaFree or any other allocating call.  A descriptor whose
+ * b200seg_conv_wgrad_workspace() exceeds that limit is rejected (returns 1, b200seg_last_error() names both sizes).
+ * Results are those of b200seg_conv_wgrad.  Every call on a device shares the one array, which keeps the last call's
+ * contents (nothing in it has to start at zero): calls that overlap on the GPU — two streams, parallel graph branches —
+ * race on it; serialise them. */
+#define B200SEG_NOALLOC_WGRAD_MAX_BYTES (16u << 20)
+int b200seg_conv_wgrad_noalloc(const b200seg_wgrad_desc* d, b200seg_stream_t st);
 
 /* ---- BatchNorm (train mode) around the conv -------------------------------------------------------------- */
 /* Per-channel sum and sum of squares of a bf16 NHWC slice into stats[2*c] (fp32; zeroed by the call).

@@ -11,6 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, 'libb200seg.so')
 
 MAX_CONV_SRC = 4
+NOALLOC_WGRAD_MAX_BYTES = 16 << 20      # B200SEG_NOALLOC_WGRAD_MAX_BYTES
 
 
 class ConvSrc(Structure):
@@ -88,6 +89,7 @@ PROTOTYPES = {
     'b200seg_conv_last_plan': (c_int, [POINTER(c_int64), POINTER(c_int64)]),
     'b200seg_conv_wgrad_plan_info': (c_int, [POINTER(WgradDesc), POINTER(c_int64), POINTER(c_int64)]),
     'b200seg_conv_wgrad': (c_int, [POINTER(WgradDesc), _P]),
+    'b200seg_conv_wgrad_noalloc': (c_int, [POINTER(WgradDesc), _P]),
     'b200seg_bn_stats': (c_int, [_P, _I, _I, _I, _L, _P, _P]),
     'b200seg_bn_finalize': (c_int, [_P, _I, _L, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P]),
     'b200seg_bn_eval_affine': (c_int, [_I, _P, _P, _P, _P, _F, _P, _P, _P, _P, _P]),

@@ -607,6 +607,34 @@ int plan_wgrad(const b200seg_wgrad_desc* d, WgradPlan* pl) {
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free variant (b200seg_conv_wgrad_noalloc): the split-K workspace lives in this file-scope device array
+// instead of caller-allocated memory.  Every GPU that loads the library holds it until the process exits.  All calls
+// share it and it keeps the last call's contents — harmless here: wgrad_kernel writes every (plane, tap, tile) of the
+// workspace it declares before wgrad_reduce_kernel reads it, nothing has to start at zero — but two calls that overlap
+// on the GPU (different streams, or graph branches) race on it.
+static __device__ __align__(256) unsigned char g_wgrad_static_ws[B200SEG_NOALLOC_WGRAD_MAX_BYTES];
+
+// The array's name is a host-side stand-in in host code; the device address comes from cudaGetSymbolAddress, once per
+// device, with that device current.
+constexpr int kMaxDevices = 64;
+int static_ws_address(void** out) {
+    static std::mutex mu;
+    static void* addr[kMaxDevices] = {};
+    int dev = -1;
+    B200SEG_CUDA(cudaGetDevice(&dev));
+    B200SEG_CHECK(dev >= 0 && dev < kMaxDevices, "conv_wgrad_noalloc: device index %d out of range", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        void* p = nullptr;
+        B200SEG_CUDA(cudaGetSymbolAddress(&p, g_wgrad_static_ws));
+        B200SEG_CHECK(p && (reinterpret_cast<uintptr_t>(p) & 255) == 0, "conv_wgrad_noalloc: bad symbol address");
+        addr[dev] = p;
+    }
+    *out = addr[dev];
+    return 0;
+}
+
 }  // namespace
 }  // namespace b200seg
 
@@ -734,6 +762,25 @@ int b200seg_conv_wgrad(const b200seg_wgrad_desc* d, b200seg_stream_t stream) {
     B200SEG_CUDA(launch_pdl(wgrad_reduce_kernel, static_cast<unsigned>((total + rb - 1) / rb), rb, 0, st,
         p.ws, d->dw, d->k_out, d->c, taps, pl.splits_hi, pl.m_pad, pl.n_pad, pl.shift_m, d->accumulate));
     return 0;
+}
+
+int b200seg_conv_wgrad_noalloc(const b200seg_wgrad_desc* d, b200seg_stream_t stream) {
+    using namespace b200seg;
+    clear_error();
+    B200SEG_CHECK(d, "conv_wgrad_noalloc: null descriptor");
+    WgradPlan pl;
+    memset(&pl, 0, sizeof(pl));
+    if (plan_wgrad(d, &pl)) return 1;
+    B200SEG_CHECK(pl.ws_bytes <= static_cast<size_t>(B200SEG_NOALLOC_WGRAD_MAX_BYTES),
+                  "conv_wgrad_noalloc: this weight gradient needs %zu bytes of split-K scratch, the static scratch holds "
+                  "%zu (B200SEG_NOALLOC_WGRAD_MAX_BYTES); use b200seg_conv_wgrad with a caller-owned workspace",
+                  pl.ws_bytes, static_cast<size_t>(B200SEG_NOALLOC_WGRAD_MAX_BYTES));
+    void* ws = nullptr;
+    if (static_ws_address(&ws)) return 1;
+    b200seg_wgrad_desc dd = *d;                 // the caller's workspace fields are ignored
+    dd.workspace = ws;
+    dd.workspace_bytes = static_cast<size_t>(B200SEG_NOALLOC_WGRAD_MAX_BYTES);
+    return b200seg_conv_wgrad(&dd, stream);
 }
 
 }  // extern "C"
