@@ -8,7 +8,8 @@ import os
 from ctypes import POINTER, Structure, c_char_p, c_double, c_float, c_int, c_int32, c_int64, c_size_t, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libb200seg.so')
+# B200SEG_LIB_PATH: another build of the library (same-box A/B of a kernel change: scripts/gpu_ab_lib.sh)
+LIB_PATH = os.environ.get('B200SEG_LIB_PATH') or os.path.join(_HERE, 'libb200seg.so')
 
 MAX_CONV_SRC = 4
 NOALLOC_WGRAD_MAX_BYTES = 16 << 20      # B200SEG_NOALLOC_WGRAD_MAX_BYTES

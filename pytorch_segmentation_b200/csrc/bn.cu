@@ -23,6 +23,12 @@ int bn_env_k(const char* name, int dflt) {
     return v == 1 || v == 2 || v == 4 ? v : dflt;
 }
 
+int bn_env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    const int v = e ? atoi(e) : dflt;
+    return v > 0 ? v : dflt;
+}
+
 // Geometry of a column reduction over a [pixels][c] slice: G = c/8 channel groups; a block covers
 // `gpb` groups (<= 256) and 256/gpb pixel rows per iteration.
 struct ColGeom {
@@ -34,6 +40,17 @@ struct ColGeom {
 // max_gpb: widest channel span of one block.  A REDUCTION ends with one atomic per channel per block, so total atomics =
 // blocks x channels-per-block: spanning 32 groups (a warp reads 512 contiguous bytes of a pixel) instead of the whole
 // row cuts them 4-8x on the 1024 / 2048-channel tensors and lets the grid's second dimension cover the rest.
+// launch geometry of the two elementwise passes (bn_apply, bn_bwd_apply): blocks per SM the grid is sized for and the
+// widest channel span of a block (A/B: B200SEG_BNAPPLY_CTAS / B200SEG_BNAPPLY_GPB)
+int apply_ctas() {
+    static const int v = bn_env_int("B200SEG_BNAPPLY_CTAS", 4);
+    return v;
+}
+int apply_gpb() {
+    static const int v = bn_env_int("B200SEG_BNAPPLY_GPB", 32);
+    return v;
+}
+
 ColGeom col_geom(int c, int64_t pixels, int ctas_per_sm = 8, int max_gpb = kRedThreads) {
     ColGeom g;
     g.groups = c / 8;
@@ -220,25 +237,26 @@ __global__ void __launch_bounds__(kRedThreads, 4) bn_apply_kernel(
     const int cw = gpb * 8;
     const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
     const int group = blockIdx.y * gpb + g_local;
-    if (threadIdx.x < gpb && group < groups) {
-        // one thread per channel group fills the block's parameter rows
-        float* dsc = bn_sp + threadIdx.x * 8;
-        float* dsh = bn_sp + cw + threadIdx.x * 8;
-        if (tr.stats) {
-            // training mode without a separate finalize launch: scale / shift from the conv epilogue's sums
-            // (bn_finalize_kernel's arithmetic); block row 0 also publishes them for the backward and moves the running
-            // statistics
-            const int c = groups * 8;
-            const bool publish = blockIdx.x == 0;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int ch = group * 8 + j;
+    {
+        // the block's parameter rows, one CHANNEL per thread (coalesced loads, every warp takes part: with one thread
+        // per 8-channel group the 32-128 threads that did this ran ~50 dependent strided loads each while the rest of
+        // the block waited — on the 1024 / 2048-channel tensors that prologue cost more than the 4-pixel sweep behind it)
+        const int c = groups * 8;
+        const int ch0 = blockIdx.y * cw;
+        const bool publish = blockIdx.x == 0;
+        for (int lc = threadIdx.x; lc < cw; lc += blockDim.x) {
+            const int ch = ch0 + lc;
+            if (ch >= c) break;
+            if (tr.stats) {
+                // training mode without a separate finalize launch: scale / shift from the conv epilogue's sums
+                // (bn_finalize_kernel's arithmetic); block row 0 also publishes them for the backward and moves the
+                // running statistics
                 const float mean = __ldg(tr.stats + ch) * tr.inv_count;
                 const float var = fmaxf(fmaf(-mean, mean, __ldg(tr.stats + c + ch) * tr.inv_count), 0.f);
                 const float invstd = rsqrtf(var + tr.eps);
                 const float scj = __ldg(tr.gamma + ch) * invstd, shj = fmaf(-mean, scj, __ldg(tr.beta + ch));
-                dsc[j] = scj;
-                dsh[j] = shj;
+                bn_sp[lc] = scj;
+                bn_sp[cw + lc] = shj;
                 if (publish) {
                     tr.vec[ch] = scj;
                     tr.vec[c + ch] = shj;
@@ -248,19 +266,13 @@ __global__ void __launch_bounds__(kRedThreads, 4) bn_apply_kernel(
                     if (tr.running_var)
                         tr.running_var[ch] = fmaf(tr.momentum, var * tr.unbias - tr.running_var[ch], tr.running_var[ch]);
                 }
+            } else {
+                bn_sp[lc] = __ldg(scale + ch);
+                bn_sp[cw + lc] = __ldg(shift + ch);
             }
-        } else {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                dsc[j] = __ldg(scale + group * 8 + j);
-                dsh[j] = __ldg(shift + group * 8 + j);
-            }
-        }
-        if (kRes == 2) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                bn_sp[2 * cw + threadIdx.x * 8 + j] = __ldg(res_scale + group * 8 + j);
-                bn_sp[3 * cw + threadIdx.x * 8 + j] = __ldg(res_shift + group * 8 + j);
+            if (kRes == 2) {
+                bn_sp[2 * cw + lc] = __ldg(res_scale + ch);
+                bn_sp[3 * cw + lc] = __ldg(res_shift + ch);
             }
         }
     }
@@ -349,12 +361,11 @@ __global__ void __launch_bounds__(kRedThreads, 4) bn_bwd_reduce_kernel(
     const int groups = c >> 3;
     const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
     const int group = blockIdx.y * gpb + g_local;
-    if (threadIdx.x < gpb && group < groups) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            bn_sp[threadIdx.x * 8 + j] = __ldg(scale + group * 8 + j);
-            bn_sp[cw + threadIdx.x * 8 + j] = __ldg(shift + group * 8 + j);
-        }
+    for (int lc = threadIdx.x; lc < cw; lc += blockDim.x) {
+        const int ch = blockIdx.y * cw + lc;
+        if (ch >= c) break;
+        bn_sp[lc] = __ldg(scale + ch);
+        bn_sp[cw + lc] = __ldg(shift + ch);
     }
     __syncthreads();
     float acc[2][8];
@@ -437,21 +448,19 @@ __global__ void __launch_bounds__(kRedThreads, 4) bn_bwd_apply_kernel(
     const int cw = gpb * 8;
     const int g_local = threadIdx.x % gpb, row = threadIdx.x / gpb;
     const int group = blockIdx.y * gpb + g_local;
-    if (threadIdx.x < gpb && group < groups) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int ch = group * 8 + j;
-            const float scj = __ldg(scale + ch);
-            float cb = 0.f, cc = 0.f;
-            if (training) {
-                cb = -scj * __ldg(invstd + ch) * __ldg(red + c + ch) * inv_count;
-                cc = -scj * __ldg(red + ch) * inv_count - cb * __ldg(mean + ch);
-            }
-            bn_sp[threadIdx.x * 8 + j] = scj;
-            bn_sp[cw + threadIdx.x * 8 + j] = __ldg(shift + ch);
-            bn_sp[2 * cw + threadIdx.x * 8 + j] = cb;
-            bn_sp[3 * cw + threadIdx.x * 8 + j] = cc;
+    for (int lc = threadIdx.x; lc < cw; lc += blockDim.x) {       // one channel per thread, coalesced (see bn_apply_kernel)
+        const int ch = blockIdx.y * cw + lc;
+        if (ch >= c) break;
+        const float scj = __ldg(scale + ch);
+        float cb = 0.f, cc = 0.f;
+        if (training) {
+            cb = -scj * __ldg(invstd + ch) * __ldg(red + c + ch) * inv_count;
+            cc = -scj * __ldg(red + ch) * inv_count - cb * __ldg(mean + ch);
         }
+        bn_sp[lc] = scj;
+        bn_sp[cw + lc] = __ldg(shift + ch);
+        bn_sp[2 * cw + lc] = cb;
+        bn_sp[3 * cw + lc] = cc;
     }
     __syncthreads();
     if (row >= rows || group >= groups) return;
@@ -790,7 +799,7 @@ int b200seg_bn_apply_add(const void* x, int x_c_total, int x_c_offset, void* y, 
     if (res && check_slice("bn_apply(res)", res, res_c_total, res_c_offset, c)) return 1;
     B200SEG_CHECK(scale && shift && pixels > 0, "bn_apply: bad arguments");
     B200SEG_CHECK((res_scale == nullptr) == (res_shift == nullptr), "bn_apply: residual scale and shift go together");
-    const ColGeom g = col_geom(c, pixels, 16);
+    const ColGeom g = col_geom(c, pixels, apply_ctas(), apply_gpb());
     static const int kk = bn_env_k("B200SEG_BN_K_APPLY", 4);
 #define B200SEG_BN_APPLY_K(RA, BITS, K)     B200SEG_CUDA(launch_pdl(bn_apply_kernel<RA, BITS, K>, dim3(g.gx, g.gy), kRedThreads, sizeof(float) * 8 * g.gpb * ((RA) == 2 ? 4 : 2), static_cast<cudaStream_t>(stream),  \
         static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset, \
@@ -836,7 +845,7 @@ int b200seg_bn_apply_train(const void* x, int x_c_total, int x_c_offset, void* y
     tr.running_var = running_var;
     tr.vec = vec;
     tr.bits = mask_bits;
-    const ColGeom g = col_geom(c, pixels, 16);
+    const ColGeom g = col_geom(c, pixels, apply_ctas(), apply_gpb());
     static const int kk = bn_env_k("B200SEG_BN_K_APPLY", 4);
 #define B200SEG_BN_APPLY_K(RA, BITS, K)     B200SEG_CUDA(launch_pdl(bn_apply_kernel<RA, BITS, K>, dim3(g.gx, g.gy), kRedThreads, sizeof(float) * 8 * g.gpb * ((RA) == 2 ? 4 : 2), static_cast<cudaStream_t>(stream), \
         static_cast<const __nv_bfloat16*>(x), x_c_total, x_c_offset, static_cast<__nv_bfloat16*>(y), y_c_total, y_c_offset, \
@@ -1066,7 +1075,7 @@ int b200seg_bn_bwd_apply_masked(const void* dy, int dy_c_total, int dy_c_offset,
     if (check_slice("bn_bwd_apply(dx)", dx, dx_c_total, dx_c_offset, c)) return 1;
     if (mask && check_slice("bn_bwd_apply(mask)", mask, mask_c_total, mask_c_offset, c)) return 1;
     B200SEG_CHECK(scale && shift && save_mean && save_invstd && red && pixels > 0, "bn_bwd_apply: bad arguments");
-    const ColGeom g = col_geom(c, pixels, 16);
+    const ColGeom g = col_geom(c, pixels, apply_ctas(), apply_gpb());
     static const int kk = bn_env_k("B200SEG_BN_K_BWD", 1);
 #define B200SEG_BN_BWD_(K, M)                                                                                                  \
     B200SEG_CUDA(launch_pdl(bn_bwd_apply_kernel<K, M>, dim3(g.gx, g.gy), kRedThreads, sizeof(float) * 32 * g.gpb, st,                                  \
