@@ -85,6 +85,8 @@ struct __align__(64) IgemmParams {
     int no_skip;             // anchored window sources: the buffer carries its own padding, every tap is in bounds
     int* sched;              // dynamic tile scheduler: {next tile - gridDim.x, CTAs done}; nullptr = static striding
     int n_fast;              // A/B switch (B200SEG_IGEMM_NFAST=1, static striding only): n_tile as the fastest tile index
+    int kpack;               // (tap, 64-channel block) operand pairs per pipeline stage: 2 when two fit a stage buffer
+                             // (bn <= 64), else 1 — see the producer loop
 };
 
 long long* g_dbg = nullptr;
@@ -204,6 +206,13 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
                 // the next id is requested before this tile's loads are issued: the atomic's latency hides under them
                 const int next = p.sched ? atomicAdd(p.sched, 1) + static_cast<int>(gridDim.x) : tile + static_cast<int>(gridDim.x);
                 const TileCoord t = decode_tile(p, tile);
+                // With a narrow N tile the tensor work of one (tap, 64-channel block) pair is 128 clk while the two
+                // single-thread control loops (this one and the MMA issuer) need 300-750 clk of issue latency per
+                // pipeline stage (try_wait ~90 clk even when complete, arrive, TMA / MMA issues, tap bookkeeping:
+                // profiles/r02_igemm_ablation.md): a stage therefore carries p.kpack pairs when they fit its buffer —
+                // one wait, one expect_tx and one commit for both.  expect_tx is posted after the loads it covers
+                // (the phase cannot complete before this thread's arrive, the tx count may run negative meanwhile).
+                int sub = 0;
                 for (int sg = 0; sg < p.nseg; ++sg) {
                     const IgemmSeg& seg = p.seg[sg];
                     for (int tp = 0; tp < seg.ntaps; ++tp) {
@@ -211,16 +220,26 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
                         if (!tap_in_bounds(p, t, dy, dx)) continue;
                         const int tap = seg.wtap[tp];
                         for (int cb = 0; cb < seg.cblks; ++cb) {
-                            mbar_wait(&empty[stage], phase ^ 1);
-                            uint8_t* sa = smem + stage * kStageBytes;
-                            mbar_arrive_expect_tx(&full[stage], tx_bytes);
+                            if (sub == 0) mbar_wait(&empty[stage], phase ^ 1);
+                            uint8_t* sa = smem + stage * kStageBytes + sub * tx_bytes;
                             tma_load_4d(sa, &p.a_map[sg], &full[stage], cb * kBK, t.x0 + dx, t.y0 + dy, t.n0);
                             tma_load_3d(sa + kABytes, &p.b_map[sg], &full[stage], cb * kBK, t.n_tile * p.bn, tap);
-                            if (++stage == kStages) {
-                                stage = 0;
-                                phase ^= 1;
+                            if (++sub == p.kpack) {
+                                mbar_arrive_expect_tx(&full[stage], sub * tx_bytes);
+                                sub = 0;
+                                if (++stage == kStages) {
+                                    stage = 0;
+                                    phase ^= 1;
+                                }
                             }
                         }
+                    }
+                }
+                if (sub) {                                   // odd tail of the tile: a stage with one pair
+                    mbar_arrive_expect_tx(&full[stage], sub * tx_bytes);
+                    if (++stage == kStages) {
+                        stage = 0;
+                        phase ^= 1;
                     }
                 }
                 tile = next;
@@ -265,16 +284,20 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
                 mbar_wait(&tempty[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * kMaxBN;
-                for (int it = 0; it < kiters; ++it) {
+                const uint32_t pair_bytes = kABytes + p.bn * kBK * 2;
+                for (int it = 0; it < kiters; it += p.kpack) {
                     mbar_wait(&full[stage], phase);
                     tc_fence_after();
-                    const uint32_t sa = smem_u32(smem + stage * kStageBytes);
-                    const uint64_t a_desc = umma_smem_desc(sa, 16, 1024);
-                    const uint64_t b_desc = umma_smem_desc(sa + kABytes, 16, 1024);
+                    const int pairs = min(p.kpack, kiters - it);      // operand pairs this stage holds
+                    for (int j = 0; j < pairs; ++j) {
+                        const uint32_t sa = smem_u32(smem + stage * kStageBytes) + j * pair_bytes;
+                        const uint64_t a_desc = umma_smem_desc(sa, 16, 1024);
+                        const uint64_t b_desc = umma_smem_desc(sa + kABytes, 16, 1024);
 #pragma unroll
-                    for (int k = 0; k < kBK / 16; ++k) {
-                        // +32 bytes (16 bf16) along K inside the 128-byte swizzle row: +2 in the address field
-                        tc_mma_f16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (it | k) != 0);
+                        for (int k = 0; k < kBK / 16; ++k) {
+                            // +32 bytes (16 bf16) along K inside the 128-byte swizzle row: +2 in the address field
+                            tc_mma_f16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (it | j | k) != 0);
+                        }
                     }
                     tc_commit(&empty[stage]);
                     if (++stage == kStages) {
@@ -735,6 +758,11 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
         return e && e[0] == '1';
     }();
     p.n_fast = n_fast && !p.sched ? 1 : 0;
+    static const bool kpack_on = [] {
+        const char* e = getenv("B200SEG_IGEMM_KPACK");
+        return !(e && e[0] == '0');
+    }();
+    p.kpack = (kpack_on && 2 * (kABytes + p.bn * kBK * 2) <= kStageBytes) ? 2 : 1;
     B200SEG_CUDA(launch_pdl(igemm_kernel, grid, kThreads, kSmemBytes, st, p));
     return 0;
 }
