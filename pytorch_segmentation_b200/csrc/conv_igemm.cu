@@ -53,6 +53,24 @@ constexpr int kTmemCols = 512;
 constexpr int kMaxSeg = 8;
 constexpr int kMaxTaps = 9;
 
+// Division of a tile index (< 2^31) by a launch constant as multiply-high + shift (Granlund-Montgomery): the three
+// single-thread / per-warp control loops each decode every tile, and four run-time divisions (~100 clk apiece when
+// dependent) were a quarter of the per-tile bookkeeping on the many-small-tile launches.
+struct FastDiv {
+    unsigned mul, shift;
+};
+inline FastDiv make_fastdiv(int d) {
+    FastDiv f;
+    unsigned l = 0;
+    while ((1u << l) < static_cast<unsigned>(d)) ++l;
+    f.shift = l;
+    f.mul = static_cast<unsigned>(((static_cast<unsigned long long>(1) << 32) * ((1ull << l) - d)) / d + 1);
+    return f;
+}
+__device__ __forceinline__ int fast_div(int n, const FastDiv& f) {
+    return static_cast<int>((__umulhi(f.mul, static_cast<unsigned>(n)) + static_cast<unsigned>(n)) >> f.shift);
+}
+
 // One reduction segment: an activation view (tensor map), a packed weight, and the filter taps that read this view
 // — each tap is a pixel shift (dy, dx) in the view's grid plus the index of its weight slab.  A stride-1 conv is one
 // segment with all R*S taps (shift = (r - R/2) * dilation); a stride-2 conv is one segment per input parity
@@ -85,6 +103,7 @@ struct __align__(64) IgemmParams {
     int no_skip;             // anchored window sources: the buffer carries its own padding, every tap is in bounds
     int* sched;              // dynamic tile scheduler: {next tile - gridDim.x, CTAs done}; nullptr = static striding
     int n_fast;              // A/B switch (B200SEG_IGEMM_NFAST=1, static striding only): n_tile as the fastest tile index
+    FastDiv d_mt, d_tx, d_ty, d_tn;   // divisions by m_tiles, tiles_x, tiles_y, tiles_n in decode_tile
     int kpack;               // (tap, 64-channel block) operand pairs per pipeline stage: 2 when two fit a stage buffer
                              // (bn <= 64), else 1 — see the producer loop
 };
@@ -114,16 +133,17 @@ __device__ __forceinline__ TileCoord decode_tile(const IgemmParams& p, int tile)
     const int m_tiles = p.tiles_x * p.tiles_y * p.tiles_i;
     int m;
     if (p.n_fast) {
-        t.n_tile = tile % p.tiles_n;
-        m = tile / p.tiles_n;
+        m = fast_div(tile, p.d_tn);
+        t.n_tile = tile - m * p.tiles_n;
     } else {
-        t.n_tile = tile / m_tiles;
+        t.n_tile = fast_div(tile, p.d_mt);
         m = tile - t.n_tile * m_tiles;
     }
-    t.x0 = (m % p.tiles_x) * p.bw;
-    m /= p.tiles_x;
-    t.y0 = (m % p.tiles_y) * p.bh;
-    t.n0 = (m / p.tiles_y) * p.bi;
+    const int my = fast_div(m, p.d_tx);
+    t.x0 = (m - my * p.tiles_x) * p.bw;
+    const int mn = fast_div(my, p.d_ty);
+    t.y0 = (my - mn * p.tiles_y) * p.bh;
+    t.n0 = mn * p.bi;
     return t;
 }
 
@@ -719,6 +739,10 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
     p.tiles_y = ceil_div(h, p.bh);
     p.tiles_i = ceil_div(n, p.bi);
     p.num_tiles = p.tiles_x * p.tiles_y * p.tiles_i * p.tiles_n;
+    p.d_mt = make_fastdiv(p.tiles_x * p.tiles_y * p.tiles_i);
+    p.d_tx = make_fastdiv(p.tiles_x);
+    p.d_ty = make_fastdiv(p.tiles_y);
+    p.d_tn = make_fastdiv(p.tiles_n);
 
     for (int i = 0; i < nseg; ++i) {
         const uint32_t abox[4] = {kBK, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bi};
