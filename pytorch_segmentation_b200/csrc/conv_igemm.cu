@@ -78,6 +78,7 @@ __device__ __forceinline__ int fast_div(int n, const FastDiv& f) {
 struct IgemmSeg {
     int ntaps, cblks;
     short dy[kMaxTaps], dx[kMaxTaps], wtap[kMaxTaps];
+    int packed[kMaxTaps];        // dy (low 12 bits, signed) | dx << 12 (12 bits, signed) | wtap << 24: one load per tap in the producer loop
 };
 
 struct __align__(64) IgemmParams {
@@ -103,6 +104,7 @@ struct __align__(64) IgemmParams {
     int no_skip;             // anchored window sources: the buffer carries its own padding, every tap is in bounds
     int* sched;              // dynamic tile scheduler: {next tile - gridDim.x, CTAs done}; nullptr = static striding
     int n_fast;              // A/B switch (B200SEG_IGEMM_NFAST=1, static striding only): n_tile as the fastest tile index
+    int dy_min, dy_max, dx_min, dx_max, iters_all;   // extremes of the tap shifts; pipeline iterations of a tile none of whose taps is all padding
     FastDiv d_mt, d_tx, d_ty, d_tn;   // divisions by m_tiles, tiles_x, tiles_y, tiles_n in decode_tile
     int kpack;               // (tap, 64-channel block) operand pairs per pipeline stage: 2 when two fit a stage buffer
                              // (bn <= 64), else 1 — see the producer loop
@@ -150,6 +152,14 @@ __device__ __forceinline__ TileCoord decode_tile(const IgemmParams& p, int tile)
 __device__ __forceinline__ bool tap_in_bounds(const IgemmParams& p, const TileCoord& t, int dy, int dx) {
     if (p.no_skip) return true;
     return (t.y0 + dy < p.H) && (t.y0 + p.bh - 1 + dy >= 0) && (t.x0 + dx < p.W) && (t.x0 + p.bw - 1 + dx >= 0);
+}
+
+// every tap of the tile reads at least one pixel inside the image (the common case away from large dilations): the
+// control loops then skip the per-tap test
+__device__ __forceinline__ bool all_taps_in_bounds(const IgemmParams& p, const TileCoord& t) {
+    if (p.no_skip) return true;
+    return (t.y0 + p.dy_max < p.H) && (t.y0 + p.bh - 1 + p.dy_min >= 0) && (t.x0 + p.dx_max < p.W) &&
+           (t.x0 + p.bw - 1 + p.dx_min >= 0);
 }
 
 __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constant__ IgemmParams p) {
@@ -233,12 +243,14 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
                 // one wait, one expect_tx and one commit for both.  expect_tx is posted after the loads it covers
                 // (the phase cannot complete before this thread's arrive, the tx count may run negative meanwhile).
                 int sub = 0;
+                const bool all_in = all_taps_in_bounds(p, t);
                 for (int sg = 0; sg < p.nseg; ++sg) {
                     const IgemmSeg& seg = p.seg[sg];
                     for (int tp = 0; tp < seg.ntaps; ++tp) {
-                        const int dy = seg.dy[tp], dx = seg.dx[tp];
-                        if (!tap_in_bounds(p, t, dy, dx)) continue;
-                        const int tap = seg.wtap[tp];
+                        const int pk = seg.packed[tp];
+                        const int dy = (pk << 20) >> 20, dx = (pk << 8) >> 20;
+                        if (!all_in && !tap_in_bounds(p, t, dy, dx)) continue;
+                        const int tap = pk >> 24;
                         for (int cb = 0; cb < seg.cblks; ++cb) {
                             if (sub == 0) mbar_wait(&empty[stage], phase ^ 1);
                             uint8_t* sa = smem + stage * kStageBytes + sub * tx_bytes;
@@ -293,11 +305,14 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
                 }
                 if (tile < 0) break;
                 const TileCoord t = decode_tile(p, tile);
-                int kiters = 0;
-                for (int sg = 0; sg < p.nseg; ++sg) {
-                    const IgemmSeg& seg = p.seg[sg];
-                    for (int tp = 0; tp < seg.ntaps; ++tp)
-                        if (tap_in_bounds(p, t, seg.dy[tp], seg.dx[tp])) kiters += seg.cblks;
+                int kiters = p.iters_all;
+                if (!all_taps_in_bounds(p, t)) {
+                    kiters = 0;
+                    for (int sg = 0; sg < p.nseg; ++sg) {
+                        const IgemmSeg& seg = p.seg[sg];
+                        for (int tp = 0; tp < seg.ntaps; ++tp)
+                            if (tap_in_bounds(p, t, seg.dy[tp], seg.dx[tp])) kiters += seg.cblks;
+                    }
                 }
                 const int acc = lt & 1;
                 const uint32_t acc_phase = (lt >> 1) & 1;
@@ -739,6 +754,23 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
     p.tiles_y = ceil_div(h, p.bh);
     p.tiles_i = ceil_div(n, p.bi);
     p.num_tiles = p.tiles_x * p.tiles_y * p.tiles_i * p.tiles_n;
+    p.dy_min = p.dx_min = 1 << 20;
+    p.dy_max = p.dx_max = -(1 << 20);
+    p.iters_all = 0;
+    for (int i = 0; i < nseg; ++i) {
+        IgemmSeg& sgm = p.seg[i];
+        p.iters_all += sgm.ntaps * sgm.cblks;
+        for (int tp = 0; tp < sgm.ntaps; ++tp) {
+            const int dy = sgm.dy[tp], dx = sgm.dx[tp];
+            B200SEG_CHECK(dy > -2048 && dy < 2048 && dx > -2048 && dx < 2048 && sgm.wtap[tp] >= 0 && sgm.wtap[tp] < 128,
+                          "conv: tap shift (%d, %d) out of the packed range", dy, dx);
+            sgm.packed[tp] = (dy & 0xfff) | ((dx & 0xfff) << 12) | (static_cast<int>(sgm.wtap[tp]) << 24);
+            p.dy_min = dy < p.dy_min ? dy : p.dy_min;
+            p.dy_max = dy > p.dy_max ? dy : p.dy_max;
+            p.dx_min = dx < p.dx_min ? dx : p.dx_min;
+            p.dx_max = dx > p.dx_max ? dx : p.dx_max;
+        }
+    }
     p.d_mt = make_fastdiv(p.tiles_x * p.tiles_y * p.tiles_i);
     p.d_tx = make_fastdiv(p.tiles_x);
     p.d_ty = make_fastdiv(p.tiles_y);
