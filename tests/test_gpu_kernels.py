@@ -90,6 +90,23 @@ STRIDE2_CASES = [
 ]
 
 
+@pytest.mark.parametrize('n,h,w,c,k,ks,dil', [(8, 128, 128, 256, 256, 3, 1), (16, 32, 32, 2048, 256, 3, 12), (4, 64, 64, 128, 128, 3, 1),
+                                              (16, 128, 128, 64, 64, 3, 1), (16, 32, 32, 1024, 256, 1, 1)])
+def test_conv_wgrad_is_bit_identical_run_to_run(E, n, h, w, c, k, ks, dil):
+    """Split-K partials meet in a fixed order — inside a cluster over DSMEM, then in wgrad_reduce_kernel — never through
+    floating-point atomics: the same operands give the same bits, also when the gradient accumulates."""
+    g = torch.Generator().manual_seed(c + k + dil)
+    xa = E.Act(torch.randn(n, h, w, c, generator=g).to(torch.bfloat16).cuda())
+    dya = E.Act(torch.randn(n, h, w, k, generator=g).to(torch.bfloat16).cuda())
+    first = E.conv_wgrad(dya, xa, k, ks, ks, dil).clone()
+    for _ in range(3):
+        assert torch.equal(E.conv_wgrad(dya, xa, k, ks, ks, dil), first)
+    base = torch.randn(k, c, ks, ks, generator=g).cuda()
+    acc = [E.conv_wgrad(dya, xa, k, ks, ks, dil, dw=base.clone()).clone() for _ in range(2)]
+    assert torch.equal(acc[0], acc[1])
+    assert float((acc[0] - (base + first)).abs().max()) <= 1e-5 * float(first.abs().max()) + 1e-6
+
+
 @pytest.mark.parametrize('n,h,w,c,k,ks', STRIDE2_CASES)
 def test_conv_stride2_fprop_dgrad_wgrad(E, n, h, w, c, k, ks):
     """Stride-2 convs of the ResNet backbone (3x3 conv2 and 1x1 downsample of layer2.0 / layer3.0): the input is
