@@ -70,6 +70,53 @@ def test_graph_step_matches_eager_step(P):
     assert float((yc - yd).abs().max()) <= 1e-2 * max(float(yd.abs().max()), 1e-6)
 
 
+def test_graph_step_equals_eager_step_tightly_in_eval_mode(P):
+    """The near-deterministic version of the test above: with BatchNorm in eval mode there are no batch statistics, so
+    the only run-to-run noise left is the order of a few fp32 atomic sums (BN parameter gradients, the class-map
+    gradient's tile halos) nudging bf16 roundings.  Two eager copies measure that floor; the graph copy (three eager
+    warm-ups, capture, replays) must sit within 3x of it or 0.2 % of the update, whichever is larger — a replay that used
+    a stale weight pack, skipped the momentum buffer or froze the learning rate would be off by a whole update — and
+    the eval outputs afterwards likewise."""
+    nc, n, h, w = 5, 2, 96, 96
+    m_a = _make(P, nc, 11).eval()
+    # eval-mode BatchNorm with fresh running statistics is the identity, and sixteen un-normalised residual blocks would
+    # double the activation variance each: damp every block's last BN so the random-init network stays O(1)
+    with torch.no_grad():
+        for name, mod in m_a.named_modules():
+            if name.endswith('bn3'):
+                mod.weight.fill_(0.2)
+    m_b, m_c = copy.deepcopy(m_a), copy.deepcopy(m_a)
+    init = torch.cat([p.detach().flatten() for p in m_a.parameters()]).clone()
+    g = torch.Generator().manual_seed(4)
+    batches = [(torch.randn(n, 3, h, w, generator=g).cuda(), torch.randint(0, nc, (n, h, w), generator=g).cuda())
+               for _ in range(5)]
+    steps = [P.TrainStep(m, P.optim.SGD(m.parameters(), lr=1e-4, momentum=0.9, weight_decay=1e-4), graph=graph, warmup=3)
+             for m, graph in ((m_a, False), (m_b, False), (m_c, True))]
+    losses = [[], [], []]
+    for x, t in batches:
+        for i, st in enumerate(steps):
+            losses[i].append(float(st(x, t)))
+    assert all(v == v and abs(v) < 1e4 for v in losses[0]), losses
+    assert steps[2].launches_per_step is not None
+
+    def update(m):
+        return torch.cat([p.detach().flatten() for p in m.parameters()]) - init
+
+    ua, ub, uc = update(m_a), update(m_b), update(m_c)
+    floor = float((ua - ub).norm())
+    print('eval-mode graph vs eager: |ua| %.4g, eager floor %.3g, graph %.3g; losses %s' % (
+        float(ua.norm()), floor, float((ua - uc).norm()), losses))
+    assert float(ua.norm()) > 0
+    assert float((ua - uc).norm()) <= max(3.0 * floor, 2e-3 * float(ua.norm())), (float((ua - uc).norm()), floor, float(ua.norm()))
+    lfloor = max(abs(a - b) for a, b in zip(losses[0], losses[1]))
+    for a, c in zip(losses[0], losses[2]):
+        assert abs(a - c) <= max(3.0 * lfloor, 1e-3 * max(1.0, abs(a))), losses
+    with torch.no_grad():
+        ya, yb, yc = m_a(batches[0][0]), m_b(batches[0][0]), m_c(batches[0][0])
+    yfloor = float((ya - yb).abs().max())
+    assert float((ya - yc).abs().max()) <= max(3.0 * yfloor, 2e-3 * float(ya.abs().max()))
+
+
 def test_graph_step_rejects_other_shapes(P):
     m = _make(P, 3, 1)
     s = P.TrainStep(m, torch.optim.SGD(m.parameters(), lr=1e-3), graph=True, warmup=1)
