@@ -46,6 +46,9 @@ CONV_CASES = [
     (4, 1, 1, 256, 256, 1, 1),
     (1, 40, 40, 128, 352, 3, 2),
     (2, 17, 23, 88, 8, 3, 1),
+    # dilated, one CTA per (tap, tile) already fills the GPU (the ASPP weight-gradient regime)
+    (2, 32, 32, 2048, 256, 3, 12),
+    (1, 32, 32, 1152, 128, 3, 18),
 ]
 
 
