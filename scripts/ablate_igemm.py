@@ -2,6 +2,8 @@
 """Timing ablations of igemm_kernel on the small-channel backbone shapes (results are garbage, only the time matters):
 B200SEG_IGEMM_ABLATE bitmask — 1 no A loads, 2 no B loads, 4 no MMAs, 8 epilogue does no work, 16 no BN statistics.
 One process per mask (the switch is read once); prints us per launch of fprop with fused statistics.
+The switches are NOT in the shipped kernel: apply profiles/dropped/r02_igemm_ablation_switches.patch and rebuild first
+(results: profiles/r02_igemm_ablation.md).
 
   python scripts/ablate_igemm.py            # driver: runs itself once per mask
 """
