@@ -61,6 +61,12 @@ struct __align__(64) WgradParams {
     int direct;            // 1: this launch's sums are final — write dw (fp32 OIHW) from the epilogue, no workspace
     float* dw;
     int k_out, c_in, accumulate;
+    // 5-D views (64 ch, W, H, N, channel block) of the same tensors, built when the channel count is a multiple of 64: ONE
+    // TMA instruction then brings all the 64-channel boxes of an operand (2 on the M side, bn/64 on the N side) — the
+    // producer is a single thread and each TMA issue costs it ~200 clk, which at six issues per stage was the whole stage
+    CUtensorMap x_map5[4];
+    CUtensorMap y_map5;
+    int x5, y5;
 };
 
 // final element (m, n) of filter tap `tap` -> dw[k][c][tap] (+)= v        (m, n) = (c, k) with X on the M side, else (k, c)
@@ -133,6 +139,10 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
     const CUtensorMap* xm = &p.x_map[p.tap_map[tap]];
     const CUtensorMap* m_map = p.shift_m ? xm : &p.y_map;
     const CUtensorMap* n_map = p.shift_m ? &p.y_map : xm;
+    const CUtensorMap* xm5 = &p.x_map5[p.tap_map[tap]];
+    const CUtensorMap* m_map5 = p.shift_m ? xm5 : &p.y_map5;
+    const CUtensorMap* n_map5 = p.shift_m ? &p.y_map5 : xm5;
+    const bool m5 = (p.shift_m ? p.x5 : p.y5) != 0, n5 = (p.shift_m ? p.y5 : p.x5) != 0;
     // a patch is skipped only when every tap of the group reads nothing but padding there (a tap that does is
     // zero-filled by the TMA unit)
     int gdy[4], gdx[4];                            // the group's shifts in registers: the walkers below are single
@@ -156,8 +166,8 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
     const int kp_end = min(kp_begin + p.patches_per_split, p.patches);
 
     if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(m_map);
-        tma_prefetch_desc(n_map);
+        tma_prefetch_desc(m5 ? m_map5 : m_map);
+        tma_prefetch_desc(n5 ? n_map5 : n_map);
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < kStages; ++i) {
@@ -196,12 +206,20 @@ __global__ void __launch_bounds__(kThreads, 1) wgrad_kernel(const __grid_constan
                 mbar_wait(&empty[stage], phase ^ 1);
                 uint8_t* sa = smem + stage * kStageBytes;
                 mbar_arrive_expect_tx(&full[stage], tx_bytes);
-                for (int b = 0; b < 2; ++b)
-                    tma_load_4d(sa + b * kBoxBytes, m_map, &full[stage], m_tile * kBM + b * 64, x0 + mdx, y0 + mdy, n0);
+                if (m5) {
+                    tma_load_5d(sa, m_map5, &full[stage], 0, x0 + mdx, y0 + mdy, n0, m_tile * (kBM / 64));
+                } else {
+                    for (int b = 0; b < 2; ++b)
+                        tma_load_4d(sa + b * kBoxBytes, m_map, &full[stage], m_tile * kBM + b * 64, x0 + mdx, y0 + mdy, n0);
+                }
                 if (!kGrouped) {
-                    for (int b = 0; b < n_boxes; ++b)
-                        tma_load_4d(sa + kABytes + b * kBoxBytes, n_map, &full[stage], n_tile * p.bn + b * 64, x0 + ndx,
-                                    y0 + ndy, n0);
+                    if (n5) {
+                        tma_load_5d(sa + kABytes, n_map5, &full[stage], 0, x0 + ndx, y0 + ndy, n0, n_tile * n_boxes);
+                    } else {
+                        for (int b = 0; b < n_boxes; ++b)
+                            tma_load_4d(sa + kABytes + b * kBoxBytes, n_map, &full[stage], n_tile * p.bn + b * 64, x0 + ndx,
+                                        y0 + ndy, n0);
+                    }
                 } else {
 #pragma unroll
                     for (int j = 0; j < 4; ++j)
@@ -722,6 +740,34 @@ int b200seg_conv_wgrad(const b200seg_wgrad_desc* d, b200seg_stream_t stream) {
                                 (size_t)d->x_c_offset * 2;
             if (encode_tmap_bf16(&p.x_map[vy * 2 + vx], xbase, 4, xdims, xstr, box)) return 1;
         }
+    // 5-D views: the channel axis split into (64, blocks); the block axis is the outermost box dimension, so one box is
+    // the same run of consecutive 8 KB boxes in shared memory that the per-box loads produce
+    static const bool tma5 = [] {
+        const char* e = getenv("B200SEG_WGRAD_TMA5");
+        return !(e && e[0] == '0');
+    }();
+    const int n_boxes_host = pl.bn / 64;
+    p.y5 = tma5 && d->k % 64 == 0 ? 1 : 0;
+    p.x5 = tma5 && d->c % 64 == 0 && !anchored ? 1 : 0;
+    if (p.y5) {
+        const uint32_t yb = pl.shift_m ? n_boxes_host : 2;       // dY is the N side when X is on the M side
+        const uint32_t box5[5] = {64, (uint32_t)pl.bw, (uint32_t)pl.bh, (uint32_t)pl.bi, yb};
+        const uint64_t dims5[5] = {64, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n, (uint64_t)d->k / 64};
+        const uint64_t str5[4] = {ystr[0], ystr[1], ystr[2], 128};
+        if (encode_tmap_bf16(&p.y_map5, ybase, 5, dims5, str5, box5)) return 1;
+    }
+    if (p.x5) {
+        const uint32_t xb = pl.shift_m ? 2 : n_boxes_host;
+        const uint32_t box5[5] = {64, (uint32_t)pl.bw, (uint32_t)pl.bh, (uint32_t)pl.bi, xb};
+        const uint64_t dims5[5] = {64, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n, (uint64_t)d->c / 64};
+        const uint64_t str5[4] = {xstr[0], xstr[1], xstr[2], 128};
+        for (int vy = 0; vy < cs; ++vy)
+            for (int vx = 0; vx < cs; ++vx) {
+                const char* xbase = static_cast<const char*>(d->x) + ((size_t)vy * wx + vx) * d->x_c_total * 2 +
+                                    (size_t)d->x_c_offset * 2;
+                if (encode_tmap_bf16(&p.x_map5[vy * 2 + vx], xbase, 5, dims5, str5, box5)) return 1;
+            }
+    }
     for (int r = 0; r < d->r; ++r)
         for (int s = 0; s < d->s; ++s) {
             const int oy = (r - d->r / 2) * d->dil, ox = (s - d->s / 2) * d->dil;
