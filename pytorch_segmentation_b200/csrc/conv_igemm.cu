@@ -105,6 +105,13 @@ struct __align__(64) IgemmParams {
     int* sched;              // dynamic tile scheduler: {next tile - gridDim.x, CTAs done}; nullptr = static striding
     int n_fast;              // A/B switch (B200SEG_IGEMM_NFAST=1, static striding only): n_tile as the fastest tile index
     int dy_min, dy_max, dx_min, dx_max, iters_all;   // extremes of the tap shifts; pipeline iterations of a tile none of whose taps is all padding
+    // Operand-role swap for launches with <= 64 output channels (layer1, the stem): D^T[k][pixel] = W[k][c] . X^T[c][pixel] —
+    // the weights are the M operand (64 real rows of 128, the rest zero-filled by the TMA unit), a 256-pixel patch the N
+    // operand, so one issued MMA does twice the useful work of the pixel-major form and the single-thread issue loops stop
+    // being the bound.  The accumulator is channel-per-lane, pixel-per-column; the epilogue transposes it through the
+    // staging slabs (one 128-pixel slab per half of the patch).  sub_dim / sub_len: the patch dimension (0 x, 1 y, 2 n)
+    // along which the patch splits into its two 128-pixel halves, and the half's extent there.
+    int swap, sub_dim, sub_len;
     FastDiv d_mt, d_tx, d_ty, d_tn;   // divisions by m_tiles, tiles_x, tiles_y, tiles_n in decode_tile
     int kpack;               // (tap, 64-channel block) operand pairs per pipeline stage: 2 when two fit a stage buffer
                              // (bn <= 64), else 1 — see the producer loop
@@ -216,7 +223,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
             // ------------------------------------------------------------ TMA producer
             int stage = 0;
             uint32_t phase = 0;
-            const uint32_t tx_bytes = kABytes + p.bn * kBK * 2;
+            const uint32_t tx_bytes = kABytes + (p.swap ? kMaxBN : p.bn) * kBK * 2;
             // This thread is also the CTA's TILE SCHEDULER.  The first tile is blockIdx.x; every later one comes from a
             // global counter (atomicAdd) instead of a static stride, so a CTA that starts late or runs on a shared SM
             // (weight-gradient kernels on the side stream, NCCL under data parallelism) simply takes fewer tiles instead
@@ -254,8 +261,13 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
                         for (int cb = 0; cb < seg.cblks; ++cb) {
                             if (sub == 0) mbar_wait(&empty[stage], phase ^ 1);
                             uint8_t* sa = smem + stage * kStageBytes + sub * tx_bytes;
-                            tma_load_4d(sa, &p.a_map[sg], &full[stage], cb * kBK, t.x0 + dx, t.y0 + dy, t.n0);
-                            tma_load_3d(sa + kABytes, &p.b_map[sg], &full[stage], cb * kBK, t.n_tile * p.bn, tap);
+                            if (p.swap) {       // M operand = 128 weight rows, N operand = the 256-pixel patch
+                                tma_load_3d(sa, &p.b_map[sg], &full[stage], cb * kBK, 0, tap);
+                                tma_load_4d(sa + kABytes, &p.a_map[sg], &full[stage], cb * kBK, t.x0 + dx, t.y0 + dy, t.n0);
+                            } else {
+                                tma_load_4d(sa, &p.a_map[sg], &full[stage], cb * kBK, t.x0 + dx, t.y0 + dy, t.n0);
+                                tma_load_3d(sa + kABytes, &p.b_map[sg], &full[stage], cb * kBK, t.n_tile * p.bn, tap);
+                            }
                             if (++sub == p.kpack) {
                                 mbar_arrive_expect_tx(&full[stage], sub * tx_bytes);
                                 sub = 0;
@@ -289,7 +301,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
     } else if (warp == 1) {
         if (lane == 0) {
             // ------------------------------------------------------------ MMA issuer
-            const uint32_t idesc = umma_idesc_bf16(kBM, p.bn, 0, 0);
+            const uint32_t idesc = umma_idesc_bf16(kBM, p.swap ? kMaxBN : p.bn, 0, 0);
             int stage = 0;
             uint32_t phase = 0;
             int lt = 0;
@@ -319,7 +331,7 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
                 mbar_wait(&tempty[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * kMaxBN;
-                const uint32_t pair_bytes = kABytes + p.bn * kBK * 2;
+                const uint32_t pair_bytes = kABytes + (p.swap ? kMaxBN : p.bn) * kBK * 2;
                 for (int it = 0; it < kiters; it += p.kpack) {
                     mbar_wait(&full[stage], phase);
                     tc_fence_after();
@@ -350,7 +362,93 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
         const int wl = row & (p.bw - 1);
         const int hl = (row >> p.lbw) & (p.bh - 1);
         const int il = row >> (p.lbw + p.lbh);
-        if (!p.out_fp32) {
+        if (!p.out_fp32 && p.swap) {
+            // ---- operand-role swap: TMEM lane = output channel, column = pixel of the 256-pixel patch.  Warps with
+            // q = 0 / 1 own channels 0-31 / 32-63; the warp pair (q = 0, 1) of each half h = 0 / 1 (warps 4, 5 / 8, 9)
+            // transposes pixels [128 h, 128 h + 128) into staging slab h and one of its lanes stores it; warps with
+            // q = 2 / 3 hold zero rows and only take part in the handshakes.
+            const int h = (warp - 4) >> 2;
+            const bool active = q < 2;
+            const int ch = q * 32 + lane;                       // this thread's output channel
+            const bool issuer = active && q == 0 && lane == 0;
+            float sc = 1.f, bi = 0.f;
+            if (active && ch < p.k_store) {
+                if (p.scale) sc = __ldg(p.scale + ch);
+                if (p.bias) bi = __ldg(p.bias + ch);
+            }
+            const bool affine = p.scale != nullptr || p.bias != nullptr || p.relu != 0;
+            float s1 = 0.f, s2 = 0.f;
+            uint8_t* buf = out_buf + h * kOutBufBytes;
+            // byte offset of this channel inside a 128-byte pixel row, before the row's swizzle
+            const int chunk = ch >> 3, within = (ch & 7) * 2;
+            int lt = 0;
+            int slot = 0;
+            uint32_t sphase = 0;
+            for (;; ++lt) {
+                mbar_wait(&sfull[slot], sphase);
+                const int tile = sched_tile[slot];
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sempty[slot]);
+                if (++slot == 2) {
+                    slot = 0;
+                    sphase ^= 1;
+                }
+                if (tile < 0) break;
+                const TileCoord t = decode_tile(p, tile);
+                const int acc = lt & 1;
+                const uint32_t acc_phase = (lt >> 1) & 1;
+                const bool border = (t.x0 + p.bw > p.W) || (t.y0 + p.bh > p.H) || (t.n0 + p.bi > p.N);
+                mbar_wait(&tfull[acc], acc_phase);
+                tc_fence_after();
+                if (active) {
+                    // the slab is free once the store issued for the previous tile has read it
+                    if (issuer) tma_store_wait_read<0>();
+                    named_bar_sync(3 + h, 64);
+                    const uint32_t taddr = tmem_base + acc * kMaxBN + (static_cast<uint32_t>(q * 32) << 16) + h * 128;
+#pragma unroll 1
+                    for (int j = 0; j < 4; ++j) {
+                        uint32_t v[32];
+                        tmem_ld_32x32(taddr + j * 32, v);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            const int r = j * 32 + i;                          // pixel row inside the slab
+                            float f = __uint_as_float(v[i]);
+                            if (affine) {
+                                f = fmaf(f, sc, bi);
+                                if (p.relu) f = fmaxf(f, 0.f);
+                            }
+                            if (border) {
+                                const int pr = h * 128 + r;                    // pixel inside the patch
+                                const int wl2 = pr & (p.bw - 1), hl2 = (pr >> p.lbw) & (p.bh - 1), il2 = pr >> (p.lbw + p.lbh);
+                                if (!((t.x0 + wl2 < p.W) && (t.y0 + hl2 < p.H) && (t.n0 + il2 < p.N))) f = 0.f;
+                            }
+                            const __nv_bfloat16 b = __float2bfloat16(f);
+                            *reinterpret_cast<__nv_bfloat16*>(buf + r * 128 + (((chunk ^ (r & 7)) << 4) | within)) = b;
+                            const float fr = __bfloat162float(b);            // statistics of the values as stored
+                            s1 += fr;
+                            s2 = fmaf(fr, fr, s2);
+                        }
+                    }
+                    fence_proxy_async();
+                    named_bar_sync(3 + h, 64);
+                    if (issuer) {
+                        const int off = h * p.sub_len;
+                        tma_store_4d(&p.y_map, buf, 0, t.x0 + (p.sub_dim == 0 ? off : 0), t.y0 + (p.sub_dim == 1 ? off : 0),
+                                     t.n0 + (p.sub_dim == 2 ? off : 0));
+                        tma_store_commit();
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tempty[acc]);
+            }
+            if (p.stats && active && ch < p.k_store) {
+                atomicAdd(p.stats + ch, s1);
+                atomicAdd(p.stats + p.k_store + ch, s2);
+            }
+            if (issuer) tma_store_wait_all<0>();
+        } else if (!p.out_fp32) {
             // bf16 output: TMEM -> registers -> (scale/bias/ReLU) -> 128-byte-swizzled shared-memory slab (64 channels
             // x 128 pixels) -> one TMA store per slab (the TMA unit clips pixels outside the image and channels
             // beyond the slice).  Eight warps: warp w reads TMEM lanes 32*(w%4).., warps 4-7 take the low 32 columns
@@ -705,13 +803,31 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
     p.bn = out->k <= 32 ? 32 : round_up(ceil_div(out->k, p.tiles_n), kOutSlab);
     B200SEG_CHECK(p.bn <= kMaxBN, "conv: internal bn %d", p.bn);
 
+    // operand-role swap (see IgemmParams::swap): narrow outputs over enough pixels to fill the GPU with 256-pixel patches
+    static const int swap_mode = [] {               // B200SEG_IGEMM_SWAP: 0 off, 1 (default) where it pays, 2 wherever legal (tests)
+        const char* e = getenv("B200SEG_IGEMM_SWAP");
+        return e ? atoi(e) : 1;
+    }();
+    {
+        int sms = gemm_sm_count();
+        if (sms <= 0) sms = 148;
+        // "where it pays": the transposing epilogue (four warps, 16-bit shared-memory stores) costs ~2 000 clk per 256-pixel
+        // patch, so the reduction has to be at least eight (tap, 64-channel block) pairs deep to hide it — 3x3 convs, not
+        // the 1x1 256 -> 64 ones (measured: 3x3 64->64 66.6 -> 56.5 us, 1x1 256->64 39.5 -> 51.8 us)
+        int depth = 0;
+        for (int i = 0; i < nseg; ++i) depth += p.seg[i].ntaps * p.seg[i].cblks;
+        p.swap = (swap_mode > 0 && out->k <= 64 && !out->out_fp32 && p.tiles_n == 1 &&
+                  (swap_mode > 1 || (depth >= 8 && static_cast<long long>(n) * h * w >= 256LL * sms))) ? 1 : 0;
+    }
+    const int patch_px = p.swap ? 256 : 128;
+
     // pixel patch: the power-of-two bw x bh x bi = 128 shape that needs the fewest pipeline iterations (memoised
     // per geometry: a training step repeats the same few)
     long long best = -1;
     {
         static std::mutex mu;
         static std::map<std::vector<int>, std::array<long long, 5>> memo;
-        std::vector<int> key = {n, h, w, nseg, p.no_skip};
+        std::vector<int> key = {n, h, w, nseg, p.no_skip, patch_px};
         for (int i = 0; i < nseg; ++i) {
             key.push_back(p.seg[i].ntaps);
             key.push_back(p.seg[i].cblks);
@@ -727,9 +843,9 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
             g_iters_run += it->second[3];
             g_iters_dense += it->second[4];
         } else {
-            for (int bi = 1; bi <= 128; bi *= 2) {
-                for (int bw = 1; bw * bi <= 128; bw *= 2) {
-                    const int bh = 128 / (bw * bi);
+            for (int bi = 1; bi <= patch_px; bi *= 2) {
+                for (int bw = 1; bw * bi <= patch_px; bw *= 2) {
+                    const int bh = patch_px / (bw * bi);
                     const long long c = patch_cost(n, h, w, bw, bh, bi, nseg, sp, no_skip);
                     if (best < 0 || c < best || (c == best && bw > p.bw)) {
                         best = c;
@@ -781,10 +897,18 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
         if (encode_tmap_bf16(&p.a_map[i], sp[i].a_base, 4, sp[i].adims, sp[i].astr, abox)) return 1;
         const uint64_t bdims[3] = {(uint64_t)sp[i].c, (uint64_t)sp[i].w_rows, (uint64_t)sp[i].w_taps};
         const uint64_t bstr[2] = {(uint64_t)sp[i].c * 2, (uint64_t)sp[i].w_rows * sp[i].c * 2};
-        const uint32_t bbox[3] = {kBK, (uint32_t)p.bn, 1};
+        const uint32_t bbox[3] = {kBK, (uint32_t)(p.swap ? kBM : p.bn), 1};      // swap: the weights are the M operand
         if (encode_tmap_bf16(&p.b_map[i], sp[i].w, 3, bdims, bstr, bbox)) return 1;
     }
-    if (!out->out_fp32) {
+    if (p.swap) {
+        // the two 128-pixel halves of the patch: split along its slowest dimension that has more than one element
+        uint32_t sb[3] = {(uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bi};
+        p.sub_dim = p.bi >= 2 ? 2 : (p.bh >= 2 ? 1 : 0);
+        sb[p.sub_dim] /= 2;
+        p.sub_len = static_cast<int>(sb[p.sub_dim]);
+        const uint32_t ybox[4] = {kOutSlab, sb[0], sb[1], sb[2]};
+        if (encode_tmap_bf16(&p.y_map, op.base, 4, op.dims, op.str, ybox)) return 1;
+    } else if (!out->out_fp32) {
         const uint32_t ybox[4] = {kOutSlab, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bi};
         if (encode_tmap_bf16(&p.y_map, op.base, 4, op.dims, op.str, ybox)) return 1;
     }
@@ -818,7 +942,7 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
         const char* e = getenv("B200SEG_IGEMM_KPACK");
         return !(e && e[0] == '0');
     }();
-    p.kpack = (kpack_on && 2 * (kABytes + p.bn * kBK * 2) <= kStageBytes) ? 2 : 1;
+    p.kpack = (kpack_on && !p.swap && 2 * (kABytes + p.bn * kBK * 2) <= kStageBytes) ? 2 : 1;
     B200SEG_CUDA(launch_pdl(igemm_kernel, grid, kThreads, kSmemBytes, st, p));
     return 0;
 }

@@ -46,6 +46,11 @@ CONV_CASES = [
     (4, 1, 1, 256, 256, 1, 1),
     (1, 40, 40, 128, 352, 3, 2),
     (2, 17, 23, 88, 8, 3, 1),
+    # <= 64 output channels over enough pixels: the operand-role swap of igemm_kernel (256-pixel patches, transposing
+    # epilogue), with a width that leaves border patches and a 32-channel output
+    (4, 128, 128, 64, 64, 3, 1),
+    (3, 128, 120, 256, 64, 1, 1),
+    (5, 100, 84, 64, 32, 3, 2),
     # dilated, one CTA per (tap, tile) already fills the GPU (the ASPP weight-gradient regime)
     (2, 32, 32, 2048, 256, 3, 12),
     (1, 32, 32, 1152, 128, 3, 18),
