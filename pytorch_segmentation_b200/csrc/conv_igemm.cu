@@ -379,8 +379,12 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
             const bool affine = p.scale != nullptr || p.bias != nullptr || p.relu != 0;
             float s1 = 0.f, s2 = 0.f;
             uint8_t* buf = out_buf + h * kOutBufBytes;
-            // byte offset of this channel inside a 128-byte pixel row, before the row's swizzle
+            // byte offset of this channel inside a 128-byte pixel row, for each of the eight swizzle phases (row & 7)
             const int chunk = ch >> 3, within = (ch & 7) * 2;
+            int sw_off[8];
+#pragma unroll
+            for (int m = 0; m < 8; ++m) sw_off[m] = ((chunk ^ m) << 4) | within;
+            const bool want_stats = p.stats != nullptr;
             int lt = 0;
             int slot = 0;
             uint32_t sphase = 0;
@@ -410,24 +414,34 @@ __global__ void __launch_bounds__(kThreads, 1) igemm_kernel(const __grid_constan
                         uint32_t v[32];
                         tmem_ld_32x32(taddr + j * 32, v);
                         tmem_ld_wait();
+                        uint8_t* rows = buf + j * 32 * 128;
+                        if (affine || border) {                                // the uncommon forms, element by element
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) {
-                            const int r = j * 32 + i;                          // pixel row inside the slab
-                            float f = __uint_as_float(v[i]);
-                            if (affine) {
-                                f = fmaf(f, sc, bi);
-                                if (p.relu) f = fmaxf(f, 0.f);
+                            for (int i = 0; i < 32; ++i) {
+                                float f = __uint_as_float(v[i]);
+                                if (affine) {
+                                    f = fmaf(f, sc, bi);
+                                    if (p.relu) f = fmaxf(f, 0.f);
+                                }
+                                if (border) {
+                                    const int pr = h * 128 + j * 32 + i;       // pixel inside the patch
+                                    const int wl2 = pr & (p.bw - 1), hl2 = (pr >> p.lbw) & (p.bh - 1), il2 = pr >> (p.lbw + p.lbh);
+                                    if (!((t.x0 + wl2 < p.W) && (t.y0 + hl2 < p.H) && (t.n0 + il2 < p.N))) f = 0.f;
+                                }
+                                v[i] = __float_as_uint(f);
                             }
-                            if (border) {
-                                const int pr = h * 128 + r;                    // pixel inside the patch
-                                const int wl2 = pr & (p.bw - 1), hl2 = (pr >> p.lbw) & (p.bh - 1), il2 = pr >> (p.lbw + p.lbh);
-                                if (!((t.x0 + wl2 < p.W) && (t.y0 + hl2 < p.H) && (t.n0 + il2 < p.N))) f = 0.f;
+                        }
+                        // two pixels per conversion; 16-bit stores at precomputed swizzled offsets (i & 7 is static)
+#pragma unroll
+                        for (int i = 0; i < 32; i += 2) {
+                            const uint32_t pk = pack_bf16x2(__uint_as_float(v[i]), __uint_as_float(v[i + 1]));
+                            *reinterpret_cast<uint16_t*>(rows + i * 128 + sw_off[i & 7]) = static_cast<uint16_t>(pk & 0xffffu);
+                            *reinterpret_cast<uint16_t*>(rows + (i + 1) * 128 + sw_off[(i + 1) & 7]) = static_cast<uint16_t>(pk >> 16);
+                            if (want_stats) {                                  // of the values as stored
+                                const float f0 = __uint_as_float(pk << 16), f1 = __uint_as_float(pk & 0xffff0000u);
+                                s1 += f0 + f1;
+                                s2 = fmaf(f0, f0, fmaf(f1, f1, s2));
                             }
-                            const __nv_bfloat16 b = __float2bfloat16(f);
-                            *reinterpret_cast<__nv_bfloat16*>(buf + r * 128 + (((chunk ^ (r & 7)) << 4) | within)) = b;
-                            const float fr = __bfloat162float(b);            // statistics of the values as stored
-                            s1 += fr;
-                            s2 = fmaf(fr, fr, s2);
                         }
                     }
                     fence_proxy_async();
@@ -811,13 +825,17 @@ int launch_planned(int n, int h, int w, int nseg, const SegPlan* sp, const OutPl
     {
         int sms = gemm_sm_count();
         if (sms <= 0) sms = 148;
-        // "where it pays": the transposing epilogue (four warps, 16-bit shared-memory stores) costs ~2 000 clk per 256-pixel
-        // patch, so the reduction has to be at least eight (tap, 64-channel block) pairs deep to hide it — 3x3 convs, not
-        // the 1x1 256 -> 64 ones (measured: 3x3 64->64 66.6 -> 56.5 us, 1x1 256->64 39.5 -> 51.8 us)
+        // "where it pays": the transposing epilogue (four warps, 16-bit shared-memory stores) has to hide under the
+        // reduction of the patch — at least four (tap, 64-channel block) pairs (measured: 3x3 64->64 66.6 -> 50.2 us,
+        // its dgrad 64.5 -> 46.3 us, 1x1 256->64 37.9 -> 35.8 us; B200SEG_IGEMM_SWAP_DEPTH)
+        static const int min_depth = [] {
+            const char* e = getenv("B200SEG_IGEMM_SWAP_DEPTH");
+            return e ? atoi(e) : 4;
+        }();
         int depth = 0;
         for (int i = 0; i < nseg; ++i) depth += p.seg[i].ntaps * p.seg[i].cblks;
         p.swap = (swap_mode > 0 && out->k <= 64 && !out->out_fp32 && p.tiles_n == 1 &&
-                  (swap_mode > 1 || (depth >= 8 && static_cast<long long>(n) * h * w >= 256LL * sms))) ? 1 : 0;
+                  (swap_mode > 1 || (depth >= min_depth && static_cast<long long>(n) * h * w >= 256LL * sms))) ? 1 : 0;
     }
     const int patch_px = p.swap ? 256 : 128;
 
